@@ -1,0 +1,160 @@
+"""Generate the pinned vectors under tests/golden/ from the UNMODIFIED reference (container only).
+
+TEST INFRASTRUCTURE.  Run:  python -m oracle.make_golden [t3] [cfm] [hift]
+
+The reference modules are imported from /root/reference through `oracle/ref_import.py`, loaded
+with the synthetic state dicts of `chatterbox_b200/synthetic.py`, and driven through their own
+public entry points:
+  * T3: `T3.inference` itself (t3.py:203-371).  Its only stochastic call, `torch.multinomial`
+    (t3.py:341), is swapped for argmax (greedy) or for the next teacher-forced id while the call
+    runs; raw logits are captured with a forward hook on `speech_head`.
+  * CFM / HiFT: see the later sections of this file.
+Every vector is also compared with the CPU restatement in `oracle/*.py` before it is written, so
+a committed fixture certifies reference == restatement at generation time.
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+import sys
+import time
+
+import torch
+from safetensors.torch import save_file
+
+from chatterbox_b200 import synthetic as S
+from oracle import ref_import as R
+from oracle import t3_oracle as T3O
+
+GOLD = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+T3_LOGIT_STEPS = [0, 1, 2, 3, 7, 15, 31, 47]
+T3_GREEDY_N = 48
+T3_FORCED_N = 24
+T3_FORCED_STEPS = [0, 5, 23]
+
+
+@contextlib.contextmanager
+def _patched_multinomial(fn):
+    orig = torch.multinomial
+    torch.multinomial = fn
+    try:
+        yield
+    finally:
+        torch.multinomial = orig
+
+
+def _ref_t3_run(t3, cond_fields, text2, n, forced=None, **kw):
+    """Run the reference T3.inference greedy / teacher-forced; return tokens, raw logits per step."""
+    from chatterbox.models.t3.modules.cond_enc import T3Cond
+    raw, step = [], [0]
+    hook = t3.speech_head.register_forward_hook(lambda m, i, o: raw.append(o[:, -1].detach().clone()))
+
+    def pick(probs, num_samples=1):
+        i = step[0]
+        step[0] += 1
+        if forced is not None:
+            return forced[:, i:i + 1].clone()
+        return probs.argmax(dim=-1, keepdim=True)
+
+    cond = T3Cond(**{k: v.clone() for k, v in cond_fields.items()})
+    with _patched_multinomial(pick):
+        toks = t3.inference(t3_cond=cond, text_tokens=text2, max_new_tokens=n, **kw)
+    hook.remove()
+    return toks, torch.stack(raw[:toks.shape[1]])
+
+
+def make_t3():
+    torch.manual_seed(0)
+    t0 = time.time()
+    sd = S.make_state_dict("t3")
+    t3 = R.build_t3()
+    t3.load_state_dict(sd)
+    print(f"[t3] reference built + synthetic weights loaded in {time.time() - t0:.1f}s")
+    cond = S.t3_cond()
+    text = S.text_tokens()
+    text2 = torch.cat([text, text], 0)
+    params = dict(cfg_weight=0.5, temperature=0.8, repetition_penalty=1.2, min_p=0.05, top_p=1.0)
+    out = {}
+
+    # conditioning prefix and prefill embeddings: reference vs restatement
+    from chatterbox.models.t3.modules.cond_enc import T3Cond
+    with torch.inference_mode():
+        ref_emb, len_cond = t3.prepare_input_embeds(
+            t3_cond=T3Cond(**{k: v.clone() for k, v in cond.items()}), text_tokens=text2,
+            speech_tokens=T3O.START_SPEECH * torch.ones_like(text2[:, :1]), cfg_weight=0.5)
+    my_emb = T3O.prepare_input_embeds(sd, cond, text2, 0.5)
+    assert len_cond == 34
+    d = (ref_emb - my_emb[:, :-1]).abs().max().item()
+    print(f"[t3] prepare_input_embeds max-abs diff restatement vs reference: {d:.3e}")
+    assert d < 1e-4
+    out["cond_emb"] = ref_emb[0, :34].clone()
+    out["embeds_row1_text0"] = ref_emb[1, 34:36].clone()
+
+    # greedy
+    t0 = time.time()
+    toks, raw = _ref_t3_run(t3, cond, text2, T3_GREEDY_N, **params)
+    print(f"[t3] reference greedy {toks.shape[1]} tokens in {time.time() - t0:.1f}s: {toks[0, :12].tolist()}")
+    my_toks, my_raw = T3O.inference(sd, cond, text2, max_new_tokens=T3_GREEDY_N, **params)
+    assert torch.equal(toks, my_toks), (toks, my_toks)
+    d = (raw - my_raw).abs().max().item()
+    print(f"[t3] greedy tokens identical; raw logits max-abs diff {d:.3e}")
+    assert d < 2e-3
+    # top-2 gap of the processed logits along the greedy path
+    gaps = []
+    gen = torch.tensor([[T3O.START_SPEECH]])
+    for i in range(toks.shape[1]):
+        p = T3O.process_logits(raw[i], gen, **params)
+        top2 = p.topk(2, dim=-1).values[0]
+        gaps.append(float(top2[0] - top2[1]))
+        gen = torch.cat([gen, toks[:, i:i + 1]], 1)
+    print(f"[t3] min top-2 gap along greedy path: {min(gaps):.4e}")
+    out["greedy_tokens"] = toks[0].to(torch.int32)
+    out["greedy_logit_steps"] = torch.tensor(T3_LOGIT_STEPS, dtype=torch.int32)
+    out["greedy_logits"] = raw[T3_LOGIT_STEPS].clone()
+    out["greedy_top2_gaps"] = torch.tensor(gaps)
+
+    # teacher-forced
+    g = torch.Generator().manual_seed(77)
+    forced = torch.randint(0, 6561, (1, T3_FORCED_N), generator=g)
+    toks_f, raw_f = _ref_t3_run(t3, cond, text2, T3_FORCED_N, forced=forced, **params)
+    assert torch.equal(toks_f, forced)
+    _, my_raw_f = T3O.inference(sd, cond, text2, max_new_tokens=T3_FORCED_N, forced_tokens=forced, **params)
+    d = (raw_f - my_raw_f).abs().max().item()
+    print(f"[t3] teacher-forced raw logits max-abs diff {d:.3e}")
+    assert d < 2e-3
+    out["forced_tokens"] = forced[0].to(torch.int32)
+    out["forced_logit_steps"] = torch.tensor(T3_FORCED_STEPS, dtype=torch.int32)
+    out["forced_logits"] = raw_f[T3_FORCED_STEPS].clone()
+
+    # logits processors alone (HF objects as t3.py:302-304 builds them), non-default top_p
+    from transformers.generation.logits_process import (MinPLogitsWarper, RepetitionPenaltyLogitsProcessor,
+                                                        TopPLogitsWarper)
+    lg = raw[3]
+    ids = torch.cat([torch.tensor([[T3O.START_SPEECH]]), toks[:, :3]], 1)
+    c = lg[0:1] + 0.5 * (lg[0:1] - lg[1:2])
+    c = c / 0.8
+    c = RepetitionPenaltyLogitsProcessor(penalty=1.3)(ids, c)
+    c = MinPLogitsWarper(min_p=0.02)(None, c)
+    c = TopPLogitsWarper(top_p=0.9)(None, c)
+    mine = T3O.process_logits(lg, ids, cfg_weight=0.5, temperature=0.8, repetition_penalty=1.3, min_p=0.02, top_p=0.9)
+    assert torch.equal(torch.isinf(c), torch.isinf(mine))
+    fin = ~torch.isinf(c)
+    assert (c[fin] - mine[fin]).abs().max() < 1e-5
+    print(f"[t3] processors: {int(fin.sum())} tokens kept of {c.numel()}")
+    out["proc_in_logits"] = lg.clone()
+    out["proc_ids"] = ids[0].to(torch.int32)
+    out["proc_out"] = c.clone()
+
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(GOLD, "t3_golden.safetensors"))
+    print("[t3] wrote tests/golden/t3_golden.safetensors")
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["t3", "cfm", "hift"]
+    torch.set_num_threads(os.cpu_count() or 8)
+    if "t3" in which:
+        make_t3()
+    if "cfm" in which and "make_cfm" in globals():
+        globals()["make_cfm"]()
+    if "hift" in which and "make_hift" in globals():
+        globals()["make_hift"]()
