@@ -1,0 +1,66 @@
+"""ctypes binding of the C-ABI library (include/cbx.h).  Fails loudly: there is no fallback path."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libcbx.so")
+
+
+class CbxError(RuntimeError):
+    pass
+
+
+class CbxT3Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("n_layers", C.c_int32), ("max_pos", C.c_int32), ("kv_fp32", C.c_int32)]
+
+
+class CbxT3Weights(C.Structure):
+    _fields_ = [("wstream", C.c_void_p), ("stride_units", C.c_int64), ("ln1", C.c_void_p), ("ln2", C.c_void_p),
+                ("final_norm", C.c_void_p), ("speech_emb", C.c_void_p), ("speech_pos_emb", C.c_void_p),
+                ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p)]
+
+
+class CbxSampleParams(C.Structure):
+    _fields_ = [("cfg_weight", C.c_float), ("temperature", C.c_float), ("repetition_penalty", C.c_float),
+                ("min_p", C.c_float), ("top_p", C.c_float), ("greedy", C.c_int32), ("stop_on_eos", C.c_int32),
+                ("seed", C.c_uint64)]
+
+
+# every symbol include/cbx.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "cbx_last_error": (C.c_char_p, []),
+    "cbx_version": (C.c_int, []),
+    "cbx_t3_grid": (C.c_int, [C.c_int]),
+    "cbx_t3_plan_count": (C.c_int, [C.c_int, C.c_int, C.c_int]),
+    "cbx_t3_plan_unit": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
+    "cbx_t3_create": (C.c_int, [C.POINTER(CbxT3Config), C.POINTER(CbxT3Weights), C.POINTER(C.c_void_p)]),
+    "cbx_t3_destroy": (C.c_int, [C.c_void_p]),
+    "cbx_t3_prefill": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "cbx_t3_decode": (C.c_int, [C.c_void_p, C.POINTER(CbxSampleParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                C.c_void_p, C.c_void_p]),
+    "cbx_t3_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                               C.POINTER(C.c_int64)]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libcbx.so (built in-tree by chatterbox_b200/build.py)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise CbxError(f"{LIB_PATH} is missing: run `python -m chatterbox_b200.build` "
+                           "(chatterbox_b200 has no CPU or PyTorch fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(_lib, name)
+            fn.restype, fn.argtypes = res, args
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise CbxError(lib().cbx_last_error().decode())

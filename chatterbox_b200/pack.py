@@ -1,0 +1,123 @@
+"""One-time weight pre-pack for the T3 decode megakernel (fp32 state dict -> bf16 per-CTA streams).
+
+The kernel's TMA producer walks ONE contiguous byte stream per CTA, in the order the static plan
+(`csrc/t3_plan.h`, exported as `cbx_t3_plan_count/unit`) says that CTA consumes 16 KB units.  A
+unit is 8 weight rows x 1024 k in bf16, stored in MMA B-fragment order [k32-block j][row g][32 k],
+so a consumer warp's 128-bit shared-memory reads are contiguous and conflict-free.
+
+State-dict keys are the reference's (`T3.state_dict()`, src/chatterbox/models/t3/t3.py:41-65).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List
+
+import torch
+
+from . import _lib
+
+H, INTER, VOCAB, UNIT_ELEMS = 1024, 4096, 8194, 8192
+PH_QKV, PH_O, PH_GU, PH_DOWN, PH_HEAD = range(5)
+PHASE_UNITS = (384, 128, 1024, 512, 1025)
+
+
+def plan_lists(G: int) -> List[List[List[int]]]:
+    """plan[c][ph] = unit ids CTA c consumes in phase ph, in order (from the C plan)."""
+    l = _lib.lib()
+    return [[[l.cbx_t3_plan_unit(ph, c, G, j) for j in range(l.cbx_t3_plan_count(ph, c, G))]
+             for ph in range(5)] for c in range(G)]
+
+
+def _frag_order(units: torch.Tensor) -> torch.Tensor:
+    """[U, 8 rows, 1024 k] -> [U, 8192] in [j (32)][g (8)][32 k] order."""
+    U = units.shape[0]
+    return units.reshape(U, 8, 32, 32).permute(0, 2, 1, 3).reshape(U, UNIT_ELEMS)
+
+
+def layer_units(sd: Dict[str, torch.Tensor], i: int, dev) -> torch.Tensor:
+    """All 2048 units of decoder layer i in phase order (qkv | o | gate-up | down): [2048, 8192] bf16."""
+    p = f"tfmr.layers.{i}."
+    g = lambda n: sd[p + n].to(dev, torch.float32)
+    qkv = torch.cat([g("self_attn.q_proj.weight"), g("self_attn.k_proj.weight"), g("self_attn.v_proj.weight")], 0)
+    a = qkv.reshape(384, 8, H)
+    c = g("self_attn.o_proj.weight").reshape(128, 8, H)
+    gate = g("mlp.gate_proj.weight").reshape(1024, 4, H)
+    up = g("mlp.up_proj.weight").reshape(1024, 4, H)
+    d = torch.cat([gate, up], 1)                                   # unit u: gate rows 4u..4u+3, up rows 4u..4u+3
+    wd = g("mlp.down_proj.weight").reshape(128, 8, 4, 1024)        # [r][row][s][k]
+    e = wd.permute(0, 2, 1, 3).reshape(512, 8, 1024)               # unit u = r*4 + s
+    return _frag_order(torch.cat([a, c, d, e], 0)).to(torch.bfloat16)
+
+
+def head_units(sd: Dict[str, torch.Tensor], dev) -> torch.Tensor:
+    w = sd["speech_head.weight"].to(dev, torch.float32)
+    w = torch.cat([w, torch.zeros(8200 - VOCAB, H, device=dev)], 0)
+    return _frag_order(w.reshape(1025, 8, H)).to(torch.bfloat16)
+
+
+def rope_tables(max_pos: int, dev) -> (torch.Tensor, torch.Tensor):
+    """cos/sin [max_pos][32] fp32 of the llama3-scaled RoPE the reference configures
+    (llama_configs.py:22-30: theta 5e5, factor 8, low/high 1/4, original ctx 8192), computed in
+    fp32 exactly as HF `_compute_llama3_parameters` + `LlamaRotaryEmbedding.forward` do."""
+    theta, factor, low_f, high_f, old_ctx, hd = 500000.0, 8.0, 1.0, 4.0, 8192, 64
+    inv = 1.0 / (theta ** (torch.arange(0, hd, 2, dtype=torch.int64).to(torch.float) / hd))
+    low_wl, high_wl = old_ctx / low_f, old_ctx / high_f
+    wl = 2 * math.pi / inv
+    inv_l = torch.where(wl > low_wl, inv / factor, inv)
+    smooth = (old_ctx / wl - low_f) / (high_f - low_f)
+    smoothed = (1 - smooth) * inv_l / factor + smooth * inv_l
+    medium = ~(wl < high_wl) * ~(wl > low_wl)
+    inv = torch.where(medium, smoothed, inv_l)
+    fr = torch.arange(max_pos, dtype=torch.float32)[:, None] * inv[None, :]
+    return fr.cos().contiguous().to(dev), fr.sin().contiguous().to(dev)
+
+
+@dataclass
+class T3Packed:
+    G: int
+    n_layers: int
+    stride_units: int
+    wstream: torch.Tensor       # [G, stride_units, 8192] bf16
+    ln1: torch.Tensor
+    ln2: torch.Tensor
+    final_norm: torch.Tensor
+    speech_emb: torch.Tensor
+    speech_pos_emb: torch.Tensor
+    rope_cos: torch.Tensor
+    rope_sin: torch.Tensor
+    max_pos: int
+
+    def weight_bytes_per_step(self) -> int:
+        """Algorithmic weight bytes one decode step streams (every unit once + norms)."""
+        return (self.n_layers * 2048 + 1025) * UNIT_ELEMS * 2 + (2 * self.n_layers + 1) * H * 4
+
+
+def pack_t3(sd: Dict[str, torch.Tensor], G: int, device, max_pos: int, n_layers: int = 30) -> T3Packed:
+    dev = torch.device(device)
+    plan = plan_lists(G)
+    offs = [0, 384, 384 + 128, 384 + 128 + 1024]
+    layer_idx = [torch.tensor([offs[ph] + u for ph in range(4) for u in plan[c][ph]], dtype=torch.long, device=dev)
+                 for c in range(G)]
+    head_idx = [torch.tensor(plan[c][PH_HEAD], dtype=torch.long, device=dev) for c in range(G)]
+    lens = [n_layers * len(layer_idx[c]) + len(head_idx[c]) for c in range(G)]
+    stride = max(lens)
+    stream = torch.zeros(G, stride, UNIT_ELEMS, dtype=torch.bfloat16, device=dev)
+    hu = head_units(sd, dev)
+    for i in range(n_layers):
+        lu = layer_units(sd, i, dev)
+        for c in range(G):
+            n = len(layer_idx[c])
+            stream[c, i * n:(i + 1) * n] = lu[layer_idx[c]]
+        del lu
+    for c in range(G):
+        n = n_layers * len(layer_idx[c])
+        stream[c, n:n + len(head_idx[c])] = hu[head_idx[c]]
+    f32 = lambda t: t.to(dev, torch.float32).contiguous()
+    ln1 = torch.stack([f32(sd[f"tfmr.layers.{i}.input_layernorm.weight"]) for i in range(n_layers)])
+    ln2 = torch.stack([f32(sd[f"tfmr.layers.{i}.post_attention_layernorm.weight"]) for i in range(n_layers)])
+    cos, sin = rope_tables(max_pos, dev)
+    return T3Packed(G=G, n_layers=n_layers, stride_units=stride, wstream=stream, ln1=ln1.contiguous(),
+                    ln2=ln2.contiguous(), final_norm=f32(sd["tfmr.norm.weight"]),
+                    speech_emb=f32(sd["speech_emb.weight"]), speech_pos_emb=f32(sd["speech_pos_emb.emb.weight"]),
+                    rope_cos=cos, rope_sin=sin, max_pos=max_pos)

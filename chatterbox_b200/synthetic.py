@@ -261,7 +261,12 @@ def init_tensor(family: str, key: str, shape, seed: int) -> torch.Tensor:
             return 1.0 + 0.1 * r
         if last == "bias":
             return 0.02 * r
-        return 0.02 * r
+        w = 0.02 * r
+        if key == "speech_head.weight" or (key.startswith("tfmr.layers.") and key.endswith("_proj.weight")):
+            # the streamed matrices are made bf16-representable, so the reference (fp32 math) and the
+            # build (bf16 storage, fp32 accumulate) run on IDENTICAL weights
+            w = w.to(torch.bfloat16).to(torch.float32)
+        return w
     if family == "flow":
         if key == "input_embedding.weight":
             return r

@@ -1,0 +1,220 @@
+"""Host-side mirror of the reference `T3` (src/chatterbox/models/t3/t3.py:31-371) over the C-ABI.
+
+Same constructor state (reference state-dict keys), same `inference(...)` signature and return
+value; the 30-layer backbone, logit processing, sampling and the decode loop run inside
+`libcbx.so` (csrc/t3_decode.cu).  The once-per-utterance conditioning front-end
+(`T3CondEnc`/`Perceiver`/embedding gathers, t3.py:71-108) is plain PyTorch on the device — SURVEY.md
+§8f lists it as a "next" row.  There is no CPU path: construction fails without CUDA + libcbx.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from .pack import T3Packed, pack_t3
+
+
+class T3Config:
+    """reference t3/modules/t3_config.py:4-27"""
+    start_text_token = 255
+    stop_text_token = 0
+    text_tokens_dict_size = 704
+    max_text_tokens = 2048
+    start_speech_token = 6561
+    stop_speech_token = 6562
+    speech_tokens_dict_size = 8194
+    max_speech_tokens = 4096
+    llama_config_name = "Llama_520M"
+    input_pos_emb = "learned"
+    speech_cond_prompt_len = 150
+    encoder_type = "voice_encoder"
+    speaker_embed_size = 256
+    use_perceiver_resampler = True
+    emotion_adv = True
+    n_channels = 1024
+
+
+@dataclass
+class T3Cond:
+    """reference t3/modules/cond_enc.py:11-38"""
+    speaker_emb: torch.Tensor
+    clap_emb: Optional[torch.Tensor] = None
+    cond_prompt_speech_tokens: Optional[torch.Tensor] = None
+    cond_prompt_speech_emb: Optional[torch.Tensor] = None
+    emotion_adv: Optional[torch.Tensor] = 0.5
+
+    def to(self, *, device=None, dtype=None):
+        for k, v in self.__dict__.items():
+            if torch.is_tensor(v):
+                is_fp = type(v.view(-1)[0].item()) is not int
+                setattr(self, k, v.to(device=device, dtype=dtype if is_fp else None))
+        return self
+
+    def save(self, fpath):
+        torch.save(self.__dict__, fpath)
+
+    @staticmethod
+    def load(fpath, map_location="cpu"):
+        return T3Cond(**torch.load(fpath, map_location=map_location, weights_only=True))
+
+
+def _ensure_BOT_EOT(text_tokens: torch.Tensor, hp):
+    B = text_tokens.size(0)
+    assert (text_tokens == hp.start_text_token).int().sum() >= B, "missing start_text_token"
+    assert (text_tokens == hp.stop_text_token).int().sum() >= B, "missing stop_text_token"
+
+
+class T3:
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", *, max_pos: int = 4096,
+                 kv_fp32: bool = False, n_layers: int = 30, hp=T3Config()):
+        if not torch.cuda.is_available():
+            raise _lib.CbxError("chatterbox_b200.T3 needs a CUDA device (no CPU fallback)")
+        self.hp = hp
+        self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.dim = 1024
+        self._lib = _lib.lib()
+        G = self._lib.cbx_t3_grid(self.device.index)
+        if G <= 0:
+            _lib.check(1)
+        self.packed: T3Packed = pack_t3(state_dict, G, self.device, max_pos, n_layers)
+        # front-end parameters (reference key names), fp32 on the device
+        keep = ("cond_enc.", "text_emb.", "text_pos_emb.")
+        self.fe = {k: v.to(self.device, torch.float32) for k, v in state_dict.items() if k.startswith(keep)}
+        self.fe["speech_emb.weight"] = self.packed.speech_emb
+        self.fe["speech_pos_emb.emb.weight"] = self.packed.speech_pos_emb
+        p = self.packed
+        cfg = _lib.CbxT3Config(self.device.index, n_layers, max_pos, 1 if kv_fp32 else 0)
+        w = _lib.CbxT3Weights(p.wstream.data_ptr(), p.stride_units, p.ln1.data_ptr(), p.ln2.data_ptr(),
+                              p.final_norm.data_ptr(), p.speech_emb.data_ptr(), p.speech_pos_emb.data_ptr(),
+                              p.rope_cos.data_ptr(), p.rope_sin.data_ptr())
+        h = C.c_void_p()
+        _lib.check(self._lib.cbx_t3_create(C.byref(cfg), C.byref(w), C.byref(h)))
+        self._h = h
+        self.max_pos = max_pos
+        self.last_logits: Optional[torch.Tensor] = None
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self._lib.cbx_t3_destroy(h)
+            self._h = None
+
+    # ---- conditioning front-end (t3.py:71-108, cond_enc.py:64-97, perceiver.py:113-212) ----
+    def _attn_block2(self, x1, x2):
+        fe, pfx = self.fe, "cond_enc.perceiver.attn."
+        lin = lambda n, x: F.linear(x, fe[pfx + n + ".weight"], fe[pfx + n + ".bias"])
+        x1n = F.layer_norm(x1, (1024,), fe[pfx + "norm.weight"], fe[pfx + "norm.bias"])
+        x2n = F.layer_norm(x2, (1024,), fe[pfx + "norm.weight"], fe[pfx + "norm.bias"])
+        sp = lambda t: t.view(t.shape[0], t.shape[1], 4, 256).permute(0, 2, 1, 3)
+        o = F.scaled_dot_product_attention(sp(lin("to_q", x1n)), sp(lin("to_k", x2n)), sp(lin("to_v", x2n)))
+        o = o.permute(0, 2, 1, 3).contiguous().view(x1.shape[0], x1.shape[1], 1024)
+        return x1 + lin("proj_out", o)
+
+    def prepare_conditioning(self, t3_cond: T3Cond) -> torch.Tensor:
+        fe = self.fe
+        if t3_cond.cond_prompt_speech_tokens is not None and t3_cond.cond_prompt_speech_emb is None:
+            toks = t3_cond.cond_prompt_speech_tokens
+            t3_cond.cond_prompt_speech_emb = fe["speech_emb.weight"][toks] + \
+                fe["speech_pos_emb.emb.weight"][: toks.shape[1]][None]
+        assert (t3_cond.cond_prompt_speech_tokens is None) == (t3_cond.cond_prompt_speech_emb is None), \
+            "no embeddings for cond_prompt_speech_tokens"
+        spk = F.linear(t3_cond.speaker_emb.view(-1, 256), fe["cond_enc.spkr_enc.weight"], fe["cond_enc.spkr_enc.bias"])[:, None]
+        empty = torch.zeros_like(spk[:, :0])
+        assert t3_cond.clap_emb is None, "clap_embed not implemented"
+        pe = t3_cond.cond_prompt_speech_emb
+        if pe is None:
+            pe = empty
+        else:
+            q = fe["cond_enc.perceiver.pre_attention_query"].expand(pe.shape[0], -1, -1)
+            pre = self._attn_block2(q, pe)
+            pe = self._attn_block2(pre, pre)
+        assert t3_cond.emotion_adv is not None
+        emo = F.linear(t3_cond.emotion_adv.view(-1, 1, 1), fe["cond_enc.emotion_adv_fc.weight"])
+        return torch.cat((spk, empty, pe, emo), dim=1)
+
+    def prepare_input_embeds(self, *, t3_cond: T3Cond, text_tokens, speech_tokens, cfg_weight: float = 0.0):
+        fe = self.fe
+        cond_emb = self.prepare_conditioning(t3_cond)
+        text_emb = fe["text_emb.weight"][text_tokens].clone()
+        if cfg_weight > 0.0:
+            text_emb[1].zero_()
+        speech_emb = fe["speech_emb.weight"][speech_tokens]
+        text_emb = text_emb + fe["text_pos_emb.emb.weight"][: text_tokens.shape[1]][None]
+        speech_emb = speech_emb + fe["speech_pos_emb.emb.weight"][: speech_tokens.shape[1]][None]
+        len_cond = cond_emb.size(1)
+        if cond_emb.size(0) != text_emb.size(0):
+            cond_emb = cond_emb.expand(text_emb.size(0), -1, -1)
+        embeds = torch.cat((cond_emb, text_emb, speech_emb), dim=1)
+        return embeds, len_cond
+
+    # ---- the decode path ----
+    @torch.inference_mode()
+    def inference(self, *, t3_cond: T3Cond, text_tokens: torch.Tensor, initial_speech_tokens=None,
+                  prepend_prompt_speech_tokens=None, num_return_sequences=1, max_new_tokens=None,
+                  stop_on_eos=True, do_sample=True, temperature=0.8, min_p=0.05, top_p=1.00,
+                  length_penalty=1.0, repetition_penalty=1.2, cfg_weight=0,
+                  forced_tokens: Optional[torch.Tensor] = None, return_logits: bool = False,
+                  seed: Optional[int] = None):
+        """Reference signature (t3.py:203-225) plus three keyword extensions used by the parity tests:
+        `forced_tokens` (teacher forcing), `return_logits` (keep raw per-step logits in
+        `self.last_logits`), `seed` (Philox seed).  `do_sample=False` selects greedy argmax (the
+        reference ignores the flag and always samples)."""
+        assert prepend_prompt_speech_tokens is None, "not implemented"
+        _ensure_BOT_EOT(text_tokens, self.hp)
+        text_tokens = torch.atleast_2d(text_tokens).to(dtype=torch.long, device=self.device)
+        if initial_speech_tokens is None:
+            initial_speech_tokens = self.hp.start_speech_token * torch.ones_like(text_tokens[:, :1])
+        embeds, _ = self.prepare_input_embeds(t3_cond=t3_cond, text_tokens=text_tokens,
+                                              speech_tokens=initial_speech_tokens, cfg_weight=cfg_weight)
+        bos = (self.fe["speech_emb.weight"][self.hp.start_speech_token] +
+               self.fe["speech_pos_emb.emb.weight"][0])[None, None]
+        if cfg_weight > 0:   # the reference appends BOS a second time (t3.py:284-295)
+            embeds = torch.cat([embeds, bos.expand(embeds.shape[0], -1, -1)], dim=1)
+        embeds = embeds.contiguous().float()
+        B, P, _ = embeds.shape
+        assert B in (1, 2), "T3.inference runs one utterance (optionally as a CFG pair)"
+        if max_new_tokens is None:
+            max_new_tokens = self.hp.max_speech_tokens
+        max_new_tokens = int(max_new_tokens)
+        if P + max_new_tokens > self.max_pos:
+            raise ValueError(f"context {P}+{max_new_tokens} exceeds the KV slab (max_pos={self.max_pos})")
+        if max_new_tokens + 1 > self.packed.speech_pos_emb.shape[0]:
+            raise ValueError("max_new_tokens exceeds the learned speech position table")
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        tokens = torch.zeros(max_new_tokens, dtype=torch.int32, device=self.device)
+        n_out = torch.zeros(1, dtype=torch.int32, device=self.device)
+        logits = torch.empty(max_new_tokens, B, 8194, dtype=torch.float32, device=self.device) if return_logits else None
+        forced = None
+        if forced_tokens is not None:
+            forced = forced_tokens.reshape(-1).to(device=self.device, dtype=torch.int32).contiguous()
+            assert forced.numel() >= max_new_tokens
+        sp = _lib.CbxSampleParams(float(cfg_weight), float(temperature), float(repetition_penalty), float(min_p),
+                                  float(top_p), 0 if do_sample else 1, 1 if stop_on_eos else 0,
+                                  int(seed if seed is not None else torch.initial_seed()) & (2 ** 64 - 1))
+        _lib.check(self._lib.cbx_t3_prefill(self._h, embeds.data_ptr(), B, P, stream))
+        _lib.check(self._lib.cbx_t3_decode(self._h, C.byref(sp), max_new_tokens,
+                                           forced.data_ptr() if forced is not None else None,
+                                           tokens.data_ptr(), n_out.data_ptr(),
+                                           logits.data_ptr() if logits is not None else None, stream))
+        n = int(n_out.item())            # the only host sync of the utterance
+        self.check_device_state()
+        self.last_logits = logits[:n] if logits is not None else None
+        return tokens[:n].to(torch.long)[None]
+
+    def state(self):
+        pos, n_gen, err, launches = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int64()
+        _lib.check(self._lib.cbx_t3_state(self._h, C.byref(pos), C.byref(n_gen), C.byref(err), C.byref(launches)))
+        return dict(pos=pos.value, n_gen=n_gen.value, err=err.value, launches=launches.value)
+
+    def check_device_state(self):
+        s = self.state()
+        if s["err"]:
+            raise _lib.CbxError(f"T3 megakernel reported device error {s['err']} (watchdog timeout)")
+        return s

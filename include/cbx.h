@@ -1,0 +1,86 @@
+/* chatterbox_b200 C-ABI — the drop-in boundary underneath the reference's Python API.
+ *
+ * The reference (rossturner/chatterbox) has no FFI layer: its boundary is the Python class API of
+ * src/chatterbox/tts.py and src/chatterbox/vc.py.  This library sits under the host-side mirrors
+ * of the inner seams the hot path goes through; each entry point cites the reference interface it
+ * replaces.  Conventions: plain C structs, raw DEVICE pointers (tensor.data_ptr()), every weight /
+ * input / output buffer is caller-owned (PyTorch), int return code (0 = ok) + cbx_last_error(),
+ * nothing throws across the ABI, calls are stream-ordered on the cudaStream_t passed as `void*`.
+ * There is no CPU fallback: every call fails loudly without a CUDA device.
+ */
+#ifndef CBX_H
+#define CBX_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* cbx_last_error(void);
+int cbx_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (1) T3 0.5B Llama backbone: prefill + per-token decode loop.
+ * Replaces T3.inference (src/chatterbox/models/t3/t3.py:203-371) below prepare_input_embeds:
+ * T3HuggingfaceBackend.forward (t3/inference/t3_hf_backend.py:73-116) = HF LlamaModel x30 +
+ * speech_head, the CFG pair as one batch-2 pass (t3.py:289-295,323-326), temperature /
+ * repetition-penalty / min-p / top-p processing (t3.py:331-337), sampling (t3.py:340-341), EOS
+ * test and next-token embedding (t3.py:343-356).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct cbx_t3 cbx_t3;
+
+typedef struct CbxT3Config {
+  int32_t device;     /* CUDA ordinal */
+  int32_t n_layers;   /* 30 (llama_configs.py:8); smaller only in tests */
+  int32_t max_pos;    /* KV slab capacity in positions (cond 34 + text + 2 BOS + speech) */
+  int32_t kv_fp32;    /* 0: bf16 KV slab (perf mode), 1: fp32 KV slab (parity mode) */
+} CbxT3Config;
+
+typedef struct CbxT3Weights {          /* device pointers, caller-owned, must outlive the handle */
+  const void* wstream;                 /* bf16 per-CTA weight streams packed by the plan below: [G][stride_units][8192] */
+  int64_t stride_units;                /* units (16 KB) between consecutive CTA streams */
+  const float* ln1;                    /* [n_layers][1024] input_layernorm.weight */
+  const float* ln2;                    /* [n_layers][1024] post_attention_layernorm.weight */
+  const float* final_norm;             /* [1024] tfmr.norm.weight */
+  const float* speech_emb;             /* [8194][1024] speech_emb.weight (t3.py:52) */
+  const float* speech_pos_emb;         /* [4100][1024] speech_pos_emb.emb.weight (t3.py:60) */
+  const float* rope_cos;               /* [max_pos][32] cos of llama3-scaled RoPE angles, fp32 */
+  const float* rope_sin;               /* [max_pos][32] */
+} CbxT3Weights;
+
+typedef struct CbxSampleParams {       /* the generate() knobs of tts.py:208-218 */
+  float cfg_weight;                    /* > 0: rows (cond, uncond), logits = c + w (c - u) */
+  float temperature;
+  float repetition_penalty;
+  float min_p;
+  float top_p;
+  int32_t greedy;                      /* 1: argmax of the processed logits (parity mode); 0: multinomial */
+  int32_t stop_on_eos;                 /* stop at token 6562 (t3.py:347) */
+  uint64_t seed;                       /* Philox seed for multinomial sampling */
+} CbxSampleParams;
+
+/* Number of CTAs (= SMs) the megakernel runs with on `device`; the weight stream is packed for it. */
+int cbx_t3_grid(int device);
+/* The static work plan (csrc/t3_plan.h): units of phase `ph` (0 qkv,1 o,2 gate/up,3 down,4 head)
+ * consumed by CTA `c` of `G`, and the id of the j-th one.  Used by the host-side weight packer. */
+int cbx_t3_plan_count(int ph, int c, int G);
+int cbx_t3_plan_unit(int ph, int c, int G, int j);
+
+int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_t3** out);
+int cbx_t3_destroy(cbx_t3* h);
+/* Prefill: embeds [B][P][1024] fp32 (output of prepare_input_embeds + doubled BOS, t3.py:240-295),
+ * B in {1,2}.  Resets the KV slab and the generated-id set (BOS 6561 seen), leaves the logits of
+ * the last position in the handle (t3.py:307-316). */
+int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void* stream);
+/* Decode loop (t3.py:319-367) as ONE persistent launch: up to max_new_tokens tokens; if
+ * forced_tokens != NULL the loop is teacher-forced with those ids.  tokens_out [max_new_tokens]
+ * int32, n_out [1] int32, logits_out (nullable) [max_new_tokens][B][8194] raw logits per step. */
+int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_tokens, const int32_t* forced_tokens,
+                  int32_t* tokens_out, int32_t* n_out, float* logits_out, void* stream);
+/* Host-visible state after a synchronised stream: cache length, tokens generated, device error flag,
+ * and the number of kernel launches issued through this handle. */
+int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CBX_H */
