@@ -32,7 +32,7 @@ constexpr int NCONS_WARPS = 8;
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
 constexpr int NTHREADS = NCONS + 32;      // + producer warp
 constexpr int MAXS = 16;                  // max KV splits per (row, head) pair
-constexpr int PART_STRIDE = 66;           // 64 o + m + l
+constexpr int PART_STRIDE = 68;           // 64 o + m + l (+2 pad: rows stay 16 B aligned)
 constexpr int STOP_SPEECH = 6562;
 constexpr int VOCAB_PAD = 8200;
 constexpr float RMS_EPS = 1e-5f;

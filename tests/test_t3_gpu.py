@@ -1,0 +1,171 @@
+"""GPU parity tests of the T3 path: CUDA megakernel (through the C-ABI) vs the reference's own
+outputs (tests/golden/t3_golden.safetensors) and vs the CPU oracle on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): teacher-forced per-step logits max-abs <= 2e-2 in the bf16
+mode; greedy speech-token sequences identical for the fp32-accumulated run on identical weights.
+"""
+import os
+
+import pytest
+import torch
+from safetensors.torch import load_file
+
+from chatterbox_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+GOLD = load_file(os.path.join(os.path.dirname(__file__), "golden", "t3_golden.safetensors"))
+PARAMS = dict(cfg_weight=0.5, temperature=0.8, repetition_penalty=1.2, min_p=0.05, top_p=1.0)
+TOL_BF16 = 2e-2     # north_star: bf16-mode logits tolerance
+TOL_FP32KV = 1e-3   # fp32 KV slab, fp32 accumulate, identical (bf16-representable) weights
+
+
+def _cond(dev="cuda"):
+    from chatterbox_b200.t3 import T3Cond
+    return T3Cond(**{k: v.clone() for k, v in S.t3_cond().items()}).to(device=dev)
+
+
+@pytest.fixture(scope="module")
+def sd30():
+    return S.make_state_dict("t3")
+
+
+@pytest.fixture(scope="module")
+def models(sd30):
+    from chatterbox_b200.t3 import T3
+    return {True: T3(sd30, "cuda", max_pos=512, kv_fp32=True), False: T3(sd30, "cuda", max_pos=512, kv_fp32=False)}
+
+
+@pytest.mark.parametrize("kv_fp32", [True, False])
+def test_teacher_forced_logits_match_reference(models, kv_fp32):
+    m = models[kv_fp32]
+    text2 = torch.cat([S.text_tokens()] * 2, 0)
+    forced = GOLD["forced_tokens"].long()[None]
+    n = forced.shape[1]
+    toks = m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=n, forced_tokens=forced,
+                       return_logits=True, do_sample=False, **PARAMS)
+    assert torch.equal(toks.cpu(), forced)
+    got = m.last_logits.cpu()
+    tol = TOL_FP32KV if kv_fp32 else TOL_BF16
+    for j, st in enumerate(GOLD["forced_logit_steps"].tolist()):
+        err = (got[st] - GOLD["forced_logits"][j]).abs().max().item()
+        print(f"kv_fp32={kv_fp32} step {st}: max-abs vs reference {err:.3e}")
+        assert err < tol
+
+
+def test_greedy_tokens_identical_to_reference(models):
+    m = models[True]
+    text2 = torch.cat([S.text_tokens()] * 2, 0)
+    n = GOLD["greedy_tokens"].numel()
+    toks = m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=n, return_logits=True,
+                       do_sample=False, **PARAMS)
+    assert torch.equal(toks[0].cpu().to(torch.int32), GOLD["greedy_tokens"])
+    got = m.last_logits.cpu()
+    for j, st in enumerate(GOLD["greedy_logit_steps"].tolist()):
+        assert (got[st] - GOLD["greedy_logits"][j]).abs().max() < TOL_FP32KV
+    s = m.state()
+    assert s["err"] == 0 and s["n_gen"] == n and s["pos"] == 102 + n
+
+
+def test_bf16_kv_greedy_choice_agrees_where_gap_is_clear(models):
+    """bf16 KV slab: teacher-force the reference's greedy path; the processed arg-max must agree with
+    the reference at every step whose reference top-2 gap exceeds the bf16 tolerance."""
+    from oracle import t3_oracle as T3O
+    m = models[False]
+    text2 = torch.cat([S.text_tokens()] * 2, 0)
+    ref_t = GOLD["greedy_tokens"].long()[None]
+    n = ref_t.shape[1]
+    m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=n, forced_tokens=ref_t, return_logits=True,
+                do_sample=False, **PARAMS)
+    got = m.last_logits.cpu()
+    gen = torch.tensor([[T3O.START_SPEECH]])
+    agree = 0
+    for i in range(n):
+        pick = int(T3O.process_logits(got[i], gen, **PARAMS).argmax())
+        if float(GOLD["greedy_top2_gaps"][i]) > TOL_BF16:
+            assert pick == int(ref_t[0, i]), i
+        agree += pick == int(ref_t[0, i])
+        gen = torch.cat([gen, ref_t[:, i:i + 1]], 1)
+    print(f"bf16-KV greedy agreement with the reference path: {agree}/{n}")
+    assert agree >= n - 4
+
+
+@pytest.mark.parametrize("n_text,cfg", [(2, 0.5), (3, 0.5), (4, 0.0), (5, 0.5)])
+def test_prefill_remainders_and_single_row(n_text, cfg):
+    """P mod 4 in {0,1,2,3} (ragged last prefill chunk) and the B=1 path (cfg_weight == 0)."""
+    from chatterbox_b200.t3 import T3
+    from oracle import t3_oracle as T3O
+    sd = S.make_state_dict("t3", n_layers=2)
+    text = S.text_tokens(n_text)
+    tt = torch.cat([text, text], 0) if cfg > 0 else text
+    forced = torch.randint(0, 6561, (1, 5), generator=torch.Generator().manual_seed(n_text))
+    p = dict(PARAMS, cfg_weight=cfg)
+    _, ref = T3O.inference(sd, S.t3_cond(), tt, max_new_tokens=5, forced_tokens=forced, n_layers=2, **p)
+    m = T3(sd, "cuda", max_pos=128, kv_fp32=True, n_layers=2)
+    m.inference(t3_cond=_cond(), text_tokens=tt, max_new_tokens=5, forced_tokens=forced, return_logits=True,
+                do_sample=False, **p)
+    assert (m.last_logits.cpu() - ref).abs().max() < 1e-3
+
+
+def test_eos_stops_the_loop_and_limits_are_checked():
+    from chatterbox_b200.t3 import T3
+    sd = S.make_state_dict("t3", n_layers=1)
+    m = T3(sd, "cuda", max_pos=64, n_layers=1)
+    text2 = torch.cat([S.text_tokens(2)] * 2, 0)
+    forced = torch.tensor([[11, 22, 6562, 33, 44, 55]])
+    toks = m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=6, forced_tokens=forced, **PARAMS)
+    assert toks.tolist() == [[11, 22, 6562]]           # EOS is emitted, then the loop ends (t3.py:343-348)
+    s = m.state()
+    assert s["n_gen"] == 3 and s["pos"] == 40 + 2      # no forward after EOS
+    toks = m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=6, forced_tokens=forced,
+                       stop_on_eos=False, **PARAMS)
+    assert toks.shape[1] == 6
+    with pytest.raises(ValueError):
+        m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=100, **PARAMS)
+    with pytest.raises(AssertionError):
+        m.inference(t3_cond=_cond(), text_tokens=torch.tensor([[5, 6, 7]]), max_new_tokens=2, **PARAMS)
+
+
+def test_long_context_split_kv():
+    """Config-5-sized context (~2.1 k positions) through the split-KV attention, bf16 KV slab."""
+    from chatterbox_b200.t3 import T3
+    from oracle import t3_oracle as T3O
+    sd = S.make_state_dict("t3", n_layers=2)
+    text2 = torch.cat([S.text_tokens(64)] * 2, 0)
+    n = 2000
+    forced = torch.randint(0, 6561, (1, n), generator=torch.Generator().manual_seed(9))
+    _, ref = T3O.inference(sd, S.t3_cond(), text2, max_new_tokens=n, forced_tokens=forced, n_layers=2,
+                           kv_round=True, **PARAMS)
+    m = T3(sd, "cuda", max_pos=2304, kv_fp32=False, n_layers=2)
+    m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=n, forced_tokens=forced, return_logits=True,
+                do_sample=False, **PARAMS)
+    got = m.last_logits.cpu()
+    for st in (0, 511, 1999):
+        assert (got[st] - ref[st]).abs().max() < TOL_BF16
+    assert m.state()["pos"] == 102 + n
+
+
+def test_sampler_respects_filters_and_distribution():
+    """Multinomial path: every draw lies in the set HF's min-p/top-p warpers keep, and the empirical
+    frequency of the dominant tokens matches the processed distribution."""
+    from chatterbox_b200.t3 import T3
+    from oracle import t3_oracle as T3O
+    sd = S.make_state_dict("t3", n_layers=1)
+    text2 = torch.cat([S.text_tokens(3)] * 2, 0)
+    p = dict(cfg_weight=0.5, temperature=0.25, repetition_penalty=1.2, min_p=0.05, top_p=0.9)
+    _, raw = T3O.inference(sd, S.t3_cond(), text2, max_new_tokens=1, n_layers=1, **p)
+    proc = T3O.process_logits(raw[0], torch.tensor([[T3O.START_SPEECH]]), **p)
+    probs = torch.softmax(proc, -1)[0]
+    kept = set(torch.nonzero(probs > 0).flatten().tolist())
+    m = T3(sd, "cuda", max_pos=64, n_layers=1)
+    draws = []
+    N = 600
+    for s in range(N):
+        t = m.inference(t3_cond=_cond(), text_tokens=text2, max_new_tokens=1, do_sample=True, seed=1000 + s, **p)
+        draws.append(int(t[0, 0]))
+    assert set(draws) <= kept, sorted(set(draws) - kept)[:5]
+    top = torch.topk(probs, 3)
+    for pr, idx in zip(top.values.tolist(), top.indices.tolist()):
+        f = draws.count(idx) / N
+        sigma = (pr * (1 - pr) / N) ** 0.5
+        assert abs(f - pr) < 5 * sigma + 0.01, (idx, f, pr)
