@@ -99,6 +99,9 @@ class T3:
         self._h = h
         self.max_pos = max_pos
         self.last_logits: Optional[torch.Tensor] = None
+        # optional CUDA-event stage timers (bench.py): set `record_events = True`, read `events`
+        self.record_events = False
+        self.events: Dict[str, torch.cuda.Event] = {}
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -198,11 +201,21 @@ class T3:
         sp = _lib.CbxSampleParams(float(cfg_weight), float(temperature), float(repetition_penalty), float(min_p),
                                   float(top_p), 0 if do_sample else 1, 1 if stop_on_eos else 0,
                                   int(seed if seed is not None else torch.initial_seed()) & (2 ** 64 - 1))
+        ev = None
+        if self.record_events:
+            ev = {k: torch.cuda.Event(enable_timing=True) for k in ("prefill0", "decode0", "decode1")}
+            ev["prefill0"].record()
         _lib.check(self._lib.cbx_t3_prefill(self._h, embeds.data_ptr(), B, P, stream))
+        if ev:
+            ev["decode0"].record()
         _lib.check(self._lib.cbx_t3_decode(self._h, C.byref(sp), max_new_tokens,
                                            forced.data_ptr() if forced is not None else None,
                                            tokens.data_ptr(), n_out.data_ptr(),
                                            logits.data_ptr() if logits is not None else None, stream))
+        if ev:
+            ev["decode1"].record()
+            self.events = ev
+        self.last_prefill_len = P
         n = int(n_out.item())            # the only host sync of the utterance
         self.check_device_state()
         self.last_logits = logits[:n] if logits is not None else None
