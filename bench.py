@@ -223,6 +223,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
+    torch.cuda.profiler.start()     # ncu --profile-from-start off: the launch list covers the timed region only
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     dec_ms, pre_ms = [], []
     e0.record()
@@ -233,6 +234,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         pre_ms.append((ev["prefill0"], ev["decode0"]))
     e1.record()
     barrier()
+    torch.cuda.profiler.stop()
     clocks = sampler.stop()
     total_ms = e0.elapsed_time(e1)
     launches = t3.state()["launches"] - l0

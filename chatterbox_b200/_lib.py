@@ -40,6 +40,7 @@ SYMBOLS = {
     "cbx_t3_prefill": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "cbx_t3_decode": (C.c_int, [C.c_void_p, C.POINTER(CbxSampleParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p]),
+    "cbx_t3_set_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "cbx_t3_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                C.POINTER(C.c_int64)]),
 }

@@ -62,6 +62,7 @@ struct T3Params {
   int B;
   const float* embeds; int P;   // prefill
   CbxSampleParams sp; int max_new; const int* forced; int* tokens_out; int* n_out; float* logits_out;
+  unsigned long long* prof; int prof_it;   // optional: CTA 0 stamps %globaltimer after every phase of iteration prof_it
 };
 
 struct Ctl {            // CTA-local control block in shared memory
@@ -670,12 +671,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     float xs[4][8];
     uint32_t A[4][8];
     const int HS = T3_MAX_NPOS * 2 * T3_H;   // one hres buffer
+    int prof_k = 0;
+#define T3_PROF() do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it) p.prof[prof_k++] = gtime_ns(); } while (0)
 
     for (int it = 0; it < n_iters; ++it) {
       int npos = 1;
       if (p.mode == 1) {
+        T3_PROF();
         if (c == 0) sample_phase(p, it, n_gen, scr, ctl, warp, lane);
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
         ++n_gen; ++n_done;
         if (__ldcg(&p.st->stop) || ctl->abort) break;
       } else {
@@ -720,9 +725,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
           }
         }
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
         // ---------- phase B: RoPE, KV append, split-KV attention ----------
         attn_phase<KVT>(p, l, pos0, npos, scr, warp, lane);
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
         // ---------- phase C: o_proj ----------
         {
           load_attn_x(xs, p, active, pp, bb, warp, tig);
@@ -737,6 +744,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
           }
         }
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
         // ---------- phase D: post-attention RMSNorm; gate/up GEMV; SwiGLU ----------
         {
           Piece pc[2] = {Piece{p.hres + (l & 1) * HS, 2 * T3_H, T3_H}, Piece{p.oproj, 2 * T3_H, T3_H}};
@@ -756,6 +764,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
           }
         }
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
         // ---------- phase E: down_proj (k-slice s of this CTA) ----------
         {
           const int n = t3_plan_count(PH_DOWN, c, G);
@@ -776,6 +785,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
           }
         }
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
       }
       // ---------- phase F: final RMSNorm + speech_head (t3_hf_backend.py:100-103) ----------
       if (p.mode == 1 || it == n_iters - 1) {
@@ -796,6 +806,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
             p.logits[(size_t)(gg & 1) * T3_VOCAB + row] = red_sum(red, j, o);
         }
         grid_barrier(p, bar_target, ctl);
+        T3_PROF();
       }
       pos0 += npos;
       if (ctl->abort) break;
@@ -829,6 +840,7 @@ struct cbx_t3 {
   void* slab;           // one allocation for all scratch
   int B;                // rows of the current utterance
   long long launches;
+  unsigned long long* prof; int prof_it;
 };
 
 extern "C" int cbx_t3_grid(int device) {
@@ -859,7 +871,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CHECK(coop, "cbx_t3_create: device lacks cooperative launch");
 
   cbx_t3* h = new cbx_t3();
-  h->cfg = *cfg; h->w = *w; h->G = G; h->B = 2; h->launches = 0;
+  h->cfg = *cfg; h->w = *w; h->G = G; h->B = 2; h->launches = 0; h->prof = nullptr; h->prof_it = -1;
   const size_t kvel = cfg->kv_fp32 ? 4 : 2;
   const size_t kv_bytes = (size_t)cfg->n_layers * 2 * T3_NH * cfg->max_pos * T3_HD * kvel;
   size_t off = 0;
@@ -947,7 +959,15 @@ extern "C" int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_t
   T3Params p = h->base;
   p.mode = 1; p.B = h->B; p.sp = *sp; p.max_new = max_new_tokens; p.forced = forced_tokens;
   p.tokens_out = tokens_out; p.n_out = n_out; p.logits_out = logits_out;
+  p.prof = h->prof; p.prof_it = h->prof_it;
   return t3_launch(h, p, st);
+}
+
+extern "C" int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it) {
+  CBX_CHECK(h, "cbx_t3_set_profile: null handle");
+  h->prof = reinterpret_cast<unsigned long long*>(stamps);
+  h->prof_it = it;
+  return CBX_OK;
 }
 
 extern "C" int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t* launches) {

@@ -80,6 +80,10 @@ int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_tokens, cons
  * and the number of kernel launches issued through this handle. */
 int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t* launches);
 
+/* Debug aid: CTA 0 writes %globaltimer (ns) after every phase of decode iteration `it` into
+ * stamps[] (device, >= 5*n_layers+4 entries); NULL disables. */
+int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it);
+
 #ifdef __cplusplus
 }
 #endif
