@@ -37,6 +37,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     flags = [f for f in NVCC_FLAGS if not f.endswith("_placeholder")]
     if verbose:
         flags += ["-Xptxas", "-v"]
+    flags += os.environ.get("CBX_NVCC_EXTRA", "").split()
     cmd = [nvcc] + flags + ["-o", LIB] + _sources()
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

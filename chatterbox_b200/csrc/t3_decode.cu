@@ -4,18 +4,22 @@
 // T3HuggingfaceBackend.forward, t3/inference/t3_hf_backend.py:73-116): ~600 library launches and a
 // host sync per token become zero launches per token.  The step is HBM-bound (1.02 GB of bf16
 // weights per token at batch 2), so the design is a weight-streaming pipeline:
-//   * one CTA per SM (cooperative launch), 8 consumer warps + 1 producer warp;
+//   * one CTA per SM (cooperative launch for co-residency), 8 consumer warps + 1 producer warp;
 //   * the producer walks this CTA's pre-packed, contiguous weight stream with 16 KB TMA bulk
-//     copies (cp.async.bulk -> UBLKCP) into an 11-deep shared-memory ring guarded by mbarriers.
-//     Weights do not depend on activations, so the producer never waits on a grid barrier: HBM
-//     keeps streaming while the consumers synchronise between dependent phases;
+//     copies (cp.async.bulk -> UBLKCP) into a 9-deep shared-memory ring guarded by mbarriers.
+//     Weights do not depend on activations, so the producer never waits on the consumers' data
+//     dependencies: HBM keeps streaming while dependent phases hand activations over;
 //   * consumers multiply each 8-row x 1024-k unit against the (<= 8) activation rows with
 //     mma.sync m16n8k16 (weights are the B operand; activations are split x = hi + lo in bf16 and
 //     occupy A rows 0-7 / 8-15, so products carry ~16 mantissa bits and accumulate in fp32);
-//   * dependent phases (qkv -> attention -> o_proj -> gate/up -> down) are separated by a
-//     counter-based grid barrier; residual adds, RMSNorm, RoPE, SwiGLU, the split-KV combine, CFG,
-//     logit processing, sampling, EOS and the next-token embedding are all fused into the phase
-//     prologues/epilogues, so nothing but weights and the KV slab touches HBM.
+//   * dependent phases (qkv -> attention -> combine -> o_proj -> gate/up -> down) hand their
+//     activations over through "LL" buffers in L2: every fp32 value travels in one 8-byte word
+//     together with a sequence flag ({value, flag}, one atomic 64-bit store), so a consumer polls
+//     the data itself and there is NO grid barrier and NO fence on the critical path;
+//   * residual adds, RMSNorm, RoPE, SwiGLU, the split-KV combine, CFG, logit processing, sampling,
+//     EOS and the next-token embedding are fused into the phase prologues/epilogues; the residual
+//     stream lives in registers (replicated per CTA), so nothing but weights and the KV slab
+//     touches HBM.
 // The same kernel runs chunked prefill (4 positions x 2 CFG rows per weight pass).
 #include "common.cuh"
 #include "t3_plan.h"
@@ -27,14 +31,16 @@
 
 namespace {
 
-constexpr int NSLOT = 11;                 // ring depth (16 KB units)
+constexpr int NSLOT = 9;                  // ring depth (16 KB units)
 constexpr int NCONS_WARPS = 8;
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
 constexpr int NTHREADS = NCONS + 32;      // + producer warp
-constexpr int MAXS = 16;                  // max KV splits per (row, head) pair
-constexpr int PART_STRIDE = 68;           // 64 o + m + l (+2 pad: rows stay 16 B aligned)
+constexpr int MAXS = 4;                   // max KV splits per (row, head) pair
+constexpr int PART_STRIDE = 68;           // 64 o + m + l (+2 pad)
 constexpr int STOP_SPEECH = 6562;
 constexpr int VOCAB_PAD = 8200;
+constexpr int MAXROWS = 2 * T3_MAX_NPOS;  // activation rows per weight pass: (position, CFG row)
+constexpr int STAGE_LD = 132;             // padded row stride of the per-warp staging tile (floats)
 constexpr float RMS_EPS = 1e-5f;
 
 constexpr int SMEM_RING = NSLOT * T3_UNIT_BYTES;
@@ -42,7 +48,24 @@ constexpr int SMEM_BARS = SMEM_RING;            // 2*NSLOT mbarriers
 constexpr int SMEM_CTL = SMEM_BARS + 256;       // control words
 constexpr int SMEM_SCRATCH = SMEM_CTL + 256;    // phase scratch (union)
 constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
-constexpr int SMEM_TOTAL = SMEM_SCRATCH + SCRATCH_BYTES;
+constexpr int SMEM_STAGE = SMEM_SCRATCH + SCRATCH_BYTES;              // [8 warps][MAXROWS][STAGE_LD] floats
+constexpr int STAGE_BYTES = NCONS_WARPS * MAXROWS * STAGE_LD * 4;
+constexpr int SMEM_SEEN = SMEM_STAGE + STAGE_BYTES;                   // generated-id set (CTA 0)
+constexpr int SMEM_LN = SMEM_SEEN + 8208;                              // [2][1024] floats: prefetched norm gains
+constexpr int SMEM_TOTAL = SMEM_LN + 2 * T3_H * 4;
+static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
+
+// LL exchange buffers (elements are {fp32 bits, flag} 8-byte words), offsets in words
+enum { LLP_QKV = 0, LLP_PART = 1, LLP_ATTN = 2, LLP_OPROJ = 3, LLP_ACT = 4, LLP_DOWN = 5, LLP_LOGITS = 6, LLP_EMB = 7 };
+constexpr size_t LL_QKV = 0;
+constexpr size_t LL_PART = LL_QKV + (size_t)MAXROWS * 3072;
+constexpr size_t LL_ATTN = LL_PART + (size_t)T3_MAX_NPOS * 32 * MAXS * PART_STRIDE;
+constexpr size_t LL_OPROJ = LL_ATTN + (size_t)MAXROWS * T3_H;
+constexpr size_t LL_ACT = LL_OPROJ + (size_t)MAXROWS * T3_H;
+constexpr size_t LL_DOWN = LL_ACT + (size_t)MAXROWS * T3_INTER;
+constexpr size_t LL_LOGITS = LL_DOWN + (size_t)T3_DOWN_KS * MAXROWS * T3_H;
+constexpr size_t LL_EMB = LL_LOGITS + (size_t)2 * VOCAB_PAD;
+constexpr size_t LL_WORDS = LL_EMB + T3_H + 8;
 
 struct T3State {   // lives in global memory, persists between launches of one utterance
   int pos;         // KV cache length
@@ -56,8 +79,9 @@ struct T3Params {
   const float *ln1, *ln2, *final_norm, *speech_emb, *speech_pos_emb, *rope_cos, *rope_sin;
   int n_layers, max_pos;
   void *kcache, *vcache;        // [layer][2][16][max_pos][64]
-  float *qkv, *hres, *oproj, *act, *down, *logits, *part;
-  unsigned* bar; T3State* st; unsigned char* seen;
+  unsigned long long* ll;       // LL exchange words (zeroed before every launch)
+  float* logits;                // [2][8194] plain copy of the last logits (crosses launches)
+  T3State* st; unsigned char* seen;
   int mode;                     // 0 prefill, 1 decode
   int B;
   const float* embeds; int P;   // prefill
@@ -99,52 +123,132 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, Ctl* c
   return true;
 }
 
-// Counter-based grid barrier (all CTAs co-resident: cooperative launch).  Consumer threads only.
-__device__ __forceinline__ void grid_barrier(const T3Params& p, unsigned& target, Ctl* ctl) {
-  target += gridDim.x;
-  cbar();
-  if (threadIdx.x == 0 && !ctl->abort) {
-    __threadfence();
-    red_release_add(p.bar, 1u);
-    unsigned long long t0 = gtime_ns();
-    unsigned spins = 0;
-    while (ld_acquire_u(p.bar) < target) {
-      if ((++spins & 255u) == 0) {
-        if (gtime_ns() - t0 > WATCHDOG_NS) { ctl->abort = 1; atomicExch(&p.st->err, 1); break; }
-        if (__ldcg(&p.st->err)) { ctl->abort = 1; break; }
+// ---- LL words: {value, flag} in one 64-bit relaxed store / load --------------------------------
+__device__ __forceinline__ unsigned ll_flag(int it, int L, int l, int ph) {
+  return 1u + (unsigned)((it * (L + 1) + l) * 8 + ph);
+}
+__device__ __forceinline__ void ll_store(unsigned long long* p, float v, unsigned flag) {
+  const unsigned long long w = ((unsigned long long)flag << 32) | (unsigned long long)__float_as_uint(v);
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_ld1(const unsigned long long* p) {
+  unsigned long long w;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  return w;
+}
+__device__ __forceinline__ void ll_ld2(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned flag) { return (unsigned)(w >> 32) == flag; }
+__device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)w); }
+
+// watchdog bookkeeping of a poll loop; returns true when the caller must give up
+__device__ __forceinline__ bool poll_timeout(unsigned& spins, unsigned long long& t0, Ctl* ctl, T3State* st) {
+  if (ctl->abort) return true;
+  if ((++spins & 255u) == 0) {
+    if (t0 == 0) t0 = gtime_ns();
+    else if (gtime_ns() - t0 > WATCHDOG_NS || __ldcg(&st->err)) {
+      ctl->abort = 1;
+      atomicExch(&st->err, 1);
+      return true;
+    }
+  }
+  return false;
+}
+
+// poll n (<= N) scattered LL words; w[i] receives the word at ptr[i]
+template <int N>
+__device__ __forceinline__ void ll_poll(const unsigned long long* (&ptr)[N], int n, unsigned flag,
+                                        unsigned long long (&w)[N], Ctl* ctl, T3State* st) {
+  unsigned spins = 0; unsigned long long t0 = 0;
+  for (;;) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < N; ++i) if (i < n) w[i] = ll_ld1(ptr[i]);
+#pragma unroll
+    for (int i = 0; i < N; ++i) if (i < n) ok = ok && ll_ok(w[i], flag);
+    if (ok) return;
+    if (poll_timeout(spins, t0, ctl, st)) return;
+  }
+}
+
+struct Piece { const unsigned long long* ptr; size_t row_stride; unsigned flag; };   // row_stride in words
+
+// Warp-cooperative load of this warp's 128-wide k slice of R activation rows from NP LL pieces
+// (summed) into the warp's staging tile stage[row][STAGE_LD].  Row r = (position r>>1, CFG row r&1)
+// is loaded only if r < nrows and (r&1) < B.  All lanes issue 2*R/PAR... loads per round and poll
+// them together, so one exchange costs about one L2 round trip.
+template <int R, int PAR>
+__device__ __forceinline__ void ll_stage(float* stage, const Piece* pc, int np, int kbase, int nrows, int B, int lane,
+                                         Ctl* ctl, T3State* st) {
+  constexpr int T = 2 * R;      // v2 loads per lane per piece: R rows * 64 v2 / 32 lanes
+  float acc[T][2];
+#pragma unroll
+  for (int t = 0; t < T; ++t) acc[t][0] = acc[t][1] = 0.f;
+  for (int p0 = 0; p0 < np; p0 += PAR) {
+    unsigned long long wa[PAR][T], wb[PAR][T];
+    unsigned spins = 0; unsigned long long t0 = 0;
+    for (;;) {
+      bool ok = true;
+#pragma unroll
+      for (int q = 0; q < PAR; ++q) {
+        if (p0 + q < np) {
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const int i = lane + 32 * t, row = i >> 6, c2 = i & 63;
+            if (row < nrows && (row & 1) < B)
+              ll_ld2(pc[p0 + q].ptr + (size_t)row * pc[p0 + q].row_stride + kbase + 2 * c2, wa[q][t], wb[q][t]);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < PAR; ++q) {
+        if (p0 + q < np) {
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const int row = (lane + 32 * t) >> 6;
+            if (row < nrows && (row & 1) < B)
+              ok = ok && ll_ok(wa[q][t], pc[p0 + q].flag) && ll_ok(wb[q][t], pc[p0 + q].flag);
+          }
+        }
+      }
+      if (ok) break;
+      if (poll_timeout(spins, t0, ctl, st)) break;
+    }
+#pragma unroll
+    for (int q = 0; q < PAR; ++q) {
+      if (p0 + q < np) {
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+          const int row = (lane + 32 * t) >> 6;
+          if (row < nrows && (row & 1) < B) { acc[t][0] += ll_val(wa[q][t]); acc[t][1] += ll_val(wb[q][t]); }
+        }
       }
     }
   }
-  cbar();
+#pragma unroll
+  for (int t = 0; t < T; ++t) {
+    const int i = lane + 32 * t, row = i >> 6, c2 = i & 63;
+    *reinterpret_cast<float2*>(stage + row * STAGE_LD + 2 * c2) = make_float2(acc[t][0], acc[t][1]);
+  }
+  __syncwarp();
+}
+
+// thread (g = lane>>2, tig = lane&3) reads its fragment values: row g, k = jj*32 + tig*8 + e of the warp slice
+__device__ __forceinline__ void stage_read(float (&xs)[4][8], const float* stage, int g, int tig) {
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) {
+    const float4 a = *reinterpret_cast<const float4*>(stage + g * STAGE_LD + jj * 32 + tig * 8);
+    const float4 b = *reinterpret_cast<const float4*>(stage + g * STAGE_LD + jj * 32 + tig * 8 + 4);
+    xs[jj][0] = a.x; xs[jj][1] = a.y; xs[jj][2] = a.z; xs[jj][3] = a.w;
+    xs[jj][4] = b.x; xs[jj][5] = b.y; xs[jj][6] = b.z; xs[jj][7] = b.w;
+  }
+  __syncwarp();
 }
 
 // ---- activation rows -> A fragments -------------------------------------------------------------
 // Lane (g = lane>>2, tig = lane&3) owns activation row g = (pos pp = g>>1, CFG row bb = g&1) and, for
 // each of the warp's four k32-blocks jj, the 8 consecutive k at warp*128 + jj*32 + tig*8.
-struct Piece { const float* ptr; int sp, sb; };   // element strides over (pp, bb)
-
-template <int NP>
-__device__ __forceinline__ void load_x(float (&xs)[4][8], const Piece (&pc)[NP], int npieces, bool active, int pp,
-                                       int bb, int kbase) {
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-    for (int e = 0; e < 8; ++e) xs[jj][e] = 0.f;
-  if (!active) return;
-#pragma unroll
-  for (int q = 0; q < NP; ++q) {
-    if (q < npieces) {
-      const float* base = pc[q].ptr + (size_t)pp * pc[q].sp + (size_t)bb * pc[q].sb + kbase;
-#pragma unroll
-      for (int jj = 0; jj < 4; ++jj) {
-        float4 a = ldcg_f4(base + jj * 32), b = ldcg_f4(base + jj * 32 + 4);
-        xs[jj][0] += a.x; xs[jj][1] += a.y; xs[jj][2] += a.z; xs[jj][3] += a.w;
-        xs[jj][4] += b.x; xs[jj][5] += b.y; xs[jj][6] += b.z; xs[jj][7] += b.w;
-      }
-    }
-  }
-}
-
 __device__ __forceinline__ void make_frags(uint32_t (&A)[4][8], const float (&xs)[4][8]) {
 #pragma unroll
   for (int jj = 0; jj < 4; ++jj) {
@@ -155,10 +259,19 @@ __device__ __forceinline__ void make_frags(uint32_t (&A)[4][8], const float (&xs
   }
 }
 
+// Norm gains travel through a double-buffered shared-memory prefetch (cp.async issued one phase
+// ahead), so the RMSNorm never waits on L2/HBM for them.
+__device__ __forceinline__ void ln_prefetch(float* lnbuf, int qq, const float* __restrict__ lnw, int tid) {
+  const uint32_t dst = smem_u32(lnbuf + (qq & 1) * T3_H + tid * 4);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(lnw + tid * 4) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
 // RMSNorm over the full 1024-wide row (reference: HF LlamaRMSNorm, eps 1e-5): the row is spread
-// over the 4 tig lanes of 8 warps; partial sums of squares meet in shared memory.
-__device__ __forceinline__ void rmsnorm_rows(float (&xs)[4][8], const float* __restrict__ lnw, int kbase, float* ssq,
-                                             int warp, int lane) {
+// over the 4 tig lanes of 8 warps; partial sums of squares meet in shared memory.  out = w * (x * rsqrt)
+__device__ __forceinline__ void rmsnorm_rows(float (&out)[4][8], const float (&xs)[4][8], const float* lnbuf, int qq,
+                                             int kw, float* ssq, int warp, int lane, unsigned long long* dbg = nullptr) {
+  if (dbg) dbg[0] = gtime_ns();
   float s = 0.f;
 #pragma unroll
   for (int jj = 0; jj < 4; ++jj)
@@ -168,46 +281,69 @@ __device__ __forceinline__ void rmsnorm_rows(float (&xs)[4][8], const float* __r
   s += __shfl_xor_sync(0xffffffffu, s, 2);
   const int g = lane >> 2;
   if ((lane & 3) == 0) ssq[warp * 8 + g] = s;
+  if (dbg) dbg[1] = gtime_ns();
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (dbg) dbg[2] = gtime_ns();
   cbar();
+  if (dbg) dbg[3] = gtime_ns();
   float tot = 0.f;
 #pragma unroll
   for (int w = 0; w < NCONS_WARPS; ++w) tot += ssq[w * 8 + g];
   const float scale = 1.0f / sqrtf(tot * (1.0f / T3_H) + RMS_EPS);
+  const float* lw = lnbuf + (qq & 1) * T3_H + kw;
 #pragma unroll
   for (int jj = 0; jj < 4; ++jj) {
-    float4 a = __ldg(reinterpret_cast<const float4*>(lnw + kbase + jj * 32));
-    float4 b = __ldg(reinterpret_cast<const float4*>(lnw + kbase + jj * 32 + 4));
-    xs[jj][0] = a.x * (xs[jj][0] * scale); xs[jj][1] = a.y * (xs[jj][1] * scale);
-    xs[jj][2] = a.z * (xs[jj][2] * scale); xs[jj][3] = a.w * (xs[jj][3] * scale);
-    xs[jj][4] = b.x * (xs[jj][4] * scale); xs[jj][5] = b.y * (xs[jj][5] * scale);
-    xs[jj][6] = b.z * (xs[jj][6] * scale); xs[jj][7] = b.w * (xs[jj][7] * scale);
+    const float4 a = *reinterpret_cast<const float4*>(lw + jj * 32);
+    const float4 b = *reinterpret_cast<const float4*>(lw + jj * 32 + 4);
+    out[jj][0] = a.x * (xs[jj][0] * scale); out[jj][1] = a.y * (xs[jj][1] * scale);
+    out[jj][2] = a.z * (xs[jj][2] * scale); out[jj][3] = a.w * (xs[jj][3] * scale);
+    out[jj][4] = b.x * (xs[jj][4] * scale); out[jj][5] = b.y * (xs[jj][5] * scale);
+    out[jj][6] = b.z * (xs[jj][6] * scale); out[jj][7] = b.w * (xs[jj][7] * scale);
   }
+  if (dbg) dbg[4] = gtime_ns();
 }
 
 // ---- consume n weight units from the ring: red[j][warp][64] = this warp's k-slice partial of unit j
-struct RingPos { int slot; uint32_t parity; int k; };
+struct RingPos { int slot; uint32_t parity; int k; unsigned long long wait_ns, mma_ns; };
 
 __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t (&A)[4][8], float* red,
                                               const uint8_t* ring, uint64_t* full, uint64_t* empty, int warp, int lane,
                                               Ctl* ctl, T3State* st) {
+  float2 prev = make_float2(0.f, 0.f);
   for (int j = 0; j < n; ++j) {
+#ifdef T3_DEBUG_WAIT
+    const unsigned long long tw0 = gtime_ns();
+#endif
     mbar_wait(&full[rp.slot], rp.parity, ctl, st);
+#ifdef T3_DEBUG_WAIT
+    const unsigned long long tw1 = gtime_ns();
+    rp.wait_ns += tw1 - tw0;
+#endif
     const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * 128 + lane;
-    float c4[4] = {0.f, 0.f, 0.f, 0.f};
     uint4 w[4];
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) w[jj] = wp[jj * 32];
-#pragma unroll
-    for (int jj = 0; jj < 4; ++jj) {
-      mma_bf16_16816(c4, A[jj][0], A[jj][1], A[jj][2], A[jj][3], w[jj].x, w[jj].y);
-      mma_bf16_16816(c4, A[jj][4], A[jj][5], A[jj][6], A[jj][7], w[jj].z, w[jj].w);
-    }
+    // the previous unit's result is stored only now, so its MMA chain overlaps this unit's loads
+    if (j > 0) reinterpret_cast<float2*>(red + ((j - 1) * NCONS_WARPS + warp) * 64)[lane] = prev;
+    float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f};   // two independent accumulator chains
+    mma_bf16_16816(c0, A[0][0], A[0][1], A[0][2], A[0][3], w[0].x, w[0].y);
+    mma_bf16_16816(c1, A[0][4], A[0][5], A[0][6], A[0][7], w[0].z, w[0].w);
+    mma_bf16_16816(c0, A[1][0], A[1][1], A[1][2], A[1][3], w[1].x, w[1].y);
+    mma_bf16_16816(c1, A[1][4], A[1][5], A[1][6], A[1][7], w[1].z, w[1].w);
+    mma_bf16_16816(c0, A[2][0], A[2][1], A[2][2], A[2][3], w[2].x, w[2].y);
+    mma_bf16_16816(c1, A[2][4], A[2][5], A[2][6], A[2][7], w[2].z, w[2].w);
+    mma_bf16_16816(c0, A[3][0], A[3][1], A[3][2], A[3][3], w[3].x, w[3].y);
+    mma_bf16_16816(c1, A[3][4], A[3][5], A[3][6], A[3][7], w[3].z, w[3].w);
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[rp.slot]);
-    reinterpret_cast<float2*>(red + (j * NCONS_WARPS + warp) * 64)[lane] = make_float2(c4[0] + c4[2], c4[1] + c4[3]);
+    prev = make_float2((c0[0] + c0[2]) + (c1[0] + c1[2]), (c0[1] + c0[3]) + (c1[1] + c1[3]));
     if (++rp.slot == NSLOT) { rp.slot = 0; rp.parity ^= 1u; }
     ++rp.k;
+#ifdef T3_DEBUG_WAIT
+    rp.mma_ns += gtime_ns() - tw1;
+#endif
   }
+  if (n > 0) reinterpret_cast<float2*>(red + ((n - 1) * NCONS_WARPS + warp) * 64)[lane] = prev;
 }
 
 __device__ __forceinline__ float red_sum(const float* red, int j, int o) {
@@ -216,10 +352,6 @@ __device__ __forceinline__ float red_sum(const float* red, int j, int o) {
   for (int w = 0; w < NCONS_WARPS; ++w) s += red[(j * NCONS_WARPS + w) * 64 + o];
   return s;
 }
-
-}  // namespace
-
-namespace {
 
 // ---- KV slab element access ---------------------------------------------------------------------
 template <typename KVT> struct KV;
@@ -273,13 +405,15 @@ __device__ __forceinline__ void osm_merge_xor(Osm& s, int mask) {
   s.m = mn;
 }
 
-// ---- phase B: RoPE + KV append + split-KV attention over the slab ------------------------------
+// ---- phase B: RoPE + KV append + split-KV attention over the slab + split combine ---------------
 // (reference: HF LlamaAttention eager path: softmax(q k^T / 8 + causal) v in fp32; rotate_half RoPE)
-// CTA c < S*npairs handles pair = c % npairs (CFG row b, head) and KV split c / npairs.
-// Output: part[pp][pair][split][0..63] = sum_i exp(s_i - m) v_i, [64] = m, [65] = l.
-template <typename KVT>
-__device__ void attn_phase(const T3Params& p, int layer, int pos0, int npos, float* scr, int warp, int lane) {
-  const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x;
+// CTA c < S*npairs handles pair = c % npairs (CFG row b, head) and KV split c / npairs; it publishes
+// {sum_i exp(s_i - m) v_i, m, l} through the LL part buffer, and the split-0 CTA of each pair merges
+// the S partials into the attention output row segment (LL attn buffer).
+template <typename KVT, int NPOS>
+__device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, int pos0, int npos, float* scr, int warp,
+                                        int lane, Ctl* ctl) {
+  const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x, L = p.n_layers;
   const int npairs = p.B * T3_NH;
   int S = G / npairs; if (S > MAXS) S = MAXS;
   if (c >= S * npairs) return;
@@ -287,36 +421,35 @@ __device__ void attn_phase(const T3Params& p, int layer, int pos0, int npos, flo
   float* q_s = scr;                       // [4][64] (pre-scaled by 1/8)
   float* k_new = scr + 256;               // [4][64]
   float* v_new = scr + 512;               // [4][64]
-  float* wpart = scr + 768;               // [8 warps][4][66]
+  float* wpart = scr + 768;               // [8 warps][4][PART_STRIDE]
   KVT* kc = reinterpret_cast<KVT*>(p.kcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
   KVT* vc = reinterpret_cast<KVT*>(p.vcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
 
+  float kr = 0.f, vr = 0.f;
   if (tid < npos * 64) {
     const int pp = tid >> 6, d = tid & 63;
-    const float* row = p.qkv + (size_t)(pp * 2 + b) * 3072 + head * 64;
+    const unsigned long long* row = p.ll + LL_QKV + (size_t)(pp * 2 + b) * 3072 + head * 64;
+    const unsigned long long* ptr[5] = {row + d, row + (d ^ 32), row + 1024 + d, row + 1024 + (d ^ 32),
+                                              row + 2048 + d};
+    unsigned long long w[5];
+    ll_poll<5>(ptr, 5, ll_flag(it, L, layer, LLP_QKV), w, ctl, p.st);
     const float cs = __ldg(p.rope_cos + (size_t)(pos0 + pp) * 32 + (d & 31));
     const float sn = __ldg(p.rope_sin + (size_t)(pos0 + pp) * 32 + (d & 31));
-    const float q = ldcg_f(row + d), qo = ldcg_f(row + (d ^ 32));
-    const float k = ldcg_f(row + 1024 + d), ko = ldcg_f(row + 1024 + (d ^ 32));
-    const float v = ldcg_f(row + 2048 + d);
+    const float q = ll_val(w[0]), qo = ll_val(w[1]), k = ll_val(w[2]), ko = ll_val(w[3]), v = ll_val(w[4]);
     const float qr = q * cs + (d < 32 ? -qo : qo) * sn;
-    const float kr = KV<KVT>::round(k * cs + (d < 32 ? -ko : ko) * sn);
-    const float vr = KV<KVT>::round(v);
+    kr = KV<KVT>::round(k * cs + (d < 32 ? -ko : ko) * sn);
+    vr = KV<KVT>::round(v);
     q_s[pp * 64 + d] = qr * 0.125f;
     k_new[pp * 64 + d] = kr;
     v_new[pp * 64 + d] = vr;
-    if (split == S - 1) {
-      KV<KVT>::store(kc + (size_t)(pos0 + pp) * 64 + d, kr);
-      KV<KVT>::store(vc + (size_t)(pos0 + pp) * 64 + d, vr);
-    }
   }
   cbar();
 
   const int lg = lane >> 3, sub = lane & 7;
-  float qv[T3_MAX_NPOS][8];
-  Osm st[T3_MAX_NPOS];
+  float qv[NPOS][8];
+  Osm st[NPOS];
 #pragma unroll
-  for (int pp = 0; pp < T3_MAX_NPOS; ++pp) {
+  for (int pp = 0; pp < NPOS; ++pp) {
     osm_init(st[pp]);
 #pragma unroll
     for (int e = 0; e < 8; ++e) qv[pp][e] = (pp < npos) ? q_s[pp * 64 + sub * 8 + e] : 0.f;
@@ -336,7 +469,7 @@ __device__ void attn_phase(const T3Params& p, int layer, int pos0, int npos, flo
       for (int e = 0; e < 8; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
     }
 #pragma unroll
-    for (int pp = 0; pp < T3_MAX_NPOS; ++pp) {
+    for (int pp = 0; pp < NPOS; ++pp) {
       if (pp < npos) {
         float s = 0.f;
 #pragma unroll
@@ -358,7 +491,7 @@ __device__ void attn_phase(const T3Params& p, int layer, int pos0, int npos, flo
       vf[e] = valid ? v_new[lg * 64 + sub * 8 + e] : 0.f;
     }
 #pragma unroll
-    for (int pp = 0; pp < T3_MAX_NPOS; ++pp) {
+    for (int pp = 0; pp < NPOS; ++pp) {
       if (pp < npos) {
         float s = 0.f;
 #pragma unroll
@@ -372,7 +505,7 @@ __device__ void attn_phase(const T3Params& p, int layer, int pos0, int npos, flo
   }
   // merge the 4 lane groups, then the 8 warps
 #pragma unroll
-  for (int pp = 0; pp < T3_MAX_NPOS; ++pp) {
+  for (int pp = 0; pp < NPOS; ++pp) {
     if (pp < npos) {
       osm_merge_xor(st[pp], 8);
       osm_merge_xor(st[pp], 16);
@@ -390,56 +523,55 @@ __device__ void attn_phase(const T3Params& p, int layer, int pos0, int npos, flo
     float M = -INFINITY;
 #pragma unroll
     for (int w = 0; w < NCONS_WARPS; ++w) M = fmaxf(M, wpart[(w * T3_MAX_NPOS + pp) * PART_STRIDE + 64]);
-    float L = 0.f, O = 0.f;
+    float Ls = 0.f, O = 0.f;
     if (M != -INFINITY) {
 #pragma unroll
       for (int w = 0; w < NCONS_WARPS; ++w) {
         const float* wp = wpart + (w * T3_MAX_NPOS + pp) * PART_STRIDE;
         const float cw = (wp[64] == -INFINITY) ? 0.f : __expf(wp[64] - M);
-        L += cw * wp[65];
+        Ls += cw * wp[65];
         O += cw * wp[d];
       }
     }
-    float* out = p.part + ((size_t)(pp * 32 + pair) * MAXS + split) * PART_STRIDE;
-    out[d] = O;
-    if (d == 0) { out[64] = M; out[65] = L; }
-  }
-}
-
-// ---- phase C prologue: combine the KV splits into the attention output rows --------------------
-__device__ __forceinline__ void load_attn_x(float (&xs)[4][8], const T3Params& p, bool active, int pp, int bb, int warp,
-                                            int tig) {
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-    for (int e = 0; e < 8; ++e) xs[jj][e] = 0.f;
-  if (!active) return;
-  const int npairs = p.B * T3_NH;
-  int S = gridDim.x / npairs; if (S > MAXS) S = MAXS;
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj) {
-    const int head = 2 * warp + (jj >> 1), d0 = (jj & 1) * 32 + tig * 8;
-    const float* base = p.part + ((size_t)(pp * 32 + bb * T3_NH + head) * MAXS) * PART_STRIDE;
-    float M = -INFINITY;
-    for (int s = 0; s < S; ++s) M = fmaxf(M, ldcg_f(base + s * PART_STRIDE + 64));
-    float L = 0.f;
-    for (int s = 0; s < S; ++s) {
-      const float ms = ldcg_f(base + s * PART_STRIDE + 64);
-      const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - M);
-      L += cw * ldcg_f(base + s * PART_STRIDE + 65);
-      const float4 a = ldcg_f4(base + s * PART_STRIDE + d0), bq = ldcg_f4(base + s * PART_STRIDE + d0 + 4);
-      xs[jj][0] += cw * a.x; xs[jj][1] += cw * a.y; xs[jj][2] += cw * a.z; xs[jj][3] += cw * a.w;
-      xs[jj][4] += cw * bq.x; xs[jj][5] += cw * bq.y; xs[jj][6] += cw * bq.z; xs[jj][7] += cw * bq.w;
+    const unsigned fl = ll_flag(it, L, layer, LLP_PART);
+    unsigned long long* out = p.ll + LL_PART + ((size_t)(pp * 32 + pair) * MAXS + split) * PART_STRIDE;
+    ll_store(out + d, O, fl);
+    if (d == 0) { ll_store(out + 64, M, fl); ll_store(out + 65, Ls, fl); }
+    // KV append after the partial is on its way; the fence orders it before this CTA's later LL stores
+    if (split == S - 1) {
+      KV<KVT>::store(kc + (size_t)(pos0 + pp) * 64 + d, kr);
+      KV<KVT>::store(vc + (size_t)(pos0 + pp) * 64 + d, vr);
+      __threadfence();
     }
-    const float inv = 1.0f / L;
+    if (split == 0) {
+      // merge the S partials of this pair -> attention output segment
+      const unsigned long long* const base = p.ll + LL_PART + ((size_t)(pp * 32 + pair) * MAXS) * PART_STRIDE;
+      const unsigned long long* ptr[3 * MAXS];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) xs[jj][e] *= inv;
+      for (int s = 0; s < MAXS; ++s) {
+        ptr[3 * s] = base + s * PART_STRIDE + d;
+        ptr[3 * s + 1] = base + s * PART_STRIDE + 64;
+        ptr[3 * s + 2] = base + s * PART_STRIDE + 65;
+      }
+      unsigned long long w[3 * MAXS];
+      ll_poll<3 * MAXS>(ptr, 3 * S, fl, w, ctl, p.st);
+      float Mx = -INFINITY;
+#pragma unroll
+      for (int s = 0; s < MAXS; ++s) if (s < S) Mx = fmaxf(Mx, ll_val(w[3 * s + 1]));
+      float Lt = 0.f, Ot = 0.f;
+#pragma unroll
+      for (int s = 0; s < MAXS; ++s) {
+        if (s < S) {
+          const float ms = ll_val(w[3 * s + 1]);
+          const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
+          Lt += cw * ll_val(w[3 * s + 2]);
+          Ot += cw * ll_val(w[3 * s]);
+        }
+      }
+      ll_store(p.ll + LL_ATTN + (size_t)(pp * 2 + b) * T3_H + head * 64 + d, Ot / Lt, ll_flag(it, L, layer, LLP_ATTN));
+    }
   }
 }
-
-}  // namespace
-
-namespace {
 
 // ---- sampling phase (CTA 0): t3.py:320-356 ------------------------------------------------------
 __device__ __forceinline__ float block_sum(float v, float* rs, int warp, int lane) {
@@ -475,26 +607,66 @@ __device__ __forceinline__ unsigned f2ord(float f) {
 }
 
 // Processes the pending logits of the CFG pair and emits token `it`.  All NCONS threads of CTA 0.
-__device__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, Ctl* ctl, int warp, int lane) {
-  const int tid = threadIdx.x;
+__device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, unsigned char* seen, Ctl* ctl, int warp,
+                             int lane) {
+  const int tid = threadIdx.x, L = p.n_layers;
   float* rs = sl + VOCAB_PAD;          // reduction scratch (64 floats)
   int* ri = reinterpret_cast<int*>(rs + 32);
   const CbxSampleParams& sp = p.sp;
   const bool cfg = sp.cfg_weight > 0.f && p.B == 2;
   // 1. CFG, temperature, repetition penalty; running max (first index on ties)
   float lmax = -INFINITY; int imax = 0x7fffffff;
-  for (int i = tid; i < T3_VOCAB; i += NCONS) {
-    const float c = ldcg_f(p.logits + i);
-    const float u = (p.B == 2) ? ldcg_f(p.logits + T3_VOCAB + i) : 0.f;
-    if (p.logits_out) {
-      p.logits_out[((size_t)it * p.B) * T3_VOCAB + i] = c;
-      if (p.B == 2) p.logits_out[((size_t)it * p.B + 1) * T3_VOCAB + i] = u;
+  constexpr int NK = (T3_VOCAB + NCONS - 1) / NCONS;   // 33
+  const unsigned lfl = ll_flag(it - 1, L, L, LLP_LOGITS);
+  for (int k0 = 0; k0 < NK; k0 += 8) {
+    float cv[8], uv[8];
+    if (it == 0) {   // logits of the previous launch (prefill or an earlier decode call)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int i = tid + (k0 + k) * NCONS;
+        cv[k] = (i < T3_VOCAB) ? __ldcg(p.logits + i) : 0.f;
+        uv[k] = (i < T3_VOCAB && p.B == 2) ? __ldcg(p.logits + T3_VOCAB + i) : 0.f;
+      }
+    } else {
+      unsigned long long wc[8], wu[8];
+      unsigned spins = 0; unsigned long long t0 = 0;
+      for (;;) {
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i = tid + (k0 + k) * NCONS;
+          if (i < T3_VOCAB) {
+            wc[k] = ll_ld1(p.ll + LL_LOGITS + i);
+            if (p.B == 2) wu[k] = ll_ld1(p.ll + LL_LOGITS + VOCAB_PAD + i);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int i = tid + (k0 + k) * NCONS;
+          if (i < T3_VOCAB) ok = ok && ll_ok(wc[k], lfl) && (p.B != 2 || ll_ok(wu[k], lfl));
+        }
+        if (ok) break;
+        if (poll_timeout(spins, t0, ctl, p.st)) break;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { cv[k] = ll_val(wc[k]); uv[k] = (p.B == 2) ? ll_val(wu[k]) : 0.f; }
     }
-    float x = cfg ? c + sp.cfg_weight * (c - u) : c;
-    if (sp.temperature != 1.0f) x = x / sp.temperature;
-    if (__ldcg(p.seen + i)) x = (x < 0.f) ? x * sp.repetition_penalty : x / sp.repetition_penalty;
-    sl[i] = x;
-    if (x > lmax) { lmax = x; imax = i; }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int i = tid + (k0 + k) * NCONS;
+      if (i < T3_VOCAB) {
+        const float c = cv[k], u = uv[k];
+        if (p.logits_out) {
+          p.logits_out[((size_t)it * p.B) * T3_VOCAB + i] = c;
+          if (p.B == 2) p.logits_out[((size_t)it * p.B + 1) * T3_VOCAB + i] = u;
+        }
+        float x = cfg ? c + sp.cfg_weight * (c - u) : c;
+        if (sp.temperature != 1.0f) x = x / sp.temperature;
+        if (seen[i]) x = (x < 0.f) ? x * sp.repetition_penalty : x / sp.repetition_penalty;
+        sl[i] = x;
+        if (x > lmax) { lmax = x; imax = i; }
+      }
+    }
   }
   // block arg-max
 #pragma unroll
@@ -573,28 +745,29 @@ __device__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, Ct
     tok = ri[16];
   }
   if (p.forced) tok = p.forced[it];
+  const bool stop = sp.stop_on_eos && tok == STOP_SPEECH;
   if (tid == 0) {
     p.tokens_out[it] = tok;
+    seen[tok] = 1;
     p.seen[tok] = 1;
-    if (sp.stop_on_eos && tok == STOP_SPEECH) { p.st->stop = 1; }
-    ctl->tok = tok;
+    if (stop) p.st->stop = 1;
   }
-  // 5. next-token embedding: speech_emb[tok] + speech_pos_emb[n_gen + 1]  (t3.py:351-356), both CFG rows
+  // 5. next-token embedding: speech_emb[tok] + speech_pos_emb[n_gen + 1]  (t3.py:351-356); both CFG rows get the
+  //    same vector, published once together with the control word {token | stop bit}
   {
+    const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
     const float4 e = __ldg(reinterpret_cast<const float4*>(p.speech_emb + (size_t)tok * T3_H) + tid);
     const float4 q = __ldg(reinterpret_cast<const float4*>(p.speech_pos_emb + (size_t)(n_gen + 1) * T3_H) + tid);
-    const float4 h = make_float4(e.x + q.x, e.y + q.y, e.z + q.z, e.w + q.w);
-    float* dst = p.hres + (size_t)1 * (T3_MAX_NPOS * 2 * T3_H);   // hres[1][pp=0][b]
-    for (int b = 0; b < p.B; ++b) reinterpret_cast<float4*>(dst + b * T3_H)[tid] = h;
+    unsigned long long* dst = p.ll + LL_EMB + 4 * tid;
+    ll_store(dst + 0, e.x + q.x, fl); ll_store(dst + 1, e.y + q.y, fl);
+    ll_store(dst + 2, e.z + q.z, fl); ll_store(dst + 3, e.w + q.w, fl);
+    if (tid == 0) ll_store(p.ll + LL_EMB + T3_H, __uint_as_float((unsigned)tok | (stop ? 0x80000000u : 0u)), fl);
   }
+  cbar();   // seen[] update visible to the next call
 }
 
-}  // namespace
-
-namespace {
-
 // ---- the megakernel -----------------------------------------------------------------------------
-template <typename KVT>
+template <typename KVT, int NPOS>
 __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
@@ -604,6 +777,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   float* scr = reinterpret_cast<float*>(smem + SMEM_SCRATCH);
   float* red = scr;                       // [MAXU][8][64]
   float* ssq = scr + T3_MAXU * 8 * 64;    // [8][8]
+  float* stage_all = reinterpret_cast<float*>(smem + SMEM_STAGE);
+  unsigned char* seen = smem + SMEM_SEEN;
+  float* lnbuf = reinterpret_cast<float*>(smem + SMEM_LN);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = gridDim.x, c = blockIdx.x;
@@ -612,12 +788,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     ctl->abort = 0; ctl->cons_done = 0; ctl->cons_k = 0; ctl->tok = 0;
     mbar_fence_init();
   }
+  for (int i = tid; i < NCONS_WARPS * MAXROWS * STAGE_LD; i += NTHREADS) stage_all[i] = 0.f;
+  if (c == 0) for (int i = tid; i < VOCAB_PAD; i += NTHREADS) seen[i] = p.seen[i];
   __syncthreads();
 
   const int L = p.n_layers;
   const int upl = t3_plan_units_per_layer(c, G);
   const int nhead = t3_plan_count(PH_HEAD, c, G);
-  const int n_iters = (p.mode == 0) ? (p.P + T3_MAX_NPOS - 1) / T3_MAX_NPOS : p.max_new;
+  const int n_iters = (p.mode == 0) ? (p.P + NPOS - 1) / NPOS : p.max_new;
 
   if (warp == NCONS_WARPS) {
     // ===== producer warp: stream this CTA's weight units through the ring =====
@@ -628,8 +806,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     for (int it = 0; it < n_iters && !stopped; ++it) {
       const bool head = (p.mode == 1) || (it == n_iters - 1);
       const int n_units = L * upl + (head ? nhead : 0);
-      const int head_skip = head ? 0 : 0;
-      (void)head_skip;
       for (int u = 0; u < n_units; ++u) {
         // wait for the slot to be free; give up if the consumers have finished (EOS / abort)
         unsigned long long t0 = 0; unsigned spins = 0;
@@ -662,152 +838,229 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     }
   } else {
     // ===== consumer warps =====
+    constexpr int R = 2 * NPOS;
+    constexpr int PAR = (NPOS == 1) ? 4 : 1;
     const int g = lane >> 2, tig = lane & 3, pp = g >> 1, bb = g & 1;
-    RingPos rp{0, 0u, 0};
-    unsigned bar_target = 0;
+    const int kwb = warp * 128, kw = kwb + tig * 8;
+    float* stage = stage_all + warp * MAXROWS * STAGE_LD;
+    RingPos rp{0, 0u, 0, 0ull, 0ull};
     int pos0 = __ldcg(&p.st->pos);
     int n_gen = __ldcg(&p.st->n_gen);
     int n_done = 0;
+    float xres[4][8];     // residual stream of row g, replicated in every CTA
     float xs[4][8];
     uint32_t A[4][8];
-    const int HS = T3_MAX_NPOS * 2 * T3_H;   // one hres buffer
     int prof_k = 0;
+    int qq = 0;           // running index of the norm whose gains sit in lnbuf[qq & 1]
+    ln_prefetch(lnbuf, 0, p.ln1, tid);
 #define T3_PROF() do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it) p.prof[prof_k++] = gtime_ns(); } while (0)
+#define T3_SUB(k) do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5) p.prof[200 + (k)] = gtime_ns(); } while (0)
+#define T3_ROW_OK(gg) ((gg) < 2 * npos && ((gg) & 1) < p.B)
 
     for (int it = 0; it < n_iters; ++it) {
       int npos = 1;
       if (p.mode == 1) {
         T3_PROF();
-        if (c == 0) sample_phase(p, it, n_gen, scr, ctl, warp, lane);
-        grid_barrier(p, bar_target, ctl);
-        T3_PROF();
+        if (c == 0) sample_phase(p, it, n_gen, scr, seen, ctl, warp, lane);
+        // control word of this iteration: token id | stop bit
+        const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
+        unsigned long long w;
+        unsigned spins = 0; unsigned long long t0 = 0;
+        for (;;) {
+          w = ll_ld1(p.ll + LL_EMB + T3_H);
+          if (ll_ok(w, fl)) break;
+          if (poll_timeout(spins, t0, ctl, p.st)) break;
+        }
         ++n_gen; ++n_done;
-        if (__ldcg(&p.st->stop) || ctl->abort) break;
+        if (((unsigned)w >> 31) || ctl->abort) break;
+        T3_PROF();
       } else {
-        npos = min(T3_MAX_NPOS, p.P - it * T3_MAX_NPOS);
+        npos = min(NPOS, p.P - it * NPOS);
       }
-      const bool active = (g < 2 * npos) && (bb < p.B);
-      const int kw = warp * 128 + tig * 8;
+      const int nrows = 2 * npos;
+      const bool active = T3_ROW_OK(g);
 
       for (int l = 0; l < L; ++l) {
         // ---------- phase A: x_l = residual; RMSNorm; fused q|k|v GEMV ----------
         {
-          Piece pc[6];
-          int np;
+          T3_SUB(0);
           if (l == 0) {
-            if (p.mode == 0) pc[0] = Piece{p.embeds + (size_t)it * T3_MAX_NPOS * T3_H, T3_H, p.P * T3_H};
-            else pc[0] = Piece{p.hres + HS, 2 * T3_H, T3_H};
-            np = 1;
-          } else {
-            pc[0] = Piece{p.hres + ((l - 1) & 1) * HS, 2 * T3_H, T3_H};
-            pc[1] = Piece{p.oproj, 2 * T3_H, T3_H};
-            for (int s = 0; s < 4; ++s) pc[2 + s] = Piece{p.down + s * HS, 2 * T3_H, T3_H};
-            np = 6;
-          }
-          load_x<6>(xs, pc, np, active, pp, bb, kw);
-          if (c == 0 && active) {
-            float* dst = p.hres + (l & 1) * HS + (pp * 2 + bb) * T3_H + kw;
+            if (p.mode == 0) {
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-              *reinterpret_cast<float4*>(dst + jj * 32) = make_float4(xs[jj][0], xs[jj][1], xs[jj][2], xs[jj][3]);
-              *reinterpret_cast<float4*>(dst + jj * 32 + 4) = make_float4(xs[jj][4], xs[jj][5], xs[jj][6], xs[jj][7]);
+              for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xres[jj][e] = 0.f;
+              if (active) {
+                const float* src = p.embeds + ((size_t)bb * p.P + (size_t)it * NPOS + pp) * T3_H + kw;
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                  const float4 a = __ldg(reinterpret_cast<const float4*>(src + jj * 32));
+                  const float4 b = __ldg(reinterpret_cast<const float4*>(src + jj * 32 + 4));
+                  xres[jj][0] = a.x; xres[jj][1] = a.y; xres[jj][2] = a.z; xres[jj][3] = a.w;
+                  xres[jj][4] = b.x; xres[jj][5] = b.y; xres[jj][6] = b.z; xres[jj][7] = b.w;
+                }
+              }
+            } else {
+              Piece pc[1] = {Piece{p.ll + LL_EMB, 0, ll_flag(it, L, 0, LLP_EMB)}};
+              ll_stage<R, 1>(stage, pc, 1, kwb, nrows, p.B, lane, ctl, p.st);
+              stage_read(xres, stage, g, tig);
             }
+          } else {
+            Piece pc[T3_DOWN_KS];
+#pragma unroll
+            for (int s = 0; s < T3_DOWN_KS; ++s)
+              pc[s] = Piece{p.ll + LL_DOWN + (size_t)s * MAXROWS * T3_H, T3_H, ll_flag(it, L, l - 1, LLP_DOWN)};
+            ll_stage<R, PAR>(stage, pc, T3_DOWN_KS, kwb, nrows, p.B, lane, ctl, p.st);
+            stage_read(xs, stage, g, tig);
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+              for (int e = 0; e < 8; ++e) xres[jj][e] += xs[jj][e];
           }
-          rmsnorm_rows(xs, p.ln1 + (size_t)l * T3_H, kw, ssq, warp, lane);
+          T3_SUB(1);
+          rmsnorm_rows(xs, xres, lnbuf, qq, kw, ssq, warp, lane);
+          ++qq;
+          ln_prefetch(lnbuf, qq, p.ln2 + (size_t)l * T3_H, tid);
           make_frags(A, xs);
+          T3_SUB(2);
           const int n = t3_plan_count(PH_QKV, c, G);
           consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
+          T3_SUB(3);
           cbar();
+          T3_SUB(4);
+          const unsigned fl = ll_flag(it, L, l, LLP_QKV);
           for (int idx = tid; idx < n * 64; idx += NCONS) {
             const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-            if (gg < 2 * npos && (gg & 1) < p.B)
-              p.qkv[(size_t)gg * 3072 + t3_plan_unit(PH_QKV, c, G, j) * 8 + nn] = red_sum(red, j, o);
+            if (T3_ROW_OK(gg))
+              ll_store(p.ll + LL_QKV + (size_t)gg * 3072 + t3_plan_unit(PH_QKV, c, G, j) * 8 + nn, red_sum(red, j, o), fl);
           }
+          T3_SUB(5);
+          cbar();
+          T3_SUB(6);
         }
-        grid_barrier(p, bar_target, ctl);
         T3_PROF();
-        // ---------- phase B: RoPE, KV append, split-KV attention ----------
-        attn_phase<KVT>(p, l, pos0, npos, scr, warp, lane);
-        grid_barrier(p, bar_target, ctl);
+        // ---------- phase B: RoPE, KV append, split-KV attention, split combine ----------
+        attn_phase<KVT, NPOS>(p, it, l, pos0, npos, scr, warp, lane, ctl);
         T3_PROF();
         // ---------- phase C: o_proj ----------
         {
-          load_attn_x(xs, p, active, pp, bb, warp, tig);
+          Piece pc[1] = {Piece{p.ll + LL_ATTN, T3_H, ll_flag(it, L, l, LLP_ATTN)}};
+          ll_stage<R, 1>(stage, pc, 1, kwb, nrows, p.B, lane, ctl, p.st);
+          stage_read(xs, stage, g, tig);
           make_frags(A, xs);
           const int n = t3_plan_count(PH_O, c, G);
+          cbar();    // the attention phase used the scratch that `red` aliases
           consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
           cbar();
+          const unsigned fl = ll_flag(it, L, l, LLP_OPROJ);
           for (int idx = tid; idx < n * 64; idx += NCONS) {
             const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-            if (gg < 2 * npos && (gg & 1) < p.B)
-              p.oproj[(size_t)gg * T3_H + t3_plan_unit(PH_O, c, G, j) * 8 + nn] = red_sum(red, j, o);
+            if (T3_ROW_OK(gg))
+              ll_store(p.ll + LL_OPROJ + (size_t)gg * T3_H + t3_plan_unit(PH_O, c, G, j) * 8 + nn, red_sum(red, j, o), fl);
           }
+          cbar();
         }
-        grid_barrier(p, bar_target, ctl);
         T3_PROF();
-        // ---------- phase D: post-attention RMSNorm; gate/up GEMV; SwiGLU ----------
+        // ---------- phase D: residual add; post-attention RMSNorm; gate/up GEMV; SwiGLU ----------
         {
-          Piece pc[2] = {Piece{p.hres + (l & 1) * HS, 2 * T3_H, T3_H}, Piece{p.oproj, 2 * T3_H, T3_H}};
-          load_x<2>(xs, pc, 2, active, pp, bb, kw);
-          rmsnorm_rows(xs, p.ln2 + (size_t)l * T3_H, kw, ssq, warp, lane);
+          T3_SUB(8);
+          Piece pc[1] = {Piece{p.ll + LL_OPROJ, T3_H, ll_flag(it, L, l, LLP_OPROJ)}};
+          ll_stage<R, 1>(stage, pc, 1, kwb, nrows, p.B, lane, ctl, p.st);
+          stage_read(xs, stage, g, tig);
+          T3_SUB(9);
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) xres[jj][e] += xs[jj][e];
+          rmsnorm_rows(xs, xres, lnbuf, qq, kw, ssq, warp, lane,
+                       (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5) ? p.prof + 216 : nullptr);
+          ++qq;
+          {
+            const bool head_next = (l == L - 1) && (p.mode == 1 || it == n_iters - 1);
+            ln_prefetch(lnbuf, qq, head_next ? p.final_norm : p.ln1 + (size_t)((l + 1) % L) * T3_H, tid);
+          }
           make_frags(A, xs);
+          T3_SUB(10);
           const int n = t3_plan_count(PH_GU, c, G);
           consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
+          T3_SUB(11);
           cbar();
+          T3_SUB(12);
+          const unsigned fl = ll_flag(it, L, l, LLP_ACT);
           for (int idx = tid; idx < n * 32; idx += NCONS) {
             const int j = idx >> 5, o2 = idx & 31, gg = o2 >> 2, nn = o2 & 3;
-            if (gg < 2 * npos && (gg & 1) < p.B) {
+            if (T3_ROW_OK(gg)) {
               const float gate = red_sum(red, j, gg * 8 + nn), up = red_sum(red, j, gg * 8 + 4 + nn);
               const float silu = gate / (1.0f + __expf(-gate));
-              p.act[(size_t)gg * T3_INTER + t3_plan_unit(PH_GU, c, G, j) * 4 + nn] = silu * up;
+              ll_store(p.ll + LL_ACT + (size_t)gg * T3_INTER + t3_plan_unit(PH_GU, c, G, j) * 4 + nn, silu * up, fl);
             }
           }
+          T3_SUB(13);
+          cbar();
+          T3_SUB(14);
         }
-        grid_barrier(p, bar_target, ctl);
         T3_PROF();
         // ---------- phase E: down_proj (k-slice s of this CTA) ----------
         {
           const int n = t3_plan_count(PH_DOWN, c, G);
           if (n > 0) {
-            const int u0 = t3_plan_unit(PH_DOWN, c, G, 0), s = u0 % T3_DOWN_KS;
-            Piece pc[1] = {Piece{p.act, 2 * T3_INTER, T3_INTER}};
-            load_x<1>(xs, pc, 1, active, pp, bb, s * 1024 + kw);
+            const int s = t3_plan_unit(PH_DOWN, c, G, 0) % T3_DOWN_KS;
+            Piece pc[1] = {Piece{p.ll + LL_ACT, T3_INTER, ll_flag(it, L, l, LLP_ACT)}};
+            ll_stage<R, 1>(stage, pc, 1, s * 1024 + kwb, nrows, p.B, lane, ctl, p.st);
+            stage_read(xs, stage, g, tig);
             make_frags(A, xs);
             consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
           }
           cbar();
+          const unsigned fl = ll_flag(it, L, l, LLP_DOWN);
           for (int idx = tid; idx < n * 64; idx += NCONS) {
             const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-            if (gg < 2 * npos && (gg & 1) < p.B) {
+            if (T3_ROW_OK(gg)) {
               const int u = t3_plan_unit(PH_DOWN, c, G, j);
-              p.down[(size_t)(u % T3_DOWN_KS) * HS + gg * T3_H + (u / T3_DOWN_KS) * 8 + nn] = red_sum(red, j, o);
+              ll_store(p.ll + LL_DOWN + (size_t)(u % T3_DOWN_KS) * MAXROWS * T3_H + (size_t)gg * T3_H +
+                           (u / T3_DOWN_KS) * 8 + nn, red_sum(red, j, o), fl);
             }
           }
+          cbar();
         }
-        grid_barrier(p, bar_target, ctl);
         T3_PROF();
       }
       // ---------- phase F: final RMSNorm + speech_head (t3_hf_backend.py:100-103) ----------
       if (p.mode == 1 || it == n_iters - 1) {
-        Piece pc[6];
-        pc[0] = Piece{p.hres + ((L - 1) & 1) * HS, 2 * T3_H, T3_H};
-        pc[1] = Piece{p.oproj, 2 * T3_H, T3_H};
-        for (int s = 0; s < 4; ++s) pc[2 + s] = Piece{p.down + s * HS, 2 * T3_H, T3_H};
-        load_x<6>(xs, pc, 6, active, pp, bb, kw);
-        rmsnorm_rows(xs, p.final_norm, kw, ssq, warp, lane);
+        Piece pc[T3_DOWN_KS];
+#pragma unroll
+        for (int s = 0; s < T3_DOWN_KS; ++s)
+          pc[s] = Piece{p.ll + LL_DOWN + (size_t)s * MAXROWS * T3_H, T3_H, ll_flag(it, L, L - 1, LLP_DOWN)};
+        ll_stage<R, PAR>(stage, pc, T3_DOWN_KS, kwb, nrows, p.B, lane, ctl, p.st);
+        stage_read(xs, stage, g, tig);
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) xres[jj][e] += xs[jj][e];
+        rmsnorm_rows(xs, xres, lnbuf, qq, kw, ssq, warp, lane);
+        ++qq;
+        ln_prefetch(lnbuf, qq, p.ln1, tid);
         make_frags(A, xs);
         consume_units(nhead, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
         cbar();
         const int plast = npos - 1;
+        const unsigned fl = ll_flag(it, L, L, LLP_LOGITS);
         for (int idx = tid; idx < nhead * 64; idx += NCONS) {
           const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
           const int row = t3_plan_unit(PH_HEAD, c, G, j) * 8 + nn;
-          if ((gg >> 1) == plast && (gg & 1) < p.B && row < T3_VOCAB)
-            p.logits[(size_t)(gg & 1) * T3_VOCAB + row] = red_sum(red, j, o);
+          if ((gg >> 1) == plast && (gg & 1) < p.B && row < T3_VOCAB) {
+            const float v = red_sum(red, j, o);
+            p.logits[(size_t)(gg & 1) * T3_VOCAB + row] = v;     // plain copy: read by the next launch
+            if (p.mode == 1) ll_store(p.ll + LL_LOGITS + (size_t)(gg & 1) * VOCAB_PAD + row, v, fl);
+          }
         }
-        grid_barrier(p, bar_target, ctl);
+        cbar();
         T3_PROF();
       }
+#ifdef T3_DEBUG_WAIT
+      if (p.prof && c == 0 && tid == 0 && it == p.prof_it) { p.prof[230] = rp.wait_ns; p.prof[231] = rp.mma_ns; p.prof[232] = rp.k; }
+      rp.wait_ns = 0; rp.mma_ns = 0;
+#endif
       pos0 += npos;
       if (ctl->abort) break;
     }
@@ -856,6 +1109,15 @@ extern "C" int cbx_t3_plan_unit(int ph, int c, int G, int j) { return t3_plan_un
 
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+template <typename F>
+static int t3_prepare_kernel(F fn) {
+  CBX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
+  int occ = 0;
+  CBX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, NTHREADS, SMEM_TOTAL));
+  CBX_CHECK(occ >= 1, "cbx_t3_create: megakernel does not fit on an SM (smem %d B)", SMEM_TOTAL);
+  return CBX_OK;
+}
+
 extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_t3** out) {
   CBX_CHECK(cfg && w && out, "cbx_t3_create: null argument");
   CBX_CHECK(cfg->n_layers >= 1 && cfg->n_layers <= 64, "cbx_t3_create: n_layers %d out of range", cfg->n_layers);
@@ -865,7 +1127,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
   CBX_CHECK(prop.major == 10, "cbx_t3_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
   const int G = prop.multiProcessorCount;
-  CBX_CHECK(G >= 129 && G * 0 + (1025 + G - 1) / G <= T3_MAXU, "cbx_t3_create: %d SMs unsupported by the plan", G);
+  CBX_CHECK(G >= 129 && (1025 + G - 1) / G <= T3_MAXU, "cbx_t3_create: %d SMs unsupported by the plan", G);
   int coop = 0;
   CBX_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, cfg->device));
   CBX_CHECK(coop, "cbx_t3_create: device lacks cooperative launch");
@@ -877,14 +1139,9 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
   const size_t o_k = take(kv_bytes), o_v = take(kv_bytes);
-  const size_t o_qkv = take(sizeof(float) * T3_MAX_NPOS * 2 * 3072);
-  const size_t o_hres = take(sizeof(float) * 2 * T3_MAX_NPOS * 2 * T3_H);
-  const size_t o_oproj = take(sizeof(float) * T3_MAX_NPOS * 2 * T3_H);
-  const size_t o_act = take(sizeof(float) * T3_MAX_NPOS * 2 * T3_INTER);
-  const size_t o_down = take(sizeof(float) * T3_DOWN_KS * T3_MAX_NPOS * 2 * T3_H);
+  const size_t o_ll = take(LL_WORDS * 8);
   const size_t o_logits = take(sizeof(float) * 2 * T3_VOCAB);
-  const size_t o_part = take(sizeof(float) * T3_MAX_NPOS * 32 * MAXS * PART_STRIDE);
-  const size_t o_bar = take(256), o_st = take(256), o_seen = take(VOCAB_PAD);
+  const size_t o_st = take(256), o_seen = take(VOCAB_PAD);
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_t3_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -901,17 +1158,15 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   p.rope_cos = w->rope_cos; p.rope_sin = w->rope_sin;
   p.n_layers = cfg->n_layers; p.max_pos = cfg->max_pos;
   p.kcache = s + o_k; p.vcache = s + o_v;
-  p.qkv = reinterpret_cast<float*>(s + o_qkv); p.hres = reinterpret_cast<float*>(s + o_hres);
-  p.oproj = reinterpret_cast<float*>(s + o_oproj); p.act = reinterpret_cast<float*>(s + o_act);
-  p.down = reinterpret_cast<float*>(s + o_down); p.logits = reinterpret_cast<float*>(s + o_logits);
-  p.part = reinterpret_cast<float*>(s + o_part);
-  p.bar = reinterpret_cast<unsigned*>(s + o_bar); p.st = reinterpret_cast<T3State*>(s + o_st);
+  p.ll = reinterpret_cast<unsigned long long*>(s + o_ll);
+  p.logits = reinterpret_cast<float*>(s + o_logits);
+  p.st = reinterpret_cast<T3State*>(s + o_st);
   p.seen = s + o_seen;
-  CBX_CUDA(cudaFuncSetAttribute(t3_megakernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
-  CBX_CUDA(cudaFuncSetAttribute(t3_megakernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
-  int occ = 0;
-  CBX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, t3_megakernel<__nv_bfloat16>, NTHREADS, SMEM_TOTAL));
-  CBX_CHECK(occ >= 1, "cbx_t3_create: megakernel does not fit on an SM (smem %d B)", SMEM_TOTAL);
+  int rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16, 1>);
+  if (!rc) rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16, T3_MAX_NPOS>);
+  if (!rc) rc = t3_prepare_kernel(t3_megakernel<float, 1>);
+  if (!rc) rc = t3_prepare_kernel(t3_megakernel<float, T3_MAX_NPOS>);
+  if (rc) { cudaFree(h->slab); delete h; return CBX_ERR; }
   *out = h;
   return CBX_OK;
 }
@@ -924,14 +1179,16 @@ extern "C" int cbx_t3_destroy(cbx_t3* h) {
 }
 
 static int t3_launch(cbx_t3* h, T3Params& p, cudaStream_t st) {
-  CBX_CUDA(cudaMemsetAsync(p.bar, 0, sizeof(unsigned), st));
+  CBX_CUDA(cudaMemsetAsync(p.ll, 0, LL_WORDS * 8, st));     // flags restart at 1 in every launch
   void* args[] = {&p};
-  const void* fn = h->cfg.kv_fp32 ? (const void*)t3_megakernel<float> : (const void*)t3_megakernel<__nv_bfloat16>;
+  const void* fn;
+  if (p.mode == 0) fn = h->cfg.kv_fp32 ? (const void*)t3_megakernel<float, T3_MAX_NPOS>
+                                       : (const void*)t3_megakernel<__nv_bfloat16, T3_MAX_NPOS>;
+  else fn = h->cfg.kv_fp32 ? (const void*)t3_megakernel<float, 1> : (const void*)t3_megakernel<__nv_bfloat16, 1>;
   CBX_CUDA(cudaLaunchCooperativeKernel(fn, dim3(h->G), dim3(NTHREADS), args, SMEM_TOTAL, st));
   h->launches += 1;
   return CBX_OK;
 }
-
 extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void* stream) {
   CBX_CHECK(h && embeds, "cbx_t3_prefill: null argument");
   CBX_CHECK(B == 1 || B == 2, "cbx_t3_prefill: B must be 1 or 2 (got %d)", B);

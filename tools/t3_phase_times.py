@@ -28,4 +28,12 @@ for it in (8, 200):
     for nm, v in agg.items():
         v2 = sorted(v)
         print(f"  {nm:7s} n={len(v):3d} mean {sum(v)/len(v)/1e3:6.2f} us  min {v2[0]/1e3:6.2f}  max {v2[-1]/1e3:6.2f}  sum {sum(v)/1e3:7.1f}")
+    sub = s[200:215]
+    lab = ["A:stage", "A:rmsnorm+frags", "A:consume", "A:cbar", "A:epilogue", "A:cbar2", "-", "-", "D:stage", "D:rmsnorm+frags",
+           "D:consume", "D:cbar", "D:epilogue", "D:cbar2"]
+    print("  sub-phase (layer 5, CTA 0 thread 0):", ", ".join(f"{lab[i]} {(sub[i+1]-sub[i])/1e3:.2f}" for i in range(14) if lab[i] != "-"))
+    dd = s[216:221]
+    print("  D rmsnorm detail: sumsq+shfl+sts %.2f, cp.async.wait %.2f, cbar %.2f, scale+ln %.2f; stage_end->rms_start %.2f, rms_end->frags_end %.2f" % (
+        (dd[1]-dd[0])/1e3, (dd[2]-dd[1])/1e3, (dd[3]-dd[2])/1e3, (dd[4]-dd[3])/1e3, (dd[0]-s[209])/1e3, (s[210]-dd[4])/1e3))
+    print(f"  ring (CTA 0 warp 0, whole iteration): waiting on full barriers {s[230]/1e3:.1f} us, load+mma+arrive {s[231]/1e3:.1f} us, units so far {s[232]}")
 _lib.check(t3._lib.cbx_t3_set_profile(t3._h, None, -1))
