@@ -346,3 +346,16 @@ def s3gen_ref(seed: int = 4, prompt_len: int = 150) -> Dict[str, torch.Tensor]:
 def speech_tokens(n: int, seed: int = 5) -> torch.Tensor:
     g = torch.Generator().manual_seed(seed)
     return torch.randint(0, S3_VOCAB, (1, n), generator=g)
+
+
+def cfm_inputs(L: int, seed: int = 6, prompt_frames: int | None = None) -> Dict[str, torch.Tensor]:
+    """Inputs of `CausalConditionalCFM.forward` (flow_matching.py:194-218) for one utterance of L mel
+    frames: mu (1,80,L) encoder output, spks (1,80) projected x-vector, cond (1,80,L) = prompt mel in
+    the first `prompt_frames` frames and zeros after (flow.py:268-270), z = the fixed noise."""
+    g = torch.Generator().manual_seed(seed)
+    mu = torch.randn(1, 80, L, generator=g)
+    spks = torch.randn(1, 80, generator=g) * 0.5
+    pf = L // 3 if prompt_frames is None else prompt_frames
+    cond = torch.zeros(1, 80, L)
+    cond[:, :, :pf] = (torch.randn(1, 80, pf, generator=g) * 2.0 - 5.0).clamp(-11.5, 2.0)
+    return dict(mu=mu, spks=spks, cond=cond, z=cfm_noise()[:, :, :L].clone())

@@ -149,6 +149,51 @@ def make_t3():
     print("[t3] wrote tests/golden/t3_golden.safetensors")
 
 
+def make_cfm():
+    """Reference ConditionalDecoder / CausalConditionalCFM vs oracle/cfm_oracle.py; golden outputs."""
+    from oracle import cfm_oracle as CO
+    torch.manual_seed(0)
+    sd_flow = S.make_state_dict("flow")
+    flow = R.build_flow()
+    missing, unexpected = flow.load_state_dict(sd_flow, strict=False)
+    assert not unexpected and all(k.endswith("rand_noise") for k in missing), (missing, unexpected)
+    cfm = flow.decoder
+    est = cfm.estimator
+    pfx = "decoder.estimator."
+    out = {}
+    # (1) one estimator call, batch 2 (CFG packing of flow_matching.py:95-108), L = 96
+    L = 96
+    inp = S.cfm_inputs(L)
+    t = torch.tensor([0.3, 0.3])
+    x_in = torch.cat([inp["z"], inp["z"]], 0)
+    mu_in = torch.cat([inp["mu"], torch.zeros_like(inp["mu"])], 0)
+    sp_in = torch.cat([inp["spks"], torch.zeros_like(inp["spks"])], 0)
+    c_in = torch.cat([inp["cond"], torch.zeros_like(inp["cond"])], 0)
+    mask = torch.ones(2, 1, L)
+    with torch.inference_mode():
+        ref = est(x_in, mask, mu_in, t, sp_in, c_in)
+        mine = CO.estimator(sd_flow, x_in, mask, mu_in, t, sp_in, c_in, pfx)
+    d = (ref - mine).abs().max().item()
+    print(f"[cfm] estimator L={L}: max-abs restatement vs reference {d:.3e} (ref rms {ref.pow(2).mean().sqrt():.3f})")
+    assert d < 1e-3
+    out["est_t0.3_L96"] = ref.clone()
+    # (2) the 10-step Euler solve through CausalConditionalCFM.forward with the injected noise, L = 96 and 130
+    for L in (96, 130):
+        inp = S.cfm_inputs(L, seed=6 + L)
+        cfm.rand_noise = S.cfm_noise()
+        t0 = time.time()
+        with torch.inference_mode():
+            ref, _ = cfm(mu=inp["mu"], mask=torch.ones(1, 1, L), n_timesteps=10, spks=inp["spks"], cond=inp["cond"])
+            mine = CO.solve_euler(sd_flow, inp["z"], inp["mu"], inp["spks"], inp["cond"], pfx=pfx)
+        rel = ((ref - mine).norm() / ref.norm()).item()
+        print(f"[cfm] solve_euler L={L}: rel-L2 restatement vs reference {rel:.3e} ({time.time() - t0:.1f}s)")
+        assert rel < 1e-4
+        out[f"mel_L{L}"] = ref.clone()
+    out["t_span"] = CO.t_schedule(10)
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(GOLD, "cfm_golden.safetensors"))
+    print("[cfm] wrote tests/golden/cfm_golden.safetensors")
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["t3", "cfm", "hift"]
     torch.set_num_threads(os.cpu_count() or 8)
