@@ -28,6 +28,11 @@ class CbxSampleParams(C.Structure):
                 ("seed", C.c_uint64)]
 
 
+class CbxCfmWeights(C.Structure):
+    _fields_ = [("bf16_blob", C.c_void_p), ("f32_blob", C.c_void_p), ("bf16_off", C.POINTER(C.c_int64)),
+                ("f32_off", C.POINTER(C.c_int64))]
+
+
 # every symbol include/cbx.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "cbx_last_error": (C.c_char_p, []),
@@ -41,6 +46,13 @@ SYMBOLS = {
     "cbx_t3_decode": (C.c_int, [C.c_void_p, C.POINTER(CbxSampleParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p]),
     "cbx_t3_set_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "cbx_cfm_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxCfmWeights), C.POINTER(C.c_void_p)]),
+    "cbx_cfm_destroy": (C.c_int, [C.c_void_p]),
+    "cbx_cfm_estimator": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int,
+                                    C.c_void_p, C.c_void_p]),
+    "cbx_cfm_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_void_p, C.c_void_p]),
+    "cbx_cfm_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "cbx_t3_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                C.POINTER(C.c_int64)]),
 }

@@ -1,0 +1,166 @@
+// Full (bidirectional) multi-head attention of the S3Gen estimator's BasicTransformerBlock
+// (reference: matcha/transformer.py:196-204 -> diffusers 0.29.0 Attention/AttnProcessor2_0: 8 heads x 64,
+// scale 1/8, key-padding bias only — all-zero for one un-padded utterance, decoder.py:269-270).
+// Flash-attention structure: a CTA owns 64 query rows of one (batch, head); K/V tiles of 64 keys are
+// double-buffered in shared memory with cp.async; S = QK^T and O += PV run on mma.sync m16n8k16 bf16
+// with fp32 accumulation and an fp32 online softmax.  (Round-1 kernel: the legacy tensor-core path;
+// the tcgen05 version is listed in DESIGN.md as the next step for this stage.)
+#include "common.cuh"
+
+namespace cbx {
+namespace {
+
+constexpr int AT_BM = 64, AT_BN = 64, AT_D = 64, AT_LD = 72;   // padded smem row stride (elements)
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
+}
+
+// qkv: bf16 [B][L][ld_qkv] with q at column 0, k at 512, v at 1024 (+ head*64); out: bf16 [B][L][512]
+__global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
+                                                      int L, int ld_qkv) {
+  __shared__ __align__(16) __nv_bfloat16 sQ[AT_BM * AT_LD];
+  __shared__ __align__(16) __nv_bfloat16 sK[2][AT_BN * AT_LD];
+  __shared__ __align__(16) __nv_bfloat16 sV[2][AT_BN * AT_LD];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q0 = blockIdx.x * AT_BM, head = blockIdx.y, b = blockIdx.z;
+  const __nv_bfloat16* base = qkv + (size_t)b * L * ld_qkv + head * AT_D;
+
+  auto load_tile = [&](__nv_bfloat16* dst, int col_off, int row0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ch = tid + i * 128, r = ch >> 3, c8 = ch & 7;
+      const bool ok = row0 + r < L;
+      cp_async16(dst + r * AT_LD + c8 * 8, base + (size_t)(ok ? row0 + r : 0) * ld_qkv + col_off + c8 * 8, ok);
+    }
+  };
+  const int ntiles = (L + AT_BN - 1) / AT_BN;
+  load_tile(sQ, 0, q0);
+  load_tile(sK[0], 512, 0);
+  load_tile(sV[0], 1024, 0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+
+  float o[8][4], m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  uint32_t qf[4][4];
+  const float sc = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
+
+  for (int kt = 0; kt < ntiles; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < ntiles) {
+      load_tile(sK[buf ^ 1], 512, (kt + 1) * AT_BN);
+      load_tile(sV[buf ^ 1], 1024, (kt + 1) * AT_BN);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    if (kt == 0) {
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        ldsm_x4(qf[ks], sQ + (warp * 16 + (lane & 15)) * AT_LD + ks * 16 + (lane >> 4) * 8);
+    }
+    // ---- S = Q K^T (16 x 64 per warp) ----
+    float s[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f; }
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {     // pairs of 8-key tiles
+        uint32_t kb[4];
+        ldsm_x4(kb, sK[buf] + ((np * 2 + (lane >> 4)) * 8 + (lane & 7)) * AT_LD + ks * 16 + ((lane >> 3) & 1) * 8);
+        mma_bf16_16816(s[np * 2], qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], kb[0], kb[1]);
+        mma_bf16_16816(s[np * 2 + 1], qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], kb[2], kb[3]);
+      }
+    }
+    // ---- scale, tail mask, online softmax (rows g = lane>>2 and g + 8) ----
+    const int kbase = kt * AT_BN + (lane & 3) * 2;
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int key = kbase + i * 8 + (e & 1);
+        const float v = (key < L) ? s[i][e] * sc : -INFINITY;
+        s[i][e] = v;
+        mx[e >> 1] = fmaxf(mx[e >> 1], v);
+      }
+    }
+    float corr[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+      const float mn = fmaxf(m_run[r], mx[r]);
+      corr[r] = exp2f(m_run[r] - mn);
+      m_run[r] = mn;
+    }
+    float ls[2] = {0.f, 0.f};
+    uint32_t pf[4][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float p0 = exp2f(s[i][0] - m_run[0]), p1 = exp2f(s[i][1] - m_run[0]);
+      const float p2 = exp2f(s[i][2] - m_run[1]), p3 = exp2f(s[i][3] - m_run[1]);
+      ls[0] += p0 + p1; ls[1] += p2 + p3;
+      pf[i >> 1][(i & 1) * 2] = pack_bf16x2(p0, p1);
+      pf[i >> 1][(i & 1) * 2 + 1] = pack_bf16x2(p2, p3);
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) l_run[r] = l_run[r] * corr[r] + ls[r];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { o[i][0] *= corr[0]; o[i][1] *= corr[0]; o[i][2] *= corr[1]; o[i][3] *= corr[1]; }
+    // ---- O += P V ----
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+      for (int dp = 0; dp < 4; ++dp) {     // pairs of 8-wide d tiles
+        uint32_t vb[4];
+        ldsm_x4_t(vb, sV[buf] + (kk * 16 + (lane & 15)) * AT_LD + (dp * 2 + (lane >> 4)) * 8);
+        mma_bf16_16816(o[dp * 2], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], vb[0], vb[1]);
+        mma_bf16_16816(o[dp * 2 + 1], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], vb[2], vb[3]);
+      }
+    }
+    __syncthreads();
+  }
+  // ---- normalise and store ----
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+  const int g = lane >> 2, c2 = (lane & 3) * 2;
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int t = q0 + warp * 16 + g + r * 8;
+    if (t < L) {
+      const float inv = 1.0f / l_run[r];
+      __nv_bfloat16* dst = out + ((size_t)b * L + t) * 512 + head * AT_D + c2;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf16x2(o[i][r * 2] * inv, o[i][r * 2 + 1] * inv);
+    }
+  }
+}
+
+}  // namespace
+
+int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, cudaStream_t st) {
+  dim3 grid((L + AT_BM - 1) / AT_BM, 8, B);
+  s3_attn_kernel<<<grid, 128, 0, st>>>(qkv, out, L, ld_qkv);
+  CBX_CUDA(cudaGetLastError());
+  return CBX_OK;
+}
+
+}  // namespace cbx

@@ -1,0 +1,306 @@
+// S3Gen conditional flow-matching solve on sm_100a: the 10-step Euler/CFG loop of
+// ConditionalCFM.solve_euler (reference src/chatterbox/models/s3gen/flow_matching.py:72-123) around the
+// ConditionalDecoder estimator (decoder.py:233-317), as a fixed sequence of tcgen05 GEMMs
+// (s3_gemm.cu), flash attention (s3_attn.cu) and a few element-wise kernels, all on one stream.
+// Activations are channel-last [2 (cond, uncond)][L][C]; the residual stream is fp32, GEMM operands bf16.
+#include "s3_gemm.cuh"
+#include "../../include/cbx.h"
+#include <map>
+#include <vector>
+
+namespace cbx {
+int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, cudaStream_t st);
+}
+using namespace cbx;
+
+namespace {
+
+constexpr int NRES = 14, NTFM = 56, C = 256, CIN = 320, NMEL = 80;
+enum { BF_RES = 0, BF_TFM = NRES * 3, BF_TAIL = BF_TFM + NTFM * 4, BF_COUNT = BF_TAIL + 4 };
+enum { F_RES = 0, F_TFM = NRES * 7, F_TAIL = F_TFM + NTFM * 7, F_TIME = F_TAIL + 6, F_COUNT = F_TIME + 6 };
+
+__device__ __forceinline__ float mish_d(float x) {
+  const float sp = (x > 20.f) ? x : log1pf(expf(x));
+  return x * tanhf(sp);
+}
+
+// ---- time embedding: SinusoidalPosEmb(320, scale 1000) -> Linear -> SiLU -> Linear; Mish kept for the resnet MLPs
+__global__ void k_temb(const float* __restrict__ tvals, const float* __restrict__ w1, const float* __restrict__ b1,
+                       const float* __restrict__ w2, const float* __restrict__ b2, float* __restrict__ mish_temb) {
+  __shared__ float emb[320];
+  __shared__ float h1[1024];
+  const int s = blockIdx.x, n = threadIdx.x;
+  const float t = tvals[s];
+  if (n < 160) {
+    const float f = expf((float)n * -(logf(10000.f) / 159.f));
+    const float a = 1000.f * t * f;
+    emb[n] = sinf(a);
+    emb[160 + n] = cosf(a);
+  }
+  __syncthreads();
+  float acc = b1[n];
+  for (int k = 0; k < 320; ++k) acc += w1[(size_t)n * 320 + k] * emb[k];
+  h1[n] = acc / (1.f + expf(-acc));
+  __syncthreads();
+  acc = b2[n];
+  for (int k = 0; k < 1024; ++k) acc += w2[(size_t)n * 1024 + k] * h1[k];
+  mish_temb[(size_t)s * 1024 + n] = mish_d(acc);
+}
+// resnet MLP: tvec[s][r][2][256] = Linear(Mish(temb))  (matcha/decoder.py:50,57), duplicated for both CFG rows
+__global__ void k_tvec(const float* __restrict__ mish_temb, const float* __restrict__ w, const float* __restrict__ bias,
+                       float* __restrict__ tvec) {
+  const int r = blockIdx.x, s = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* x = mish_temb + (size_t)s * 1024;
+  for (int n = warp; n < C; n += blockDim.x / 32) {
+    const float* wr = w + ((size_t)r * C + n) * 1024;
+    float acc = 0.f;
+    for (int k = lane; k < 1024; k += 32) acc += wr[k] * x[k];
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      const float v = acc + bias[r * C + n];
+      float* o = tvec + ((size_t)(s * NRES + r) * 2) * C;
+      o[n] = v;
+      o[C + n] = v;
+    }
+  }
+}
+// xin[b][t][0:80] = x, [80:160] = mu, [160:240] = spks, [240:320] = cond (decoder.py:254-260); inputs are the
+// reference's channel-first fp32 tensors per CFG row; a null row-1 pointer means zeros (flow_matching.py:95-108)
+struct PackIn { const float *x[2], *mu[2], *spks[2], *cond[2]; };
+__global__ void k_pack(PackIn in, float* __restrict__ x, __nv_bfloat16* __restrict__ xin, int L) {
+  const int t = blockIdx.x, c = threadIdx.x;   // 320 threads
+  const int part = c / NMEL, ch = c % NMEL;
+#pragma unroll
+  for (int b = 0; b < 2; ++b) {
+    float v = 0.f;
+    if (part == 0) { if (in.x[b]) v = in.x[b][(size_t)ch * L + t]; }
+    else if (part == 1) { if (in.mu[b]) v = in.mu[b][(size_t)ch * L + t]; }
+    else if (part == 2) { if (in.spks[b]) v = in.spks[b][ch]; }
+    else { if (in.cond[b]) v = in.cond[b][(size_t)ch * L + t]; }
+    if (part == 0 && b == 0 && x) x[(size_t)t * NMEL + ch] = v;
+    xin[((size_t)b * L + t) * CIN + c] = __float2bfloat16_rn(v);
+  }
+}
+// est [2][L][80] -> out [2][80][L] (the reference's channel-first layout)
+__global__ void k_unpack(const float* __restrict__ est, float* __restrict__ out, int L) {
+  const int t = blockIdx.x, ch = threadIdx.x;
+#pragma unroll
+  for (int b = 0; b < 2; ++b) out[((size_t)b * NMEL + ch) * L + t] = est[((size_t)b * L + t) * NMEL + ch];
+}
+// v = (1 + r) v_c - r v_u;  x += dt v  (flow_matching.py:115-117)
+__global__ void k_euler(const float* __restrict__ est, float* __restrict__ x, __nv_bfloat16* __restrict__ xin,
+                        float* __restrict__ mel_out, float dt, float rate, int L, int last) {
+  const int t = blockIdx.x, ch = threadIdx.x;   // 80 threads
+  const float vc = est[(size_t)t * NMEL + ch], vu = est[((size_t)L + t) * NMEL + ch];
+  const float v = (1.0f + rate) * vc - rate * vu;
+  const float xn = x[(size_t)t * NMEL + ch] + dt * v;
+  x[(size_t)t * NMEL + ch] = xn;
+  const __nv_bfloat16 xb = __float2bfloat16_rn(xn);
+  xin[(size_t)t * CIN + ch] = xb;
+  xin[((size_t)L + t) * CIN + ch] = xb;
+  if (last) mel_out[(size_t)ch * L + t] = xn;
+}
+
+struct Op { int kind; GemmDesc g; int temb_res; };   // kind 0 gemm, 1 attention, 2 skip copy
+struct Plan { int L; std::vector<Op> ops; };
+
+}  // namespace
+
+struct cbx_cfm {
+  int device, max_len;
+  const __nv_bfloat16* wbf; const float* wf;
+  std::vector<long long> bo, fo;
+  void* slab;
+  __nv_bfloat16 *xin, *cur_a, *cur_b, *cat, *ln, *qkv, *att, *ff, *h1;
+  float *res, *h2, *est, *x, *mish_temb, *tvec, *tvals;
+  int max_steps;
+  std::map<int, Plan> plans;
+  long long launches;
+};
+
+static const __nv_bfloat16* BFW(cbx_cfm* h, int i) { return h->wbf + h->bo[i]; }
+static const float* FW(cbx_cfm* h, int i) { return h->wf + h->fo[i]; }
+
+// ---- the fixed op sequence of one estimator call for mel length L ----
+static int build_plan(cbx_cfm* h, int L, Plan** out) {
+  auto it = h->plans.find(L);
+  if (it != h->plans.end()) { *out = &it->second; return CBX_OK; }
+  Plan pl; pl.L = L;
+  int rc = CBX_OK;
+  auto G = [&](const __nv_bfloat16* A, int lda, int wi, int N, int K, int taps, const GemmEpi& e, int temb_res) {
+    Op op; op.kind = 0; op.temb_res = temb_res;
+    if (gemm_make(&op.g, A, lda, BFW(h, wi), 2, L, N, K, taps, e)) rc = CBX_ERR;
+    pl.ops.push_back(op);
+  };
+  auto resnet = [&](int r, const __nv_bfloat16* X, int ldx, int cin, int first_tfm) {
+    const int f = F_RES + r * 7;
+    GemmEpi e1{}; e1.bias = FW(h, f + 0); e1.ln_g = FW(h, f + 1); e1.ln_b = FW(h, f + 2); e1.out_bf16 = h->h1; e1.ld_bf16 = C;
+    G(X, ldx, BF_RES + r * 3 + 0, C, cin, 3, e1, r);
+    GemmEpi e2{}; e2.bias = FW(h, f + 3); e2.ln_g = FW(h, f + 4); e2.ln_b = FW(h, f + 5); e2.out_f32 = h->h2; e2.ld_f32 = C;
+    G(h->h1, C, BF_RES + r * 3 + 1, C, C, 3, e2, -1);
+    GemmEpi e3{}; e3.bias = FW(h, f + 6); e3.resid = h->h2; e3.ld_resid = C; e3.out_f32 = h->res; e3.ld_f32 = C;
+    e3.ln2_g = FW(h, F_TFM + first_tfm * 7 + 0); e3.ln2_b = FW(h, F_TFM + first_tfm * 7 + 1); e3.out_ln = h->ln; e3.ld_ln = C;
+    G(X, ldx, BF_RES + r * 3 + 2, C, cin, 1, e3, -1);
+  };
+  auto tfm = [&](int i, bool last, __nv_bfloat16* dst, int ld_dst) {
+    const int f = F_TFM + i * 7, w = BF_TFM + i * 4;
+    GemmEpi eq{}; eq.out_bf16 = h->qkv; eq.ld_bf16 = 1536;
+    G(h->ln, C, w + 0, 1536, C, 1, eq, -1);
+    Op at; at.kind = 1; at.temb_res = -1; pl.ops.push_back(at);
+    GemmEpi eo{}; eo.bias = FW(h, f + 2); eo.resid = h->res; eo.ld_resid = C; eo.out_f32 = h->res; eo.ld_f32 = C;
+    eo.ln2_g = FW(h, f + 3); eo.ln2_b = FW(h, f + 4); eo.out_ln = h->ln; eo.ld_ln = C;
+    G(h->att, 512, w + 1, C, 512, 1, eo, -1);
+    GemmEpi e1{}; e1.bias = FW(h, f + 5); e1.gelu = 1; e1.out_bf16 = h->ff; e1.ld_bf16 = 1024;
+    G(h->ln, C, w + 2, 1024, C, 1, e1, -1);
+    GemmEpi e2{}; e2.bias = FW(h, f + 6); e2.resid = h->res; e2.ld_resid = C; e2.out_f32 = h->res; e2.ld_f32 = C;
+    if (!last) { e2.ln2_g = FW(h, f + 7); e2.ln2_b = FW(h, f + 8); e2.out_ln = h->ln; e2.ld_ln = C; }   // next block's norm1
+    else { e2.out_bf16 = dst; e2.ld_bf16 = ld_dst; }
+    G(h->ff, 1024, w + 3, C, 1024, 1, e2, -1);
+  };
+  auto group = [&](int r, __nv_bfloat16* dst, int ld_dst) {
+    for (int j = 0; j < 4; ++j) tfm(r * 4 + j, j == 3, dst, ld_dst);
+  };
+  // down block
+  resnet(0, h->xin, CIN, CIN, 0);
+  group(0, h->cur_a, C);
+  { Op cp; cp.kind = 2; cp.temb_res = -1; pl.ops.push_back(cp); }          // skip connection -> cat[:, 256:512]
+  { GemmEpi e{}; e.bias = FW(h, F_TAIL + 0); e.out_bf16 = h->cur_b; e.ld_bf16 = C; G(h->cur_a, C, BF_TAIL + 0, C, C, 3, e, -1); }
+  // mid blocks
+  for (int m = 1; m <= 12; ++m) {
+    resnet(m, h->cur_b, C, C, m * 4);
+    if (m < 12) group(m, h->cur_b, C); else group(m, h->cat, 2 * C);
+  }
+  // up block: input = [x | skip]
+  resnet(13, h->cat, 2 * C, 2 * C, 52);
+  group(13, h->cur_a, C);
+  { GemmEpi e{}; e.bias = FW(h, F_TAIL + 1); e.out_bf16 = h->cur_b; e.ld_bf16 = C; G(h->cur_a, C, BF_TAIL + 1, C, C, 3, e, -1); }
+  { GemmEpi e{}; e.bias = FW(h, F_TAIL + 2); e.ln_g = FW(h, F_TAIL + 3); e.ln_b = FW(h, F_TAIL + 4); e.out_bf16 = h->h1; e.ld_bf16 = C;
+    G(h->cur_b, C, BF_TAIL + 2, C, C, 3, e, -1); }
+  { GemmEpi e{}; e.bias = FW(h, F_TAIL + 5); e.out_f32 = h->est; e.ld_f32 = NMEL; G(h->h1, C, BF_TAIL + 3, NMEL, C, 1, e, -1); }
+  if (rc) return CBX_ERR;
+  auto ins = h->plans.emplace(L, std::move(pl));
+  *out = &ins.first->second;
+  return CBX_OK;
+}
+
+static int run_estimator(cbx_cfm* h, Plan* pl, int step, cudaStream_t st) {
+  const int L = pl->L;
+  for (Op& op : pl->ops) {
+    if (op.kind == 0) {
+      if (op.temb_res >= 0) {
+        GemmDesc d = op.g;
+        d.epi.temb = h->tvec + ((size_t)(step * NRES + op.temb_res) * 2) * C;
+        if (gemm_launch(d, st)) return CBX_ERR;
+      } else if (gemm_launch(op.g, st)) return CBX_ERR;
+    } else if (op.kind == 1) {
+      if (s3_attn_launch(h->qkv, h->att, 2, L, 1536, st)) return CBX_ERR;
+    } else {
+      CBX_CUDA(cudaMemcpy2DAsync(h->cat + C, 2 * C * 2, h->cur_a, C * 2, C * 2, (size_t)2 * L, cudaMemcpyDeviceToDevice, st));
+    }
+    h->launches += 1;
+  }
+  return CBX_OK;
+}
+
+static int time_vectors(cbx_cfm* h, const float* t_host, int n, cudaStream_t st) {
+  CBX_CHECK(n >= 1 && n <= h->max_steps, "cfm: n_steps %d out of range (max %d)", n, h->max_steps);
+  CBX_CUDA(cudaMemcpyAsync(h->tvals, t_host, n * sizeof(float), cudaMemcpyHostToDevice, st));
+  k_temb<<<n, 1024, 0, st>>>(h->tvals, FW(h, F_TIME + 0), FW(h, F_TIME + 1), FW(h, F_TIME + 2), FW(h, F_TIME + 3), h->mish_temb);
+  k_tvec<<<dim3(NRES, n), 256, 0, st>>>(h->mish_temb, FW(h, F_TIME + 4), FW(h, F_TIME + 5), h->tvec);
+  CBX_CUDA(cudaGetLastError());
+  h->launches += 2;
+  return CBX_OK;
+}
+
+// =================================================================================================
+// C-ABI (include/cbx.h)
+// =================================================================================================
+extern "C" int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, cbx_cfm** out) {
+  CBX_CHECK(w && out && w->bf16_blob && w->f32_blob && w->bf16_off && w->f32_off, "cbx_cfm_create: null argument");
+  CBX_CHECK(max_len >= 1, "cbx_cfm_create: max_len must be positive");
+  CBX_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CBX_CUDA(cudaGetDeviceProperties(&prop, device));
+  CBX_CHECK(prop.major == 10, "cbx_cfm_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
+  cbx_cfm* h = new cbx_cfm();
+  h->device = device; h->max_len = max_len; h->launches = 0; h->max_steps = 64;
+  h->wbf = static_cast<const __nv_bfloat16*>(w->bf16_blob); h->wf = w->f32_blob;
+  h->bo.assign(w->bf16_off, w->bf16_off + BF_COUNT);
+  h->fo.assign(w->f32_off, w->f32_off + F_COUNT);
+  const size_t R = (size_t)2 * max_len;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = (off + bytes + 1023) / 1024 * 1024; return o; };
+  const size_t o_xin = take(R * CIN * 2), o_ca = take(R * C * 2), o_cb = take(R * C * 2), o_cat = take(R * 2 * C * 2);
+  const size_t o_ln = take(R * C * 2), o_qkv = take(R * 1536 * 2), o_att = take(R * 512 * 2), o_ff = take(R * 1024 * 2);
+  const size_t o_h1 = take(R * C * 2), o_res = take(R * C * 4), o_h2 = take(R * C * 4), o_est = take(R * NMEL * 4);
+  const size_t o_x = take((size_t)max_len * NMEL * 4), o_mt = take((size_t)h->max_steps * 1024 * 4);
+  const size_t o_tv = take((size_t)h->max_steps * NRES * 2 * C * 4), o_t = take(h->max_steps * 4);
+  if (cudaMalloc(&h->slab, off) != cudaSuccess) {
+    cbx_set_error("cbx_cfm_create: cudaMalloc of %zu bytes failed", off);
+    delete h;
+    return CBX_ERR;
+  }
+  cudaMemset(h->slab, 0, off);
+  uint8_t* s = static_cast<uint8_t*>(h->slab);
+  h->xin = (__nv_bfloat16*)(s + o_xin); h->cur_a = (__nv_bfloat16*)(s + o_ca); h->cur_b = (__nv_bfloat16*)(s + o_cb);
+  h->cat = (__nv_bfloat16*)(s + o_cat); h->ln = (__nv_bfloat16*)(s + o_ln); h->qkv = (__nv_bfloat16*)(s + o_qkv);
+  h->att = (__nv_bfloat16*)(s + o_att); h->ff = (__nv_bfloat16*)(s + o_ff); h->h1 = (__nv_bfloat16*)(s + o_h1);
+  h->res = (float*)(s + o_res); h->h2 = (float*)(s + o_h2); h->est = (float*)(s + o_est); h->x = (float*)(s + o_x);
+  h->mish_temb = (float*)(s + o_mt); h->tvec = (float*)(s + o_tv); h->tvals = (float*)(s + o_t);
+  *out = h;
+  return CBX_OK;
+}
+
+extern "C" int cbx_cfm_destroy(cbx_cfm* h) {
+  if (!h) return CBX_OK;
+  cudaFree(h->slab);
+  delete h;
+  return CBX_OK;
+}
+
+extern "C" int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, const float* spks, const float* cond, float t,
+                                 int L, float* out, void* stream) {
+  CBX_CHECK(h && x && mu && spks && cond && out, "cbx_cfm_estimator: null argument");
+  CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_estimator: L=%d exceeds max_len %d", L, h->max_len);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CBX_CUDA(cudaSetDevice(h->device));
+  Plan* pl;
+  if (build_plan(h, L, &pl)) return CBX_ERR;
+  if (time_vectors(h, &t, 1, st)) return CBX_ERR;
+  const size_t n = (size_t)NMEL * L;
+  PackIn in{{x, x + n}, {mu, mu + n}, {spks, spks + NMEL}, {cond, cond + n}};
+  k_pack<<<L, CIN, 0, st>>>(in, nullptr, h->xin, L);
+  if (run_estimator(h, pl, 0, st)) return CBX_ERR;
+  k_unpack<<<L, NMEL, 0, st>>>(h->est, out, L);
+  CBX_CUDA(cudaGetLastError());
+  h->launches += 2;
+  return CBX_OK;
+}
+
+extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
+                             int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out,
+                             void* stream) {
+  CBX_CHECK(h && z && mu && spks && cond && t_vals && dt_vals && mel_out, "cbx_cfm_solve: null argument");
+  CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_solve: L=%d exceeds max_len %d", L, h->max_len);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CBX_CUDA(cudaSetDevice(h->device));
+  Plan* pl;
+  if (build_plan(h, L, &pl)) return CBX_ERR;
+  if (time_vectors(h, t_vals, n_steps, st)) return CBX_ERR;
+  PackIn in{{z, z}, {mu, nullptr}, {spks, nullptr}, {cond, nullptr}};
+  k_pack<<<L, CIN, 0, st>>>(in, h->x, h->xin, L);
+  h->launches += 1;
+  for (int s = 0; s < n_steps; ++s) {
+    if (run_estimator(h, pl, s, st)) return CBX_ERR;
+    k_euler<<<L, NMEL, 0, st>>>(h->est, h->x, h->xin, mel_out, dt_vals[s], cfg_rate, L, s == n_steps - 1);
+    h->launches += 1;
+  }
+  CBX_CUDA(cudaGetLastError());
+  return CBX_OK;
+}
+
+extern "C" int cbx_cfm_launches(cbx_cfm* h, int64_t* launches) {
+  CBX_CHECK(h && launches, "cbx_cfm_launches: null argument");
+  *launches = h->launches;
+  return CBX_OK;
+}

@@ -84,6 +84,34 @@ int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t*
  * stamps[] (device, >= 5*n_layers+4 entries); NULL disables. */
 int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it);
 
+/* ------------------------------------------------------------------------------------------
+ * (2) S3Gen conditional flow matching: the Euler/CFG solve around the ConditionalDecoder estimator.
+ * Replaces CausalConditionalCFM.forward / ConditionalCFM.solve_euler
+ * (src/chatterbox/models/s3gen/flow_matching.py:194-218, 72-123) and ConditionalDecoder.forward
+ * (s3gen/decoder.py:233-317; call signature forward(x, mask, mu, t, spks, cond), flow_matching.py:125-127).
+ * Tensors are the reference's channel-first fp32 layouts; the mask is all-ones (one un-padded utterance).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct cbx_cfm cbx_cfm;
+
+typedef struct CbxCfmWeights {     /* device pointers, caller-owned, must outlive the handle */
+  const void* bf16_blob;           /* GEMM matrices, bf16, [N][taps*K] each (chatterbox_b200/cfm.py: pack order) */
+  const float* f32_blob;           /* biases, LayerNorm gains, time-embedding MLPs */
+  const int64_t* bf16_off;         /* HOST array [270]: element offsets into bf16_blob */
+  const int64_t* f32_off;          /* HOST array [502]: element offsets into f32_blob */
+} CbxCfmWeights;
+
+int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, cbx_cfm** out);
+int cbx_cfm_destroy(cbx_cfm* h);
+/* One estimator call on a batch of 2 rows sharing t: x, mu, cond [2][80][L], spks [2][80] -> out [2][80][L]. */
+int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, const float* spks, const float* cond, float t,
+                      int L, float* out, void* stream);
+/* n_steps Euler steps with classifier-free guidance: z, mu, cond [80][L], spks [80]; t_vals / dt_vals are HOST
+ * arrays [n_steps] (time fed to step s and its step size, computed by the caller exactly as flow_matching.py
+ * does); mel_out [80][L]. */
+int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
+                  int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out, void* stream);
+int cbx_cfm_launches(cbx_cfm* h, int64_t* launches);
+
 #ifdef __cplusplus
 }
 #endif
