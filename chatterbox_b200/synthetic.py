@@ -289,6 +289,10 @@ def init_tensor(family: str, key: str, shape, seed: int) -> torch.Tensor:
             return 0.02 * r
         if key.startswith("m_source.l_linear"):
             return 0.3 * r
+        if key == "f0_predictor.classifier.bias":
+            return torch.full(tuple(shape), 140.0)       # random-init f0 lands in the voiced range (> 10 Hz)
+        if key == "f0_predictor.classifier.weight":
+            return 40.0 * r
         return (1.0 / math.sqrt(_fan_in(shape))) * r
     raise ValueError(family)
 
@@ -359,3 +363,9 @@ def cfm_inputs(L: int, seed: int = 6, prompt_frames: int | None = None) -> Dict[
     cond = torch.zeros(1, 80, L)
     cond[:, :, :pf] = (torch.randn(1, 80, pf, generator=g) * 2.0 - 5.0).clamp(-11.5, 2.0)
     return dict(mu=mu, spks=spks, cond=cond, z=cfm_noise()[:, :, :L].clone())
+
+
+def mel_input(L: int, seed: int = 7) -> torch.Tensor:
+    """(1, 80, L) log-mel-like features (utils/mel.py range) for the vocoder tests."""
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(1, 80, L, generator=g) * 2.0 - 5.0).clamp(-11.5, 2.0)

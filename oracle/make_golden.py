@@ -194,6 +194,57 @@ def make_cfm():
     print("[cfm] wrote tests/golden/cfm_golden.safetensors")
 
 
+def make_hift():
+    """Reference HiFTGenerator / ConvRNNF0Predictor vs oracle/hift_oracle.py; golden outputs."""
+    import numpy as np
+    from torch.distributions.uniform import Uniform
+    from oracle import hift_oracle as HO
+    sd = S.make_state_dict("hift")
+    hift = R.build_hift()
+    missing, unexpected = hift.load_state_dict(sd, strict=False)
+    assert not unexpected and all("stft_window" in k for k in missing), (missing, unexpected)
+    w = HO.fold_weight_norm(sd)
+    out = {}
+    for L in (12, 40):
+        mel = S.mel_input(L, seed=7 + L)
+        with torch.inference_mode():
+            f0_ref = hift.f0_predictor(mel)
+            f0 = HO.f0_predictor(w, mel)
+        d = (f0_ref - f0).abs().max().item()
+        print(f"[hift] L={L} f0 range {f0_ref.min():.1f}..{f0_ref.max():.1f} Hz; restatement max-abs {d:.3e}")
+        assert d < 1e-2
+        # source: replicate the reference's RNG draws (hifigan.py:212-214,226) under one seed
+        torch.manual_seed(1000 + L)
+        with torch.inference_mode():
+            s_ref, _, _ = hift.m_source(hift.f0_upsamp(f0_ref[:, None]).transpose(1, 2))
+        s_ref = s_ref.transpose(1, 2)
+        torch.manual_seed(1000 + L)
+        pv = Uniform(low=-np.pi, high=np.pi).sample(sample_shape=(1, 9, 1))
+        pv[:, 0, :] = 0
+        nz = torch.randn(1, 9, 480 * L)
+        s_mine = HO.sine_source(w, f0_ref, pv, nz)
+        d = (s_ref - s_mine).abs().max().item()
+        print(f"[hift] L={L} source max-abs restatement vs reference {d:.3e} (rms {s_ref.pow(2).mean().sqrt():.3f})")
+        assert d < 1e-4
+        with torch.inference_mode():
+            wav_ref = hift.decode(x=mel, s=s_ref)
+            wav = HO.decode(w, mel, s_ref)
+        rel = ((wav_ref - wav).norm() / wav_ref.norm()).item()
+        print(f"[hift] L={L} decode rel-L2 restatement vs reference {rel:.3e}; wav rms {wav_ref.pow(2).mean().sqrt():.4f}, "
+              f"clamped {float((wav_ref.abs() >= 0.99).float().mean()):.3f}")
+        assert rel < 1e-4
+        out[f"f0_L{L}"] = f0_ref.clone()
+        out[f"s_L{L}"] = s_ref.clone()
+        out[f"phase_L{L}"] = pv.clone()
+        out[f"wav_L{L}"] = wav_ref.clone()
+        if L == 12:
+            out["noise_L12"] = nz.clone()
+            out["stage0_L12"] = HO.decode(w, mel, s_ref, stop_after="stage0")
+            out["stage2_L12"] = HO.decode(w, mel, s_ref, stop_after="stage2")
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(GOLD, "hift_golden.safetensors"))
+    print("[hift] wrote tests/golden/hift_golden.safetensors")
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["t3", "cfm", "hift"]
     torch.set_num_threads(os.cpu_count() or 8)
