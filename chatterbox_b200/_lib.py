@@ -33,6 +33,11 @@ class CbxCfmWeights(C.Structure):
                 ("f32_off", C.POINTER(C.c_int64))]
 
 
+class CbxHiftWeights(C.Structure):
+    _fields_ = [("bf16_blob", C.c_void_p), ("f32_blob", C.c_void_p), ("bf16_off", C.POINTER(C.c_int64)),
+                ("f32_off", C.POINTER(C.c_int64))]
+
+
 # every symbol include/cbx.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "cbx_last_error": (C.c_char_p, []),
@@ -53,6 +58,15 @@ SYMBOLS = {
     "cbx_cfm_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                 C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_void_p, C.c_void_p]),
     "cbx_cfm_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "cbx_hift_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxHiftWeights), C.POINTER(C.c_void_p)]),
+    "cbx_hift_destroy": (C.c_int, [C.c_void_p]),
+    "cbx_hift_f0": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "cbx_hift_source": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                                  C.c_void_p]),
+    "cbx_hift_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "cbx_hift_inference": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]),
+    "cbx_hift_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "cbx_t3_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                C.POINTER(C.c_int64)]),
 }

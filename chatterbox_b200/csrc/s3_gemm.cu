@@ -58,7 +58,7 @@ constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers
 
 struct GemmParams {
   CUtensorMap tmA, tmW;
-  int B, L, N, K, taps, n_tile, tiles_l;
+  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out;
   GemmEpi e;
 };
 
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         const int tap = kb / kpb, kk = kb % kpb;
         uint8_t* sa = smem + s * STAGE_BYTES;
         mbar_arrive_expect_tx(&full[s], tx);
-        tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap - (p.taps - 1), b);
+        tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
         tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kb * BK, n0, 0);
       }
     }
@@ -127,8 +127,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   } else {
     // ===== epilogue: thread <-> accumulator row =====
     const int q = warp & 3, row = q * 32 + lane, t = t0 + row;
-    const bool valid = t < p.L;
-    const size_t grow = (size_t)b * p.L + (valid ? t : 0);
+    const bool valid = t < p.M_out;
+    const size_t grow = (size_t)b * p.M_out + (valid ? t : 0);
     const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
     const GemmEpi& e = p.e;
     const int nch = p.n_tile / 16;
@@ -154,14 +154,16 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       float v[16];
       tmem_ld16(trow + c * 16, v);
       const int nb = n0 + c * 16;
+      const int bb0 = e.bias_mod > 0 ? nb % e.bias_mod : nb;
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
-        float x = v[i] + (e.bias ? __ldg(e.bias + nb + i) : 0.f);
+        float x = v[i] + (e.bias ? __ldg(e.bias + bb0 + i) : 0.f);
         if (e.ln_g) {
           x = mish_f((x - mean1) * rstd1 * __ldg(e.ln_g + nb + i) + __ldg(e.ln_b + nb + i));
           if (e.temb) x += __ldg(e.temb + (size_t)b * p.N + nb + i);
         }
         if (e.gelu) x = gelu_f(x);
+        if (e.elu) x = x > 0.f ? x : expm1f(x);
         v[i] = x;
       }
       if (valid) {
@@ -170,12 +172,30 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
 #pragma unroll
           for (int i = 0; i < 4; ++i) { const float4 rr = r[i]; v[4 * i] += rr.x; v[4 * i + 1] += rr.y; v[4 * i + 2] += rr.z; v[4 * i + 3] += rr.w; }
         }
-        if (e.out_f32) {
-          float4* o = reinterpret_cast<float4*>(e.out_f32 + grow * e.ld_f32 + nb);
+        if (e.resid2) {
+          const float4* r = reinterpret_cast<const float4*>(e.resid2 + grow * e.ld_resid2 + nb);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) o[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          for (int i = 0; i < 4; ++i) { const float4 rr = r[i]; v[4 * i] += rr.x; v[4 * i + 1] += rr.y; v[4 * i + 2] += rr.z; v[4 * i + 3] += rr.w; }
+        }
+        if (e.out_f32) {
+          const long long off = (long long)(grow * e.ld_f32 + nb) + e.out_shift;
+          if (e.out_limit == 0 || (off >= 0 && off + 16 <= e.out_limit)) {
+            float4* o = reinterpret_cast<float4*>(e.out_f32 + off);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          }
         }
         if (e.out_bf16) {
+          if (e.snake_alpha) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float a = __ldg(e.snake_alpha + nb + i), sn = sinf(v[i] * a);
+              v[i] = v[i] + (1.0f / (a + 1e-9f)) * sn * sn;
+            }
+          } else if (e.lrelu != 0.f) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * e.lrelu;
+          }
           uint4* o = reinterpret_cast<uint4*>(e.out_bf16 + grow * e.ld_bf16 + nb);
           o[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
           o[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
@@ -215,12 +235,20 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
 
 int gemm_make(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int B, int L, int N, int K, int taps,
               const GemmEpi& epi) {
+  return gemm_make_conv(d, A, lda, W, B, L, N, K, taps, 1, taps - 1, L, epi);
+}
+
+int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int B, int L, int N, int K, int taps,
+                   int dil, int pad, int M_out, const GemmEpi& epi) {
   CBX_CHECK(K % BK == 0 && K >= BK, "gemm_make: K=%d must be a multiple of 64", K);
-  int n_tile = N <= 256 ? N : 256;
-  CBX_CHECK(N % n_tile == 0 && n_tile % 16 == 0 && n_tile >= 16, "gemm_make: N=%d unsupported", N);
+  int n_tile = 0;
+  for (int c = 256; c >= 16; c -= 16) if (N % c == 0) { n_tile = c; break; }
+  CBX_CHECK(n_tile > 0, "gemm_make: N=%d unsupported (needs a divisor that is a multiple of 16, <= 256)", N);
+  CBX_CHECK(B == 1 || M_out == L, "gemm_make: M_out != L needs B == 1");
   CBX_CHECK(!(epi.ln_g || epi.out_ln) || n_tile == N, "gemm_make: row LayerNorm needs the whole row in one tile (N=%d)", N);
   CBX_CHECK(!epi.out_ln || epi.out_f32, "gemm_make: out_ln needs out_f32");
   d->B = B; d->L = L; d->N = N; d->K = K; d->taps = taps; d->n_tile = n_tile; d->epi = epi;
+  d->dil = dil; d->pad = pad; d->M_out = M_out;
   if (make_tmap_bf16_3d(&d->tmA, A, K, L, B, lda, (uint64_t)lda * L, BK, BM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW, W, (uint64_t)taps * K, N, 1, (uint64_t)taps * K, (uint64_t)taps * K * N, BK, n_tile)) return CBX_ERR;
   return CBX_OK;
@@ -235,7 +263,8 @@ int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   GemmParams p;
   p.tmA = d.tmA; p.tmW = d.tmW;
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;
-  p.tiles_l = (d.L + BM - 1) / BM;
+  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out;
+  p.tiles_l = (d.M_out + BM - 1) / BM;
   p.e = d.epi;
   dim3 grid(d.B * p.tiles_l, d.N / d.n_tile);
   s3_gemm_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(p);

@@ -6,27 +6,37 @@ namespace cbx {
 
 struct GemmEpi {
   const float* bias;                       // [N] or null
+  int bias_mod;                            // > 0: bias index is n % bias_mod (polyphase transposed convolution)
   const float* ln_g; const float* ln_b;    // LayerNorm over the N outputs of a row, then Mish (needs n_tile == N)
   const float* temb;                       // [B][N] added after Mish, or null
   int gelu;                                // exact (erf) GELU
+  int elu;                                 // ELU(alpha = 1)
   const float* resid; int ld_resid;        // fp32 [rows][ld] added last
+  const float* resid2; int ld_resid2;      // second fp32 addend (running sum over parallel branches)
+  long long out_shift, out_limit;          // out_f32 only: flat element offset added to row*ld + n; stores outside
+                                           // [0, out_limit) are dropped (out_limit 0 = no shift / no clipping)
+  const float* snake_alpha;                // bf16 output = v + sin^2(alpha[n] v) / (alpha[n] + 1e-9)   (HiFT Snake)
+  float lrelu;                             // bf16 output = leaky_relu(v, lrelu) when != 0
   float* out_f32; int ld_f32;
   __nv_bfloat16* out_bf16; int ld_bf16;
   const float* ln2_g; const float* ln2_b;  // LayerNorm of the final row value -> out_ln (needs out_f32, n_tile == N)
   __nv_bfloat16* out_ln; int ld_ln;
 };
 
-// C[b][t][n] = sum_tap sum_k A[b][t + tap - (taps-1)][k] * W[n][tap*K + k]   (rows t < 0 read as zero)
+// C[b][t][n] = sum_tap sum_k A[b][t + tap*dil - pad][k] * W[n][tap*K + k]   (rows outside [0, L) read as zero),
+// for t in [0, M_out)
 struct GemmDesc {
   CUtensorMap tmA;     // bf16 [B][L][K] view (K innermost), box {64, 128, 1}
   CUtensorMap tmW;     // bf16 [N][taps*K], box {64, n_tile, 1}
-  int B, L, N, K, taps, n_tile;
+  int B, L, N, K, taps, n_tile, dil, pad, M_out;
   GemmEpi epi;
 };
 
 // builds the tensor maps; A has row stride lda elements (>= K), W is dense [N][taps*K]
 int gemm_make(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int B, int L, int N, int K, int taps,
-              const GemmEpi& epi);
+              const GemmEpi& epi);    // causal taps: dil 1, pad taps-1, M_out = L
+int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int B, int L, int N, int K, int taps,
+                   int dil, int pad, int M_out, const GemmEpi& epi);
 int gemm_launch(const GemmDesc& d, cudaStream_t st);
 
 }  // namespace cbx

@@ -112,6 +112,34 @@ int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks
                   int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out, void* stream);
 int cbx_cfm_launches(cbx_cfm* h, int64_t* launches);
 
+/* ------------------------------------------------------------------------------------------
+ * (3) HiFT-GAN vocoder: mel -> f0 -> harmonic source -> waveform.
+ * Replaces HiFTGenerator.inference / decode (src/chatterbox/models/s3gen/hifigan.py:462-474, 412-444),
+ * ConvRNNF0Predictor.forward (s3gen/f0_predictor.py:52-55), SourceModuleHnNSF / SineGen (hifigan.py:200-283)
+ * and the trim_fade of S3Token2Wav.inference (s3gen/s3gen.py:233-236, 296).  mel is the reference's
+ * channel-first fp32 [80][L]; waveforms are [480 L] fp32 at 24 kHz.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct cbx_hift cbx_hift;
+
+typedef struct CbxHiftWeights {    /* device pointers, caller-owned, must outlive the handle */
+  const void* bf16_blob;           /* convolution matrices, weight-norm folded, bf16 (chatterbox_b200/hift.py pack order) */
+  const float* f32_blob;           /* biases, Snake alphas, 18-channel source convolutions, small linears */
+  const int64_t* bf16_off;         /* HOST array [82] */
+  const int64_t* f32_off;          /* HOST array [164] */
+} CbxHiftWeights;
+
+int cbx_hift_create(int device, int max_frames, const CbxHiftWeights* w, cbx_hift** out);
+int cbx_hift_destroy(cbx_hift* h);
+int cbx_hift_f0(cbx_hift* h, const float* mel, int L, float* f0_out, void* stream);
+/* phase [9] / noise [9][480 L] (device) may be NULL: then drawn from Philox(seed) (the reference uses torch's global RNG). */
+int cbx_hift_source(cbx_hift* h, const float* f0, int L, const float* phase, const float* noise, uint64_t seed,
+                    float* s_out, void* stream);
+int cbx_hift_decode(cbx_hift* h, const float* mel, int L, const float* s, int apply_fade, float* wav_out, void* stream);
+/* f0 -> source (unless source_in is given) -> decode; source_out (nullable) receives the source signal used. */
+int cbx_hift_inference(cbx_hift* h, const float* mel, int L, const float* source_in, uint64_t seed, int apply_fade,
+                       float* wav_out, float* source_out, void* stream);
+int cbx_hift_launches(cbx_hift* h, int64_t* launches);
+
 #ifdef __cplusplus
 }
 #endif
