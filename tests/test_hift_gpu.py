@@ -61,19 +61,21 @@ def test_decode_matches_reference_golden(hift, L):
     assert r < TOL
 
 
-@pytest.mark.parametrize("L", [1, 3, 17, 129])
+@pytest.mark.parametrize("L", [1, 2, 3, 17, 129])
 def test_decode_ragged_lengths_vs_oracle(hift, L):
     from oracle import hift_oracle as HO
     w = HO.fold_weight_norm(S.make_state_dict("hift"))
     mel = S.mel_input(L, seed=50 + L)
     s = torch.tanh(torch.randn(1, 1, 480 * L, generator=torch.Generator().manual_seed(L)) * 0.3)
+    fade = L >= 2      # the reference's trim_fade (s3gen.py:296) itself needs >= 960 samples
     with torch.inference_mode():
-        ref, _ = HO.inference(w, mel, s=s, apply_trim_fade=True)
-    wav = hift.decode(mel, s, apply_fade=True).cpu()
+        ref, _ = HO.inference(w, mel, s=s, apply_trim_fade=fade)
+    wav = hift.decode(mel, s, apply_fade=fade).cpu()
     r = _rel(wav, ref)
     print(f"decode+fade L={L} rel-L2 vs oracle {r:.3e}")
     assert r < TOL
-    assert float(wav[0, : min(480, wav.shape[1])].abs().max()) == 0.0      # trim_fade: first 20 ms are silent
+    if fade:
+        assert float(wav[0, :480].abs().max()) == 0.0      # trim_fade: first 20 ms are silent
 
 
 def test_inference_end_to_end_uses_own_source(hift):
