@@ -245,8 +245,37 @@ def make_hift():
     print("[hift] wrote tests/golden/hift_golden.safetensors")
 
 
+def make_flow():
+    """Reference CausalMaskedDiffWithXvec.inference: captures the CFM inputs the front-end produces and the
+    final mel; checks chatterbox_b200/flow_frontend.py (plain torch) against them."""
+    from chatterbox_b200 import flow_frontend as FF
+    sd = S.make_state_dict("flow")
+    flow = R.build_flow()
+    flow.load_state_dict(sd, strict=False)
+    flow.decoder.rand_noise = S.cfm_noise()
+    ref = S.s3gen_ref(seed=4, prompt_len=20)
+    tok = S.speech_tokens(30, seed=5)
+    cap = {}
+    hk = flow.decoder.register_forward_pre_hook(lambda m, a, kw: cap.update({k: v.clone() for k, v in kw.items() if torch.is_tensor(v)}),
+                                                with_kwargs=True)
+    with torch.inference_mode():
+        feat, _ = flow.inference(token=tok, token_len=torch.tensor([30]), prompt_token=ref["prompt_token"],
+                                 prompt_token_len=ref["prompt_token_len"], prompt_feat=ref["prompt_feat"],
+                                 prompt_feat_len=None, embedding=ref["embedding"], finalize=True)
+        mu, spks, cond, l1 = FF.flow_inputs(sd, tok, ref["prompt_token"], ref["prompt_feat"], ref["embedding"])
+    hk.remove()
+    for name, mine in (("mu", mu), ("spks", spks), ("cond", cond)):
+        d = (cap[name] - mine).abs().max().item()
+        print(f"[flow] front-end {name}: max-abs vs reference {d:.3e} (rms {cap[name].pow(2).mean().sqrt():.3f})")
+        assert d < 1e-3
+    assert l1 == 40 and feat.shape == (1, 80, 60)
+    out = {"mu": cap["mu"], "spks": cap["spks"], "cond": cap["cond"], "feat": feat.clone()}
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(GOLD, "flow_golden.safetensors"))
+    print("[flow] wrote tests/golden/flow_golden.safetensors")
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["t3", "cfm", "hift"]
+    which = sys.argv[1:] or ["t3", "cfm", "hift", "flow"]
     torch.set_num_threads(os.cpu_count() or 8)
     if "t3" in which:
         make_t3()
@@ -254,3 +283,5 @@ if __name__ == "__main__":
         globals()["make_cfm"]()
     if "hift" in which and "make_hift" in globals():
         globals()["make_hift"]()
+    if "flow" in which:
+        make_flow()
