@@ -4,11 +4,13 @@
   python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
   python bench.py --impl reference --gpus N --steps K ...   # the reference's algorithm on the host cores
 
-A "step" is one utterance of BASELINE.json configs[1]: a 64-token (+SOT/EOT) synthetic sentence, a
-6 s synthetic reference voice (150 conditioning tokens), cfg_weight 0.5, exaggeration 0.5, greedy,
-exactly 256 speech tokens (EOS suppressed), random-init weights of the named architecture.  The
-stages that exist in this build run inside the step (see `config.stages`); the headline metric is
-T3 speech tokens/s (whole job, all GPUs), with RTF and utterances/s reported beside it.
+A "step" is one utterance of BASELINE.json configs[1], the full generate() pipeline: a 64-token (+SOT/EOT)
+synthetic sentence, a 6 s synthetic reference voice (150 conditioning tokens, 300 prompt mel frames),
+cfg_weight 0.5, exaggeration 0.5, greedy, exactly 256 speech tokens (EOS suppressed), random-init weights
+of the named architecture: T3 prefill + 256-token decode -> flow front-end -> 10-step CFM solve at
+L = 812 mel frames -> HiFT vocoder for 512 frames (10.24 s of audio).  The headline metric is speech
+tokens/s through that whole pipeline (whole job, all GPUs); T3-decode tokens/s, RTF and utterances/s are
+reported beside it, and the roofline object describes the dominant kernel (the T3 decode megakernel).
 
 Timing: W >= 3 untimed steps, then K steps between barrier + cuda synchronize, CUDA events on the
 launching stream, MAX over ranks.  L2: every decode step streams 1.02 GB of weights (> 126 MB L2), so
@@ -34,7 +36,8 @@ import torch  # noqa: E402
 N_TEXT, PROMPT_LEN, N_SPEECH = 64, 150, 256
 SAMPLE = dict(cfg_weight=0.5, temperature=0.8, repetition_penalty=1.2, min_p=0.05, top_p=1.0)
 KV_BYTES_PER_POS = 30 * 2 * 1024 * 2 * 2          # layers x (K,V) x hidden x CFG rows x bf16
-METRIC, UNIT = "t3_speech_tokens_per_s", "tokens/s"
+METRIC, UNIT = "speech_tokens_per_s", "tokens/s"
+AUDIO_S = N_SPEECH / 25.0
 
 
 def _peaks():
@@ -107,20 +110,23 @@ def _decode_bytes(weight_bytes: int, P: int, n: int) -> int:
 _SD_CACHE = {}
 
 
+def _sd(name):
+    from chatterbox_b200 import synthetic as S
+    if name not in _SD_CACHE:
+        _SD_CACHE[name] = S.make_state_dict(name)
+    return _SD_CACHE[name]
+
+
 def cpu_t3_sample(n_decode: int, threads: int):
     """Prefill + n_decode greedy tokens of the full 30-layer model through the oracle restatement of
-    T3.inference (oracle/t3_oracle.py; reference t3.py:203-371) in fp32 on `threads` host threads.
-    Returns (prefill_s, per_token_s)."""
+    T3.inference (oracle/t3_oracle.py; reference t3.py:203-371), fp32.  Returns (prefill_s, per_token_s)."""
     from chatterbox_b200 import synthetic as S
     from oracle import t3_oracle as T3O
     torch.set_num_threads(threads)
-    if "t3" not in _SD_CACHE:
-        _SD_CACHE["t3"] = S.make_state_dict("t3")
-    sd = _SD_CACHE["t3"]
+    sd = _sd("t3")
     cond = S.t3_cond(prompt_len=PROMPT_LEN)
     text2 = torch.cat([S.text_tokens(N_TEXT)] * 2, 0)
     with torch.inference_mode():
-        t0 = time.perf_counter()
         emb = T3O.prepare_input_embeds(sd, cond, text2, SAMPLE["cfg_weight"])
         m = T3O.LlamaOracle(sd)
         t0 = time.perf_counter()
@@ -138,37 +144,68 @@ def cpu_t3_sample(n_decode: int, threads: int):
     return t_prefill, t_tok
 
 
+def cpu_s3gen_sample(n_euler: int, threads: int):
+    """Flow front-end + n_euler (of 10) Euler/CFG steps at L = 812 + the full HiFT decode for 512 frames through the
+    oracle restatements (oracle/cfm_oracle.py, oracle/hift_oracle.py), fp32 (the vocoder on a 128-frame slice, scaled x4).  Returns (front_s, per_euler_step_s, hift_s)."""
+    from chatterbox_b200 import flow_frontend as FF, synthetic as S
+    from oracle import cfm_oracle as CO, hift_oracle as HO
+    torch.set_num_threads(threads)
+    sd, ref = _sd("flow"), S.s3gen_ref(seed=4, prompt_len=PROMPT_LEN)
+    tok = S.speech_tokens(N_SPEECH, seed=5)
+    with torch.inference_mode():
+        t0 = time.perf_counter()
+        mu, spks, cond, l1 = FF.flow_inputs(sd, tok, ref["prompt_token"], ref["prompt_feat"], ref["embedding"])
+        t_front = time.perf_counter() - t0
+        L = mu.shape[2]
+        t0 = time.perf_counter()
+        x = CO.solve_euler(sd, S.cfm_noise()[:, :, :L], mu, spks, cond, n_timesteps=n_euler, pfx="decoder.estimator.")
+        t_step = (time.perf_counter() - t0) / n_euler
+        w = HO.fold_weight_norm(_sd("hift"))
+        mel = x[:, :, l1:l1 + 128]                 # 128 of the 512 frames; the vocoder is linear in length
+        s = torch.tanh(torch.randn(1, 1, 480 * mel.shape[2]) * 0.3)
+        t0 = time.perf_counter()
+        HO.decode(w, mel, s)
+        t_hift = (time.perf_counter() - t0) * (2 * N_SPEECH / 128.0)
+    return t_front, t_step, t_hift
+
+
+def cpu_pipeline_sample(ref_tokens: int, ref_euler: int, threads: int):
+    tp, tt = cpu_t3_sample(ref_tokens, threads)
+    tf, ts, th = cpu_s3gen_sample(ref_euler, threads)
+    utt_s = tp + N_SPEECH * tt + tf + 10 * ts + th
+    sample = (f"oracle ports on {threads} host threads, fp32: T3 full prefill + {ref_tokens} greedy tokens (x{N_SPEECH} "
+              f"extrapolated: prefill {tp:.2f} s, {tt * 1e3:.1f} ms/token), flow front-end {tf:.2f} s, {ref_euler} of 10 "
+              f"Euler/CFG steps at L=812 ({ts:.2f} s/step, x10 extrapolated), HiFT decode of 128 of 512 frames (x4 extrapolated: {th:.2f} s)")
+    return utt_s, sample, dict(t3_prefill_s=tp, t3_per_token_s=tt, front_s=tf, euler_step_s=ts, hift_s=th)
+
+
 def run_reference(args, rank: int):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    n_dec = args.ref_tokens
-    times = []
+    vals = []
     for i in range(args.warmup + args.steps):
-        tp, tt = cpu_t3_sample(n_dec, threads)
+        utt_s, sample, parts = cpu_pipeline_sample(args.ref_tokens, args.ref_euler, threads)
         if i >= args.warmup:
-            times.append((tp, tt))
-    tp = statistics.mean(t[0] for t in times)
-    tt = statistics.mean(t[1] for t in times)
-    utt_s = tp + N_SPEECH * tt
+            vals.append(utt_s)
+    utt_s = statistics.mean(vals)
     val = N_SPEECH / utt_s
-    sample = (f"oracle port of T3.inference (fp32, torch CPU, {threads} threads): full prefill (P=102, CFG pair) + "
-              f"{n_dec} greedy decode tokens per step, extrapolated to {N_SPEECH} tokens as "
-              f"prefill_s + {N_SPEECH} x per_token_s")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": utt_s * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": _config(["t3"]),
+            "config": _config(),
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "rtf": utt_s / AUDIO_S, "utterances_per_s": 1.0 / utt_s, "stages_s": parts}
     print(json.dumps(line), flush=True)
 
 
-def _config(stages):
-    return {"workload": "configs[1]: single utterance, 64+2 text tokens, 6 s voice (150 cond tokens), cfg 0.5, "
-                        "exaggeration 0.5, greedy, 256 speech tokens, random-init weights",
-            "stages": stages, "utterances_per_step_per_gpu": 1, "speech_tokens": N_SPEECH,
+def _config():
+    return {"workload": "configs[1]: full generate() pipeline, single utterance: 64+2 text tokens, 6 s voice (150 cond "
+                        "tokens, 300 prompt mel frames), cfg 0.5, exaggeration 0.5, greedy, 256 speech tokens, CFM 10 "
+                        "steps at L=812, HiFT 512 frames (10.24 s audio), random-init weights",
+            "stages": ["t3_prefill", "t3_decode", "flow_frontend", "cfm_solve", "hift"],
+            "utterances_per_step_per_gpu": 1, "speech_tokens": N_SPEECH,
             "l2": "inputs larger than L2 (1.02 GB of weights streamed per decode step)"}
 
 
@@ -178,7 +215,8 @@ def _config(stages):
 def run_ours(args, rank: int, world: int, local_rank: int):
     import torch.distributed as dist
     from chatterbox_b200 import synthetic as S
-    from chatterbox_b200.t3 import T3, T3Cond
+    from chatterbox_b200.t3 import T3Cond
+    from chatterbox_b200.tts import ChatterboxTTS, Conditionals
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -190,34 +228,39 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # independent utterance per rank (seeds differ), same shapes
-    sd = S.make_state_dict("t3")
-    t3 = T3(sd, dev, max_pos=512, kv_fp32=False)
-    del sd
+    # one replica per rank, an independent utterance per rank (seeds differ), same shapes
+    conds = Conditionals(T3Cond(**S.t3_cond(seed=2 + 10 * rank, prompt_len=PROMPT_LEN)),
+                         S.s3gen_ref(seed=4 + 10 * rank, prompt_len=PROMPT_LEN))
+    tts = ChatterboxTTS.from_state_dicts(S.make_state_dict("t3"), S.make_state_dict("flow"), S.make_state_dict("hift"),
+                                         dev, conds=conds, rand_noise=S.cfm_noise(), max_speech_tokens=N_SPEECH,
+                                         max_text_tokens=N_TEXT + 2, max_prompt_tokens=PROMPT_LEN)
+    t3, s3 = tts.t3, tts.s3gen
     t3.record_events = True
-    cond_host = {k: v.pin_memory() for k, v in S.t3_cond(seed=2 + 10 * rank, prompt_len=PROMPT_LEN).items()}
-    text_host = torch.cat([S.text_tokens(N_TEXT, seed=1 + rank)] * 2, 0).pin_memory()
-    cond_dev = T3Cond(**{k: v.to(dev) for k, v in cond_host.items()})
-    text_dev = text_host.to(dev)
-    kw = dict(max_new_tokens=N_SPEECH, do_sample=False, stop_on_eos=False, **SAMPLE)
+    s3.record_events = True
+    ids_host = S.text_tokens(N_TEXT, seed=1 + rank)[:, 1:-1].to(torch.int32).pin_memory()    # generate() adds SOT/EOT
+    text_dev = torch.cat([S.text_tokens(N_TEXT, seed=1 + rank)] * 2, 0).to(dev)
+    gen_kw = dict(do_sample=False, stop_on_eos=False, max_new_tokens=N_SPEECH, seed=7, **SAMPLE)
 
     def step_resident():
-        c = T3Cond(speaker_emb=cond_dev.speaker_emb, cond_prompt_speech_tokens=cond_dev.cond_prompt_speech_tokens,
-                   emotion_adv=cond_dev.emotion_adv)
-        return t3.inference(t3_cond=c, text_tokens=text_dev, **kw)
+        """the inner seams generate() goes through, inputs already in HBM, output left in HBM"""
+        c = tts.conds.t3
+        cond = T3Cond(speaker_emb=c.speaker_emb, cond_prompt_speech_tokens=c.cond_prompt_speech_tokens, emotion_adv=c.emotion_adv)
+        toks = t3.inference(t3_cond=cond, text_tokens=text_dev, max_new_tokens=N_SPEECH, do_sample=False,
+                            stop_on_eos=False, seed=7, **SAMPLE)
+        wav, _ = s3.inference(speech_tokens=toks[0], ref_dict=tts.conds.gen, seed=7)
+        return toks, wav
 
     def step_e2e():
-        c = T3Cond(**{k: v.to(dev, non_blocking=True) for k, v in cond_host.items()})
-        toks = t3.inference(t3_cond=c, text_tokens=text_host.to(dev, non_blocking=True), **kw)
-        return toks.cpu()
+        """the public call: host token ids in, host waveform out (tts.py:208-272)"""
+        return tts.generate(text_tokens=ids_host, **gen_kw)
 
-    h2d = sum(v.numel() * v.element_size() for v in cond_host.values()) + text_host.numel() * text_host.element_size()
-    d2h = N_SPEECH * 8 + 4
+    def counters():
+        return t3.state()["launches"] + s3.launches()
 
     for _ in range(max(args.warmup, 3)):
-        toks = step_resident()
-        assert toks.shape[1] == N_SPEECH
-    l0 = t3.state()["launches"]
+        toks, wav = step_resident()
+        assert toks.shape[1] == N_SPEECH and int((toks >= 6561).sum()) == 0 and wav.shape[1] == 480 * 2 * N_SPEECH
+    l0 = counters()
 
     # ---- timed region 1: inputs resident in HBM ----
     sampler = ClockSampler(local_rank)
@@ -225,23 +268,25 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     sampler.start()
     torch.cuda.profiler.start()     # ncu --profile-from-start off: the launch list covers the timed region only
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    dec_ms, pre_ms = [], []
+    evs = []
     e0.record()
     for _ in range(args.steps):
         step_resident()
-        ev = t3.events
-        dec_ms.append((ev["decode0"], ev["decode1"]))
-        pre_ms.append((ev["prefill0"], ev["decode0"]))
+        evs.append({**t3.events, **s3.events})
     e1.record()
     barrier()
     torch.cuda.profiler.stop()
     clocks = sampler.stop()
     total_ms = e0.elapsed_time(e1)
-    launches = t3.state()["launches"] - l0
-    dec_ms = [a.elapsed_time(b) for a, b in dec_ms]
-    pre_ms = [a.elapsed_time(b) for a, b in pre_ms]
+    launches = counters() - l0
 
-    # ---- timed region 2: end to end through the public call with HOST inputs/outputs ----
+    def stage(a, b):
+        return statistics.mean(ev[a].elapsed_time(ev[b]) for ev in evs)
+
+    stages = {"t3_prefill": stage("prefill0", "decode0"), "t3_decode": stage("decode0", "decode1"),
+              "flow_frontend": stage("front0", "cfm0"), "cfm_solve": stage("cfm0", "cfm1"), "hift": stage("hift0", "hift1")}
+
+    # ---- timed region 2: end to end through the public API with HOST inputs / outputs ----
     for _ in range(2):
         step_e2e()
     barrier()
@@ -251,7 +296,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     e1.record()
     barrier()
     e2e_ms = e0.elapsed_time(e1)
-    assert out.shape[1] == N_SPEECH
+    assert out.shape == (1, 480 * 2 * N_SPEECH) and out.device.type == "cpu"
 
     t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -263,33 +308,37 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         P = t3.last_prefill_len
         wbytes = t3.packed.weight_bytes_per_step()
         dbytes = _decode_bytes(wbytes, P, N_SPEECH)
-        d_ms = statistics.mean(dec_ms)
+        d_ms = stages["t3_decode"]
         achieved = dbytes / (d_ms * 1e-3) / 1e9
         tokens = N_SPEECH * args.steps * world
+        step_s = total_ms / args.steps * 1e-3
+        L = 2 * (PROMPT_LEN + N_SPEECH)
+        cfm_flop = 10 * 2 * L * (132.18e6 + 114688.0 * L)              # per estimator call x 10 steps
+        hift_flop = 612.3e6 * 2 * N_SPEECH
         line = {"metric": METRIC, "value": tokens / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-                "data": "synthetic", "config": _config(["t3_prefill", "t3_decode"]),
-                "e2e": {"value": tokens / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                        "d2h_bytes_per_step": d2h},
+                "data": "synthetic", "config": _config(),
+                "e2e": {"value": tokens / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(ids_host.numel() * 4),
+                        "d2h_bytes_per_step": int(out.numel() * 4) + 4},
                 "gpu_launches": int(launches),
                 "clocks": clocks,
-                "roofline": {"kernel": "t3_megakernel<bf16> (decode launch: 256 tokens)", "bound": "hbm",
+                "roofline": {"kernel": "t3_megakernel<bf16,1> (one decode launch = 256 tokens)", "bound": "hbm",
                              "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "peak_source": peak_src,
-                             "algorithmic_bytes_per_launch": dbytes, "launch_ms": d_ms},
-                "stages_ms": {"t3_prefill": statistics.mean(pre_ms), "t3_decode": d_ms},
-                "decode_tokens_per_s": N_SPEECH / (d_ms * 1e-3),
+                             "algorithmic_bytes_per_launch": dbytes, "launch_ms": d_ms,
+                             "share_of_step": d_ms / (total_ms / args.steps)},
+                "stages_ms": stages,
+                "t3_decode_tokens_per_s": N_SPEECH / (d_ms * 1e-3),
+                "cfm_tflops": cfm_flop / (stages["cfm_solve"] * 1e-3) / 1e12,
+                "hift_tflops": hift_flop / (stages["hift"] * 1e-3) / 1e12,
                 "utterances_per_s": args.steps * world / (total_ms * 1e-3),
-                "rtf_t3_only": (total_ms / args.steps * 1e-3) / (N_SPEECH / 25.0)}
+                "rtf": step_s / AUDIO_S, "rtf_e2e": (e2e_ms / args.steps * 1e-3) / AUDIO_S}
         if not args.no_cpu_baseline and world == 1:
             threads = os.cpu_count() or 1
-            tp, tt = cpu_t3_sample(args.ref_tokens, threads)
-            v = N_SPEECH / (tp + N_SPEECH * tt)
-            line["cpu_baseline"] = {
-                "value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                "sample": f"oracle port of T3.inference fp32 on {threads} threads: full prefill + {args.ref_tokens} "
-                          f"greedy tokens, extrapolated to {N_SPEECH} tokens (prefill {tp:.2f} s, {tt * 1e3:.1f} ms/token)"}
+            utt_s, sample, parts = cpu_pipeline_sample(args.ref_tokens, args.ref_euler, threads)
+            line["cpu_baseline"] = {"value": N_SPEECH / utt_s, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": sample, "rtf": utt_s / AUDIO_S}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -301,7 +350,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--ref-tokens", type=int, default=16, help="decode tokens per CPU sample")
+    ap.add_argument("--ref-tokens", type=int, default=16, help="T3 decode tokens per CPU sample")
+    ap.add_argument("--ref-euler", type=int, default=2, help="Euler steps (of 10) per CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -1,0 +1,103 @@
+"""Host-side mirror of the reference `S3Token2Wav` / `S3Gen` (src/chatterbox/models/s3gen/s3gen.py:212-298):
+speech tokens + reference-voice dict -> mel (flow-matching) -> waveform (HiFT), same method names and
+return values.  The CFM solve and the vocoder run in `libcbx.so`; the once-per-utterance token front-end
+(`flow_frontend.py`) is plain torch on the GPU.
+
+Not provided (conditioning preparation, out of the hot path — SURVEY.md §2 rows 9, 12 and §8f row 4):
+`embed_ref` (needs the absent third-party `s3tokenizer` network, CAM++ and librosa mel) — callers pass a
+pre-computed `ref_dict` exactly as the reference's production path does (`tts.py:266-269`).
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _lib, flow_frontend
+from .cfm import CausalConditionalCFM, ConditionalDecoder
+from .hift import HiFTGenerator
+
+S3GEN_SR = 24000
+
+
+class S3Gen:
+    def __init__(self, flow_sd: Dict[str, torch.Tensor], hift_sd: Dict[str, torch.Tensor], device="cuda", *,
+                 rand_noise: Optional[torch.Tensor] = None, max_mel_len: int = 4096):
+        if not torch.cuda.is_available():
+            raise _lib.CbxError("chatterbox_b200.S3Gen needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        keep = ("input_embedding.", "spk_embed_affine_layer.", "encoder.", "encoder_proj.")
+        self.front = {k: v.to(self.device, torch.float32) for k, v in flow_sd.items() if k.startswith(keep)}
+        self.estimator = ConditionalDecoder(flow_sd, self.device, prefix="decoder.estimator.", max_len=max_mel_len)
+        self.decoder = CausalConditionalCFM(self.estimator, rand_noise=rand_noise)
+        self.mel2wav = HiFTGenerator(hift_sd, self.device, max_frames=max_mel_len)
+        self.record_events = False
+        self.events: Dict[str, torch.cuda.Event] = {}
+
+    @classmethod
+    def from_state_dict(cls, sd: Dict[str, torch.Tensor], device="cuda", **kw) -> "S3Gen":
+        """`s3gen.safetensors` layout: `flow.*`, `mel2wav.*` (+ tokenizer / speaker_encoder entries, unused here)."""
+        flow = {k[len("flow."):]: v for k, v in sd.items() if k.startswith("flow.")}
+        hift = {k[len("mel2wav."):]: v for k, v in sd.items() if k.startswith("mel2wav.")}
+        return cls(flow, hift, device, **kw)
+
+    def embed_ref(self, *a, **k):
+        raise NotImplementedError("embed_ref (reference-voice conditioning prep) is outside the accelerated path; "
+                                  "pass a pre-computed ref_dict (Conditionals.gen)")
+
+    def _ref(self, ref_dict):
+        out = {}
+        for k, v in ref_dict.items():
+            if isinstance(v, np.ndarray):
+                v = torch.from_numpy(v)
+            out[k] = v.to(self.device) if torch.is_tensor(v) else v
+        return out
+
+    @torch.inference_mode()
+    def flow_inference(self, speech_tokens, ref_wav=None, ref_sr=None, ref_dict: Optional[dict] = None, finalize: bool = True):
+        assert ref_wav is None and ref_dict is not None, "pass a pre-computed ref_dict (embed_ref is not provided)"
+        assert finalize, "streaming (finalize=False) is not supported"
+        ref = self._ref(ref_dict)
+        tok = speech_tokens.to(self.device)
+        if tok.dim() == 1:
+            tok = tok.unsqueeze(0)
+        assert tok.shape[0] == 1
+        ev = {k: torch.cuda.Event(enable_timing=True) for k in ("front0", "cfm0", "cfm1")} if self.record_events else None
+        if ev:
+            ev["front0"].record()
+        mu, spks, cond, mel_len1 = flow_frontend.flow_inputs(self.front, tok.long(), ref["prompt_token"].long(),
+                                                             ref["prompt_feat"].float(), ref["embedding"].float())
+        if ev:
+            ev["cfm0"].record()
+        L = mu.shape[2]
+        feat, _ = self.decoder(mu=mu, mask=torch.ones(1, 1, L, device=self.device), n_timesteps=10, spks=spks, cond=cond)
+        if ev:
+            ev["cfm1"].record()
+            self.events.update(ev)
+        return feat[:, :, mel_len1:].contiguous()
+
+    @torch.inference_mode()
+    def hift_inference(self, speech_feat, cache_source: Optional[torch.Tensor] = None, *, seed: Optional[int] = None,
+                       apply_fade: bool = False):
+        return self.mel2wav.inference(speech_feat, cache_source, seed=seed, apply_fade=apply_fade)
+
+    @torch.inference_mode()
+    def inference(self, speech_tokens, ref_wav=None, ref_sr=None, ref_dict: Optional[dict] = None,
+                  cache_source: Optional[torch.Tensor] = None, finalize: bool = True, *, seed: Optional[int] = None):
+        """-> (wav (1, n), source (1, 1, n)); trim_fade (s3gen.py:296) is applied inside the vocoder's last kernel."""
+        mels = self.flow_inference(speech_tokens, ref_wav=ref_wav, ref_sr=ref_sr, ref_dict=ref_dict, finalize=finalize)
+        ev = {k: torch.cuda.Event(enable_timing=True) for k in ("hift0", "hift1")} if self.record_events else None
+        if ev:
+            ev["hift0"].record()
+        assert mels.shape[2] >= 2, "the reference's trim_fade needs at least 2 mel frames"
+        wav, src = self.hift_inference(mels, cache_source, seed=seed, apply_fade=True)
+        if ev:
+            ev["hift1"].record()
+            self.events.update(ev)
+        return wav, src
+
+    def launches(self) -> int:
+        return self.estimator.launches() + self.mel2wav.launches()

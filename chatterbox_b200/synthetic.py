@@ -262,6 +262,11 @@ def init_tensor(family: str, key: str, shape, seed: int) -> torch.Tensor:
         if last == "bias":
             return 0.02 * r
         w = 0.02 * r
+        if key == "speech_head.weight":
+            # a trained T3 does not emit the ids S3Gen cannot consume (>= 6561: BOS/EOS/unused, tts.py:257-262);
+            # zero rows give those ids logit 0, below the winning logit of any step, so synthetic utterances keep
+            # every generated token and the S3Gen workload is exactly 2 x 256 mel frames
+            w[S3_VOCAB:] = 0.0
         if key == "speech_head.weight" or (key.startswith("tfmr.layers.") and key.endswith("_proj.weight")):
             # the streamed matrices are made bf16-representable, so the reference (fp32 math) and the
             # build (bf16 storage, fp32 accumulate) run on IDENTICAL weights

@@ -1,0 +1,113 @@
+"""The drop-in boundary (chatterbox_b200.tts / vc / s3gen mirrors of the reference API): host logic on CPU,
+the full T3 -> S3Gen -> HiFT pipeline on the GPU against the chained CPU oracles."""
+import os
+
+import pytest
+import torch
+
+from chatterbox_b200 import synthetic as S
+
+
+def test_punc_norm_known_answers():
+    from chatterbox_b200.tts import punc_norm
+    assert punc_norm("") == "You need to add some text for me to talk."
+    assert punc_norm("hello   world") == "Hello world."
+    assert punc_norm("wait... what; no: yes") == "Wait,  what,  no, yes."     # replacements run after the space collapse
+    assert punc_norm("“quoted” – dash — ok!") == "\"quoted\" - dash - ok!"
+    assert punc_norm("trailing space ,here ") == "Trailing space,here."
+
+
+@pytest.mark.refonly
+def test_punc_norm_equals_reference_source():
+    """Executes the reference's own punc_norm (extracted from tts.py with ast; the module itself needs librosa)."""
+    import ast
+    from chatterbox_b200.tts import punc_norm
+    src = open("/root/reference/src/chatterbox/tts.py").read()
+    fn = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "punc_norm")
+    ns = {}
+    exec(compile(ast.Module([fn], []), "ref_punc_norm", "exec"), ns)
+    for t in ["", "a", "hello   world", "wait... what; no: yes", "x — y – z", "“q” ‘r’", "end , mid ;", "Ok?", "dash -",
+              "multi\nline  text…", " lead", "colon: semi; dots..."]:
+        assert punc_norm(t) == ns["punc_norm"](t), t
+
+
+def test_drop_invalid_tokens_and_conditionals_roundtrip(tmp_path):
+    from chatterbox_b200.tts import Conditionals, drop_invalid_tokens
+    from chatterbox_b200.t3 import T3Cond
+    assert drop_invalid_tokens(torch.tensor([6561, 5, 6, 6562, 7])).tolist() == [5, 6]
+    assert drop_invalid_tokens(torch.tensor([[1, 2, 3]])).tolist() == [1, 2, 3]
+    assert drop_invalid_tokens(torch.tensor([4, 6562])).tolist() == [4]
+    c = Conditionals(T3Cond(**S.t3_cond()), {k: v for k, v in S.s3gen_ref().items()})
+    p = tmp_path / "conds.pt"
+    c.save(p)
+    d = Conditionals.load(p)
+    assert torch.equal(d.t3.cond_prompt_speech_tokens, c.t3.cond_prompt_speech_tokens)
+    assert torch.equal(d.gen["prompt_feat"], c.gen["prompt_feat"]) and d.gen["prompt_feat_len"] is None
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_models_refuse_to_build_without_cuda():
+    from chatterbox_b200._lib import CbxError
+    from chatterbox_b200.tts import ChatterboxTTS
+    with pytest.raises(CbxError):
+        ChatterboxTTS.from_state_dicts({}, {}, {}, "cuda")
+
+
+@pytest.fixture(scope="module")
+def tts():
+    from chatterbox_b200.t3 import T3Cond
+    from chatterbox_b200.tts import ChatterboxTTS, Conditionals
+    conds = Conditionals(T3Cond(**S.t3_cond(prompt_len=30)), S.s3gen_ref(seed=4, prompt_len=20))
+    return ChatterboxTTS.from_state_dicts(S.make_state_dict("t3"), S.make_state_dict("flow"), S.make_state_dict("hift"),
+                                          "cuda", conds=conds, rand_noise=S.cfm_noise(), max_speech_tokens=64,
+                                          max_text_tokens=32, max_prompt_tokens=32)
+
+
+@pytest.mark.gpu
+def test_generate_end_to_end(tts):
+    ids = S.text_tokens(10)[:, 1:-1]            # generate() adds SOT / EOT itself (tts.py:240-243)
+    wav = tts.generate(text_tokens=ids, do_sample=False, max_new_tokens=24, stop_on_eos=False, seed=3)
+    n_tok = int(tts.last_speech_tokens.numel())
+    assert wav.device.type == "cpu" and wav.shape == (1, 960 * n_tok) and n_tok > 0
+    assert torch.isfinite(wav).all() and float(wav.abs().max()) <= 0.99 + 1e-6
+    assert float(wav[0, :480].abs().max()) == 0.0
+    # sampling path + exaggeration update side effect (tts.py:225-231)
+    wav2 = tts.generate(text_tokens=ids, exaggeration=0.7, max_new_tokens=12, stop_on_eos=False, seed=4)
+    assert float(tts.conds.t3.emotion_adv[0, 0, 0]) == pytest.approx(0.7) and wav2.shape[0] == 1
+    with pytest.raises(AssertionError):
+        tts.generate(text="hello")            # no tokenizer.json offline
+
+
+@pytest.mark.gpu
+def test_s3gen_chain_matches_chained_oracles(tts):
+    """tokens -> mel -> wav on the GPU vs flow front-end + CFM oracle + HiFT oracle on the CPU, with the GPU's
+    own (stochastic) source signal injected into the oracle vocoder."""
+    from chatterbox_b200 import flow_frontend as FF
+    from oracle import cfm_oracle as CO, hift_oracle as HO
+    tok = S.speech_tokens(24, seed=9)
+    ref = S.s3gen_ref(seed=4, prompt_len=20)
+    wav, src = tts.s3gen.inference(tok, ref_dict=ref, seed=5)
+    mel_gpu = tts.s3gen.flow_inference(tok, ref_dict=ref).cpu()
+    sd = S.make_state_dict("flow")
+    with torch.inference_mode():
+        mu, spks, cond, l1 = FF.flow_inputs(sd, tok, ref["prompt_token"], ref["prompt_feat"], ref["embedding"])
+        mel = CO.solve_euler(sd, S.cfm_noise()[:, :, : mu.shape[2]], mu, spks, cond, pfx="decoder.estimator.")[:, :, l1:]
+        w = HO.fold_weight_norm(S.make_state_dict("hift"))
+        ref_wav, _ = HO.inference(w, mel, s=src.cpu())
+        ref_wav_same_mel, _ = HO.inference(w, mel_gpu, s=src.cpu())
+    r_mel = float((mel_gpu - mel).norm() / mel.norm())
+    r_voc = float((wav.cpu() - ref_wav_same_mel).norm() / ref_wav_same_mel.norm())
+    r_all = float((wav.cpu() - ref_wav).norm() / ref_wav.norm())
+    print(f"mel rel-L2 {r_mel:.3e}; vocoder (same mel) rel-L2 {r_voc:.3e}; chained wav rel-L2 {r_all:.3e}")
+    assert r_mel < 2e-2 and r_voc < 2e-2
+    assert r_all < 1e-1      # chained: the vocoder amplifies the (in-tolerance) mel difference
+
+
+@pytest.mark.gpu
+def test_vc_generate(tts):
+    from chatterbox_b200.vc import ChatterboxVC
+    vc = ChatterboxVC(tts.s3gen, "cuda", ref_dict=S.s3gen_ref(seed=4, prompt_len=20))
+    wav = vc.generate(speech_tokens=S.speech_tokens(20, seed=2), seed=1)
+    assert wav.shape == (1, 960 * 20) and wav.device.type == "cpu"
+    with pytest.raises(NotImplementedError):
+        vc.generate("some.wav")
