@@ -299,6 +299,10 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
   return CBX_OK;
 }
 
+namespace cbx { void gemm_set_debug(unsigned long long* buf); }
+/* Debug aid (not in cbx.h): every following GEMM launch writes 8 %globaltimer stamps of CTA (0,0) to buf and advances it. */
+extern "C" int cbx_dbg_gemm_stamps(unsigned long long* buf) { cbx::gemm_set_debug(buf); return 0; }
+
 extern "C" int cbx_cfm_launches(cbx_cfm* h, int64_t* launches) {
   CBX_CHECK(h && launches, "cbx_cfm_launches: null argument");
   *launches = h->launches;

@@ -60,6 +60,7 @@ struct GemmParams {
   CUtensorMap tmA, tmW;
   int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out;
   GemmEpi e;
+  unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0,0) (debug aid)
 };
 
 __device__ __forceinline__ float mish_f(float x) {
@@ -67,6 +68,13 @@ __device__ __forceinline__ float mish_f(float x) {
   return x * tanhf(sp);
 }
 __device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define GEMM_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0) p.dbg[k] = gtimer(); } while (0)
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -77,6 +85,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) GEMM_STAMP(0);
   const int b = blockIdx.x / p.tiles_l, t0 = (blockIdx.x % p.tiles_l) * BM;
   const int n0 = blockIdx.y * p.n_tile;
   const int kpb = p.K / BK, nkb = p.taps * kpb;
@@ -94,6 +103,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) GEMM_STAMP(1);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -107,6 +117,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
         tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kb * BK, n0, 0);
       }
+      GEMM_STAMP(2);
     }
   } else if (warp == 1) {
     if (lane == 0) {
@@ -123,17 +134,24 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         umma_commit(&empty[s]);
       }
       umma_commit(accum_bar);
+      GEMM_STAMP(3);
     }
   } else {
-    // ===== epilogue: thread <-> accumulator row =====
-    const int q = warp & 3, row = q * 32 + lane, t = t0 + row;
-    const bool valid = t < p.M_out;
-    const size_t grow = (size_t)b * p.M_out + (valid ? t : 0);
+    // ===== epilogue =====
+    // phase 1: thread <-> accumulator row (TMEM lane): bias, LayerNorm + Mish (+ time embedding), GELU / ELU in
+    //          registers; the fp32 tile goes to shared memory (the operand ring is idle once accum_bar fires);
+    // phase 2: warp <-> its own 32 rows with the lanes spread over the columns, so residual loads and every
+    //          store are coalesced, rows are processed four at a time to keep loads in flight, and the
+    //          LayerNorm feeding the next GEMM is a warp reduction.
+    const int q = warp & 3, row = q * 32 + lane;
     const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
     const GemmEpi& e = p.e;
     const int nch = p.n_tile / 16;
+    const int pitch = p.n_tile + 4;            // floats: row-per-lane float4 stores stay bank-conflict free
+    float* tile = reinterpret_cast<float*>(smem);
     mbar_wait_spin(accum_bar, 0);
     tc_fence_after();
+    if (threadIdx.x == 64) GEMM_STAMP(4);
     float mean1 = 0.f, rstd1 = 1.f;
     if (e.ln_g) {
       float s1 = 0.f, s2 = 0.f;
@@ -149,7 +167,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       mean1 = s1 / p.n_tile;
       rstd1 = rsqrtf(fmaxf(s2 / p.n_tile - mean1 * mean1, 0.f) + 1e-5f);
     }
-    float t1 = 0.f, t2 = 0.f;
     for (int c = 0; c < nch; ++c) {
       float v[16];
       tmem_ld16(trow + c * 16, v);
@@ -166,65 +183,120 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         if (e.elu) x = x > 0.f ? x : expm1f(x);
         v[i] = x;
       }
-      if (valid) {
-        if (e.resid) {
-          const float4* r = reinterpret_cast<const float4*>(e.resid + grow * e.ld_resid + nb);
+      float4* dst = reinterpret_cast<float4*>(tile + (size_t)row * pitch + c * 16);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { const float4 rr = r[i]; v[4 * i] += rr.x; v[4 * i + 1] += rr.y; v[4 * i + 2] += rr.z; v[4 * i + 3] += rr.w; }
+      for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+    __syncwarp();
+    if (threadIdx.x == 64) GEMM_STAMP(5);
+    // ---- phase 2 ----
+    const int ngrp = p.n_tile / 4;             // float4 column groups per row; lane owns groups lane and lane + 32
+    float g2[2][4], b2[2][4], sa[2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int gi = lane + 32 * i;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const bool ok = gi < ngrp;
+        g2[i][k] = (ok && e.out_ln) ? __ldg(e.ln2_g + n0 + gi * 4 + k) : 0.f;
+        b2[i][k] = (ok && e.out_ln) ? __ldg(e.ln2_b + n0 + gi * 4 + k) : 0.f;
+        sa[i][k] = (ok && e.snake_alpha) ? __ldg(e.snake_alpha + n0 + gi * 4 + k) : 1.f;
+      }
+    }
+    for (int r0 = 0; r0 < 32; r0 += 4) {
+      float4 v[4][2];
+      bool okr[4];
+      size_t grow[4];
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr) {
+        const int r = q * 32 + r0 + rr, t = t0 + r;
+        okr[rr] = t < p.M_out;
+        grow[rr] = (size_t)b * p.M_out + (okr[rr] ? t : 0);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int gi = lane + 32 * i;
+          v[rr][i] = (gi < ngrp) ? *reinterpret_cast<const float4*>(tile + (size_t)r * pitch + gi * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        if (e.resid2) {
-          const float4* r = reinterpret_cast<const float4*>(e.resid2 + grow * e.ld_resid2 + nb);
+      }
+      if (e.resid) {
+        float4 rv[4][2];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { const float4 rr = r[i]; v[4 * i] += rr.x; v[4 * i + 1] += rr.y; v[4 * i + 2] += rr.z; v[4 * i + 3] += rr.w; }
-        }
-        if (e.out_f32) {
-          const long long off = (long long)(grow * e.ld_f32 + nb) + e.out_shift;
-          if (e.out_limit == 0 || (off >= 0 && off + 16 <= e.out_limit)) {
-            float4* o = reinterpret_cast<float4*>(e.out_f32 + off);
+        for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
-            for (int i = 0; i < 4; ++i) o[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          for (int i = 0; i < 2; ++i) {
+            const int gi = lane + 32 * i;
+            rv[rr][i] = (okr[rr] && gi < ngrp) ? *reinterpret_cast<const float4*>(e.resid + grow[rr] * e.ld_resid + n0 + gi * 4)
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
           }
-        }
-        if (e.out_bf16) {
-          if (e.snake_alpha) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float a = __ldg(e.snake_alpha + nb + i), sn = sinf(v[i] * a);
-              v[i] = v[i] + (1.0f / (a + 1e-9f)) * sn * sn;
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) { v[rr][i].x += rv[rr][i].x; v[rr][i].y += rv[rr][i].y; v[rr][i].z += rv[rr][i].z; v[rr][i].w += rv[rr][i].w; }
+      }
+      if (e.resid2) {
+        float4 rv[4][2];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int gi = lane + 32 * i;
+            rv[rr][i] = (okr[rr] && gi < ngrp) ? *reinterpret_cast<const float4*>(e.resid2 + grow[rr] * e.ld_resid2 + n0 + gi * 4)
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) { v[rr][i].x += rv[rr][i].x; v[rr][i].y += rv[rr][i].y; v[rr][i].z += rv[rr][i].z; v[rr][i].w += rv[rr][i].w; }
+      }
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr) {
+        float mean2 = 0.f, rstd2 = 1.f;
+        if (e.out_ln) {
+          float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            s1 += v[rr][i].x + v[rr][i].y + v[rr][i].z + v[rr][i].w;
+            s2 += v[rr][i].x * v[rr][i].x + v[rr][i].y * v[rr][i].y + v[rr][i].z * v[rr][i].z + v[rr][i].w * v[rr][i].w;
+          }
+          s1 = warp_sum(s1); s2 = warp_sum(s2);
+          mean2 = s1 / p.n_tile;
+          rstd2 = rsqrtf(fmaxf(s2 / p.n_tile - mean2 * mean2, 0.f) + 1e-5f);
+        }
+        if (!okr[rr]) continue;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int gi = lane + 32 * i;
+          if (gi >= ngrp) continue;
+          const int nb = n0 + gi * 4;
+          const float4 x = v[rr][i];
+          if (e.out_f32) {
+            const long long off = (long long)(grow[rr] * e.ld_f32 + nb) + e.out_shift;
+            if (e.out_limit == 0 || (off >= 0 && off + 4 <= e.out_limit)) *reinterpret_cast<float4*>(e.out_f32 + off) = x;
+          }
+          if (e.out_bf16) {
+            float y[4] = {x.x, x.y, x.z, x.w};
+            if (e.snake_alpha) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) { const float sn = sinf(y[k] * sa[i][k]); y[k] = y[k] + (1.0f / (sa[i][k] + 1e-9f)) * sn * sn; }
+            } else if (e.lrelu != 0.f) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) y[k] = y[k] > 0.f ? y[k] : y[k] * e.lrelu;
             }
-          } else if (e.lrelu != 0.f) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * e.lrelu;
+            *reinterpret_cast<uint2*>(e.out_bf16 + grow[rr] * e.ld_bf16 + nb) = make_uint2(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]));
           }
-          uint4* o = reinterpret_cast<uint4*>(e.out_bf16 + grow * e.ld_bf16 + nb);
-          o[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-          o[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+          if (e.out_ln) {
+            const float y0 = (x.x - mean2) * rstd2 * g2[i][0] + b2[i][0], y1 = (x.y - mean2) * rstd2 * g2[i][1] + b2[i][1];
+            const float y2 = (x.z - mean2) * rstd2 * g2[i][2] + b2[i][2], y3 = (x.w - mean2) * rstd2 * g2[i][3] + b2[i][3];
+            *reinterpret_cast<uint2*>(e.out_ln + grow[rr] * e.ld_ln + nb) = make_uint2(pack_bf16x2(y0, y1), pack_bf16x2(y2, y3));
+          }
         }
       }
-      if (e.out_ln) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) { t1 += v[i]; t2 += v[i] * v[i]; }
-      }
     }
-    if (e.out_ln && valid) {
-      const float mean2 = t1 / p.n_tile;
-      const float rstd2 = rsqrtf(fmaxf(t2 / p.n_tile - mean2 * mean2, 0.f) + 1e-5f);
-      for (int c = 0; c < nch; ++c) {
-        const int nb = n0 + c * 16;
-        const float4* src = reinterpret_cast<const float4*>(e.out_f32 + grow * e.ld_f32 + nb);   // own writes
-        float v[16];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { const float4 rr = src[i]; v[4 * i] = rr.x; v[4 * i + 1] = rr.y; v[4 * i + 2] = rr.z; v[4 * i + 3] = rr.w; }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = (v[i] - mean2) * rstd2 * __ldg(e.ln2_g + nb + i) + __ldg(e.ln2_b + nb + i);
-        uint4* o = reinterpret_cast<uint4*>(e.out_ln + grow * e.ld_ln + nb);
-        o[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-        o[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
-      }
-    }
+    if (threadIdx.x == 64) GEMM_STAMP(6);
     tc_fence_before();
   }
   __syncthreads();
+  if (threadIdx.x == 0) GEMM_STAMP(7);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, tmem_cols);
@@ -246,13 +318,15 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
   CBX_CHECK(n_tile > 0, "gemm_make: N=%d unsupported (needs a divisor that is a multiple of 16, <= 256)", N);
   CBX_CHECK(B == 1 || M_out == L, "gemm_make: M_out != L needs B == 1");
   CBX_CHECK(!(epi.ln_g || epi.out_ln) || n_tile == N, "gemm_make: row LayerNorm needs the whole row in one tile (N=%d)", N);
-  CBX_CHECK(!epi.out_ln || epi.out_f32, "gemm_make: out_ln needs out_f32");
-  d->B = B; d->L = L; d->N = N; d->K = K; d->taps = taps; d->n_tile = n_tile; d->epi = epi;
+    d->B = B; d->L = L; d->N = N; d->K = K; d->taps = taps; d->n_tile = n_tile; d->epi = epi;
   d->dil = dil; d->pad = pad; d->M_out = M_out;
   if (make_tmap_bf16_3d(&d->tmA, A, K, L, B, lda, (uint64_t)lda * L, BK, BM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW, W, (uint64_t)taps * K, N, 1, (uint64_t)taps * K, (uint64_t)taps * K * N, BK, n_tile)) return CBX_ERR;
   return CBX_OK;
 }
+
+static unsigned long long* g_gemm_dbg = nullptr;
+void gemm_set_debug(unsigned long long* buf) { g_gemm_dbg = buf; }
 
 int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   static bool attr_set = false;
@@ -266,6 +340,8 @@ int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out;
   p.tiles_l = (d.M_out + BM - 1) / BM;
   p.e = d.epi;
+  p.dbg = g_gemm_dbg;
+  if (g_gemm_dbg) g_gemm_dbg += 8;
   dim3 grid(d.B * p.tiles_l, d.N / d.n_tile);
   s3_gemm_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(p);
   CBX_CUDA(cudaGetLastError());

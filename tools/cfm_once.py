@@ -1,0 +1,21 @@
+"""One CFM solve at the bench shape (L = 812) — a short target for ncu captures of the GEMM / attention kernels."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from chatterbox_b200 import synthetic as S
+from chatterbox_b200.cfm import CausalConditionalCFM, ConditionalDecoder
+
+L = int(sys.argv[1]) if len(sys.argv) > 1 else 812
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+est = ConditionalDecoder(S.make_state_dict("flow"), "cuda", prefix="decoder.estimator.", max_len=1024)
+cfm = CausalConditionalCFM(est, rand_noise=S.cfm_noise())
+inp = {k: v.cuda() for k, v in S.cfm_inputs(L).items()}
+for _ in range(2):
+    cfm(mu=inp["mu"], mask=torch.ones(1, 1, L), n_timesteps=steps, spks=inp["spks"], cond=inp["cond"])
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+cfm(mu=inp["mu"], mask=torch.ones(1, 1, L), n_timesteps=steps, spks=inp["spks"], cond=inp["cond"])
+e1.record()
+torch.cuda.synchronize()
+print(f"cfm solve L={L} steps={steps}: {e0.elapsed_time(e1):.2f} ms, launches so far {est.launches()}")
