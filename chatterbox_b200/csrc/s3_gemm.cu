@@ -10,9 +10,12 @@
 //   warp 1   : MMA issuer — one elected thread issues tcgen05.mma (kind::f16, bf16 x bf16 -> fp32,
 //              M = 128, N = n_tile, K = 16) x 4 per stage, tcgen05.commit frees the stage / signals
 //              the epilogue; also owns the TMEM allocation;
-//   warps 2-5: epilogue — each thread owns one accumulator row (TMEM lane) and walks its columns with
-//              tcgen05.ld: bias, LayerNorm-over-channels + Mish (+ time embedding), exact GELU,
-//              residual add, fp32 / bf16 stores, and the LayerNorm feeding the next GEMM.
+//   warps 2-5: drain — each thread owns one accumulator row (TMEM lane) and copies it with tcgen05.ld to an
+//              fp32 tile in shared memory (the operand ring, idle by then);
+//   warps 6-15 stage the per-column epilogue vectors meanwhile; then all 16 warps run the epilogue with the
+//              lanes across columns (coalesced): bias, LayerNorm-over-channels + Mish (+ time embedding),
+//              GELU / ELU, residual adds, fp32 / bf16 stores (Snake / leaky-ReLU), and the LayerNorm
+//              feeding the next GEMM.
 #include "s3_gemm.cuh"
 #include "../../include/cbx.h"
 
@@ -53,8 +56,10 @@ constexpr int BM = 128, BK = 64, STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;                 // 16 KB
 constexpr int W_BYTES_MAX = 256 * BK * 2;            // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + W_BYTES_MAX;
-constexpr int GEMM_THREADS = 192;
-constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int GEMM_THREADS = 512;
+enum { PAR_BIAS = 0, PAR_G1, PAR_B1, PAR_TEMB, PAR_G2, PAR_B2, PAR_ALPHA, PAR_COUNT };   // per-column epilogue vectors
+constexpr int PAR_BYTES = PAR_COUNT * 256 * 4;
+constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + PAR_BYTES;
 
 struct GemmParams {
   CUtensorMap tmA, tmW;
@@ -63,11 +68,31 @@ struct GemmParams {
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0,0) (debug aid)
 };
 
+// mish(x) = x tanh(softplus(x)) = x t / (t + 2) with t = e^x (e^x + 2); one ex2 and one fast division
 __device__ __forceinline__ float mish_f(float x) {
-  const float sp = (x > 20.f) ? x : log1pf(expf(x));
-  return x * tanhf(sp);
+  const float n = __expf(fminf(x, 20.f));
+  const float t = n * (n + 2.0f);
+  return x * __fdividef(t, t + 2.0f);
 }
-__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// exact-GELU through erf(z) = sign(z) (1 - P(u) e^{-z^2}), u = 1 / (1 + 0.3275911 |z|)  (Abramowitz-Stegun 7.1.26,
+// |error| <= 1.5e-7 — two orders below the bf16 rounding of the value this feeds)
+__device__ __forceinline__ float gelu_f(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float u = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  float pl = fmaf(1.061405429f, u, -1.453152027f);
+  pl = fmaf(pl, u, 1.421413741f);
+  pl = fmaf(pl, u, -0.284496736f);
+  pl = fmaf(pl, u, 0.254829592f);
+  const float er = 1.0f - pl * u * __expf(-z * z);
+  return 0.5f * x * (1.0f + copysignf(er, x));
+}
+// sin with a two-constant Cody-Waite reduction to [-pi, pi] ahead of the SFU approximation
+__device__ __forceinline__ float sin_f(float x) {
+  const float k = rintf(x * 0.15915494309189535f);
+  float r = fmaf(k, -6.28318548202514648f, x);
+  r = fmaf(k, 1.74845553e-7f, r);
+  return __sinf(r);
+}
 
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
@@ -83,12 +108,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   uint64_t* empty = full + STAGES;
   uint64_t* accum_bar = empty + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  float* par = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
+  float* tile = reinterpret_cast<float*>(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) GEMM_STAMP(0);
   const int b = blockIdx.x / p.tiles_l, t0 = (blockIdx.x % p.tiles_l) * BM;
   const int n0 = blockIdx.y * p.n_tile;
   const int kpb = p.K / BK, nkb = p.taps * kpb;
+  const int pitch = p.n_tile + 4;            // floats: row-per-lane float4 stores stay bank-conflict free
   const uint32_t tmem_cols = p.n_tile > 128 ? 256u : (p.n_tile > 64 ? 128u : (p.n_tile > 32 ? 64u : 32u));
 
   if (threadIdx.x == 0) {
@@ -136,165 +164,223 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       umma_commit(accum_bar);
       GEMM_STAMP(3);
     }
+  } else if (warp >= 6) {
+    // idle until the epilogue: stage the per-column epilogue vectors of this tile in shared memory
+    const GemmEpi& e = p.e;
+    for (int c = threadIdx.x - 6 * 32; c < p.n_tile; c += GEMM_THREADS - 6 * 32) {
+      const int n = n0 + c;
+      par[PAR_BIAS * 256 + c] = e.bias ? __ldg(e.bias + (e.bias_mod > 0 ? n % e.bias_mod : n)) : 0.f;
+      par[PAR_G1 * 256 + c] = e.ln_g ? __ldg(e.ln_g + n) : 0.f;
+      par[PAR_B1 * 256 + c] = e.ln_g ? __ldg(e.ln_b + n) : 0.f;
+      par[PAR_TEMB * 256 + c] = e.temb ? __ldg(e.temb + (size_t)b * p.N + n) : 0.f;
+      par[PAR_G2 * 256 + c] = e.out_ln ? __ldg(e.ln2_g + n) : 0.f;
+      par[PAR_B2 * 256 + c] = e.out_ln ? __ldg(e.ln2_b + n) : 0.f;
+      par[PAR_ALPHA * 256 + c] = e.snake_alpha ? __ldg(e.snake_alpha + n) : 1.f;
+    }
   } else {
-    // ===== epilogue =====
-    // phase 1: thread <-> accumulator row (TMEM lane): bias, LayerNorm + Mish (+ time embedding), GELU / ELU in
-    //          registers; the fp32 tile goes to shared memory (the operand ring is idle once accum_bar fires);
-    // phase 2: warp <-> its own 32 rows with the lanes spread over the columns, so residual loads and every
-    //          store are coalesced, rows are processed four at a time to keep loads in flight, and the
-    //          LayerNorm feeding the next GEMM is a warp reduction.
+    // ===== epilogue, phase 1 (warps 2-5): drain the accumulator, thread <-> row (TMEM lane), to an fp32 tile in
+    // shared memory (the operand ring is idle once accum_bar fires) =====
     const int q = warp & 3, row = q * 32 + lane;
     const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
-    const GemmEpi& e = p.e;
-    const int nch = p.n_tile / 16;
-    const int pitch = p.n_tile + 4;            // floats: row-per-lane float4 stores stay bank-conflict free
-    float* tile = reinterpret_cast<float*>(smem);
     mbar_wait_spin(accum_bar, 0);
     tc_fence_after();
     if (threadIdx.x == 64) GEMM_STAMP(4);
-    float mean1 = 0.f, rstd1 = 1.f;
-    if (e.ln_g) {
-      float s1 = 0.f, s2 = 0.f;
-      for (int c = 0; c < nch; ++c) {
-        float v[16];
-        tmem_ld16(trow + c * 16, v);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float x = v[i] + (e.bias ? __ldg(e.bias + n0 + c * 16 + i) : 0.f);
-          s1 += x; s2 += x * x;
-        }
-      }
-      mean1 = s1 / p.n_tile;
-      rstd1 = rsqrtf(fmaxf(s2 / p.n_tile - mean1 * mean1, 0.f) + 1e-5f);
-    }
+    const int nch = p.n_tile / 16;
     for (int c = 0; c < nch; ++c) {
       float v[16];
       tmem_ld16(trow + c * 16, v);
-      const int nb = n0 + c * 16;
-      const int bb0 = e.bias_mod > 0 ? nb % e.bias_mod : nb;
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        float x = v[i] + (e.bias ? __ldg(e.bias + bb0 + i) : 0.f);
-        if (e.ln_g) {
-          x = mish_f((x - mean1) * rstd1 * __ldg(e.ln_g + nb + i) + __ldg(e.ln_b + nb + i));
-          if (e.temb) x += __ldg(e.temb + (size_t)b * p.N + nb + i);
-        }
-        if (e.gelu) x = gelu_f(x);
-        if (e.elu) x = x > 0.f ? x : expm1f(x);
-        v[i] = x;
-      }
       float4* dst = reinterpret_cast<float4*>(tile + (size_t)row * pitch + c * 16);
 #pragma unroll
       for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
     }
-    __syncwarp();
+    tc_fence_before();
     if (threadIdx.x == 64) GEMM_STAMP(5);
-    // ---- phase 2 ----
-    const int ngrp = p.n_tile / 4;             // float4 column groups per row; lane owns groups lane and lane + 32
-    float g2[2][4], b2[2][4], sa[2][4];
+  }
+  __syncthreads();
+  // ===== epilogue, phase 2 (all 16 warps): warp <-> 8 rows, lanes across float4 column groups (lane, lane + 32),
+  // four rows in flight: bias, LayerNorm + Mish (+ time embedding), GELU / ELU, residuals, stores, next LayerNorm.
+  // Every mode test below is on a kernel parameter, hoisted out of the element loops. =====
+  {
+    const GemmEpi& e = p.e;
+    const bool has_ln1 = e.ln_g != nullptr, has_gelu = e.gelu != 0, has_elu = e.elu != 0;
+    const bool has_ln2 = e.out_ln != nullptr, has_snake = e.snake_alpha != nullptr;
+    const float inv_n = 1.0f / (float)p.n_tile;
+    const int ngrp = p.n_tile / 4;
+    const bool g_ok[2] = {lane < ngrp, lane + 32 < ngrp};
+    const int gcol[2] = {lane * 4, g_ok[1] ? (lane + 32) * 4 : 0};
+    float4 bias4[2];
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int gi = lane + 32 * i;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const bool ok = gi < ngrp;
-        g2[i][k] = (ok && e.out_ln) ? __ldg(e.ln2_g + n0 + gi * 4 + k) : 0.f;
-        b2[i][k] = (ok && e.out_ln) ? __ldg(e.ln2_b + n0 + gi * 4 + k) : 0.f;
-        sa[i][k] = (ok && e.snake_alpha) ? __ldg(e.snake_alpha + n0 + gi * 4 + k) : 1.f;
-      }
-    }
-    for (int r0 = 0; r0 < 32; r0 += 4) {
-      float4 v[4][2];
+    for (int i = 0; i < 2; ++i) bias4[i] = g_ok[i] ? *reinterpret_cast<const float4*>(par + PAR_BIAS * 256 + gcol[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int r0 = warp * 8; r0 < warp * 8 + 8; r0 += 4) {
+      float x[4][2][4];
       bool okr[4];
       size_t grow[4];
 #pragma unroll
       for (int rr = 0; rr < 4; ++rr) {
-        const int r = q * 32 + r0 + rr, t = t0 + r;
+        const int t = t0 + r0 + rr;
         okr[rr] = t < p.M_out;
         grow[rr] = (size_t)b * p.M_out + (okr[rr] ? t : 0);
+      }
+      // residual loads first: they overlap the LayerNorm / activation math below
+      float4 rv[4][2];
+      if (e.resid) {
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+            rv[rr][i] = (okr[rr] && g_ok[i]) ? *reinterpret_cast<const float4*>(e.resid + grow[rr] * e.ld_resid + n0 + gcol[i])
+                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-          const int gi = lane + 32 * i;
-          v[rr][i] = (gi < ngrp) ? *reinterpret_cast<const float4*>(tile + (size_t)r * pitch + gi * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float4 v = g_ok[i] ? *reinterpret_cast<const float4*>(tile + (size_t)(r0 + rr) * pitch + gcol[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          x[rr][i][0] = v.x + bias4[i].x; x[rr][i][1] = v.y + bias4[i].y; x[rr][i][2] = v.z + bias4[i].z; x[rr][i][3] = v.w + bias4[i].w;
         }
+      if (has_ln1) {
+        float s1[4], s2[4];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+          s1[rr] = 0.f; s2[rr] = 0.f;
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { s1[rr] += x[rr][i][k]; s2[rr] += x[rr][i][k] * x[rr][i][k]; }   // masked groups hold zeros
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr) {
+            s1[rr] += __shfl_xor_sync(0xffffffffu, s1[rr], o);
+            s2[rr] += __shfl_xor_sync(0xffffffffu, s2[rr], o);
+          }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          if (!g_ok[i]) continue;
+          const float4 g = *reinterpret_cast<const float4*>(par + PAR_G1 * 256 + gcol[i]);
+          const float4 bb = *reinterpret_cast<const float4*>(par + PAR_B1 * 256 + gcol[i]);
+          const float4 te = *reinterpret_cast<const float4*>(par + PAR_TEMB * 256 + gcol[i]);
+          const float gg[4] = {g.x, g.y, g.z, g.w}, bv[4] = {bb.x, bb.y, bb.z, bb.w}, tv[4] = {te.x, te.y, te.z, te.w};
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr) {
+            const float mean = s1[rr] * inv_n;
+            const float rstd = rsqrtf(fmaxf(s2[rr] * inv_n - mean * mean, 0.f) + 1e-5f);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) x[rr][i][k] = mish_f((x[rr][i][k] - mean) * rstd * gg[k] + bv[k]) + tv[k];
+          }
+        }
+      }
+      if (has_gelu) {
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) x[rr][i][k] = gelu_f(x[rr][i][k]);
+      }
+      if (has_elu) {
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) x[rr][i][k] = x[rr][i][k] > 0.f ? x[rr][i][k] : __expf(x[rr][i][k]) - 1.0f;
       }
       if (e.resid) {
-        float4 rv[4][2];
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const int gi = lane + 32 * i;
-            rv[rr][i] = (okr[rr] && gi < ngrp) ? *reinterpret_cast<const float4*>(e.resid + grow[rr] * e.ld_resid + n0 + gi * 4)
-                                              : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-#pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
-#pragma unroll
-          for (int i = 0; i < 2; ++i) { v[rr][i].x += rv[rr][i].x; v[rr][i].y += rv[rr][i].y; v[rr][i].z += rv[rr][i].z; v[rr][i].w += rv[rr][i].w; }
+          for (int i = 0; i < 2; ++i) { x[rr][i][0] += rv[rr][i].x; x[rr][i][1] += rv[rr][i].y; x[rr][i][2] += rv[rr][i].z; x[rr][i][3] += rv[rr][i].w; }
       }
       if (e.resid2) {
-        float4 rv[4][2];
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const int gi = lane + 32 * i;
-            rv[rr][i] = (okr[rr] && gi < ngrp) ? *reinterpret_cast<const float4*>(e.resid2 + grow[rr] * e.ld_resid2 + n0 + gi * 4)
-                                              : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
+          for (int i = 0; i < 2; ++i)
+            rv[rr][i] = (okr[rr] && g_ok[i]) ? *reinterpret_cast<const float4*>(e.resid2 + grow[rr] * e.ld_resid2 + n0 + gcol[i])
+                                             : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
-          for (int i = 0; i < 2; ++i) { v[rr][i].x += rv[rr][i].x; v[rr][i].y += rv[rr][i].y; v[rr][i].z += rv[rr][i].z; v[rr][i].w += rv[rr][i].w; }
+          for (int i = 0; i < 2; ++i) { x[rr][i][0] += rv[rr][i].x; x[rr][i][1] += rv[rr][i].y; x[rr][i][2] += rv[rr][i].z; x[rr][i][3] += rv[rr][i].w; }
       }
+      if (e.out_f32) {
 #pragma unroll
-      for (int rr = 0; rr < 4; ++rr) {
-        float mean2 = 0.f, rstd2 = 1.f;
-        if (e.out_ln) {
-          float s1 = 0.f, s2 = 0.f;
+        for (int rr = 0; rr < 4; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i) {
-            s1 += v[rr][i].x + v[rr][i].y + v[rr][i].z + v[rr][i].w;
-            s2 += v[rr][i].x * v[rr][i].x + v[rr][i].y * v[rr][i].y + v[rr][i].z * v[rr][i].z + v[rr][i].w * v[rr][i].w;
+            if (!okr[rr] || !g_ok[i]) continue;
+            const long long off = (long long)(grow[rr] * e.ld_f32 + n0 + gcol[i]) + e.out_shift;
+            if (e.out_limit == 0 || (off >= 0 && off + 4 <= e.out_limit))
+              *reinterpret_cast<float4*>(e.out_f32 + off) = make_float4(x[rr][i][0], x[rr][i][1], x[rr][i][2], x[rr][i][3]);
           }
-          s1 = warp_sum(s1); s2 = warp_sum(s2);
-          mean2 = s1 / p.n_tile;
-          rstd2 = rsqrtf(fmaxf(s2 / p.n_tile - mean2 * mean2, 0.f) + 1e-5f);
+      }
+      if (e.out_bf16) {
+        float al[2][4], ial[2][4];
+        if (has_snake) {
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const float4 a4 = *reinterpret_cast<const float4*>(par + PAR_ALPHA * 256 + gcol[i]);
+            al[i][0] = a4.x; al[i][1] = a4.y; al[i][2] = a4.z; al[i][3] = a4.w;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) ial[i][k] = 1.0f / (al[i][k] + 1e-9f);
+          }
         }
-        if (!okr[rr]) continue;
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            if (!okr[rr] || !g_ok[i]) continue;
+            float y[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              y[k] = x[rr][i][k];
+              if (has_snake) { const float sn = sin_f(y[k] * al[i][k]); y[k] += ial[i][k] * sn * sn; }
+              else if (e.lrelu != 0.f) y[k] = y[k] > 0.f ? y[k] : y[k] * e.lrelu;
+            }
+            *reinterpret_cast<uint2*>(e.out_bf16 + grow[rr] * e.ld_bf16 + n0 + gcol[i]) = make_uint2(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]));
+          }
+      }
+      if (has_ln2) {
+        float s1[4], s2[4];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+          s1[rr] = 0.f; s2[rr] = 0.f;
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            if (!g_ok[i]) continue;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { s1[rr] += x[rr][i][k]; s2[rr] += x[rr][i][k] * x[rr][i][k]; }
+          }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr) {
+            s1[rr] += __shfl_xor_sync(0xffffffffu, s1[rr], o);
+            s2[rr] += __shfl_xor_sync(0xffffffffu, s2[rr], o);
+          }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-          const int gi = lane + 32 * i;
-          if (gi >= ngrp) continue;
-          const int nb = n0 + gi * 4;
-          const float4 x = v[rr][i];
-          if (e.out_f32) {
-            const long long off = (long long)(grow[rr] * e.ld_f32 + nb) + e.out_shift;
-            if (e.out_limit == 0 || (off >= 0 && off + 4 <= e.out_limit)) *reinterpret_cast<float4*>(e.out_f32 + off) = x;
-          }
-          if (e.out_bf16) {
-            float y[4] = {x.x, x.y, x.z, x.w};
-            if (e.snake_alpha) {
+          if (!g_ok[i]) continue;
+          const float4 g = *reinterpret_cast<const float4*>(par + PAR_G2 * 256 + gcol[i]);
+          const float4 bb = *reinterpret_cast<const float4*>(par + PAR_B2 * 256 + gcol[i]);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) { const float sn = sinf(y[k] * sa[i][k]); y[k] = y[k] + (1.0f / (sa[i][k] + 1e-9f)) * sn * sn; }
-            } else if (e.lrelu != 0.f) {
-#pragma unroll
-              for (int k = 0; k < 4; ++k) y[k] = y[k] > 0.f ? y[k] : y[k] * e.lrelu;
-            }
-            *reinterpret_cast<uint2*>(e.out_bf16 + grow[rr] * e.ld_bf16 + nb) = make_uint2(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]));
-          }
-          if (e.out_ln) {
-            const float y0 = (x.x - mean2) * rstd2 * g2[i][0] + b2[i][0], y1 = (x.y - mean2) * rstd2 * g2[i][1] + b2[i][1];
-            const float y2 = (x.z - mean2) * rstd2 * g2[i][2] + b2[i][2], y3 = (x.w - mean2) * rstd2 * g2[i][3] + b2[i][3];
-            *reinterpret_cast<uint2*>(e.out_ln + grow[rr] * e.ld_ln + nb) = make_uint2(pack_bf16x2(y0, y1), pack_bf16x2(y2, y3));
+          for (int rr = 0; rr < 4; ++rr) {
+            if (!okr[rr]) continue;
+            const float mean = s1[rr] * inv_n;
+            const float rstd = rsqrtf(fmaxf(s2[rr] * inv_n - mean * mean, 0.f) + 1e-5f);
+            const float y0 = (x[rr][i][0] - mean) * rstd * g.x + bb.x, y1 = (x[rr][i][1] - mean) * rstd * g.y + bb.y;
+            const float y2 = (x[rr][i][2] - mean) * rstd * g.z + bb.z, y3 = (x[rr][i][3] - mean) * rstd * g.w + bb.w;
+            *reinterpret_cast<uint2*>(e.out_ln + grow[rr] * e.ld_ln + n0 + gcol[i]) = make_uint2(pack_bf16x2(y0, y1), pack_bf16x2(y2, y3));
           }
         }
       }
     }
-    if (threadIdx.x == 64) GEMM_STAMP(6);
-    tc_fence_before();
   }
+  if (threadIdx.x == 64) GEMM_STAMP(6);
   __syncthreads();
   if (threadIdx.x == 0) GEMM_STAMP(7);
   if (warp == 1) {
