@@ -17,6 +17,7 @@
 //              GELU / ELU, residual adds, fp32 / bf16 stores (Snake / leaky-ReLU), and the LayerNorm
 //              feeding the next GEMM.
 #include "s3_gemm.cuh"
+#include <cstdlib>
 #include "../../include/cbx.h"
 
 namespace cbx {
@@ -57,13 +58,15 @@ constexpr int A_BYTES = BM * BK * 2;                 // 16 KB
 constexpr int W_BYTES_MAX = 256 * BK * 2;            // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + W_BYTES_MAX;
 constexpr int GEMM_THREADS = 512;
+constexpr int MAX_SPLIT = 4;                         // largest split-K cluster
+constexpr int EPI_R = 2;                             // rows per epilogue iteration and warp
 enum { PAR_BIAS = 0, PAR_G1, PAR_B1, PAR_TEMB, PAR_G2, PAR_B2, PAR_ALPHA, PAR_COUNT };   // per-column epilogue vectors
 constexpr int PAR_BYTES = PAR_COUNT * 256 * 4;
 constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + PAR_BYTES;
 
 struct GemmParams {
   CUtensorMap tmA, tmW;
-  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out;
+  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out, ksplit;
   GemmEpi e;
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0,0) (debug aid)
 };
@@ -99,8 +102,15 @@ __device__ __forceinline__ unsigned long long gtimer() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-#define GEMM_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0) p.dbg[k] = gtimer(); } while (0)
+#define GEMM_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) p.dbg[k] = gtimer(); } while (0)
 
+// FEAT: the epilogue features an instantiation carries code for.  The epilogue body runs cold once per CTA, so
+// what it costs is instruction fetch over everything on its path — dispatching to the narrowest instantiation
+// (gemm_launch) keeps the common estimator epilogues short.
+enum : uint32_t { F_LN1 = 1, F_GELU = 2, F_ELU = 4, F_RESID = 8, F_RESID2 = 16, F_F32 = 32, F_BF16 = 64, F_LN2 = 128,
+                  F_ACT = 256 /* snake / leaky-relu on the bf16 output */, F_SHIFT = 512, F_ALL = 1023 };
+
+template <uint32_t FEAT>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -115,7 +125,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   if (threadIdx.x == 0) GEMM_STAMP(0);
   const int b = blockIdx.x / p.tiles_l, t0 = (blockIdx.x % p.tiles_l) * BM;
   const int n0 = blockIdx.y * p.n_tile;
-  const int kpb = p.K / BK, nkb = p.taps * kpb;
+  // split-K over a cluster (1, 1, S): CTA `rank` accumulates K panels [kb0, kb0 + nkb) of the tile into its own
+  // TMEM, the partial tiles meet in distributed shared memory and each CTA finishes 128 / S rows of the tile
+  const int S = p.ksplit, rank = blockIdx.z;
+  const int kpb = p.K / BK, nkb_all = p.taps * kpb;
+  const int nkb = nkb_all / S + (rank < nkb_all % S ? 1 : 0);                 // >= 1 (host: nkb_all >= S)
+  const int kb0 = rank * (nkb_all / S) + min(rank, nkb_all % S);
+  const int row_base = rank * (BM / S), rpw = 8 / S;        // epilogue rows of this CTA / per warp
   const int pitch = p.n_tile + 4;            // floats: row-per-lane float4 stores stay bank-conflict free
   const uint32_t tmem_cols = p.n_tile > 128 ? 256u : (p.n_tile > 64 ? 128u : (p.n_tile > 32 ? 64u : 32u));
 
@@ -133,11 +149,39 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   const uint32_t tmem_base = *tmem_slot;
   if (threadIdx.x == 0) GEMM_STAMP(1);
 
+  // epilogue state shared by all warps (see phase 2 below)
+  const GemmEpi& e = p.e;
+  const bool has_ln1 = (FEAT & F_LN1) && e.ln_g != nullptr, has_gelu = (FEAT & F_GELU) && e.gelu != 0;
+  const bool has_elu = (FEAT & F_ELU) && e.elu != 0, has_resid = (FEAT & F_RESID) && e.resid != nullptr;
+  const bool has_resid2 = (FEAT & F_RESID2) && e.resid2 != nullptr;
+  const bool has_f32 = (FEAT & F_F32) && e.out_f32 != nullptr, has_bf16 = (FEAT & F_BF16) && e.out_bf16 != nullptr;
+  const bool has_ln2 = (FEAT & F_LN2) && e.out_ln != nullptr, has_snake = (FEAT & F_ACT) && e.snake_alpha != nullptr;
+  const float lrelu = (FEAT & F_ACT) ? e.lrelu : 0.f;
+  const long long out_shift = (FEAT & F_SHIFT) ? e.out_shift : 0, out_limit = (FEAT & F_SHIFT) ? e.out_limit : 0;
+  const int ngrp = p.n_tile / 4;
+  const bool g_ok[2] = {lane < ngrp, lane + 32 < ngrp};
+  const int gcol[2] = {lane * 4, g_ok[1] ? (lane + 32) * 4 : 0};
+  float4 rvn[EPI_R][2];
+  auto load_resid = [&](int r0) {
+#pragma unroll
+    for (int rr = 0; rr < EPI_R; ++rr) {
+      const int t = t0 + r0 + rr;
+      const size_t gr = (size_t)b * p.M_out + (t < p.M_out ? t : 0);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+        rvn[rr][i] = (t < p.M_out && g_ok[i]) ? *reinterpret_cast<const float4*>(e.resid + gr * e.ld_resid + n0 + gcol[i])
+                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+#pragma unroll
+  for (int rr = 0; rr < EPI_R; ++rr) { rvn[rr][0] = make_float4(0.f, 0.f, 0.f, 0.f); rvn[rr][1] = rvn[rr][0]; }
+  if (has_resid) load_resid(row_base + warp * rpw);
+
   if (warp == 0) {
     if (lane == 0) {
       const uint32_t tx = A_BYTES + p.n_tile * BK * 2;
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % STAGES, ph = (kb / STAGES) & 1;
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES, ph = (i / STAGES) & 1, kb = kb0 + i;
         mbar_wait_spin(&empty[s], ph ^ 1);
         const int tap = kb / kpb, kk = kb % kpb;
         uint8_t* sa = smem + s * STAGE_BYTES;
@@ -150,7 +194,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(BM, p.n_tile);
-      for (int kb = 0; kb < nkb; ++kb) {
+      for (int kb = 0; kb < nkb; ++kb) {      // kb: local panel index
         const int s = kb % STAGES, ph = (kb / STAGES) & 1;
         mbar_wait_spin(&full[s], ph);
         tc_fence_after();
@@ -166,7 +210,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
     }
   } else if (warp >= 6) {
     // idle until the epilogue: stage the per-column epilogue vectors of this tile in shared memory
-    const GemmEpi& e = p.e;
     for (int c = threadIdx.x - 6 * 32; c < p.n_tile; c += GEMM_THREADS - 6 * 32) {
       const int n = n0 + c;
       par[PAR_BIAS * 256 + c] = e.bias ? __ldg(e.bias + (e.bias_mod > 0 ? n % e.bias_mod : n)) : 0.f;
@@ -196,53 +239,71 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
     tc_fence_before();
     if (threadIdx.x == 64) GEMM_STAMP(5);
   }
-  __syncthreads();
+  __syncwarp();                                   // warps 0 / 1: lane 0 rejoins before the aligned barrier
+  if (S > 1) cluster_sync_all(); else __syncthreads();
+  if (threadIdx.x == 64) GEMM_STAMP(8);
   // ===== epilogue, phase 2 (all 16 warps): warp <-> 8 rows, lanes across float4 column groups (lane, lane + 32),
-  // four rows in flight: bias, LayerNorm + Mish (+ time embedding), GELU / ELU, residuals, stores, next LayerNorm.
-  // Every mode test below is on a kernel parameter, hoisted out of the element loops. =====
+  // two rows per iteration of a ROLLED loop (the body is executed cold once per CTA, so instruction fetch — not
+  // issue — is what a large unrolled body costs); the residual rows of the next iteration are loaded one
+  // iteration ahead, the first pair before the barrier (behind the main loop).  Every mode test is on a kernel
+  // parameter, hoisted out of the element loops. =====
   {
-    const GemmEpi& e = p.e;
-    const bool has_ln1 = e.ln_g != nullptr, has_gelu = e.gelu != 0, has_elu = e.elu != 0;
-    const bool has_ln2 = e.out_ln != nullptr, has_snake = e.snake_alpha != nullptr;
     const float inv_n = 1.0f / (float)p.n_tile;
-    const int ngrp = p.n_tile / 4;
-    const bool g_ok[2] = {lane < ngrp, lane + 32 < ngrp};
-    const int gcol[2] = {lane * 4, g_ok[1] ? (lane + 32) * 4 : 0};
     float4 bias4[2];
 #pragma unroll
     for (int i = 0; i < 2; ++i) bias4[i] = g_ok[i] ? *reinterpret_cast<const float4*>(par + PAR_BIAS * 256 + gcol[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
-    for (int r0 = warp * 8; r0 < warp * 8 + 8; r0 += 4) {
-      float x[4][2][4];
-      bool okr[4];
-      size_t grow[4];
+    for (int it = 0; it < rpw / EPI_R; ++it) {
+      const int r0 = row_base + warp * rpw + it * EPI_R;
+      float x[EPI_R][2][4];
+      bool okr[EPI_R];
+      size_t grow[EPI_R];
+      float4 rv[EPI_R][2];
 #pragma unroll
-      for (int rr = 0; rr < 4; ++rr) {
+      for (int rr = 0; rr < EPI_R; ++rr) {
         const int t = t0 + r0 + rr;
         okr[rr] = t < p.M_out;
         grow[rr] = (size_t)b * p.M_out + (okr[rr] ? t : 0);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) rv[rr][i] = rvn[rr][i];
       }
-      // residual loads first: they overlap the LayerNorm / activation math below
-      float4 rv[4][2];
-      if (e.resid) {
+      if (has_resid && it + 1 < rpw / EPI_R) load_resid(r0 + EPI_R);
+      if (S == 1) {
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
-          for (int i = 0; i < 2; ++i)
-            rv[rr][i] = (okr[rr] && g_ok[i]) ? *reinterpret_cast<const float4*>(e.resid + grow[rr] * e.ld_resid + n0 + gcol[i])
-                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int i = 0; i < 2; ++i) {
+            const float4 v = g_ok[i] ? *reinterpret_cast<const float4*>(tile + (size_t)(r0 + rr) * pitch + gcol[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            x[rr][i][0] = v.x + bias4[i].x; x[rr][i][1] = v.y + bias4[i].y; x[rr][i][2] = v.z + bias4[i].z; x[rr][i][3] = v.w + bias4[i].w;
+          }
+      } else {
+        // partial tiles of the S cluster CTAs: all loads of a row pair issued before the first add; summed in rank
+        // order, so the result does not depend on which CTA finishes the row
+        float4 u[EPI_R][2][MAX_SPLIT];
+#pragma unroll
+        for (int rr = 0; rr < EPI_R; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const uint32_t la = smem_u32(tile + (size_t)(r0 + rr) * pitch + gcol[i]);
+#pragma unroll
+            for (int j = 0; j < MAX_SPLIT; ++j)
+              u[rr][i][j] = (g_ok[i] && j < S) ? dsmem_ld4(dsmem_addr(la, (uint32_t)j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+        for (int rr = 0; rr < EPI_R; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            float4 v = u[rr][i][0];
+#pragma unroll
+            for (int j = 1; j < MAX_SPLIT; ++j) { v.x += u[rr][i][j].x; v.y += u[rr][i][j].y; v.z += u[rr][i][j].z; v.w += u[rr][i][j].w; }
+            x[rr][i][0] = v.x + bias4[i].x; x[rr][i][1] = v.y + bias4[i].y; x[rr][i][2] = v.z + bias4[i].z; x[rr][i][3] = v.w + bias4[i].w;
+          }
       }
-#pragma unroll
-      for (int rr = 0; rr < 4; ++rr)
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const float4 v = g_ok[i] ? *reinterpret_cast<const float4*>(tile + (size_t)(r0 + rr) * pitch + gcol[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
-          x[rr][i][0] = v.x + bias4[i].x; x[rr][i][1] = v.y + bias4[i].y; x[rr][i][2] = v.z + bias4[i].z; x[rr][i][3] = v.w + bias4[i].w;
-        }
+      if (threadIdx.x == 64 && it == 0) { if (x[0][0][0] == 123.456f) GEMM_STAMP(15); GEMM_STAMP(9); }
       if (has_ln1) {
-        float s1[4], s2[4];
+        float s1[EPI_R], s2[EPI_R];
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
+        for (int rr = 0; rr < EPI_R; ++rr) {
           s1[rr] = 0.f; s2[rr] = 0.f;
 #pragma unroll
           for (int i = 0; i < 2; ++i)
@@ -252,7 +313,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-          for (int rr = 0; rr < 4; ++rr) {
+          for (int rr = 0; rr < EPI_R; ++rr) {
             s1[rr] += __shfl_xor_sync(0xffffffffu, s1[rr], o);
             s2[rr] += __shfl_xor_sync(0xffffffffu, s2[rr], o);
           }
@@ -264,7 +325,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
           const float4 te = *reinterpret_cast<const float4*>(par + PAR_TEMB * 256 + gcol[i]);
           const float gg[4] = {g.x, g.y, g.z, g.w}, bv[4] = {bb.x, bb.y, bb.z, bb.w}, tv[4] = {te.x, te.y, te.z, te.w};
 #pragma unroll
-          for (int rr = 0; rr < 4; ++rr) {
+          for (int rr = 0; rr < EPI_R; ++rr) {
             const float mean = s1[rr] * inv_n;
             const float rstd = rsqrtf(fmaxf(s2[rr] * inv_n - mean * mean, 0.f) + 1e-5f);
 #pragma unroll
@@ -274,7 +335,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       }
       if (has_gelu) {
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i)
 #pragma unroll
@@ -282,71 +343,71 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       }
       if (has_elu) {
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i)
 #pragma unroll
             for (int k = 0; k < 4; ++k) x[rr][i][k] = x[rr][i][k] > 0.f ? x[rr][i][k] : __expf(x[rr][i][k]) - 1.0f;
       }
-      if (e.resid) {
+      if (has_resid) {
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i) { x[rr][i][0] += rv[rr][i].x; x[rr][i][1] += rv[rr][i].y; x[rr][i][2] += rv[rr][i].z; x[rr][i][3] += rv[rr][i].w; }
       }
-      if (e.resid2) {
+      if (has_resid2) {
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i)
             rv[rr][i] = (okr[rr] && g_ok[i]) ? *reinterpret_cast<const float4*>(e.resid2 + grow[rr] * e.ld_resid2 + n0 + gcol[i])
                                              : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i) { x[rr][i][0] += rv[rr][i].x; x[rr][i][1] += rv[rr][i].y; x[rr][i][2] += rv[rr][i].z; x[rr][i][3] += rv[rr][i].w; }
       }
-      if (e.out_f32) {
+      if (threadIdx.x == 64 && it == 0) { if (x[0][0][0] == 123.456f) GEMM_STAMP(15); GEMM_STAMP(10); }
+      if (has_f32) {
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
+        for (int rr = 0; rr < EPI_R; ++rr)
 #pragma unroll
           for (int i = 0; i < 2; ++i) {
             if (!okr[rr] || !g_ok[i]) continue;
-            const long long off = (long long)(grow[rr] * e.ld_f32 + n0 + gcol[i]) + e.out_shift;
-            if (e.out_limit == 0 || (off >= 0 && off + 4 <= e.out_limit))
+            const long long off = (long long)(grow[rr] * e.ld_f32 + n0 + gcol[i]) + out_shift;
+            if (out_limit == 0 || (off >= 0 && off + 4 <= out_limit))
               *reinterpret_cast<float4*>(e.out_f32 + off) = make_float4(x[rr][i][0], x[rr][i][1], x[rr][i][2], x[rr][i][3]);
           }
       }
-      if (e.out_bf16) {
-        float al[2][4], ial[2][4];
-        if (has_snake) {
+      if (has_bf16) {
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 2; ++i) {
+          if (!g_ok[i]) continue;
+          float al[4] = {1.f, 1.f, 1.f, 1.f}, ial[4] = {1.f, 1.f, 1.f, 1.f};
+          if (has_snake) {
             const float4 a4 = *reinterpret_cast<const float4*>(par + PAR_ALPHA * 256 + gcol[i]);
-            al[i][0] = a4.x; al[i][1] = a4.y; al[i][2] = a4.z; al[i][3] = a4.w;
+            al[0] = a4.x; al[1] = a4.y; al[2] = a4.z; al[3] = a4.w;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) ial[i][k] = 1.0f / (al[i][k] + 1e-9f);
+            for (int k = 0; k < 4; ++k) ial[k] = 1.0f / (al[k] + 1e-9f);
           }
-        }
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr)
-#pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            if (!okr[rr] || !g_ok[i]) continue;
+          for (int rr = 0; rr < EPI_R; ++rr) {
+            if (!okr[rr]) continue;
             float y[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               y[k] = x[rr][i][k];
-              if (has_snake) { const float sn = sin_f(y[k] * al[i][k]); y[k] += ial[i][k] * sn * sn; }
-              else if (e.lrelu != 0.f) y[k] = y[k] > 0.f ? y[k] : y[k] * e.lrelu;
+              if (has_snake) { const float sn = sin_f(y[k] * al[k]); y[k] += ial[k] * sn * sn; }
+              else if (lrelu != 0.f) y[k] = y[k] > 0.f ? y[k] : y[k] * lrelu;
             }
             *reinterpret_cast<uint2*>(e.out_bf16 + grow[rr] * e.ld_bf16 + n0 + gcol[i]) = make_uint2(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]));
           }
+        }
       }
       if (has_ln2) {
-        float s1[4], s2[4];
+        float s1[EPI_R], s2[EPI_R];
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
+        for (int rr = 0; rr < EPI_R; ++rr) {
           s1[rr] = 0.f; s2[rr] = 0.f;
 #pragma unroll
           for (int i = 0; i < 2; ++i) {
@@ -358,7 +419,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-          for (int rr = 0; rr < 4; ++rr) {
+          for (int rr = 0; rr < EPI_R; ++rr) {
             s1[rr] += __shfl_xor_sync(0xffffffffu, s1[rr], o);
             s2[rr] += __shfl_xor_sync(0xffffffffu, s2[rr], o);
           }
@@ -368,7 +429,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
           const float4 g = *reinterpret_cast<const float4*>(par + PAR_G2 * 256 + gcol[i]);
           const float4 bb = *reinterpret_cast<const float4*>(par + PAR_B2 * 256 + gcol[i]);
 #pragma unroll
-          for (int rr = 0; rr < 4; ++rr) {
+          for (int rr = 0; rr < EPI_R; ++rr) {
             if (!okr[rr]) continue;
             const float mean = s1[rr] * inv_n;
             const float rstd = rsqrtf(fmaxf(s2[rr] * inv_n - mean * mean, 0.f) + 1e-5f);
@@ -381,7 +442,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
     }
   }
   if (threadIdx.x == 64) GEMM_STAMP(6);
-  __syncthreads();
+  __syncwarp();
+  if (S > 1) cluster_sync_all(); else __syncthreads();     // peers may still be reading this CTA's partial tile
   if (threadIdx.x == 0) GEMM_STAMP(7);
   if (warp == 1) {
     tc_fence_after();
@@ -406,6 +468,12 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
   CBX_CHECK(!(epi.ln_g || epi.out_ln) || n_tile == N, "gemm_make: row LayerNorm needs the whole row in one tile (N=%d)", N);
     d->B = B; d->L = L; d->N = N; d->K = K; d->taps = taps; d->n_tile = n_tile; d->epi = epi;
   d->dil = dil; d->pad = pad; d->M_out = M_out;
+  // few output tiles (the estimator's 2 x ceil(L / 128) row tiles): spread the K panels of each tile over a cluster
+  const int tiles = B * ((M_out + BM - 1) / BM) * (N / n_tile), nkb_all = taps * (K / BK);
+  d->ksplit = 1;
+  static const int max_split = [] { const char* v = getenv("CBX_GEMM_KSPLIT"); return v ? atoi(v) : 2; }();
+  for (int sp = max_split; sp >= 2; sp >>= 1)
+    if (nkb_all >= sp && tiles * sp <= 148) { d->ksplit = sp; break; }
   if (make_tmap_bf16_3d(&d->tmA, A, K, L, B, lda, (uint64_t)lda * L, BK, BM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW, W, (uint64_t)taps * K, N, 1, (uint64_t)taps * K, (uint64_t)taps * K * N, BK, n_tile)) return CBX_ERR;
   return CBX_OK;
@@ -414,24 +482,63 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
 static unsigned long long* g_gemm_dbg = nullptr;
 void gemm_set_debug(unsigned long long* buf) { g_gemm_dbg = buf; }
 
-int gemm_launch(const GemmDesc& d, cudaStream_t st) {
+namespace {
+uint32_t epi_features(const GemmEpi& e) {
+  uint32_t f = 0;
+  if (e.ln_g) f |= F_LN1;
+  if (e.gelu) f |= F_GELU;
+  if (e.elu) f |= F_ELU;
+  if (e.resid) f |= F_RESID;
+  if (e.resid2) f |= F_RESID2;
+  if (e.out_f32) f |= F_F32;
+  if (e.out_bf16) f |= F_BF16;
+  if (e.out_ln) f |= F_LN2;
+  if (e.snake_alpha || e.lrelu != 0.f) f |= F_ACT;
+  if (e.out_limit != 0 || e.out_shift != 0) f |= F_SHIFT;
+  return f;
+}
+template <uint32_t FEAT>
+int launch_as(const GemmParams& p, dim3 grid, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    CBX_CUDA(cudaFuncSetAttribute(s3_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
+    CBX_CUDA(cudaFuncSetAttribute(s3_gemm_kernel<FEAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
     attr_set = true;
   }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = GEMM_SMEM; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = grid.z;
+  cfg.attrs = at; cfg.numAttrs = grid.z > 1 ? 1 : 0;
+  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_gemm_kernel<FEAT>, p));
+  return CBX_OK;
+}
+// instantiations, narrowest first: the estimator's five epilogue shapes, then everything
+constexpr uint32_t V_PLAIN = F_BF16;                                  // q/k/v projection
+constexpr uint32_t V_GELU = F_BF16 | F_GELU;                          // feed-forward up-projection
+constexpr uint32_t V_RESLN = F_RESID | F_F32 | F_LN2 | F_BF16;        // attention out / feed-forward down (+ next LayerNorm)
+constexpr uint32_t V_LN1 = F_LN1 | F_BF16;                            // resnet block1: conv + LayerNorm + Mish + time embedding
+constexpr uint32_t V_LN1R = F_LN1 | F_RESID | F_F32 | F_LN2 | F_BF16; // resnet block2 (+ skip path, + next LayerNorm)
+}  // namespace
+
+int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   GemmParams p;
   p.tmA = d.tmA; p.tmW = d.tmW;
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;
-  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out;
+  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit;
   p.tiles_l = (d.M_out + BM - 1) / BM;
   p.e = d.epi;
   p.dbg = g_gemm_dbg;
-  if (g_gemm_dbg) g_gemm_dbg += 8;
-  dim3 grid(d.B * p.tiles_l, d.N / d.n_tile);
-  s3_gemm_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(p);
-  CBX_CUDA(cudaGetLastError());
-  return CBX_OK;
+  if (g_gemm_dbg) g_gemm_dbg += 16;
+  const dim3 grid(d.B * p.tiles_l, d.N / d.n_tile, d.ksplit);
+  const uint32_t f = epi_features(d.epi);
+  auto within = [f](uint32_t v) { return (f & ~v) == 0; };
+  if (within(V_PLAIN)) return launch_as<V_PLAIN>(p, grid, st);
+  if (within(V_GELU)) return launch_as<V_GELU>(p, grid, st);
+  if (within(V_RESLN)) return launch_as<V_RESLN>(p, grid, st);
+  if (within(V_LN1)) return launch_as<V_LN1>(p, grid, st);
+  if (within(V_LN1R)) return launch_as<V_LN1R>(p, grid, st);
+  return launch_as<F_ALL>(p, grid, st);
 }
 
 }  // namespace cbx

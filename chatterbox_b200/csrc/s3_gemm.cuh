@@ -29,6 +29,7 @@ struct GemmDesc {
   CUtensorMap tmA;     // bf16 [B][L][K] view (K innermost), box {64, 128, 1}
   CUtensorMap tmW;     // bf16 [N][taps*K], box {64, n_tile, 1}
   int B, L, N, K, taps, n_tile, dil, pad, M_out;
+  int ksplit;          // CTAs per cluster sharing one output tile, each accumulating 1/ksplit of the K panels
   GemmEpi epi;
 };
 
