@@ -4,23 +4,29 @@
 // T3HuggingfaceBackend.forward, t3/inference/t3_hf_backend.py:73-116): ~600 library launches and a
 // host sync per token become zero launches per token.  The step is HBM-bound (1.02 GB of bf16
 // weights per token at batch 2), so the design is a weight-streaming pipeline:
-//   * one CTA per SM (cooperative launch for co-residency), 8 consumer warps + 1 producer warp;
-//   * the producer walks this CTA's pre-packed, contiguous weight stream with 16 KB TMA bulk
-//     copies (cp.async.bulk -> UBLKCP) into a 9-deep shared-memory ring guarded by mbarriers.
-//     Weights do not depend on activations, so the producer never waits on the consumers' data
-//     dependencies: HBM keeps streaming while dependent phases hand activations over;
-//   * consumers multiply each 8-row x 1024-k unit against the (<= 8) activation rows with
-//     mma.sync m16n8k16 (weights are the B operand; activations are split x = hi + lo in bf16 and
-//     occupy A rows 0-7 / 8-15, so products carry ~16 mantissa bits and accumulate in fp32);
-//   * dependent phases (qkv -> attention -> combine -> o_proj -> gate/up -> down) hand their
-//     activations over through "LL" buffers in L2: every fp32 value travels in one 8-byte word
-//     together with a sequence flag ({value, flag}, one atomic 64-bit store), so a consumer polls
-//     the data itself and there is NO grid barrier and NO fence on the critical path;
-//   * residual adds, RMSNorm, RoPE, SwiGLU, the split-KV combine, CFG, logit processing, sampling,
-//     EOS and the next-token embedding are fused into the phase prologues/epilogues; the residual
-//     stream lives in registers (replicated per CTA), so nothing but weights and the KV slab
-//     touches HBM.
-// The same kernel runs chunked prefill (4 positions x 2 CFG rows per weight pass).
+//   * one CTA per SM (cooperative launch for co-residency), 8 warps = 2 per scheduler, so every
+//     thread may use up to 255 registers (a 9th, dedicated producer warp would cap them at 168);
+//   * this CTA's pre-packed, contiguous weight stream arrives in 32 KB TMA bulk copies
+//     (cp.async.bulk -> UBLKCP) through a 5-deep shared-memory ring: the warp that releases a
+//     slot last re-arms it with the copy of the unit 5 ahead.  Weights do not depend on
+//     activations, so HBM keeps streaming while dependent phases hand activations over;
+//   * consumers multiply each 16-row x 1024-k unit against the CFG pair of activation rows with
+//     mma.sync m16n8k16: the WEIGHTS are the A operand (16 rows per instruction, pre-packed in
+//     fragment order so one 128-bit shared load feeds one MMA), the activations the B operand
+//     with columns {row0 hi, row0 lo, row1 hi, row1 lo}: x = hi + lo in bf16, so products carry
+//     ~16 mantissa bits and accumulate in fp32.  The 8 warps split K; partials meet in smem;
+//   * dependent phases (qkv -> attention -> o_proj -> gate/up -> down) hand their activations
+//     over through "LL" buffers in L2: every fp32 value travels in one 8-byte word together with
+//     a sequence flag ({value, flag}, one atomic 64-bit store), so a consumer polls the data
+//     itself and there is NO grid barrier and NO fence on the critical path;
+//   * a lane owns 8 consecutive k of one activation row; residual adds, the RMSNorm gain, the
+//     hi/lo split and the split-KV combine happen in those registers.  The RMSNorm scale is a per-
+//     row scalar, so it is applied to the OUTPUTS in the phase epilogue: the MMAs start without
+//     waiting for the sum of squares;
+//   * RoPE, SwiGLU, CFG, logit processing, sampling, EOS and the next-token embedding are fused
+//     into the phase prologues/epilogues; the residual stream lives in registers (replicated per
+//     CTA), so nothing but weights and the KV slab touches HBM.
+// Prefill runs the same kernel one position per weight pass (mode 0).
 #include "common.cuh"
 #include "t3_plan.h"
 #include "../../include/cbx.h"
@@ -31,40 +37,39 @@
 
 namespace {
 
-constexpr int NSLOT = 9;                  // ring depth (16 KB units)
+constexpr int NSLOT = 5;                  // ring depth (32 KB units)
 constexpr int NCONS_WARPS = 8;
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
-constexpr int NTHREADS = NCONS + 32;      // + producer warp
+constexpr int NTHREADS = NCONS;
 constexpr int MAXS = 4;                   // max KV splits per (row, head) pair
 constexpr int PART_STRIDE = 68;           // 64 o + m + l (+2 pad)
 constexpr int STOP_SPEECH = 6562;
-constexpr int VOCAB_PAD = 8200;
-constexpr int MAXROWS = 2 * T3_MAX_NPOS;  // activation rows per weight pass: (position, CFG row)
-constexpr int STAGE_LD = 132;             // padded row stride of the per-warp staging tile (floats)
+constexpr int VOCAB_PAD = T3_VOCAB_PAD;
 constexpr float RMS_EPS = 1e-5f;
 
 constexpr int SMEM_RING = NSLOT * T3_UNIT_BYTES;
 constexpr int SMEM_BARS = SMEM_RING;            // 2*NSLOT mbarriers
 constexpr int SMEM_CTL = SMEM_BARS + 256;       // control words
-constexpr int SMEM_SCRATCH = SMEM_CTL + 256;    // phase scratch (union)
+constexpr int SMEM_RED = SMEM_CTL + 256;        // [2 phase parities][MAXU][8 warps][32] k-slice partials
+constexpr int RED_FLOATS = T3_MAXU * NCONS_WARPS * 32;
+constexpr int SMEM_SSQ = SMEM_RED + 2 * RED_FLOATS * 4;      // [2][8 warps][2 rows] partial sums of squares
+constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [8 warps][2 rows][128] activation slices (fragment build)
+constexpr int SMEM_SCRATCH = SMEM_XT + NCONS_WARPS * 2 * 128 * 4;   // attention scratch / sampling logits (union)
 constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
-constexpr int SMEM_STAGE = SMEM_SCRATCH + SCRATCH_BYTES;              // [8 warps][MAXROWS][STAGE_LD] floats
-constexpr int STAGE_BYTES = NCONS_WARPS * MAXROWS * STAGE_LD * 4;
-constexpr int SMEM_SEEN = SMEM_STAGE + STAGE_BYTES;                   // generated-id set (CTA 0)
-constexpr int SMEM_LN = SMEM_SEEN + 8208;                              // [2][1024] floats: prefetched norm gains
-constexpr int SMEM_TOTAL = SMEM_LN + 2 * T3_H * 4;
+constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0)
+constexpr int SMEM_TOTAL = SMEM_SEEN + VOCAB_PAD;
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
+static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
 
 // LL exchange buffers (elements are {fp32 bits, flag} 8-byte words), offsets in words
-enum { LLP_QKV = 0, LLP_PART = 1, LLP_ATTN = 2, LLP_OPROJ = 3, LLP_ACT = 4, LLP_DOWN = 5, LLP_LOGITS = 6, LLP_EMB = 7 };
-constexpr size_t LL_QKV = 0;
-constexpr size_t LL_PART = LL_QKV + (size_t)MAXROWS * 3072;
-constexpr size_t LL_ATTN = LL_PART + (size_t)T3_MAX_NPOS * 32 * MAXS * PART_STRIDE;
-constexpr size_t LL_OPROJ = LL_ATTN + (size_t)MAXROWS * T3_H;
-constexpr size_t LL_ACT = LL_OPROJ + (size_t)MAXROWS * T3_H;
-constexpr size_t LL_DOWN = LL_ACT + (size_t)MAXROWS * T3_INTER;
-constexpr size_t LL_LOGITS = LL_DOWN + (size_t)T3_DOWN_KS * MAXROWS * T3_H;
-constexpr size_t LL_EMB = LL_LOGITS + (size_t)2 * VOCAB_PAD;
+enum { LLP_QKV = 0, LLP_PART = 1, LLP_OPROJ = 3, LLP_ACT = 4, LLP_DOWN = 5, LLP_LOGITS = 6, LLP_EMB = 7 };
+constexpr size_t LL_QKV = 0;                                          // [2][3072]
+constexpr size_t LL_PART = LL_QKV + (size_t)2 * 3072;                 // [32 pairs][MAXS][PART_STRIDE]
+constexpr size_t LL_OPROJ = LL_PART + (size_t)32 * MAXS * PART_STRIDE;   // [2][1024]
+constexpr size_t LL_ACT = LL_OPROJ + (size_t)2 * T3_H;                // [2][4096]
+constexpr size_t LL_DOWN = LL_ACT + (size_t)2 * T3_INTER;             // [4 k-slices][2][1024]
+constexpr size_t LL_LOGITS = LL_DOWN + (size_t)T3_DOWN_KS * 2 * T3_H; // [2][VOCAB_PAD]
+constexpr size_t LL_EMB = LL_LOGITS + (size_t)2 * VOCAB_PAD;          // [1024] + control word
 constexpr size_t LL_WORDS = LL_EMB + T3_H + 8;
 
 struct T3State {   // lives in global memory, persists between launches of one utterance
@@ -91,10 +96,14 @@ struct T3Params {
 
 struct Ctl {            // CTA-local control block in shared memory
   volatile int abort;   // set after a watchdog timeout: every later wait returns at once
-  volatile int cons_done;
-  volatile int cons_k;
-  volatile int tok;
+  int released[NSLOT];  // warps that have finished reading the slot's current unit
+  // cursor of the weight stream (next unit to copy): touched only by the one thread re-arming a slot
+  int next_idx;         // unit index inside the per-CTA stream
+  int next_iter;        // iteration that unit belongs to
+  int plan_n[PH_COUNT];            // units of each phase on this CTA
+  int plan_u[PH_COUNT][T3_MAXU];   // their unit ids
 };
+static_assert(sizeof(Ctl) <= 256, "control block");
 
 using namespace cbx;
 
@@ -107,9 +116,9 @@ constexpr unsigned long long WATCHDOG_NS = 4000000000ull;
 
 __device__ __forceinline__ void cbar() { asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory"); }
 
-// Wait on an mbarrier phase with a watchdog; returns false if aborted.
-__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, Ctl* ctl, T3State* st) {
-  if (mbar_try_wait(bar, parity)) return true;
+// Wait on an mbarrier phase with a watchdog; returns false if aborted.  The slow path stays out of line: the
+// layer loop has to stay resident in the instruction cache.
+__device__ __noinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parity, Ctl* ctl, T3State* st) {
   unsigned long long t0 = gtime_ns();
   unsigned spins = 0;
   while (!mbar_try_wait(bar, parity)) {
@@ -121,6 +130,10 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, Ctl* c
     }
   }
   return true;
+}
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, Ctl* ctl, T3State* st) {
+  if (mbar_try_wait(bar, parity)) return true;
+  return mbar_wait_slow(bar, parity, ctl, st);
 }
 
 // ---- LL words: {value, flag} in one 64-bit relaxed store / load --------------------------------
@@ -139,20 +152,28 @@ __device__ __forceinline__ unsigned long long ll_ld1(const unsigned long long* p
 __device__ __forceinline__ void ll_ld2(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
   asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
 }
+// same with a compile-time byte offset folded into the address operand: polling many words off one base costs
+// one pointer register pair, not one per word
+template <int OFF>
+__device__ __forceinline__ void ll_ld2_off(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2+%3];" : "=l"(a), "=l"(b) : "l"(p), "n"(OFF) : "memory");
+}
 __device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned flag) { return (unsigned)(w >> 32) == flag; }
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)w); }
 
 // watchdog bookkeeping of a poll loop; returns true when the caller must give up
+__device__ __noinline__ bool poll_timeout_slow(unsigned long long& t0, Ctl* ctl, T3State* st) {
+  if (t0 == 0) t0 = gtime_ns();
+  else if (gtime_ns() - t0 > WATCHDOG_NS || __ldcg(&st->err)) {
+    ctl->abort = 1;
+    atomicExch(&st->err, 1);
+    return true;
+  }
+  return false;
+}
 __device__ __forceinline__ bool poll_timeout(unsigned& spins, unsigned long long& t0, Ctl* ctl, T3State* st) {
   if (ctl->abort) return true;
-  if ((++spins & 255u) == 0) {
-    if (t0 == 0) t0 = gtime_ns();
-    else if (gtime_ns() - t0 > WATCHDOG_NS || __ldcg(&st->err)) {
-      ctl->abort = 1;
-      atomicExch(&st->err, 1);
-      return true;
-    }
-  }
+  if ((++spins & 255u) == 0) return poll_timeout_slow(t0, ctl, st);
   return false;
 }
 
@@ -172,184 +193,164 @@ __device__ __forceinline__ void ll_poll(const unsigned long long* (&ptr)[N], int
   }
 }
 
-struct Piece { const unsigned long long* ptr; size_t row_stride; unsigned flag; };   // row_stride in words
+// ---- activation slices ---------------------------------------------------------------------------
+// Warp w owns k in [128w, 128w + 128) of the two activation rows (CFG cond / uncond); lane owns row
+// lane >> 4 and the 8 consecutive k at 128w + (lane & 15) * 8.
 
-// Warp-cooperative load of this warp's 128-wide k slice of R activation rows from NP LL pieces
-// (summed) into the warp's staging tile stage[row][STAGE_LD].  Row r = (position r>>1, CFG row r&1)
-// is loaded only if r < nrows and (r&1) < B.  All lanes issue 2*R/PAR... loads per round and poll
-// them together, so one exchange costs about one L2 round trip.
-template <int R, int PAR>
-__device__ __forceinline__ void ll_stage(float* stage, const Piece* pc, int np, int kbase, int nrows, int B, int lane,
-                                         Ctl* ctl, T3State* st) {
-  constexpr int T = 2 * R;      // v2 loads per lane per piece: R rows * 64 v2 / 32 lanes
-  float acc[T][2];
-#pragma unroll
-  for (int t = 0; t < T; ++t) acc[t][0] = acc[t][1] = 0.f;
-  for (int p0 = 0; p0 < np; p0 += PAR) {
-    unsigned long long wa[PAR][T], wb[PAR][T];
+// x[e] = sum over np (<= 4) pieces, `stride` words apart, of the 8 LL words at base (fixed order -> deterministic
+// sum).  One instance serves every phase: all loads of a round are in flight together.
+__device__ __forceinline__ void ll_load8(float (&x)[8], const unsigned long long* base, size_t stride, int np, unsigned flag,
+                                         bool active, Ctl* ctl, T3State* st) {
+  unsigned long long w[4][8];
+  if (active) {
     unsigned spins = 0; unsigned long long t0 = 0;
     for (;;) {
       bool ok = true;
 #pragma unroll
-      for (int q = 0; q < PAR; ++q) {
-        if (p0 + q < np) {
-#pragma unroll
-          for (int t = 0; t < T; ++t) {
-            const int i = lane + 32 * t, row = i >> 6, c2 = i & 63;
-            if (row < nrows && (row & 1) < B)
-              ll_ld2(pc[p0 + q].ptr + (size_t)row * pc[p0 + q].row_stride + kbase + 2 * c2, wa[q][t], wb[q][t]);
-          }
+      for (int q = 0; q < 4; ++q) {
+        if (q < np) {
+          const unsigned long long* pq = base + q * stride;
+          ll_ld2_off<0>(pq, w[q][0], w[q][1]);
+          ll_ld2_off<16>(pq, w[q][2], w[q][3]);
+          ll_ld2_off<32>(pq, w[q][4], w[q][5]);
+          ll_ld2_off<48>(pq, w[q][6], w[q][7]);
         }
       }
 #pragma unroll
-      for (int q = 0; q < PAR; ++q) {
-        if (p0 + q < np) {
+      for (int q = 0; q < 4; ++q)
+        if (q < np) {
 #pragma unroll
-          for (int t = 0; t < T; ++t) {
-            const int row = (lane + 32 * t) >> 6;
-            if (row < nrows && (row & 1) < B)
-              ok = ok && ll_ok(wa[q][t], pc[p0 + q].flag) && ll_ok(wb[q][t], pc[p0 + q].flag);
-          }
+          for (int e = 0; e < 8; ++e) ok = ok && ll_ok(w[q][e], flag);
         }
-      }
       if (ok) break;
       if (poll_timeout(spins, t0, ctl, st)) break;
     }
+  }
 #pragma unroll
-    for (int q = 0; q < PAR; ++q) {
-      if (p0 + q < np) {
+  for (int e = 0; e < 8; ++e) {
+    float sum = 0.f;
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-          const int row = (lane + 32 * t) >> 6;
-          if (row < nrows && (row & 1) < B) { acc[t][0] += ll_val(wa[q][t]); acc[t][1] += ll_val(wb[q][t]); }
-        }
-      }
+    for (int q = 0; q < 4; ++q) sum += (active && q < np) ? ll_val(w[q][e]) : 0.f;
+    x[e] = sum;
+  }
+}
+
+// B fragments of the warp's k-slice: Bf[s][0..1] for k16 step s.  Column n = lane >> 2 of the MMA is
+// {row0 hi, row0 lo, row1 hi, row1 lo, 0, 0, 0, 0}; the slice goes through a 1 KB per-warp tile.
+__device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[8][2], const float (&x)[8], float* xt, int lane) {
+  __syncwarp();     // previous readers of the tile are done
+  *reinterpret_cast<float4*>(xt + lane * 8) = make_float4(x[0], x[1], x[2], x[3]);
+  *reinterpret_cast<float4*>(xt + lane * 8 + 4) = make_float4(x[4], x[5], x[6], x[7]);
+  __syncwarp();
+  const int g = lane >> 2, tig = lane & 3;
+#pragma unroll
+  for (int s = 0; s < 8; ++s) { Bf[s][0] = 0u; Bf[s][1] = 0u; }
+  if (g < 4) {
+    const float* src = xt + (g >> 1) * 128 + 2 * tig;
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      const float2 v0 = *reinterpret_cast<const float2*>(src + 16 * s);
+      const float2 v1 = *reinterpret_cast<const float2*>(src + 16 * s + 8);
+      uint32_t h0, l0, h1, l1;
+      split_hi_lo(v0.x, v0.y, h0, l0);
+      split_hi_lo(v1.x, v1.y, h1, l1);
+      Bf[s][0] = (g & 1) ? l0 : h0;
+      Bf[s][1] = (g & 1) ? l1 : h1;
     }
   }
-#pragma unroll
-  for (int t = 0; t < T; ++t) {
-    const int i = lane + 32 * t, row = i >> 6, c2 = i & 63;
-    *reinterpret_cast<float2*>(stage + row * STAGE_LD + 2 * c2) = make_float2(acc[t][0], acc[t][1]);
-  }
-  __syncwarp();
 }
 
-// thread (g = lane>>2, tig = lane&3) reads its fragment values: row g, k = jj*32 + tig*8 + e of the warp slice
-__device__ __forceinline__ void stage_read(float (&xs)[4][8], const float* stage, int g, int tig) {
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj) {
-    const float4 a = *reinterpret_cast<const float4*>(stage + g * STAGE_LD + jj * 32 + tig * 8);
-    const float4 b = *reinterpret_cast<const float4*>(stage + g * STAGE_LD + jj * 32 + tig * 8 + 4);
-    xs[jj][0] = a.x; xs[jj][1] = a.y; xs[jj][2] = a.z; xs[jj][3] = a.w;
-    xs[jj][4] = b.x; xs[jj][5] = b.y; xs[jj][6] = b.z; xs[jj][7] = b.w;
-  }
-  __syncwarp();
-}
-
-// ---- activation rows -> A fragments -------------------------------------------------------------
-// Lane (g = lane>>2, tig = lane&3) owns activation row g = (pos pp = g>>1, CFG row bb = g&1) and, for
-// each of the warp's four k32-blocks jj, the 8 consecutive k at warp*128 + jj*32 + tig*8.
-__device__ __forceinline__ void make_frags(uint32_t (&A)[4][8], const float (&xs)[4][8]) {
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj) {
-    split_hi_lo(xs[jj][0], xs[jj][1], A[jj][0], A[jj][1]);   // step 0: a0 (hi), a1 (lo)  k = 2tig,2tig+1
-    split_hi_lo(xs[jj][2], xs[jj][3], A[jj][2], A[jj][3]);   //         a2 (hi), a3 (lo)  k = 2tig+8,+9
-    split_hi_lo(xs[jj][4], xs[jj][5], A[jj][4], A[jj][5]);   // step 1
-    split_hi_lo(xs[jj][6], xs[jj][7], A[jj][6], A[jj][7]);
-  }
-}
-
-// Norm gains travel through a double-buffered shared-memory prefetch (cp.async issued one phase
-// ahead), so the RMSNorm never waits on L2/HBM for them.
-__device__ __forceinline__ void ln_prefetch(float* lnbuf, int qq, const float* __restrict__ lnw, int tid) {
-  const uint32_t dst = smem_u32(lnbuf + (qq & 1) * T3_H + tid * 4);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(lnw + tid * 4) : "memory");
-  asm volatile("cp.async.commit_group;" ::: "memory");
-}
-
-// RMSNorm over the full 1024-wide row (reference: HF LlamaRMSNorm, eps 1e-5): the row is spread
-// over the 4 tig lanes of 8 warps; partial sums of squares meet in shared memory.  out = w * (x * rsqrt)
-__device__ __forceinline__ void rmsnorm_rows(float (&out)[4][8], const float (&xs)[4][8], const float* lnbuf, int qq,
-                                             int kw, float* ssq, int warp, int lane, unsigned long long* dbg = nullptr) {
-  if (dbg) dbg[0] = gtime_ns();
+// sum of squares of the lane's 8 values, reduced over the 16 lanes of the row; lane & 15 == 0 stores it
+__device__ __forceinline__ void ssq_partial(const float (&x)[8], float* ssq, int warp, int lane) {
   float s = 0.f;
 #pragma unroll
-  for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-    for (int e = 0; e < 8; ++e) s += xs[jj][e] * xs[jj][e];
+  for (int e = 0; e < 8; ++e) s += x[e] * x[e];
   s += __shfl_xor_sync(0xffffffffu, s, 1);
   s += __shfl_xor_sync(0xffffffffu, s, 2);
-  const int g = lane >> 2;
-  if ((lane & 3) == 0) ssq[warp * 8 + g] = s;
-  if (dbg) dbg[1] = gtime_ns();
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  if (dbg) dbg[2] = gtime_ns();
-  cbar();
-  if (dbg) dbg[3] = gtime_ns();
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 8);
+  if ((lane & 15) == 0) ssq[warp * 2 + (lane >> 4)] = s;
+}
+__device__ __forceinline__ float rms_scale(const float* ssq, int b) {
   float tot = 0.f;
 #pragma unroll
-  for (int w = 0; w < NCONS_WARPS; ++w) tot += ssq[w * 8 + g];
-  const float scale = 1.0f / sqrtf(tot * (1.0f / T3_H) + RMS_EPS);
-  const float* lw = lnbuf + (qq & 1) * T3_H + kw;
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj) {
-    const float4 a = *reinterpret_cast<const float4*>(lw + jj * 32);
-    const float4 b = *reinterpret_cast<const float4*>(lw + jj * 32 + 4);
-    out[jj][0] = a.x * (xs[jj][0] * scale); out[jj][1] = a.y * (xs[jj][1] * scale);
-    out[jj][2] = a.z * (xs[jj][2] * scale); out[jj][3] = a.w * (xs[jj][3] * scale);
-    out[jj][4] = b.x * (xs[jj][4] * scale); out[jj][5] = b.y * (xs[jj][5] * scale);
-    out[jj][6] = b.z * (xs[jj][6] * scale); out[jj][7] = b.w * (xs[jj][7] * scale);
-  }
-  if (dbg) dbg[4] = gtime_ns();
+  for (int w = 0; w < NCONS_WARPS; ++w) tot += ssq[w * 2 + b];
+  return rsqrtf(tot * (1.0f / T3_H) + RMS_EPS);
+}
+// 8 norm gains of this lane's k range, fetched one phase ahead into registers
+__device__ __forceinline__ void ln_fetch(float (&g)[8], const float* __restrict__ lnw, int k) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(lnw + k));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(lnw + k + 4));
+  g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
 }
 
-// ---- consume n weight units from the ring: red[j][warp][64] = this warp's k-slice partial of unit j
-struct RingPos { int slot; uint32_t parity; int k; unsigned long long wait_ns, mma_ns; };
+// The weight stream of one CTA: every iteration walks the L layers' units, iterations >= head_from_iter walk the
+// head units after them.  Units are copied in stream order; the cursor lives in the control block.
+struct Stream {
+  const uint8_t* base; uint64_t policy;
+  int per_iter_layers;      // L * units per layer
+  int nhead;
+  int head_from_iter;       // iterations >= this one include the head units
+  int n_iters;
+};
+// copy the next unit of the stream into `slot` (one thread); no-op past the end of the stream
+__device__ __forceinline__ void stream_issue_next(const Stream& sm, Ctl* ctl, int slot, uint8_t* ring, uint64_t* full) {
+  const int it = ctl->next_iter;
+  if (it >= sm.n_iters) return;
+  const int idx = ctl->next_idx;
+  mbar_arrive_expect_tx(&full[slot], T3_UNIT_BYTES);
+  tma_bulk_g2s(ring + slot * T3_UNIT_BYTES, sm.base + (size_t)idx * T3_UNIT_BYTES, T3_UNIT_BYTES, &full[slot], sm.policy);
+  const int end = sm.per_iter_layers + (it >= sm.head_from_iter ? sm.nhead : 0);
+  if (idx + 1 == end) { ctl->next_idx = 0; ctl->next_iter = it + 1; }
+  else ctl->next_idx = idx + 1;
+}
 
-__device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t (&A)[4][8], float* red,
-                                              const uint8_t* ring, uint64_t* full, uint64_t* empty, int warp, int lane,
-                                              Ctl* ctl, T3State* st) {
-  float2 prev = make_float2(0.f, 0.f);
+// ---- consume n weight units from the ring: red[j][warp][32] = this warp's k-slice partial of unit j,
+// index = row * 16 + weight row of the unit
+struct RingPos { int slot; uint32_t parity; long long k; };
+
+__device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t (&Bf)[8][2], float* red, uint8_t* ring,
+                                              uint64_t* full, const Stream& sm, int warp, int lane, Ctl* ctl, T3State* st) {
+  const int g = lane >> 2, tig = lane & 3;
+#pragma unroll 1
   for (int j = 0; j < n; ++j) {
-#ifdef T3_DEBUG_WAIT
-    const unsigned long long tw0 = gtime_ns();
-#endif
     mbar_wait(&full[rp.slot], rp.parity, ctl, st);
-#ifdef T3_DEBUG_WAIT
-    const unsigned long long tw1 = gtime_ns();
-    rp.wait_ns += tw1 - tw0;
-#endif
-    const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * 128 + lane;
-    uint4 w[4];
+    const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * 256 + lane;
+    uint4 w[8];
 #pragma unroll
-    for (int jj = 0; jj < 4; ++jj) w[jj] = wp[jj * 32];
-    // the previous unit's result is stored only now, so its MMA chain overlaps this unit's loads
-    if (j > 0) reinterpret_cast<float2*>(red + ((j - 1) * NCONS_WARPS + warp) * 64)[lane] = prev;
-    float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f};   // two independent accumulator chains
-    mma_bf16_16816(c0, A[0][0], A[0][1], A[0][2], A[0][3], w[0].x, w[0].y);
-    mma_bf16_16816(c1, A[0][4], A[0][5], A[0][6], A[0][7], w[0].z, w[0].w);
-    mma_bf16_16816(c0, A[1][0], A[1][1], A[1][2], A[1][3], w[1].x, w[1].y);
-    mma_bf16_16816(c1, A[1][4], A[1][5], A[1][6], A[1][7], w[1].z, w[1].w);
-    mma_bf16_16816(c0, A[2][0], A[2][1], A[2][2], A[2][3], w[2].x, w[2].y);
-    mma_bf16_16816(c1, A[2][4], A[2][5], A[2][6], A[2][7], w[2].z, w[2].w);
-    mma_bf16_16816(c0, A[3][0], A[3][1], A[3][2], A[3][3], w[3].x, w[3].y);
-    mma_bf16_16816(c1, A[3][4], A[3][5], A[3][6], A[3][7], w[3].z, w[3].w);
+    for (int s = 0; s < 8; ++s) w[s] = wp[s * 32];
+    float c[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { c[q][0] = 0.f; c[q][1] = 0.f; c[q][2] = 0.f; c[q][3] = 0.f; }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) mma_bf16_16816(c[s & 3], w[s].x, w[s].y, w[s].z, w[s].w, Bf[s][0], Bf[s][1]);
     __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[rp.slot]);
-    prev = make_float2((c0[0] + c0[2]) + (c1[0] + c1[2]), (c0[1] + c0[3]) + (c1[1] + c1[3]));
+    if (lane == 0) {
+      // release the slot; the warp that releases it last re-arms it with the unit NSLOT ahead
+      if (atomicAdd(&ctl->released[rp.slot], 1) == NCONS_WARPS - 1) {
+        ctl->released[rp.slot] = 0;
+        __threadfence_block();
+        if (!ctl->abort) {
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          stream_issue_next(sm, ctl, rp.slot, ring, full);
+        }
+        __threadfence_block();
+      }
+    }
+    if (tig < 2) {   // columns 2 tig, 2 tig + 1 = hi and lo of activation row tig
+      float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g;
+      dst[0] = ((c[0][0] + c[0][1]) + (c[1][0] + c[1][1])) + ((c[2][0] + c[2][1]) + (c[3][0] + c[3][1]));
+      dst[8] = ((c[0][2] + c[0][3]) + (c[1][2] + c[1][3])) + ((c[2][2] + c[2][3]) + (c[3][2] + c[3][3]));
+    }
     if (++rp.slot == NSLOT) { rp.slot = 0; rp.parity ^= 1u; }
     ++rp.k;
-#ifdef T3_DEBUG_WAIT
-    rp.mma_ns += gtime_ns() - tw1;
-#endif
   }
-  if (n > 0) reinterpret_cast<float2*>(red + ((n - 1) * NCONS_WARPS + warp) * 64)[lane] = prev;
 }
 
 __device__ __forceinline__ float red_sum(const float* red, int j, int o) {
   float s = 0.f;
 #pragma unroll
-  for (int w = 0; w < NCONS_WARPS; ++w) s += red[(j * NCONS_WARPS + w) * 64 + o];
+  for (int w = 0; w < NCONS_WARPS; ++w) s += red[(j * NCONS_WARPS + w) * 32 + o];
   return s;
 }
 
@@ -405,55 +406,57 @@ __device__ __forceinline__ void osm_merge_xor(Osm& s, int mask) {
   s.m = mn;
 }
 
-// ---- phase B: RoPE + KV append + split-KV attention over the slab + split combine ---------------
+__device__ __forceinline__ int attn_splits(int G, int B) {
+  int S = G / (B * T3_NH);
+  return S > MAXS ? MAXS : S;
+}
+
+// ---- phase B: RoPE + KV append + split-KV attention over the slab -------------------------------
 // (reference: HF LlamaAttention eager path: softmax(q k^T / 8 + causal) v in fp32; rotate_half RoPE)
 // CTA c < S*npairs handles pair = c % npairs (CFG row b, head) and KV split c / npairs; it publishes
-// {sum_i exp(s_i - m) v_i, m, l} through the LL part buffer, and the split-0 CTA of each pair merges
-// the S partials into the attention output row segment (LL attn buffer).
-template <typename KVT, int NPOS>
-__device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, int pos0, int npos, float* scr, int warp,
-                                        int lane, Ctl* ctl) {
+// {sum_i exp(s_i - m) v_i, m, l} through the LL part buffer.  The S partials of a pair are merged by
+// their consumers (the o_proj prologue), so there is no separate combine hop.
+template <typename KVT>
+__device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, int pos0, float* scr, int warp, int lane,
+                                        Ctl* ctl) {
   const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x, L = p.n_layers;
   const int npairs = p.B * T3_NH;
-  int S = G / npairs; if (S > MAXS) S = MAXS;
+  const int S = attn_splits(G, p.B);
   if (c >= S * npairs) return;
   const int pair = c % npairs, split = c / npairs, b = pair / T3_NH, head = pair % T3_NH;
-  float* q_s = scr;                       // [4][64] (pre-scaled by 1/8)
-  float* k_new = scr + 256;               // [4][64]
-  float* v_new = scr + 512;               // [4][64]
-  float* wpart = scr + 768;               // [8 warps][4][PART_STRIDE]
+  float* q_s = scr;                       // [64] (pre-scaled by 1/8)
+  float* k_new = scr + 64;                // [64]
+  float* v_new = scr + 128;               // [64]
+  float* wpart = scr + 192;               // [8 warps][PART_STRIDE]
   KVT* kc = reinterpret_cast<KVT*>(p.kcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
   KVT* vc = reinterpret_cast<KVT*>(p.vcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
 
   float kr = 0.f, vr = 0.f;
-  if (tid < npos * 64) {
-    const int pp = tid >> 6, d = tid & 63;
-    const unsigned long long* row = p.ll + LL_QKV + (size_t)(pp * 2 + b) * 3072 + head * 64;
+  if (tid < 64) {
+    const int d = tid;
+    const unsigned long long* row = p.ll + LL_QKV + (size_t)b * 3072 + head * 64;
     const unsigned long long* ptr[5] = {row + d, row + (d ^ 32), row + 1024 + d, row + 1024 + (d ^ 32),
                                               row + 2048 + d};
     unsigned long long w[5];
     ll_poll<5>(ptr, 5, ll_flag(it, L, layer, LLP_QKV), w, ctl, p.st);
-    const float cs = __ldg(p.rope_cos + (size_t)(pos0 + pp) * 32 + (d & 31));
-    const float sn = __ldg(p.rope_sin + (size_t)(pos0 + pp) * 32 + (d & 31));
+    const float cs = __ldg(p.rope_cos + (size_t)pos0 * 32 + (d & 31));
+    const float sn = __ldg(p.rope_sin + (size_t)pos0 * 32 + (d & 31));
     const float q = ll_val(w[0]), qo = ll_val(w[1]), k = ll_val(w[2]), ko = ll_val(w[3]), v = ll_val(w[4]);
     const float qr = q * cs + (d < 32 ? -qo : qo) * sn;
     kr = KV<KVT>::round(k * cs + (d < 32 ? -ko : ko) * sn);
     vr = KV<KVT>::round(v);
-    q_s[pp * 64 + d] = qr * 0.125f;
-    k_new[pp * 64 + d] = kr;
-    v_new[pp * 64 + d] = vr;
+    q_s[d] = qr * 0.125f;
+    k_new[d] = kr;
+    v_new[d] = vr;
   }
   cbar();
 
   const int lg = lane >> 3, sub = lane & 7;
-  float qv[NPOS][8];
-  Osm st[NPOS];
+  float qv[8];
+  Osm st;
+  osm_init(st);
 #pragma unroll
-  for (int pp = 0; pp < NPOS; ++pp) {
-    osm_init(st[pp]);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) qv[pp][e] = (pp < npos) ? q_s[pp * 64 + sub * 8 + e] : 0.f;
-  }
+  for (int e = 0; e < 8; ++e) qv[e] = q_s[sub * 8 + e];
   const int chunk = (pos0 + S - 1) / S;
   const int lo = split * chunk;
   const int hi = min(pos0, lo + chunk);
@@ -468,109 +471,122 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
 #pragma unroll
       for (int e = 0; e < 8; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
     }
+    float s = 0.f;
 #pragma unroll
-    for (int pp = 0; pp < NPOS; ++pp) {
-      if (pp < npos) {
-        float s = 0.f;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) s += qv[pp][e] * kf[e];
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        if (valid) osm_update(st[pp], s, vf);
-      }
-    }
+    for (int e = 0; e < 8; ++e) s += qv[e] * kf[e];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (valid) osm_update(st, s, vf);
   }
-  // keys of this chunk of positions itself (causal inside the chunk): last split, warp 0, lane group = key
+  // the key of this position itself: last split, warp 0, lane group 0
   if (split == S - 1 && warp == 0) {
-    const bool valid = lg < npos;
     float kf[8], vf[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      kf[e] = valid ? k_new[lg * 64 + sub * 8 + e] : 0.f;
-      vf[e] = valid ? v_new[lg * 64 + sub * 8 + e] : 0.f;
-    }
+    for (int e = 0; e < 8; ++e) { kf[e] = k_new[sub * 8 + e]; vf[e] = v_new[sub * 8 + e]; }
+    float s = 0.f;
 #pragma unroll
-    for (int pp = 0; pp < NPOS; ++pp) {
-      if (pp < npos) {
-        float s = 0.f;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) s += qv[pp][e] * kf[e];
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        if (valid && lg <= pp) osm_update(st[pp], s, vf);
-      }
-    }
+    for (int e = 0; e < 8; ++e) s += qv[e] * kf[e];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (lg == 0) osm_update(st, s, vf);
   }
   // merge the 4 lane groups, then the 8 warps
+  osm_merge_xor(st, 8);
+  osm_merge_xor(st, 16);
+  if (lg == 0) {
+    float* w = wpart + warp * PART_STRIDE;
 #pragma unroll
-  for (int pp = 0; pp < NPOS; ++pp) {
-    if (pp < npos) {
-      osm_merge_xor(st[pp], 8);
-      osm_merge_xor(st[pp], 16);
-      if (lg == 0) {
-        float* w = wpart + (warp * T3_MAX_NPOS + pp) * PART_STRIDE;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) w[sub * 8 + e] = st[pp].o[e];
-        if (sub == 0) { w[64] = st[pp].m; w[65] = st[pp].l; }
-      }
-    }
+    for (int e = 0; e < 8; ++e) w[sub * 8 + e] = st.o[e];
+    if (sub == 0) { w[64] = st.m; w[65] = st.l; }
   }
   cbar();
-  if (tid < npos * 64) {
-    const int pp = tid >> 6, d = tid & 63;
+  if (tid < 64) {
+    const int d = tid;
     float M = -INFINITY;
 #pragma unroll
-    for (int w = 0; w < NCONS_WARPS; ++w) M = fmaxf(M, wpart[(w * T3_MAX_NPOS + pp) * PART_STRIDE + 64]);
+    for (int w = 0; w < NCONS_WARPS; ++w) M = fmaxf(M, wpart[w * PART_STRIDE + 64]);
     float Ls = 0.f, O = 0.f;
     if (M != -INFINITY) {
 #pragma unroll
       for (int w = 0; w < NCONS_WARPS; ++w) {
-        const float* wp = wpart + (w * T3_MAX_NPOS + pp) * PART_STRIDE;
+        const float* wp = wpart + w * PART_STRIDE;
         const float cw = (wp[64] == -INFINITY) ? 0.f : __expf(wp[64] - M);
         Ls += cw * wp[65];
         O += cw * wp[d];
       }
     }
     const unsigned fl = ll_flag(it, L, layer, LLP_PART);
-    unsigned long long* out = p.ll + LL_PART + ((size_t)(pp * 32 + pair) * MAXS + split) * PART_STRIDE;
+    unsigned long long* out = p.ll + LL_PART + ((size_t)pair * MAXS + split) * PART_STRIDE;
     ll_store(out + d, O, fl);
     if (d == 0) { ll_store(out + 64, M, fl); ll_store(out + 65, Ls, fl); }
     // KV append after the partial is on its way; the fence orders it before this CTA's later LL stores
     if (split == S - 1) {
-      KV<KVT>::store(kc + (size_t)(pos0 + pp) * 64 + d, kr);
-      KV<KVT>::store(vc + (size_t)(pos0 + pp) * 64 + d, vr);
+      KV<KVT>::store(kc + (size_t)pos0 * 64 + d, kr);
+      KV<KVT>::store(vc + (size_t)pos0 * 64 + d, vr);
       __threadfence();
     }
-    if (split == 0) {
-      // merge the S partials of this pair -> attention output segment
-      const unsigned long long* const base = p.ll + LL_PART + ((size_t)(pp * 32 + pair) * MAXS) * PART_STRIDE;
-      const unsigned long long* ptr[3 * MAXS];
-#pragma unroll
-      for (int s = 0; s < MAXS; ++s) {
-        ptr[3 * s] = base + s * PART_STRIDE + d;
-        ptr[3 * s + 1] = base + s * PART_STRIDE + 64;
-        ptr[3 * s + 2] = base + s * PART_STRIDE + 65;
-      }
-      unsigned long long w[3 * MAXS];
-      ll_poll<3 * MAXS>(ptr, 3 * S, fl, w, ctl, p.st);
-      float Mx = -INFINITY;
-#pragma unroll
-      for (int s = 0; s < MAXS; ++s) if (s < S) Mx = fmaxf(Mx, ll_val(w[3 * s + 1]));
-      float Lt = 0.f, Ot = 0.f;
+  }
+}
+
+// o_proj prologue: merge the S split-KV partials of (row b, head) for this lane's 8 head dims
+template <int SI>
+struct PartLoad {
+  static __device__ __forceinline__ void issue(const unsigned long long* bo, const unsigned long long* bm, int S,
+                                               unsigned long long (&wo)[MAXS][8], unsigned long long (&wm)[MAXS],
+                                               unsigned long long (&wl)[MAXS]) {
+    if (SI < S) {
+      ll_ld2_off<(SI * PART_STRIDE + 0) * 8>(bo, wo[SI][0], wo[SI][1]);
+      ll_ld2_off<(SI * PART_STRIDE + 2) * 8>(bo, wo[SI][2], wo[SI][3]);
+      ll_ld2_off<(SI * PART_STRIDE + 4) * 8>(bo, wo[SI][4], wo[SI][5]);
+      ll_ld2_off<(SI * PART_STRIDE + 6) * 8>(bo, wo[SI][6], wo[SI][7]);
+      ll_ld2_off<(SI * PART_STRIDE + 64) * 8>(bm, wm[SI], wl[SI]);
+    }
+    if constexpr (SI + 1 < MAXS) PartLoad<SI + 1>::issue(bo, bm, S, wo, wm, wl);
+  }
+};
+__device__ __forceinline__ void attn_combine8(float (&x)[8], const T3Params& p, int S, int b, int k, unsigned flag, bool active,
+                                              Ctl* ctl) {
+  unsigned long long wo[MAXS][8], wm[MAXS], wl[MAXS];
+  const int head = k >> 6, d = k & 63;
+  const unsigned long long* base = p.ll + LL_PART + ((size_t)(b * T3_NH + head) * MAXS) * PART_STRIDE;
+  if (active) {
+    unsigned spins = 0; unsigned long long t0 = 0;
+    for (;;) {
+      bool ok = true;
+      PartLoad<0>::issue(base + d, base, S, wo, wm, wl);
 #pragma unroll
       for (int s = 0; s < MAXS; ++s) {
         if (s < S) {
-          const float ms = ll_val(w[3 * s + 1]);
-          const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
-          Lt += cw * ll_val(w[3 * s + 2]);
-          Ot += cw * ll_val(w[3 * s]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ok = ok && ll_ok(wo[s][e], flag);
+          ok = ok && ll_ok(wm[s], flag) && ll_ok(wl[s], flag);
         }
       }
-      ll_store(p.ll + LL_ATTN + (size_t)(pp * 2 + b) * T3_H + head * 64 + d, Ot / Lt, ll_flag(it, L, layer, LLP_ATTN));
+      if (ok) break;
+      if (poll_timeout(spins, t0, ctl, p.st)) break;
     }
   }
+  float Mx = -INFINITY;
+#pragma unroll
+  for (int s = 0; s < MAXS; ++s) if (s < S && active) Mx = fmaxf(Mx, ll_val(wm[s]));
+  float Lt = 0.f;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) x[e] = 0.f;
+#pragma unroll
+  for (int s = 0; s < MAXS; ++s) {
+    if (s < S && active) {
+      const float ms = ll_val(wm[s]);
+      const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
+      Lt += cw * ll_val(wl[s]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) x[e] += cw * ll_val(wo[s][e]);
+    }
+  }
+  const float inv = (active && Lt > 0.f) ? 1.0f / Lt : 0.f;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) x[e] *= inv;
 }
 
 // ---- sampling phase (CTA 0): t3.py:320-356 ------------------------------------------------------
@@ -767,315 +783,190 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
 }
 
 // ---- the megakernel -----------------------------------------------------------------------------
-template <typename KVT, int NPOS>
+// One iteration = one position.  Its 4 L (+1) GEMV steps — step = 4 l + phase, phase in {qkv, o, gate/up, down},
+// then the head — run through ONE rolled loop body, so the code of a step is shared by every phase and layer and
+// stays resident in the instruction cache; what differs between phases is data (a few switches).
+template <typename KVT>
 __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + SMEM_BARS);
-  uint64_t* empty = full + NSLOT;
   Ctl* ctl = reinterpret_cast<Ctl*>(smem + SMEM_CTL);
+  float* red_all = reinterpret_cast<float*>(smem + SMEM_RED);
+  float* ssq_all = reinterpret_cast<float*>(smem + SMEM_SSQ);
   float* scr = reinterpret_cast<float*>(smem + SMEM_SCRATCH);
-  float* red = scr;                       // [MAXU][8][64]
-  float* ssq = scr + T3_MAXU * 8 * 64;    // [8][8]
-  float* stage_all = reinterpret_cast<float*>(smem + SMEM_STAGE);
   unsigned char* seen = smem + SMEM_SEEN;
-  float* lnbuf = reinterpret_cast<float*>(smem + SMEM_LN);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = gridDim.x, c = blockIdx.x;
+  const int L = p.n_layers;
+  const int n_iters = (p.mode == 0) ? p.P : p.max_new;
+  Stream sm;
+  sm.base = p.wstream + (size_t)c * p.stride_bytes;
+  sm.policy = l2_policy_evict_first();
+  sm.per_iter_layers = L * t3_plan_units_per_layer(c, G);
+  sm.nhead = t3_plan_count(PH_HEAD, c, G);
+  sm.head_from_iter = (p.mode == 1) ? 0 : n_iters - 1;
+  sm.n_iters = n_iters;
   if (tid == 0) {
-    for (int s = 0; s < NSLOT; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NCONS_WARPS); }
-    ctl->abort = 0; ctl->cons_done = 0; ctl->cons_k = 0; ctl->tok = 0;
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(&full[s], 1); ctl->released[s] = 0; }
+    ctl->abort = 0; ctl->next_idx = 0; ctl->next_iter = 0;
     mbar_fence_init();
+    for (int s = 0; s < NSLOT; ++s) stream_issue_next(sm, ctl, s, ring, full);
   }
-  for (int i = tid; i < NCONS_WARPS * MAXROWS * STAGE_LD; i += NTHREADS) stage_all[i] = 0.f;
+  if (tid < PH_COUNT * T3_MAXU) {
+    const int ph = tid / T3_MAXU, j = tid % T3_MAXU, n = t3_plan_count(ph, c, G);
+    if (j == 0) ctl->plan_n[ph] = n;
+    ctl->plan_u[ph][j] = j < n ? t3_plan_unit(ph, c, G, j) : 0;
+  }
   if (c == 0) for (int i = tid; i < VOCAB_PAD; i += NTHREADS) seen[i] = p.seen[i];
   __syncthreads();
 
-  const int L = p.n_layers;
-  const int upl = t3_plan_units_per_layer(c, G);
-  const int nhead = t3_plan_count(PH_HEAD, c, G);
-  const int n_iters = (p.mode == 0) ? (p.P + NPOS - 1) / NPOS : p.max_new;
-
-  if (warp == NCONS_WARPS) {
-    // ===== producer warp: stream this CTA's weight units through the ring =====
-    const uint64_t policy = l2_policy_evict_first();
-    const uint8_t* base = p.wstream + (size_t)c * p.stride_bytes;
-    int slot = 0; uint32_t parity = 1; int k = 0;
-    bool stopped = false;
-    for (int it = 0; it < n_iters && !stopped; ++it) {
-      const bool head = (p.mode == 1) || (it == n_iters - 1);
-      const int n_units = L * upl + (head ? nhead : 0);
-      for (int u = 0; u < n_units; ++u) {
-        // wait for the slot to be free; give up if the consumers have finished (EOS / abort)
-        unsigned long long t0 = 0; unsigned spins = 0;
-        while (!mbar_try_wait(&empty[slot], parity)) {
-          if (ctl->cons_done || ctl->abort) { stopped = true; break; }
-          if ((++spins & 1023u) == 0) {
-            if (t0 == 0) t0 = gtime_ns();
-            else if (gtime_ns() - t0 > WATCHDOG_NS) { ctl->abort = 1; atomicExch(&p.st->err, 1); stopped = true; break; }
-          }
-        }
-        if (stopped) break;
-        if (lane == 0) {
-          mbar_arrive_expect_tx(&full[slot], T3_UNIT_BYTES);
-          tma_bulk_g2s(ring + slot * T3_UNIT_BYTES, base + (size_t)u * T3_UNIT_BYTES, T3_UNIT_BYTES, &full[slot], policy);
-        }
-        __syncwarp();
-        if (++slot == NSLOT) { slot = 0; parity ^= 1u; }
-        ++k;
-      }
-    }
-    // drain: every issued copy must have landed before the CTA may exit
-    {
-      unsigned long long t0 = gtime_ns(); unsigned spins = 0;
-      while (!ctl->cons_done) {
-        if ((++spins & 1023u) == 0 && gtime_ns() - t0 > 4 * WATCHDOG_NS) break;
-      }
-      __threadfence_block();
-      const int ck = ctl->cons_k;
-      for (int kk = ck; kk < k; ++kk) mbar_wait(&full[kk % NSLOT], (kk / NSLOT) & 1, ctl, p.st);
-    }
-  } else {
-    // ===== consumer warps =====
-    constexpr int R = 2 * NPOS;
-    constexpr int PAR = (NPOS == 1) ? 4 : 1;
-    const int g = lane >> 2, tig = lane & 3, pp = g >> 1, bb = g & 1;
-    const int kwb = warp * 128, kw = kwb + tig * 8;
-    float* stage = stage_all + warp * MAXROWS * STAGE_LD;
-    RingPos rp{0, 0u, 0, 0ull, 0ull};
-    int pos0 = __ldcg(&p.st->pos);
-    int n_gen = __ldcg(&p.st->n_gen);
-    int n_done = 0;
-    float xres[4][8];     // residual stream of row g, replicated in every CTA
-    float xs[4][8];
-    uint32_t A[4][8];
-    int prof_k = 0;
-    int qq = 0;           // running index of the norm whose gains sit in lnbuf[qq & 1]
-    ln_prefetch(lnbuf, 0, p.ln1, tid);
+  const int b = lane >> 4;                        // activation row (CFG cond / uncond) of this lane
+  const int kq = warp * 128 + (lane & 15) * 8;    // its 8 consecutive k in a 1024-wide vector
+  const bool active = b < p.B;
+  float* xt = reinterpret_cast<float*>(smem + SMEM_XT) + warp * 256;
+  const int S = attn_splits(G, p.B);
+  const int down_slice = ctl->plan_u[PH_DOWN][0] % T3_DOWN_KS;
+  RingPos rp{0, 0u, 0ll};
+  int pos0 = __ldcg(&p.st->pos);
+  int n_gen = __ldcg(&p.st->n_gen);
+  int n_done = 0;
+  float xres[8];        // residual stream slice, replicated in every CTA
+  float x[8];
+  float gn[8];          // gains of the next RMSNorm (fetched a phase ahead)
+  uint32_t Bf[8][2];
+  int prof_k = 0;
+  int par = 0;          // parity of the running step counter: red / ssq double buffer
+  ln_fetch(gn, p.ln1, kq);
 #define T3_PROF() do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it) p.prof[prof_k++] = gtime_ns(); } while (0)
-#define T3_SUB(k) do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5) p.prof[200 + (k)] = gtime_ns(); } while (0)
-#define T3_ROW_OK(gg) ((gg) < 2 * npos && ((gg) & 1) < p.B)
+#define T3_SUB(k) do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5 && (ph == PH_QKV || ph == PH_GU)) \
+                         p.prof[200 + (ph == PH_GU ? 8 : 0) + (k)] = gtime_ns(); } while (0)
 
-    for (int it = 0; it < n_iters; ++it) {
-      int npos = 1;
-      if (p.mode == 1) {
-        T3_PROF();
-        if (c == 0) sample_phase(p, it, n_gen, scr, seen, ctl, warp, lane);
-        // control word of this iteration: token id | stop bit
-        const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
-        unsigned long long w;
-        unsigned spins = 0; unsigned long long t0 = 0;
-        for (;;) {
-          w = ll_ld1(p.ll + LL_EMB + T3_H);
-          if (ll_ok(w, fl)) break;
-          if (poll_timeout(spins, t0, ctl, p.st)) break;
-        }
-        ++n_gen; ++n_done;
-        if (((unsigned)w >> 31) || ctl->abort) break;
-        T3_PROF();
+  for (int it = 0; it < n_iters; ++it) {
+    if (p.mode == 1) {
+      T3_PROF();
+      if (c == 0) sample_phase(p, it, n_gen, scr, seen, ctl, warp, lane);
+      // control word of this iteration: token id | stop bit
+      const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
+      unsigned long long w;
+      unsigned spins = 0; unsigned long long t0 = 0;
+      for (;;) {
+        w = ll_ld1(p.ll + LL_EMB + T3_H);
+        if (ll_ok(w, fl)) break;
+        if (poll_timeout(spins, t0, ctl, p.st)) break;
+      }
+      ++n_gen; ++n_done;
+      if (((unsigned)w >> 31) || ctl->abort) break;
+      T3_PROF();
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) xres[e] = 0.f;
+    const bool with_head = (p.mode == 1) || (it == n_iters - 1);
+    const int n_steps = 4 * L + (with_head ? 1 : 0);
+
+#pragma unroll 1
+    for (int step = 0; step < n_steps; ++step) {
+      const int l = step >> 2;
+      const int ph = (l == L) ? PH_HEAD : (step & 3);
+      float* red = red_all + par * RED_FLOATS;
+      float* ssq = ssq_all + par * 16;
+      // ---------- prologue: this lane's 8 input values ----------
+      T3_SUB(0);
+      if (ph == PH_O) {
+        attn_combine8(x, p, S, b, kq, ll_flag(it, L, l, LLP_PART), active, ctl);
+      } else if (ph == PH_QKV && l == 0 && p.mode == 0) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) x[e] = 0.f;
+        if (active) ln_fetch(x, p.embeds + ((size_t)b * p.P + it) * T3_H, kq);
       } else {
-        npos = min(NPOS, p.P - it * NPOS);
+        const unsigned long long* base; size_t stride = 0; int np = 1; unsigned fl;
+        if (ph == PH_GU) { base = p.ll + LL_OPROJ + (size_t)b * T3_H + kq; fl = ll_flag(it, L, l, LLP_OPROJ); }
+        else if (ph == PH_DOWN) { base = p.ll + LL_ACT + (size_t)b * T3_INTER + down_slice * 1024 + kq; fl = ll_flag(it, L, l, LLP_ACT); }
+        else if (l == 0) { base = p.ll + LL_EMB + kq; fl = ll_flag(it, L, 0, LLP_EMB); }          // qkv of layer 0
+        else { base = p.ll + LL_DOWN + (size_t)b * T3_H + kq; stride = 2 * T3_H; np = T3_DOWN_KS; fl = ll_flag(it, L, l - 1, LLP_DOWN); }
+        ll_load8(x, base, stride, np, fl, active && (ph != PH_DOWN || ctl->plan_n[PH_DOWN] > 0), ctl, p.st);
       }
-      const int nrows = 2 * npos;
-      const bool active = T3_ROW_OK(g);
-
-      for (int l = 0; l < L; ++l) {
-        // ---------- phase A: x_l = residual; RMSNorm; fused q|k|v GEMV ----------
-        {
-          T3_SUB(0);
-          if (l == 0) {
-            if (p.mode == 0) {
+      T3_SUB(1);
+      // ---------- residual add + RMSNorm gain (the scale is applied in the epilogue) ----------
+      if (ph == PH_QKV || ph == PH_GU || ph == PH_HEAD) {
 #pragma unroll
-              for (int jj = 0; jj < 4; ++jj)
+        for (int e = 0; e < 8; ++e) xres[e] += x[e];
+        ssq_partial(xres, ssq, warp, lane);
 #pragma unroll
-                for (int e = 0; e < 8; ++e) xres[jj][e] = 0.f;
-              if (active) {
-                const float* src = p.embeds + ((size_t)bb * p.P + (size_t)it * NPOS + pp) * T3_H + kw;
-#pragma unroll
-                for (int jj = 0; jj < 4; ++jj) {
-                  const float4 a = __ldg(reinterpret_cast<const float4*>(src + jj * 32));
-                  const float4 b = __ldg(reinterpret_cast<const float4*>(src + jj * 32 + 4));
-                  xres[jj][0] = a.x; xres[jj][1] = a.y; xres[jj][2] = a.z; xres[jj][3] = a.w;
-                  xres[jj][4] = b.x; xres[jj][5] = b.y; xres[jj][6] = b.z; xres[jj][7] = b.w;
-                }
-              }
-            } else {
-              Piece pc[1] = {Piece{p.ll + LL_EMB, 0, ll_flag(it, L, 0, LLP_EMB)}};
-              ll_stage<R, 1>(stage, pc, 1, kwb, nrows, p.B, lane, ctl, p.st);
-              stage_read(xres, stage, g, tig);
+        for (int e = 0; e < 8; ++e) x[e] = xres[e] * gn[e];
+        const float* nxt;
+        if (ph == PH_QKV) nxt = p.ln2 + (size_t)l * T3_H;
+        else if (ph == PH_GU) nxt = (l == L - 1 && with_head) ? p.final_norm : p.ln1 + (size_t)((l + 1) % L) * T3_H;
+        else nxt = p.ln1;
+        ln_fetch(gn, nxt, kq);
+      }
+      make_bfrags(Bf, x, xt, lane);
+      T3_SUB(2);
+      const int n = ctl->plan_n[ph];
+      consume_units(n, rp, Bf, red, ring, full, sm, warp, lane, ctl, p.st);
+      T3_SUB(3);
+      cbar();
+      T3_SUB(4);
+      // ---------- epilogue: cross-warp sum, scale / SwiGLU, publish ----------
+      if (tid < n * 32) {
+        const int j = tid >> 5, o = tid & 31, bb = o >> 4, row = o & 15;
+        const int u = ctl->plan_u[ph][j];
+        float v = red_sum(red, j, o);
+        // gate/up: rows 0-7 of the unit are gate rows, 8-15 the matching up rows: lane o pairs with lane o + 8
+        // (whole-warp shuffle: kept outside the row test, B == 1 leaves lanes 16-31 without a row)
+        const float other = __shfl_down_sync(0xffffffffu, v, 8);
+        if (bb < p.B) {
+          if (ph == PH_QKV) {
+            ll_store(p.ll + LL_QKV + (size_t)bb * 3072 + u * 16 + row, v * rms_scale(ssq, bb), ll_flag(it, L, l, LLP_QKV));
+          } else if (ph == PH_O) {
+            ll_store(p.ll + LL_OPROJ + (size_t)bb * T3_H + u * 16 + row, v, ll_flag(it, L, l, LLP_OPROJ));
+          } else if (ph == PH_GU) {
+            const float sc = rms_scale(ssq, bb);
+            if (row < 8) {
+              const float gate = v * sc, up = other * sc;
+              ll_store(p.ll + LL_ACT + (size_t)bb * T3_INTER + u * 8 + row, gate / (1.0f + __expf(-gate)) * up,
+                       ll_flag(it, L, l, LLP_ACT));
             }
+          } else if (ph == PH_DOWN) {
+            ll_store(p.ll + LL_DOWN + (size_t)((u % T3_DOWN_KS) * 2 + bb) * T3_H + (u / T3_DOWN_KS) * 16 + row, v,
+                     ll_flag(it, L, l, LLP_DOWN));
           } else {
-            Piece pc[T3_DOWN_KS];
-#pragma unroll
-            for (int s = 0; s < T3_DOWN_KS; ++s)
-              pc[s] = Piece{p.ll + LL_DOWN + (size_t)s * MAXROWS * T3_H, T3_H, ll_flag(it, L, l - 1, LLP_DOWN)};
-            ll_stage<R, PAR>(stage, pc, T3_DOWN_KS, kwb, nrows, p.B, lane, ctl, p.st);
-            stage_read(xs, stage, g, tig);
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-              for (int e = 0; e < 8; ++e) xres[jj][e] += xs[jj][e];
-          }
-          T3_SUB(1);
-          rmsnorm_rows(xs, xres, lnbuf, qq, kw, ssq, warp, lane);
-          ++qq;
-          ln_prefetch(lnbuf, qq, p.ln2 + (size_t)l * T3_H, tid);
-          make_frags(A, xs);
-          T3_SUB(2);
-          const int n = t3_plan_count(PH_QKV, c, G);
-          consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
-          T3_SUB(3);
-          cbar();
-          T3_SUB(4);
-          const unsigned fl = ll_flag(it, L, l, LLP_QKV);
-          for (int idx = tid; idx < n * 64; idx += NCONS) {
-            const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-            if (T3_ROW_OK(gg))
-              ll_store(p.ll + LL_QKV + (size_t)gg * 3072 + t3_plan_unit(PH_QKV, c, G, j) * 8 + nn, red_sum(red, j, o), fl);
-          }
-          T3_SUB(5);
-          cbar();
-          T3_SUB(6);
-        }
-        T3_PROF();
-        // ---------- phase B: RoPE, KV append, split-KV attention, split combine ----------
-        attn_phase<KVT, NPOS>(p, it, l, pos0, npos, scr, warp, lane, ctl);
-        T3_PROF();
-        // ---------- phase C: o_proj ----------
-        {
-          Piece pc[1] = {Piece{p.ll + LL_ATTN, T3_H, ll_flag(it, L, l, LLP_ATTN)}};
-          ll_stage<R, 1>(stage, pc, 1, kwb, nrows, p.B, lane, ctl, p.st);
-          stage_read(xs, stage, g, tig);
-          make_frags(A, xs);
-          const int n = t3_plan_count(PH_O, c, G);
-          cbar();    // the attention phase used the scratch that `red` aliases
-          consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
-          cbar();
-          const unsigned fl = ll_flag(it, L, l, LLP_OPROJ);
-          for (int idx = tid; idx < n * 64; idx += NCONS) {
-            const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-            if (T3_ROW_OK(gg))
-              ll_store(p.ll + LL_OPROJ + (size_t)gg * T3_H + t3_plan_unit(PH_O, c, G, j) * 8 + nn, red_sum(red, j, o), fl);
-          }
-          cbar();
-        }
-        T3_PROF();
-        // ---------- phase D: residual add; post-attention RMSNorm; gate/up GEMV; SwiGLU ----------
-        {
-          T3_SUB(8);
-          Piece pc[1] = {Piece{p.ll + LL_OPROJ, T3_H, ll_flag(it, L, l, LLP_OPROJ)}};
-          ll_stage<R, 1>(stage, pc, 1, kwb, nrows, p.B, lane, ctl, p.st);
-          stage_read(xs, stage, g, tig);
-          T3_SUB(9);
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-            for (int e = 0; e < 8; ++e) xres[jj][e] += xs[jj][e];
-          rmsnorm_rows(xs, xres, lnbuf, qq, kw, ssq, warp, lane,
-                       (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5) ? p.prof + 216 : nullptr);
-          ++qq;
-          {
-            const bool head_next = (l == L - 1) && (p.mode == 1 || it == n_iters - 1);
-            ln_prefetch(lnbuf, qq, head_next ? p.final_norm : p.ln1 + (size_t)((l + 1) % L) * T3_H, tid);
-          }
-          make_frags(A, xs);
-          T3_SUB(10);
-          const int n = t3_plan_count(PH_GU, c, G);
-          consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
-          T3_SUB(11);
-          cbar();
-          T3_SUB(12);
-          const unsigned fl = ll_flag(it, L, l, LLP_ACT);
-          for (int idx = tid; idx < n * 32; idx += NCONS) {
-            const int j = idx >> 5, o2 = idx & 31, gg = o2 >> 2, nn = o2 & 3;
-            if (T3_ROW_OK(gg)) {
-              const float gate = red_sum(red, j, gg * 8 + nn), up = red_sum(red, j, gg * 8 + 4 + nn);
-              const float silu = gate / (1.0f + __expf(-gate));
-              ll_store(p.ll + LL_ACT + (size_t)gg * T3_INTER + t3_plan_unit(PH_GU, c, G, j) * 4 + nn, silu * up, fl);
+            const int vrow = u * 16 + row;
+            if (vrow < T3_VOCAB) {
+              v *= rms_scale(ssq, bb);
+              p.logits[(size_t)bb * T3_VOCAB + vrow] = v;     // plain copy: read by the next launch
+              if (p.mode == 1) ll_store(p.ll + LL_LOGITS + (size_t)bb * VOCAB_PAD + vrow, v, ll_flag(it, L, L, LLP_LOGITS));
             }
           }
-          T3_SUB(13);
-          cbar();
-          T3_SUB(14);
         }
-        T3_PROF();
-        // ---------- phase E: down_proj (k-slice s of this CTA) ----------
-        {
-          const int n = t3_plan_count(PH_DOWN, c, G);
-          if (n > 0) {
-            const int s = t3_plan_unit(PH_DOWN, c, G, 0) % T3_DOWN_KS;
-            Piece pc[1] = {Piece{p.ll + LL_ACT, T3_INTER, ll_flag(it, L, l, LLP_ACT)}};
-            ll_stage<R, 1>(stage, pc, 1, s * 1024 + kwb, nrows, p.B, lane, ctl, p.st);
-            stage_read(xs, stage, g, tig);
-            make_frags(A, xs);
-            consume_units(n, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
-          }
-          cbar();
-          const unsigned fl = ll_flag(it, L, l, LLP_DOWN);
-          for (int idx = tid; idx < n * 64; idx += NCONS) {
-            const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-            if (T3_ROW_OK(gg)) {
-              const int u = t3_plan_unit(PH_DOWN, c, G, j);
-              ll_store(p.ll + LL_DOWN + (size_t)(u % T3_DOWN_KS) * MAXROWS * T3_H + (size_t)gg * T3_H +
-                           (u / T3_DOWN_KS) * 8 + nn, red_sum(red, j, o), fl);
-            }
-          }
-          cbar();
-        }
+      }
+      T3_SUB(5);
+      par ^= 1;
+      T3_PROF();
+      // ---------- RoPE, KV append, split-KV attention between the qkv and o_proj steps ----------
+      if (ph == PH_QKV) {
+        attn_phase<KVT>(p, it, l, pos0, scr, warp, lane, ctl);
         T3_PROF();
       }
-      // ---------- phase F: final RMSNorm + speech_head (t3_hf_backend.py:100-103) ----------
-      if (p.mode == 1 || it == n_iters - 1) {
-        Piece pc[T3_DOWN_KS];
-#pragma unroll
-        for (int s = 0; s < T3_DOWN_KS; ++s)
-          pc[s] = Piece{p.ll + LL_DOWN + (size_t)s * MAXROWS * T3_H, T3_H, ll_flag(it, L, L - 1, LLP_DOWN)};
-        ll_stage<R, PAR>(stage, pc, T3_DOWN_KS, kwb, nrows, p.B, lane, ctl, p.st);
-        stage_read(xs, stage, g, tig);
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj)
-#pragma unroll
-          for (int e = 0; e < 8; ++e) xres[jj][e] += xs[jj][e];
-        rmsnorm_rows(xs, xres, lnbuf, qq, kw, ssq, warp, lane);
-        ++qq;
-        ln_prefetch(lnbuf, qq, p.ln1, tid);
-        make_frags(A, xs);
-        consume_units(nhead, rp, A, red, ring, full, empty, warp, lane, ctl, p.st);
-        cbar();
-        const int plast = npos - 1;
-        const unsigned fl = ll_flag(it, L, L, LLP_LOGITS);
-        for (int idx = tid; idx < nhead * 64; idx += NCONS) {
-          const int j = idx >> 6, o = idx & 63, gg = o >> 3, nn = o & 7;
-          const int row = t3_plan_unit(PH_HEAD, c, G, j) * 8 + nn;
-          if ((gg >> 1) == plast && (gg & 1) < p.B && row < T3_VOCAB) {
-            const float v = red_sum(red, j, o);
-            p.logits[(size_t)(gg & 1) * T3_VOCAB + row] = v;     // plain copy: read by the next launch
-            if (p.mode == 1) ll_store(p.ll + LL_LOGITS + (size_t)(gg & 1) * VOCAB_PAD + row, v, fl);
-          }
-        }
-        cbar();
-        T3_PROF();
-      }
-#ifdef T3_DEBUG_WAIT
-      if (p.prof && c == 0 && tid == 0 && it == p.prof_it) { p.prof[230] = rp.wait_ns; p.prof[231] = rp.mma_ns; p.prof[232] = rp.k; }
-      rp.wait_ns = 0; rp.mma_ns = 0;
-#endif
-      pos0 += npos;
-      if (ctl->abort) break;
     }
-    // publish state + tell the producer how far we got
-    if (c == 0 && tid == 0) {
-      p.st->pos = pos0;
-      p.st->n_gen = n_gen;
-      if (p.mode == 1 && p.n_out) *p.n_out = n_done;
-    }
-    cbar();
-    if (tid == 0) {
-      ctl->cons_k = rp.k;
-      __threadfence_block();
-      ctl->cons_done = 1;
-    }
+    pos0 += 1;
+    if (ctl->abort) break;
+  }
+  // publish state
+  if (c == 0 && tid == 0) {
+    p.st->pos = pos0;
+    p.st->n_gen = n_gen;
+    if (p.mode == 1 && p.n_out) *p.n_out = n_done;
+  }
+  __syncthreads();
+  // drain: every copy in flight must have landed before the CTA may exit (early stop on EOS / abort)
+  if (tid == 0) {
+    // units issued so far = consumed + those still in the ring; the cursor tells how many were issued
+    long long issued = 0;
+    for (int i2 = 0; i2 < ctl->next_iter && i2 < n_iters; ++i2) issued += sm.per_iter_layers + (i2 >= sm.head_from_iter ? sm.nhead : 0);
+    if (ctl->next_iter < n_iters) issued += ctl->next_idx;
+    for (long long kk = rp.k; kk < issued; ++kk) mbar_wait(&full[kk % NSLOT], (uint32_t)((kk / NSLOT) & 1), ctl, p.st);
   }
   __syncthreads();
 }
@@ -1127,7 +1018,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
   CBX_CHECK(prop.major == 10, "cbx_t3_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
   const int G = prop.multiProcessorCount;
-  CBX_CHECK(G >= 129 && (1025 + G - 1) / G <= T3_MAXU, "cbx_t3_create: %d SMs unsupported by the plan", G);
+  CBX_CHECK(G >= 129 && (513 + G - 1) / G <= T3_MAXU, "cbx_t3_create: %d SMs unsupported by the plan", G);
   int coop = 0;
   CBX_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, cfg->device));
   CBX_CHECK(coop, "cbx_t3_create: device lacks cooperative launch");
@@ -1162,10 +1053,8 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   p.logits = reinterpret_cast<float*>(s + o_logits);
   p.st = reinterpret_cast<T3State*>(s + o_st);
   p.seen = s + o_seen;
-  int rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16, 1>);
-  if (!rc) rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16, T3_MAX_NPOS>);
-  if (!rc) rc = t3_prepare_kernel(t3_megakernel<float, 1>);
-  if (!rc) rc = t3_prepare_kernel(t3_megakernel<float, T3_MAX_NPOS>);
+  int rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16>);
+  if (!rc) rc = t3_prepare_kernel(t3_megakernel<float>);
   if (rc) { cudaFree(h->slab); delete h; return CBX_ERR; }
   *out = h;
   return CBX_OK;
@@ -1181,10 +1070,7 @@ extern "C" int cbx_t3_destroy(cbx_t3* h) {
 static int t3_launch(cbx_t3* h, T3Params& p, cudaStream_t st) {
   CBX_CUDA(cudaMemsetAsync(p.ll, 0, LL_WORDS * 8, st));     // flags restart at 1 in every launch
   void* args[] = {&p};
-  const void* fn;
-  if (p.mode == 0) fn = h->cfg.kv_fp32 ? (const void*)t3_megakernel<float, T3_MAX_NPOS>
-                                       : (const void*)t3_megakernel<__nv_bfloat16, T3_MAX_NPOS>;
-  else fn = h->cfg.kv_fp32 ? (const void*)t3_megakernel<float, 1> : (const void*)t3_megakernel<__nv_bfloat16, 1>;
+  const void* fn = h->cfg.kv_fp32 ? (const void*)t3_megakernel<float> : (const void*)t3_megakernel<__nv_bfloat16>;
   CBX_CUDA(cudaLaunchCooperativeKernel(fn, dim3(h->G), dim3(NTHREADS), args, SMEM_TOTAL, st));
   h->launches += 1;
   return CBX_OK;

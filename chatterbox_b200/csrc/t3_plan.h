@@ -3,14 +3,14 @@
 // by the host-side weight packer, so the per-CTA weight streams in HBM are laid out in exactly the
 // order the TMA producer walks them.
 //
-// A unit is 8 weight rows x 1024 k (bf16) = 16 KB.  Per decoder layer (HF LlamaDecoderLayer as
+// A unit is 16 weight rows x 1024 k (bf16) = 32 KB.  Per decoder layer (HF LlamaDecoderLayer as
 // configured by reference src/chatterbox/models/t3/llama_configs.py:1-33):
-//   PH_QKV  : 3072 x 1024 fused q|k|v          -> 384 units, unit u = rows [8u, 8u+8)
-//   PH_O    : 1024 x 1024 o_proj               -> 128 units
-//   PH_GU   : 8192 x 1024 gate/up interleaved  -> 1024 units, unit u = gate rows 4u..4u+3 then up rows 4u..4u+3
-//   PH_DOWN : 1024 x 4096 down_proj            -> 512 units, unit u = r*4+s: rows [8r,8r+8), k-slice [1024s, 1024s+1024)
+//   PH_QKV  : 3072 x 1024 fused q|k|v          -> 192 units, unit u = rows [16u, 16u+16)
+//   PH_O    : 1024 x 1024 o_proj               -> 64 units
+//   PH_GU   : 8192 x 1024 gate/up interleaved  -> 512 units, unit u = gate rows 8u..8u+7 then up rows 8u..8u+7
+//   PH_DOWN : 1024 x 4096 down_proj            -> 256 units, unit u = r*4+s: rows [16r,16r+16), k-slice [1024s, 1024s+1024)
 // and once per step
-//   PH_HEAD : 8194(->8200) x 1024 speech_head  -> 1025 units (reference t3/t3.py:64)
+//   PH_HEAD : 8194(->8208) x 1024 speech_head  -> 513 units (reference t3/t3.py:64)
 // Units of a phase are dealt round-robin over the G CTAs starting at a per-phase rotation chosen so
 // that the per-layer totals differ by at most one unit between CTAs.  In PH_DOWN all units of a CTA
 // share one k-slice so its activation fragments stay in registers.
@@ -29,20 +29,20 @@ enum { PH_QKV = 0, PH_O = 1, PH_GU = 2, PH_DOWN = 3, PH_HEAD = 4, PH_COUNT = 5 }
 #define T3_HD 64
 #define T3_INTER 4096
 #define T3_VOCAB 8194
-#define T3_UNIT_ROWS 8
-#define T3_UNIT_BYTES 16384
-#define T3_MAXU 8          // max units of one phase on one CTA (needs G >= 129)
-#define T3_MAX_NPOS 4      // positions processed per weight pass (1 = decode, up to 4 = chunked prefill)
-#define T3_DOWN_ROWG 128   // 1024 / 8 row groups of down_proj
+#define T3_VOCAB_PAD 8208  // speech_head rows padded to whole units
+#define T3_UNIT_ROWS 16
+#define T3_UNIT_BYTES 32768
+#define T3_MAXU 4          // max units of one phase on one CTA (needs G >= 129)
+#define T3_DOWN_ROWG 64    // 1024 / 16 row groups of down_proj
 #define T3_DOWN_KS 4       // k-slices of down_proj
 
 CBX_HD int t3_phase_units(int ph) {
-  return ph == PH_QKV ? 384 : ph == PH_O ? 128 : ph == PH_GU ? 1024 : ph == PH_DOWN ? 512 : 1025;
+  return ph == PH_QKV ? 192 : ph == PH_O ? 64 : ph == PH_GU ? 512 : ph == PH_DOWN ? 256 : 513;
 }
 CBX_HD int t3_phase_rot(int ph, int G) {
   // cumulative unit count of the preceding phases of the layer, mod G
-  return ph == PH_QKV ? 0 : ph == PH_O ? (384 % G) : ph == PH_GU ? ((384 + 128) % G)
-       : ph == PH_DOWN ? ((384 + 128 + 1024) % G) : 0;
+  return ph == PH_QKV ? 0 : ph == PH_O ? (192 % G) : ph == PH_GU ? ((192 + 64) % G)
+       : ph == PH_DOWN ? ((192 + 64 + 512) % G) : 0;
 }
 // number of units of phase `ph` that CTA `c` of `G` consumes
 CBX_HD int t3_plan_count(int ph, int c, int G) {

@@ -1,9 +1,10 @@
 """One-time weight pre-pack for the T3 decode megakernel (fp32 state dict -> bf16 per-CTA streams).
 
 The kernel's TMA producer walks ONE contiguous byte stream per CTA, in the order the static plan
-(`csrc/t3_plan.h`, exported as `cbx_t3_plan_count/unit`) says that CTA consumes 16 KB units.  A
-unit is 8 weight rows x 1024 k in bf16, stored in MMA B-fragment order [k32-block j][row g][32 k],
-so a consumer warp's 128-bit shared-memory reads are contiguous and conflict-free.
+(`csrc/t3_plan.h`, exported as `cbx_t3_plan_count/unit`) says that CTA consumes 32 KB units.  A
+unit is 16 weight rows x 1024 k in bf16, stored in mma.m16n8k16 A-fragment order
+[warp k-slice w][k16 step s][lane][a0 a1 a2 a3], so every consumer lane fetches the four A registers of
+one MMA with a single conflict-free 128-bit shared-memory read.
 
 State-dict keys are the reference's (`T3.state_dict()`, src/chatterbox/models/t3/t3.py:41-65).
 """
@@ -17,9 +18,10 @@ import torch
 
 from . import _lib
 
-H, INTER, VOCAB, UNIT_ELEMS = 1024, 4096, 8194, 8192
+H, INTER, VOCAB, VOCAB_PAD, UNIT_ROWS, UNIT_ELEMS = 1024, 4096, 8194, 8208, 16, 16384
 PH_QKV, PH_O, PH_GU, PH_DOWN, PH_HEAD = range(5)
-PHASE_UNITS = (384, 128, 1024, 512, 1025)
+PHASE_UNITS = (192, 64, 512, 256, 513)
+LAYER_UNITS = sum(PHASE_UNITS[:4])
 
 
 def plan_lists(G: int) -> List[List[List[int]]]:
@@ -30,30 +32,31 @@ def plan_lists(G: int) -> List[List[List[int]]]:
 
 
 def _frag_order(units: torch.Tensor) -> torch.Tensor:
-    """[U, 8 rows, 1024 k] -> [U, 8192] in [j (32)][g (8)][32 k] order."""
+    """[U, 16 rows, 1024 k] -> [U, 16384] in A-fragment order: row = rh*8 + g, k = w*128 + s*16 + kh*8 + tig*2 + e
+    -> [w][s][g][tig][kh][rh][e]  (a0 = (kh 0, rh 0), a1 = (0, 1), a2 = (1, 0), a3 = (1, 1))."""
     U = units.shape[0]
-    return units.reshape(U, 8, 32, 32).permute(0, 2, 1, 3).reshape(U, UNIT_ELEMS)
+    return units.reshape(U, 2, 8, 8, 8, 2, 4, 2).permute(0, 3, 4, 2, 6, 5, 1, 7).reshape(U, UNIT_ELEMS)
 
 
 def layer_units(sd: Dict[str, torch.Tensor], i: int, dev) -> torch.Tensor:
-    """All 2048 units of decoder layer i in phase order (qkv | o | gate-up | down): [2048, 8192] bf16."""
+    """All 1024 units of decoder layer i in phase order (qkv | o | gate-up | down): [1024, 16384] bf16."""
     p = f"tfmr.layers.{i}."
     g = lambda n: sd[p + n].to(dev, torch.float32)
     qkv = torch.cat([g("self_attn.q_proj.weight"), g("self_attn.k_proj.weight"), g("self_attn.v_proj.weight")], 0)
-    a = qkv.reshape(384, 8, H)
-    c = g("self_attn.o_proj.weight").reshape(128, 8, H)
-    gate = g("mlp.gate_proj.weight").reshape(1024, 4, H)
-    up = g("mlp.up_proj.weight").reshape(1024, 4, H)
-    d = torch.cat([gate, up], 1)                                   # unit u: gate rows 4u..4u+3, up rows 4u..4u+3
-    wd = g("mlp.down_proj.weight").reshape(128, 8, 4, 1024)        # [r][row][s][k]
-    e = wd.permute(0, 2, 1, 3).reshape(512, 8, 1024)               # unit u = r*4 + s
+    a = qkv.reshape(192, 16, H)
+    c = g("self_attn.o_proj.weight").reshape(64, 16, H)
+    gate = g("mlp.gate_proj.weight").reshape(512, 8, H)
+    up = g("mlp.up_proj.weight").reshape(512, 8, H)
+    d = torch.cat([gate, up], 1)                                   # unit u: gate rows 8u..8u+7, up rows 8u..8u+7
+    wd = g("mlp.down_proj.weight").reshape(64, 16, 4, 1024)        # [r][row][s][k]
+    e = wd.permute(0, 2, 1, 3).reshape(256, 16, 1024)              # unit u = r*4 + s
     return _frag_order(torch.cat([a, c, d, e], 0)).to(torch.bfloat16)
 
 
 def head_units(sd: Dict[str, torch.Tensor], dev) -> torch.Tensor:
     w = sd["speech_head.weight"].to(dev, torch.float32)
-    w = torch.cat([w, torch.zeros(8200 - VOCAB, H, device=dev)], 0)
-    return _frag_order(w.reshape(1025, 8, H)).to(torch.bfloat16)
+    w = torch.cat([w, torch.zeros(VOCAB_PAD - VOCAB, H, device=dev)], 0)
+    return _frag_order(w.reshape(513, 16, H)).to(torch.bfloat16)
 
 
 def rope_tables(max_pos: int, dev) -> (torch.Tensor, torch.Tensor):
@@ -78,7 +81,7 @@ class T3Packed:
     G: int
     n_layers: int
     stride_units: int
-    wstream: torch.Tensor       # [G, stride_units, 8192] bf16
+    wstream: torch.Tensor       # [G, stride_units, 16384] bf16
     ln1: torch.Tensor
     ln2: torch.Tensor
     final_norm: torch.Tensor
@@ -90,13 +93,13 @@ class T3Packed:
 
     def weight_bytes_per_step(self) -> int:
         """Algorithmic weight bytes one decode step streams (every unit once + norms)."""
-        return (self.n_layers * 2048 + 1025) * UNIT_ELEMS * 2 + (2 * self.n_layers + 1) * H * 4
+        return (self.n_layers * LAYER_UNITS + PHASE_UNITS[4]) * UNIT_ELEMS * 2 + (2 * self.n_layers + 1) * H * 4
 
 
 def pack_t3(sd: Dict[str, torch.Tensor], G: int, device, max_pos: int, n_layers: int = 30) -> T3Packed:
     dev = torch.device(device)
     plan = plan_lists(G)
-    offs = [0, 384, 384 + 128, 384 + 128 + 1024]
+    offs = [0, 192, 192 + 64, 192 + 64 + 512]
     layer_idx = [torch.tensor([offs[ph] + u for ph in range(4) for u in plan[c][ph]], dtype=torch.long, device=dev)
                  for c in range(G)]
     head_idx = [torch.tensor(plan[c][PH_HEAD], dtype=torch.long, device=dev) for c in range(G)]

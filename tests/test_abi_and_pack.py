@@ -28,7 +28,7 @@ def test_plan_is_a_partition(G):
     for ph, U in enumerate(pack.PHASE_UNITS):
         units = sorted(u for c in range(G) for u in plan[c][ph])
         assert units == list(range(U)), (G, ph)
-        assert max(len(plan[c][ph]) for c in range(G)) <= 8
+        assert max(len(plan[c][ph]) for c in range(G)) <= 4
     # all DOWN units of a CTA share one k-slice
     for c in range(G):
         assert len({u % 4 for u in plan[c][pack.PH_DOWN]}) <= 1
@@ -43,33 +43,35 @@ def test_pack_layout_follows_plan():
     plan = pack.plan_lists(G)
     assert pk.wstream.shape[0] == G and pk.wstream.dtype == torch.bfloat16
 
-    def unit_rows(c, slot):   # undo the fragment order -> [8 rows, 1024 k]
-        return pk.wstream[c, slot].float().reshape(32, 8, 32).permute(1, 0, 2).reshape(8, 1024)
+    def unit_rows(c, slot):   # undo the A-fragment order -> [16 rows, 1024 k]
+        f = pk.wstream[c, slot].float().reshape(8, 8, 8, 4, 2, 2, 2)          # [w][s][g][tig][kh][rh][e]
+        return f.permute(5, 2, 0, 1, 4, 3, 6).reshape(16, 1024)               # row = rh*8+g, k = w*128+s*16+kh*8+tig*2+e
 
     q = sd["tfmr.layers.0.self_attn.q_proj.weight"]
     gate, up = sd["tfmr.layers.0.mlp.gate_proj.weight"], sd["tfmr.layers.0.mlp.up_proj.weight"]
     down, head = sd["tfmr.layers.0.mlp.down_proj.weight"], sd["speech_head.weight"]
+    bf = lambda t: t.to(torch.bfloat16).float()
     for c in (0, 57, 147):
         slot = 0
         u = plan[c][0][0]
-        if u < 128:
-            assert torch.equal(unit_rows(c, slot), q[8 * u:8 * u + 8])
+        if u < 64:
+            assert torch.equal(unit_rows(c, slot), bf(q[16 * u:16 * u + 16]))
         slot = len(plan[c][0]) + len(plan[c][1])
         u = plan[c][2][0]
-        assert torch.equal(unit_rows(c, slot), torch.cat([gate[4 * u:4 * u + 4], up[4 * u:4 * u + 4]]))
+        assert torch.equal(unit_rows(c, slot), bf(torch.cat([gate[8 * u:8 * u + 8], up[8 * u:8 * u + 8]])))
         slot += len(plan[c][2])
         if plan[c][3]:
             u = plan[c][3][-1]
             r, s = divmod(u, 4)
-            assert torch.equal(unit_rows(c, slot + len(plan[c][3]) - 1), down[8 * r:8 * r + 8, 1024 * s:1024 * s + 1024])
+            assert torch.equal(unit_rows(c, slot + len(plan[c][3]) - 1), bf(down[16 * r:16 * r + 16, 1024 * s:1024 * s + 1024]))
         slot += len(plan[c][3])
         u = plan[c][4][0]
-        assert torch.equal(unit_rows(c, slot), head[8 * u:8 * u + 8])
+        assert torch.equal(unit_rows(c, slot), bf(head[16 * u:16 * u + 16]))
     # zero padding of the head beyond row 8194
-    c = [c for c in range(G) if 1024 in plan[c][4]][0]
-    slot = nl * sum(len(plan[c][ph]) for ph in range(4)) + plan[c][4].index(1024)
+    c = [c for c in range(G) if 512 in plan[c][4]][0]
+    slot = nl * sum(len(plan[c][ph]) for ph in range(4)) + plan[c][4].index(512)
     rows = unit_rows(c, slot)
-    assert torch.equal(rows[:2], head[8192:8194]) and float(rows[2:].abs().max()) == 0.0
+    assert torch.equal(rows[:2], bf(head[8192:8194])) and float(rows[2:].abs().max()) == 0.0
 
 
 def test_rope_tables_match_oracle():
