@@ -840,6 +840,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   int par = 0;          // parity of the running step counter: red / ssq double buffer
   ln_fetch(gn, p.ln1, kq);
 #define T3_PROF() do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it) p.prof[prof_k++] = gtime_ns(); } while (0)
+// timeline build (-DT3_TIMELINE, tools/t3_timeline.py): thread 0 of EVERY CTA stamps prologue / consume / epilogue
+// end of every step at prof[1024 + c * 1024 + 4 * step + k].  Off by default: even the dead test costs ~5 %.
+#ifdef T3_TIMELINE
+#define T3_TL(k) do { if (p.prof && tid == 0 && (p.prof_it & 0x40000000) && it == (p.prof_it & 0xffff)) \
+                        p.prof[1024 + (size_t)c * 1024 + 4 * step + (k)] = gtime_ns(); } while (0)
+#else
+#define T3_TL(k) do {} while (0)
+#endif
 #define T3_SUB(k) do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5 && (ph == PH_QKV || ph == PH_GU)) \
                          p.prof[200 + (ph == PH_GU ? 8 : 0) + (k)] = gtime_ns(); } while (0)
 
@@ -888,6 +896,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
         ll_load8(x, base, stride, np, fl, active && (ph != PH_DOWN || ctl->plan_n[PH_DOWN] > 0), ctl, p.st);
       }
       T3_SUB(1);
+      T3_TL(0);
       // ---------- residual add + RMSNorm gain (the scale is applied in the epilogue) ----------
       if (ph == PH_QKV || ph == PH_GU || ph == PH_HEAD) {
 #pragma unroll
@@ -906,6 +915,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       const int n = ctl->plan_n[ph];
       consume_units(n, rp, Bf, red, ring, full, sm, warp, lane, ctl, p.st);
       T3_SUB(3);
+      T3_TL(1);
       cbar();
       T3_SUB(4);
       // ---------- epilogue: cross-warp sum, scale / SwiGLU, publish ----------
@@ -942,11 +952,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
         }
       }
       T3_SUB(5);
+      T3_TL(2);
       par ^= 1;
       T3_PROF();
       // ---------- RoPE, KV append, split-KV attention between the qkv and o_proj steps ----------
       if (ph == PH_QKV) {
         attn_phase<KVT>(p, it, l, pos0, scr, warp, lane, ctl);
+        T3_TL(3);
         T3_PROF();
       }
     }

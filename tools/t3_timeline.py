@@ -1,0 +1,46 @@
+"""All-CTA timeline of one decode iteration of the T3 megakernel: for every step, when each CTA finished its
+prologue (inputs staged), its weight units and its epilogue — separates hand-over latency from CTA skew.
+Needs a timeline build of the library: CBX_NVCC_EXTRA=-DT3_TIMELINE python -m chatterbox_b200.build --force"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from chatterbox_b200 import synthetic as S, _lib
+from chatterbox_b200.t3 import T3, T3Cond
+
+dev = torch.device("cuda:0")
+t3 = T3(S.make_state_dict("t3"), dev, max_pos=512)
+cond = T3Cond(**{k: v.to(dev) for k, v in S.t3_cond().items()})
+text = torch.cat([S.text_tokens(64)] * 2, 0).to(dev)
+kw = dict(max_new_tokens=256, do_sample=False, stop_on_eos=False, cfg_weight=0.5, temperature=0.8,
+          repetition_penalty=1.2, min_p=0.05, top_p=1.0)
+for _ in range(2):
+    t3.inference(t3_cond=cond, text_tokens=text, **kw)
+G = _lib.lib().cbx_t3_grid(0)
+it = 200
+st = torch.zeros(1024 + G * 1024, dtype=torch.int64, device=dev)
+_lib.check(t3._lib.cbx_t3_set_profile(t3._h, st.data_ptr(), it | 0x40000000))
+t3.inference(t3_cond=cond, text_tokens=text, **kw)
+_lib.check(t3._lib.cbx_t3_set_profile(t3._h, None, -1))
+tl = st[1024:].view(G, 256, 4).cpu().double() / 1e3          # [cta][step][prologue, consume, epilogue, attn] in us
+names = ["qkv", "oproj", "gateup", "down"]
+import statistics as stt
+rows = {n: [] for n in names}
+for step in range(4, 120):
+    ph = step & 3
+    pro, con, epi, att = (tl[:, step, k] for k in range(4))
+    prev_epi = tl[:, step - 1, 2] if ph != 1 else tl[:, step - 1, 3]     # producer finish (attention end before oproj)
+    prev_epi = prev_epi[prev_epi > 0]
+    act = epi > 0
+    rows[names[ph]].append(dict(
+        prod_skew=float(prev_epi.max() - prev_epi.median()),                 # slowest producer vs median producer
+        handover=float(pro[act].min() - prev_epi.max()),                     # last producer done -> first consumer staged
+        stage_spread=float(pro[act].max() - pro[act].min()),
+        frags_consume=float((con - pro)[act].median()),
+        consume_max=float((con - pro)[act].max()),
+        epilogue=float((epi - con)[act].median()),
+        step_total=float(epi[act].max() - prev_epi.max())))
+for n in names:
+    r = rows[n]
+    print(n, {k: round(stt.mean(x[k] for x in r), 2) for k in r[0]})
+e0 = tl[:, 4, 2]; e1 = tl[:, 116, 2]
+print("per-layer (steps 4..116):", float((e1.max() - e0.max()) / 28))
