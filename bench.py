@@ -214,6 +214,7 @@ def _config():
 # -------------------------------------------------------------------------------------------------
 def run_ours(args, rank: int, world: int, local_rank: int):
     import torch.distributed as dist
+    from chatterbox_b200 import dispatch as D
     from chatterbox_b200 import synthetic as S
     from chatterbox_b200.t3 import T3Cond
     from chatterbox_b200.tts import ChatterboxTTS, Conditionals
@@ -224,8 +225,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
-        if world > 1:
-            dist.barrier()
+        D.barrier(world)
         torch.cuda.synchronize()
 
     # one replica per rank, an independent utterance per rank (seeds differ), same shapes
@@ -298,10 +298,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     e2e_ms = e0.elapsed_time(e1)
     assert out.shape == (1, 480 * 2 * N_SPEECH) and out.device.type == "cpu"
 
-    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = t.tolist()
+    total_ms, e2e_ms = D.max_over_ranks([total_ms, e2e_ms], dev, world)
 
     if rank == 0:
         peak, peak_src = _peaks()
@@ -315,7 +312,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         L = 2 * (PROMPT_LEN + N_SPEECH)
         cfm_flop = 10 * 2 * L * (132.18e6 + 114688.0 * L)              # per estimator call x 10 steps
         hift_flop = 612.3e6 * 2 * N_SPEECH
-        line = {"metric": METRIC, "value": tokens / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        line = {"metric": METRIC, "value": D.whole_job_rate(N_SPEECH * args.steps, world, total_ms), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic", "config": _config(),
