@@ -19,7 +19,7 @@ class CbxT3Config(C.Structure):
 class CbxT3Weights(C.Structure):
     _fields_ = [("wstream", C.c_void_p), ("stride_units", C.c_int64), ("ln1", C.c_void_p), ("ln2", C.c_void_p),
                 ("final_norm", C.c_void_p), ("speech_emb", C.c_void_p), ("speech_pos_emb", C.c_void_p),
-                ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p)]
+                ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p), ("wplain", C.c_void_p)]
 
 
 class CbxSampleParams(C.Structure):

@@ -66,7 +66,7 @@ constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers
 
 struct GemmParams {
   CUtensorMap tmA, tmW;
-  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out, ksplit;
+  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out, ksplit, hilo;
   GemmEpi e;
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0,0) (debug aid)
 };
@@ -108,7 +108,8 @@ __device__ __forceinline__ unsigned long long gtimer() {
 // what it costs is instruction fetch over everything on its path — dispatching to the narrowest instantiation
 // (gemm_launch) keeps the common estimator epilogues short.
 enum : uint32_t { F_LN1 = 1, F_GELU = 2, F_ELU = 4, F_RESID = 8, F_RESID2 = 16, F_F32 = 32, F_BF16 = 64, F_LN2 = 128,
-                  F_ACT = 256 /* snake / leaky-relu on the bf16 output */, F_SHIFT = 512, F_ALL = 1023 };
+                  F_ACT = 256 /* snake / leaky-relu on the bf16 output */, F_SHIFT = 512, F_HILO = 1024, F_SWIGLU = 2048,
+                  F_ALL = 4095 };
 
 template <uint32_t FEAT>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_constant__ GemmParams p) {
@@ -156,6 +157,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   const bool has_resid2 = (FEAT & F_RESID2) && e.resid2 != nullptr;
   const bool has_f32 = (FEAT & F_F32) && e.out_f32 != nullptr, has_bf16 = (FEAT & F_BF16) && e.out_bf16 != nullptr;
   const bool has_ln2 = (FEAT & F_LN2) && e.out_ln != nullptr, has_snake = (FEAT & F_ACT) && e.snake_alpha != nullptr;
+  const bool has_hilo = (FEAT & F_HILO) && e.out_hilo != nullptr, has_swiglu = (FEAT & F_SWIGLU) && e.swiglu != 0;
   const float lrelu = (FEAT & F_ACT) ? e.lrelu : 0.f;
   const long long out_shift = (FEAT & F_SHIFT) ? e.out_shift : 0, out_limit = (FEAT & F_SHIFT) ? e.out_limit : 0;
   const int ngrp = p.n_tile / 4;
@@ -186,8 +188,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         const int tap = kb / kpb, kk = kb % kpb;
         uint8_t* sa = smem + s * STAGE_BYTES;
         mbar_arrive_expect_tx(&full[s], tx);
-        tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
-        tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kb * BK, n0, 0);
+        if (p.hilo) {      // plane `tap` of A against the same W panel
+          tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0, tap);
+          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kk * BK, n0, 0);
+        } else {
+          tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
+          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kb * BK, n0, 0);
+        }
       }
       GEMM_STAMP(2);
     }
@@ -368,6 +375,31 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
           for (int i = 0; i < 2; ++i) { x[rr][i][0] += rv[rr][i].x; x[rr][i][1] += rv[rr][i].y; x[rr][i][2] += rv[rr][i].z; x[rr][i][3] += rv[rr][i].w; }
       }
       if (threadIdx.x == 64 && it == 0) { if (x[0][0][0] == 123.456f) GEMM_STAMP(15); GEMM_STAMP(10); }
+      if (has_swiglu) {    // group 0 = gate columns, group 1 = the matching up columns (n_tile == 256)
+#pragma unroll
+        for (int rr = 0; rr < EPI_R; ++rr)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float gte = x[rr][0][k];
+            x[rr][0][k] = __fdividef(gte, 1.0f + __expf(-gte)) * x[rr][1][k];
+          }
+      }
+      if (has_hilo) {
+        const int ngroups = has_swiglu ? 1 : 2;
+        const int ncol0 = has_swiglu ? (n0 >> 1) : n0;
+#pragma unroll
+        for (int rr = 0; rr < EPI_R; ++rr)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            if (!okr[rr] || !g_ok[i] || i >= ngroups) continue;
+            uint32_t h0, l0, h1, l1;
+            split_hi_lo(x[rr][i][0], x[rr][i][1], h0, l0);
+            split_hi_lo(x[rr][i][2], x[rr][i][3], h1, l1);
+            __nv_bfloat16* dsth = e.out_hilo + grow[rr] * e.ld_hilo + ncol0 + gcol[i];
+            *reinterpret_cast<uint2*>(dsth) = make_uint2(h0, h1);
+            *reinterpret_cast<uint2*>(dsth + e.hilo_plane) = make_uint2(l0, l1);
+          }
+      }
       if (has_f32) {
 #pragma unroll
         for (int rr = 0; rr < EPI_R; ++rr)
@@ -467,7 +499,7 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
   CBX_CHECK(B == 1 || M_out == L, "gemm_make: M_out != L needs B == 1");
   CBX_CHECK(!(epi.ln_g || epi.out_ln) || n_tile == N, "gemm_make: row LayerNorm needs the whole row in one tile (N=%d)", N);
     d->B = B; d->L = L; d->N = N; d->K = K; d->taps = taps; d->n_tile = n_tile; d->epi = epi;
-  d->dil = dil; d->pad = pad; d->M_out = M_out;
+  d->dil = dil; d->pad = pad; d->M_out = M_out; d->hilo = 0;
   // few output tiles (the estimator's 2 x ceil(L / 128) row tiles): spread the K panels of each tile over a cluster
   const int tiles = B * ((M_out + BM - 1) / BM) * (N / n_tile), nkb_all = taps * (K / BK);
   d->ksplit = 1;
@@ -476,6 +508,25 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
     if (nkb_all >= sp && tiles * sp <= 148) { d->ksplit = sp; break; }
   if (make_tmap_bf16_3d(&d->tmA, A, K, L, B, lda, (uint64_t)lda * L, BK, BM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW, W, (uint64_t)taps * K, N, 1, (uint64_t)taps * K, (uint64_t)taps * K * N, BK, n_tile)) return CBX_ERR;
+  return CBX_OK;
+}
+
+int gemm_make_hilo(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int K,
+                   const GemmEpi& epi) {
+  CBX_CHECK(K % BK == 0 && K >= BK, "gemm_make_hilo: K=%d must be a multiple of 64", K);
+  int n_tile = 0;
+  for (int c = 256; c >= 16; c -= 16) if (N % c == 0) { n_tile = c; break; }
+  CBX_CHECK(n_tile > 0, "gemm_make_hilo: N=%d unsupported", N);
+  CBX_CHECK(!epi.swiglu || n_tile == 256, "gemm_make_hilo: SwiGLU pairs the halves of a 256-column tile (N=%d)", N);
+  CBX_CHECK(!epi.ln_g && !epi.out_ln, "gemm_make_hilo: no row LayerNorm on this path");
+  d->B = 1; d->L = M; d->N = N; d->K = K; d->taps = 2; d->n_tile = n_tile; d->epi = epi;
+  d->dil = 0; d->pad = 0; d->M_out = M; d->hilo = 1;
+  const int tiles = ((M + BM - 1) / BM) * (N / n_tile), nkb_all = 2 * (K / BK);
+  d->ksplit = 1;
+  for (int sp = 2; sp >= 2; sp >>= 1)
+    if (nkb_all >= sp && tiles * sp <= 148) { d->ksplit = sp; break; }
+  if (make_tmap_bf16_3d(&d->tmA, A, K, M, 2, lda, (uint64_t)plane, BK, BM)) return CBX_ERR;
+  if (make_tmap_bf16_3d(&d->tmW, W, K, N, 1, K, (uint64_t)K * N, BK, n_tile)) return CBX_ERR;
   return CBX_OK;
 }
 
@@ -495,6 +546,8 @@ uint32_t epi_features(const GemmEpi& e) {
   if (e.out_ln) f |= F_LN2;
   if (e.snake_alpha || e.lrelu != 0.f) f |= F_ACT;
   if (e.out_limit != 0 || e.out_shift != 0) f |= F_SHIFT;
+  if (e.out_hilo) f |= F_HILO;
+  if (e.swiglu) f |= F_SWIGLU;
   return f;
 }
 template <uint32_t FEAT>
@@ -519,13 +572,15 @@ constexpr uint32_t V_GELU = F_BF16 | F_GELU;                          // feed-fo
 constexpr uint32_t V_RESLN = F_RESID | F_F32 | F_LN2 | F_BF16;        // attention out / feed-forward down (+ next LayerNorm)
 constexpr uint32_t V_LN1 = F_LN1 | F_BF16;                            // resnet block1: conv + LayerNorm + Mish + time embedding
 constexpr uint32_t V_LN1R = F_LN1 | F_RESID | F_F32 | F_LN2 | F_BF16; // resnet block2 (+ skip path, + next LayerNorm)
+constexpr uint32_t V_T3_F32 = F_RESID | F_F32;                        // T3 prefill: q|k|v (plain fp32) / o_proj, down (+ residual)
+constexpr uint32_t V_T3_GU = F_SWIGLU | F_HILO;                       // T3 prefill: gate/up + SwiGLU -> hi/lo planes
 }  // namespace
 
 int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   GemmParams p;
   p.tmA = d.tmA; p.tmW = d.tmW;
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;
-  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit;
+  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit; p.hilo = d.hilo;
   p.tiles_l = (d.M_out + BM - 1) / BM;
   p.e = d.epi;
   p.dbg = g_gemm_dbg;
@@ -534,6 +589,8 @@ int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   const uint32_t f = epi_features(d.epi);
   auto within = [f](uint32_t v) { return (f & ~v) == 0; };
   if (within(V_PLAIN)) return launch_as<V_PLAIN>(p, grid, st);
+  if (within(V_T3_F32)) return launch_as<V_T3_F32>(p, grid, st);
+  if (within(V_T3_GU)) return launch_as<V_T3_GU>(p, grid, st);
   if (within(V_GELU)) return launch_as<V_GELU>(p, grid, st);
   if (within(V_RESLN)) return launch_as<V_RESLN>(p, grid, st);
   if (within(V_LN1)) return launch_as<V_LN1>(p, grid, st);

@@ -21,6 +21,11 @@ struct GemmEpi {
   __nv_bfloat16* out_bf16; int ld_bf16;
   const float* ln2_g; const float* ln2_b;  // LayerNorm of the final row value -> out_ln (needs out_f32, n_tile == N)
   __nv_bfloat16* out_ln; int ld_ln;
+  // T3 prefill: the value leaves as TWO bf16 planes (hi = bf16(v), lo = bf16(v - hi)) so the next GEMM keeps ~16
+  // mantissa bits of its activations; plane 1 starts hilo_plane elements after plane 0
+  __nv_bfloat16* out_hilo; int ld_hilo; long long hilo_plane;
+  int swiglu;                              // n_tile == 256 holds 128 gate then the 128 matching up columns:
+                                           // v = silu(gate) * up, 128 output columns per tile (Llama MLP)
 };
 
 // C[b][t][n] = sum_tap sum_k A[b][t + tap*dil - pad][k] * W[n][tap*K + k]   (rows outside [0, L) read as zero),
@@ -30,6 +35,7 @@ struct GemmDesc {
   CUtensorMap tmW;     // bf16 [N][taps*K], box {64, n_tile, 1}
   int B, L, N, K, taps, n_tile, dil, pad, M_out;
   int ksplit;          // CTAs per cluster sharing one output tile, each accumulating 1/ksplit of the K panels
+  int hilo;            // A is two planes (tensor-map dim 2): tap t reads plane t against the SAME W panel
   GemmEpi epi;
 };
 
@@ -38,6 +44,9 @@ int gemm_make(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16*
               const GemmEpi& epi);    // causal taps: dil 1, pad taps-1, M_out = L
 int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int B, int L, int N, int K, int taps,
                    int dil, int pad, int M_out, const GemmEpi& epi);
+// C[m][n] = sum_k (A_hi[m][k] + A_lo[m][k]) * W[n][k]: A = two bf16 planes [2][M][lda], plane stride in elements
+int gemm_make_hilo(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int K,
+                   const GemmEpi& epi);
 int gemm_launch(const GemmDesc& d, cudaStream_t st);
 
 }  // namespace cbx

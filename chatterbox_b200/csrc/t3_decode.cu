@@ -29,10 +29,12 @@
 // Prefill runs the same kernel one position per weight pass (mode 0).
 #include "common.cuh"
 #include "t3_plan.h"
+#include "t3_prefill.h"
 #include "../../include/cbx.h"
 
 #include <cooperative_groups.h>
 #include <math.h>
+#include <stdlib.h>
 #include <stdarg.h>
 
 namespace {
@@ -997,6 +999,7 @@ struct cbx_t3 {
   int B;                // rows of the current utterance
   long long launches;
   unsigned long long* prof; int prof_it;
+  void* prefill_ws;     // workspace of the GEMM prefill (NULL without plain weights)
 };
 
 extern "C" int cbx_t3_grid(int device) {
@@ -1045,6 +1048,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   const size_t o_ll = take(LL_WORDS * 8);
   const size_t o_logits = take(sizeof(float) * 2 * T3_VOCAB);
   const size_t o_st = take(256), o_seen = take(VOCAB_PAD);
+  const size_t o_ws = w->wplain ? take(cbx::t3_prefill_workspace_bytes(cfg->max_pos)) : 0;
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_t3_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -1065,6 +1069,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   p.logits = reinterpret_cast<float*>(s + o_logits);
   p.st = reinterpret_cast<T3State*>(s + o_st);
   p.seen = s + o_seen;
+  h->prefill_ws = w->wplain ? s + o_ws : nullptr;
   int rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16>);
   if (!rc) rc = t3_prepare_kernel(t3_megakernel<float>);
   if (rc) { cudaFree(h->slab); delete h; return CBX_ERR; }
@@ -1100,6 +1105,18 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
   CBX_CUDA(cudaMemsetAsync(p.seen, 0, VOCAB_PAD, st));
   CBX_CUDA(cudaMemsetAsync(p.seen + 6561, 1, 1, st));
   p.mode = 0; p.B = B; p.embeds = embeds; p.P = P;
+  static const bool force_mega = [] { const char* v = getenv("CBX_T3_PREFILL"); return v && v[0] == 'm'; }();
+  if (h->prefill_ws && !force_mega) {
+    // the prompt through each weight matrix once (tcgen05 GEMMs); leaves the slab, the position counter and the
+    // pending logits as the megakernel's own prefill mode would
+    cbx::T3PrefillArgs a;
+    a.embeds = embeds; a.B = B; a.P = P; a.n_layers = h->cfg.n_layers; a.max_pos = h->cfg.max_pos; a.kv_fp32 = h->cfg.kv_fp32;
+    a.wplain = h->w.wplain; a.ln1 = p.ln1; a.ln2 = p.ln2; a.final_norm = p.final_norm;
+    a.rope_cos = p.rope_cos; a.rope_sin = p.rope_sin; a.kcache = p.kcache; a.vcache = p.vcache;
+    a.logits = p.logits; a.state = reinterpret_cast<int*>(p.st); a.workspace = h->prefill_ws;
+    h->launches += 1 + h->cfg.n_layers * 8 + 2;
+    return cbx::t3_prefill_gemm(a, st);
+  }
   return t3_launch(h, p, st);
 }
 

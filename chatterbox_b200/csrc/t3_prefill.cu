@@ -1,0 +1,256 @@
+// T3 prompt prefill as batched GEMMs on the tcgen05 path (reference: the first `patched_model(inputs_embeds=...)`
+// call of T3.inference, src/chatterbox/models/t3/t3.py:307-316 -> HF LlamaModel.forward over the whole prompt).
+//
+// The decode megakernel (t3_decode.cu) is a weight-streaming GEMV: run over a P-position prompt it streams the
+// 1 GB of weights P times.  Here the prompt's 2 P rows (CFG pair) go through each matrix once:
+//   x (fp32 residual stream, [B*P][1024])
+//   -> k_rms_hilo: RMSNorm gain * x * rstd, written as TWO bf16 planes (hi, lo = bf16(v - hi))
+//   -> q|k|v GEMM (A = hi plane + lo plane against the same bf16 weights: ~16 mantissa bits, fp32 accumulate in TMEM)
+//   -> k_rope_kv: llama3 RoPE on q, k; K / V appended to the decode kernel's KV slab (same rounding as decode)
+//   -> k_attn_prefill: causal softmax(q k^T / 8) v in fp32 on CUDA cores (42 MFLOP per layer at P = 102)
+//   -> o_proj GEMM + residual, RMSNorm, gate/up GEMM with the SwiGLU epilogue (hi/lo planes out), down GEMM + residual
+//   -> final RMSNorm + speech_head GEMV of the LAST position only (t3_hf_backend.py:100-103) -> logits[2][8194]
+// so the decode launch that follows finds the slab, the position counter and the pending logits exactly as the
+// megakernel's own prefill mode leaves them.
+#include "t3_prefill.h"
+#include "s3_gemm.cuh"
+#include "../../include/cbx.h"
+
+namespace cbx {
+namespace {
+
+constexpr int H = 1024, NH = 16, HD = 64, INTER = 4096, VOCAB = 8194;
+constexpr float RMS_EPS = 1e-5f;
+
+// one row per CTA (256 threads x 4 values): out planes [2][rows][1024] = hi / lo of gain * x * rsqrt(mean(x^2) + eps)
+__global__ void __launch_bounds__(256) k_rms_hilo(const float* __restrict__ x, const float* __restrict__ gain,
+                                                  __nv_bfloat16* __restrict__ out, long long plane) {
+  __shared__ float red[8];
+  const int row = blockIdx.x, t = threadIdx.x;
+  const float4 v = *reinterpret_cast<const float4*>(x + (size_t)row * H + t * 4);
+  float s = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  s = warp_sum(s);
+  if ((t & 31) == 0) red[t >> 5] = s;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) tot += red[w];
+  const float sc = rsqrtf(tot * (1.0f / H) + RMS_EPS);
+  const float4 g = __ldg(reinterpret_cast<const float4*>(gain + t * 4));
+  uint32_t h0, l0, h1, l1;
+  split_hi_lo(g.x * (v.x * sc), g.y * (v.y * sc), h0, l0);
+  split_hi_lo(g.z * (v.z * sc), g.w * (v.w * sc), h1, l1);
+  __nv_bfloat16* d = out + (size_t)row * H + t * 4;
+  *reinterpret_cast<uint2*>(d) = make_uint2(h0, h1);
+  *reinterpret_cast<uint2*>(d + plane) = make_uint2(l0, l1);
+}
+
+template <typename KVT> struct KVS;
+template <> struct KVS<__nv_bfloat16> {
+  static __device__ __forceinline__ float round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+template <> struct KVS<float> {
+  static __device__ __forceinline__ float round(float v) { return v; }
+  static __device__ __forceinline__ void store(float* p, float v) { *p = v; }
+};
+
+// grid (P, B), 1024 threads = (head, d): RoPE (rotate_half pairing d <-> d ^ 32) on q and k in place, q pre-scaled by
+// 1/8; K / V rounded to the slab's element type, appended at position pos0 + p and written back so the attention
+// below sees exactly what later decode steps will read from the slab.
+template <typename KVT>
+__global__ void __launch_bounds__(1024) k_rope_kv(float* __restrict__ qkv, int P, int pos0, const float* __restrict__ rope_cos,
+                                                  const float* __restrict__ rope_sin, KVT* __restrict__ kc, KVT* __restrict__ vc,
+                                                  int layer, int max_pos) {
+  const int p = blockIdx.x, b = blockIdx.y, head = threadIdx.x >> 6, d = threadIdx.x & 63;
+  float* row = qkv + ((size_t)b * P + p) * 3072 + head * 64;
+  const float q = row[d], qo = row[d ^ 32], k = row[1024 + d], ko = row[1024 + (d ^ 32)], v = row[2048 + d];
+  const float cs = __ldg(rope_cos + (size_t)(pos0 + p) * 32 + (d & 31)), sn = __ldg(rope_sin + (size_t)(pos0 + p) * 32 + (d & 31));
+  const float qr = (q * cs + (d < 32 ? -qo : qo) * sn) * 0.125f;
+  const float kr = KVS<KVT>::round(k * cs + (d < 32 ? -ko : ko) * sn);
+  const float vr = KVS<KVT>::round(v);
+  __syncthreads();            // every thread has read its partner before anyone overwrites
+  row[d] = qr; row[1024 + d] = kr; row[2048 + d] = vr;
+  const size_t off = (((size_t)(layer * 2 + b) * NH + head) * max_pos + (pos0 + p)) * HD + d;
+  KVS<KVT>::store(kc + off, kr);
+  KVS<KVT>::store(vc + off, vr);
+}
+
+// Causal attention of the prompt over itself, fp32.  grid (ceil(P / 32), NH, B), 256 threads = 8 warps x 4 queries.
+// Keys are walked in tiles of 64 through shared memory (rows padded to 65 floats); a lane scores keys l and l + 32,
+// the warp keeps an online softmax per query, then lane l accumulates output dims l and l + 32.  Output: hi / lo planes.
+constexpr int QT = 32, KT = 64, KPAD = 65;
+__global__ void __launch_bounds__(256) k_attn_prefill(const float* __restrict__ qkv, int P, __nv_bfloat16* __restrict__ out,
+                                                      long long plane) {
+  __shared__ float Ks[KT * KPAD], Vs[KT * KPAD], Qs[QT * 64], Ps[8][KT];
+  const int q0 = blockIdx.x * QT, head = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float* base = qkv + (size_t)b * P * 3072 + head * 64;
+  for (int i = tid; i < QT * 64; i += 256) {
+    const int qi = q0 + (i >> 6);
+    Qs[i] = qi < P ? base[(size_t)qi * 3072 + (i & 63)] : 0.f;
+  }
+  float m[4], l[4], o0[4], o1[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { m[j] = -INFINITY; l[j] = 0.f; o0[j] = 0.f; o1[j] = 0.f; }
+  const int kmax = min(P, q0 + QT);        // causal: no key beyond the last query of the tile
+  for (int k0 = 0; k0 < kmax; k0 += KT) {
+    __syncthreads();
+    for (int i = tid; i < KT * 64; i += 256) {
+      const int kk = k0 + (i >> 6), d = i & 63;
+      const bool ok = kk < kmax;
+      Ks[(i >> 6) * KPAD + d] = ok ? base[(size_t)kk * 3072 + 1024 + d] : 0.f;
+      Vs[(i >> 6) * KPAD + d] = ok ? base[(size_t)kk * 3072 + 2048 + d] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int qi = q0 + warp * 4 + j;
+      if (qi >= P) continue;               // warp-uniform
+      const float* qv = Qs + (warp * 4 + j) * 64;
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll 16
+      for (int d = 0; d < 64; ++d) {
+        const float qd = qv[d];
+        s0 += qd * Ks[lane * KPAD + d];
+        s1 += qd * Ks[(lane + 32) * KPAD + d];
+      }
+      if (k0 + lane > qi) s0 = -INFINITY;
+      if (k0 + lane + 32 > qi) s1 = -INFINITY;
+      float mx = fmaxf(s0, s1);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      const float mn = fmaxf(m[j], mx);    // finite: key k0 <= qi is always present in the first tile
+      const float corr = __expf(m[j] - mn);
+      const float p0 = __expf(s0 - mn), p1 = __expf(s1 - mn);
+      float ps = warp_sum(p0 + p1);
+      l[j] = l[j] * corr + ps;
+      m[j] = mn;
+      __syncwarp();
+      Ps[warp][lane] = p0; Ps[warp][lane + 32] = p1;
+      __syncwarp();
+      float a0 = o0[j] * corr, a1 = o1[j] * corr;
+#pragma unroll 16
+      for (int kk = 0; kk < KT; ++kk) {
+        const float pk = Ps[warp][kk];
+        a0 += pk * Vs[kk * KPAD + lane];
+        a1 += pk * Vs[kk * KPAD + lane + 32];
+      }
+      o0[j] = a0; o1[j] = a1;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int qi = q0 + warp * 4 + j;
+    if (qi >= P) continue;
+    const float inv = 1.0f / l[j];
+    const float v0 = o0[j] * inv, v1 = o1[j] * inv;
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(v0), h1 = __float2bfloat16_rn(v1);
+    __nv_bfloat16* d = out + ((size_t)b * P + qi) * H + head * 64;
+    d[lane] = h0; d[lane + 32] = h1;
+    d[plane + lane] = __float2bfloat16_rn(v0 - __bfloat162float(h0));
+    d[plane + lane + 32] = __float2bfloat16_rn(v1 - __bfloat162float(h1));
+  }
+}
+
+// final RMSNorm of the last position of each CFG row + speech_head GEMV: one warp per vocabulary row
+__global__ void __launch_bounds__(256) k_head(const float* __restrict__ x, int P, int B, const float* __restrict__ gain,
+                                              const __nv_bfloat16* __restrict__ w, float* __restrict__ logits) {
+  __shared__ float xs[2][H];
+  __shared__ float red[2][8];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int b = 0; b < B; ++b) {
+    const float4 v = *reinterpret_cast<const float4*>(x + ((size_t)b * P + (P - 1)) * H + tid * 4);
+    float s = warp_sum(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w);
+    if (lane == 0) red[b][warp] = s;
+    *reinterpret_cast<float4*>(&xs[b][tid * 4]) = v;
+  }
+  __syncthreads();
+  for (int b = 0; b < B; ++b) {
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) tot += red[b][i];
+    const float sc = rsqrtf(tot * (1.0f / H) + RMS_EPS);
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gain + tid * 4));
+    float4 v = *reinterpret_cast<float4*>(&xs[b][tid * 4]);
+    v.x = g.x * (v.x * sc); v.y = g.y * (v.y * sc); v.z = g.z * (v.z * sc); v.w = g.w * (v.w * sc);
+    *reinterpret_cast<float4*>(&xs[b][tid * 4]) = v;
+  }
+  __syncthreads();
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= VOCAB) return;
+  const __nv_bfloat16* wr = w + (size_t)row * H;
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int k = i * 256 + lane * 8;
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(wr + k));
+    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h2[e]);
+      a0 += f.x * xs[0][k + 2 * e] + f.y * xs[0][k + 2 * e + 1];
+      if (B == 2) a1 += f.x * xs[1][k + 2 * e] + f.y * xs[1][k + 2 * e + 1];
+    }
+  }
+  a0 = warp_sum(a0); a1 = warp_sum(a1);
+  if (lane == 0) {
+    logits[row] = a0;
+    if (B == 2) logits[VOCAB + row] = a1;
+  }
+}
+
+__global__ void k_set_pos(int* st, int pos) { st[0] = pos; st[1] = 0; st[2] = 0; }
+
+}  // namespace
+
+size_t t3_prefill_workspace_bytes(int max_pos) {
+  const size_t rows = 2 * (size_t)max_pos;
+  return rows * H * 4 + rows * 3072 * 4 + 2 * rows * H * 2 + 2 * rows * INTER * 2 + 1024;
+}
+
+int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
+  const int rows = a.B * a.P;
+  const size_t maxrows = 2 * (size_t)a.max_pos;
+  uint8_t* ws = static_cast<uint8_t*>(a.workspace);
+  float* x = reinterpret_cast<float*>(ws);
+  float* qkv = reinterpret_cast<float*>(ws + maxrows * H * 4);
+  __nv_bfloat16* hl = reinterpret_cast<__nv_bfloat16*>(ws + maxrows * H * 4 + maxrows * 3072 * 4);
+  __nv_bfloat16* act = hl + 2 * maxrows * H;
+  const long long hl_plane = (long long)rows * H, act_plane = (long long)rows * INTER;
+  CBX_CUDA(cudaMemcpyAsync(x, a.embeds, (size_t)rows * H * 4, cudaMemcpyDeviceToDevice, st));
+  const __nv_bfloat16* wp = static_cast<const __nv_bfloat16*>(a.wplain);
+  const size_t per_layer = (size_t)3072 * H + (size_t)H * H + (size_t)8192 * H + (size_t)H * INTER;
+  for (int l = 0; l < a.n_layers; ++l) {
+    const __nv_bfloat16* wqkv = wp + l * per_layer;
+    const __nv_bfloat16* wo = wqkv + (size_t)3072 * H;
+    const __nv_bfloat16* wgu = wo + (size_t)H * H;
+    const __nv_bfloat16* wdn = wgu + (size_t)8192 * H;
+    GemmDesc d;
+    GemmEpi e;
+    k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln1 + (size_t)l * H, hl, hl_plane);
+    e = GemmEpi{}; e.out_f32 = qkv; e.ld_f32 = 3072;
+    if (gemm_make_hilo(&d, hl, H, hl_plane, wqkv, rows, 3072, H, e) || gemm_launch(d, st)) return CBX_ERR;
+    if (a.kv_fp32)
+      k_rope_kv<float><<<dim3(a.P, a.B), 1024, 0, st>>>(qkv, a.P, 0, a.rope_cos, a.rope_sin, static_cast<float*>(a.kcache),
+                                                        static_cast<float*>(a.vcache), l, a.max_pos);
+    else
+      k_rope_kv<__nv_bfloat16><<<dim3(a.P, a.B), 1024, 0, st>>>(qkv, a.P, 0, a.rope_cos, a.rope_sin,
+                                                               static_cast<__nv_bfloat16*>(a.kcache),
+                                                               static_cast<__nv_bfloat16*>(a.vcache), l, a.max_pos);
+    k_attn_prefill<<<dim3((a.P + QT - 1) / QT, NH, a.B), 256, 0, st>>>(qkv, a.P, hl, hl_plane);
+    e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
+    if (gemm_make_hilo(&d, hl, H, hl_plane, wo, rows, H, H, e) || gemm_launch(d, st)) return CBX_ERR;
+    k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln2 + (size_t)l * H, hl, hl_plane);
+    e = GemmEpi{}; e.swiglu = 1; e.out_hilo = act; e.ld_hilo = INTER; e.hilo_plane = act_plane;
+    if (gemm_make_hilo(&d, hl, H, hl_plane, wgu, rows, 8192, H, e) || gemm_launch(d, st)) return CBX_ERR;
+    e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
+    if (gemm_make_hilo(&d, act, INTER, act_plane, wdn, rows, H, INTER, e) || gemm_launch(d, st)) return CBX_ERR;
+  }
+  k_head<<<(VOCAB + 7) / 8, 256, 0, st>>>(x, a.P, a.B, a.final_norm, wp + a.n_layers * per_layer, a.logits);
+  k_set_pos<<<1, 1, 0, st>>>(a.state, a.P);
+  CBX_CUDA(cudaGetLastError());
+  return CBX_OK;
+}
+
+}  // namespace cbx

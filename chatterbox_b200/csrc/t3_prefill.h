@@ -1,0 +1,23 @@
+// Host interface of the GEMM-based T3 prompt prefill (csrc/t3_prefill.cu), called by cbx_t3_prefill.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+namespace cbx {
+
+struct T3PrefillArgs {
+  const float* embeds;       // [B][P][1024] fp32 (t3.py:228-252)
+  int B, P, n_layers, max_pos, kv_fp32;
+  const void* wplain;        // bf16, per layer [q|k|v 3072x1024][o 1024x1024][gate/up 8192x1024, 128 gate + 128 up rows per
+                             // 256-row tile][down 1024x4096], then speech_head [8194][1024]
+  const float *ln1, *ln2, *final_norm, *rope_cos, *rope_sin;
+  void *kcache, *vcache;     // the decode kernel's slab [layer][2][16][max_pos][64]
+  float* logits;             // [2][8194] pending logits of the last prompt position
+  int* state;                // {pos, n_gen, stop, err}
+  void* workspace;           // t3_prefill_workspace_bytes(max_pos)
+};
+
+size_t t3_prefill_workspace_bytes(int max_pos);
+int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st);
+
+}  // namespace cbx

@@ -59,6 +59,24 @@ def head_units(sd: Dict[str, torch.Tensor], dev) -> torch.Tensor:
     return _frag_order(w.reshape(513, 16, H)).to(torch.bfloat16)
 
 
+def plain_weights(sd: Dict[str, torch.Tensor], dev, n_layers: int) -> torch.Tensor:
+    """Row-major bf16 copies for the GEMM prefill (csrc/t3_prefill.cu): per layer q|k|v, o, gate/up interleaved in
+    128-row groups (tile t = gate rows [128t, 128t+128) then up rows [128t, 128t+128): the SwiGLU epilogue pairs the two
+    halves of a 256-column tile), down; then speech_head.  One flat tensor."""
+    parts = []
+    for i in range(n_layers):
+        p = f"tfmr.layers.{i}."
+        g = lambda n: sd[p + n].to(dev, torch.float32)
+        parts.append(torch.cat([g("self_attn.q_proj.weight"), g("self_attn.k_proj.weight"), g("self_attn.v_proj.weight")], 0))
+        parts.append(g("self_attn.o_proj.weight"))
+        gate = g("mlp.gate_proj.weight").reshape(32, 128, H)
+        up = g("mlp.up_proj.weight").reshape(32, 128, H)
+        parts.append(torch.cat([gate, up], 1).reshape(8192, H))
+        parts.append(g("mlp.down_proj.weight"))
+    parts.append(sd["speech_head.weight"].to(dev, torch.float32))
+    return torch.cat([t.reshape(-1).to(torch.bfloat16) for t in parts])
+
+
 def rope_tables(max_pos: int, dev) -> (torch.Tensor, torch.Tensor):
     """cos/sin [max_pos][32] fp32 of the llama3-scaled RoPE the reference configures
     (llama_configs.py:22-30: theta 5e5, factor 8, low/high 1/4, original ctx 8192), computed in
@@ -90,13 +108,15 @@ class T3Packed:
     rope_cos: torch.Tensor
     rope_sin: torch.Tensor
     max_pos: int
+    wplain: torch.Tensor = None   # plain matrices for the GEMM prefill (None: prefill through the decode kernel)
 
     def weight_bytes_per_step(self) -> int:
         """Algorithmic weight bytes one decode step streams (every unit once + norms)."""
         return (self.n_layers * LAYER_UNITS + PHASE_UNITS[4]) * UNIT_ELEMS * 2 + (2 * self.n_layers + 1) * H * 4
 
 
-def pack_t3(sd: Dict[str, torch.Tensor], G: int, device, max_pos: int, n_layers: int = 30) -> T3Packed:
+def pack_t3(sd: Dict[str, torch.Tensor], G: int, device, max_pos: int, n_layers: int = 30,
+            gemm_prefill: bool = True) -> T3Packed:
     dev = torch.device(device)
     plan = plan_lists(G)
     offs = [0, 192, 192 + 64, 192 + 64 + 512]
@@ -123,4 +143,5 @@ def pack_t3(sd: Dict[str, torch.Tensor], G: int, device, max_pos: int, n_layers:
     return T3Packed(G=G, n_layers=n_layers, stride_units=stride, wstream=stream, ln1=ln1.contiguous(),
                     ln2=ln2.contiguous(), final_norm=f32(sd["tfmr.norm.weight"]),
                     speech_emb=f32(sd["speech_emb.weight"]), speech_pos_emb=f32(sd["speech_pos_emb.emb.weight"]),
-                    rope_cos=cos, rope_sin=sin, max_pos=max_pos)
+                    rope_cos=cos, rope_sin=sin, max_pos=max_pos,
+                    wplain=plain_weights(sd, dev, n_layers) if gemm_prefill else None)

@@ -71,7 +71,7 @@ def _ensure_BOT_EOT(text_tokens: torch.Tensor, hp):
 
 class T3:
     def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", *, max_pos: int = 4096,
-                 kv_fp32: bool = False, n_layers: int = 30, hp=T3Config()):
+                 kv_fp32: bool = False, n_layers: int = 30, hp=T3Config(), gemm_prefill: bool = True):
         if not torch.cuda.is_available():
             raise _lib.CbxError("chatterbox_b200.T3 needs a CUDA device (no CPU fallback)")
         self.hp = hp
@@ -83,7 +83,7 @@ class T3:
         G = self._lib.cbx_t3_grid(self.device.index)
         if G <= 0:
             _lib.check(1)
-        self.packed: T3Packed = pack_t3(state_dict, G, self.device, max_pos, n_layers)
+        self.packed: T3Packed = pack_t3(state_dict, G, self.device, max_pos, n_layers, gemm_prefill=gemm_prefill)
         # front-end parameters (reference key names), fp32 on the device
         keep = ("cond_enc.", "text_emb.", "text_pos_emb.")
         self.fe = {k: v.to(self.device, torch.float32) for k, v in state_dict.items() if k.startswith(keep)}
@@ -93,7 +93,8 @@ class T3:
         cfg = _lib.CbxT3Config(self.device.index, n_layers, max_pos, 1 if kv_fp32 else 0)
         w = _lib.CbxT3Weights(p.wstream.data_ptr(), p.stride_units, p.ln1.data_ptr(), p.ln2.data_ptr(),
                               p.final_norm.data_ptr(), p.speech_emb.data_ptr(), p.speech_pos_emb.data_ptr(),
-                              p.rope_cos.data_ptr(), p.rope_sin.data_ptr())
+                              p.rope_cos.data_ptr(), p.rope_sin.data_ptr(),
+                              p.wplain.data_ptr() if p.wplain is not None else None)
         h = C.c_void_p()
         _lib.check(self._lib.cbx_t3_create(C.byref(cfg), C.byref(w), C.byref(h)))
         self._h = h

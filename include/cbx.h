@@ -36,8 +36,8 @@ typedef struct CbxT3Config {
 } CbxT3Config;
 
 typedef struct CbxT3Weights {          /* device pointers, caller-owned, must outlive the handle */
-  const void* wstream;                 /* bf16 per-CTA weight streams packed by the plan below: [G][stride_units][8192] */
-  int64_t stride_units;                /* units (16 KB) between consecutive CTA streams */
+  const void* wstream;                 /* bf16 per-CTA weight streams packed by the plan below: [G][stride_units][16384] */
+  int64_t stride_units;                /* units (32 KB) between consecutive CTA streams */
   const float* ln1;                    /* [n_layers][1024] input_layernorm.weight */
   const float* ln2;                    /* [n_layers][1024] post_attention_layernorm.weight */
   const float* final_norm;             /* [1024] tfmr.norm.weight */
@@ -45,6 +45,11 @@ typedef struct CbxT3Weights {          /* device pointers, caller-owned, must ou
   const float* speech_pos_emb;         /* [4100][1024] speech_pos_emb.emb.weight (t3.py:60) */
   const float* rope_cos;               /* [max_pos][32] cos of llama3-scaled RoPE angles, fp32 */
   const float* rope_sin;               /* [max_pos][32] */
+  const void* wplain;                  /* optional (may be NULL): the same weights as plain bf16 row-major matrices for the
+                                          GEMM prefill — per layer [q|k|v 3072x1024][o 1024x1024][gate/up 8192x1024 with 128
+                                          gate rows then the 128 matching up rows per 256-row tile][down 1024x4096], then
+                                          speech_head [8194][1024].  NULL: the prompt is prefilled by the decode kernel,
+                                          one position per weight pass */
 } CbxT3Weights;
 
 typedef struct CbxSampleParams {       /* the generate() knobs of tts.py:208-218 */

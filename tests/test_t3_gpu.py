@@ -169,3 +169,21 @@ def test_sampler_respects_filters_and_distribution():
         f = draws.count(idx) / N
         sigma = (pr * (1 - pr) / N) ** 0.5
         assert abs(f - pr) < 5 * sigma + 0.01, (idx, f, pr)
+
+
+@pytest.mark.parametrize("n_text", [3, 40])
+def test_gemm_prefill_matches_the_position_by_position_prefill(n_text):
+    """The tcgen05 GEMM prefill and the decode kernel's own prefill mode fill the same KV slab and pending logits:
+    teacher-forced logits of the following decode steps agree to fp32 rounding (fp32 slab), for a prompt shorter and
+    longer than one 128-row GEMM tile."""
+    from chatterbox_b200.t3 import T3
+    sd = S.make_state_dict("t3", n_layers=2)
+    tt = torch.cat([S.text_tokens(n_text)] * 2, 0)
+    forced = torch.randint(0, 6561, (1, 4), generator=torch.Generator().manual_seed(7))
+    outs = []
+    for gemm in (True, False):
+        m = T3(sd, "cuda", max_pos=160, kv_fp32=True, n_layers=2, gemm_prefill=gemm)
+        m.inference(t3_cond=_cond(), text_tokens=tt, max_new_tokens=4, forced_tokens=forced, return_logits=True,
+                    do_sample=False, **PARAMS)
+        outs.append(m.last_logits.cpu())
+    assert (outs[0] - outs[1]).abs().max() < 2e-4
