@@ -39,7 +39,7 @@
 
 namespace {
 
-constexpr int NSLOT = 5;                  // ring depth (32 KB units)
+constexpr int NSLOT = 4;                  // ring depth (32 KB units)
 constexpr int NCONS_WARPS = 8;
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
 constexpr int NTHREADS = NCONS;
@@ -281,8 +281,8 @@ __device__ __forceinline__ float rms_scale(const float* ssq, int b) {
 }
 // 8 norm gains of this lane's k range, fetched one phase ahead into registers
 __device__ __forceinline__ void ln_fetch(float (&g)[8], const float* __restrict__ lnw, int k) {
-  const float4 a = __ldg(reinterpret_cast<const float4*>(lnw + k));
-  const float4 b = __ldg(reinterpret_cast<const float4*>(lnw + k + 4));
+  const float4 a = __ldcg(reinterpret_cast<const float4*>(lnw + k));      // L2 only: keep the small L1 for the stack
+  const float4 b = __ldcg(reinterpret_cast<const float4*>(lnw + k + 4));
   g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
 }
 
