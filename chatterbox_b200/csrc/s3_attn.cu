@@ -2,7 +2,7 @@
 // (reference: matcha/transformer.py:196-204 -> diffusers 0.29.0 Attention/AttnProcessor2_0: 8 heads x 64,
 // scale 1/8, key-padding bias only — all-zero for one un-padded utterance, decoder.py:269-270).
 // Flash-attention structure: a CTA owns 64 query rows of one (batch, head); K/V tiles of 64 keys are
-// double-buffered in shared memory with cp.async; S = QK^T and O += PV run on mma.sync m16n8k16 bf16
+// stream through a 4-deep cp.async pipeline in shared memory (one tile of lookahead left the loop waiting on L2); S = QK^T and O += PV run on mma.sync m16n8k16 bf16
 // with fp32 accumulation and an fp32 online softmax.  (Round-1 kernel: the legacy tensor-core path;
 // the tcgen05 version is listed in DESIGN.md as the next step for this stage.)
 #include "common.cuh"
@@ -11,6 +11,9 @@ namespace cbx {
 namespace {
 
 constexpr int AT_BM = 64, AT_BN = 64, AT_D = 64, AT_LD = 72;   // padded smem row stride (elements)
+constexpr int AT_NST = 4;                                       // K/V pipeline depth
+constexpr int AT_TILE = AT_BN * AT_LD;                          // elements of one staged tile
+constexpr int AT_SMEM = (1 + 2 * AT_NST) * AT_TILE * 2;         // Q + NST x (K, V), bytes
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool valid) {
   const int sz = valid ? 16 : 0;
@@ -28,9 +31,10 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
 // qkv: bf16 [B][L][ld_qkv] with q at column 0, k at 512, v at 1024 (+ head*64); out: bf16 [B][L][512]
 __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
                                                       int L, int ld_qkv) {
-  __shared__ __align__(16) __nv_bfloat16 sQ[AT_BM * AT_LD];
-  __shared__ __align__(16) __nv_bfloat16 sK[2][AT_BN * AT_LD];
-  __shared__ __align__(16) __nv_bfloat16 sV[2][AT_BN * AT_LD];
+  extern __shared__ __align__(16) __nv_bfloat16 at_smem[];
+  __nv_bfloat16* sQ = at_smem;
+  __nv_bfloat16* sKb = at_smem + AT_TILE;                 // [NST][tile]
+  __nv_bfloat16* sVb = at_smem + (1 + AT_NST) * AT_TILE;  // [NST][tile]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * AT_BM, head = blockIdx.y, b = blockIdx.z;
   const __nv_bfloat16* base = qkv + (size_t)b * L * ld_qkv + head * AT_D;
@@ -45,9 +49,14 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
   };
   const int ntiles = (L + AT_BN - 1) / AT_BN;
   load_tile(sQ, 0, q0);
-  load_tile(sK[0], 512, 0);
-  load_tile(sV[0], 1024, 0);
-  asm volatile("cp.async.commit_group;" ::: "memory");
+#pragma unroll
+  for (int t = 0; t < AT_NST - 1; ++t) {
+    if (t < ntiles) {
+      load_tile(sKb + t * AT_TILE, 512, t * AT_BN);
+      load_tile(sVb + t * AT_TILE, 1024, t * AT_BN);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");      // one group per tile (possibly empty)
+  }
 
   float o[8][4], m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
 #pragma unroll
@@ -56,14 +65,16 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
   const float sc = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
 
   for (int kt = 0; kt < ntiles; ++kt) {
-    const int buf = kt & 1;
-    if (kt + 1 < ntiles) {
-      load_tile(sK[buf ^ 1], 512, (kt + 1) * AT_BN);
-      load_tile(sV[buf ^ 1], 1024, (kt + 1) * AT_BN);
+    const __nv_bfloat16* sK = sKb + (kt % AT_NST) * AT_TILE;
+    const __nv_bfloat16* sV = sVb + (kt % AT_NST) * AT_TILE;
+    {
+      const int nt = kt + AT_NST - 1;       // refills the buffer tile kt - 1 used (freed by the barrier ending that iteration)
+      if (nt < ntiles) {
+        load_tile(sKb + (nt % AT_NST) * AT_TILE, 512, nt * AT_BN);
+        load_tile(sVb + (nt % AT_NST) * AT_TILE, 1024, nt * AT_BN);
+      }
       asm volatile("cp.async.commit_group;" ::: "memory");
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    } else {
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      asm volatile("cp.async.wait_group %0;" ::"n"(AT_NST - 1) : "memory");      // tile kt (and Q) have landed
     }
     __syncthreads();
     if (kt == 0) {
@@ -80,7 +91,7 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
 #pragma unroll
       for (int np = 0; np < 4; ++np) {     // pairs of 8-key tiles
         uint32_t kb[4];
-        ldsm_x4(kb, sK[buf] + ((np * 2 + (lane >> 4)) * 8 + (lane & 7)) * AT_LD + ks * 16 + ((lane >> 3) & 1) * 8);
+        ldsm_x4(kb, sK + ((np * 2 + (lane >> 4)) * 8 + (lane & 7)) * AT_LD + ks * 16 + ((lane >> 3) & 1) * 8);
         mma_bf16_16816(s[np * 2], qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], kb[0], kb[1]);
         mma_bf16_16816(s[np * 2 + 1], qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], kb[2], kb[3]);
       }
@@ -127,7 +138,7 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
 #pragma unroll
       for (int dp = 0; dp < 4; ++dp) {     // pairs of 8-wide d tiles
         uint32_t vb[4];
-        ldsm_x4_t(vb, sV[buf] + (kk * 16 + (lane & 15)) * AT_LD + (dp * 2 + (lane >> 4)) * 8);
+        ldsm_x4_t(vb, sV + (kk * 16 + (lane & 15)) * AT_LD + (dp * 2 + (lane >> 4)) * 8);
         mma_bf16_16816(o[dp * 2], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], vb[0], vb[1]);
         mma_bf16_16816(o[dp * 2 + 1], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], vb[2], vb[3]);
       }
@@ -158,7 +169,12 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
 
 int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, cudaStream_t st) {
   dim3 grid((L + AT_BM - 1) / AT_BM, 8, B);
-  s3_attn_kernel<<<grid, 128, 0, st>>>(qkv, out, L, ld_qkv);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CBX_CUDA(cudaFuncSetAttribute(s3_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    attr_set = true;
+  }
+  s3_attn_kernel<<<grid, 128, AT_SMEM, st>>>(qkv, out, L, ld_qkv);
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;
 }

@@ -5,6 +5,7 @@
 // Activations are channel-last [2 (cond, uncond)][L][C]; the residual stream is fp32, GEMM operands bf16.
 #include "s3_gemm.cuh"
 #include "../../include/cbx.h"
+#include <cstdlib>
 #include <map>
 #include <vector>
 
@@ -116,6 +117,13 @@ struct cbx_cfm {
   int max_steps;
   std::map<int, Plan> plans;
   long long launches;
+  // a solve seen twice with the same (L, schedule, cfg rate) is captured into a CUDA graph: ~3 400 launches become
+  // one graph launch (the inter-kernel gaps were a fifth of the solve).  Caller buffers are staged so the graph's
+  // baked pointers stay valid.
+  struct SolveGraph { int L, n, seen; float cfg; std::vector<float> t, dt; cudaGraphExec_t exec; long long launches; };
+  std::vector<SolveGraph> graphs;
+  float *st_z, *st_mu, *st_spks, *st_cond, *st_out;
+  cudaStream_t cap_stream;
 };
 
 static const __nv_bfloat16* BFW(cbx_cfm* h, int i) { return h->wbf + h->bo[i]; }
@@ -235,6 +243,8 @@ extern "C" int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, c
   const size_t o_h1 = take(R * C * 2), o_res = take(R * C * 4), o_h2 = take(R * C * 4), o_est = take(R * NMEL * 4);
   const size_t o_x = take((size_t)max_len * NMEL * 4), o_mt = take((size_t)h->max_steps * 1024 * 4);
   const size_t o_tv = take((size_t)h->max_steps * NRES * 2 * C * 4), o_t = take(h->max_steps * 4);
+  const size_t o_sz = take((size_t)max_len * NMEL * 4), o_sm = take((size_t)max_len * NMEL * 4), o_ss = take(NMEL * 4);
+  const size_t o_sc = take((size_t)max_len * NMEL * 4), o_so = take((size_t)max_len * NMEL * 4);
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_cfm_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -247,12 +257,17 @@ extern "C" int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, c
   h->att = (__nv_bfloat16*)(s + o_att); h->ff = (__nv_bfloat16*)(s + o_ff); h->h1 = (__nv_bfloat16*)(s + o_h1);
   h->res = (float*)(s + o_res); h->h2 = (float*)(s + o_h2); h->est = (float*)(s + o_est); h->x = (float*)(s + o_x);
   h->mish_temb = (float*)(s + o_mt); h->tvec = (float*)(s + o_tv); h->tvals = (float*)(s + o_t);
+  h->st_z = (float*)(s + o_sz); h->st_mu = (float*)(s + o_sm); h->st_spks = (float*)(s + o_ss); h->st_cond = (float*)(s + o_sc);
+  h->st_out = (float*)(s + o_so);
+  h->cap_stream = nullptr;
   *out = h;
   return CBX_OK;
 }
 
 extern "C" int cbx_cfm_destroy(cbx_cfm* h) {
   if (!h) return CBX_OK;
+  for (auto& g : h->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   cudaFree(h->slab);
   delete h;
   return CBX_OK;
@@ -277,25 +292,74 @@ extern "C" int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, co
   return CBX_OK;
 }
 
-extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
-                             int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out,
-                             void* stream) {
-  CBX_CHECK(h && z && mu && spks && cond && t_vals && dt_vals && mel_out, "cbx_cfm_solve: null argument");
-  CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_solve: L=%d exceeds max_len %d", L, h->max_len);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  CBX_CUDA(cudaSetDevice(h->device));
-  Plan* pl;
-  if (build_plan(h, L, &pl)) return CBX_ERR;
-  if (time_vectors(h, t_vals, n_steps, st)) return CBX_ERR;
+// the kernel sequence of one Euler solve on the handle's own buffers (stream-ordered; capturable)
+static int solve_body(cbx_cfm* h, Plan* pl, const float* z, const float* mu, const float* spks, const float* cond, int L,
+                      int n_steps, const float* dt_vals, float cfg_rate, float* mel_out, cudaStream_t st) {
+  k_temb<<<n_steps, 1024, 0, st>>>(h->tvals, FW(h, F_TIME + 0), FW(h, F_TIME + 1), FW(h, F_TIME + 2), FW(h, F_TIME + 3), h->mish_temb);
+  k_tvec<<<dim3(NRES, n_steps), 256, 0, st>>>(h->mish_temb, FW(h, F_TIME + 4), FW(h, F_TIME + 5), h->tvec);
   PackIn in{{z, z}, {mu, nullptr}, {spks, nullptr}, {cond, nullptr}};
   k_pack<<<L, CIN, 0, st>>>(in, h->x, h->xin, L);
-  h->launches += 1;
+  h->launches += 3;
   for (int s = 0; s < n_steps; ++s) {
     if (run_estimator(h, pl, s, st)) return CBX_ERR;
     k_euler<<<L, NMEL, 0, st>>>(h->est, h->x, h->xin, mel_out, dt_vals[s], cfg_rate, L, s == n_steps - 1);
     h->launches += 1;
   }
   CBX_CUDA(cudaGetLastError());
+  return CBX_OK;
+}
+
+extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
+                             int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out,
+                             void* stream) {
+  CBX_CHECK(h && z && mu && spks && cond && t_vals && dt_vals && mel_out, "cbx_cfm_solve: null argument");
+  CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_solve: L=%d exceeds max_len %d", L, h->max_len);
+  CBX_CHECK(n_steps >= 1 && n_steps <= h->max_steps, "cfm: n_steps %d out of range (max %d)", n_steps, h->max_steps);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CBX_CUDA(cudaSetDevice(h->device));
+  Plan* pl;
+  if (build_plan(h, L, &pl)) return CBX_ERR;
+  CBX_CUDA(cudaMemcpyAsync(h->tvals, t_vals, n_steps * sizeof(float), cudaMemcpyHostToDevice, st));
+  static const bool use_graph = [] { const char* v = getenv("CBX_CFM_GRAPH"); return !(v && v[0] == '0'); }();
+  cbx_cfm::SolveGraph* g = nullptr;
+  if (use_graph) {
+    for (auto& c : h->graphs)
+      if (c.L == L && c.n == n_steps && c.cfg == cfg_rate && c.t == std::vector<float>(t_vals, t_vals + n_steps) &&
+          c.dt == std::vector<float>(dt_vals, dt_vals + n_steps)) { g = &c; break; }
+    if (!g) {
+      h->graphs.push_back({L, n_steps, 0, cfg_rate, std::vector<float>(t_vals, t_vals + n_steps),
+                           std::vector<float>(dt_vals, dt_vals + n_steps), nullptr, 0});
+      g = &h->graphs.back();
+    }
+    g->seen += 1;
+  }
+  if (!g || g->seen < 2) return solve_body(h, pl, z, mu, spks, cond, L, n_steps, dt_vals, cfg_rate, mel_out, st);   // eager
+  const size_t nb = (size_t)NMEL * L * sizeof(float);
+  if (!g->exec) {
+    if (!h->cap_stream) CBX_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+    const long long before = h->launches;
+    cudaGraph_t graph = nullptr;
+    CBX_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = solve_body(h, pl, h->st_z, h->st_mu, h->st_spks, h->st_cond, L, n_steps, dt_vals, cfg_rate, h->st_out, h->cap_stream);
+    const cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
+    g->launches = h->launches - before;
+    h->launches = before;
+    if (rc || ce != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      cbx_set_error("cbx_cfm_solve: graph capture failed (%s)", cudaGetErrorString(ce));
+      return CBX_ERR;
+    }
+    const cudaError_t ie = cudaGraphInstantiate(&g->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    CBX_CHECK(ie == cudaSuccess, "cbx_cfm_solve: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ie));
+  }
+  CBX_CUDA(cudaMemcpyAsync(h->st_z, z, nb, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_mu, mu, nb, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_spks, spks, NMEL * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_cond, cond, nb, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaGraphLaunch(g->exec, st));
+  CBX_CUDA(cudaMemcpyAsync(mel_out, h->st_out, nb, cudaMemcpyDeviceToDevice, st));
+  h->launches += g->launches;
   return CBX_OK;
 }
 
