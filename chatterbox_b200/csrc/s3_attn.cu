@@ -2,7 +2,9 @@
 // (reference: matcha/transformer.py:196-204 -> diffusers 0.29.0 Attention/AttnProcessor2_0: 8 heads x 64,
 // scale 1/8, key-padding bias only — all-zero for one un-padded utterance, decoder.py:269-270).
 // Flash-attention structure: a CTA owns 64 query rows of one (batch, head); K/V tiles of 64 keys are
-// stream through a 4-deep cp.async pipeline in shared memory (one tile of lookahead left the loop waiting on L2); S = QK^T and O += PV run on mma.sync m16n8k16 bf16
+// stream through a cp.async pipeline in shared memory; TWO groups of 4 warps share a CTA and take alternate key
+// tiles (the per-tile dependency chain, not bandwidth, bounds this kernel: splitting the keys halves it), their
+// online-softmax states are merged through shared memory at the end; S = QK^T and O += PV run on mma.sync m16n8k16 bf16
 // with fp32 accumulation and an fp32 online softmax.  (Round-1 kernel: the legacy tensor-core path;
 // the tcgen05 version is listed in DESIGN.md as the next step for this stage.)
 #include "common.cuh"
@@ -11,7 +13,8 @@ namespace cbx {
 namespace {
 
 constexpr int AT_BM = 64, AT_BN = 64, AT_D = 64, AT_LD = 72;   // padded smem row stride (elements)
-constexpr int AT_NST = 4;                                       // K/V pipeline depth
+constexpr int AT_G = 2;                                         // warp groups (key split inside the CTA)
+constexpr int AT_NST = 2 * AT_G;                                // staged K/V tiles: two rounds of AT_G tiles
 constexpr int AT_TILE = AT_BN * AT_LD;                          // elements of one staged tile
 constexpr int AT_SMEM = (1 + 2 * AT_NST) * AT_TILE * 2;         // Q + NST x (K, V), bytes
 
@@ -29,34 +32,35 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
 }
 
 // qkv: bf16 [B][L][ld_qkv] with q at column 0, k at 512, v at 1024 (+ head*64); out: bf16 [B][L][512]
-__global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
+__global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
                                                       int L, int ld_qkv) {
   extern __shared__ __align__(16) __nv_bfloat16 at_smem[];
   __nv_bfloat16* sQ = at_smem;
   __nv_bfloat16* sKb = at_smem + AT_TILE;                 // [NST][tile]
   __nv_bfloat16* sVb = at_smem + (1 + AT_NST) * AT_TILE;  // [NST][tile]
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, grp = tid >> 7, warp = (tid >> 5) & 3, lane = tid & 31;
   const int q0 = blockIdx.x * AT_BM, head = blockIdx.y, b = blockIdx.z;
   const __nv_bfloat16* base = qkv + (size_t)b * L * ld_qkv + head * AT_D;
 
   auto load_tile = [&](__nv_bfloat16* dst, int col_off, int row0) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int ch = tid + i * 128, r = ch >> 3, c8 = ch & 7;
+    for (int i = 0; i < 4 / AT_G; ++i) {
+      const int ch = tid + i * 128 * AT_G, r = ch >> 3, c8 = ch & 7;
       const bool ok = row0 + r < L;
       cp_async16(dst + r * AT_LD + c8 * 8, base + (size_t)(ok ? row0 + r : 0) * ld_qkv + col_off + c8 * 8, ok);
     }
   };
   const int ntiles = (L + AT_BN - 1) / AT_BN;
   load_tile(sQ, 0, q0);
+  const int nrounds = (ntiles + AT_G - 1) / AT_G;        // a round = AT_G consecutive key tiles, one per warp group
 #pragma unroll
-  for (int t = 0; t < AT_NST - 1; ++t) {
+  for (int t = 0; t < AT_G; ++t) {
     if (t < ntiles) {
       load_tile(sKb + t * AT_TILE, 512, t * AT_BN);
       load_tile(sVb + t * AT_TILE, 1024, t * AT_BN);
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");      // one group per tile (possibly empty)
   }
+  asm volatile("cp.async.commit_group;" ::: "memory");        // one commit group per round
 
   float o[8][4], m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
 #pragma unroll
@@ -64,24 +68,27 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
   uint32_t qf[4][4];
   const float sc = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
 
-  for (int kt = 0; kt < ntiles; ++kt) {
+  for (int rd = 0; rd < nrounds; ++rd) {
+    const int kt = rd * AT_G + grp;            // this group's key tile of the round
     const __nv_bfloat16* sK = sKb + (kt % AT_NST) * AT_TILE;
     const __nv_bfloat16* sV = sVb + (kt % AT_NST) * AT_TILE;
-    {
-      const int nt = kt + AT_NST - 1;       // refills the buffer tile kt - 1 used (freed by the barrier ending that iteration)
+#pragma unroll
+    for (int t = 0; t < AT_G; ++t) {           // next round's tiles into the other half of the ring (freed by the barrier
+      const int nt = (rd + 1) * AT_G + t;      // that ended round rd - 1)
       if (nt < ntiles) {
         load_tile(sKb + (nt % AT_NST) * AT_TILE, 512, nt * AT_BN);
         load_tile(sVb + (nt % AT_NST) * AT_TILE, 1024, nt * AT_BN);
       }
-      asm volatile("cp.async.commit_group;" ::: "memory");
-      asm volatile("cp.async.wait_group %0;" ::"n"(AT_NST - 1) : "memory");      // tile kt (and Q) have landed
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");      // round rd (and Q) have landed
     __syncthreads();
-    if (kt == 0) {
+    if (rd == 0) {
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks)
         ldsm_x4(qf[ks], sQ + (warp * 16 + (lane & 15)) * AT_LD + ks * 16 + (lane >> 4) * 8);
     }
+    if (kt < ntiles) {
     // ---- S = Q K^T (16 x 64 per warp) ----
     float s[8][4];
 #pragma unroll
@@ -143,7 +150,35 @@ __global__ void __launch_bounds__(128) s3_attn_kernel(const __nv_bfloat16* __res
         mma_bf16_16816(o[dp * 2 + 1], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], vb[2], vb[3]);
       }
     }
+    }
     __syncthreads();
+  }
+  // ---- merge the warp groups' partial states (group g > 0 -> shared memory -> group 0) ----
+  {
+    float* xch = reinterpret_cast<float*>(sKb);                 // ring is idle now: [128 threads][36 floats]
+    const int t128 = tid & 127;
+    if (grp == 1) {
+      float* d = xch + t128 * 36;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { d[i * 4] = o[i][0]; d[i * 4 + 1] = o[i][1]; d[i * 4 + 2] = o[i][2]; d[i * 4 + 3] = o[i][3]; }
+      d[32] = m_run[0]; d[33] = m_run[1]; d[34] = l_run[0]; d[35] = l_run[1];
+    }
+    __syncthreads();
+    if (grp != 0) return;
+    const float* d = xch + t128 * 36;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const float m1 = d[32 + r], l1 = d[34 + r];
+      const float mn = fmaxf(m_run[r], m1);
+      const float c0 = (m_run[r] == -INFINITY) ? 0.f : exp2f(m_run[r] - mn), c1 = (m1 == -INFINITY) ? 0.f : exp2f(m1 - mn);
+      l_run[r] = l_run[r] * c0 + l1 * c1;
+      m_run[r] = mn;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        o[i][r * 2] = o[i][r * 2] * c0 + d[i * 4 + r * 2] * c1;
+        o[i][r * 2 + 1] = o[i][r * 2 + 1] * c0 + d[i * 4 + r * 2 + 1] * c1;
+      }
+    }
   }
   // ---- normalise and store ----
 #pragma unroll
@@ -174,7 +209,7 @@ int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, i
     CBX_CUDA(cudaFuncSetAttribute(s3_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     attr_set = true;
   }
-  s3_attn_kernel<<<grid, 128, AT_SMEM, st>>>(qkv, out, L, ld_qkv);
+  s3_attn_kernel<<<grid, 128 * AT_G, AT_SMEM, st>>>(qkv, out, L, ld_qkv);
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;
 }
