@@ -7,7 +7,7 @@
 // online-softmax states are merged through shared memory at the end; S = QK^T and O += PV run on mma.sync m16n8k16 bf16
 // with fp32 accumulation and an fp32 online softmax.  (Round-1 kernel: the legacy tensor-core path;
 // the tcgen05 version is listed in DESIGN.md as the next step for this stage.)
-#include "common.cuh"
+#include "s3_gemm.cuh"
 
 namespace cbx {
 namespace {
@@ -51,6 +51,8 @@ __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16
     }
   };
   const int ntiles = (L + AT_BN - 1) / AT_BN;
+  pdl_launch_dependents();
+  pdl_wait();                 // q|k|v come from the GEMM just before
   load_tile(sQ, 0, q0);
   const int nrounds = (ntiles + AT_G - 1) / AT_G;        // a round = AT_G consecutive key tiles, one per warp group
 #pragma unroll
@@ -209,7 +211,13 @@ int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, i
     CBX_CUDA(cudaFuncSetAttribute(s3_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     attr_set = true;
   }
-  s3_attn_kernel<<<grid, 128 * AT_G, AT_SMEM, st>>>(qkv, out, L, ld_qkv);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = dim3(128 * AT_G); cfg.dynamicSmemBytes = AT_SMEM; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_attn_kernel, qkv, out, L, ld_qkv));
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;
 }

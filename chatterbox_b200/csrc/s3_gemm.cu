@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   float* tile = reinterpret_cast<float*>(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();      // the next kernel may be scheduled: it waits (pdl_wait) for this grid to finish
   if (threadIdx.x == 0) GEMM_STAMP(0);
   const int b = blockIdx.x / p.tiles_l, t0 = (blockIdx.x % p.tiles_l) * BM;
   const int n0 = blockIdx.y * p.n_tile;
@@ -149,6 +150,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (threadIdx.x == 0) GEMM_STAMP(1);
+  pdl_wait();                   // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel
 
   // epilogue state shared by all warps (see phase 2 below)
   const GemmEpi& e = p.e;
@@ -530,6 +532,11 @@ int gemm_make_hilo(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane
   return CBX_OK;
 }
 
+bool pdl_enabled() {
+  static const bool on = [] { const char* v = getenv("CBX_PDL"); return !(v && v[0] == '0'); }();
+  return on;
+}
+
 static unsigned long long* g_gemm_dbg = nullptr;
 void gemm_set_debug(unsigned long long* buf) { g_gemm_dbg = buf; }
 
@@ -559,10 +566,19 @@ int launch_as(const GemmParams& p, dim3 grid, cudaStream_t st) {
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = GEMM_SMEM; cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = grid.z;
-  cfg.attrs = at; cfg.numAttrs = grid.z > 1 ? 1 : 0;
+  cudaLaunchAttribute at[2];
+  int na = 0;
+  if (grid.z > 1) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = 1; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = grid.z;
+    ++na;
+  }
+  if (pdl_enabled()) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = at; cfg.numAttrs = na;
   CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_gemm_kernel<FEAT>, p));
   return CBX_OK;
 }

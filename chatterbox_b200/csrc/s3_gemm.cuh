@@ -48,5 +48,7 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
 int gemm_make_hilo(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int K,
                    const GemmEpi& epi);
 int gemm_launch(const GemmDesc& d, cudaStream_t st);
+// true unless CBX_PDL=0: kernels are launched with programmatic stream serialization (prologue overlap)
+bool pdl_enabled();
 
 }  // namespace cbx

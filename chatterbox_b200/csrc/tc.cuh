@@ -36,6 +36,11 @@ __device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---- programmatic dependent launch (PDL): the next kernel of the stream / graph may start its prologue while this
+// one runs; it must call pdl_wait() before touching anything an earlier kernel wrote ----
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- thread-block clusters: barrier and distributed-shared-memory loads ----
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
