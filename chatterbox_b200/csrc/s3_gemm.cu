@@ -150,7 +150,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (threadIdx.x == 0) GEMM_STAMP(1);
-  pdl_wait();                   // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel
+  // PDL: everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel.  Warp 0 goes on to
+  // issue the WEIGHT panels (constant data) before it waits; every other warp waits here, before its first read of
+  // anything an earlier kernel wrote (residual rows, time-embedding vector).
+  if (warp != 0) pdl_wait();
 
   // epilogue state shared by all warps (see phase 2 below)
   const GemmEpi& e = p.e;
@@ -179,24 +182,30 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   };
 #pragma unroll
   for (int rr = 0; rr < EPI_R; ++rr) { rvn[rr][0] = make_float4(0.f, 0.f, 0.f, 0.f); rvn[rr][1] = rvn[rr][0]; }
-  if (has_resid) load_resid(row_base + warp * rpw);
+  if (has_resid && warp != 0) load_resid(row_base + warp * rpw);
 
   if (warp == 0) {
     if (lane == 0) {
       const uint32_t tx = A_BYTES + p.n_tile * BK * 2;
+      const int npre = nkb < STAGES ? nkb : STAGES;
+      // weight panels of the first ring pass: issued before the PDL wait (they do not depend on the previous kernel)
+      for (int i = 0; i < npre; ++i) {
+        const int kb = kb0 + i;
+        mbar_arrive_expect_tx(&full[i], tx);
+        tma_load_3d(smem + i * STAGE_BYTES + A_BYTES, &p.tmW, &full[i], (p.hilo ? kb % kpb : kb) * BK, n0, 0);
+      }
+      pdl_wait();
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES, ph = (i / STAGES) & 1, kb = kb0 + i;
-        mbar_wait_spin(&empty[s], ph ^ 1);
         const int tap = kb / kpb, kk = kb % kpb;
         uint8_t* sa = smem + s * STAGE_BYTES;
-        mbar_arrive_expect_tx(&full[s], tx);
-        if (p.hilo) {      // plane `tap` of A against the same W panel
-          tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0, tap);
-          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kk * BK, n0, 0);
-        } else {
-          tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
-          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kb * BK, n0, 0);
+        if (i >= npre) {
+          mbar_wait_spin(&empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full[s], tx);
+          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], (p.hilo ? kk : kb) * BK, n0, 0);
         }
+        if (p.hilo) tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0, tap);      // plane `tap` of A against the same W panel
+        else tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
       }
       GEMM_STAMP(2);
     }
@@ -257,6 +266,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   // iteration ahead, the first pair before the barrier (behind the main loop).  Every mode test is on a kernel
   // parameter, hoisted out of the element loops. =====
   {
+    if (warp == 0) {            // the producer warp skipped the early residual prefetch (it was issuing TMA loads)
+      pdl_wait();
+      if (has_resid) load_resid(row_base);
+    }
     const float inv_n = 1.0f / (float)p.n_tile;
     float4 bias4[2];
 #pragma unroll
