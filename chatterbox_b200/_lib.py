@@ -43,6 +43,7 @@ SYMBOLS = {
     "cbx_last_error": (C.c_char_p, []),
     "cbx_version": (C.c_int, []),
     "cbx_t3_grid": (C.c_int, [C.c_int]),
+    "cbx_t3_kwarps": (C.c_int, []),
     "cbx_t3_plan_count": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "cbx_t3_plan_unit": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "cbx_t3_create": (C.c_int, [C.POINTER(CbxT3Config), C.POINTER(CbxT3Weights), C.POINTER(C.c_void_p)]),

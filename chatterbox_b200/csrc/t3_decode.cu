@@ -40,7 +40,9 @@
 namespace {
 
 constexpr int NSLOT = 4;                  // ring depth (32 KB units)
-constexpr int NCONS_WARPS = 8;
+constexpr int NCONS_WARPS = T3_KW;
+constexpr int VPL = 1024 / NCONS_WARPS / 16;   // consecutive k one lane owns (8 or 4) = k16 steps of a warp's k-slice
+static_assert(VPL == 8 || VPL == 4, "T3_KW must be 8 or 16");
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
 constexpr int NTHREADS = NCONS;
 constexpr int MAXS = 4;                   // max KV splits per (row, head) pair
@@ -52,15 +54,16 @@ constexpr float RMS_EPS = 1e-5f;
 constexpr int SMEM_RING = NSLOT * T3_UNIT_BYTES;
 constexpr int SMEM_BARS = SMEM_RING;            // 2*NSLOT mbarriers
 constexpr int SMEM_CTL = SMEM_BARS + 256;       // control words
-constexpr int SMEM_RED = SMEM_CTL + 256;        // [2 phase parities][MAXU][8 warps][32] k-slice partials
+constexpr int SMEM_RED = SMEM_CTL + 256;        // [2 phase parities][MAXU][warps][32] k-slice partials
 constexpr int RED_FLOATS = T3_MAXU * NCONS_WARPS * 32;
-constexpr int SMEM_SSQ = SMEM_RED + 2 * RED_FLOATS * 4;      // [2][8 warps][2 rows] partial sums of squares
-constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [8 warps][2 rows][128] activation slices (fragment build)
-constexpr int SMEM_SCRATCH = SMEM_XT + NCONS_WARPS * 2 * 128 * 4;   // attention scratch / sampling logits (union)
+constexpr int SMEM_SSQ = SMEM_RED + 2 * RED_FLOATS * 4;      // [2][warps][2 rows] partial sums of squares
+constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [warps][2 rows][16 VPL] activation slices (fragment build)
+constexpr int SMEM_SCRATCH = SMEM_XT + NCONS_WARPS * 2 * 16 * VPL * 4;   // attention scratch / sampling logits (union)
 constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
 constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0)
 constexpr int SMEM_TOTAL = SMEM_SEEN + VOCAB_PAD;
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
+static_assert(2 * NCONS_WARPS * 2 * 4 <= 256, "ssq buffer");
 static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
 
 // LL exchange buffers (elements are {fp32 bits, flag} 8-byte words), offsets in words
@@ -201,9 +204,9 @@ __device__ __forceinline__ void ll_poll(const unsigned long long* (&ptr)[N], int
 
 // x[e] = sum over np (<= 4) pieces, `stride` words apart, of the 8 LL words at base (fixed order -> deterministic
 // sum).  One instance serves every phase: all loads of a round are in flight together.
-__device__ __forceinline__ void ll_load8(float (&x)[8], const unsigned long long* base, size_t stride, int np, unsigned flag,
+__device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long long* base, size_t stride, int np, unsigned flag,
                                          bool active, Ctl* ctl, T3State* st) {
-  unsigned long long w[4][8];
+  unsigned long long w[4][VPL];
   if (active) {
     unsigned spins = 0; unsigned long long t0 = 0;
     for (;;) {
@@ -214,22 +217,24 @@ __device__ __forceinline__ void ll_load8(float (&x)[8], const unsigned long long
           const unsigned long long* pq = base + q * stride;
           ll_ld2_off<0>(pq, w[q][0], w[q][1]);
           ll_ld2_off<16>(pq, w[q][2], w[q][3]);
-          ll_ld2_off<32>(pq, w[q][4], w[q][5]);
-          ll_ld2_off<48>(pq, w[q][6], w[q][7]);
+          if constexpr (VPL == 8) {
+            ll_ld2_off<32>(pq, w[q][VPL - 4], w[q][VPL - 3]);
+            ll_ld2_off<48>(pq, w[q][VPL - 2], w[q][VPL - 1]);
+          }
         }
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q)
         if (q < np) {
 #pragma unroll
-          for (int e = 0; e < 8; ++e) ok = ok && ll_ok(w[q][e], flag);
+          for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(w[q][e], flag);
         }
       if (ok) break;
       if (poll_timeout(spins, t0, ctl, st)) break;
     }
   }
 #pragma unroll
-  for (int e = 0; e < 8; ++e) {
+  for (int e = 0; e < VPL; ++e) {
     float sum = 0.f;
 #pragma unroll
     for (int q = 0; q < 4; ++q) sum += (active && q < np) ? ll_val(w[q][e]) : 0.f;
@@ -239,18 +244,18 @@ __device__ __forceinline__ void ll_load8(float (&x)[8], const unsigned long long
 
 // B fragments of the warp's k-slice: Bf[s][0..1] for k16 step s.  Column n = lane >> 2 of the MMA is
 // {row0 hi, row0 lo, row1 hi, row1 lo, 0, 0, 0, 0}; the slice goes through a 1 KB per-warp tile.
-__device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[8][2], const float (&x)[8], float* xt, int lane) {
+__device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[VPL][2], const float (&x)[VPL], float* xt, int lane) {
   __syncwarp();     // previous readers of the tile are done
-  *reinterpret_cast<float4*>(xt + lane * 8) = make_float4(x[0], x[1], x[2], x[3]);
-  *reinterpret_cast<float4*>(xt + lane * 8 + 4) = make_float4(x[4], x[5], x[6], x[7]);
+  *reinterpret_cast<float4*>(xt + lane * VPL) = make_float4(x[0], x[1], x[2], x[3]);
+  if constexpr (VPL == 8) *reinterpret_cast<float4*>(xt + lane * VPL + 4) = make_float4(x[VPL - 4], x[VPL - 3], x[VPL - 2], x[VPL - 1]);
   __syncwarp();
   const int g = lane >> 2, tig = lane & 3;
 #pragma unroll
-  for (int s = 0; s < 8; ++s) { Bf[s][0] = 0u; Bf[s][1] = 0u; }
+  for (int s = 0; s < VPL; ++s) { Bf[s][0] = 0u; Bf[s][1] = 0u; }
   if (g < 4) {
-    const float* src = xt + (g >> 1) * 128 + 2 * tig;
+    const float* src = xt + (g >> 1) * (16 * VPL) + 2 * tig;
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
+    for (int s = 0; s < VPL; ++s) {
       const float2 v0 = *reinterpret_cast<const float2*>(src + 16 * s);
       const float2 v1 = *reinterpret_cast<const float2*>(src + 16 * s + 8);
       uint32_t h0, l0, h1, l1;
@@ -263,10 +268,10 @@ __device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[8][2], const float (&
 }
 
 // sum of squares of the lane's 8 values, reduced over the 16 lanes of the row; lane & 15 == 0 stores it
-__device__ __forceinline__ void ssq_partial(const float (&x)[8], float* ssq, int warp, int lane) {
+__device__ __forceinline__ void ssq_partial(const float (&x)[VPL], float* ssq, int warp, int lane) {
   float s = 0.f;
 #pragma unroll
-  for (int e = 0; e < 8; ++e) s += x[e] * x[e];
+  for (int e = 0; e < VPL; ++e) s += x[e] * x[e];
   s += __shfl_xor_sync(0xffffffffu, s, 1);
   s += __shfl_xor_sync(0xffffffffu, s, 2);
   s += __shfl_xor_sync(0xffffffffu, s, 4);
@@ -280,10 +285,13 @@ __device__ __forceinline__ float rms_scale(const float* ssq, int b) {
   return rsqrtf(tot * (1.0f / T3_H) + RMS_EPS);
 }
 // 8 norm gains of this lane's k range, fetched one phase ahead into registers
-__device__ __forceinline__ void ln_fetch(float (&g)[8], const float* __restrict__ lnw, int k) {
+__device__ __forceinline__ void ln_fetch(float (&g)[VPL], const float* __restrict__ lnw, int k) {
   const float4 a = __ldcg(reinterpret_cast<const float4*>(lnw + k));      // L2 only: keep the small L1 for the stack
-  const float4 b = __ldcg(reinterpret_cast<const float4*>(lnw + k + 4));
-  g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+  g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w;
+  if constexpr (VPL == 8) {
+    const float4 b = __ldcg(reinterpret_cast<const float4*>(lnw + k + 4));
+    g[VPL - 4] = b.x; g[VPL - 3] = b.y; g[VPL - 2] = b.z; g[VPL - 1] = b.w;
+  }
 }
 
 // The weight stream of one CTA: every iteration walks the L layers' units, iterations >= head_from_iter walk the
@@ -311,21 +319,21 @@ __device__ __forceinline__ void stream_issue_next(const Stream& sm, Ctl* ctl, in
 // index = row * 16 + weight row of the unit
 struct RingPos { int slot; uint32_t parity; long long k; };
 
-__device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t (&Bf)[8][2], float* red, uint8_t* ring,
+__device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t (&Bf)[VPL][2], float* red, uint8_t* ring,
                                               uint64_t* full, const Stream& sm, int warp, int lane, Ctl* ctl, T3State* st) {
   const int g = lane >> 2, tig = lane & 3;
 #pragma unroll 1
   for (int j = 0; j < n; ++j) {
     mbar_wait(&full[rp.slot], rp.parity, ctl, st);
-    const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * 256 + lane;
-    uint4 w[8];
+    const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * (VPL * 32) + lane;
+    uint4 w[VPL];
 #pragma unroll
-    for (int s = 0; s < 8; ++s) w[s] = wp[s * 32];
+    for (int s = 0; s < VPL; ++s) w[s] = wp[s * 32];
     float c[4][4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) { c[q][0] = 0.f; c[q][1] = 0.f; c[q][2] = 0.f; c[q][3] = 0.f; }
 #pragma unroll
-    for (int s = 0; s < 8; ++s) mma_bf16_16816(c[s & 3], w[s].x, w[s].y, w[s].z, w[s].w, Bf[s][0], Bf[s][1]);
+    for (int s = 0; s < VPL; ++s) mma_bf16_16816(c[s & 3], w[s].x, w[s].y, w[s].z, w[s].w, Bf[s][0], Bf[s][1]);
     __syncwarp();
     if (lane == 0) {
       // release the slot; the warp that releases it last re-arms it with the unit NSLOT ahead
@@ -429,7 +437,7 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
   float* q_s = scr;                       // [64] (pre-scaled by 1/8)
   float* k_new = scr + 64;                // [64]
   float* v_new = scr + 128;               // [64]
-  float* wpart = scr + 192;               // [8 warps][PART_STRIDE]
+  float* wpart = scr + 192;               // [warps][PART_STRIDE]
   KVT* kc = reinterpret_cast<KVT*>(p.kcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
   KVT* vc = reinterpret_cast<KVT*>(p.vcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
 
@@ -494,7 +502,7 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
     s += __shfl_xor_sync(0xffffffffu, s, 4);
     if (lg == 0) osm_update(st, s, vf);
   }
-  // merge the 4 lane groups, then the 8 warps
+  // merge the 4 lane groups, then the warps
   osm_merge_xor(st, 8);
   osm_merge_xor(st, 16);
   if (lg == 0) {
@@ -536,21 +544,23 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
 template <int SI>
 struct PartLoad {
   static __device__ __forceinline__ void issue(const unsigned long long* bo, const unsigned long long* bm, int S,
-                                               unsigned long long (&wo)[MAXS][8], unsigned long long (&wm)[MAXS],
+                                               unsigned long long (&wo)[MAXS][VPL], unsigned long long (&wm)[MAXS],
                                                unsigned long long (&wl)[MAXS]) {
     if (SI < S) {
       ll_ld2_off<(SI * PART_STRIDE + 0) * 8>(bo, wo[SI][0], wo[SI][1]);
       ll_ld2_off<(SI * PART_STRIDE + 2) * 8>(bo, wo[SI][2], wo[SI][3]);
-      ll_ld2_off<(SI * PART_STRIDE + 4) * 8>(bo, wo[SI][4], wo[SI][5]);
-      ll_ld2_off<(SI * PART_STRIDE + 6) * 8>(bo, wo[SI][6], wo[SI][7]);
+      if constexpr (VPL == 8) {
+        ll_ld2_off<(SI * PART_STRIDE + 4) * 8>(bo, wo[SI][VPL - 4], wo[SI][VPL - 3]);
+        ll_ld2_off<(SI * PART_STRIDE + 6) * 8>(bo, wo[SI][VPL - 2], wo[SI][VPL - 1]);
+      }
       ll_ld2_off<(SI * PART_STRIDE + 64) * 8>(bm, wm[SI], wl[SI]);
     }
     if constexpr (SI + 1 < MAXS) PartLoad<SI + 1>::issue(bo, bm, S, wo, wm, wl);
   }
 };
-__device__ __forceinline__ void attn_combine8(float (&x)[8], const T3Params& p, int S, int b, int k, unsigned flag, bool active,
+__device__ __forceinline__ void attn_combine8(float (&x)[VPL], const T3Params& p, int S, int b, int k, unsigned flag, bool active,
                                               Ctl* ctl) {
-  unsigned long long wo[MAXS][8], wm[MAXS], wl[MAXS];
+  unsigned long long wo[MAXS][VPL], wm[MAXS], wl[MAXS];
   const int head = k >> 6, d = k & 63;
   const unsigned long long* base = p.ll + LL_PART + ((size_t)(b * T3_NH + head) * MAXS) * PART_STRIDE;
   if (active) {
@@ -562,7 +572,7 @@ __device__ __forceinline__ void attn_combine8(float (&x)[8], const T3Params& p, 
       for (int s = 0; s < MAXS; ++s) {
         if (s < S) {
 #pragma unroll
-          for (int e = 0; e < 8; ++e) ok = ok && ll_ok(wo[s][e], flag);
+          for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(wo[s][e], flag);
           ok = ok && ll_ok(wm[s], flag) && ll_ok(wl[s], flag);
         }
       }
@@ -575,7 +585,7 @@ __device__ __forceinline__ void attn_combine8(float (&x)[8], const T3Params& p, 
   for (int s = 0; s < MAXS; ++s) if (s < S && active) Mx = fmaxf(Mx, ll_val(wm[s]));
   float Lt = 0.f;
 #pragma unroll
-  for (int e = 0; e < 8; ++e) x[e] = 0.f;
+  for (int e = 0; e < VPL; ++e) x[e] = 0.f;
 #pragma unroll
   for (int s = 0; s < MAXS; ++s) {
     if (s < S && active) {
@@ -583,12 +593,12 @@ __device__ __forceinline__ void attn_combine8(float (&x)[8], const T3Params& p, 
       const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
       Lt += cw * ll_val(wl[s]);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) x[e] += cw * ll_val(wo[s][e]);
+      for (int e = 0; e < VPL; ++e) x[e] += cw * ll_val(wo[s][e]);
     }
   }
   const float inv = (active && Lt > 0.f) ? 1.0f / Lt : 0.f;
 #pragma unroll
-  for (int e = 0; e < 8; ++e) x[e] *= inv;
+  for (int e = 0; e < VPL; ++e) x[e] *= inv;
 }
 
 // ---- sampling phase (CTA 0): t3.py:320-356 ------------------------------------------------------
@@ -772,7 +782,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
   }
   // 5. next-token embedding: speech_emb[tok] + speech_pos_emb[n_gen + 1]  (t3.py:351-356); both CFG rows get the
   //    same vector, published once together with the control word {token | stop bit}
-  {
+  if (tid < T3_H / 4) {
     const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
     const float4 e = __ldg(reinterpret_cast<const float4*>(p.speech_emb + (size_t)tok * T3_H) + tid);
     const float4 q = __ldg(reinterpret_cast<const float4*>(p.speech_pos_emb + (size_t)(n_gen + 1) * T3_H) + tid);
@@ -825,19 +835,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   __syncthreads();
 
   const int b = lane >> 4;                        // activation row (CFG cond / uncond) of this lane
-  const int kq = warp * 128 + (lane & 15) * 8;    // its 8 consecutive k in a 1024-wide vector
+  const int kq = warp * (16 * VPL) + (lane & 15) * VPL;    // its VPL consecutive k in a 1024-wide vector
   const bool active = b < p.B;
-  float* xt = reinterpret_cast<float*>(smem + SMEM_XT) + warp * 256;
+  float* xt = reinterpret_cast<float*>(smem + SMEM_XT) + warp * (32 * VPL);
   const int S = attn_splits(G, p.B);
   const int down_slice = ctl->plan_u[PH_DOWN][0] % T3_DOWN_KS;
   RingPos rp{0, 0u, 0ll};
   int pos0 = __ldcg(&p.st->pos);
   int n_gen = __ldcg(&p.st->n_gen);
   int n_done = 0;
-  float xres[8];        // residual stream slice, replicated in every CTA
-  float x[8];
-  float gn[8];          // gains of the next RMSNorm (fetched a phase ahead)
-  uint32_t Bf[8][2];
+  float xres[VPL];      // residual stream slice, replicated in every CTA
+  float x[VPL];
+  float gn[VPL];         // gains of the next RMSNorm (fetched a phase ahead)
+  uint32_t Bf[VPL][2];
   int prof_k = 0;
   int par = 0;          // parity of the running step counter: red / ssq double buffer
   ln_fetch(gn, p.ln1, kq);
@@ -871,7 +881,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       T3_PROF();
     }
 #pragma unroll
-    for (int e = 0; e < 8; ++e) xres[e] = 0.f;
+    for (int e = 0; e < VPL; ++e) xres[e] = 0.f;
     const bool with_head = (p.mode == 1) || (it == n_iters - 1);
     const int n_steps = 4 * L + (with_head ? 1 : 0);
 
@@ -880,14 +890,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       const int l = step >> 2;
       const int ph = (l == L) ? PH_HEAD : (step & 3);
       float* red = red_all + par * RED_FLOATS;
-      float* ssq = ssq_all + par * 16;
+      float* ssq = ssq_all + par * (NCONS_WARPS * 2);
       // ---------- prologue: this lane's 8 input values ----------
       T3_SUB(0);
       if (ph == PH_O) {
         attn_combine8(x, p, S, b, kq, ll_flag(it, L, l, LLP_PART), active, ctl);
       } else if (ph == PH_QKV && l == 0 && p.mode == 0) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) x[e] = 0.f;
+        for (int e = 0; e < VPL; ++e) x[e] = 0.f;
         if (active) ln_fetch(x, p.embeds + ((size_t)b * p.P + it) * T3_H, kq);
       } else {
         const unsigned long long* base; size_t stride = 0; int np = 1; unsigned fl;
@@ -902,10 +912,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       // ---------- residual add + RMSNorm gain (the scale is applied in the epilogue) ----------
       if (ph == PH_QKV || ph == PH_GU || ph == PH_HEAD) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) xres[e] += x[e];
+        for (int e = 0; e < VPL; ++e) xres[e] += x[e];
         ssq_partial(xres, ssq, warp, lane);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) x[e] = xres[e] * gn[e];
+        for (int e = 0; e < VPL; ++e) x[e] = xres[e] * gn[e];
         const float* nxt;
         if (ph == PH_QKV) nxt = p.ln2 + (size_t)l * T3_H;
         else if (ph == PH_GU) nxt = (l == L - 1 && with_head) ? p.final_norm : p.ln1 + (size_t)((l + 1) % L) * T3_H;
@@ -1010,6 +1020,7 @@ extern "C" int cbx_t3_grid(int device) {
   }
   return prop.multiProcessorCount;
 }
+extern "C" int cbx_t3_kwarps(void) { return T3_KW; }
 extern "C" int cbx_t3_plan_count(int ph, int c, int G) { return t3_plan_count(ph, c, G); }
 extern "C" int cbx_t3_plan_unit(int ph, int c, int G, int j) { return t3_plan_unit(ph, c, G, j); }
 

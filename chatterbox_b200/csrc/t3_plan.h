@@ -33,6 +33,7 @@ enum { PH_QKV = 0, PH_O = 1, PH_GU = 2, PH_DOWN = 3, PH_HEAD = 4, PH_COUNT = 5 }
 #define T3_UNIT_ROWS 16
 #define T3_UNIT_BYTES 32768
 #define T3_MAXU 4          // max units of one phase on one CTA (needs G >= 129)
+#define T3_KW 8            // warps of a CTA; they split the 1024-wide k range of a unit (the fragment layout depends on it)
 #define T3_DOWN_ROWG 64    // 1024 / 16 row groups of down_proj
 #define T3_DOWN_KS 4       // k-slices of down_proj
 

@@ -31,11 +31,18 @@ def plan_lists(G: int) -> List[List[List[int]]]:
              for ph in range(5)] for c in range(G)]
 
 
+def kwarps() -> int:
+    """Warps of a megakernel CTA = k-slices of a unit (csrc/t3_plan.h: T3_KW), asked from the library."""
+    return _lib.lib().cbx_t3_kwarps()
+
+
 def _frag_order(units: torch.Tensor) -> torch.Tensor:
-    """[U, 16 rows, 1024 k] -> [U, 16384] in A-fragment order: row = rh*8 + g, k = w*128 + s*16 + kh*8 + tig*2 + e
-    -> [w][s][g][tig][kh][rh][e]  (a0 = (kh 0, rh 0), a1 = (0, 1), a2 = (1, 0), a3 = (1, 1))."""
+    """[U, 16 rows, 1024 k] -> [U, 16384] in A-fragment order: row = rh*8 + g, k = w*(16 KS) + s*16 + kh*8 + tig*2 + e
+    -> [w][s][g][tig][kh][rh][e]  (a0 = (kh 0, rh 0), a1 = (0, 1), a2 = (1, 0), a3 = (1, 1)); KS = 64 / KW k16 steps."""
     U = units.shape[0]
-    return units.reshape(U, 2, 8, 8, 8, 2, 4, 2).permute(0, 3, 4, 2, 6, 5, 1, 7).reshape(U, UNIT_ELEMS)
+    KW = kwarps()
+    KS = 1024 // KW // 16
+    return units.reshape(U, 2, 8, KW, KS, 2, 4, 2).permute(0, 3, 4, 2, 6, 5, 1, 7).reshape(U, UNIT_ELEMS)
 
 
 def layer_units(sd: Dict[str, torch.Tensor], i: int, dev) -> torch.Tensor:

@@ -69,6 +69,8 @@ int cbx_t3_grid(int device);
  * consumed by CTA `c` of `G`, and the id of the j-th one.  Used by the host-side weight packer. */
 int cbx_t3_plan_count(int ph, int c, int G);
 int cbx_t3_plan_unit(int ph, int c, int G, int j);
+/* k-slices of a weight unit = warps of a megakernel CTA (8 or 16): the packer's fragment order depends on it. */
+int cbx_t3_kwarps(void);
 
 int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_t3** out);
 int cbx_t3_destroy(cbx_t3* h);

@@ -44,8 +44,8 @@ def test_pack_layout_follows_plan():
     assert pk.wstream.shape[0] == G and pk.wstream.dtype == torch.bfloat16
 
     def unit_rows(c, slot):   # undo the A-fragment order -> [16 rows, 1024 k]
-        f = pk.wstream[c, slot].float().reshape(8, 8, 8, 4, 2, 2, 2)          # [w][s][g][tig][kh][rh][e]
-        return f.permute(5, 2, 0, 1, 4, 3, 6).reshape(16, 1024)               # row = rh*8+g, k = w*128+s*16+kh*8+tig*2+e
+        f = pk.wstream[c, slot].float().reshape(pack.kwarps(), 64 // pack.kwarps(), 8, 4, 2, 2, 2)   # [w][s][g][tig][kh][rh][e]
+        return f.permute(5, 2, 0, 1, 4, 3, 6).reshape(16, 1024)               # row = rh*8+g, k = w*16KS+s*16+kh*8+tig*2+e
 
     q = sd["tfmr.layers.0.self_attn.q_proj.weight"]
     gate, up = sd["tfmr.layers.0.mlp.gate_proj.weight"], sd["tfmr.layers.0.mlp.up_proj.weight"]

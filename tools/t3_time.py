@@ -2,6 +2,9 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+from chatterbox_b200 import _lib
+if len(sys.argv) > 1:      # A/B: time another build of the library (python tools/t3_time.py _variants/libcbx_x.so)
+    _lib.LIB_PATH = os.path.abspath(sys.argv[1])
 from chatterbox_b200 import synthetic as S
 from chatterbox_b200.t3 import T3, T3Cond
 dev = torch.device("cuda:0")
