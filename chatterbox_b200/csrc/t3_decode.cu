@@ -61,7 +61,11 @@ constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [warps][2 rows][
 constexpr int SMEM_SCRATCH = SMEM_XT + NCONS_WARPS * 2 * 16 * VPL * 4;   // attention scratch / sampling logits (union)
 constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
 constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0)
-constexpr int SMEM_TOTAL = SMEM_SEEN + VOCAB_PAD;
+// copy of the kernel parameters for the out-of-line phases (attention, sampling): a reference to the parameter
+// block itself would make the compiler keep it on the stack and turn every p.field in the step loop into a local
+// load (L1 is small here: a miss costs an L2 round trip on the critical path)
+constexpr int SMEM_PARAMS = SMEM_SEEN + VOCAB_PAD;
+constexpr int SMEM_TOTAL = SMEM_PARAMS + 512;
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
 static_assert(2 * NCONS_WARPS * 2 * 4 <= 256, "ssq buffer");
 static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
@@ -101,7 +105,6 @@ struct T3Params {
 
 struct Ctl {            // CTA-local control block in shared memory
   volatile int abort;   // set after a watchdog timeout: every later wait returns at once
-  int released[NSLOT];  // warps that have finished reading the slot's current unit
   // cursor of the weight stream (next unit to copy): touched only by the one thread re-arming a slot
   int next_idx;         // unit index inside the per-CTA stream
   int next_iter;        // iteration that unit belongs to
@@ -109,6 +112,8 @@ struct Ctl {            // CTA-local control block in shared memory
   int plan_u[PH_COUNT][T3_MAXU];   // their unit ids
 };
 static_assert(sizeof(Ctl) <= 256, "control block");
+static_assert(T3_MAXU <= NSLOT && T3_MAXU < NCONS_WARPS, "a step's units fit the ring; the last warp is free in the epilogue");
+static_assert(sizeof(T3Params) <= 512 && SMEM_PARAMS % 16 == 0, "parameter copy");
 
 using namespace cbx;
 
@@ -334,19 +339,6 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
     for (int q = 0; q < 4; ++q) { c[q][0] = 0.f; c[q][1] = 0.f; c[q][2] = 0.f; c[q][3] = 0.f; }
 #pragma unroll
     for (int s = 0; s < VPL; ++s) mma_bf16_16816(c[s & 3], w[s].x, w[s].y, w[s].z, w[s].w, Bf[s][0], Bf[s][1]);
-    __syncwarp();
-    if (lane == 0) {
-      // release the slot; the warp that releases it last re-arms it with the unit NSLOT ahead
-      if (atomicAdd(&ctl->released[rp.slot], 1) == NCONS_WARPS - 1) {
-        ctl->released[rp.slot] = 0;
-        __threadfence_block();
-        if (!ctl->abort) {
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          stream_issue_next(sm, ctl, rp.slot, ring, full);
-        }
-        __threadfence_block();
-      }
-    }
     if (tig < 2) {   // columns 2 tig, 2 tig + 1 = hi and lo of activation row tig
       float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g;
       dst[0] = ((c[0][0] + c[0][1]) + (c[1][0] + c[1][1])) + ((c[2][0] + c[2][1]) + (c[3][0] + c[3][1]));
@@ -375,6 +367,12 @@ template <> struct KV<__nv_bfloat16> {
   }
   static __device__ __forceinline__ float round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
   static __device__ __forceinline__ void store(__nv_bfloat16* p, float x) { *p = __float2bfloat16_rn(x); }
+  static __device__ __forceinline__ void lds8(const __nv_bfloat16* p, float (&f)[8]) {     // same from shared memory
+    uint4 v = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 t = __bfloat1622float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+  }
 };
 template <> struct KV<float> {
   static __device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
@@ -383,6 +381,10 @@ template <> struct KV<float> {
   }
   static __device__ __forceinline__ float round(float x) { return x; }
   static __device__ __forceinline__ void store(float* p, float x) { *p = x; }
+  static __device__ __forceinline__ void lds8(const float* p, float (&f)[8]) {
+    float4 a = *reinterpret_cast<const float4*>(p), b = *(reinterpret_cast<const float4*>(p) + 1);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+  }
 };
 
 // online-softmax state of one query over the keys a lane group has seen
@@ -426,6 +428,12 @@ __device__ __forceinline__ int attn_splits(int G, int B) {
 // CTA c < S*npairs handles pair = c % npairs (CFG row b, head) and KV split c / npairs; it publishes
 // {sum_i exp(s_i - m) v_i, m, l} through the LL part buffer.  The S partials of a pair are merged by
 // their consumers (the o_proj prologue), so there is no separate combine hop.
+#ifdef T3_TIMELINE
+#define T3_ATL(k) do { if (p.prof && tid == 0 && (p.prof_it & 0x40000000) && it == (p.prof_it & 0xffff)) \
+                         p.prof[1024 + (size_t)c * 1024 + 512 + 4 * layer + (k)] = gtime_ns(); } while (0)
+#else
+#define T3_ATL(k) do {} while (0)
+#endif
 template <typename KVT>
 __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, int pos0, float* scr, int warp, int lane,
                                         Ctl* ctl) {
@@ -441,16 +449,43 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
   KVT* kc = reinterpret_cast<KVT*>(p.kcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
   KVT* vc = reinterpret_cast<KVT*>(p.vcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
 
+  // The keys / values of the past positions do not depend on this step: their copies into shared memory
+  // (cp.async, no registers: the caller's live state leaves this function few) are issued BEFORE the wait for
+  // q, k, v, so their L2 / HBM latency hides behind the qkv hand-over instead of following it.  Every thread
+  // copies exactly the 16-byte pieces it reads back itself: no barrier, only its own cp.async.wait_all.
+  const int lg = lane >> 3, sub = lane & 7;
+  const int chunk = (pos0 + S - 1) / S;
+  const int lo = split * chunk;
+  const int hi = min(pos0, lo + chunk);
+  constexpr int PIECES = sizeof(KVT) * 8 / 16;            // 16-byte pieces per 8 elements (1 bf16, 2 fp32)
+  constexpr int APF = (sizeof(KVT) == 2) ? 3 : 1;         // prefetched rounds of 4 positions per warp
+  static_assert((192 + NCONS_WARPS * PART_STRIDE) * 4 <= 4096 && 4096 + APF * NCONS * 2 * PIECES * 16 <= SCRATCH_BYTES, "attention scratch");
+  uint8_t* pf = reinterpret_cast<uint8_t*>(scr) + 4096 + (size_t)tid * (2 * PIECES * 16);   // [round][thread][K|V][pieces]
+#pragma unroll
+  for (int n = 0; n < APF; ++n) {
+    const int i = lo + warp * 4 + lg + n * (NCONS_WARPS * 4);
+    if (i < hi) {
+      const uint32_t dst = smem_u32(pf + (size_t)n * (NCONS * 2 * PIECES * 16));
+      const KVT* ks = kc + (size_t)i * 64 + sub * 8;
+      const KVT* vs = vc + (size_t)i * 64 + sub * 8;
+#pragma unroll
+      for (int q = 0; q < PIECES; ++q) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + q * 16), "l"(reinterpret_cast<const uint8_t*>(ks) + q * 16) : "memory");
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (PIECES + q) * 16), "l"(reinterpret_cast<const uint8_t*>(vs) + q * 16) : "memory");
+      }
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
   float kr = 0.f, vr = 0.f;
   if (tid < 64) {
     const int d = tid;
+    const float cs = __ldg(p.rope_cos + (size_t)pos0 * 32 + (d & 31));
+    const float sn = __ldg(p.rope_sin + (size_t)pos0 * 32 + (d & 31));
     const unsigned long long* row = p.ll + LL_QKV + (size_t)b * 3072 + head * 64;
     const unsigned long long* ptr[5] = {row + d, row + (d ^ 32), row + 1024 + d, row + 1024 + (d ^ 32),
                                               row + 2048 + d};
     unsigned long long w[5];
     ll_poll<5>(ptr, 5, ll_flag(it, L, layer, LLP_QKV), w, ctl, p.st);
-    const float cs = __ldg(p.rope_cos + (size_t)pos0 * 32 + (d & 31));
-    const float sn = __ldg(p.rope_sin + (size_t)pos0 * 32 + (d & 31));
     const float q = ll_val(w[0]), qo = ll_val(w[1]), k = ll_val(w[2]), ko = ll_val(w[3]), v = ll_val(w[4]);
     const float qr = q * cs + (d < 32 ? -qo : qo) * sn;
     kr = KV<KVT>::round(k * cs + (d < 32 ? -ko : ko) * sn);
@@ -459,18 +494,38 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
     k_new[d] = kr;
     v_new[d] = vr;
   }
+  T3_ATL(0);
   cbar();
+  T3_ATL(1);
 
-  const int lg = lane >> 3, sub = lane & 7;
   float qv[8];
   Osm st;
   osm_init(st);
 #pragma unroll
   for (int e = 0; e < 8; ++e) qv[e] = q_s[sub * 8 + e];
-  const int chunk = (pos0 + S - 1) / S;
-  const int lo = split * chunk;
-  const int hi = min(pos0, lo + chunk);
-  for (int base = lo + warp * 4; base < hi; base += NCONS_WARPS * 4) {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+#pragma unroll
+  for (int n = 0; n < APF; ++n) {
+    const int i = lo + warp * 4 + lg + n * (NCONS_WARPS * 4);
+    const bool valid = i < hi;
+    float kf[8], vf[8];
+    if (valid) {
+      const KVT* src = reinterpret_cast<const KVT*>(pf + (size_t)n * (NCONS * 2 * PIECES * 16));
+      KV<KVT>::lds8(src, kf);
+      KV<KVT>::lds8(src + 8, vf);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s += qv[e] * kf[e];
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (valid) osm_update(st, s, vf);
+  }
+  for (int base = lo + warp * 4 + APF * (NCONS_WARPS * 4); base < hi; base += NCONS_WARPS * 4) {
     const int i = base + lg;
     const bool valid = i < hi;
     float kf[8], vf[8];
@@ -511,6 +566,7 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
     for (int e = 0; e < 8; ++e) w[sub * 8 + e] = st.o[e];
     if (sub == 0) { w[64] = st.m; w[65] = st.l; }
   }
+  T3_ATL(2);
   cbar();
   if (tid < 64) {
     const int d = tid;
@@ -808,6 +864,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   float* ssq_all = reinterpret_cast<float*>(smem + SMEM_SSQ);
   float* scr = reinterpret_cast<float*>(smem + SMEM_SCRATCH);
   unsigned char* seen = smem + SMEM_SEEN;
+  T3Params* ps = reinterpret_cast<T3Params*>(smem + SMEM_PARAMS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = gridDim.x, c = blockIdx.x;
@@ -820,8 +877,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   sm.nhead = t3_plan_count(PH_HEAD, c, G);
   sm.head_from_iter = (p.mode == 1) ? 0 : n_iters - 1;
   sm.n_iters = n_iters;
+  if (tid == 32) *ps = p;
   if (tid == 0) {
-    for (int s = 0; s < NSLOT; ++s) { mbar_init(&full[s], 1); ctl->released[s] = 0; }
+    for (int s = 0; s < NSLOT; ++s) mbar_init(&full[s], 1);
     ctl->abort = 0; ctl->next_idx = 0; ctl->next_iter = 0;
     mbar_fence_init();
     for (int s = 0; s < NSLOT; ++s) stream_issue_next(sm, ctl, s, ring, full);
@@ -866,7 +924,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   for (int it = 0; it < n_iters; ++it) {
     if (p.mode == 1) {
       T3_PROF();
-      if (c == 0) sample_phase(p, it, n_gen, scr, seen, ctl, warp, lane);
+      if (c == 0) sample_phase(*ps, it, n_gen, scr, seen, ctl, warp, lane);
       // control word of this iteration: token id | stop bit
       const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
       unsigned long long w;
@@ -894,7 +952,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       // ---------- prologue: this lane's 8 input values ----------
       T3_SUB(0);
       if (ph == PH_O) {
-        attn_combine8(x, p, S, b, kq, ll_flag(it, L, l, LLP_PART), active, ctl);
+        // CTAs without an o_proj unit do not need the attention output at all (x only feeds the fragments)
+        attn_combine8(x, p, S, b, kq, ll_flag(it, L, l, LLP_PART), active && ctl->plan_n[PH_O] > 0, ctl);
       } else if (ph == PH_QKV && l == 0 && p.mode == 0) {
 #pragma unroll
         for (int e = 0; e < VPL; ++e) x[e] = 0.f;
@@ -929,6 +988,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       T3_SUB(3);
       T3_TL(1);
       cbar();
+      // every warp is past its reads of the n slots of this step: the last warp (never part of the epilogue, which
+      // takes warps 0..n-1) re-arms them with the units NSLOT ahead in the stream.  No per-unit release counting: the
+      // unit loop stays free of atomics, and HBM has the slack (the copies are needed a whole step later).
+      if (tid == NCONS - 32 && n > 0 && !ctl->abort) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        int sl = rp.slot - n;
+        if (sl < 0) sl += NSLOT;
+        for (int j = 0; j < n; ++j) {
+          stream_issue_next(sm, ctl, sl, ring, full);
+          if (++sl == NSLOT) sl = 0;
+        }
+      }
       T3_SUB(4);
       // ---------- epilogue: cross-warp sum, scale / SwiGLU, publish ----------
       if (tid < n * 32) {
@@ -969,7 +1040,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       T3_PROF();
       // ---------- RoPE, KV append, split-KV attention between the qkv and o_proj steps ----------
       if (ph == PH_QKV) {
-        attn_phase<KVT>(p, it, l, pos0, scr, warp, lane, ctl);
+        attn_phase<KVT>(*ps, it, l, pos0, scr, warp, lane, ctl);
         T3_TL(3);
         T3_PROF();
       }

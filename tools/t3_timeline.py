@@ -5,6 +5,8 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from chatterbox_b200 import synthetic as S, _lib
+if len(sys.argv) > 1:      # time another build of the library (python tools/t3_timeline.py _variants/libcbx_tl.so)
+    _lib.LIB_PATH = os.path.abspath(sys.argv[1])
 from chatterbox_b200.t3 import T3, T3Cond
 
 dev = torch.device("cuda:0")
@@ -44,3 +46,16 @@ for n in names:
     print(n, {k: round(stt.mean(x[k] for x in r), 2) for k in r[0]})
 e0 = tl[:, 4, 2]; e1 = tl[:, 116, 2]
 print("per-layer (steps 4..116):", float((e1.max() - e0.max()) / 28))
+# attention sub-stamps (CTAs that own a (pair, split)): q staged / barrier / keys done / published, relative to the
+# last qkv epilogue of the layer
+at = st[1024:].view(G, 1024)[:, 512:512 + 120].view(G, 30, 4).cpu().double() / 1e3
+acc = {k: [] for k in ("q_polled_med", "q_polled_max", "keys_done_max", "published_max", "keys_dur_med")}
+for l in range(1, 29):
+    qkv_done = tl[:, 4 * l, 2]; qkv_done = qkv_done[qkv_done > 0].max()
+    a = at[:, l, :]; m = a[:, 0] > 0
+    acc["q_polled_med"].append(float((a[m, 0] - qkv_done).median()))
+    acc["q_polled_max"].append(float((a[m, 0] - qkv_done).max()))
+    acc["keys_done_max"].append(float((a[m, 2] - qkv_done).max()))
+    acc["keys_dur_med"].append(float((a[m, 2] - a[m, 1]).median()))
+    acc["published_max"].append(float((tl[m, 4 * l, 3] - qkv_done).max()))
+print("attention vs last qkv epilogue:", {k: round(stt.mean(v), 2) for k, v in acc.items()})
