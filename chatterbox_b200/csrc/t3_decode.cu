@@ -168,7 +168,11 @@ template <int OFF>
 __device__ __forceinline__ void ll_ld2_off(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
   asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2+%3];" : "=l"(a), "=l"(b) : "l"(p), "n"(OFF) : "memory");
 }
+#ifdef T3_ABL_NOPOLL   // ablation build (timing only, results are garbage): every word counts as arrived
+__device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned flag) { return true; }
+#else
 __device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned flag) { return (unsigned)(w >> 32) == flag; }
+#endif
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)w); }
 
 // watchdog bookkeeping of a poll loop; returns true when the caller must give up
@@ -205,13 +209,21 @@ __device__ __forceinline__ void ll_poll(const unsigned long long* (&ptr)[N], int
 
 // ---- activation slices ---------------------------------------------------------------------------
 // Warp w owns k in [128w, 128w + 128) of the two activation rows (CFG cond / uncond); lane owns row
-// lane >> 4 and the 8 consecutive k at 128w + (lane & 15) * 8.
+// lane >> 4 and the VPL/2 PAIRS of k at 128w + 2 (lane & 15) + 32 r (r = 0..VPL/2-1): element e of its slice is
+// k = kq + 32 (e >> 1) + (e & 1).  Consecutive lanes read consecutive 16-byte LL packets, so one warp-wide poll
+// instruction touches 4 cache lines, not 16: the LSU issues one wavefront per line, and with 8 consecutive words
+// per lane a poll round of the 8 warps cost ~1 us in wavefronts alone (measured by ablation).
 
-// x[e] = sum over np (<= 4) pieces, `stride` words apart, of the 8 LL words at base (fixed order -> deterministic
-// sum).  One instance serves every phase: all loads of a round are in flight together.
+// x[e] = sum over np (<= 4) pieces, `stride` words apart, of this lane's LL words (base already points at its first
+// pair; fixed order -> deterministic sum).  One instance serves every phase: all loads of a round are in flight together.
 __device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long long* base, size_t stride, int np, unsigned flag,
                                          bool active, Ctl* ctl, T3State* st) {
   unsigned long long w[4][VPL];
+#ifdef T3_ABL_NOLOAD
+#pragma unroll
+  for (int e = 0; e < VPL; ++e) x[e] = 0.001f * e;
+  return;
+#endif
   if (active) {
     unsigned spins = 0; unsigned long long t0 = 0;
     for (;;) {
@@ -221,10 +233,10 @@ __device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long lo
         if (q < np) {
           const unsigned long long* pq = base + q * stride;
           ll_ld2_off<0>(pq, w[q][0], w[q][1]);
-          ll_ld2_off<16>(pq, w[q][2], w[q][3]);
+          ll_ld2_off<256>(pq, w[q][2], w[q][3]);
           if constexpr (VPL == 8) {
-            ll_ld2_off<32>(pq, w[q][VPL - 4], w[q][VPL - 3]);
-            ll_ld2_off<48>(pq, w[q][VPL - 2], w[q][VPL - 1]);
+            ll_ld2_off<512>(pq, w[q][VPL - 4], w[q][VPL - 3]);
+            ll_ld2_off<768>(pq, w[q][VPL - 2], w[q][VPL - 1]);
           }
         }
       }
@@ -250,9 +262,15 @@ __device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long lo
 // B fragments of the warp's k-slice: Bf[s][0..1] for k16 step s.  Column n = lane >> 2 of the MMA is
 // {row0 hi, row0 lo, row1 hi, row1 lo, 0, 0, 0, 0}; the slice goes through a 1 KB per-warp tile.
 __device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[VPL][2], const float (&x)[VPL], float* xt, int lane) {
+#ifdef T3_ABL_NOFRAGS
+#pragma unroll
+  for (int s = 0; s < VPL; ++s) { Bf[s][0] = __float_as_uint(x[s]); Bf[s][1] = 0u; }
+  return;
+#endif
   __syncwarp();     // previous readers of the tile are done
-  *reinterpret_cast<float4*>(xt + lane * VPL) = make_float4(x[0], x[1], x[2], x[3]);
-  if constexpr (VPL == 8) *reinterpret_cast<float4*>(xt + lane * VPL + 4) = make_float4(x[VPL - 4], x[VPL - 3], x[VPL - 2], x[VPL - 1]);
+  float* dstx = xt + (lane >> 4) * (16 * VPL) + (lane & 15) * 2;
+#pragma unroll
+  for (int r = 0; r < VPL / 2; ++r) *reinterpret_cast<float2*>(dstx + 32 * r) = make_float2(x[2 * r], x[2 * r + 1]);
   __syncwarp();
   const int g = lane >> 2, tig = lane & 3;
 #pragma unroll
@@ -289,13 +307,12 @@ __device__ __forceinline__ float rms_scale(const float* ssq, int b) {
   for (int w = 0; w < NCONS_WARPS; ++w) tot += ssq[w * 2 + b];
   return rsqrtf(tot * (1.0f / T3_H) + RMS_EPS);
 }
-// 8 norm gains of this lane's k range, fetched one phase ahead into registers
+// norm gains (or any fp32 vector) at this lane's k pairs, fetched one phase ahead into registers
 __device__ __forceinline__ void ln_fetch(float (&g)[VPL], const float* __restrict__ lnw, int k) {
-  const float4 a = __ldcg(reinterpret_cast<const float4*>(lnw + k));      // L2 only: keep the small L1 for the stack
-  g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w;
-  if constexpr (VPL == 8) {
-    const float4 b = __ldcg(reinterpret_cast<const float4*>(lnw + k + 4));
-    g[VPL - 4] = b.x; g[VPL - 3] = b.y; g[VPL - 2] = b.z; g[VPL - 1] = b.w;
+#pragma unroll
+  for (int r = 0; r < VPL / 2; ++r) {
+    const float2 a = __ldcg(reinterpret_cast<const float2*>(lnw + k + 32 * r));      // L2 only: keep the small L1 for the stack
+    g[2 * r] = a.x; g[2 * r + 1] = a.y;
   }
 }
 
@@ -310,6 +327,9 @@ struct Stream {
 };
 // copy the next unit of the stream into `slot` (one thread); no-op past the end of the stream
 __device__ __forceinline__ void stream_issue_next(const Stream& sm, Ctl* ctl, int slot, uint8_t* ring, uint64_t* full) {
+#ifdef T3_ABL_NOUNITS
+  return;
+#endif
   const int it = ctl->next_iter;
   if (it >= sm.n_iters) return;
   const int idx = ctl->next_idx;
@@ -329,6 +349,10 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
   const int g = lane >> 2, tig = lane & 3;
 #pragma unroll 1
   for (int j = 0; j < n; ++j) {
+#ifdef T3_ABL_NOUNITS
+    if (tig < 2) { float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g; dst[0] = 0.f; dst[8] = 0.f; }
+    continue;
+#endif
     mbar_wait(&full[rp.slot], rp.parity, ctl, st);
     const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * (VPL * 32) + lane;
     uint4 w[VPL];
@@ -441,6 +465,9 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
   const int npairs = p.B * T3_NH;
   const int S = attn_splits(G, p.B);
   if (c >= S * npairs) return;
+#ifdef T3_ABL_NOATTN
+  return;
+#endif
   const int pair = c % npairs, split = c / npairs, b = pair / T3_NH, head = pair % T3_NH;
   float* q_s = scr;                       // [64] (pre-scaled by 1/8)
   float* k_new = scr + 64;                // [64]
@@ -596,28 +623,33 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
   }
 }
 
-// o_proj prologue: merge the S split-KV partials of (row b, head) for this lane's 8 head dims
+// o_proj prologue: merge the S split-KV partials of (row b, head) for this lane's k pairs.  Pair r of the lane
+// sits in head (kq >> 6) + (r >> 1) at d = (kq & 63) + 32 (r & 1): the 128-wide slice of a warp spans HPS heads.
+constexpr int HPS = (16 * VPL) / 64;      // heads per warp slice (2, or 1 with 16 warps)
+static_assert(HPS == 1 || HPS == 2, "slice layout");
 template <int SI>
 struct PartLoad {
   static __device__ __forceinline__ void issue(const unsigned long long* bo, const unsigned long long* bm, int S,
-                                               unsigned long long (&wo)[MAXS][VPL], unsigned long long (&wm)[MAXS],
-                                               unsigned long long (&wl)[MAXS]) {
+                                               unsigned long long (&wo)[MAXS][VPL], unsigned long long (&wm)[MAXS][HPS],
+                                               unsigned long long (&wl)[MAXS][HPS]) {
     if (SI < S) {
+      // the next head of the same row lies MAXS * PART_STRIDE words further
       ll_ld2_off<(SI * PART_STRIDE + 0) * 8>(bo, wo[SI][0], wo[SI][1]);
-      ll_ld2_off<(SI * PART_STRIDE + 2) * 8>(bo, wo[SI][2], wo[SI][3]);
+      ll_ld2_off<(SI * PART_STRIDE + 32) * 8>(bo, wo[SI][2], wo[SI][3]);
+      ll_ld2_off<(SI * PART_STRIDE + 64) * 8>(bm, wm[SI][0], wl[SI][0]);
       if constexpr (VPL == 8) {
-        ll_ld2_off<(SI * PART_STRIDE + 4) * 8>(bo, wo[SI][VPL - 4], wo[SI][VPL - 3]);
-        ll_ld2_off<(SI * PART_STRIDE + 6) * 8>(bo, wo[SI][VPL - 2], wo[SI][VPL - 1]);
+        ll_ld2_off<((MAXS + SI) * PART_STRIDE + 0) * 8>(bo, wo[SI][VPL - 4], wo[SI][VPL - 3]);
+        ll_ld2_off<((MAXS + SI) * PART_STRIDE + 32) * 8>(bo, wo[SI][VPL - 2], wo[SI][VPL - 1]);
+        ll_ld2_off<((MAXS + SI) * PART_STRIDE + 64) * 8>(bm, wm[SI][HPS - 1], wl[SI][HPS - 1]);
       }
-      ll_ld2_off<(SI * PART_STRIDE + 64) * 8>(bm, wm[SI], wl[SI]);
     }
     if constexpr (SI + 1 < MAXS) PartLoad<SI + 1>::issue(bo, bm, S, wo, wm, wl);
   }
 };
 __device__ __forceinline__ void attn_combine8(float (&x)[VPL], const T3Params& p, int S, int b, int k, unsigned flag, bool active,
                                               Ctl* ctl) {
-  unsigned long long wo[MAXS][VPL], wm[MAXS], wl[MAXS];
-  const int head = k >> 6, d = k & 63;
+  unsigned long long wo[MAXS][VPL], wm[MAXS][HPS], wl[MAXS][HPS];
+  const int head = k >> 6, d = k & 63;       // first head of the slice; d = 2 (lane & 15) (+ 64-slices: see HPS)
   const unsigned long long* base = p.ll + LL_PART + ((size_t)(b * T3_NH + head) * MAXS) * PART_STRIDE;
   if (active) {
     unsigned spins = 0; unsigned long long t0 = 0;
@@ -629,32 +661,35 @@ __device__ __forceinline__ void attn_combine8(float (&x)[VPL], const T3Params& p
         if (s < S) {
 #pragma unroll
           for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(wo[s][e], flag);
-          ok = ok && ll_ok(wm[s], flag) && ll_ok(wl[s], flag);
+#pragma unroll
+          for (int h = 0; h < HPS; ++h) ok = ok && ll_ok(wm[s][h], flag) && ll_ok(wl[s][h], flag);
         }
       }
       if (ok) break;
       if (poll_timeout(spins, t0, ctl, p.st)) break;
     }
   }
-  float Mx = -INFINITY;
 #pragma unroll
-  for (int s = 0; s < MAXS; ++s) if (s < S && active) Mx = fmaxf(Mx, ll_val(wm[s]));
-  float Lt = 0.f;
+  for (int h = 0; h < HPS; ++h) {
+    float Mx = -INFINITY;
 #pragma unroll
-  for (int e = 0; e < VPL; ++e) x[e] = 0.f;
+    for (int s = 0; s < MAXS; ++s) if (s < S && active) Mx = fmaxf(Mx, ll_val(wm[s][h]));
+    float Lt = 0.f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int s = 0; s < MAXS; ++s) {
-    if (s < S && active) {
-      const float ms = ll_val(wm[s]);
-      const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
-      Lt += cw * ll_val(wl[s]);
+    for (int s = 0; s < MAXS; ++s) {
+      if (s < S && active) {
+        const float ms = ll_val(wm[s][h]);
+        const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
+        Lt += cw * ll_val(wl[s][h]);
 #pragma unroll
-      for (int e = 0; e < VPL; ++e) x[e] += cw * ll_val(wo[s][e]);
+        for (int e = 0; e < 4; ++e) acc[e] += cw * ll_val(wo[s][(VPL == 8 ? 4 * h : 0) + e]);
+      }
     }
-  }
-  const float inv = (active && Lt > 0.f) ? 1.0f / Lt : 0.f;
+    const float inv = (active && Lt > 0.f) ? 1.0f / Lt : 0.f;
 #pragma unroll
-  for (int e = 0; e < VPL; ++e) x[e] *= inv;
+    for (int e = 0; e < 4; ++e) x[(VPL == 8 ? 4 * h : 0) + e] = acc[e] * inv;
+  }
 }
 
 // ---- sampling phase (CTA 0): t3.py:320-356 ------------------------------------------------------
@@ -700,7 +735,11 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
   const bool cfg = sp.cfg_weight > 0.f && p.B == 2;
   // 1. CFG, temperature, repetition penalty; running max (first index on ties)
   float lmax = -INFINITY; int imax = 0x7fffffff;
+#ifdef T3_ABL_NOSAMPLE
+  constexpr int NK = 0;
+#else
   constexpr int NK = (T3_VOCAB + NCONS - 1) / NCONS;   // 33
+#endif
   const unsigned lfl = ll_flag(it - 1, L, L, LLP_LOGITS);
   for (int k0 = 0; k0 < NK; k0 += 8) {
     float cv[8], uv[8];
@@ -829,6 +868,9 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
     tok = ri[16];
   }
   if (p.forced) tok = p.forced[it];
+#if defined(T3_ABL_NOPOLL) || defined(T3_ABL_NOUNITS)
+  tok = (unsigned)(tok + it) % 6000u;
+#endif
   const bool stop = sp.stop_on_eos && tok == STOP_SPEECH;
   if (tid == 0) {
     p.tokens_out[it] = tok;
@@ -893,7 +935,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   __syncthreads();
 
   const int b = lane >> 4;                        // activation row (CFG cond / uncond) of this lane
-  const int kq = warp * (16 * VPL) + (lane & 15) * VPL;    // its VPL consecutive k in a 1024-wide vector
+  const int kq = warp * (16 * VPL) + (lane & 15) * 2;      // its first k pair in a 1024-wide vector (the others: + 32 r)
   const bool active = b < p.B;
   float* xt = reinterpret_cast<float*>(smem + SMEM_XT) + warp * (32 * VPL);
   const int S = attn_splits(G, p.B);
@@ -1002,7 +1044,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       }
       T3_SUB(4);
       // ---------- epilogue: cross-warp sum, scale / SwiGLU, publish ----------
+#ifdef T3_ABL_NOEPI
+      if (false) {
+#else
       if (tid < n * 32) {
+#endif
         const int j = tid >> 5, o = tid & 31, bb = o >> 4, row = o & 15;
         const int u = ctl->plan_u[ph][j];
         float v = red_sum(red, j, o);
