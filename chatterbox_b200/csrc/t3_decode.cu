@@ -40,6 +40,9 @@
 namespace {
 
 constexpr int NSLOT = 4;                  // ring depth (32 KB units)
+#ifndef T3_PF_DIST
+#define T3_PF_DIST 6                      // L2 prefetch distance in units (0 = off)
+#endif
 constexpr int NCONS_WARPS = T3_KW;
 constexpr int VPL = 1024 / NCONS_WARPS / 16;   // consecutive k one lane owns (8 or 4) = k16 steps of a warp's k-slice
 static_assert(VPL == 8 || VPL == 4, "T3_KW must be 8 or 16");
@@ -327,7 +330,7 @@ struct Stream {
 };
 // copy the next unit of the stream into `slot` (one thread); no-op past the end of the stream
 __device__ __forceinline__ void stream_issue_next(const Stream& sm, Ctl* ctl, int slot, uint8_t* ring, uint64_t* full) {
-#ifdef T3_ABL_NOUNITS
+#if defined(T3_ABL_NOUNITS) || defined(T3_ABL_NOSTREAM)
   return;
 #endif
   const int it = ctl->next_iter;
@@ -336,6 +339,21 @@ __device__ __forceinline__ void stream_issue_next(const Stream& sm, Ctl* ctl, in
   mbar_arrive_expect_tx(&full[slot], T3_UNIT_BYTES);
   tma_bulk_g2s(ring + slot * T3_UNIT_BYTES, sm.base + (size_t)idx * T3_UNIT_BYTES, T3_UNIT_BYTES, &full[slot], sm.policy);
   const int end = sm.per_iter_layers + (it >= sm.head_from_iter ? sm.nhead : 0);
+#if T3_PF_DIST > 0
+  // The ring (128 KB) holds about half a layer of this CTA's weights, and all CTAs re-arm in the same microsecond
+  // (the hand-overs keep them in lockstep), so HBM sees bursts it cannot serve in time.  The unit T3_PF_DIST ahead is
+  // therefore pulled into L2 now: the ring's own copies then hit L2, and HBM streams a layer or two ahead of the
+  // dependency chain.  (Next iteration = same addresses; a wrong guess at the prefill/decode seam is harmless.)
+  {
+    int pf = idx + T3_PF_DIST;
+    if (pf >= end) pf -= end;
+#ifdef T3_PF_HINT
+    if (pf < end) l2_prefetch_bulk(sm.base + (size_t)pf * T3_UNIT_BYTES, T3_UNIT_BYTES, sm.policy);
+#else
+    if (pf < end) l2_prefetch_bulk(sm.base + (size_t)pf * T3_UNIT_BYTES, T3_UNIT_BYTES);
+#endif
+  }
+#endif
   if (idx + 1 == end) { ctl->next_idx = 0; ctl->next_iter = it + 1; }
   else ctl->next_idx = idx + 1;
 }
@@ -353,7 +371,9 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
     if (tig < 2) { float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g; dst[0] = 0.f; dst[8] = 0.f; }
     continue;
 #endif
+#if !defined(T3_ABL_NOSTREAM) && !defined(T3_ABL_NOWAIT)    // timing-only builds: MMAs on whatever the ring holds
     mbar_wait(&full[rp.slot], rp.parity, ctl, st);
+#endif
     const uint4* wp = reinterpret_cast<const uint4*>(ring + rp.slot * T3_UNIT_BYTES) + warp * (VPL * 32) + lane;
     uint4 w[VPL];
 #pragma unroll
@@ -868,7 +888,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
     tok = ri[16];
   }
   if (p.forced) tok = p.forced[it];
-#if defined(T3_ABL_NOPOLL) || defined(T3_ABL_NOUNITS)
+#if defined(T3_ABL_NOPOLL) || defined(T3_ABL_NOUNITS) || defined(T3_ABL_NOSTREAM) || defined(T3_ABL_NOWAIT)
   tok = (unsigned)(tok + it) % 6000u;
 #endif
   const bool stop = sp.stop_on_eos && tok == STOP_SPEECH;
@@ -924,6 +944,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     for (int s = 0; s < NSLOT; ++s) mbar_init(&full[s], 1);
     ctl->abort = 0; ctl->next_idx = 0; ctl->next_iter = 0;
     mbar_fence_init();
+#if T3_PF_DIST > 0
+    for (int u = NSLOT; u < T3_PF_DIST && u < sm.per_iter_layers; ++u) l2_prefetch_bulk(sm.base + (size_t)u * T3_UNIT_BYTES, T3_UNIT_BYTES);
+#endif
     for (int s = 0; s < NSLOT; ++s) stream_issue_next(sm, ctl, s, ring, full);
   }
   if (tid < PH_COUNT * T3_MAXU) {
