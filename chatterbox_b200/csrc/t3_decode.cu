@@ -479,7 +479,7 @@ __device__ __forceinline__ int attn_splits(int G, int B) {
 #define T3_ATL(k) do {} while (0)
 #endif
 template <typename KVT>
-__device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, int pos0, float* scr, int warp, int lane,
+__device__ __noinline__ void attn_phase_stream(const T3Params& p, int it, int layer, int pos0, float* scr, int warp, int lane,
                                         Ctl* ctl) {
   const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x, L = p.n_layers;
   const int npairs = p.B * T3_NH;
@@ -640,6 +640,163 @@ __device__ __noinline__ void attn_phase(const T3Params& p, int it, int layer, in
       KV<KVT>::store(vc + (size_t)pos0 * 64 + d, vr);
       __threadfence();
     }
+  }
+}
+
+// ---- phase B, short contexts (bf16 slab, <= ATT_TP past positions per split): two-pass softmax on a tile ----
+// Same contract as attn_phase_stream.  The split's K/V rows are copied into shared memory before the wait for q (as
+// above) but as plain [position][64] tiles, the position's own key/value becomes one more row, and the work is laid
+// out to shorten the dependency chain instead of streaming: (1) every score at once, 4 threads per position;
+// (2) each warp takes the max / exponentials / sum of ALL positions redundantly (same order -> bit-identical in
+// all warps, so no barrier is needed to agree on m and l); (3) warp w accumulates output dims 8w..8w+7 over all
+// positions (a lane owns positions lane + 32 k and their p in registers) and a 9-shuffle reduce-scatter leaves
+// one dim in every fourth lane, which publishes it.  Two CTA barriers, no online rescaling, no cross-warp merge.
+constexpr int ATT_TP = 96;                       // past positions a tile holds (+ 1 row for the position itself)
+constexpr int ATT_RS = 72;                       // tile row stride in bf16 (144 B: 16-byte column reads of 32 rows are conflict-free)
+constexpr int ATT_TILE_OFF = 1024;               // bytes: q_s [64] fp32, scores [128] fp32 before the tiles
+static_assert(ATT_TILE_OFF + 2 * (ATT_TP + 1) * ATT_RS * 2 <= SCRATCH_BYTES, "attention tiles fit the scratch area");
+__device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int layer, int pos0, float* scr, int warp, int lane,
+                                             Ctl* ctl) {
+  const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x, L = p.n_layers;
+  const int npairs = p.B * T3_NH;
+  const int S = attn_splits(G, p.B);
+  if (c >= S * npairs) return;
+#ifdef T3_ABL_NOATTN
+  return;
+#endif
+  const int pair = c % npairs, split = c / npairs, b = pair / T3_NH, head = pair % T3_NH;
+  float* q_s = scr;                        // [64], pre-scaled by 1/8
+  float* s_sm = scr + 64;                  // [128] scores
+  __nv_bfloat16* kt = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<uint8_t*>(scr) + ATT_TILE_OFF);
+  __nv_bfloat16* vt = kt + (ATT_TP + 1) * ATT_RS;
+  __nv_bfloat16* kc = reinterpret_cast<__nv_bfloat16*>(p.kcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
+  __nv_bfloat16* vc = reinterpret_cast<__nv_bfloat16*>(p.vcache) + ((size_t)(layer * 2 + b) * T3_NH + head) * p.max_pos * T3_HD;
+  const int chunk = (pos0 + S - 1) / S;
+  const int lo = split * chunk;
+  const int hi = min(pos0, lo + chunk);
+  const int n = max(hi - lo, 0);           // past positions of this split (<= ATT_TP, checked by the caller)
+  const bool last = split == S - 1;
+  const int nrows = n + (last ? 1 : 0);
+  // 1. tiles on their way (16-byte pieces: row = piece / 8)
+  for (int ch = tid; ch < n * 8; ch += NCONS) {
+    const int r = ch >> 3, c8 = ch & 7;
+    const uint32_t dk = smem_u32(kt + r * ATT_RS + c8 * 8), dv = smem_u32(vt + r * ATT_RS + c8 * 8);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dk), "l"(kc + (size_t)(lo + r) * 64 + c8 * 8) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dv), "l"(vc + (size_t)(lo + r) * 64 + c8 * 8) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  // 2. q, k, v of this position: RoPE; the new key / value row joins the tile of the last split
+  float kr = 0.f, vr = 0.f;
+  if (tid < 64) {
+    const int d = tid;
+    const float cs = __ldg(p.rope_cos + (size_t)pos0 * 32 + (d & 31));
+    const float sn = __ldg(p.rope_sin + (size_t)pos0 * 32 + (d & 31));
+    const unsigned long long* row = p.ll + LL_QKV + (size_t)b * 3072 + head * 64;
+    const unsigned long long* ptr[5] = {row + d, row + (d ^ 32), row + 1024 + d, row + 1024 + (d ^ 32),
+                                              row + 2048 + d};
+    unsigned long long w[5];
+    ll_poll<5>(ptr, 5, ll_flag(it, L, layer, LLP_QKV), w, ctl, p.st);
+    const float q = ll_val(w[0]), qo = ll_val(w[1]), k = ll_val(w[2]), ko = ll_val(w[3]), v = ll_val(w[4]);
+    const float qr = q * cs + (d < 32 ? -qo : qo) * sn;
+    kr = KV<__nv_bfloat16>::round(k * cs + (d < 32 ? -ko : ko) * sn);
+    vr = KV<__nv_bfloat16>::round(v);
+    q_s[d] = qr * 0.125f;
+    if (last) { kt[n * ATT_RS + d] = __float2bfloat16_rn(kr); vt[n * ATT_RS + d] = __float2bfloat16_rn(vr); }
+  }
+  T3_ATL(0);
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  cbar();
+  T3_ATL(1);
+  // 3. scores: thread -> (position tid >> 2 (+ 64), 16 dims)
+  {
+    const int qd = tid & 3;
+    float qv[16];
+#pragma unroll
+    for (int e = 0; e < 16; e += 4) {
+      const float4 t4 = *reinterpret_cast<const float4*>(q_s + qd * 16 + e);
+      qv[e] = t4.x; qv[e + 1] = t4.y; qv[e + 2] = t4.z; qv[e + 3] = t4.w;
+    }
+#pragma unroll
+    for (int rr = 0; rr < 2; ++rr) {
+      const int i = (tid >> 2) + 64 * rr;
+      float acc = 0.f;
+      if (i < nrows) {
+        float kf[8];
+        KV<__nv_bfloat16>::lds8(kt + i * ATT_RS + qd * 16, kf);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc += qv[e] * kf[e];
+        KV<__nv_bfloat16>::lds8(kt + i * ATT_RS + qd * 16 + 8, kf);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc += qv[8 + e] * kf[e];
+      }
+      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+      if (qd == 0 && i < nrows) s_sm[i] = acc;
+    }
+  }
+  T3_ATL(2);
+  cbar();
+  // 4. max, exponentials, sum: every warp over all rows (lane owns rows lane + 32 k)
+  float pk[4];
+  float M = -INFINITY;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = lane + 32 * k;
+    pk[k] = (i < nrows) ? s_sm[i] : -INFINITY;
+    M = fmaxf(M, pk[k]);
+  }
+  M = warp_max(M);
+  float lsum = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { pk[k] = (pk[k] == -INFINITY) ? 0.f : __expf(pk[k] - M); lsum += pk[k]; }
+  lsum = warp_sum(lsum);
+  // 5. output dims 8 warp .. 8 warp + 7
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int i = lane + 32 * k;
+    if (i < nrows) {
+      float vf[8];
+      KV<__nv_bfloat16>::lds8(vt + i * ATT_RS + warp * 8, vf);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += pk[k] * vf[e];
+    }
+  }
+  // reduce-scatter over the 32 lanes: 8 -> 4 -> 2 -> 1 values, then two plain steps; lane 4 j ends with dim j
+  {
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+    float a4[4], a2[2], a1;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float send = h16 ? acc[e] : acc[4 + e];
+      const float got = __shfl_xor_sync(0xffffffffu, send, 16);
+      a4[e] = (h16 ? acc[4 + e] : acc[e]) + got;
+    }
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const float send = h8 ? a4[e] : a4[2 + e];
+      const float got = __shfl_xor_sync(0xffffffffu, send, 8);
+      a2[e] = (h8 ? a4[2 + e] : a4[e]) + got;
+    }
+    {
+      const float send = h4 ? a2[0] : a2[1];
+      const float got = __shfl_xor_sync(0xffffffffu, send, 4);
+      a1 = (h4 ? a2[1] : a2[0]) + got;
+    }
+    a1 += __shfl_xor_sync(0xffffffffu, a1, 2);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
+    const unsigned fl = ll_flag(it, L, layer, LLP_PART);
+    unsigned long long* out = p.ll + LL_PART + ((size_t)pair * MAXS + split) * PART_STRIDE;
+    if ((lane & 3) == 0) ll_store(out + warp * 8 + (lane >> 2), a1, fl);
+    if (warp == 0 && lane == 1) { ll_store(out + 64, M, fl); ll_store(out + 65, lsum, fl); }
+  }
+  // KV append after the partial is on its way; the fence orders it before this CTA's later LL stores
+  if (last && tid < 64) {
+    kc[(size_t)pos0 * 64 + tid] = __float2bfloat16_rn(kr);
+    vc[(size_t)pos0 * 64 + tid] = __float2bfloat16_rn(vr);
+    __threadfence();
   }
 }
 
@@ -1109,7 +1266,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       T3_PROF();
       // ---------- RoPE, KV append, split-KV attention between the qkv and o_proj steps ----------
       if (ph == PH_QKV) {
-        attn_phase<KVT>(*ps, it, l, pos0, scr, warp, lane, ctl);
+        bool tile_path = false;
+        if constexpr (sizeof(KVT) == 2) tile_path = (pos0 + S - 1) / S <= ATT_TP;
+#ifdef T3_ATTN_STREAM
+        tile_path = false;
+#endif
+        if (tile_path) attn_phase_tile(*ps, it, l, pos0, scr, warp, lane, ctl);
+        else attn_phase_stream<KVT>(*ps, it, l, pos0, scr, warp, lane, ctl);
         T3_TL(3);
         T3_PROF();
       }
