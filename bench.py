@@ -98,6 +98,20 @@ class ClockSampler:
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def _ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of the decode launch (same 256-token workload) from the latest
+    committed `ncu --set full` capture (profiles/*_t3_ncu_traffic.json); None if no capture is committed."""
+    import glob
+    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_t3_ncu_traffic.json")))
+    if not files:
+        return None
+    try:
+        with open(files[-1]) as f:
+            return json.load(f)["traffic_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def _decode_bytes(weight_bytes: int, P: int, n: int) -> int:
     """Algorithmic HBM bytes of one decode launch of n tokens starting at cache length P:
     per token: every weight once + KV read of the cached context + KV write of one position."""
@@ -322,7 +336,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                 "clocks": clocks,
                 "roofline": {"kernel": "t3_megakernel<bf16,1> (one decode launch = 256 tokens)", "bound": "hbm",
                              "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": peak_src,
+                             "traffic": _ncu_traffic(), "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": dbytes, "launch_ms": d_ms,
                              "share_of_step": d_ms / (total_ms / args.steps)},
                 "stages_ms": stages,

@@ -39,7 +39,10 @@
 
 namespace {
 
-constexpr int NSLOT = 4;                  // ring depth (32 KB units)
+#ifndef T3_NSLOT
+#define T3_NSLOT 4                        // 5 measured 1 % slower (the L1 left for the stack shrinks to ~4 KB)
+#endif
+constexpr int NSLOT = T3_NSLOT;           // ring depth (32 KB units)
 #ifndef T3_PF_DIST
 #define T3_PF_DIST 6                      // L2 prefetch distance in units (0 = off)
 #endif
@@ -1131,7 +1134,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   int prof_k = 0;
   int par = 0;          // parity of the running step counter: red / ssq double buffer
   ln_fetch(gn, p.ln1, kq);
+#ifdef T3_NO_PROF
+#define T3_PROF() do {} while (0)
+#else
 #define T3_PROF() do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it) p.prof[prof_k++] = gtime_ns(); } while (0)
+#endif
 // timeline build (-DT3_TIMELINE, tools/t3_timeline.py): thread 0 of EVERY CTA stamps prologue / consume / epilogue
 // end of every step at prof[1024 + c * 1024 + 4 * step + k].  Off by default: even the dead test costs ~5 %.
 #ifdef T3_TIMELINE
@@ -1140,8 +1147,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
 #else
 #define T3_TL(k) do {} while (0)
 #endif
+#ifdef T3_NO_PROF
+#define T3_SUB(k) do {} while (0)
+#else
 #define T3_SUB(k) do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5 && (ph == PH_QKV || ph == PH_GU)) \
                          p.prof[200 + (ph == PH_GU ? 8 : 0) + (k)] = gtime_ns(); } while (0)
+#endif
 
   for (int it = 0; it < n_iters; ++it) {
     if (p.mode == 1) {

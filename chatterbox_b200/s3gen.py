@@ -36,6 +36,36 @@ class S3Gen:
         self.mel2wav = HiFTGenerator(hift_sd, self.device, max_frames=max_mel_len)
         self.record_events = False
         self.events: Dict[str, torch.cuda.Event] = {}
+        # token front-end replayed as a CUDA graph from its second call with the same lengths (it is ~300 small
+        # library launches: launch-bound when run eagerly); `front_graphs = False` keeps it eager
+        self.front_graphs = True
+        self._front_cache: Dict[tuple, dict] = {}
+
+    def _front(self, tok, prompt_token, prompt_feat, embedding):
+        """flow_frontend.flow_inputs, eager on the first call for a (T, Tp, 2Tp) shape, captured on the second,
+        replayed afterwards.  The returned tensors of a replay are the graph's static outputs: they are consumed
+        by the CFM solve on the same stream before the next replay can overwrite them."""
+        args = (tok, prompt_token, prompt_feat, embedding)
+        if not self.front_graphs:
+            return flow_frontend.flow_inputs(self.front, *args)
+        key = (tok.shape[1], prompt_token.shape[1], prompt_feat.shape[1])
+        ent = self._front_cache.get(key)
+        if ent is None:
+            if len(self._front_cache) >= 8:          # bound the captured pools
+                self._front_cache.pop(next(iter(self._front_cache)))
+            self._front_cache[key] = {"graph": None}
+            return flow_frontend.flow_inputs(self.front, *args)
+        if ent["graph"] is None:
+            static = [a.clone() for a in args]
+            g = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize(self.device)
+            with torch.cuda.graph(g):
+                outs = flow_frontend.flow_inputs(self.front, *static)
+            ent.update(graph=g, static=static, outs=outs)
+        for dst, src in zip(ent["static"], args):
+            dst.copy_(src)
+        ent["graph"].replay()
+        return ent["outs"]
 
     @classmethod
     def from_state_dict(cls, sd: Dict[str, torch.Tensor], device="cuda", **kw) -> "S3Gen":
@@ -68,8 +98,8 @@ class S3Gen:
         ev = {k: torch.cuda.Event(enable_timing=True) for k in ("front0", "cfm0", "cfm1")} if self.record_events else None
         if ev:
             ev["front0"].record()
-        mu, spks, cond, mel_len1 = flow_frontend.flow_inputs(self.front, tok.long(), ref["prompt_token"].long(),
-                                                             ref["prompt_feat"].float(), ref["embedding"].float())
+        mu, spks, cond, mel_len1 = self._front(tok.long(), ref["prompt_token"].long(), ref["prompt_feat"].float(),
+                                               ref["embedding"].float())
         if ev:
             ev["cfm0"].record()
         L = mu.shape[2]

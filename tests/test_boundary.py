@@ -111,3 +111,21 @@ def test_vc_generate(tts):
     assert wav.shape == (1, 960 * 20) and wav.device.type == "cpu"
     with pytest.raises(NotImplementedError):
         vc.generate("some.wav")
+
+
+@pytest.mark.gpu
+def test_front_end_graph_replay_equals_eager(tts):
+    """The token front-end runs eagerly on the first call for a shape, is captured on the second and replayed from
+    the third: every variant must give the eager mel for the tokens of THAT call (the static input buffers are
+    refreshed before a replay)."""
+    ref = S.s3gen_ref(seed=4, prompt_len=20)
+    s3 = tts.s3gen
+    toks = [S.speech_tokens(31, seed=s) for s in (11, 12, 13, 14)]
+    s3.front_graphs = False
+    want = [s3.flow_inference(t, ref_dict=ref).clone() for t in toks]
+    s3.front_graphs = True
+    s3._front_cache.clear()
+    got = [s3.flow_inference(t, ref_dict=ref).clone() for t in toks]      # eager, capture + replay, replay, replay
+    assert s3._front_cache[(31, 20, 40)]["graph"] is not None
+    for w, g in zip(want, got):       # library GEMMs may pick another algorithm under capture: fp32 rounding only
+        assert float((w - g).norm() / w.norm()) < 1e-4
