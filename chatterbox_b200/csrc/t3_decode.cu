@@ -71,7 +71,10 @@ constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set
 // block itself would make the compiler keep it on the stack and turn every p.field in the step loop into a local
 // load (L1 is small here: a miss costs an L2 round trip on the critical path)
 constexpr int SMEM_PARAMS = SMEM_SEEN + VOCAB_PAD;
-constexpr int SMEM_TOTAL = SMEM_PARAMS + 512;
+// norm gains of the NEXT RMSNorm, copied a phase ahead by cp.async (warp w copies exactly the 128 gains its own lanes
+// read, so a warp-level sync is enough).  In registers they were 8 long-lived values the compiler spilled every step.
+constexpr int SMEM_GN = SMEM_PARAMS + 512;
+constexpr int SMEM_TOTAL = SMEM_GN + T3_H * 4;
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
 static_assert(2 * NCONS_WARPS * 2 * 4 <= 256, "ssq buffer");
 static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
@@ -320,6 +323,21 @@ __device__ __forceinline__ void ln_fetch(float (&g)[VPL], const float* __restric
     const float2 a = __ldcg(reinterpret_cast<const float2*>(lnw + k + 32 * r));      // L2 only: keep the small L1 for the stack
     g[2 * r] = a.x; g[2 * r + 1] = a.y;
   }
+}
+
+// copy the 128 gains of this warp's k-slice into shared memory (lane -> 16 bytes); gn_wait before reading them
+__device__ __forceinline__ void gn_prefetch(float* gn_s, const float* __restrict__ lnw, int warp, int lane) {
+  __syncwarp();       // the warp's reads of the previous gains are done
+  const int k = warp * (16 * VPL) + lane * (VPL / 2);
+  if constexpr (VPL == 8)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(gn_s + k)), "l"(lnw + k) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(gn_s + k)), "l"(lnw + k) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void gn_wait() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncwarp();
 }
 
 // The weight stream of one CTA: every iteration walks the L layers' units, iterations >= head_from_iter walk the
@@ -1129,11 +1147,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   int n_done = 0;
   float xres[VPL];      // residual stream slice, replicated in every CTA
   float x[VPL];
-  float gn[VPL];         // gains of the next RMSNorm (fetched a phase ahead)
+  float* gn_s = reinterpret_cast<float*>(smem + SMEM_GN);     // gains of the next RMSNorm (copied a phase ahead)
   uint32_t Bf[VPL][2];
   int prof_k = 0;
   int par = 0;          // parity of the running step counter: red / ssq double buffer
-  ln_fetch(gn, p.ln1, kq);
+  gn_prefetch(gn_s, p.ln1, warp, lane);
 #ifdef T3_NO_PROF
 #define T3_PROF() do {} while (0)
 #else
@@ -1206,13 +1224,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
 #pragma unroll
         for (int e = 0; e < VPL; ++e) xres[e] += x[e];
         ssq_partial(xres, ssq, warp, lane);
+        gn_wait();
 #pragma unroll
-        for (int e = 0; e < VPL; ++e) x[e] = xres[e] * gn[e];
+        for (int r = 0; r < VPL / 2; ++r) {
+          const float2 g2 = *reinterpret_cast<const float2*>(gn_s + kq + 32 * r);
+          x[2 * r] = xres[2 * r] * g2.x; x[2 * r + 1] = xres[2 * r + 1] * g2.y;
+        }
         const float* nxt;
         if (ph == PH_QKV) nxt = p.ln2 + (size_t)l * T3_H;
         else if (ph == PH_GU) nxt = (l == L - 1 && with_head) ? p.final_norm : p.ln1 + (size_t)((l + 1) % L) * T3_H;
         else nxt = p.ln1;
-        ln_fetch(gn, nxt, kq);
+        gn_prefetch(gn_s, nxt, warp, lane);
       }
       make_bfrags(Bf, x, xt, lane);
       T3_SUB(2);
