@@ -66,15 +66,21 @@ constexpr int SMEM_SSQ = SMEM_RED + 2 * RED_FLOATS * 4;      // [2][warps][2 row
 constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [warps][2 rows][16 VPL] activation slices (fragment build)
 constexpr int SMEM_SCRATCH = SMEM_XT + NCONS_WARPS * 2 * 16 * VPL * 4;   // attention scratch / sampling logits (union)
 constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
-constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0)
+constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0), one bit per id
+constexpr int SEEN_WORDS = (VOCAB_PAD + 31) / 32;
+constexpr int SEEN_BYTES = (SEEN_WORDS * 4 + 15) / 16 * 16;
 // copy of the kernel parameters for the out-of-line phases (attention, sampling): a reference to the parameter
 // block itself would make the compiler keep it on the stack and turn every p.field in the step loop into a local
 // load (L1 is small here: a miss costs an L2 round trip on the critical path)
-constexpr int SMEM_PARAMS = SMEM_SEEN + VOCAB_PAD;
+constexpr int SMEM_PARAMS = SMEM_SEEN + SEEN_BYTES;
 // norm gains of the NEXT RMSNorm, copied a phase ahead by cp.async (warp w copies exactly the 128 gains its own lanes
 // read, so a warp-level sync is enough).  In registers they were 8 long-lived values the compiler spilled every step.
 constexpr int SMEM_GN = SMEM_PARAMS + 512;
-constexpr int SMEM_TOTAL = SMEM_GN + T3_H * 4;
+// residual stream (this CTA's replica, [warps][2 rows][16 VPL] like the fragment tile): 8 values per lane that live
+// for a whole token and are touched in 3 of 5 steps — in registers the compiler spilled them to local memory
+constexpr int SMEM_XR = SMEM_GN + T3_H * 4;
+constexpr int SMEM_TOTAL = SMEM_XR + NCONS_WARPS * 2 * 16 * VPL * 4;
+static_assert(SMEM_TOTAL + 1024 <= 196 * 1024, "stay inside the 196 KB carve-out: the rest of the 256 KB is L1 for the stack");
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
 static_assert(2 * NCONS_WARPS * 2 * 4 <= 256, "ssq buffer");
 static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
@@ -924,7 +930,7 @@ __device__ __forceinline__ unsigned f2ord(float f) {
 }
 
 // Processes the pending logits of the CFG pair and emits token `it`.  All NCONS threads of CTA 0.
-__device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, unsigned char* seen, Ctl* ctl, int warp,
+__device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, unsigned* seen, Ctl* ctl, int warp,
                              int lane) {
   const int tid = threadIdx.x, L = p.n_layers;
   float* rs = sl + VOCAB_PAD;          // reduction scratch (64 floats)
@@ -983,7 +989,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
         }
         float x = cfg ? c + sp.cfg_weight * (c - u) : c;
         if (sp.temperature != 1.0f) x = x / sp.temperature;
-        if (seen[i]) x = (x < 0.f) ? x * sp.repetition_penalty : x / sp.repetition_penalty;
+        if ((seen[i >> 5] >> (i & 31)) & 1u) x = (x < 0.f) ? x * sp.repetition_penalty : x / sp.repetition_penalty;
         sl[i] = x;
         if (x > lmax) { lmax = x; imax = i; }
       }
@@ -1072,7 +1078,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
   const bool stop = sp.stop_on_eos && tok == STOP_SPEECH;
   if (tid == 0) {
     p.tokens_out[it] = tok;
-    seen[tok] = 1;
+    seen[tok >> 5] |= 1u << (tok & 31);
     p.seen[tok] = 1;
     if (stop) p.st->stop = 1;
   }
@@ -1103,7 +1109,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   float* red_all = reinterpret_cast<float*>(smem + SMEM_RED);
   float* ssq_all = reinterpret_cast<float*>(smem + SMEM_SSQ);
   float* scr = reinterpret_cast<float*>(smem + SMEM_SCRATCH);
-  unsigned char* seen = smem + SMEM_SEEN;
+  unsigned* seen = reinterpret_cast<unsigned*>(smem + SMEM_SEEN);
   T3Params* ps = reinterpret_cast<T3Params*>(smem + SMEM_PARAMS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -1132,7 +1138,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     if (j == 0) ctl->plan_n[ph] = n;
     ctl->plan_u[ph][j] = j < n ? t3_plan_unit(ph, c, G, j) : 0;
   }
-  if (c == 0) for (int i = tid; i < VOCAB_PAD; i += NTHREADS) seen[i] = p.seen[i];
+  if (c == 0)      // byte set in global memory (crosses launches) -> bit set: one ballot per 32 ids
+    for (int i = tid; i < SEEN_WORDS * 32; i += NTHREADS) {
+      const unsigned m = __ballot_sync(0xffffffffu, i < VOCAB_PAD && p.seen[i] != 0);
+      if ((tid & 31) == 0) seen[i >> 5] = m;
+    }
   __syncthreads();
 
   const int b = lane >> 4;                        // activation row (CFG cond / uncond) of this lane
@@ -1145,7 +1155,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   int pos0 = __ldcg(&p.st->pos);
   int n_gen = __ldcg(&p.st->n_gen);
   int n_done = 0;
-  float xres[VPL];      // residual stream slice, replicated in every CTA
+  // residual stream slice (replicated in every CTA): this lane's pairs, at + 32 r floats
+  float* xr = reinterpret_cast<float*>(smem + SMEM_XR) + warp * (32 * VPL) + (lane >> 4) * (16 * VPL) + (lane & 15) * 2;
   float x[VPL];
   float* gn_s = reinterpret_cast<float*>(smem + SMEM_GN);     // gains of the next RMSNorm (copied a phase ahead)
   uint32_t Bf[VPL][2];
@@ -1190,7 +1201,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       T3_PROF();
     }
 #pragma unroll
-    for (int e = 0; e < VPL; ++e) xres[e] = 0.f;
+    for (int r = 0; r < VPL / 2; ++r) *reinterpret_cast<float2*>(xr + 32 * r) = make_float2(0.f, 0.f);
     const bool with_head = (p.mode == 1) || (it == n_iters - 1);
     const int n_steps = 4 * L + (with_head ? 1 : 0);
 
@@ -1222,13 +1233,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       // ---------- residual add + RMSNorm gain (the scale is applied in the epilogue) ----------
       if (ph == PH_QKV || ph == PH_GU || ph == PH_HEAD) {
 #pragma unroll
-        for (int e = 0; e < VPL; ++e) xres[e] += x[e];
-        ssq_partial(xres, ssq, warp, lane);
+        for (int r = 0; r < VPL / 2; ++r) {
+          float2 v = *reinterpret_cast<const float2*>(xr + 32 * r);
+          v.x += x[2 * r]; v.y += x[2 * r + 1];
+          *reinterpret_cast<float2*>(xr + 32 * r) = v;
+          x[2 * r] = v.x; x[2 * r + 1] = v.y;
+        }
+        ssq_partial(x, ssq, warp, lane);
         gn_wait();
 #pragma unroll
         for (int r = 0; r < VPL / 2; ++r) {
           const float2 g2 = *reinterpret_cast<const float2*>(gn_s + kq + 32 * r);
-          x[2 * r] = xres[2 * r] * g2.x; x[2 * r + 1] = xres[2 * r + 1] * g2.y;
+          x[2 * r] *= g2.x; x[2 * r + 1] *= g2.y;
         }
         const float* nxt;
         if (ph == PH_QKV) nxt = p.ln2 + (size_t)l * T3_H;
