@@ -63,8 +63,8 @@ constexpr int SMEM_CTL = SMEM_BARS + 256;       // control words
 constexpr int SMEM_RED = SMEM_CTL + 256;        // [2 phase parities][MAXU][warps][32] k-slice partials
 constexpr int RED_FLOATS = T3_MAXU * NCONS_WARPS * 32;
 constexpr int SMEM_SSQ = SMEM_RED + 2 * RED_FLOATS * 4;      // [2][warps][2 rows] partial sums of squares
-constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [warps][2 rows][16 VPL] activation slices (fragment build)
-constexpr int SMEM_SCRATCH = SMEM_XT + NCONS_WARPS * 2 * 16 * VPL * 4;   // attention scratch / sampling logits (union)
+constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [warps][XT_WORDS] packed hi/lo activation fragments
+constexpr int SMEM_SCRATCH = SMEM_XT + (NCONS_WARPS * (2 * (2 * 4 * (2 * VPL + 4) + 4)) * 4 + 15) / 16 * 16;   // fragment tiles (XT_WORDS per warp); then attention scratch / sampling logits (union)
 constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
 constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0), one bit per id
 constexpr int SEEN_WORDS = (VOCAB_PAD + 31) / 32;
@@ -275,32 +275,45 @@ __device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long lo
 }
 
 // B fragments of the warp's k-slice: Bf[s][0..1] for k16 step s.  Column n = lane >> 2 of the MMA is
-// {row0 hi, row0 lo, row1 hi, row1 lo, 0, 0, 0, 0}; the slice goes through a 1 KB per-warp tile.
-__device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[VPL][2], const float (&x)[VPL], float* xt, int lane) {
+// {row0 hi, row0 lo, row1 hi, row1 lo, 0, 0, 0, 0}.  The OWNING lane splits its pairs into packed bf16x2 hi / lo
+// words (all 32 lanes busy, 6 instructions per pair) and scatters them into a per-warp tile laid out in fragment
+// order [plane hi|lo][row][tig][k16 step][half]; lane (g < 4, tig) then fetches its 16 fragment words with four
+// 128-bit loads and no arithmetic.  (Splitting after the transpose cost 212 instructions per step on the 16 reading
+// lanes, 22 % of all instructions of the kernel.)  Strides are padded so the scattered stores are conflict-free.
+constexpr int XT_T = 2 * VPL + 4;            // words per tig
+constexpr int XT_R = 4 * XT_T;               // per row
+constexpr int XT_P = 2 * XT_R + 4;           // per plane
+constexpr int XT_WORDS = 2 * XT_P;           // per warp
+static_assert(XT_T % 4 == 0 && XT_P % 4 == 0 && XT_WORDS % 4 == 0, "128-bit fragment loads");
+__device__ __forceinline__ void make_bfrags(uint32_t (&Bf)[VPL][2], const float (&x)[VPL], uint32_t* xt, int lane) {
 #ifdef T3_ABL_NOFRAGS
 #pragma unroll
   for (int s = 0; s < VPL; ++s) { Bf[s][0] = __float_as_uint(x[s]); Bf[s][1] = 0u; }
   return;
 #endif
   __syncwarp();     // previous readers of the tile are done
-  float* dstx = xt + (lane >> 4) * (16 * VPL) + (lane & 15) * 2;
+  {
+    const int j = lane & 15;
+    // k_local = 2 j + 32 r: k16 step 2 r + (j >> 3), tig = j & 3, half = (j >> 2) & 1
+    uint32_t* dst = xt + (lane >> 4) * XT_R + (j & 3) * XT_T + (j >> 3) * 2 + ((j >> 2) & 1);
 #pragma unroll
-  for (int r = 0; r < VPL / 2; ++r) *reinterpret_cast<float2*>(dstx + 32 * r) = make_float2(x[2 * r], x[2 * r + 1]);
+    for (int r = 0; r < VPL / 2; ++r) {
+      uint32_t hi, lo;
+      split_hi_lo(x[2 * r], x[2 * r + 1], hi, lo);
+      dst[4 * r] = hi;
+      dst[XT_P + 4 * r] = lo;
+    }
+  }
   __syncwarp();
   const int g = lane >> 2, tig = lane & 3;
 #pragma unroll
   for (int s = 0; s < VPL; ++s) { Bf[s][0] = 0u; Bf[s][1] = 0u; }
   if (g < 4) {
-    const float* src = xt + (g >> 1) * (16 * VPL) + 2 * tig;
+    const uint4* src = reinterpret_cast<const uint4*>(xt + (g & 1) * XT_P + (g >> 1) * XT_R + tig * XT_T);
 #pragma unroll
-    for (int s = 0; s < VPL; ++s) {
-      const float2 v0 = *reinterpret_cast<const float2*>(src + 16 * s);
-      const float2 v1 = *reinterpret_cast<const float2*>(src + 16 * s + 8);
-      uint32_t h0, l0, h1, l1;
-      split_hi_lo(v0.x, v0.y, h0, l0);
-      split_hi_lo(v1.x, v1.y, h1, l1);
-      Bf[s][0] = (g & 1) ? l0 : h0;
-      Bf[s][1] = (g & 1) ? l1 : h1;
+    for (int i = 0; i < VPL / 2; ++i) {
+      const uint4 v = src[i];
+      Bf[2 * i][0] = v.x; Bf[2 * i][1] = v.y; Bf[2 * i + 1][0] = v.z; Bf[2 * i + 1][1] = v.w;
     }
   }
 }
@@ -392,12 +405,50 @@ struct RingPos { int slot; uint32_t parity; long long k; };
 __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t (&Bf)[VPL][2], float* red, uint8_t* ring,
                                               uint64_t* full, const Stream& sm, int warp, int lane, Ctl* ctl, T3State* st) {
   const int g = lane >> 2, tig = lane & 3;
+#ifdef T3_ABL_NOUNITS
+  for (int j = 0; j < n; ++j)
+    if (tig < 2) { float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g; dst[0] = 0.f; dst[8] = 0.f; }
+  return;
+#endif
+#ifdef T3_UNIT_PIPE
+  // Software pipeline over the units of a step: the shared-memory loads of unit j + 1 are in flight while the MMAs
+  // of unit j issue (rolled loop, register copy between the two fragment sets).
+  uint4 wn[VPL];
+  int slot = rp.slot; uint32_t par = rp.parity;
+  const int lofs = warp * (VPL * 32) + lane;
+  if (n > 0) {
+    mbar_wait(&full[slot], par, ctl, st);
+    const uint4* wp = reinterpret_cast<const uint4*>(ring + slot * T3_UNIT_BYTES) + lofs;
+#pragma unroll
+    for (int s = 0; s < VPL; ++s) wn[s] = wp[s * 32];
+  }
 #pragma unroll 1
   for (int j = 0; j < n; ++j) {
-#ifdef T3_ABL_NOUNITS
-    if (tig < 2) { float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g; dst[0] = 0.f; dst[8] = 0.f; }
-    continue;
-#endif
+    uint4 w[VPL];
+#pragma unroll
+    for (int s = 0; s < VPL; ++s) w[s] = wn[s];
+    if (++slot == NSLOT) { slot = 0; par ^= 1u; }
+    if (j + 1 < n) {
+      mbar_wait(&full[slot], par, ctl, st);
+      const uint4* wp = reinterpret_cast<const uint4*>(ring + slot * T3_UNIT_BYTES) + lofs;
+#pragma unroll
+      for (int s = 0; s < VPL; ++s) wn[s] = wp[s * 32];
+    }
+    float c[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { c[q][0] = 0.f; c[q][1] = 0.f; c[q][2] = 0.f; c[q][3] = 0.f; }
+#pragma unroll
+    for (int s = 0; s < VPL; ++s) mma_bf16_16816(c[s & 3], w[s].x, w[s].y, w[s].z, w[s].w, Bf[s][0], Bf[s][1]);
+    if (tig < 2) {
+      float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g;
+      dst[0] = ((c[0][0] + c[0][1]) + (c[1][0] + c[1][1])) + ((c[2][0] + c[2][1]) + (c[3][0] + c[3][1]));
+      dst[8] = ((c[0][2] + c[0][3]) + (c[1][2] + c[1][3])) + ((c[2][2] + c[2][3]) + (c[3][2] + c[3][3]));
+    }
+  }
+  rp.slot = slot; rp.parity = par; rp.k += n;
+#else
+#pragma unroll 1
+  for (int j = 0; j < n; ++j) {
 #if !defined(T3_ABL_NOSTREAM) && !defined(T3_ABL_NOWAIT)    // timing-only builds: MMAs on whatever the ring holds
     mbar_wait(&full[rp.slot], rp.parity, ctl, st);
 #endif
@@ -418,6 +469,7 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
     if (++rp.slot == NSLOT) { rp.slot = 0; rp.parity ^= 1u; }
     ++rp.k;
   }
+#endif
 }
 
 __device__ __forceinline__ float red_sum(const float* red, int j, int o) {
@@ -1148,7 +1200,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   const int b = lane >> 4;                        // activation row (CFG cond / uncond) of this lane
   const int kq = warp * (16 * VPL) + (lane & 15) * 2;      // its first k pair in a 1024-wide vector (the others: + 32 r)
   const bool active = b < p.B;
-  float* xt = reinterpret_cast<float*>(smem + SMEM_XT) + warp * (32 * VPL);
+  uint32_t* xt = reinterpret_cast<uint32_t*>(smem + SMEM_XT) + warp * XT_WORDS;
   const int S = attn_splits(G, p.B);
   const int down_slice = ctl->plan_u[PH_DOWN][0] % T3_DOWN_KS;
   RingPos rp{0, 0u, 0ll};
