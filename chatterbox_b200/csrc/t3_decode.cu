@@ -231,47 +231,54 @@ __device__ __forceinline__ void ll_poll(const unsigned long long* (&ptr)[N], int
 
 // x[e] = sum over np (<= 4) pieces, `stride` words apart, of this lane's LL words (base already points at its first
 // pair; fixed order -> deterministic sum).  One instance serves every phase: all loads of a round are in flight together.
-__device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long long* base, size_t stride, int np, unsigned flag,
-                                         bool active, Ctl* ctl, T3State* st) {
-  unsigned long long w[4][VPL];
-#ifdef T3_ABL_NOLOAD
-#pragma unroll
-  for (int e = 0; e < VPL; ++e) x[e] = 0.001f * e;
-  return;
-#endif
+template <int NP>
+__device__ __forceinline__ void ll_load8_n(float (&x)[VPL], const unsigned long long* base, size_t stride, unsigned flag,
+                                           bool active, Ctl* ctl, T3State* st) {
+  unsigned long long w[NP][VPL];
   if (active) {
     unsigned spins = 0; unsigned long long t0 = 0;
     for (;;) {
       bool ok = true;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (q < np) {
-          const unsigned long long* pq = base + q * stride;
-          ll_ld2_off<0>(pq, w[q][0], w[q][1]);
-          ll_ld2_off<256>(pq, w[q][2], w[q][3]);
-          if constexpr (VPL == 8) {
-            ll_ld2_off<512>(pq, w[q][VPL - 4], w[q][VPL - 3]);
-            ll_ld2_off<768>(pq, w[q][VPL - 2], w[q][VPL - 1]);
-          }
+      for (int q = 0; q < NP; ++q) {
+        const unsigned long long* pq = base + q * stride;
+        ll_ld2_off<0>(pq, w[q][0], w[q][1]);
+        ll_ld2_off<256>(pq, w[q][2], w[q][3]);
+        if constexpr (VPL == 8) {
+          ll_ld2_off<512>(pq, w[q][VPL - 4], w[q][VPL - 3]);
+          ll_ld2_off<768>(pq, w[q][VPL - 2], w[q][VPL - 1]);
         }
       }
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if (q < np) {
+      for (int q = 0; q < NP; ++q) {
 #pragma unroll
-          for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(w[q][e], flag);
-        }
+        for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(w[q][e], flag);
+      }
       if (ok) break;
       if (poll_timeout(spins, t0, ctl, st)) break;
     }
-  }
 #pragma unroll
-  for (int e = 0; e < VPL; ++e) {
-    float sum = 0.f;
+    for (int e = 0; e < VPL; ++e) {
+      float sum = ll_val(w[0][e]);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) sum += (active && q < np) ? ll_val(w[q][e]) : 0.f;
-    x[e] = sum;
+      for (int q = 1; q < NP; ++q) sum += ll_val(w[q][e]);
+      x[e] = sum;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < VPL; ++e) x[e] = 0.f;
   }
+}
+// the two piece counts the kernel uses get their own straight-line code (no per-word selects on np)
+__device__ __forceinline__ void ll_load8(float (&x)[VPL], const unsigned long long* base, size_t stride, int np, unsigned flag,
+                                         bool active, Ctl* ctl, T3State* st) {
+#ifdef T3_ABL_NOLOAD
+#pragma unroll
+  for (int e = 0; e < VPL; ++e) x[e] = 0.001f * e;
+  return;
+#endif
+  if (np == 1) ll_load8_n<1>(x, base, stride, flag, active, ctl, st);
+  else ll_load8_n<T3_DOWN_KS>(x, base, stride, flag, active, ctl, st);
 }
 
 // B fragments of the warp's k-slice: Bf[s][0..1] for k16 step s.  Column n = lane >> 2 of the MMA is
@@ -1212,10 +1219,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   float x[VPL];
   float* gn_s = reinterpret_cast<float*>(smem + SMEM_GN);     // gains of the next RMSNorm (copied a phase ahead)
   uint32_t Bf[VPL][2];
-  int prof_k = 0;
+  [[maybe_unused]] int prof_k = 0;
   int par = 0;          // parity of the running step counter: red / ssq double buffer
   gn_prefetch(gn_s, p.ln1, warp, lane);
-#ifdef T3_NO_PROF
+#ifndef T3_PROFILE     // phase stamps (tools/t3_phase_times.py) only in -DT3_PROFILE builds: even dead tests cost issue slots
 #define T3_PROF() do {} while (0)
 #else
 #define T3_PROF() do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it) p.prof[prof_k++] = gtime_ns(); } while (0)
@@ -1228,7 +1235,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
 #else
 #define T3_TL(k) do {} while (0)
 #endif
-#ifdef T3_NO_PROF
+#ifndef T3_PROFILE
 #define T3_SUB(k) do {} while (0)
 #else
 #define T3_SUB(k) do { if (p.prof && c == 0 && tid == 0 && it == p.prof_it && l == 5 && (ph == PH_QKV || ph == PH_GU)) \

@@ -1,4 +1,5 @@
-"""Per-phase timing of one decode iteration of the T3 megakernel (CTA 0 %globaltimer stamps)."""
+"""Per-phase timing of one decode iteration of the T3 megakernel (CTA 0 %globaltimer stamps).
+Needs a profiling build of the library: CBX_NVCC_EXTRA=-DT3_PROFILE python -m chatterbox_b200.build --force"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
