@@ -417,43 +417,6 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
     if (tig < 2) { float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g; dst[0] = 0.f; dst[8] = 0.f; }
   return;
 #endif
-#ifdef T3_UNIT_PIPE
-  // Software pipeline over the units of a step: the shared-memory loads of unit j + 1 are in flight while the MMAs
-  // of unit j issue (rolled loop, register copy between the two fragment sets).
-  uint4 wn[VPL];
-  int slot = rp.slot; uint32_t par = rp.parity;
-  const int lofs = warp * (VPL * 32) + lane;
-  if (n > 0) {
-    mbar_wait(&full[slot], par, ctl, st);
-    const uint4* wp = reinterpret_cast<const uint4*>(ring + slot * T3_UNIT_BYTES) + lofs;
-#pragma unroll
-    for (int s = 0; s < VPL; ++s) wn[s] = wp[s * 32];
-  }
-#pragma unroll 1
-  for (int j = 0; j < n; ++j) {
-    uint4 w[VPL];
-#pragma unroll
-    for (int s = 0; s < VPL; ++s) w[s] = wn[s];
-    if (++slot == NSLOT) { slot = 0; par ^= 1u; }
-    if (j + 1 < n) {
-      mbar_wait(&full[slot], par, ctl, st);
-      const uint4* wp = reinterpret_cast<const uint4*>(ring + slot * T3_UNIT_BYTES) + lofs;
-#pragma unroll
-      for (int s = 0; s < VPL; ++s) wn[s] = wp[s * 32];
-    }
-    float c[4][4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) { c[q][0] = 0.f; c[q][1] = 0.f; c[q][2] = 0.f; c[q][3] = 0.f; }
-#pragma unroll
-    for (int s = 0; s < VPL; ++s) mma_bf16_16816(c[s & 3], w[s].x, w[s].y, w[s].z, w[s].w, Bf[s][0], Bf[s][1]);
-    if (tig < 2) {
-      float* dst = red + (j * NCONS_WARPS + warp) * 32 + tig * 16 + g;
-      dst[0] = ((c[0][0] + c[0][1]) + (c[1][0] + c[1][1])) + ((c[2][0] + c[2][1]) + (c[3][0] + c[3][1]));
-      dst[8] = ((c[0][2] + c[0][3]) + (c[1][2] + c[1][3])) + ((c[2][2] + c[2][3]) + (c[3][2] + c[3][3]));
-    }
-  }
-  rp.slot = slot; rp.parity = par; rp.k += n;
-#else
 #pragma unroll 1
   for (int j = 0; j < n; ++j) {
 #if !defined(T3_ABL_NOSTREAM) && !defined(T3_ABL_NOWAIT)    // timing-only builds: MMAs on whatever the ring holds
@@ -476,7 +439,6 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
     if (++rp.slot == NSLOT) { rp.slot = 0; rp.parity ^= 1u; }
     ++rp.k;
   }
-#endif
 }
 
 __device__ __forceinline__ float red_sum(const float* red, int j, int o) {
@@ -890,66 +852,61 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
 // sits in head (kq >> 6) + (r >> 1) at d = (kq & 63) + 32 (r & 1): the 128-wide slice of a warp spans HPS heads.
 constexpr int HPS = (16 * VPL) / 64;      // heads per warp slice (2, or 1 with 16 warps)
 static_assert(HPS == 1 || HPS == 2, "slice layout");
-template <int SI>
-struct PartLoad {
-  static __device__ __forceinline__ void issue(const unsigned long long* bo, const unsigned long long* bm, int S,
-                                               unsigned long long (&wo)[MAXS][VPL], unsigned long long (&wm)[MAXS][HPS],
-                                               unsigned long long (&wl)[MAXS][HPS]) {
-    if (SI < S) {
-      // the next head of the same row lies MAXS * PART_STRIDE words further
-      ll_ld2_off<(SI * PART_STRIDE + 0) * 8>(bo, wo[SI][0], wo[SI][1]);
-      ll_ld2_off<(SI * PART_STRIDE + 32) * 8>(bo, wo[SI][2], wo[SI][3]);
-      ll_ld2_off<(SI * PART_STRIDE + 64) * 8>(bm, wm[SI][0], wl[SI][0]);
-      if constexpr (VPL == 8) {
-        ll_ld2_off<((MAXS + SI) * PART_STRIDE + 0) * 8>(bo, wo[SI][VPL - 4], wo[SI][VPL - 3]);
-        ll_ld2_off<((MAXS + SI) * PART_STRIDE + 32) * 8>(bo, wo[SI][VPL - 2], wo[SI][VPL - 1]);
-        ll_ld2_off<((MAXS + SI) * PART_STRIDE + 64) * 8>(bm, wm[SI][HPS - 1], wl[SI][HPS - 1]);
-      }
-    }
-    if constexpr (SI + 1 < MAXS) PartLoad<SI + 1>::issue(bo, bm, S, wo, wm, wl);
-  }
-};
-__device__ __forceinline__ void attn_combine8(float (&x)[VPL], const T3Params& p, int S, int b, int k, unsigned flag, bool active,
+// (S == MAXS on every supported device: cbx_t3_create requires >= 129 SMs, so S = min(MAXS, G / (B 16)) = MAXS; the
+// split count is a compile-time constant here and the merge is straight-line code.)
+__device__ __forceinline__ void attn_combine8(float (&x)[VPL], const T3Params& p, int b, int k, unsigned flag, bool active,
                                               Ctl* ctl) {
   unsigned long long wo[MAXS][VPL], wm[MAXS][HPS], wl[MAXS][HPS];
-  const int head = k >> 6, d = k & 63;       // first head of the slice; d = 2 (lane & 15) (+ 64-slices: see HPS)
-  const unsigned long long* base = p.ll + LL_PART + ((size_t)(b * T3_NH + head) * MAXS) * PART_STRIDE;
-  if (active) {
-    unsigned spins = 0; unsigned long long t0 = 0;
-    for (;;) {
-      bool ok = true;
-      PartLoad<0>::issue(base + d, base, S, wo, wm, wl);
+  const int head = k >> 6, d = k & 63;       // first head of the slice; d = 2 (lane & 15)
+  const unsigned long long* bm = p.ll + LL_PART + ((size_t)(b * T3_NH + head) * MAXS) * PART_STRIDE;
+  const unsigned long long* bo = bm + d;
+  if (!active) {
 #pragma unroll
-      for (int s = 0; s < MAXS; ++s) {
-        if (s < S) {
+    for (int e = 0; e < VPL; ++e) x[e] = 0.f;
+    return;
+  }
+  unsigned spins = 0; unsigned long long t0 = 0;
+  for (;;) {
+    bool ok = true;
 #pragma unroll
-          for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(wo[s][e], flag);
-#pragma unroll
-          for (int h = 0; h < HPS; ++h) ok = ok && ll_ok(wm[s][h], flag) && ll_ok(wl[s][h], flag);
-        }
+    for (int s = 0; s < MAXS; ++s) {
+      const unsigned long long* po = bo + s * PART_STRIDE;
+      const unsigned long long* pm = bm + s * PART_STRIDE;
+      ll_ld2_off<0>(po, wo[s][0], wo[s][1]);
+      ll_ld2_off<32 * 8>(po, wo[s][2], wo[s][3]);
+      ll_ld2_off<64 * 8>(pm, wm[s][0], wl[s][0]);
+      if constexpr (VPL == 8) {     // the next head of the same row lies MAXS * PART_STRIDE words further
+        ll_ld2_off<(MAXS * PART_STRIDE) * 8>(po, wo[s][VPL - 4], wo[s][VPL - 3]);
+        ll_ld2_off<(MAXS * PART_STRIDE + 32) * 8>(po, wo[s][VPL - 2], wo[s][VPL - 1]);
+        ll_ld2_off<(MAXS * PART_STRIDE + 64) * 8>(pm, wm[s][HPS - 1], wl[s][HPS - 1]);
       }
-      if (ok) break;
-      if (poll_timeout(spins, t0, ctl, p.st)) break;
     }
+#pragma unroll
+    for (int s = 0; s < MAXS; ++s) {
+#pragma unroll
+      for (int e = 0; e < VPL; ++e) ok = ok && ll_ok(wo[s][e], flag);
+#pragma unroll
+      for (int h = 0; h < HPS; ++h) ok = ok && ll_ok(wm[s][h], flag) && ll_ok(wl[s][h], flag);
+    }
+    if (ok) break;
+    if (poll_timeout(spins, t0, ctl, p.st)) break;
   }
 #pragma unroll
   for (int h = 0; h < HPS; ++h) {
     float Mx = -INFINITY;
 #pragma unroll
-    for (int s = 0; s < MAXS; ++s) if (s < S && active) Mx = fmaxf(Mx, ll_val(wm[s][h]));
+    for (int s = 0; s < MAXS; ++s) Mx = fmaxf(Mx, ll_val(wm[s][h]));
     float Lt = 0.f;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int s = 0; s < MAXS; ++s) {
-      if (s < S && active) {
-        const float ms = ll_val(wm[s][h]);
-        const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
-        Lt += cw * ll_val(wl[s][h]);
+      const float ms = ll_val(wm[s][h]);
+      const float cw = (ms == -INFINITY) ? 0.f : __expf(ms - Mx);
+      Lt += cw * ll_val(wl[s][h]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) acc[e] += cw * ll_val(wo[s][(VPL == 8 ? 4 * h : 0) + e]);
-      }
+      for (int e = 0; e < 4; ++e) acc[e] += cw * ll_val(wo[s][(VPL == 8 ? 4 * h : 0) + e]);
     }
-    const float inv = (active && Lt > 0.f) ? 1.0f / Lt : 0.f;
+    const float inv = (Lt > 0.f) ? 1.0f / Lt : 0.f;
 #pragma unroll
     for (int e = 0; e < 4; ++e) x[(VPL == 8 ? 4 * h : 0) + e] = acc[e] * inv;
   }
@@ -1274,7 +1231,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       T3_SUB(0);
       if (ph == PH_O) {
         // CTAs without an o_proj unit do not need the attention output at all (x only feeds the fragments)
-        attn_combine8(x, p, S, b, kq, ll_flag(it, L, l, LLP_PART), active && ctl->plan_n[PH_O] > 0, ctl);
+        attn_combine8(x, p, b, kq, ll_flag(it, L, l, LLP_PART), active && ctl->plan_n[PH_O] > 0, ctl);
       } else if (ph == PH_QKV && l == 0 && p.mode == 0) {
 #pragma unroll
         for (int e = 0; e < VPL; ++e) x[e] = 0.f;
@@ -1456,6 +1413,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CHECK(prop.major == 10, "cbx_t3_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
   const int G = prop.multiProcessorCount;
   CBX_CHECK(G >= 129 && (513 + G - 1) / G <= T3_MAXU, "cbx_t3_create: %d SMs unsupported by the plan", G);
+  CBX_CHECK(G / (2 * T3_NH) >= MAXS, "cbx_t3_create: %d SMs give fewer than %d KV splits", G, MAXS);
   int coop = 0;
   CBX_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, cfg->device));
   CBX_CHECK(coop, "cbx_t3_create: device lacks cooperative launch");
