@@ -80,7 +80,7 @@ constexpr int SMEM_GN = SMEM_PARAMS + 512;
 // for a whole token and are touched in 3 of 5 steps — in registers the compiler spilled them to local memory
 constexpr int SMEM_XR = SMEM_GN + T3_H * 4;
 constexpr int SMEM_TOTAL = SMEM_XR + NCONS_WARPS * 2 * 16 * VPL * 4;
-static_assert(SMEM_TOTAL + 1024 <= 196 * 1024, "stay inside the 196 KB carve-out: the rest of the 256 KB is L1 for the stack");
+static_assert(NSLOT > 4 || SMEM_TOTAL + 1024 <= 196 * 1024, "4-slot build: stay inside the 196 KB carve-out (the rest of the 256 KB is L1)");
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
 static_assert(2 * NCONS_WARPS * 2 * 4 <= 256, "ssq buffer");
 static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
@@ -946,6 +946,11 @@ __device__ __forceinline__ unsigned f2ord(float f) {
 }
 
 // Processes the pending logits of the CFG pair and emits token `it`.  All NCONS threads of CTA 0.
+#ifdef T3_PROFILE
+#define T3_SPROF(k) do { if (p.prof && threadIdx.x == 0 && it == p.prof_it) p.prof[300 + (k)] = gtime_ns(); } while (0)
+#else
+#define T3_SPROF(k) do {} while (0)
+#endif
 __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, unsigned* seen, Ctl* ctl, int warp,
                              int lane) {
   const int tid = threadIdx.x, L = p.n_layers;
@@ -953,6 +958,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
   int* ri = reinterpret_cast<int*>(rs + 32);
   const CbxSampleParams& sp = p.sp;
   const bool cfg = sp.cfg_weight > 0.f && p.B == 2;
+  T3_SPROF(0);
   // 1. CFG, temperature, repetition penalty; running max (first index on ties)
   float lmax = -INFINITY; int imax = 0x7fffffff;
 #ifdef T3_ABL_NOSAMPLE
@@ -961,56 +967,63 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
   constexpr int NK = (T3_VOCAB + NCONS - 1) / NCONS;   // 33
 #endif
   const unsigned lfl = ll_flag(it - 1, L, L, LLP_LOGITS);
-  for (int k0 = 0; k0 < NK; k0 += 8) {
-    float cv[8], uv[8];
+  // Every field this loop needs is copied into registers first: `p` is a shared-memory copy, and after each polling
+  // asm (a compiler barrier) or store to sl[] the compiler would have to reload p.B, p.ll, sp.* from it again, each a
+  // dependent shared-memory round trip in front of the next load (measured: 16 us of the 18 us of this phase).
+  const int B2 = p.B == 2;
+  const unsigned long long* llc = p.ll + LL_LOGITS;
+  const unsigned long long* llu = llc + VOCAB_PAD;
+  const float* plog = p.logits;
+  float* lout = p.logits_out;
+  const float cfgw = sp.cfg_weight, temp = sp.temperature, rpen = sp.repetition_penalty;
+  T3State* stp = p.st;
+  constexpr int KB = 11;                  // words per row in flight per thread: 33 = 3 batches
+  for (int k0 = 0; k0 < NK; k0 += KB) {
+    float cv[KB], uv[KB];
     if (it == 0) {   // logits of the previous launch (prefill or an earlier decode call)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
+      for (int k = 0; k < KB; ++k) {
         const int i = tid + (k0 + k) * NCONS;
-        cv[k] = (i < T3_VOCAB) ? __ldcg(p.logits + i) : 0.f;
-        uv[k] = (i < T3_VOCAB && p.B == 2) ? __ldcg(p.logits + T3_VOCAB + i) : 0.f;
+        cv[k] = (i < T3_VOCAB) ? __ldcg(plog + i) : 0.f;
+        uv[k] = (i < T3_VOCAB && B2) ? __ldcg(plog + T3_VOCAB + i) : 0.f;
       }
     } else {
-      unsigned long long wc[8], wu[8];
+      unsigned long long wc[KB], wu[KB];
       unsigned spins = 0; unsigned long long t0 = 0;
       for (;;) {
         bool ok = true;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const int i = tid + (k0 + k) * NCONS;
-          if (i < T3_VOCAB) {
-            wc[k] = ll_ld1(p.ll + LL_LOGITS + i);
-            if (p.B == 2) wu[k] = ll_ld1(p.ll + LL_LOGITS + VOCAB_PAD + i);
-          }
+        for (int k = 0; k < KB; ++k) {
+          const int i = min(tid + (k0 + k) * NCONS, T3_VOCAB - 1);    // tail threads re-read the last word: no branch
+          wc[k] = ll_ld1(llc + i);
+          wu[k] = ll_ld1((B2 ? llu : llc) + i);
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const int i = tid + (k0 + k) * NCONS;
-          if (i < T3_VOCAB) ok = ok && ll_ok(wc[k], lfl) && (p.B != 2 || ll_ok(wu[k], lfl));
-        }
+        for (int k = 0; k < KB; ++k) ok = ok && ll_ok(wc[k], lfl) && ll_ok(wu[k], lfl);
         if (ok) break;
-        if (poll_timeout(spins, t0, ctl, p.st)) break;
+        if (poll_timeout(spins, t0, ctl, stp)) break;
       }
 #pragma unroll
-      for (int k = 0; k < 8; ++k) { cv[k] = ll_val(wc[k]); uv[k] = (p.B == 2) ? ll_val(wu[k]) : 0.f; }
+      for (int k = 0; k < KB; ++k) { cv[k] = ll_val(wc[k]); uv[k] = B2 ? ll_val(wu[k]) : 0.f; }
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < KB; ++k) {
       const int i = tid + (k0 + k) * NCONS;
       if (i < T3_VOCAB) {
         const float c = cv[k], u = uv[k];
-        if (p.logits_out) {
-          p.logits_out[((size_t)it * p.B) * T3_VOCAB + i] = c;
-          if (p.B == 2) p.logits_out[((size_t)it * p.B + 1) * T3_VOCAB + i] = u;
+        if (lout) {
+          lout[((size_t)it * (1 + B2)) * T3_VOCAB + i] = c;
+          if (B2) lout[((size_t)it * 2 + 1) * T3_VOCAB + i] = u;
         }
-        float x = cfg ? c + sp.cfg_weight * (c - u) : c;
-        if (sp.temperature != 1.0f) x = x / sp.temperature;
-        if ((seen[i >> 5] >> (i & 31)) & 1u) x = (x < 0.f) ? x * sp.repetition_penalty : x / sp.repetition_penalty;
+        float x = cfg ? c + cfgw * (c - u) : c;
+        if (temp != 1.0f) x = x / temp;
+        if ((seen[i >> 5] >> (i & 31)) & 1u) x = (x < 0.f) ? x * rpen : x / rpen;
         sl[i] = x;
         if (x > lmax) { lmax = x; imax = i; }
       }
     }
   }
+  T3_SPROF(1);
   // block arg-max
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -1087,6 +1100,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
     cbar();
     tok = ri[16];
   }
+  T3_SPROF(2);
   if (p.forced) tok = p.forced[it];
 #if defined(T3_ABL_NOPOLL) || defined(T3_ABL_NOUNITS) || defined(T3_ABL_NOSTREAM) || defined(T3_ABL_NOWAIT)
   tok = (unsigned)(tok + it) % 6000u;
@@ -1109,6 +1123,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
     ll_store(dst + 2, e.z + q.z, fl); ll_store(dst + 3, e.w + q.w, fl);
     if (tid == 0) ll_store(p.ll + LL_EMB + T3_H, __uint_as_float((unsigned)tok | (stop ? 0x80000000u : 0u)), fl);
   }
+  T3_SPROF(3);
   cbar();   // seen[] update visible to the next call
 }
 

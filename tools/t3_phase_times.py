@@ -4,6 +4,8 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from chatterbox_b200 import synthetic as S, _lib
+if len(sys.argv) > 1:      # python tools/t3_phase_times.py _variants/libcbx_prof.so
+    _lib.LIB_PATH = os.path.abspath(sys.argv[1])
 from chatterbox_b200.t3 import T3, T3Cond
 
 dev = torch.device("cuda:0")
@@ -15,7 +17,7 @@ kw = dict(max_new_tokens=256, do_sample=False, stop_on_eos=False, cfg_weight=0.5
 for _ in range(2):
     t3.inference(t3_cond=cond, text_tokens=text, **kw)
 for it in (8, 200):
-    st = torch.zeros(256, dtype=torch.int64, device=dev)
+    st = torch.zeros(512, dtype=torch.int64, device=dev)
     _lib.check(t3._lib.cbx_t3_set_profile(t3._h, st.data_ptr(), it))
     t3.inference(t3_cond=cond, text_tokens=text, **kw)
     s = st.cpu().tolist()
@@ -29,6 +31,8 @@ for it in (8, 200):
     for nm, v in agg.items():
         v2 = sorted(v)
         print(f"  {nm:7s} n={len(v):3d} mean {sum(v)/len(v)/1e3:6.2f} us  min {v2[0]/1e3:6.2f}  max {v2[-1]/1e3:6.2f}  sum {sum(v)/1e3:7.1f}")
+    sp = [v / 1e3 for v in s[300:304]]
+    print('  sample phase (CTA 0): wait+process logits %.2f, argmax %.2f, token+embedding publish %.2f us' % tuple(sp[i + 1] - sp[i] for i in range(3)))
     sub = s[200:215]
     lab = ["A:stage", "A:rmsnorm+frags", "A:consume", "A:cbar", "A:epilogue", "A:cbar2", "-", "-", "D:stage", "D:rmsnorm+frags",
            "D:consume", "D:cbar", "D:epilogue", "D:cbar2"]

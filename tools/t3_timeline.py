@@ -59,3 +59,9 @@ for l in range(1, 29):
     acc["keys_dur_med"].append(float((a[m, 2] - a[m, 1]).median()))
     acc["published_max"].append(float((tl[m, 4 * l, 3] - qkv_done).max()))
 print("attention vs last qkv epilogue:", {k: round(stt.mean(v), 2) for k, v in acc.items()})
+# head step (step 4 L): when do the CTAs stage / finish, relative to the last down epilogue of the last layer
+hs = 120
+d_end = tl[:, hs - 1, 2]; d_end = d_end[d_end > 0].max()
+for nm, k in (("staged", 0), ("units done", 1), ("published", 2)):
+    v = tl[:, hs, k]; v = v[v > 0] - d_end
+    print(f"head {nm}: min {float(v.min()):.2f} median {float(v.median()):.2f} max {float(v.max()):.2f} us after the last down epilogue")
