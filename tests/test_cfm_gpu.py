@@ -89,3 +89,21 @@ def test_general_second_row_and_limits(est):
     from chatterbox_b200._lib import CbxError
     with pytest.raises(CbxError):
         est(torch.zeros(2, 80, 2000), torch.ones(2, 1, 2000), torch.zeros(2, 80, 2000), t, sp, torch.zeros(2, 80, 2000))
+
+
+@pytest.mark.parametrize("L", [812, 1800])
+def test_estimator_at_baseline_sizes_vs_oracle(L):
+    """BASELINE.json sizes: config 2 (L = 812: 6 s voice + 256 speech tokens) and config 3 (L = 1800: 30 s voice
+    conversion) — one estimator call against the CPU oracle (a second or two of host time each)."""
+    from chatterbox_b200.cfm import ConditionalDecoder
+    from oracle import cfm_oracle as CO
+    sd = S.make_state_dict("flow")
+    big = ConditionalDecoder(sd, "cuda", prefix=PFX, max_len=2048)
+    z2, mu2, sp2, c2 = _pair(S.cfm_inputs(L, seed=7))
+    t = torch.tensor([0.42, 0.42])
+    with torch.inference_mode():
+        ref = CO.estimator(sd, z2, torch.ones(2, 1, L), mu2, t, sp2, c2, PFX)
+    out = big(z2, torch.ones(2, 1, L), mu2, t, sp2, c2).cpu()
+    r = _rel(out, ref)
+    print(f"estimator L={L} rel-L2 vs oracle: {r:.3e}")
+    assert r < TOL

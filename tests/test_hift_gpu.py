@@ -88,3 +88,21 @@ def test_inference_end_to_end_uses_own_source(hift):
     from chatterbox_b200._lib import CbxError
     with pytest.raises(CbxError):
         hift.f0_predictor(torch.zeros(1, 80, 1000))
+
+
+def test_decode_at_baseline_size_vs_oracle():
+    """Config 2 size: 512 mel frames (10.24 s of audio) against the CPU oracle with the same source signal."""
+    from chatterbox_b200.hift import HiFTGenerator
+    from oracle import hift_oracle as HO
+    L = 512
+    sd = S.make_state_dict("hift")
+    big = HiFTGenerator(sd, "cuda", max_frames=L)
+    w = HO.fold_weight_norm(sd)
+    mel = S.mel_input(L, seed=77)
+    s = torch.tanh(torch.randn(1, 1, 480 * L, generator=torch.Generator().manual_seed(L)) * 0.3)
+    with torch.inference_mode():
+        ref, _ = HO.inference(w, mel, s=s, apply_trim_fade=True)
+    wav = big.decode(mel, s, apply_fade=True).cpu()
+    r = _rel(wav, ref)
+    print(f"decode+fade L={L} rel-L2 vs oracle {r:.3e}")
+    assert r < TOL
