@@ -36,6 +36,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <stdarg.h>
+#include <vector>
 
 namespace {
 
@@ -1393,6 +1394,12 @@ struct cbx_t3 {
   long long launches;
   unsigned long long* prof; int prof_it;
   void* prefill_ws;     // workspace of the GEMM prefill (NULL without plain weights)
+  // the GEMM prefill of a (B, P) seen twice is captured into a CUDA graph (it is ~240 short launches: launch-bound);
+  // the caller's embeddings are staged so the pointers baked into the graph stay valid
+  struct PrefillGraph { int B, P, seen; cudaGraphExec_t exec; };
+  std::vector<PrefillGraph> pf_graphs;
+  float* pf_embeds;
+  cudaStream_t cap_stream;
 };
 
 extern "C" int cbx_t3_grid(int device) {
@@ -1444,6 +1451,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   const size_t o_logits = take(sizeof(float) * 2 * T3_VOCAB);
   const size_t o_st = take(256), o_seen = take(VOCAB_PAD);
   const size_t o_ws = w->wplain ? take(cbx::t3_prefill_workspace_bytes(cfg->max_pos)) : 0;
+  const size_t o_pfe = w->wplain ? take((size_t)2 * cfg->max_pos * T3_H * sizeof(float)) : 0;
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_t3_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -1465,6 +1473,8 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   p.st = reinterpret_cast<T3State*>(s + o_st);
   p.seen = s + o_seen;
   h->prefill_ws = w->wplain ? s + o_ws : nullptr;
+  h->pf_embeds = w->wplain ? reinterpret_cast<float*>(s + o_pfe) : nullptr;
+  h->cap_stream = nullptr;
   int rc = t3_prepare_kernel(t3_megakernel<__nv_bfloat16>);
   if (!rc) rc = t3_prepare_kernel(t3_megakernel<float>);
   if (rc) { cudaFree(h->slab); delete h; return CBX_ERR; }
@@ -1474,6 +1484,8 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
 
 extern "C" int cbx_t3_destroy(cbx_t3* h) {
   if (!h) return CBX_OK;
+  for (auto& g : h->pf_graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   cudaFree(h->slab);
   delete h;
   return CBX_OK;
@@ -1510,7 +1522,41 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
     a.rope_cos = p.rope_cos; a.rope_sin = p.rope_sin; a.kcache = p.kcache; a.vcache = p.vcache;
     a.logits = p.logits; a.state = reinterpret_cast<int*>(p.st); a.workspace = h->prefill_ws;
     h->launches += 1 + h->cfg.n_layers * 8 + 2;
-    return cbx::t3_prefill_gemm(a, st);
+    static const bool use_graph = [] { const char* v = getenv("CBX_T3_PREFILL_GRAPH"); return !(v && v[0] == '0'); }();
+    cbx_t3::PrefillGraph* g = nullptr;
+    if (use_graph) {
+      for (auto& c : h->pf_graphs) if (c.B == B && c.P == P) { g = &c; break; }
+      if (!g) {
+        if (h->pf_graphs.size() >= 32) {            // bound the cache: drop the oldest entry
+          if (h->pf_graphs.front().exec) cudaGraphExecDestroy(h->pf_graphs.front().exec);
+          h->pf_graphs.erase(h->pf_graphs.begin());
+        }
+        h->pf_graphs.push_back({B, P, 0, nullptr});
+        g = &h->pf_graphs.back();
+      }
+      g->seen += 1;
+    }
+    if (!g || g->seen < 2) return cbx::t3_prefill_gemm(a, st);          // eager
+    if (!g->exec) {
+      if (!h->cap_stream) CBX_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+      cbx::T3PrefillArgs ag = a;
+      ag.embeds = h->pf_embeds;
+      cudaGraph_t graph = nullptr;
+      CBX_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+      const int rc = cbx::t3_prefill_gemm(ag, h->cap_stream);
+      const cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
+      if (rc || ce != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cbx_set_error("cbx_t3_prefill: graph capture failed (%s)", cudaGetErrorString(ce));
+        return CBX_ERR;
+      }
+      const cudaError_t ie = cudaGraphInstantiate(&g->exec, graph, 0);
+      cudaGraphDestroy(graph);
+      CBX_CHECK(ie == cudaSuccess, "cbx_t3_prefill: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ie));
+    }
+    CBX_CUDA(cudaMemcpyAsync(h->pf_embeds, embeds, (size_t)B * P * T3_H * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    CBX_CUDA(cudaGraphLaunch(g->exec, st));
+    return CBX_OK;
   }
   return t3_launch(h, p, st);
 }

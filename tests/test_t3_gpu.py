@@ -187,3 +187,25 @@ def test_gemm_prefill_matches_the_position_by_position_prefill(n_text):
                     do_sample=False, **PARAMS)
         outs.append(m.last_logits.cpu())
     assert (outs[0] - outs[1]).abs().max() < 2e-4
+
+
+def test_prefill_graph_replay_equals_eager():
+    """The GEMM prefill runs eagerly on the first call for a (B, P), is captured into a CUDA graph on the second and
+    replayed from the third; with different text of the same length every variant must reproduce the eager logits."""
+    from chatterbox_b200.t3 import T3
+    sd = S.make_state_dict("t3", n_layers=2)
+    m = T3(sd, "cuda", max_pos=160, kv_fp32=True, n_layers=2)
+    texts = [torch.cat([S.text_tokens(20, seed=s)] * 2, 0) for s in (31, 32, 33, 34)]
+    forced = torch.randint(0, 6561, (1, 6), generator=torch.Generator().manual_seed(4))
+    os.environ.pop("CBX_T3_PREFILL_GRAPH", None)
+    got = []
+    for t in texts:            # eager, capture + replay, replay, replay
+        m.inference(t3_cond=_cond(), text_tokens=t, max_new_tokens=6, forced_tokens=forced, return_logits=True,
+                    do_sample=False, **PARAMS)
+        got.append(m.last_logits.cpu().clone())
+    ref = T3(sd, "cuda", max_pos=160, kv_fp32=True, n_layers=2, gemm_prefill=False)     # position-by-position prefill
+    for t, g in zip(texts, got):
+        ref.inference(t3_cond=_cond(), text_tokens=t, max_new_tokens=6, forced_tokens=forced, return_logits=True,
+                      do_sample=False, **PARAMS)
+        assert (ref.last_logits.cpu() - g).abs().max() < 5e-4
+    assert not torch.equal(got[0], got[1])      # different text really gives different logits
