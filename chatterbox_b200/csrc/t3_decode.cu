@@ -557,11 +557,12 @@ __device__ __noinline__ void attn_phase_stream(const T3Params& p, int it, int la
   constexpr int APF = (sizeof(KVT) == 2) ? 3 : 1;         // prefetched rounds of 4 positions per warp
   static_assert((192 + NCONS_WARPS * PART_STRIDE) * 4 <= 4096 && 4096 + APF * NCONS * 2 * PIECES * 16 <= SCRATCH_BYTES, "attention scratch");
   uint8_t* pf = reinterpret_cast<uint8_t*>(scr) + 4096 + (size_t)tid * (2 * PIECES * 16);   // [round][thread][K|V][pieces]
-#pragma unroll
-  for (int n = 0; n < APF; ++n) {
-    const int i = lo + warp * 4 + lg + n * (NCONS_WARPS * 4);
+  // round r = positions lo + 32 r + (warp * 4 + lg); a ring of APF rounds stays in flight: round r + APF is issued
+  // into the slot round r just left, one commit group per round (empty groups keep the count uniform)
+  auto issue_round = [&](int r) {
+    const int i = lo + warp * 4 + lg + r * (NCONS_WARPS * 4);
     if (i < hi) {
-      const uint32_t dst = smem_u32(pf + (size_t)n * (NCONS * 2 * PIECES * 16));
+      const uint32_t dst = smem_u32(pf + (size_t)(r % APF) * (NCONS * 2 * PIECES * 16));
       const KVT* ks = kc + (size_t)i * 64 + sub * 8;
       const KVT* vs = vc + (size_t)i * 64 + sub * 8;
 #pragma unroll
@@ -570,8 +571,11 @@ __device__ __noinline__ void attn_phase_stream(const T3Params& p, int it, int la
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (PIECES + q) * 16), "l"(reinterpret_cast<const uint8_t*>(vs) + q * 16) : "memory");
       }
     }
-  }
-  asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const int rounds = (max(hi - lo, 0) + NCONS_WARPS * 4 - 1) / (NCONS_WARPS * 4);
+#pragma unroll
+  for (int n = 0; n < APF; ++n) issue_round(n);
   float kr = 0.f, vr = 0.f;
   if (tid < 64) {
     const int d = tid;
@@ -599,20 +603,21 @@ __device__ __noinline__ void attn_phase_stream(const T3Params& p, int it, int la
   osm_init(st);
 #pragma unroll
   for (int e = 0; e < 8; ++e) qv[e] = q_s[sub * 8 + e];
-  asm volatile("cp.async.wait_all;" ::: "memory");
-#pragma unroll
-  for (int n = 0; n < APF; ++n) {
-    const int i = lo + warp * 4 + lg + n * (NCONS_WARPS * 4);
+#pragma unroll 1
+  for (int r = 0; r < rounds; ++r) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(APF - 1) : "memory");      // round r has landed (groups complete in order)
+    const int i = lo + warp * 4 + lg + r * (NCONS_WARPS * 4);
     const bool valid = i < hi;
     float kf[8], vf[8];
     if (valid) {
-      const KVT* src = reinterpret_cast<const KVT*>(pf + (size_t)n * (NCONS * 2 * PIECES * 16));
+      const KVT* src = reinterpret_cast<const KVT*>(pf + (size_t)(r % APF) * (NCONS * 2 * PIECES * 16));
       KV<KVT>::lds8(src, kf);
       KV<KVT>::lds8(src + 8, vf);
     } else {
 #pragma unroll
       for (int e = 0; e < 8; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
     }
+    issue_round(r + APF);          // the slot is free: this thread has its values in registers
     float s = 0.f;
 #pragma unroll
     for (int e = 0; e < 8; ++e) s += qv[e] * kf[e];
@@ -621,25 +626,7 @@ __device__ __noinline__ void attn_phase_stream(const T3Params& p, int it, int la
     s += __shfl_xor_sync(0xffffffffu, s, 4);
     if (valid) osm_update(st, s, vf);
   }
-  for (int base = lo + warp * 4 + APF * (NCONS_WARPS * 4); base < hi; base += NCONS_WARPS * 4) {
-    const int i = base + lg;
-    const bool valid = i < hi;
-    float kf[8], vf[8];
-    if (valid) {
-      KV<KVT>::load8(kc + (size_t)i * 64 + sub * 8, kf);
-      KV<KVT>::load8(vc + (size_t)i * 64 + sub * 8, vf);
-    } else {
-#pragma unroll
-      for (int e = 0; e < 8; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
-    }
-    float s = 0.f;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) s += qv[e] * kf[e];
-    s += __shfl_xor_sync(0xffffffffu, s, 1);
-    s += __shfl_xor_sync(0xffffffffu, s, 2);
-    s += __shfl_xor_sync(0xffffffffu, s, 4);
-    if (valid) osm_update(st, s, vf);
-  }
+  asm volatile("cp.async.wait_all;" ::: "memory");
   // the key of this position itself: last split, warp 0, lane group 0
   if (split == S - 1 && warp == 0) {
     float kf[8], vf[8];
