@@ -44,6 +44,9 @@ namespace {
 #define T3_NSLOT 4                        // 5 measured 1 % slower (the L1 left for the stack shrinks to ~4 KB)
 #endif
 constexpr int NSLOT = T3_NSLOT;           // ring depth (32 KB units)
+#ifndef T3_SAMPLE_KB
+#define T3_SAMPLE_KB 11
+#endif
 #ifndef T3_PF_DIST
 #define T3_PF_DIST 6                      // L2 prefetch distance in units (0 = off)
 #endif
@@ -965,7 +968,7 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
   float* lout = p.logits_out;
   const float cfgw = sp.cfg_weight, temp = sp.temperature, rpen = sp.repetition_penalty;
   T3State* stp = p.st;
-  constexpr int KB = 11;                  // words per row in flight per thread: 33 = 3 batches
+  constexpr int KB = T3_SAMPLE_KB;       // words per row in flight per thread (33 = 3 batches of 11)
   for (int k0 = 0; k0 < NK; k0 += KB) {
     float cv[KB], uv[KB];
     if (it == 0) {   // logits of the previous launch (prefill or an earlier decode call)

@@ -88,7 +88,9 @@ int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_tokens, cons
 int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t* launches);
 
 /* Debug aid: CTA 0 writes %globaltimer (ns) after every phase of decode iteration `it` into
- * stamps[] (device, >= 5*n_layers+4 entries); NULL disables. */
+ * stamps[] (device, >= 512 entries); NULL disables.  The stamps are compiled in only with
+ * -DT3_PROFILE (phases) or -DT3_TIMELINE (every CTA, stamps[] >= 1024 + 1024 * SMs entries): in the
+ * default build even the dead tests cost issue slots on the critical path, and this call records nothing. */
 int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it);
 
 /* ------------------------------------------------------------------------------------------
