@@ -47,6 +47,9 @@ constexpr int NSLOT = T3_NSLOT;           // ring depth (32 KB units)
 #ifndef T3_SAMPLE_KB
 #define T3_SAMPLE_KB 11
 #endif
+#if !defined(T3_RING)
+#define T3_DIRECT 1                        // weight units straight from L2 into registers (-DT3_RING: the shared-memory TMA ring)
+#endif
 #ifndef T3_PF_DIST
 #define T3_PF_DIST 6                      // L2 prefetch distance in units (0 = off)
 #endif
@@ -444,6 +447,42 @@ __device__ __forceinline__ void consume_units(int n, RingPos& rp, const uint32_t
     ++rp.k;
   }
 }
+
+#ifdef T3_DIRECT
+// ---- experimental: weight units straight from L2 into registers (no shared-memory ring) --------------------------
+// The unit's fragments are loaded with coalesced 128-bit loads BEFORE the wait for the step's inputs (weights do not
+// depend on activations), so on the critical path a unit is 8 MMAs; HBM -> L2 runs ahead by bulk L2 prefetches.
+__device__ __forceinline__ uint4 ldg_w(const uint4* p, uint64_t policy) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(policy));
+  return v;
+}
+template <int J>
+__device__ __forceinline__ void direct_load(uint4 (&w)[T3_MAXU][VPL], int n, const uint8_t* ub, int lofs, uint64_t policy) {
+  if (J < n) {
+    const uint4* wp = reinterpret_cast<const uint4*>(ub + (size_t)J * T3_UNIT_BYTES) + lofs;
+#pragma unroll
+    for (int s = 0; s < VPL; ++s) w[J][s] = ldg_w(wp + s * 32, policy);
+  }
+}
+template <int J>
+__device__ __forceinline__ void direct_mma(const uint4 (&w)[T3_MAXU][VPL], int n, const uint32_t (&Bf)[VPL][2], float* red,
+                                           int warp, int g, int tig) {
+  if (J < n) {
+    float c[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { c[q][0] = 0.f; c[q][1] = 0.f; c[q][2] = 0.f; c[q][3] = 0.f; }
+#pragma unroll
+    for (int s = 0; s < VPL; ++s) mma_bf16_16816(c[s & 3], w[J][s].x, w[J][s].y, w[J][s].z, w[J][s].w, Bf[s][0], Bf[s][1]);
+    if (tig < 2) {
+      float* dst = red + (J * NCONS_WARPS + warp) * 32 + tig * 16 + g;
+      dst[0] = ((c[0][0] + c[0][1]) + (c[1][0] + c[1][1])) + ((c[2][0] + c[2][1]) + (c[3][0] + c[3][1]));
+      dst[8] = ((c[0][2] + c[0][3]) + (c[1][2] + c[1][3])) + ((c[2][2] + c[2][3]) + (c[3][2] + c[3][3]));
+    }
+  }
+}
+#endif
 
 __device__ __forceinline__ float red_sum(const float* red, int j, int o) {
   float s = 0.f;
@@ -1153,7 +1192,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
 #if T3_PF_DIST > 0
     for (int u = NSLOT; u < T3_PF_DIST && u < sm.per_iter_layers; ++u) l2_prefetch_bulk(sm.base + (size_t)u * T3_UNIT_BYTES, T3_UNIT_BYTES);
 #endif
+#ifndef T3_DIRECT
     for (int s = 0; s < NSLOT; ++s) stream_issue_next(sm, ctl, s, ring, full);
+#endif
   }
   if (tid < PH_COUNT * T3_MAXU) {
     const int ph = tid / T3_MAXU, j = tid % T3_MAXU, n = t3_plan_count(ph, c, G);
@@ -1226,6 +1267,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     for (int r = 0; r < VPL / 2; ++r) *reinterpret_cast<float2*>(xr + 32 * r) = make_float2(0.f, 0.f);
     const bool with_head = (p.mode == 1) || (it == n_iters - 1);
     const int n_steps = 4 * L + (with_head ? 1 : 0);
+#ifdef T3_DIRECT
+    int uidx = 0;        // unit index inside this CTA's per-iteration stream
+#endif
 
 #pragma unroll 1
     for (int step = 0; step < n_steps; ++step) {
@@ -1233,6 +1277,28 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       const int ph = (l == L) ? PH_HEAD : (step & 3);
       float* red = red_all + par * RED_FLOATS;
       float* ssq = ssq_all + par * (NCONS_WARPS * 2);
+#ifdef T3_DIRECT
+      const int n = ctl->plan_n[ph];
+      uint4 wreg[T3_MAXU][VPL];
+      {
+        const uint8_t* ub = sm.base + (size_t)uidx * T3_UNIT_BYTES;
+        const int lofs = warp * (VPL * 32) + lane;
+        direct_load<0>(wreg, n, ub, lofs, sm.policy);
+        direct_load<1>(wreg, n, ub, lofs, sm.policy);
+        if (ph != PH_HEAD) {         // the head's prologue polls 4 pieces: its last two units are loaded after it
+          direct_load<2>(wreg, n, ub, lofs, sm.policy);
+          direct_load<3>(wreg, n, ub, lofs, sm.policy);
+        }
+        if (tid == NCONS - 32) {      // HBM -> L2, T3_PF_DIST units ahead of the units of this step
+          const int end = sm.per_iter_layers + (with_head ? sm.nhead : 0);
+          for (int j = 0; j < n; ++j) {
+            int pf = uidx + j + T3_PF_DIST;
+            if (pf >= end) pf -= end;
+            if (pf < end) l2_prefetch_bulk(sm.base + (size_t)pf * T3_UNIT_BYTES, T3_UNIT_BYTES);
+          }
+        }
+      }
+#endif
       // ---------- prologue: this lane's 8 input values ----------
       T3_SUB(0);
       if (ph == PH_O) {
@@ -1276,14 +1342,32 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       }
       make_bfrags(Bf, x, xt, lane);
       T3_SUB(2);
+#ifdef T3_DIRECT
+      {
+        const int g = lane >> 2, tig = lane & 3;
+        if (ph == PH_HEAD) {
+          const uint8_t* ub = sm.base + (size_t)uidx * T3_UNIT_BYTES;
+          const int lofs = warp * (VPL * 32) + lane;
+          direct_load<2>(wreg, n, ub, lofs, sm.policy);
+          direct_load<3>(wreg, n, ub, lofs, sm.policy);
+        }
+        direct_mma<0>(wreg, n, Bf, red, warp, g, tig);
+        direct_mma<1>(wreg, n, Bf, red, warp, g, tig);
+        direct_mma<2>(wreg, n, Bf, red, warp, g, tig);
+        direct_mma<3>(wreg, n, Bf, red, warp, g, tig);
+        uidx += n;
+      }
+#else
       const int n = ctl->plan_n[ph];
       consume_units(n, rp, Bf, red, ring, full, sm, warp, lane, ctl, p.st);
+#endif
       T3_SUB(3);
       T3_TL(1);
       cbar();
       // every warp is past its reads of the n slots of this step: the last warp (never part of the epilogue, which
       // takes warps 0..n-1) re-arms them with the units NSLOT ahead in the stream.  No per-unit release counting: the
       // unit loop stays free of atomics, and HBM has the slack (the copies are needed a whole step later).
+#ifndef T3_DIRECT
       if (tid == NCONS - 32 && n > 0 && !ctl->abort) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         int sl = rp.slot - n;
@@ -1293,6 +1377,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
           if (++sl == NSLOT) sl = 0;
         }
       }
+#endif
       T3_SUB(4);
       // ---------- epilogue: cross-warp sum, scale / SwiGLU, publish ----------
 #ifdef T3_ABL_NOEPI
