@@ -64,7 +64,11 @@ constexpr int STOP_SPEECH = 6562;
 constexpr int VOCAB_PAD = T3_VOCAB_PAD;
 constexpr float RMS_EPS = 1e-5f;
 
+#ifdef T3_DIRECT
+constexpr int SMEM_RING = 0;                    // no weight ring: units go from L2 to registers
+#else
 constexpr int SMEM_RING = NSLOT * T3_UNIT_BYTES;
+#endif
 constexpr int SMEM_BARS = SMEM_RING;            // 2*NSLOT mbarriers
 constexpr int SMEM_CTL = SMEM_BARS + 256;       // control words
 constexpr int SMEM_RED = SMEM_CTL + 256;        // [2 phase parities][MAXU][warps][32] k-slice partials
