@@ -76,7 +76,15 @@ constexpr int RED_FLOATS = T3_MAXU * NCONS_WARPS * 32;
 constexpr int SMEM_SSQ = SMEM_RED + 2 * RED_FLOATS * 4;      // [2][warps][2 rows] partial sums of squares
 constexpr int SMEM_XT = SMEM_SSQ + 256;                      // [warps][XT_WORDS] packed hi/lo activation fragments
 constexpr int SMEM_SCRATCH = SMEM_XT + (NCONS_WARPS * (2 * (2 * 4 * (2 * VPL + 4) + 4)) * 4 + 15) / 16 * 16;   // fragment tiles (XT_WORDS per warp); then attention scratch / sampling logits (union)
-constexpr int SCRATCH_BYTES = VOCAB_PAD * 4 + 1024;
+// past positions an attention tile holds (+ 1 row for the position itself).  The direct build has the ring's 128 KB
+// to spare: 544 positions per split cover contexts up to 2 176 (config 5) on the tile path.
+#ifdef T3_DIRECT
+constexpr int ATT_TP = 544;
+#else
+constexpr int ATT_TP = 96;
+#endif
+constexpr int ATT_TILE_BYTES = (64 + (ATT_TP + 1 + 31) / 32 * 32) * 4 + 2 * (ATT_TP + 1) * 72 * 2;
+constexpr int SCRATCH_BYTES = (VOCAB_PAD * 4 + 1024 > ATT_TILE_BYTES ? VOCAB_PAD * 4 + 1024 : ATT_TILE_BYTES + 15) / 16 * 16;
 constexpr int SMEM_SEEN = SMEM_SCRATCH + SCRATCH_BYTES;      // generated-id set (CTA 0), one bit per id
 constexpr int SEEN_WORDS = (VOCAB_PAD + 31) / 32;
 constexpr int SEEN_BYTES = (SEEN_WORDS * 4 + 15) / 16 * 16;
@@ -733,10 +741,10 @@ __device__ __noinline__ void attn_phase_stream(const T3Params& p, int it, int la
 // all warps, so no barrier is needed to agree on m and l); (3) warp w accumulates output dims 8w..8w+7 over all
 // positions (a lane owns positions lane + 32 k and their p in registers) and a 9-shuffle reduce-scatter leaves
 // one dim in every fourth lane, which publishes it.  Two CTA barriers, no online rescaling, no cross-warp merge.
-constexpr int ATT_TP = 96;                       // past positions a tile holds (+ 1 row for the position itself)
 constexpr int ATT_RS = 72;                       // tile row stride in bf16 (144 B: 16-byte column reads of 32 rows are conflict-free)
-constexpr int ATT_TILE_OFF = 1024;               // bytes: q_s [64] fp32, scores [128] fp32 before the tiles
-static_assert(ATT_TILE_OFF + 2 * (ATT_TP + 1) * ATT_RS * 2 <= SCRATCH_BYTES, "attention tiles fit the scratch area");
+constexpr int ATT_SCAP = (ATT_TP + 1 + 31) / 32 * 32;          // score slots
+constexpr int ATT_TILE_OFF = (64 + ATT_SCAP) * 4;              // bytes: q_s [64] fp32, scores [ATT_SCAP] fp32 before the tiles
+static_assert(ATT_TILE_OFF % 16 == 0 && ATT_TILE_OFF + 2 * (ATT_TP + 1) * ATT_RS * 2 <= SCRATCH_BYTES, "attention tiles fit the scratch area");
 __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int layer, int pos0, float* scr, int warp, int lane,
                                              Ctl* ctl) {
   const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x, L = p.n_layers;
@@ -798,9 +806,9 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
       const float4 t4 = *reinterpret_cast<const float4*>(q_s + qd * 16 + e);
       qv[e] = t4.x; qv[e + 1] = t4.y; qv[e + 2] = t4.z; qv[e + 3] = t4.w;
     }
-#pragma unroll
-    for (int rr = 0; rr < 2; ++rr) {
-      const int i = (tid >> 2) + 64 * rr;
+#pragma unroll 1
+    for (int i0 = 0; i0 < nrows; i0 += 64) {
+      const int i = (tid >> 2) + i0;
       float acc = 0.f;
       if (i < nrows) {
         float kf[8];
@@ -818,34 +826,32 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
   }
   T3_ATL(2);
   cbar();
-  // 4. max, exponentials, sum: every warp over all rows (lane owns rows lane + 32 k)
-  float pk[4];
+  // 4. max, then exponentials / their sum / output dims 8 warp .. 8 warp + 7 in one sweep: every warp over all rows
+  //    (lane owns rows lane + 32 k)
   float M = -INFINITY;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int i = lane + 32 * k;
-    pk[k] = (i < nrows) ? s_sm[i] : -INFINITY;
-    M = fmaxf(M, pk[k]);
+#pragma unroll 1
+  for (int k0 = 0; k0 < nrows; k0 += 32) {
+    const int i = lane + k0;
+    M = fmaxf(M, (i < nrows) ? s_sm[i] : -INFINITY);
   }
   M = warp_max(M);
   float lsum = 0.f;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) { pk[k] = (pk[k] == -INFINITY) ? 0.f : __expf(pk[k] - M); lsum += pk[k]; }
-  lsum = warp_sum(lsum);
-  // 5. output dims 8 warp .. 8 warp + 7
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int i = lane + 32 * k;
+#pragma unroll 1
+  for (int k0 = 0; k0 < nrows; k0 += 32) {
+    const int i = lane + k0;
     if (i < nrows) {
+      const float pk = __expf(s_sm[i] - M);
+      lsum += pk;
       float vf[8];
       KV<__nv_bfloat16>::lds8(vt + i * ATT_RS + warp * 8, vf);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += pk[k] * vf[e];
+      for (int e = 0; e < 8; ++e) acc[e] += pk * vf[e];
     }
   }
+  lsum = warp_sum(lsum);
   // reduce-scatter over the 32 lanes: 8 -> 4 -> 2 -> 1 values, then two plain steps; lane 4 j ends with dim j
   {
     const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
