@@ -2,7 +2,9 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from chatterbox_b200 import synthetic as S
+from chatterbox_b200 import synthetic as S, _lib
+if len(sys.argv) > 3:      # A/B: python tools/cfm_once.py 812 10 _variants/libcbx_x.so
+    _lib.LIB_PATH = os.path.abspath(sys.argv[3])
 from chatterbox_b200.cfm import CausalConditionalCFM, ConditionalDecoder
 
 L = int(sys.argv[1]) if len(sys.argv) > 1 else 812
