@@ -5,27 +5,31 @@
 // host sync per token become zero launches per token.  The step is HBM-bound (1.02 GB of bf16
 // weights per token at batch 2), so the design is a weight-streaming pipeline:
 //   * one CTA per SM (cooperative launch for co-residency), 8 warps = 2 per scheduler, so every
-//     thread may use up to 255 registers (a 9th, dedicated producer warp would cap them at 168);
-//   * this CTA's pre-packed, contiguous weight stream arrives in 32 KB TMA bulk copies
-//     (cp.async.bulk -> UBLKCP) through a 5-deep shared-memory ring: the warp that releases a
-//     slot last re-arms it with the copy of the unit 5 ahead.  Weights do not depend on
-//     activations, so HBM keeps streaming while dependent phases hand activations over;
-//   * consumers multiply each 16-row x 1024-k unit against the CFG pair of activation rows with
-//     mma.sync m16n8k16: the WEIGHTS are the A operand (16 rows per instruction, pre-packed in
-//     fragment order so one 128-bit shared load feeds one MMA), the activations the B operand
-//     with columns {row0 hi, row0 lo, row1 hi, row1 lo}: x = hi + lo in bf16, so products carry
-//     ~16 mantissa bits and accumulate in fp32.  The 8 warps split K; partials meet in smem;
+//     thread may use up to 255 registers;
+//   * this CTA's pre-packed, contiguous weight stream is consumed in 32 KB "units" (16 rows x 1024 k in MMA
+//     fragment order).  Default build: the units of a step are loaded with coalesced 128-bit loads straight from
+//     L2 into registers BEFORE the wait for the step's inputs (weights do not depend on activations), and
+//     cp.async.bulk.prefetch.L2 pulls the units 6 ahead from HBM, so HBM streams ahead of the dependency chain.
+//     -DT3_RING: the first design, 32 KB TMA bulk copies (cp.async.bulk) through a 4-deep shared-memory ring
+//     with mbarrier completion (kept for A/B: 406 against 357 us/token);
+//   * consumers multiply each unit against the CFG pair of activation rows with mma.sync m16n8k16: the WEIGHTS
+//     are the A operand (16 rows per instruction, one 128-bit load feeds one MMA), the activations the B operand
+//     with columns {row0 hi, row0 lo, row1 hi, row1 lo}: x = hi + lo in bf16, so products carry ~16 mantissa
+//     bits and accumulate in fp32.  The 8 warps split K; partials meet in smem;
 //   * dependent phases (qkv -> attention -> o_proj -> gate/up -> down) hand their activations
 //     over through "LL" buffers in L2: every fp32 value travels in one 8-byte word together with
 //     a sequence flag ({value, flag}, one atomic 64-bit store), so a consumer polls the data
 //     itself and there is NO grid barrier and NO fence on the critical path;
-//   * a lane owns 8 consecutive k of one activation row; residual adds, the RMSNorm gain, the
-//     hi/lo split and the split-KV combine happen in those registers.  The RMSNorm scale is a per-
-//     row scalar, so it is applied to the OUTPUTS in the phase epilogue: the MMAs start without
-//     waiting for the sum of squares;
+//   * a lane owns four PAIRS of k, 32 apart, of one activation row, so every poll instruction of a warp is
+//     coalesced (4 cache lines, not 16 LSU wavefronts); the owning lane splits its values into packed hi/lo bf16
+//     words and a fragment-order tile turns them into B fragments with four 128-bit loads.  The residual slice and
+//     the next norm gains live in shared memory (no spills).  The RMSNorm scale is a per-row scalar, so it is
+//     applied to the OUTPUTS in the phase epilogue: the MMAs start without waiting for the sum of squares;
+//   * attention: the split's K/V rows are copied to shared memory before the wait for q/k/v; contexts up to 544
+//     positions per split take a two-pass tile path (all scores at once, per-warp redundant softmax statistics,
+//     reduce-scatter output), longer ones and the fp32 slab an online-softmax stream with a cp.async ring;
 //   * RoPE, SwiGLU, CFG, logit processing, sampling, EOS and the next-token embedding are fused
-//     into the phase prologues/epilogues; the residual stream lives in registers (replicated per
-//     CTA), so nothing but weights and the KV slab touches HBM.
+//     into the phase prologues/epilogues, so nothing but weights and the KV slab touches HBM.
 // Prefill runs the same kernel one position per weight pass (mode 0).
 #include "common.cuh"
 #include "t3_plan.h"
