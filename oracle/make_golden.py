@@ -1,6 +1,6 @@
 """Generate the pinned vectors under tests/golden/ from the UNMODIFIED reference (container only).
 
-TEST INFRASTRUCTURE.  Run:  python -m oracle.make_golden [t3] [cfm] [hift]
+TEST INFRASTRUCTURE.  Run:  python -m oracle.make_golden [t3] [t3w] [cfm] [hift] [flow]
 
 The reference modules are imported from /root/reference through `oracle/ref_import.py`, loaded
 with the synthetic state dicts of `chatterbox_b200/synthetic.py`, and driven through their own
@@ -149,6 +149,65 @@ def make_t3():
     print("[t3] wrote tests/golden/t3_golden.safetensors")
 
 
+T3W_N = 256                      # the bench workload: 256 speech tokens (BASELINE configs 1-2)
+T3W_FULL_STEPS = [0, 1, 7, 31, 63, 127, 191, 255]
+T3W_SAMPLE_COLS = 384            # vocabulary columns kept for EVERY step (full rows only at T3W_FULL_STEPS)
+
+
+def make_t3w():
+    """The bench's own configuration on UN-ROUNDED fp32 weights (`make_state_dict("t3", bf16_exact=False)`, what a
+    real t3_cfg.safetensors holds): 30 layers, 256 greedy + 256 teacher-forced steps through the reference
+    `T3.inference`.  Full logit rows are kept at T3W_FULL_STEPS, a fixed sample of vocabulary columns at every
+    step (a full 256 x 2 x 8194 fp32 dump would be 16.8 MB)."""
+    torch.manual_seed(0)
+    t0 = time.time()
+    sd = S.make_state_dict("t3", bf16_exact=False)
+    t3 = R.build_t3()
+    t3.load_state_dict(sd)
+    print(f"[t3w] reference built + fp32 synthetic weights loaded in {time.time() - t0:.1f}s")
+    cond = S.t3_cond()
+    text = S.text_tokens()
+    text2 = torch.cat([text, text], 0)
+    params = dict(cfg_weight=0.5, temperature=0.8, repetition_penalty=1.2, min_p=0.05, top_p=1.0)
+    g = torch.Generator().manual_seed(4242)
+    cols = torch.randperm(8194, generator=g)[:T3W_SAMPLE_COLS].sort().values
+    out = {"sample_cols": cols.to(torch.int32), "full_steps": torch.tensor(T3W_FULL_STEPS, dtype=torch.int32)}
+
+    t0 = time.time()
+    toks, raw = _ref_t3_run(t3, cond, text2, T3W_N, **params)
+    print(f"[t3w] reference greedy {toks.shape[1]} tokens in {time.time() - t0:.1f}s: {toks[0, :12].tolist()}")
+    assert toks.shape[1] == T3W_N, "synthetic weights must not emit EOS inside the bench workload"
+    gaps = []
+    gen = torch.tensor([[T3O.START_SPEECH]])
+    for i in range(toks.shape[1]):
+        p = T3O.process_logits(raw[i], gen, **params)
+        top2 = p.topk(2, dim=-1).values[0]
+        gaps.append(float(top2[0] - top2[1]))
+        gen = torch.cat([gen, toks[:, i:i + 1]], 1)
+    print(f"[t3w] min / median top-2 gap along the greedy path: {min(gaps):.4e} / {sorted(gaps)[len(gaps) // 2]:.4e}")
+    out["greedy_tokens"] = toks[0].to(torch.int32)
+    out["greedy_top2_gaps"] = torch.tensor(gaps)
+    out["greedy_logits_full"] = raw[T3W_FULL_STEPS].clone()
+    out["greedy_logits_cols"] = raw[:, :, cols].clone()
+    # the restatement on the same weights, every 32nd step (it is what the GPU box can run)
+    my_toks, my_raw = T3O.inference(sd, cond, text2, max_new_tokens=64, forced_tokens=toks, **params)
+    d = (raw[:64] - my_raw).abs().max().item()
+    print(f"[t3w] restatement vs reference over the first 64 forced steps: raw logits max-abs {d:.3e}")
+    assert d < 2e-3
+
+    g = torch.Generator().manual_seed(78)
+    forced = torch.randint(0, 6561, (1, T3W_N), generator=g)
+    t0 = time.time()
+    toks_f, raw_f = _ref_t3_run(t3, cond, text2, T3W_N, forced=forced, **params)
+    print(f"[t3w] reference teacher-forced {toks_f.shape[1]} steps in {time.time() - t0:.1f}s")
+    assert torch.equal(toks_f, forced)
+    out["forced_tokens"] = forced[0].to(torch.int32)
+    out["forced_logits_full"] = raw_f[T3W_FULL_STEPS].clone()
+    out["forced_logits_cols"] = raw_f[:, :, cols].clone()
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(GOLD, "t3_fp32w_golden.safetensors"))
+    print("[t3w] wrote tests/golden/t3_fp32w_golden.safetensors")
+
+
 def make_cfm():
     """Reference ConditionalDecoder / CausalConditionalCFM vs oracle/cfm_oracle.py; golden outputs."""
     from oracle import cfm_oracle as CO
@@ -279,6 +338,8 @@ if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count() or 8)
     if "t3" in which:
         make_t3()
+    if "t3w" in which:
+        make_t3w()
     if "cfm" in which and "make_cfm" in globals():
         globals()["make_cfm"]()
     if "hift" in which and "make_hift" in globals():

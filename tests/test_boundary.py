@@ -129,3 +129,34 @@ def test_front_end_graph_replay_equals_eager(tts):
     assert s3._front_cache[(31, 20, 40)]["graph"] is not None
     for w, g in zip(want, got):       # library GEMMs may pick another algorithm under capture: fp32 rounding only
         assert float((w - g).norm() / w.norm()) < 1e-4
+
+
+@pytest.mark.gpu
+def test_s3gen_chain_at_the_bench_shape():
+    """BASELINE configs[1] S3Gen stage at its own size: 256 speech tokens + a 150-token prompt -> L = 812 mel frames
+    through the 10-step solve -> 512 frames through HiFT (10.24 s of audio), against the chained CPU oracles with the
+    GPU's source signal injected.  Reports mel and waveform rel-L2."""
+    from chatterbox_b200 import flow_frontend as FF
+    from chatterbox_b200.s3gen import S3Gen
+    from oracle import cfm_oracle as CO, hift_oracle as HO
+    sd, sdh = S.make_state_dict("flow"), S.make_state_dict("hift")
+    s3 = S3Gen(sd, sdh, "cuda", rand_noise=S.cfm_noise(), max_mel_len=1024)
+    tok = S.speech_tokens(256, seed=5)
+    ref = S.s3gen_ref(seed=4, prompt_len=150)
+    wav, src = s3.inference(tok, ref_dict=ref, seed=5)
+    mel_gpu = s3.flow_inference(tok, ref_dict=ref).cpu()
+    assert mel_gpu.shape == (1, 80, 512) and wav.shape == (1, 480 * 512)
+    with torch.inference_mode():
+        mu, spks, cond, l1 = FF.flow_inputs(sd, tok, ref["prompt_token"], ref["prompt_feat"], ref["embedding"])
+        assert mu.shape[2] == 812 and l1 == 300
+        mel = CO.solve_euler(sd, S.cfm_noise()[:, :, :812], mu, spks, cond, pfx="decoder.estimator.")[:, :, l1:]
+        w = HO.fold_weight_norm(sdh)
+        ref_wav_same_mel, _ = HO.inference(w, mel_gpu, s=src.cpu())
+        ref_wav, _ = HO.inference(w, mel, s=src.cpu())
+    r_mel = float((mel_gpu - mel).norm() / mel.norm())
+    r_voc = float((wav.cpu() - ref_wav_same_mel).norm() / ref_wav_same_mel.norm())
+    r_all = float((wav.cpu() - ref_wav).norm() / ref_wav.norm())
+    print(f"bench shape (256 tokens, L=812, 512 frames): mel rel-L2 {r_mel:.3e}; vocoder on the same mel {r_voc:.3e}; "
+          f"chained waveform {r_all:.3e}")
+    assert r_mel < 2e-2 and r_voc < 2e-2
+    assert r_all < 1e-1      # the vocoder amplifies the (in-tolerance) mel difference; stated, not hidden

@@ -107,3 +107,23 @@ def test_estimator_at_baseline_sizes_vs_oracle(L):
     r = _rel(out, ref)
     print(f"estimator L={L} rel-L2 vs oracle: {r:.3e}")
     assert r < TOL
+
+
+@pytest.mark.parametrize("L", [812, 1800])
+def test_full_euler_solve_at_baseline_sizes_vs_oracle(L):
+    """The COMPOUNDED 10-step Euler/CFG solve (flow_matching.py:72-123) at the bench's own mel lengths — config 2
+    (L = 812) and config 3 (L = 1800) — against `cfm_oracle.solve_euler` on the host cores: the rel-L2 is taken on
+    the final mel, so estimator errors are carried through all ten steps.  Second call = the CUDA-graph replay."""
+    from chatterbox_b200.cfm import CausalConditionalCFM, ConditionalDecoder
+    from oracle import cfm_oracle as CO
+    sd = S.make_state_dict("flow")
+    est_big = ConditionalDecoder(sd, "cuda", prefix=PFX, max_len=2048)
+    cfm = CausalConditionalCFM(est_big, rand_noise=S.cfm_noise())
+    inp = S.cfm_inputs(L, seed=11)
+    with torch.inference_mode():
+        ref = CO.solve_euler(sd, inp["z"], inp["mu"], inp["spks"], inp["cond"], pfx=PFX)
+    for rep in ("eager", "graph capture", "graph replay"):
+        mel, _ = cfm(mu=inp["mu"], mask=torch.ones(1, 1, L), n_timesteps=10, spks=inp["spks"], cond=inp["cond"])
+        r = _rel(mel.cpu(), ref)
+        print(f"10-step solve L={L} ({rep}) mel rel-L2 vs oracle: {r:.3e}")
+        assert r < TOL
