@@ -13,7 +13,8 @@ class CbxError(RuntimeError):
 
 
 class CbxT3Config(C.Structure):
-    _fields_ = [("device", C.c_int32), ("n_layers", C.c_int32), ("max_pos", C.c_int32), ("kv_fp32", C.c_int32)]
+    _fields_ = [("device", C.c_int32), ("n_layers", C.c_int32), ("max_pos", C.c_int32), ("kv_fp32", C.c_int32),
+                ("speech_pos_rows", C.c_int32)]
 
 
 class CbxT3Weights(C.Structure):
@@ -59,6 +60,7 @@ SYMBOLS = {
     "cbx_cfm_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                 C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_void_p, C.c_void_p]),
     "cbx_cfm_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "cbx_cfm_cache_sizes": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "cbx_hift_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxHiftWeights), C.POINTER(C.c_void_p)]),
     "cbx_hift_destroy": (C.c_int, [C.c_void_p]),
     "cbx_hift_f0": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),

@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcbx.so")
 SOURCES = ["cbx_core.cu", "t3_decode.cu", "t3_prefill.cu", "s3_gemm.cu", "s3_attn.cu", "s3_cfm.cu", "s3_hift.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC", "--use_fast_math_off_placeholder"]
+              "-shared", "-Xcompiler", "-fPIC"]
 
 
 def _sources():
@@ -34,7 +34,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    flags = [f for f in NVCC_FLAGS if not f.endswith("_placeholder")]
+    flags = list(NVCC_FLAGS)
     if verbose:
         flags += ["-Xptxas", "-v"]
     flags += os.environ.get("CBX_NVCC_EXTRA", "").split()

@@ -94,6 +94,14 @@ def euler_schedule(n_timesteps: int):
     return ts, dts
 
 
+def _check_mask(mask) -> None:
+    """One un-padded utterance = an all-ones mask (decoder.py:25-33 then adds a zero bias).  `None` means exactly
+    that and costs nothing; a host tensor is checked on the host; a DEVICE tensor is checked too, which is a host
+    sync — the in-tree callers (s3gen.py) pass None."""
+    if mask is not None:
+        assert bool((mask == 1).all()), "only un-padded utterances (all-ones mask) are supported"
+
+
 class ConditionalDecoder:
     """The estimator (decoder.py:100-317).  forward(x, mask, mu, t, spks, cond) with batch 2."""
 
@@ -127,10 +135,15 @@ class ConditionalDecoder:
         _lib.check(self._lib.cbx_cfm_launches(self._h, C.byref(n)))
         return n.value
 
+    def cache_sizes(self):
+        g, p = C.c_int32(), C.c_int32()
+        _lib.check(self._lib.cbx_cfm_cache_sizes(self._h, C.byref(g), C.byref(p)))
+        return g.value, p.value
+
     @torch.inference_mode()
     def forward(self, x, mask, mu, t, spks=None, cond=None):
         assert x.shape[0] == 2 and x.shape[1] == 80, "estimator runs the CFG pair (batch 2)"
-        assert bool((mask == 1).all()), "only un-padded utterances (all-ones mask) are supported"
+        _check_mask(mask)
         assert float(t[0]) == float(t[1])
         L = x.shape[2]
         f = lambda a: a.to(self.device, torch.float32).contiguous()
@@ -160,7 +173,7 @@ class CausalConditionalCFM:
     @torch.inference_mode()
     def forward(self, mu, mask, n_timesteps, temperature=1.0, spks=None, cond=None):
         assert mu.shape[0] == 1 and mu.shape[1] == 80
-        assert bool((mask == 1).all()), "only un-padded utterances (all-ones mask) are supported"
+        _check_mask(mask)
         L = mu.shape[2]
         e = self.estimator
         f = lambda a: a.to(self.device, torch.float32).contiguous()

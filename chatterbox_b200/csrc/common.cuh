@@ -26,6 +26,24 @@ void cbx_set_error(const char* fmt, ...);
     }                                                                                          \
   } while (0)
 
+// Entry points run on the handle's device and leave the caller's current device as they found it.
+struct CbxDeviceGuard {
+  int prev, dev; bool ok;
+  explicit CbxDeviceGuard(int d) : prev(-1), dev(d), ok(true) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != d) ok = cudaSetDevice(d) == cudaSuccess;
+  }
+  ~CbxDeviceGuard() { if (prev >= 0 && prev != dev) cudaSetDevice(prev); }
+};
+#define CBX_ON_DEVICE(d)                                                                        \
+  CbxDeviceGuard guard__(d);                                                                    \
+  CBX_CHECK(guard__.ok, "cudaSetDevice(%d) failed (this library has no CPU fallback)", (int)(d))
+// once-per-device flag for per-function attributes (cudaFuncSetAttribute applies to the current device only)
+struct CbxPerDeviceOnce {
+  bool done[64] = {};
+  bool first() { int d = 0; cudaGetDevice(&d); d &= 63; const bool f = !done[d]; done[d] = true; return f; }
+};
+
 #ifdef __CUDACC__
 namespace cbx {
 

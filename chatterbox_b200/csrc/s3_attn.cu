@@ -206,11 +206,9 @@ __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16
 
 int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, cudaStream_t st) {
   dim3 grid((L + AT_BM - 1) / AT_BM, 8, B);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static CbxPerDeviceOnce once;
+  if (once.first())
     CBX_CUDA(cudaFuncSetAttribute(s3_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
-    attr_set = true;
-  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = dim3(128 * AT_G); cfg.dynamicSmemBytes = AT_SMEM; cfg.stream = st;
   cudaLaunchAttribute at[1];

@@ -102,6 +102,8 @@ __global__ void k_euler(const float* __restrict__ est, float* __restrict__ x, __
   if (last) mel_out[(size_t)ch * L + t] = xn;
 }
 
+constexpr int CFM_MAX_GRAPHS = 8;      // cached executable solve graphs (LRU)
+constexpr int CFM_MAX_PLANS = 64;      // cached per-length op plans (331 tensor maps each, host memory)
 struct Op { int kind; GemmDesc g; int temb_res; };   // kind 0 gemm, 1 attention, 2 skip copy
 struct Plan { int L; std::vector<Op> ops; };
 
@@ -186,6 +188,7 @@ static int build_plan(cbx_cfm* h, int L, Plan** out) {
     G(h->cur_b, C, BF_TAIL + 2, C, C, 3, e, -1); }
   { GemmEpi e{}; e.bias = FW(h, F_TAIL + 5); e.out_f32 = h->est; e.ld_f32 = NMEL; G(h->h1, C, BF_TAIL + 3, NMEL, C, 1, e, -1); }
   if (rc) return CBX_ERR;
+  if ((int)h->plans.size() >= CFM_MAX_PLANS) h->plans.erase(h->plans.begin());   // plans are rebuilt on demand (host work only)
   auto ins = h->plans.emplace(L, std::move(pl));
   *out = &ins.first->second;
   return CBX_OK;
@@ -226,7 +229,7 @@ static int time_vectors(cbx_cfm* h, const float* t_host, int n, cudaStream_t st)
 extern "C" int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, cbx_cfm** out) {
   CBX_CHECK(w && out && w->bf16_blob && w->f32_blob && w->bf16_off && w->f32_off, "cbx_cfm_create: null argument");
   CBX_CHECK(max_len >= 1, "cbx_cfm_create: max_len must be positive");
-  CBX_CUDA(cudaSetDevice(device));
+  CBX_ON_DEVICE(device);
   cudaDeviceProp prop;
   CBX_CUDA(cudaGetDeviceProperties(&prop, device));
   CBX_CHECK(prop.major == 10, "cbx_cfm_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
@@ -278,7 +281,7 @@ extern "C" int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, co
   CBX_CHECK(h && x && mu && spks && cond && out, "cbx_cfm_estimator: null argument");
   CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_estimator: L=%d exceeds max_len %d", L, h->max_len);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  CBX_CUDA(cudaSetDevice(h->device));
+  CBX_ON_DEVICE(h->device);
   Plan* pl;
   if (build_plan(h, L, &pl)) return CBX_ERR;
   if (time_vectors(h, &t, 1, st)) return CBX_ERR;
@@ -316,7 +319,7 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
   CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_solve: L=%d exceeds max_len %d", L, h->max_len);
   CBX_CHECK(n_steps >= 1 && n_steps <= h->max_steps, "cfm: n_steps %d out of range (max %d)", n_steps, h->max_steps);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  CBX_CUDA(cudaSetDevice(h->device));
+  CBX_ON_DEVICE(h->device);
   Plan* pl;
   if (build_plan(h, L, &pl)) return CBX_ERR;
   CBX_CUDA(cudaMemcpyAsync(h->tvals, t_vals, n_steps * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -327,8 +330,19 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
       if (c.L == L && c.n == n_steps && c.cfg == cfg_rate && c.t == std::vector<float>(t_vals, t_vals + n_steps) &&
           c.dt == std::vector<float>(dt_vals, dt_vals + n_steps)) { g = &c; break; }
     if (!g) {
+      // bounded: a long-lived server sees ~1 250 distinct mel lengths; the oldest entry (and its ~3 400-node
+      // executable graph) is dropped, its length simply runs eagerly again until it is seen twice
+      if ((int)h->graphs.size() >= CFM_MAX_GRAPHS) {
+        if (h->graphs.front().exec) cudaGraphExecDestroy(h->graphs.front().exec);
+        h->graphs.erase(h->graphs.begin());
+      }
       h->graphs.push_back({L, n_steps, 0, cfg_rate, std::vector<float>(t_vals, t_vals + n_steps),
                            std::vector<float>(dt_vals, dt_vals + n_steps), nullptr, 0});
+      g = &h->graphs.back();
+    } else if (g != &h->graphs.back()) {          // most recently used last
+      cbx_cfm::SolveGraph tmp = std::move(*g);
+      h->graphs.erase(h->graphs.begin() + (g - &h->graphs[0]));
+      h->graphs.push_back(std::move(tmp));
       g = &h->graphs.back();
     }
     g->seen += 1;
@@ -366,6 +380,13 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
 namespace cbx { void gemm_set_debug(unsigned long long* buf); }
 /* Debug aid (not in cbx.h): every following GEMM launch writes 8 %globaltimer stamps of CTA (0,0) to buf and advances it. */
 extern "C" int cbx_dbg_gemm_stamps(unsigned long long* buf) { cbx::gemm_set_debug(buf); return 0; }
+
+extern "C" int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans) {
+  CBX_CHECK(h, "cbx_cfm_cache_sizes: null handle");
+  if (n_graphs) *n_graphs = (int32_t)h->graphs.size();
+  if (n_plans) *n_plans = (int32_t)h->plans.size();
+  return CBX_OK;
+}
 
 extern "C" int cbx_cfm_launches(cbx_cfm* h, int64_t* launches) {
   CBX_CHECK(h && launches, "cbx_cfm_launches: null argument");

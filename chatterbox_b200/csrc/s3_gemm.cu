@@ -572,11 +572,9 @@ uint32_t epi_features(const GemmEpi& e) {
 }
 template <uint32_t FEAT>
 int launch_as(const GemmParams& p, dim3 grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static CbxPerDeviceOnce once;        // per device: a single-process multi-GPU server launches on every ordinal
+  if (once.first())
     CBX_CUDA(cudaFuncSetAttribute(s3_gemm_kernel<FEAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    attr_set = true;
-  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = GEMM_SMEM; cfg.stream = st;
   cudaLaunchAttribute at[2];

@@ -347,7 +347,7 @@ static int hift_decode(cbx_hift* h, const float* mel, int L, const float* s, int
 extern "C" int cbx_hift_create(int device, int max_frames, const CbxHiftWeights* w, cbx_hift** out) {
   CBX_CHECK(w && out && w->bf16_blob && w->f32_blob && w->bf16_off && w->f32_off, "cbx_hift_create: null argument");
   CBX_CHECK(max_frames >= 1, "cbx_hift_create: max_frames must be positive");
-  CBX_CUDA(cudaSetDevice(device));
+  CBX_ON_DEVICE(device);
   cudaDeviceProp prop;
   CBX_CUDA(cudaGetDeviceProperties(&prop, device));
   CBX_CHECK(prop.major == 10, "cbx_hift_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
@@ -393,7 +393,7 @@ extern "C" int cbx_hift_destroy(cbx_hift* h) {
   CBX_CHECK(h, name ": null handle");                                                               \
   CBX_CHECK(L >= 1 && L <= h->max_frames, name ": L=%d exceeds max_frames %d", L, h->max_frames);  \
   cudaStream_t st = static_cast<cudaStream_t>(stream);                                             \
-  CBX_CUDA(cudaSetDevice(h->device));
+  CBX_ON_DEVICE(h->device);
 
 extern "C" int cbx_hift_f0(cbx_hift* h, const float* mel, int L, float* f0_out, void* stream) {
   HIFT_ENTER("cbx_hift_f0");

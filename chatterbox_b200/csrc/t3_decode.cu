@@ -1454,7 +1454,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   if (c == 0 && tid == 0) {
     p.st->pos = pos0;
     p.st->n_gen = n_gen;
-    if (p.mode == 1 && p.n_out) *p.n_out = n_done;
+    // a device error (watchdog) reaches the host in the same word as the token count: -(n + 1)
+    if (p.mode == 1 && p.n_out) *p.n_out = (ctl->abort || __ldcg(&p.st->err)) ? -(n_done + 1) : n_done;
   }
   __syncthreads();
   // drain: every copy in flight must have landed before the CTA may exit (early stop on EOS / abort)
@@ -1480,6 +1481,8 @@ struct cbx_t3 {
   T3Params base;        // pointers to owned scratch, filled at create
   void* slab;           // one allocation for all scratch
   int B;                // rows of the current utterance
+  int host_pos;         // upper bound of the cache length after the calls issued so far (EOS may stop a launch early)
+  int host_gen;         // same for the generated-token count
   long long launches;
   unsigned long long* prof; int prof_it;
   void* prefill_ws;     // workspace of the GEMM prefill (NULL without plain weights)
@@ -1518,7 +1521,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CHECK(cfg && w && out, "cbx_t3_create: null argument");
   CBX_CHECK(cfg->n_layers >= 1 && cfg->n_layers <= 64, "cbx_t3_create: n_layers %d out of range", cfg->n_layers);
   CBX_CHECK(cfg->max_pos >= 8, "cbx_t3_create: max_pos too small");
-  CBX_CUDA(cudaSetDevice(cfg->device));
+  CBX_ON_DEVICE(cfg->device);
   cudaDeviceProp prop;
   CBX_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
   CBX_CHECK(prop.major == 10, "cbx_t3_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
@@ -1530,7 +1533,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CHECK(coop, "cbx_t3_create: device lacks cooperative launch");
 
   cbx_t3* h = new cbx_t3();
-  h->cfg = *cfg; h->w = *w; h->G = G; h->B = 2; h->launches = 0; h->prof = nullptr; h->prof_it = -1;
+  h->cfg = *cfg; h->w = *w; h->G = G; h->B = 2; h->host_pos = 0; h->host_gen = 0; h->launches = 0; h->prof = nullptr; h->prof_it = -1;
   const size_t kvel = cfg->kv_fp32 ? 4 : 2;
   const size_t kv_bytes = (size_t)cfg->n_layers * 2 * T3_NH * cfg->max_pos * T3_HD * kvel;
   size_t off = 0;
@@ -1593,9 +1596,9 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
   CBX_CHECK(B == 1 || B == 2, "cbx_t3_prefill: B must be 1 or 2 (got %d)", B);
   CBX_CHECK(P >= 1 && P <= h->cfg.max_pos, "cbx_t3_prefill: P=%d exceeds the KV slab (max_pos %d)", P, h->cfg.max_pos);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  CBX_CUDA(cudaSetDevice(h->cfg.device));
+  CBX_ON_DEVICE(h->cfg.device);
   T3Params p = h->base;
-  h->B = B;
+  h->B = B; h->host_pos = P; h->host_gen = 0;
   // reset per-utterance state: cache length 0, generated set = {BOS 6561} (t3.py:298)
   CBX_CUDA(cudaMemsetAsync(p.st, 0, sizeof(T3State), st));
   CBX_CUDA(cudaMemsetAsync(p.seen, 0, VOCAB_PAD, st));
@@ -1656,8 +1659,15 @@ extern "C" int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_t
   CBX_CHECK(max_new_tokens >= 1, "cbx_t3_decode: max_new_tokens must be >= 1");
   CBX_CHECK(sp->temperature > 0.f, "cbx_t3_decode: temperature must be > 0");
   CBX_CHECK(sp->repetition_penalty > 0.f, "cbx_t3_decode: repetition_penalty must be > 0");
+  CBX_CHECK(h->host_pos > 0, "cbx_t3_decode: no prefill on this handle yet");
+  CBX_CHECK(h->host_pos + max_new_tokens <= h->cfg.max_pos, "cbx_t3_decode: %d cached + %d new positions exceed the KV slab (max_pos %d)",
+            h->host_pos, max_new_tokens, h->cfg.max_pos);
+  CBX_CHECK(h->cfg.speech_pos_rows <= 0 || h->host_gen + max_new_tokens + 1 <= h->cfg.speech_pos_rows,
+            "cbx_t3_decode: %d + %d tokens exceed the learned speech position table (%d rows)", h->host_gen, max_new_tokens,
+            h->cfg.speech_pos_rows);
+  h->host_pos += max_new_tokens; h->host_gen += max_new_tokens;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  CBX_CUDA(cudaSetDevice(h->cfg.device));
+  CBX_ON_DEVICE(h->cfg.device);
   T3Params p = h->base;
   p.mode = 1; p.B = h->B; p.sp = *sp; p.max_new = max_new_tokens; p.forced = forced_tokens;
   p.tokens_out = tokens_out; p.n_out = n_out; p.logits_out = logits_out;

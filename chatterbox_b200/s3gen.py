@@ -103,7 +103,7 @@ class S3Gen:
         if ev:
             ev["cfm0"].record()
         L = mu.shape[2]
-        feat, _ = self.decoder(mu=mu, mask=torch.ones(1, 1, L, device=self.device), n_timesteps=10, spks=spks, cond=cond)
+        feat, _ = self.decoder(mu=mu, mask=None, n_timesteps=10, spks=spks, cond=cond)     # None = all ones, no host sync
         if ev:
             ev["cfm1"].record()
             self.events.update(ev)

@@ -90,7 +90,7 @@ class T3:
         self.fe["speech_emb.weight"] = self.packed.speech_emb
         self.fe["speech_pos_emb.emb.weight"] = self.packed.speech_pos_emb
         p = self.packed
-        cfg = _lib.CbxT3Config(self.device.index, n_layers, max_pos, 1 if kv_fp32 else 0)
+        cfg = _lib.CbxT3Config(self.device.index, n_layers, max_pos, 1 if kv_fp32 else 0, int(p.speech_pos_emb.shape[0]))
         w = _lib.CbxT3Weights(p.wstream.data_ptr(), p.stride_units, p.ln1.data_ptr(), p.ln2.data_ptr(),
                               p.final_norm.data_ptr(), p.speech_emb.data_ptr(), p.speech_pos_emb.data_ptr(),
                               p.rope_cos.data_ptr(), p.rope_sin.data_ptr(),
@@ -217,8 +217,9 @@ class T3:
             ev["decode1"].record()
             self.events = ev
         self.last_prefill_len = P
-        n = int(n_out.item())            # the only host sync of the utterance
-        self.check_device_state()
+        n = int(n_out.item())            # the only host sync of the utterance (a device error comes back as n < 0)
+        if n < 0:
+            raise _lib.CbxError(f"T3 megakernel reported a device error after {-n - 1} tokens (watchdog timeout)")
         self.last_logits = logits[:n] if logits is not None else None
         return tokens[:n].to(torch.long)[None]
 

@@ -20,7 +20,7 @@ import torch.nn.functional as F
 
 from . import _lib
 from .s3gen import S3GEN_SR, S3Gen
-from .t3 import T3, T3Cond
+from .t3 import T3, T3Cond, T3Config
 
 REPO_ID = "ResembleAI/chatterbox"
 S3_SR = 16000
@@ -112,7 +112,8 @@ class ChatterboxTTS:
     @classmethod
     def from_state_dicts(cls, t3_sd: Dict[str, torch.Tensor], flow_sd: Dict[str, torch.Tensor],
                          hift_sd: Dict[str, torch.Tensor], device="cuda", conds: Optional[Conditionals] = None,
-                         tokenizer=None, *, rand_noise=None, max_speech_tokens: int = 1000, max_text_tokens: int = 256,
+                         tokenizer=None, *, rand_noise=None, max_speech_tokens: int = 1000,
+                         max_text_tokens: int = T3Config.max_text_tokens,
                          max_prompt_tokens: int = 250) -> "ChatterboxTTS":
         max_pos = 34 + max_text_tokens + 4 + max_speech_tokens + 8
         t3 = T3(t3_sd, device, max_pos=max_pos)
@@ -146,6 +147,15 @@ class ChatterboxTTS:
             local_path = hf_hub_download(repo_id=REPO_ID, filename=fpath)
         return cls.from_local(Path(local_path).parent, device)
 
+    def _emotion_adv_host(self) -> float:
+        """`conds.t3.emotion_adv` as a host float, read from the device once per T3Cond object (the reference
+        compares against the tensor on every call, tts.py:225: a host sync per utterance when conds live on the GPU)."""
+        c = self.conds.t3
+        key = (id(c), id(c.emotion_adv))
+        if getattr(self, "_emo_cache", (None, None))[0] != key:
+            self._emo_cache = (key, float(c.emotion_adv.reshape(-1)[0]))
+        return self._emo_cache[1]
+
     def prepare_conditionals(self, wav_fpath, exaggeration=0.5):
         raise NotImplementedError("prepare_conditionals (voice encoder, S3 tokenizer, CAM++ x-vector) is outside the "
                                   "accelerated path and its third-party networks are not bundled; load pre-computed "
@@ -158,10 +168,11 @@ class ChatterboxTTS:
             self.prepare_conditionals(audio_prompt_path, exaggeration=exaggeration)
         else:
             assert self.conds is not None, "Please `prepare_conditionals` first or specify `audio_prompt_path`"
-        if exaggeration != self.conds.t3.emotion_adv[0, 0, 0]:
+        if exaggeration != self._emotion_adv_host():
             _cond = self.conds.t3
             self.conds.t3 = T3Cond(speaker_emb=_cond.speaker_emb, cond_prompt_speech_tokens=_cond.cond_prompt_speech_tokens,
                                    emotion_adv=exaggeration * torch.ones(1, 1, 1)).to(device=self.device)
+            self._emo_cache = ((id(self.conds.t3), id(self.conds.t3.emotion_adv)), float(exaggeration))
         if text_tokens is None:
             assert self.tokenizer is not None, "no tokenizer.json loaded: pass text_tokens=<ids> instead of text"
             text_tokens = self.tokenizer.text_to_tokens(punc_norm(text))

@@ -33,6 +33,7 @@ typedef struct CbxT3Config {
   int32_t n_layers;   /* 30 (llama_configs.py:8); smaller only in tests */
   int32_t max_pos;    /* KV slab capacity in positions (cond 34 + text + 2 BOS + speech) */
   int32_t kv_fp32;    /* 0: bf16 KV slab (perf mode), 1: fp32 KV slab (parity mode) */
+  int32_t speech_pos_rows; /* rows of speech_pos_emb (4100); decode calls that would index past it are rejected; 0 = unchecked */
 } CbxT3Config;
 
 typedef struct CbxT3Weights {          /* device pointers, caller-owned, must outlive the handle */
@@ -80,7 +81,9 @@ int cbx_t3_destroy(cbx_t3* h);
 int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void* stream);
 /* Decode loop (t3.py:319-367) as ONE persistent launch: up to max_new_tokens tokens; if
  * forced_tokens != NULL the loop is teacher-forced with those ids.  tokens_out [max_new_tokens]
- * int32, n_out [1] int32, logits_out (nullable) [max_new_tokens][B][8194] raw logits per step. */
+ * int32, n_out [1] int32 (tokens emitted; -(n + 1) if the device watchdog fired), logits_out (nullable)
+ * [max_new_tokens][B][8194] raw logits per step.  Calls that would run past the KV slab or the learned
+ * position table are rejected with an error before anything is launched. */
 int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_tokens, const int32_t* forced_tokens,
                   int32_t* tokens_out, int32_t* n_out, float* logits_out, void* stream);
 /* Host-visible state after a synchronised stream: cache length, tokens generated, device error flag,
@@ -120,6 +123,8 @@ int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, const float* 
 int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
                   int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out, void* stream);
 int cbx_cfm_launches(cbx_cfm* h, int64_t* launches);
+/* Entries of the handle's two bounded caches: executable solve graphs (LRU, at most 8) and per-length op plans (at most 64). */
+int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans);
 
 /* ------------------------------------------------------------------------------------------
  * (3) HiFT-GAN vocoder: mel -> f0 -> harmonic source -> waveform.

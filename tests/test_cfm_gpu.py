@@ -127,3 +127,22 @@ def test_full_euler_solve_at_baseline_sizes_vs_oracle(L):
         r = _rel(mel.cpu(), ref)
         print(f"10-step solve L={L} ({rep}) mel rel-L2 vs oracle: {r:.3e}")
         assert r < TOL
+
+
+def test_solve_graph_cache_is_bounded(est):
+    """A long-lived server sees many distinct mel lengths: the executable-graph cache is an LRU of 8 and the plan
+    cache holds at most 64 lengths; an evicted length still gives the same mel (it runs eagerly again)."""
+    from chatterbox_b200.cfm import CausalConditionalCFM
+    cfm = CausalConditionalCFM(est, rand_noise=S.cfm_noise())
+    first = None
+    for L in list(range(16, 16 + 12)) + [16]:
+        inp = S.cfm_inputs(L, seed=3)
+        for _ in range(2):                        # second call of a length captures + replays its graph
+            mel, _ = cfm(mu=inp["mu"], mask=None, n_timesteps=2, spks=inp["spks"], cond=inp["cond"])
+        if L == 16:
+            if first is None:
+                first = mel.clone()
+            else:
+                assert _rel(mel, first) < 1e-5
+    g, p = est.cache_sizes()
+    assert g <= 8 and p <= 64, (g, p)
