@@ -119,7 +119,8 @@ def _decode_bytes(weight_bytes: int, P: int, n: int) -> int:
 
 
 # -------------------------------------------------------------------------------------------------
-# reference arm / cpu_baseline: the oracle port of the reference's algorithm on the host cores
+# reference arm / cpu_baseline / cuda_eager_baseline: the oracle ports of the reference's algorithm, fp32 eager torch.
+# One call = ONE FULL utterance of the bench workload (nothing is sampled down or extrapolated).
 # -------------------------------------------------------------------------------------------------
 _SD_CACHE = {}
 
@@ -131,86 +132,113 @@ def _sd(name):
     return _SD_CACHE[name]
 
 
-def cpu_t3_sample(n_decode: int, threads: int):
-    """Prefill + n_decode greedy tokens of the full 30-layer model through the oracle restatement of
-    T3.inference (oracle/t3_oracle.py; reference t3.py:203-371), fp32.  Returns (prefill_s, per_token_s)."""
-    from chatterbox_b200 import synthetic as S
-    from oracle import t3_oracle as T3O
-    torch.set_num_threads(threads)
-    sd = _sd("t3")
-    cond = S.t3_cond(prompt_len=PROMPT_LEN)
-    text2 = torch.cat([S.text_tokens(N_TEXT)] * 2, 0)
-    with torch.inference_mode():
-        emb = T3O.prepare_input_embeds(sd, cond, text2, SAMPLE["cfg_weight"])
-        m = T3O.LlamaOracle(sd)
-        t0 = time.perf_counter()
-        logits = m.forward(emb)[:, -1]
-        t_prefill = time.perf_counter() - t0
-        gen = torch.tensor([[T3O.START_SPEECH]], dtype=torch.long)
-        t0 = time.perf_counter()
-        for i in range(n_decode):
-            proc = T3O.process_logits(logits, gen, **SAMPLE)
-            nxt = proc.argmax(dim=-1, keepdim=True)
-            gen = torch.cat([gen, nxt], dim=1)
-            e = (sd["speech_emb.weight"][nxt] + sd["speech_pos_emb.emb.weight"][i + 1]).expand(2, -1, -1)
-            logits = m.forward(e)[:, -1]
-        t_tok = (time.perf_counter() - t0) / n_decode
-    return t_prefill, t_tok
+class OraclePipeline:
+    """The reference's own math for the whole path — `T3.inference` (t3.py:203-371) greedy for 256 tokens ->
+    `flow.inference` front-end (flow.py:236-282) -> 10-step Euler/CFG solve at L = 812 (flow_matching.py:72-123) ->
+    `HiFTGenerator.inference` for 512 frames (hifigan.py:462-474) — through oracle/*.py on `device` ("cpu": the
+    reference arm; "cuda:0": PyTorch eager on the same B200, the library-call bar of BASELINE.md section 1).
+    Weights are moved / concatenated once at construction (model load), not per utterance."""
+
+    def __init__(self, device: str, threads: int):
+        from chatterbox_b200 import synthetic as S
+        from oracle import hift_oracle as HO, t3_oracle as T3O
+        self.dev = torch.device(device)
+        if self.dev.type == "cpu":
+            torch.set_num_threads(threads)
+        mv = lambda d: {k: v.to(self.dev) for k, v in d.items()}
+        self.sd_t3, self.sd_flow = mv(_sd("t3")), mv(_sd("flow"))
+        self.w_hift = mv(HO.fold_weight_norm(_sd("hift")))
+        self.cond = {k: v.to(self.dev) for k, v in S.t3_cond(prompt_len=PROMPT_LEN).items()}
+        self.text2 = torch.cat([S.text_tokens(N_TEXT)] * 2, 0).to(self.dev)
+        self.ref = {k: (v.to(self.dev) if torch.is_tensor(v) else v) for k, v in S.s3gen_ref(seed=4, prompt_len=PROMPT_LEN).items()}
+        self.noise = S.cfm_noise().to(self.dev)
+        self.llama = T3O.LlamaOracle(self.sd_t3)
+        g = torch.Generator().manual_seed(11)
+        self.phase = torch.zeros(1, 9, 1)
+        self.phase[:, 1:] = (torch.rand(1, 8, 1, generator=g) * 2 - 1) * torch.pi
+        self.phase = self.phase.to(self.dev)
+        self.src_noise = torch.randn(1, 9, 480 * 2 * N_SPEECH, generator=g).to(self.dev)
+
+    def _sync(self):
+        if self.dev.type == "cuda":
+            torch.cuda.synchronize(self.dev)
+
+    def utterance(self):
+        """-> (seconds, per-stage seconds, n_tokens, wav)"""
+        from oracle import cfm_oracle as CO, flow_oracle as FO, hift_oracle as HO, t3_oracle as T3O
+        sd, m = self.sd_t3, self.llama
+        m.k = [None] * m.n_layers
+        m.v = [None] * m.n_layers
+        m.pos = 0
+        parts = {}
+        with torch.inference_mode():
+            self._sync()
+            t0 = time.perf_counter()
+            emb = T3O.prepare_input_embeds(sd, self.cond, self.text2, SAMPLE["cfg_weight"])
+            logits = m.forward(emb)[:, -1]
+            self._sync()
+            t1 = time.perf_counter()
+            gen = torch.tensor([[T3O.START_SPEECH]], dtype=torch.long, device=self.dev)
+            for i in range(N_SPEECH):
+                proc = T3O.process_logits(logits, gen, **SAMPLE)
+                nxt = proc.argmax(dim=-1, keepdim=True)
+                gen = torch.cat([gen, nxt], dim=1)
+                e = (sd["speech_emb.weight"][nxt] + sd["speech_pos_emb.emb.weight"][i + 1]).expand(2, -1, -1)
+                logits = m.forward(e)[:, -1]
+            toks = gen[:, 1:]
+            toks = toks[toks < 6561][None]          # drop_invalid_tokens (tts.py:257-262)
+            self._sync()
+            t2 = time.perf_counter()
+            mu, spks, cond, l1 = FO.flow_inputs(self.sd_flow, toks, self.ref["prompt_token"], self.ref["prompt_feat"],
+                                                self.ref["embedding"])
+            self._sync()
+            t3 = time.perf_counter()
+            L = mu.shape[2]
+            mel = CO.solve_euler(self.sd_flow, self.noise[:, :, :L], mu, spks, cond, pfx="decoder.estimator.")[:, :, l1:]
+            self._sync()
+            t4 = time.perf_counter()
+            n = 480 * mel.shape[2]
+            wav, _ = HO.inference(self.w_hift, mel, phase_vec=self.phase, noise=self.src_noise[:, :, :n])
+            self._sync()
+            t5 = time.perf_counter()
+        parts = dict(t3_prefill_s=t1 - t0, t3_decode_s=t2 - t1, front_s=t3 - t2, cfm_solve_s=t4 - t3, hift_s=t5 - t4)
+        return t5 - t0, parts, int(toks.shape[1]), wav
 
 
-def cpu_s3gen_sample(n_euler: int, threads: int):
-    """Flow front-end + n_euler (of 10) Euler/CFG steps at L = 812 + the full HiFT decode for 512 frames through the
-    oracle restatements (oracle/cfm_oracle.py, oracle/hift_oracle.py), fp32 (the vocoder on a 128-frame slice, scaled x4).  Returns (front_s, per_euler_step_s, hift_s)."""
-    from chatterbox_b200 import flow_frontend as FF, synthetic as S
-    from oracle import cfm_oracle as CO, hift_oracle as HO
-    torch.set_num_threads(threads)
-    sd, ref = _sd("flow"), S.s3gen_ref(seed=4, prompt_len=PROMPT_LEN)
-    tok = S.speech_tokens(N_SPEECH, seed=5)
-    with torch.inference_mode():
-        t0 = time.perf_counter()
-        mu, spks, cond, l1 = FF.flow_inputs(sd, tok, ref["prompt_token"], ref["prompt_feat"], ref["embedding"])
-        t_front = time.perf_counter() - t0
-        L = mu.shape[2]
-        t0 = time.perf_counter()
-        x = CO.solve_euler(sd, S.cfm_noise()[:, :, :L], mu, spks, cond, n_timesteps=n_euler, pfx="decoder.estimator.")
-        t_step = (time.perf_counter() - t0) / n_euler
-        w = HO.fold_weight_norm(_sd("hift"))
-        mel = x[:, :, l1:l1 + 128]                 # 128 of the 512 frames; the vocoder is linear in length
-        s = torch.tanh(torch.randn(1, 1, 480 * mel.shape[2]) * 0.3)
-        t0 = time.perf_counter()
-        HO.decode(w, mel, s)
-        t_hift = (time.perf_counter() - t0) * (2 * N_SPEECH / 128.0)
-    return t_front, t_step, t_hift
-
-
-def cpu_pipeline_sample(ref_tokens: int, ref_euler: int, threads: int):
-    tp, tt = cpu_t3_sample(ref_tokens, threads)
-    tf, ts, th = cpu_s3gen_sample(ref_euler, threads)
-    utt_s = tp + N_SPEECH * tt + tf + 10 * ts + th
-    sample = (f"oracle ports on {threads} host threads, fp32: T3 full prefill + {ref_tokens} greedy tokens (x{N_SPEECH} "
-              f"extrapolated: prefill {tp:.2f} s, {tt * 1e3:.1f} ms/token), flow front-end {tf:.2f} s, {ref_euler} of 10 "
-              f"Euler/CFG steps at L=812 ({ts:.2f} s/step, x10 extrapolated), HiFT decode of 128 of 512 frames (x4 extrapolated: {th:.2f} s)")
-    return utt_s, sample, dict(t3_prefill_s=tp, t3_per_token_s=tt, front_s=tf, euler_step_s=ts, hift_s=th)
+def _oracle_sample_text(threads, dev):
+    where = f"{threads} host threads" if dev == "cpu" else "cuda:0 (PyTorch eager, library kernels)"
+    return (f"oracle ports (oracle/*.py = the reference's fp32 math) on {where}: ONE FULL utterance of the workload per step — "
+            f"T3 prefill + {N_SPEECH} greedy tokens, flow front-end, 10 Euler/CFG steps at L=812, HiFT {2 * N_SPEECH} frames; "
+            "nothing extrapolated")
 
 
 def run_reference(args, rank: int):
+    """`--impl reference`: the reference's CPU implementation of the path on the box's host cores, all threads, the
+    whole workload every step.  Under torchrun rank 0 alone runs it (the other ranks exit): at N > 1 the line is still
+    ONE host process, so only the N = 1 ratio compares like with like."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    vals = []
+    pipe = OraclePipeline("cpu", threads)
+    vals, parts_all = [], []
     for i in range(args.warmup + args.steps):
-        utt_s, sample, parts = cpu_pipeline_sample(args.ref_tokens, args.ref_euler, threads)
+        utt_s, parts, n_tok, _ = pipe.utterance()
+        assert n_tok == N_SPEECH
         if i >= args.warmup:
             vals.append(utt_s)
+            parts_all.append(parts)
     utt_s = statistics.mean(vals)
+    parts = {k: statistics.mean(p[k] for p in parts_all) for k in parts_all[0]}
     val = N_SPEECH / utt_s
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": utt_s * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": _config(),
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": _oracle_sample_text(threads, "cpu")},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0, "rtf": utt_s / AUDIO_S, "utterances_per_s": 1.0 / utt_s, "stages_s": parts}
+            "gpu_launches": 0, "rtf": utt_s / AUDIO_S, "utterances_per_s": 1.0 / utt_s, "stages_s": parts,
+            "host_processes": 1}
     print(json.dumps(line), flush=True)
 
 
@@ -346,10 +374,21 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                 "utterances_per_s": args.steps * world / (total_ms * 1e-3),
                 "rtf": step_s / AUDIO_S, "rtf_e2e": (e2e_ms / args.steps * 1e-3) / AUDIO_S}
         if not args.no_cpu_baseline and world == 1:
+            # the same restatements as PyTorch eager on this B200 (library kernels, fp32): the bar BASELINE.md section 1 names
+            eager = OraclePipeline(f"cuda:{local_rank}", 1)
+            eager.utterance()
+            runs = [eager.utterance() for _ in range(2)]
+            es = statistics.mean(r[0] for r in runs)
+            line["cuda_eager_baseline"] = {"value": N_SPEECH / es, "unit": UNIT, "kind": "port",
+                                           "sample": _oracle_sample_text(1, "cuda"), "ms_per_utterance": es * 1e3,
+                                           "stages_s": {k: statistics.mean(r[1][k] for r in runs) for k in runs[0][1]},
+                                           "rtf": es / AUDIO_S}
+            del eager
+            torch.cuda.empty_cache()
             threads = os.cpu_count() or 1
-            utt_s, sample, parts = cpu_pipeline_sample(args.ref_tokens, args.ref_euler, threads)
+            utt_s, parts, n_tok, _ = OraclePipeline("cpu", threads).utterance()
             line["cpu_baseline"] = {"value": N_SPEECH / utt_s, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": sample, "rtf": utt_s / AUDIO_S}
+                                    "sample": _oracle_sample_text(threads, "cpu"), "rtf": utt_s / AUDIO_S, "stages_s": parts}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -361,8 +400,6 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--ref-tokens", type=int, default=16, help="T3 decode tokens per CPU sample")
-    ap.add_argument("--ref-euler", type=int, default=2, help="Euler steps (of 10) per CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -62,7 +62,10 @@ constexpr int VPL = 1024 / NCONS_WARPS / 16;   // consecutive k one lane owns (8
 static_assert(VPL == 8 || VPL == 4, "T3_KW must be 8 or 16");
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
 constexpr int NTHREADS = NCONS;
-constexpr int MAXS = 4;                   // max KV splits per (row, head) pair
+#ifndef T3_MAXS
+#define T3_MAXS 4
+#endif
+constexpr int MAXS = T3_MAXS;             // KV splits per (row, head) pair (4: 128 attention CTAs; 2: 64, half the partial words)
 constexpr int PART_STRIDE = 68;           // 64 o + m + l (+2 pad)
 constexpr int STOP_SPEECH = 6562;
 constexpr int VOCAB_PAD = T3_VOCAB_PAD;
@@ -1283,6 +1286,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     const int n_steps = 4 * L + (with_head ? 1 : 0);
 #ifdef T3_DIRECT
     int uidx = 0;        // unit index inside this CTA's per-iteration stream
+    uint4 wreg[T3_MAXU][VPL];
+    [[maybe_unused]] bool preloaded = false;     // -DT3_EARLY: this step's units were requested at the end of the previous step
+    // request the units of a step (phase ph_, first unit u0): all of them, except the head's last two (its prologue polls
+    // four pieces: they follow the poll); HBM -> L2 runs T3_PF_DIST units ahead
+    auto issue_units = [&](int ph_, int u0) {
+      const int n_ = ctl->plan_n[ph_];
+      const uint8_t* ub = sm.base + (size_t)u0 * T3_UNIT_BYTES;
+      const int lofs = warp * (VPL * 32) + lane;
+      direct_load<0>(wreg, n_, ub, lofs, sm.policy);
+      direct_load<1>(wreg, n_, ub, lofs, sm.policy);
+      if (ph_ != PH_HEAD) {
+        direct_load<2>(wreg, n_, ub, lofs, sm.policy);
+        direct_load<3>(wreg, n_, ub, lofs, sm.policy);
+      }
+      if (tid == NCONS - 32) {
+        const int end = sm.per_iter_layers + (with_head ? sm.nhead : 0);
+        for (int j = 0; j < n_; ++j) {
+          int pf = u0 + j + T3_PF_DIST;
+          if (pf >= end) pf -= end;
+          if (pf < end) l2_prefetch_bulk(sm.base + (size_t)pf * T3_UNIT_BYTES, T3_UNIT_BYTES);
+        }
+      }
+    };
 #endif
 
 #pragma unroll 1
@@ -1293,25 +1319,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
       float* ssq = ssq_all + par * (NCONS_WARPS * 2);
 #ifdef T3_DIRECT
       const int n = ctl->plan_n[ph];
-      uint4 wreg[T3_MAXU][VPL];
-      {
-        const uint8_t* ub = sm.base + (size_t)uidx * T3_UNIT_BYTES;
-        const int lofs = warp * (VPL * 32) + lane;
-        direct_load<0>(wreg, n, ub, lofs, sm.policy);
-        direct_load<1>(wreg, n, ub, lofs, sm.policy);
-        if (ph != PH_HEAD) {         // the head's prologue polls 4 pieces: its last two units are loaded after it
-          direct_load<2>(wreg, n, ub, lofs, sm.policy);
-          direct_load<3>(wreg, n, ub, lofs, sm.policy);
-        }
-        if (tid == NCONS - 32) {      // HBM -> L2, T3_PF_DIST units ahead of the units of this step
-          const int end = sm.per_iter_layers + (with_head ? sm.nhead : 0);
-          for (int j = 0; j < n; ++j) {
-            int pf = uidx + j + T3_PF_DIST;
-            if (pf >= end) pf -= end;
-            if (pf < end) l2_prefetch_bulk(sm.base + (size_t)pf * T3_UNIT_BYTES, T3_UNIT_BYTES);
-          }
-        }
-      }
+#ifdef T3_EARLY
+      if (!preloaded) issue_units(ph, uidx);
+#else
+      issue_units(ph, uidx);
+#endif
 #endif
       // ---------- prologue: this lane's 8 input values ----------
       T3_SUB(0);
@@ -1370,6 +1382,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
         direct_mma<2>(wreg, n, Bf, red, warp, g, tig);
         direct_mma<3>(wreg, n, Bf, red, warp, g, tig);
         uidx += n;
+#ifdef T3_EARLY
+        // The registers of this step's units are free: request the NEXT step's units now, so their L2 -> SM transfer
+        // (up to 128 KB on a 4-unit CTA, ~1 us of ingress that the polls of the next prologue would queue behind) overlaps
+        // this step's reduction / epilogue and the hand-over.  Not across the attention call (128 live registers would be
+        // spilled around it): the o_proj units (one per CTA) are requested at the top of their step as before.
+        preloaded = false;
+        if (ph != PH_QKV && step + 1 < n_steps) {
+          const int l1 = (step + 1) >> 2;
+          issue_units((l1 == L) ? PH_HEAD : ((step + 1) & 3), uidx);
+          preloaded = true;
+        }
+#endif
       }
 #else
       const int n = ctl->plan_n[ph];

@@ -34,7 +34,7 @@ def time_embedding(sd: Dict[str, torch.Tensor], t: torch.Tensor, pfx: str = "") 
     """t (B,) -> (B, 1024)."""
     half = 160
     e = math.log(10000) / (half - 1)
-    e = torch.exp(torch.arange(half).float() * -e)
+    e = torch.exp(torch.arange(half, device=t.device).float() * -e)
     e = 1000 * t.unsqueeze(1) * e.unsqueeze(0)
     e = torch.cat((e.sin(), e.cos()), dim=-1)
     h = F.linear(e, sd[pfx + "time_mlp.linear_1.weight"], sd[pfx + "time_mlp.linear_1.bias"])
@@ -113,9 +113,9 @@ def t_schedule(n_timesteps: int = 10) -> torch.Tensor:
 def solve_euler(sd, z, mu, spks, cond, n_timesteps: int = 10, cfg_rate: float = 0.7, pfx: str = "",
                 n_mid: int = 12, n_tfm: int = 4, trace: Optional[List[torch.Tensor]] = None) -> torch.Tensor:
     """z, mu, cond (1,80,T); spks (1,80).  Returns x after n_timesteps Euler steps (1,80,T)."""
-    t_span = t_schedule(n_timesteps)
+    t_span = t_schedule(n_timesteps).to(z.device)
     T = z.shape[-1]
-    mask = torch.ones(1, 1, T)
+    mask = torch.ones(1, 1, T, device=z.device)
     x = z
     t, dt = t_span[0].unsqueeze(0), t_span[1] - t_span[0]
     for step in range(1, len(t_span)):

@@ -80,7 +80,7 @@ def sine_source(w, f0: torch.Tensor, phase_vec: torch.Tensor, noise: torch.Tenso
 
 def stft(s: torch.Tensor) -> torch.Tensor:
     """s (1, T) -> (1, 18, T/4 + 1): real parts of the 9 bins then imaginary parts (center=True, reflect pad)."""
-    spec = torch.stft(s, N_FFT, HOP, N_FFT, window=hann_periodic(), return_complex=True)
+    spec = torch.stft(s, N_FFT, HOP, N_FFT, window=hann_periodic().to(s.device), return_complex=True)
     spec = torch.view_as_real(spec)
     return torch.cat([spec[..., 0], spec[..., 1]], dim=1)
 
@@ -88,7 +88,7 @@ def stft(s: torch.Tensor) -> torch.Tensor:
 def istft(mag: torch.Tensor, phase: torch.Tensor) -> torch.Tensor:
     mag = torch.clip(mag, max=1e2)
     spec = torch.complex(mag * torch.cos(phase), mag * torch.sin(phase))
-    return torch.istft(spec, N_FFT, HOP, N_FFT, window=hann_periodic())
+    return torch.istft(spec, N_FFT, HOP, N_FFT, window=hann_periodic().to(spec.device))
 
 
 def snake(x: torch.Tensor, alpha: torch.Tensor) -> torch.Tensor:
@@ -152,7 +152,7 @@ def inference(w, mel: torch.Tensor, s: Optional[torch.Tensor] = None, phase_vec=
         s = sine_source(w, f0_predictor(w, mel), phase_vec, noise)
     wav = decode(w, mel, s)
     if apply_trim_fade:
-        tf = trim_fade()
+        tf = trim_fade().to(wav.device)
         wav = wav.clone()
         wav[:, : len(tf)] *= tf
     return wav, s

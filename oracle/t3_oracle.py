@@ -146,9 +146,11 @@ class LlamaOracle:
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """x (B, T, 1024) at absolute positions [pos, pos+T) -> logits (B, T, 8194)."""
         B, T, _ = x.shape
+        dev = x.device
         cos, sin = rope_cos_sin(torch.arange(self.pos, self.pos + T))
+        cos, sin = cos.to(dev), sin.to(dev)
         C = self.pos + T
-        mask = torch.full((T, C), float("-inf")).triu(diagonal=self.pos + 1)
+        mask = torch.full((T, C), float("-inf"), device=dev).triu(diagonal=self.pos + 1)
         for li, w in enumerate(self.L):
             h = _rmsnorm(x, w["ln1"])
             qkv = F.linear(h, w["wqkv"]).view(B, T, 3, NH, HD)

@@ -28,6 +28,22 @@ def test_frontend_matches_reference_capture():
     assert torch.equal(cond, GOLD["cond"])
 
 
+def test_oracle_frontend_matches_reference_capture():
+    """oracle/flow_oracle.py (the checker / CPU-baseline restatement) against the same reference capture, and the
+    product's torch front-end against the oracle at another shape."""
+    from oracle import flow_oracle as FO
+    sd = S.make_state_dict("flow")
+    ref, tok = _inputs()
+    with torch.inference_mode():
+        mu, spks, cond, l1 = FO.flow_inputs(sd, tok, ref["prompt_token"], ref["prompt_feat"], ref["embedding"])
+        assert l1 == 40 and (mu - GOLD["mu"]).abs().max() < 1e-4 and (spks - GOLD["spks"]).abs().max() < 1e-6
+        assert torch.equal(cond, GOLD["cond"])
+        ref2, tok2 = S.s3gen_ref(seed=9, prompt_len=7), S.speech_tokens(13, seed=6)
+        a = FO.flow_inputs(sd, tok2, ref2["prompt_token"], ref2["prompt_feat"], ref2["embedding"])
+        b = FF.flow_inputs(sd, tok2, ref2["prompt_token"], ref2["prompt_feat"], ref2["embedding"])
+    assert (a[0] - b[0]).abs().max() < 1e-5 and (a[1] - b[1]).abs().max() < 1e-6 and torch.equal(a[2], b[2])
+
+
 def test_rel_shift_known_answer():
     x = torch.arange(2 * 5, dtype=torch.float32).view(1, 1, 2, 5)      # T = 2... uses (T, 2T-1) = (3,5) below
     x = torch.arange(3 * 5, dtype=torch.float32).view(1, 1, 3, 5)
