@@ -29,6 +29,12 @@ class CbxSampleParams(C.Structure):
                 ("seed", C.c_uint64)]
 
 
+class CbxT3BatchConfig(C.Structure):
+    _fields_ = [("device", C.c_int32), ("n_layers", C.c_int32), ("n_slots", C.c_int32), ("max_pos", C.c_int32),
+                ("kv_fp32", C.c_int32), ("max_new_cap", C.c_int32), ("keep_logits", C.c_int32),
+                ("speech_pos_rows", C.c_int32)]
+
+
 class CbxCfmWeights(C.Structure):
     _fields_ = [("bf16_blob", C.c_void_p), ("f32_blob", C.c_void_p), ("bf16_off", C.POINTER(C.c_int64)),
                 ("f32_off", C.POINTER(C.c_int64))]
@@ -53,6 +59,17 @@ SYMBOLS = {
     "cbx_t3_decode": (C.c_int, [C.c_void_p, C.POINTER(CbxSampleParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p]),
     "cbx_t3_set_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "cbx_t3_batch_create": (C.c_int, [C.POINTER(CbxT3BatchConfig), C.POINTER(CbxT3Weights), C.POINTER(C.c_void_p)]),
+    "cbx_t3_batch_destroy": (C.c_int, [C.c_void_p]),
+    "cbx_t3_batch_prefill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(CbxSampleParams), C.c_int,
+                                       C.c_void_p, C.c_void_p]),
+    "cbx_t3_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_void_p]),
+    "cbx_t3_batch_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                    C.c_void_p]),
+    "cbx_t3_batch_tokens": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "cbx_t3_batch_logits": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "cbx_t3_batch_release": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "cbx_t3_batch_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "cbx_cfm_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxCfmWeights), C.POINTER(C.c_void_p)]),
     "cbx_cfm_destroy": (C.c_int, [C.c_void_p]),
     "cbx_cfm_estimator": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int,

@@ -53,7 +53,8 @@ int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1
 
 namespace {
 
-constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int BM = 128, BK = 64, STAGES = 4;         // STAGES: ring depth at the widest tile (n_tile = 256)
+constexpr int MAX_STAGES = 8;                        // narrower tiles get a deeper ring in the same shared memory
 constexpr int A_BYTES = BM * BK * 2;                 // 16 KB
 constexpr int W_BYTES_MAX = 256 * BK * 2;            // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + W_BYTES_MAX;
@@ -67,6 +68,7 @@ constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers
 struct GemmParams {
   CUtensorMap tmA, tmW;
   int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out, ksplit, hilo;
+  int nstages, stage_bytes;   // ring geometry: stage = A tile (16 KB) + W tile (n_tile x 128 B), 1024-byte aligned
   GemmEpi e;
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0,0) (debug aid)
 };
@@ -116,8 +118,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* empty = full + STAGES;
-  uint64_t* accum_bar = empty + STAGES;
+  uint64_t* empty = full + MAX_STAGES;
+  uint64_t* accum_bar = empty + MAX_STAGES;
+  const int NS = p.nstages, SB = p.stage_bytes;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
   float* par = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
   float* tile = reinterpret_cast<float*>(smem);
@@ -138,7 +141,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   const uint32_t tmem_cols = p.n_tile > 128 ? 256u : (p.n_tile > 64 ? 128u : (p.n_tile > 32 ? 64u : 32u));
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(accum_bar, 1);
     mbar_fence_init();
     tma_prefetch_desc(&p.tmA);
@@ -187,18 +190,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   if (warp == 0) {
     if (lane == 0) {
       const uint32_t tx = A_BYTES + p.n_tile * BK * 2;
-      const int npre = nkb < STAGES ? nkb : STAGES;
+      const int npre = nkb < NS ? nkb : NS;
       // weight panels of the first ring pass: issued before the PDL wait (they do not depend on the previous kernel)
       for (int i = 0; i < npre; ++i) {
         const int kb = kb0 + i;
         mbar_arrive_expect_tx(&full[i], tx);
-        tma_load_3d(smem + i * STAGE_BYTES + A_BYTES, &p.tmW, &full[i], (p.hilo ? kb % kpb : kb) * BK, n0, 0);
+        tma_load_3d(smem + i * SB + A_BYTES, &p.tmW, &full[i], (p.hilo ? kb % kpb : kb) * BK, n0, 0);
       }
       pdl_wait();
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % STAGES, ph = (i / STAGES) & 1, kb = kb0 + i;
+        const int s = i % NS, ph = (i / NS) & 1, kb = kb0 + i;
         const int tap = kb / kpb, kk = kb % kpb;
-        uint8_t* sa = smem + s * STAGE_BYTES;
+        uint8_t* sa = smem + s * SB;
         if (i >= npre) {
           mbar_wait_spin(&empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&full[s], tx);
@@ -213,10 +216,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(BM, p.n_tile);
       for (int kb = 0; kb < nkb; ++kb) {      // kb: local panel index
-        const int s = kb % STAGES, ph = (kb / STAGES) & 1;
+        const int s = kb % NS, ph = (kb / NS) & 1;
         mbar_wait_spin(&full[s], ph);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+        const uint32_t sa = smem_u32(smem + s * SB);
         const uint64_t da = umma_desc_k128(sa), db = umma_desc_k128(sa + A_BYTES);
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k)    // +32 bytes per K=16 step inside the 128-byte swizzle row
@@ -528,20 +531,34 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
 
 int gemm_make_hilo(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int K,
                    const GemmEpi& epi) {
+  return gemm_make_hilo_ex(d, A, lda, plane, W, M, N, N, K, epi, 0, 0);
+}
+
+int gemm_make_hilo_ex(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int N_w,
+                      int K, const GemmEpi& epi, int n_tile_req, int ksplit_req) {
   CBX_CHECK(K % BK == 0 && K >= BK, "gemm_make_hilo: K=%d must be a multiple of 64", K);
   int n_tile = 0;
-  for (int c = 256; c >= 16; c -= 16) if (N % c == 0) { n_tile = c; break; }
-  CBX_CHECK(n_tile > 0, "gemm_make_hilo: N=%d unsupported", N);
+  if (n_tile_req > 0) { if (n_tile_req % 16 == 0 && n_tile_req <= 256 && N % n_tile_req == 0) n_tile = n_tile_req; }
+  else for (int c = 256; c >= 16; c -= 16) if (N % c == 0) { n_tile = c; break; }
+  CBX_CHECK(n_tile > 0, "gemm_make_hilo: N=%d unsupported (tile %d)", N, n_tile_req);
+  CBX_CHECK(N_w >= 1 && N_w <= N, "gemm_make_hilo: %d weight rows for %d output columns", N_w, N);
   CBX_CHECK(!epi.swiglu || n_tile == 256, "gemm_make_hilo: SwiGLU pairs the halves of a 256-column tile (N=%d)", N);
   CBX_CHECK(!epi.ln_g && !epi.out_ln, "gemm_make_hilo: no row LayerNorm on this path");
   d->B = 1; d->L = M; d->N = N; d->K = K; d->taps = 2; d->n_tile = n_tile; d->epi = epi;
   d->dil = 0; d->pad = 0; d->M_out = M; d->hilo = 1;
   const int tiles = ((M + BM - 1) / BM) * (N / n_tile), nkb_all = 2 * (K / BK);
   d->ksplit = 1;
-  for (int sp = 2; sp >= 2; sp >>= 1)
-    if (nkb_all >= sp && tiles * sp <= 148) { d->ksplit = sp; break; }
+  if (ksplit_req > 0) {
+    CBX_CHECK(ksplit_req <= MAX_SPLIT && (ksplit_req & (ksplit_req - 1)) == 0 && nkb_all >= ksplit_req,
+              "gemm_make_hilo: split-K %d unsupported", ksplit_req);
+    d->ksplit = ksplit_req;
+  } else {
+    for (int sp = 2; sp >= 2; sp >>= 1)
+      if (nkb_all >= sp && tiles * sp <= 148) { d->ksplit = sp; break; }
+  }
   if (make_tmap_bf16_3d(&d->tmA, A, K, M, 2, lda, (uint64_t)plane, BK, BM)) return CBX_ERR;
-  if (make_tmap_bf16_3d(&d->tmW, W, K, N, 1, K, (uint64_t)K * N, BK, n_tile)) return CBX_ERR;
+  // N_w < N: weight rows past the matrix arrive as zeros (TMA out-of-bounds fill), the output buffer is padded to N
+  if (make_tmap_bf16_3d(&d->tmW, W, K, N_w, 1, K, (uint64_t)K * N_w, BK, n_tile)) return CBX_ERR;
   return CBX_OK;
 }
 
@@ -609,6 +626,9 @@ int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;
   p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit; p.hilo = d.hilo;
   p.tiles_l = (d.M_out + BM - 1) / BM;
+  p.stage_bytes = (A_BYTES + d.n_tile * BK * 2 + 1023) / 1024 * 1024;      // 128-byte-swizzled tiles start 1024-byte aligned
+  p.nstages = (STAGES * STAGE_BYTES) / p.stage_bytes;
+  if (p.nstages > MAX_STAGES) p.nstages = MAX_STAGES;
   p.e = d.epi;
   p.dbg = g_gemm_dbg;
   if (g_gemm_dbg) g_gemm_dbg += 16;

@@ -47,6 +47,11 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
 // C[m][n] = sum_k (A_hi[m][k] + A_lo[m][k]) * W[n][k]: A = two bf16 planes [2][M][lda], plane stride in elements
 int gemm_make_hilo(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int K,
                    const GemmEpi& epi);
+// same with an explicit column tile (0 = widest divisor of N), explicit split-K cluster size (0 = automatic) and a
+// weight matrix of N_w <= N rows (output columns >= N_w are zero): the skinny (M <= 128) decode GEMMs of the batched
+// T3 engine want many narrow tiles so that every SM streams weights
+int gemm_make_hilo_ex(GemmDesc* d, const __nv_bfloat16* A, int lda, long long plane, const __nv_bfloat16* W, int M, int N, int N_w,
+                      int K, const GemmEpi& epi, int n_tile, int ksplit);
 int gemm_launch(const GemmDesc& d, cudaStream_t st);
 // true unless CBX_PDL=0: kernels are launched with programmatic stream serialization (prologue overlap)
 bool pdl_enabled();

@@ -1632,7 +1632,7 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
   if (h->prefill_ws && !force_mega) {
     // the prompt through each weight matrix once (tcgen05 GEMMs); leaves the slab, the position counter and the
     // pending logits as the megakernel's own prefill mode would
-    cbx::T3PrefillArgs a;
+    cbx::T3PrefillArgs a{};
     a.embeds = embeds; a.B = B; a.P = P; a.n_layers = h->cfg.n_layers; a.max_pos = h->cfg.max_pos; a.kv_fp32 = h->cfg.kv_fp32;
     a.wplain = h->w.wplain; a.ln1 = p.ln1; a.ln2 = p.ln2; a.final_norm = p.final_norm;
     a.rope_cos = p.rope_cos; a.rope_sin = p.rope_sin; a.kcache = p.kcache; a.vcache = p.vcache;

@@ -14,46 +14,13 @@
 // megakernel's own prefill mode leaves them.
 #include "t3_prefill.h"
 #include "s3_gemm.cuh"
+#include "t3_rows.cuh"
 #include "../../include/cbx.h"
 
 namespace cbx {
 namespace {
 
-constexpr int H = 1024, NH = 16, HD = 64, INTER = 4096, VOCAB = 8194;
-constexpr float RMS_EPS = 1e-5f;
-
-// one row per CTA (256 threads x 4 values): out planes [2][rows][1024] = hi / lo of gain * x * rsqrt(mean(x^2) + eps)
-__global__ void __launch_bounds__(256) k_rms_hilo(const float* __restrict__ x, const float* __restrict__ gain,
-                                                  __nv_bfloat16* __restrict__ out, long long plane) {
-  __shared__ float red[8];
-  const int row = blockIdx.x, t = threadIdx.x;
-  const float4 v = *reinterpret_cast<const float4*>(x + (size_t)row * H + t * 4);
-  float s = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-  s = warp_sum(s);
-  if ((t & 31) == 0) red[t >> 5] = s;
-  __syncthreads();
-  float tot = 0.f;
-#pragma unroll
-  for (int w = 0; w < 8; ++w) tot += red[w];
-  const float sc = rsqrtf(tot * (1.0f / H) + RMS_EPS);
-  const float4 g = __ldg(reinterpret_cast<const float4*>(gain + t * 4));
-  uint32_t h0, l0, h1, l1;
-  split_hi_lo(g.x * (v.x * sc), g.y * (v.y * sc), h0, l0);
-  split_hi_lo(g.z * (v.z * sc), g.w * (v.w * sc), h1, l1);
-  __nv_bfloat16* d = out + (size_t)row * H + t * 4;
-  *reinterpret_cast<uint2*>(d) = make_uint2(h0, h1);
-  *reinterpret_cast<uint2*>(d + plane) = make_uint2(l0, l1);
-}
-
-template <typename KVT> struct KVS;
-template <> struct KVS<__nv_bfloat16> {
-  static __device__ __forceinline__ float round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
-  static __device__ __forceinline__ void store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
-};
-template <> struct KVS<float> {
-  static __device__ __forceinline__ float round(float v) { return v; }
-  static __device__ __forceinline__ void store(float* p, float v) { *p = v; }
-};
+using namespace t3rows;
 
 // grid (P, B), 1024 threads = (head, d): RoPE (rotate_half pairing d <-> d ^ 32) on q and k in place, q pre-scaled by
 // 1/8; K / V rounded to the slab's element type, appended at position pos0 + p and written back so the attention
@@ -155,7 +122,7 @@ __global__ void __launch_bounds__(256) k_attn_prefill(const float* __restrict__ 
 
 // final RMSNorm of the last position of each CFG row + speech_head GEMV: one warp per vocabulary row
 __global__ void __launch_bounds__(256) k_head(const float* __restrict__ x, int P, int B, const float* __restrict__ gain,
-                                              const __nv_bfloat16* __restrict__ w, float* __restrict__ logits) {
+                                              const __nv_bfloat16* __restrict__ w, float* __restrict__ logits, int ld) {
   __shared__ float xs[2][H];
   __shared__ float red[2][8];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -196,7 +163,7 @@ __global__ void __launch_bounds__(256) k_head(const float* __restrict__ x, int P
   a0 = warp_sum(a0); a1 = warp_sum(a1);
   if (lane == 0) {
     logits[row] = a0;
-    if (B == 2) logits[VOCAB + row] = a1;
+    if (B == 2) logits[ld + row] = a1;
   }
 }
 
@@ -247,7 +214,8 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
     if (gemm_make_hilo(&d, act, INTER, act_plane, wdn, rows, H, INTER, e) || gemm_launch(d, st)) return CBX_ERR;
   }
-  k_head<<<(VOCAB + 7) / 8, 256, 0, st>>>(x, a.P, a.B, a.final_norm, wp + a.n_layers * per_layer, a.logits);
+  k_head<<<(VOCAB + 7) / 8, 256, 0, st>>>(x, a.P, a.B, a.final_norm, wp + a.n_layers * per_layer, a.logits,
+                                           a.logits_ld > 0 ? a.logits_ld : VOCAB);
   k_set_pos<<<1, 1, 0, st>>>(a.state, a.P);
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;

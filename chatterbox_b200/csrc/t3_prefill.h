@@ -12,7 +12,8 @@ struct T3PrefillArgs {
                              // 256-row tile][down 1024x4096], then speech_head [8194][1024]
   const float *ln1, *ln2, *final_norm, *rope_cos, *rope_sin;
   void *kcache, *vcache;     // the decode kernel's slab [layer][2][16][max_pos][64]
-  float* logits;             // [2][8194] pending logits of the last prompt position
+  float* logits;             // [2][logits_ld] pending logits of the last prompt position
+  int logits_ld;             // floats between the two rows (0 = 8194)
   int* state;                // {pos, n_gen, stop, err}
   void* workspace;           // t3_prefill_workspace_bytes(max_pos)
 };

@@ -97,6 +97,50 @@ int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t*
 int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it);
 
 /* ------------------------------------------------------------------------------------------
+ * (1b) Batched T3 decode: up to 64 concurrent utterances ("slots") per handle, one pass of all slots' CFG pairs
+ * through every weight matrix per step (BASELINE config 4).  Replaces the reference server's one-request-at-a-time
+ * loop (src/server/server.py:189-299: one synchronous tts_model.generate per request, :223,232; global
+ * model.conds swap, src/server/voice_manager.py:370-379): the per-request state — KV slab, generated-id set,
+ * sampling knobs, Philox stream, EOS flag — lives in per-slot device arrays, so requests with different voices and
+ * knobs share the 1.02 GB weight stream of a step.  Same arithmetic per utterance as (1): hi / lo activation
+ * planes against bf16 weights, fp32 accumulate, bf16 (or fp32) KV, identical logit processing and sampling.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct cbx_t3b cbx_t3b;
+
+typedef struct CbxT3BatchConfig {
+  int32_t device;
+  int32_t n_layers;        /* 30 */
+  int32_t n_slots;         /* U: concurrent utterances, 1..64 (2 U rows = one 128-row GEMM tile) */
+  int32_t max_pos;         /* KV capacity of ONE slot in positions */
+  int32_t kv_fp32;         /* 0: bf16 slab, 1: fp32 slab (parity mode) */
+  int32_t max_new_cap;     /* token capacity of a slot (max max_new_tokens of a request) */
+  int32_t keep_logits;     /* 1: keep raw per-step logits [slot][max_new_cap][2][8194] (tests; 67 KB per token) */
+  int32_t speech_pos_rows; /* rows of speech_pos_emb, 0 = unchecked */
+} CbxT3BatchConfig;
+
+/* Needs CbxT3Weights.wplain (the plain matrices); wstream is not used by this engine. */
+int cbx_t3_batch_create(const CbxT3BatchConfig* cfg, const CbxT3Weights* w, cbx_t3b** out);
+int cbx_t3_batch_destroy(cbx_t3b* h);
+/* Admit a request into `slot`: prompt prefill of embeds [2][P][1024] (CFG pair; duplicate the row for cfg_weight 0)
+ * into the slot's KV slab, pending logits, per-slot knobs.  forced_tokens: nullable DEVICE array [max_new_tokens]
+ * (teacher forcing).  The slot then takes part in every following cbx_t3_decode_batch until EOS / max_new_tokens. */
+int cbx_t3_batch_prefill(cbx_t3b* h, int slot, const float* embeds, int P, const CbxSampleParams* sp, int max_new_tokens,
+                         const int32_t* forced_tokens, void* stream);
+/* n_steps decode steps (t3.py:319-367, one token per running slot and step), each ONE CUDA-graph launch.  slots:
+ * HOST array of the slots to advance, NULL = every running slot.  Finished / free slots ride along as inert rows. */
+int cbx_t3_decode_batch(cbx_t3b* h, const int32_t* slots, int n_slots, int n_steps, void* stream);
+/* Synchronises `stream` and reports per slot (HOST arrays [n_slots], each nullable): tokens emitted, done flag
+ * (1 finished, 0 running, -1 free), cache length. */
+int cbx_t3_batch_poll(cbx_t3b* h, int32_t* n_gen, int32_t* done, int32_t* pos, void* stream);
+/* Copies the first n tokens of `slot` into a DEVICE buffer (stream-ordered). */
+int cbx_t3_batch_tokens(cbx_t3b* h, int slot, int32_t* tokens_out, int n, void* stream);
+/* keep_logits engines: device pointer to the slot's raw logits [max_new_cap][2][8194]. */
+int cbx_t3_batch_logits(cbx_t3b* h, int slot, const float** logits);
+/* Frees the slot for the next request. */
+int cbx_t3_batch_release(cbx_t3b* h, int slot, void* stream);
+int cbx_t3_batch_info(cbx_t3b* h, int32_t* kv_splits, int64_t* launches, int64_t* launches_per_step);
+
+/* ------------------------------------------------------------------------------------------
  * (2) S3Gen conditional flow matching: the Euler/CFG solve around the ConditionalDecoder estimator.
  * Replaces CausalConditionalCFM.forward / ConditionalCFM.solve_euler
  * (src/chatterbox/models/s3gen/flow_matching.py:194-218, 72-123) and ConditionalDecoder.forward
