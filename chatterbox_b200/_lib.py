@@ -67,7 +67,7 @@ SYMBOLS = {
     "cbx_t3_batch_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                     C.c_void_p]),
     "cbx_t3_batch_tokens": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
-    "cbx_t3_batch_logits": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "cbx_t3_batch_logits": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "cbx_t3_batch_release": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "cbx_t3_batch_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "cbx_cfm_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxCfmWeights), C.POINTER(C.c_void_p)]),

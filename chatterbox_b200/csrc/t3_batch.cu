@@ -735,11 +735,13 @@ extern "C" int cbx_t3_batch_tokens(cbx_t3b* h, int slot, int32_t* tokens_out, in
   return CBX_OK;
 }
 
-extern "C" int cbx_t3_batch_logits(cbx_t3b* h, int slot, const float** logits) {
-  CBX_CHECK(h && logits, "cbx_t3_batch_logits: null argument");
+extern "C" int cbx_t3_batch_logits(cbx_t3b* h, int slot, float* logits_out, int n, void* stream) {
+  CBX_CHECK(h && logits_out, "cbx_t3_batch_logits: null argument");
   CBX_CHECK(h->logits_out, "cbx_t3_batch_logits: the engine was created without keep_logits");
-  CBX_CHECK(slot >= 0 && slot < h->U, "cbx_t3_batch_logits: slot %d out of range", slot);
-  *logits = h->logits_out + (size_t)slot * h->cfg.max_new_cap * 2 * VOCAB;
+  CBX_CHECK(slot >= 0 && slot < h->U && n >= 0 && n <= h->cfg.max_new_cap, "cbx_t3_batch_logits: slot %d / count %d out of range", slot, n);
+  CBX_ON_DEVICE(h->cfg.device);
+  CBX_CUDA(cudaMemcpyAsync(logits_out, h->logits_out + (size_t)slot * h->cfg.max_new_cap * 2 * VOCAB, (size_t)n * 2 * VOCAB * 4,
+                           cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
   return CBX_OK;
 }
 

@@ -134,8 +134,8 @@ int cbx_t3_decode_batch(cbx_t3b* h, const int32_t* slots, int n_slots, int n_ste
 int cbx_t3_batch_poll(cbx_t3b* h, int32_t* n_gen, int32_t* done, int32_t* pos, void* stream);
 /* Copies the first n tokens of `slot` into a DEVICE buffer (stream-ordered). */
 int cbx_t3_batch_tokens(cbx_t3b* h, int slot, int32_t* tokens_out, int n, void* stream);
-/* keep_logits engines: device pointer to the slot's raw logits [max_new_cap][2][8194]. */
-int cbx_t3_batch_logits(cbx_t3b* h, int slot, const float** logits);
+/* keep_logits engines: copies the raw logits of the slot's first n steps, [n][2][8194] fp32, into a DEVICE buffer. */
+int cbx_t3_batch_logits(cbx_t3b* h, int slot, float* logits_out, int n, void* stream);
 /* Frees the slot for the next request. */
 int cbx_t3_batch_release(cbx_t3b* h, int slot, void* stream);
 int cbx_t3_batch_info(cbx_t3b* h, int32_t* kv_splits, int64_t* launches, int64_t* launches_per_step);
