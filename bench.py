@@ -394,6 +394,123 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         dist.destroy_process_group()
 
 
+# -------------------------------------------------------------------------------------------------
+# --workload config4: BASELINE configs[3], 64 concurrent utterances per GPU (batched T3 decode), data-parallel ranks
+# -------------------------------------------------------------------------------------------------
+def run_config4(args, rank: int, world: int, local_rank: int):
+    """A step = one batch of U utterances (independent seeds, same shapes as config 2) per GPU: U prompt prefills into
+    the slots of the batched engine, 256 decode steps shared by all slots (one CUDA graph per step), then S3Gen
+    (front-end + 10-step CFM + HiFT) per utterance.  Reported: whole-job speech tokens/s through the pipeline (value),
+    the batched-decode tokens/s per GPU, utterances/s, and the HBM roofline of the decode stage
+    (1.02 GB of weights + sum over slots of 245 760 B x (context + 1) per step)."""
+    import torch.distributed as dist
+    from chatterbox_b200 import dispatch as D
+    from chatterbox_b200 import synthetic as S
+    from chatterbox_b200.s3gen import S3Gen
+    from chatterbox_b200.t3 import T3, T3Cond
+    from chatterbox_b200.t3_batch import T3Batch, T3Request
+
+    U = args.slots
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        D.barrier(world)
+        torch.cuda.synchronize()
+
+    max_pos = 34 + N_TEXT + 2 + 2 + N_SPEECH + 8
+    t3 = T3(S.make_state_dict("t3"), dev, max_pos=max_pos)
+    eng = T3Batch(t3, U, max_pos=max_pos, max_new_cap=N_SPEECH)
+    s3 = S3Gen(S.make_state_dict("flow"), S.make_state_dict("hift"), dev, rand_noise=S.cfm_noise(),
+               max_mel_len=2 * (PROMPT_LEN + N_SPEECH))
+    reqs, refs = [], []
+    for k in range(U):
+        sd = 100 + k + 1000 * rank                     # SURVEY 8d: independent seeds 100 + k
+        cond = T3Cond(**S.t3_cond(seed=sd, prompt_len=PROMPT_LEN)).to(device=dev)
+        text2 = torch.cat([S.text_tokens(N_TEXT, seed=sd)] * 2, 0).to(dev)
+        reqs.append(T3Request(t3_cond=cond, text_tokens=text2, max_new_tokens=N_SPEECH, do_sample=False, stop_on_eos=False,
+                              seed=sd, **SAMPLE))
+        refs.append({k2: (v.to(dev) if torch.is_tensor(v) else v) for k2, v in S.s3gen_ref(seed=sd, prompt_len=PROMPT_LEN).items()})
+    ev = {k: torch.cuda.Event(enable_timing=True) for k in ("p0", "d0", "d1", "s1")}
+
+    def step():
+        ev["p0"].record()
+        for k in range(U):
+            eng.admit(k, reqs[k])
+        ev["d0"].record()
+        eng.step(N_SPEECH)
+        ev["d1"].record()
+        toks = [eng.tokens(k, N_SPEECH) for k in range(U)]
+        wavs = []
+        for k in range(U):
+            t = toks[k][0]
+            wav, _ = s3.inference(speech_tokens=t[t < 6561], ref_dict=refs[k], seed=7)
+            wavs.append(wav)
+        ev["s1"].record()
+        for k in range(U):
+            eng.release(k)
+        return toks, wavs
+
+    for _ in range(3):
+        toks, wavs = step()
+    assert all(int(t.shape[1]) == N_SPEECH for t in toks) and all(w.shape[1] == 480 * 2 * N_SPEECH for w in wavs)
+    l0 = t3.state()["launches"] + eng.info()["launches"] + s3.launches()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    torch.cuda.profiler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    st = {"prefill": [], "decode": [], "s3gen": []}
+    e0.record()
+    for _ in range(args.steps):
+        step()
+        torch.cuda.synchronize()
+        st["prefill"].append(ev["p0"].elapsed_time(ev["d0"]))
+        st["decode"].append(ev["d0"].elapsed_time(ev["d1"]))
+        st["s3gen"].append(ev["d1"].elapsed_time(ev["s1"]))
+    e1.record()
+    barrier()
+    torch.cuda.profiler.stop()
+    clocks = sampler.stop()
+    total_ms = e0.elapsed_time(e1)
+    launches = t3.state()["launches"] + eng.info()["launches"] + s3.launches() - l0
+    (total_ms,) = D.max_over_ranks([total_ms], dev, world)
+    if rank == 0:
+        peak, peak_src = _peaks()
+        P = eng.prefill_len[0]
+        wbytes = t3.packed.weight_bytes_per_step()
+        # per decode step i (0-based): weights once + every slot's KV read (P + i positions) and write (1 position);
+        # the last step's forward is skipped by the engine (its logits would never be read)
+        dbytes = sum(wbytes + U * KV_BYTES_PER_POS * (P + i + 1) for i in range(N_SPEECH - 1))
+        d_ms = statistics.mean(st["decode"])
+        achieved = dbytes / (d_ms * 1e-3) / 1e9
+        step_ms = total_ms / args.steps
+        line = {"metric": METRIC, "value": D.whole_job_rate(U * N_SPEECH * args.steps, world, total_ms), "unit": UNIT,
+                "n_gpus": world, "steps": args.steps, "warmup": 3, "ms_per_step": step_ms, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": f"configs[3]: {U} concurrent utterances per GPU, data-parallel ranks; each utterance as configs[1] "
+                                       "(64+2 text tokens, 150 cond tokens, cfg 0.5, greedy, 256 speech tokens, CFM 10 steps at L=812, "
+                                       "HiFT 512 frames), independent seeds; batched T3 decode (one CUDA graph per step), S3Gen per utterance",
+                           "utterances_per_step_per_gpu": U, "speech_tokens": N_SPEECH,
+                           "l2": "inputs larger than L2 (1.02 GB of weights + the slots' KV slabs streamed per decode step)"},
+                "gpu_launches": int(launches), "clocks": clocks,
+                "roofline": {"kernel": "batched decode stage (per step: graph of tcgen05 GEMMs + k_b_attn + k_b_sample)",
+                             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dbytes,
+                             "launch_ms": d_ms, "share_of_step": d_ms / step_ms},
+                "stages_ms": {k: statistics.mean(v) for k, v in st.items()},
+                "t3_decode_tokens_per_s_per_gpu": U * N_SPEECH / (d_ms * 1e-3),
+                "t3_tokens_per_s_per_gpu_incl_prefill": U * N_SPEECH / ((d_ms + statistics.mean(st["prefill"])) * 1e-3),
+                "ms_per_decode_step": d_ms / N_SPEECH,
+                "utterances_per_s": U * args.steps * world / (total_ms * 1e-3),
+                "rtf": (step_ms * 1e-3) / (U * AUDIO_S), "kv_splits": eng.info()["kv_splits"]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -401,6 +518,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="config2", choices=["config2", "config4"],
+                    help="config2 (default, the headline): one utterance per GPU; config4: --slots concurrent utterances per GPU")
+    ap.add_argument("--slots", type=int, default=64, help="config4: concurrent utterances per GPU (1..64)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -410,6 +530,9 @@ def main():
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this build has no CPU path (use --impl reference for the CPU arm)")
+    if args.workload == "config4":
+        run_config4(args, rank, world, local_rank)
+        return
     run_ours(args, rank, world, local_rank)
 
 
