@@ -14,6 +14,10 @@ static __global__ void __launch_bounds__(256) k_rms_hilo(const float* __restrict
                                                   __nv_bfloat16* __restrict__ out, long long plane) {
   __shared__ float red[8];
   const int row = blockIdx.x, t = threadIdx.x;
+  // programmatic dependent launch (the batched engine launches this kernel with the attribute): let the next kernel's
+  // prologue start, and wait for the producer of x before the first read.  Both are no-ops in a plain launch.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const float4 v = *reinterpret_cast<const float4*>(x + (size_t)row * H + t * 4);
   float s = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
   s = warp_sum(s);
