@@ -87,6 +87,9 @@ SYMBOLS = {
     "cbx_hift_inference": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
     "cbx_hift_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "cbx_hift_source_static_max_frames": (C.c_int, []),
+    "cbx_hift_source_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                         C.c_uint64, C.c_void_p, C.c_void_p]),
     "cbx_t3_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                C.POINTER(C.c_int64)]),
 }

@@ -436,3 +436,48 @@ extern "C" int cbx_hift_launches(cbx_hift* h, int64_t* launches) {
   *launches = h->launches;
   return CBX_OK;
 }
+
+// =================================================================================================
+// Allocation-free variant of cbx_hift_source (include/cbx.h, section 3b).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  Same two kernels as hift_source above; what differs is where the scratch
+// lives: the double-precision phase prefix (one entry per mel frame) sits in a file-scope device array instead of the
+// handle's cudaMalloc'ed slab, and the two SourceModuleHnNSF linear weights come from the caller, so no handle is
+// needed either.  Every GPU that loads the library holds the array (32 KB) until exit.
+//   * The array is shared by every call on a device and keeps the last call's contents.  Nothing has to start at
+//     zero: k_f0_prefix rewrites entries [0, L) before k_source reads them, on the same stream.
+//   * Calls that overlap on the GPU (different streams, or host threads on different streams) RACE on the array:
+//     serialise them on one stream.
+// In host code the array's name is a host-side stand-in, not a device address: its address is taken once per device
+// with cudaGetSymbolAddress (that device current) and that pointer is what the kernels receive.
+// =================================================================================================
+#define CBX_HIFT_SOURCE_STATIC_MAX_FRAMES 4096      // 4096 mel frames = 81.92 s of audio at 24 kHz
+static __device__ __align__(256) double g_source_prefix_scratch[CBX_HIFT_SOURCE_STATIC_MAX_FRAMES];
+
+extern "C" int cbx_hift_source_static_max_frames(void) { return CBX_HIFT_SOURCE_STATIC_MAX_FRAMES; }
+
+extern "C" int cbx_hift_source_static(int device, const float* lin_w, const float* lin_b, const float* f0, int L,
+                                      const float* phase, const float* noise, uint64_t seed, float* s_out, void* stream) {
+  CBX_CHECK(lin_w && lin_b && f0 && s_out, "cbx_hift_source_static: null argument");
+  CBX_CHECK(L >= 1, "cbx_hift_source_static: L must be >= 1 (got %d)", L);
+  CBX_CHECK(L <= CBX_HIFT_SOURCE_STATIC_MAX_FRAMES,
+            "cbx_hift_source_static: L=%d exceeds the static scratch (%d mel frames); use cbx_hift_source with a handle sized for it",
+            L, CBX_HIFT_SOURCE_STATIC_MAX_FRAMES);
+  CBX_CHECK(device >= 0 && device < 64, "cbx_hift_source_static: device ordinal %d out of range", device);
+  CBX_ON_DEVICE(device);
+  static double* scratch_of_device[64] = {};          // device address of the array, per device (set up once each)
+  if (!scratch_of_device[device]) {
+    double* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_source_prefix_scratch);
+    CBX_CHECK(e == cudaSuccess && ptr, "cbx_hift_source_static: cudaGetSymbolAddress failed on device %d (%s)", device,
+              cudaGetErrorString(e));
+    scratch_of_device[device] = ptr;
+  }
+  double* prefix = scratch_of_device[device];
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int T = UPS * L;
+  k_f0_prefix<<<1, 32, 0, st>>>(f0, prefix, L);
+  k_source<<<(T + 255) / 256, 256, 0, st>>>(f0, prefix, phase, noise, seed, lin_w, lin_b, s_out, T);
+  CBX_CUDA(cudaGetLastError());
+  return CBX_OK;
+}

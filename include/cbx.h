@@ -198,6 +198,20 @@ int cbx_hift_inference(cbx_hift* h, const float* mel, int L, const float* source
                        float* wav_out, float* source_out, void* stream);
 int cbx_hift_launches(cbx_hift* h, int64_t* launches);
 
+/* ------------------------------------------------------------------------------------------
+ * (3b) Allocation-free harmonic source.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arithmetic and kernels as cbx_hift_source (SineGen + SourceModuleHnNSF, hifigan.py:200-283), but handle-free
+ * and without any allocation: the double-precision phase-prefix scratch is a file-scope static __device__ array of
+ * cbx_hift_source_static_max_frames() = 4096 entries (32 KB per GPU, held until exit); larger L is rejected with an
+ * error.  The array is shared by all calls on a device: calls that overlap on the GPU race — serialise them on one
+ * stream.  lin_w [9] / lin_b [1]: m_source.l_linear.weight / .bias (device, fp32); f0 [L]; phase [9] / noise [9][480 L]
+ * nullable (then drawn from Philox(seed)); s_out [480 L].
+ * ------------------------------------------------------------------------------------------ */
+int cbx_hift_source_static_max_frames(void);
+int cbx_hift_source_static(int device, const float* lin_w, const float* lin_b, const float* f0, int L, const float* phase,
+                           const float* noise, uint64_t seed, float* s_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
