@@ -424,7 +424,7 @@ def run_config4(args, rank: int, world: int, local_rank: int):
     t3 = T3(S.make_state_dict("t3"), dev, max_pos=max_pos)
     eng = T3Batch(t3, U, max_pos=max_pos, max_new_cap=N_SPEECH)
     s3 = S3Gen(S.make_state_dict("flow"), S.make_state_dict("hift"), dev, rand_noise=S.cfm_noise(),
-               max_mel_len=2 * (PROMPT_LEN + N_SPEECH))
+               max_mel_len=2 * (PROMPT_LEN + N_SPEECH), max_batch=args.s3_batch)
     reqs, refs = [], []
     for k in range(U):
         sd = 100 + k + 1000 * rank                     # independent seeds 100 + k
@@ -444,10 +444,10 @@ def run_config4(args, rank: int, world: int, local_rank: int):
         ev["d1"].record()
         toks = [eng.tokens(k, N_SPEECH) for k in range(U)]
         wavs = []
-        for k in range(U):
-            t = toks[k][0]
-            wav, _ = s3.inference(speech_tokens=t[t < 6561], ref_dict=refs[k], seed=7)
-            wavs.append(wav)
+        for k0 in range(0, U, args.s3_batch):          # the flow-matching stage of s3_batch utterances as one solve
+            ks = range(k0, min(U, k0 + args.s3_batch))
+            outs = s3.inference_batch([toks[k][0][toks[k][0] < 6561] for k in ks], [refs[k] for k in ks], seed=7)
+            wavs += [w for w, _ in outs]
         ev["s1"].record()
         for k in range(U):
             eng.release(k)
@@ -505,7 +505,7 @@ def run_config4(args, rank: int, world: int, local_rank: int):
                 "t3_tokens_per_s_per_gpu_incl_prefill": U * N_SPEECH / ((d_ms + statistics.mean(st["prefill"])) * 1e-3),
                 "ms_per_decode_step": d_ms / N_SPEECH,
                 "utterances_per_s": U * args.steps * world / (total_ms * 1e-3),
-                "rtf": (step_ms * 1e-3) / (U * AUDIO_S), "kv_splits": eng.info()["kv_splits"]}
+                "rtf": (step_ms * 1e-3) / (U * AUDIO_S), "kv_splits": eng.info()["kv_splits"], "s3_batch": args.s3_batch}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -521,6 +521,7 @@ def main():
     ap.add_argument("--workload", default="config2", choices=["config2", "config4"],
                     help="config2 (default, the headline): one utterance per GPU; config4: --slots concurrent utterances per GPU")
     ap.add_argument("--slots", type=int, default=64, help="config4: concurrent utterances per GPU (1..64)")
+    ap.add_argument("--s3-batch", type=int, default=16, help="config4: utterances per batched flow-matching solve")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

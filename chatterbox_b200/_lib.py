@@ -76,6 +76,10 @@ SYMBOLS = {
                                     C.c_void_p, C.c_void_p]),
     "cbx_cfm_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                 C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_void_p, C.c_void_p]),
+    "cbx_cfm_create_batched": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(CbxCfmWeights), C.POINTER(C.c_void_p)]),
+    "cbx_cfm_solve_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int32),
+                                      C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_void_p,
+                                      C.c_void_p]),
     "cbx_cfm_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "cbx_cfm_cache_sizes": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "cbx_hift_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxHiftWeights), C.POINTER(C.c_void_p)]),

@@ -105,7 +105,8 @@ def _check_mask(mask) -> None:
 class ConditionalDecoder:
     """The estimator (decoder.py:100-317).  forward(x, mask, mu, t, spks, cond) with batch 2."""
 
-    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", *, prefix: str = "", max_len: int = 4096):
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda", *, prefix: str = "", max_len: int = 4096,
+                 max_batch: int = 1):
         if not torch.cuda.is_available():
             raise _lib.CbxError("chatterbox_b200.cfm needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device)
@@ -117,9 +118,10 @@ class ConditionalDecoder:
         self._fo = (C.c_int64 * len(fo))(*fo)
         w = _lib.CbxCfmWeights(self.bf.data_ptr(), self.f32.data_ptr(), self._bfo, self._fo)
         h = C.c_void_p()
-        _lib.check(self._lib.cbx_cfm_create(self.device.index, int(max_len), C.byref(w), C.byref(h)))
+        _lib.check(self._lib.cbx_cfm_create_batched(self.device.index, int(max_len), int(max_batch), C.byref(w), C.byref(h)))
         self._h = h
         self.max_len = max_len
+        self.max_batch = max_batch
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -190,3 +192,29 @@ class CausalConditionalCFM:
         return out, None
 
     __call__ = forward
+
+    @torch.inference_mode()
+    def forward_batch(self, mu, lens, n_timesteps, temperature=1.0, spks=None, cond=None):
+        """The same solve for nb utterances at once (BASELINE config 4): mu, cond (nb, 80, L) padded to the longest
+        utterance, spks (nb, 80), lens = true mel lengths (list of ints, or None when all are L).  This is the reference's
+        padded-batch call `forward(mu, mask=~make_pad_mask(lens), ...)` (flow_matching.py:194-218, utils/mask.py:167-193):
+        every utterance starts from the same `rand_noise[:, :, :L]`.  Frames past lens[u] of the result are unspecified
+        (the reference zeroes them): slice them off."""
+        nb, _, L = mu.shape
+        e = self.estimator
+        assert mu.shape[1] == 80 and nb <= e.max_batch, (mu.shape, e.max_batch)
+        f = lambda a: a.to(self.device, torch.float32).contiguous()
+        z = (self.rand_noise[:, :, :L] * temperature).expand(nb, -1, -1).contiguous()
+        mu, spks, cond = f(mu), f(spks), f(cond)
+        if n_timesteps not in self._sched:
+            ts, dts = euler_schedule(n_timesteps)
+            self._sched[n_timesteps] = ((C.c_float * n_timesteps)(*ts), (C.c_float * n_timesteps)(*dts))
+        ts, dts = self._sched[n_timesteps]
+        larr = None
+        if lens is not None and any(int(x) != L for x in lens):
+            larr = (C.c_int32 * nb)(*[int(x) for x in lens])
+        out = torch.empty(nb, 80, L, dtype=torch.float32, device=self.device)
+        _lib.check(e._lib.cbx_cfm_solve_batch(e._h, nb, z.data_ptr(), mu.data_ptr(), spks.data_ptr(), cond.data_ptr(), larr, L,
+                                              int(n_timesteps), ts, dts, float(self.inference_cfg_rate), out.data_ptr(),
+                                              e._stream()))
+        return out

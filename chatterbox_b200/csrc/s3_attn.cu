@@ -33,7 +33,7 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
 
 // qkv: bf16 [B][L][ld_qkv] with q at column 0, k at 512, v at 1024 (+ head*64); out: bf16 [B][L][512]
 __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
-                                                      int L, int ld_qkv) {
+                                                      int L, int ld_qkv, const int* __restrict__ lens) {
   extern __shared__ __align__(16) __nv_bfloat16 at_smem[];
   __nv_bfloat16* sQ = at_smem;
   __nv_bfloat16* sKb = at_smem + AT_TILE;                 // [NST][tile]
@@ -50,9 +50,12 @@ __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16
       cp_async16(dst + r * AT_LD + c8 * 8, base + (size_t)(ok ? row0 + r : 0) * ld_qkv + col_off + c8 * 8, ok);
     }
   };
-  const int ntiles = (L + AT_BN - 1) / AT_BN;
   pdl_launch_dependents();
   pdl_wait();                 // q|k|v come from the GEMM just before
+  // key-padding mask of a padded batch (decoder.py:25-33, utils/mask.py:167-193): row b attends to its first Lk keys only;
+  // key tiles past Lk are not even loaded.  lens == NULL: every row is L long (one un-padded utterance).
+  const int Lk = lens ? min(max(lens[b], 1), L) : L;
+  const int ntiles = (Lk + AT_BN - 1) / AT_BN;
   load_tile(sQ, 0, q0);
   const int nrounds = (ntiles + AT_G - 1) / AT_G;        // a round = AT_G consecutive key tiles, one per warp group
 #pragma unroll
@@ -113,7 +116,7 @@ __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const int key = kbase + i * 8 + (e & 1);
-        const float v = (key < L) ? s[i][e] * sc : -INFINITY;
+        const float v = (key < Lk) ? s[i][e] * sc : -INFINITY;
         s[i][e] = v;
         mx[e >> 1] = fmaxf(mx[e >> 1], v);
       }
@@ -204,7 +207,7 @@ __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16
 
 }  // namespace
 
-int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, cudaStream_t st) {
+int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st) {
   dim3 grid((L + AT_BM - 1) / AT_BM, 8, B);
   static CbxPerDeviceOnce once;
   if (once.first())
@@ -215,7 +218,7 @@ int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, i
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_attn_kernel, qkv, out, L, ld_qkv));
+  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_attn_kernel, qkv, out, L, ld_qkv, lens));
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;
 }

@@ -10,7 +10,7 @@
 #include <vector>
 
 namespace cbx {
-int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, cudaStream_t st);
+int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st);
 }
 using namespace cbx;
 
@@ -104,25 +104,56 @@ __global__ void k_euler(const float* __restrict__ est, float* __restrict__ x, __
 
 constexpr int CFM_MAX_GRAPHS = 8;      // cached executable solve graphs (LRU)
 constexpr int CFM_MAX_PLANS = 64;      // cached per-length op plans (331 tensor maps each, host memory)
+// ---- batched solve (nb utterances, rows 2u = conditional / 2u + 1 = unconditional of utterance u, all padded to L) ----
+// z, mu, cond [nb][80][L], spks [nb][80]  ->  x [nb][L][80] fp32 state, xin [2 nb][L][320] bf16 (flow_matching.py:95-108)
+__global__ void k_pack_b(const float* __restrict__ z, const float* __restrict__ mu, const float* __restrict__ spks,
+                         const float* __restrict__ cond, float* __restrict__ x, __nv_bfloat16* __restrict__ xin, int L) {
+  const int t = blockIdx.x, u = blockIdx.y, c = threadIdx.x;   // 320 threads
+  const int part = c / NMEL, ch = c % NMEL;
+  const size_t o = ((size_t)u * NMEL + ch) * L + t;
+  float v;
+  if (part == 0) v = z[o];
+  else if (part == 1) v = mu[o];
+  else if (part == 2) v = spks[(size_t)u * NMEL + ch];
+  else v = cond[o];
+  if (part == 0) x[((size_t)u * L + t) * NMEL + ch] = v;
+  xin[((size_t)(2 * u) * L + t) * CIN + c] = __float2bfloat16_rn(v);
+  xin[((size_t)(2 * u + 1) * L + t) * CIN + c] = __float2bfloat16_rn(part == 0 ? v : 0.f);
+}
+__global__ void k_euler_b(const float* __restrict__ est, float* __restrict__ x, __nv_bfloat16* __restrict__ xin,
+                          float* __restrict__ mel_out, float dt, float rate, int L, int last) {
+  const int t = blockIdx.x, u = blockIdx.y, ch = threadIdx.x;   // 80 threads
+  const float vc = est[((size_t)(2 * u) * L + t) * NMEL + ch], vu = est[((size_t)(2 * u + 1) * L + t) * NMEL + ch];
+  const float v = (1.0f + rate) * vc - rate * vu;
+  const size_t xo = ((size_t)u * L + t) * NMEL + ch;
+  const float xn = x[xo] + dt * v;
+  x[xo] = xn;
+  const __nv_bfloat16 xb = __float2bfloat16_rn(xn);
+  xin[((size_t)(2 * u) * L + t) * CIN + ch] = xb;
+  xin[((size_t)(2 * u + 1) * L + t) * CIN + ch] = xb;
+  if (last) mel_out[((size_t)u * NMEL + ch) * L + t] = xn;
+}
+
 struct Op { int kind; GemmDesc g; int temb_res; };   // kind 0 gemm, 1 attention, 2 skip copy
-struct Plan { int L; std::vector<Op> ops; };
+struct Plan { int L, nb; std::vector<Op> ops; };
 
 }  // namespace
 
 struct cbx_cfm {
-  int device, max_len;
+  int device, max_len, max_batch;
+  int* lens_dev;         // [2 max_batch] key length of every batch row (padded batches)
   const __nv_bfloat16* wbf; const float* wf;
   std::vector<long long> bo, fo;
   void* slab;
   __nv_bfloat16 *xin, *cur_a, *cur_b, *cat, *ln, *qkv, *att, *ff, *h1;
   float *res, *h2, *est, *x, *mish_temb, *tvec, *tvals;
   int max_steps;
-  std::map<int, Plan> plans;
+  std::map<long long, Plan> plans;      // key = L * 256 + nb
   long long launches;
   // a solve seen twice with the same (L, schedule, cfg rate) is captured into a CUDA graph: ~3 400 launches become
   // one graph launch (the inter-kernel gaps were a fifth of the solve).  Caller buffers are staged so the graph's
   // baked pointers stay valid.
-  struct SolveGraph { int L, n, seen; float cfg; std::vector<float> t, dt; cudaGraphExec_t exec; long long launches; };
+  struct SolveGraph { int L, nb, n, seen; float cfg; std::vector<float> t, dt; cudaGraphExec_t exec; long long launches; };
   std::vector<SolveGraph> graphs;
   float *st_z, *st_mu, *st_spks, *st_cond, *st_out;
   cudaStream_t cap_stream;
@@ -132,14 +163,15 @@ static const __nv_bfloat16* BFW(cbx_cfm* h, int i) { return h->wbf + h->bo[i]; }
 static const float* FW(cbx_cfm* h, int i) { return h->wf + h->fo[i]; }
 
 // ---- the fixed op sequence of one estimator call for mel length L ----
-static int build_plan(cbx_cfm* h, int L, Plan** out) {
-  auto it = h->plans.find(L);
+static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
+  const long long key = (long long)L * 256 + nb;
+  auto it = h->plans.find(key);
   if (it != h->plans.end()) { *out = &it->second; return CBX_OK; }
-  Plan pl; pl.L = L;
+  Plan pl; pl.L = L; pl.nb = nb;
   int rc = CBX_OK;
   auto G = [&](const __nv_bfloat16* A, int lda, int wi, int N, int K, int taps, const GemmEpi& e, int temb_res) {
     Op op; op.kind = 0; op.temb_res = temb_res;
-    if (gemm_make(&op.g, A, lda, BFW(h, wi), 2, L, N, K, taps, e)) rc = CBX_ERR;
+    if (gemm_make(&op.g, A, lda, BFW(h, wi), 2 * nb, L, N, K, taps, e)) rc = CBX_ERR;
     pl.ops.push_back(op);
   };
   auto resnet = [&](int r, const __nv_bfloat16* X, int ldx, int cin, int first_tfm) {
@@ -189,24 +221,24 @@ static int build_plan(cbx_cfm* h, int L, Plan** out) {
   { GemmEpi e{}; e.bias = FW(h, F_TAIL + 5); e.out_f32 = h->est; e.ld_f32 = NMEL; G(h->h1, C, BF_TAIL + 3, NMEL, C, 1, e, -1); }
   if (rc) return CBX_ERR;
   if ((int)h->plans.size() >= CFM_MAX_PLANS) h->plans.erase(h->plans.begin());   // plans are rebuilt on demand (host work only)
-  auto ins = h->plans.emplace(L, std::move(pl));
+  auto ins = h->plans.emplace(key, std::move(pl));
   *out = &ins.first->second;
   return CBX_OK;
 }
 
-static int run_estimator(cbx_cfm* h, Plan* pl, int step, cudaStream_t st) {
-  const int L = pl->L;
+static int run_estimator(cbx_cfm* h, Plan* pl, int step, const int* lens, cudaStream_t st) {
+  const int L = pl->L, B = 2 * pl->nb;
   for (Op& op : pl->ops) {
     if (op.kind == 0) {
       if (op.temb_res >= 0) {
         GemmDesc d = op.g;
-        d.epi.temb = h->tvec + ((size_t)(step * NRES + op.temb_res) * 2) * C;
+        d.epi.temb = h->tvec + ((size_t)(step * NRES + op.temb_res) * 2) * C;      // [2][C] copies; the GEMM reads the first
         if (gemm_launch(d, st)) return CBX_ERR;
       } else if (gemm_launch(op.g, st)) return CBX_ERR;
     } else if (op.kind == 1) {
-      if (s3_attn_launch(h->qkv, h->att, 2, L, 1536, st)) return CBX_ERR;
+      if (s3_attn_launch(h->qkv, h->att, B, L, 1536, lens, st)) return CBX_ERR;
     } else {
-      CBX_CUDA(cudaMemcpy2DAsync(h->cat + C, 2 * C * 2, h->cur_a, C * 2, C * 2, (size_t)2 * L, cudaMemcpyDeviceToDevice, st));
+      CBX_CUDA(cudaMemcpy2DAsync(h->cat + C, 2 * C * 2, h->cur_a, C * 2, C * 2, (size_t)B * L, cudaMemcpyDeviceToDevice, st));
     }
     h->launches += 1;
   }
@@ -226,28 +258,33 @@ static int time_vectors(cbx_cfm* h, const float* t_host, int n, cudaStream_t st)
 // =================================================================================================
 // C-ABI (include/cbx.h)
 // =================================================================================================
+extern "C" int cbx_cfm_create_batched(int device, int max_len, int max_batch, const CbxCfmWeights* w, cbx_cfm** out);
 extern "C" int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, cbx_cfm** out) {
+  return cbx_cfm_create_batched(device, max_len, 1, w, out);
+}
+extern "C" int cbx_cfm_create_batched(int device, int max_len, int max_batch, const CbxCfmWeights* w, cbx_cfm** out) {
   CBX_CHECK(w && out && w->bf16_blob && w->f32_blob && w->bf16_off && w->f32_off, "cbx_cfm_create: null argument");
   CBX_CHECK(max_len >= 1, "cbx_cfm_create: max_len must be positive");
+  CBX_CHECK(max_batch >= 1 && max_batch <= 128, "cbx_cfm_create: max_batch %d out of range (1..128)", max_batch);
   CBX_ON_DEVICE(device);
   cudaDeviceProp prop;
   CBX_CUDA(cudaGetDeviceProperties(&prop, device));
   CBX_CHECK(prop.major == 10, "cbx_cfm_create: built for sm_100a only, device is sm_%d%d", prop.major, prop.minor);
   cbx_cfm* h = new cbx_cfm();
-  h->device = device; h->max_len = max_len; h->launches = 0; h->max_steps = 64;
+  h->device = device; h->max_len = max_len; h->max_batch = max_batch; h->launches = 0; h->max_steps = 64;
   h->wbf = static_cast<const __nv_bfloat16*>(w->bf16_blob); h->wf = w->f32_blob;
   h->bo.assign(w->bf16_off, w->bf16_off + BF_COUNT);
   h->fo.assign(w->f32_off, w->f32_off + F_COUNT);
-  const size_t R = (size_t)2 * max_len;
+  const size_t R = (size_t)2 * max_len * max_batch, U1 = (size_t)max_len * max_batch;     // batch rows x frames
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = (off + bytes + 1023) / 1024 * 1024; return o; };
   const size_t o_xin = take(R * CIN * 2), o_ca = take(R * C * 2), o_cb = take(R * C * 2), o_cat = take(R * 2 * C * 2);
   const size_t o_ln = take(R * C * 2), o_qkv = take(R * 1536 * 2), o_att = take(R * 512 * 2), o_ff = take(R * 1024 * 2);
   const size_t o_h1 = take(R * C * 2), o_res = take(R * C * 4), o_h2 = take(R * C * 4), o_est = take(R * NMEL * 4);
-  const size_t o_x = take((size_t)max_len * NMEL * 4), o_mt = take((size_t)h->max_steps * 1024 * 4);
+  const size_t o_x = take(U1 * NMEL * 4), o_mt = take((size_t)h->max_steps * 1024 * 4);
   const size_t o_tv = take((size_t)h->max_steps * NRES * 2 * C * 4), o_t = take(h->max_steps * 4);
-  const size_t o_sz = take((size_t)max_len * NMEL * 4), o_sm = take((size_t)max_len * NMEL * 4), o_ss = take(NMEL * 4);
-  const size_t o_sc = take((size_t)max_len * NMEL * 4), o_so = take((size_t)max_len * NMEL * 4);
+  const size_t o_sz = take(U1 * NMEL * 4), o_sm = take(U1 * NMEL * 4), o_ss = take((size_t)max_batch * NMEL * 4);
+  const size_t o_sc = take(U1 * NMEL * 4), o_so = take(U1 * NMEL * 4), o_len = take((size_t)2 * max_batch * 4);
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_cfm_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -261,7 +298,7 @@ extern "C" int cbx_cfm_create(int device, int max_len, const CbxCfmWeights* w, c
   h->res = (float*)(s + o_res); h->h2 = (float*)(s + o_h2); h->est = (float*)(s + o_est); h->x = (float*)(s + o_x);
   h->mish_temb = (float*)(s + o_mt); h->tvec = (float*)(s + o_tv); h->tvals = (float*)(s + o_t);
   h->st_z = (float*)(s + o_sz); h->st_mu = (float*)(s + o_sm); h->st_spks = (float*)(s + o_ss); h->st_cond = (float*)(s + o_sc);
-  h->st_out = (float*)(s + o_so);
+  h->st_out = (float*)(s + o_so); h->lens_dev = (int*)(s + o_len);
   h->cap_stream = nullptr;
   *out = h;
   return CBX_OK;
@@ -283,12 +320,12 @@ extern "C" int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, co
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CBX_ON_DEVICE(h->device);
   Plan* pl;
-  if (build_plan(h, L, &pl)) return CBX_ERR;
+  if (build_plan(h, L, 1, &pl)) return CBX_ERR;
   if (time_vectors(h, &t, 1, st)) return CBX_ERR;
   const size_t n = (size_t)NMEL * L;
   PackIn in{{x, x + n}, {mu, mu + n}, {spks, spks + NMEL}, {cond, cond + n}};
   k_pack<<<L, CIN, 0, st>>>(in, nullptr, h->xin, L);
-  if (run_estimator(h, pl, 0, st)) return CBX_ERR;
+  if (run_estimator(h, pl, 0, nullptr, st)) return CBX_ERR;
   k_unpack<<<L, NMEL, 0, st>>>(h->est, out, L);
   CBX_CUDA(cudaGetLastError());
   h->launches += 2;
@@ -297,37 +334,60 @@ extern "C" int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, co
 
 // the kernel sequence of one Euler solve on the handle's own buffers (stream-ordered; capturable)
 static int solve_body(cbx_cfm* h, Plan* pl, const float* z, const float* mu, const float* spks, const float* cond, int L,
-                      int n_steps, const float* dt_vals, float cfg_rate, float* mel_out, cudaStream_t st) {
+                      int n_steps, const float* dt_vals, float cfg_rate, float* mel_out, const int* lens, cudaStream_t st) {
+  const int nb = pl->nb;
   k_temb<<<n_steps, 1024, 0, st>>>(h->tvals, FW(h, F_TIME + 0), FW(h, F_TIME + 1), FW(h, F_TIME + 2), FW(h, F_TIME + 3), h->mish_temb);
   k_tvec<<<dim3(NRES, n_steps), 256, 0, st>>>(h->mish_temb, FW(h, F_TIME + 4), FW(h, F_TIME + 5), h->tvec);
-  PackIn in{{z, z}, {mu, nullptr}, {spks, nullptr}, {cond, nullptr}};
-  k_pack<<<L, CIN, 0, st>>>(in, h->x, h->xin, L);
+  k_pack_b<<<dim3(L, nb), CIN, 0, st>>>(z, mu, spks, cond, h->x, h->xin, L);
   h->launches += 3;
   for (int s = 0; s < n_steps; ++s) {
-    if (run_estimator(h, pl, s, st)) return CBX_ERR;
-    k_euler<<<L, NMEL, 0, st>>>(h->est, h->x, h->xin, mel_out, dt_vals[s], cfg_rate, L, s == n_steps - 1);
+    if (run_estimator(h, pl, s, lens, st)) return CBX_ERR;
+    k_euler_b<<<dim3(L, nb), NMEL, 0, st>>>(h->est, h->x, h->xin, mel_out, dt_vals[s], cfg_rate, L, s == n_steps - 1);
     h->launches += 1;
   }
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;
 }
 
+extern "C" int cbx_cfm_solve_batch(cbx_cfm* h, int nb, const float* z, const float* mu, const float* spks, const float* cond,
+                                   const int32_t* lens, int L, int n_steps, const float* t_vals, const float* dt_vals,
+                                   float cfg_rate, float* mel_out, void* stream);
+
 extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
                              int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out,
                              void* stream) {
+  return cbx_cfm_solve_batch(h, 1, z, mu, spks, cond, nullptr, L, n_steps, t_vals, dt_vals, cfg_rate, mel_out, stream);
+}
+
+extern "C" int cbx_cfm_solve_batch(cbx_cfm* h, int nb, const float* z, const float* mu, const float* spks, const float* cond,
+                                   const int32_t* lens, int L, int n_steps, const float* t_vals, const float* dt_vals,
+                                   float cfg_rate, float* mel_out, void* stream) {
   CBX_CHECK(h && z && mu && spks && cond && t_vals && dt_vals && mel_out, "cbx_cfm_solve: null argument");
+  CBX_CHECK(nb >= 1 && nb <= h->max_batch, "cbx_cfm_solve: batch %d exceeds max_batch %d", nb, h->max_batch);
   CBX_CHECK(L >= 1 && L <= h->max_len, "cbx_cfm_solve: L=%d exceeds max_len %d", L, h->max_len);
   CBX_CHECK(n_steps >= 1 && n_steps <= h->max_steps, "cfm: n_steps %d out of range (max %d)", n_steps, h->max_steps);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CBX_ON_DEVICE(h->device);
   Plan* pl;
-  if (build_plan(h, L, &pl)) return CBX_ERR;
+  if (build_plan(h, L, nb, &pl)) return CBX_ERR;
   CBX_CUDA(cudaMemcpyAsync(h->tvals, t_vals, n_steps * sizeof(float), cudaMemcpyHostToDevice, st));
+  // key lengths per batch row (rows 2u, 2u + 1 = utterance u); NULL = every utterance is L frames long
+  const int* lens_dev = nullptr;
+  if (lens) {
+    std::vector<int> rows(2 * nb);
+    for (int u = 0; u < nb; ++u) {
+      CBX_CHECK(lens[u] >= 1 && lens[u] <= L, "cbx_cfm_solve_batch: lens[%d] = %d outside [1, L = %d]", u, lens[u], L);
+      rows[2 * u] = rows[2 * u + 1] = lens[u];
+    }
+    CBX_CUDA(cudaMemcpyAsync(h->lens_dev, rows.data(), rows.size() * sizeof(int), cudaMemcpyHostToDevice, st));   // pageable: staged before return
+    lens_dev = h->lens_dev;
+  }
   static const bool use_graph = [] { const char* v = getenv("CBX_CFM_GRAPH"); return !(v && v[0] == '0'); }();
   cbx_cfm::SolveGraph* g = nullptr;
+  const int masked = lens ? 1 : 0;         // the graph bakes lens_dev (or NULL) into the attention launches
   if (use_graph) {
     for (auto& c : h->graphs)
-      if (c.L == L && c.n == n_steps && c.cfg == cfg_rate && c.t == std::vector<float>(t_vals, t_vals + n_steps) &&
+      if (c.L == L && c.nb == nb * 2 + masked && c.n == n_steps && c.cfg == cfg_rate && c.t == std::vector<float>(t_vals, t_vals + n_steps) &&
           c.dt == std::vector<float>(dt_vals, dt_vals + n_steps)) { g = &c; break; }
     if (!g) {
       // bounded: a long-lived server sees ~1 250 distinct mel lengths; the oldest entry (and its ~3 400-node
@@ -336,7 +396,7 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
         if (h->graphs.front().exec) cudaGraphExecDestroy(h->graphs.front().exec);
         h->graphs.erase(h->graphs.begin());
       }
-      h->graphs.push_back({L, n_steps, 0, cfg_rate, std::vector<float>(t_vals, t_vals + n_steps),
+      h->graphs.push_back({L, nb * 2 + masked, n_steps, 0, cfg_rate, std::vector<float>(t_vals, t_vals + n_steps),
                            std::vector<float>(dt_vals, dt_vals + n_steps), nullptr, 0});
       g = &h->graphs.back();
     } else if (g != &h->graphs.back()) {          // most recently used last
@@ -347,14 +407,14 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
     }
     g->seen += 1;
   }
-  if (!g || g->seen < 2) return solve_body(h, pl, z, mu, spks, cond, L, n_steps, dt_vals, cfg_rate, mel_out, st);   // eager
-  const size_t nb = (size_t)NMEL * L * sizeof(float);
+  if (!g || g->seen < 2) return solve_body(h, pl, z, mu, spks, cond, L, n_steps, dt_vals, cfg_rate, mel_out, lens_dev, st);   // eager
+  const size_t nb_bytes = (size_t)nb * NMEL * L * sizeof(float);
   if (!g->exec) {
     if (!h->cap_stream) CBX_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
     const long long before = h->launches;
     cudaGraph_t graph = nullptr;
     CBX_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
-    const int rc = solve_body(h, pl, h->st_z, h->st_mu, h->st_spks, h->st_cond, L, n_steps, dt_vals, cfg_rate, h->st_out, h->cap_stream);
+    const int rc = solve_body(h, pl, h->st_z, h->st_mu, h->st_spks, h->st_cond, L, n_steps, dt_vals, cfg_rate, h->st_out, lens_dev, h->cap_stream);
     const cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
     g->launches = h->launches - before;
     h->launches = before;
@@ -367,12 +427,12 @@ extern "C" int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const 
     cudaGraphDestroy(graph);
     CBX_CHECK(ie == cudaSuccess, "cbx_cfm_solve: cudaGraphInstantiate failed (%s)", cudaGetErrorString(ie));
   }
-  CBX_CUDA(cudaMemcpyAsync(h->st_z, z, nb, cudaMemcpyDeviceToDevice, st));
-  CBX_CUDA(cudaMemcpyAsync(h->st_mu, mu, nb, cudaMemcpyDeviceToDevice, st));
-  CBX_CUDA(cudaMemcpyAsync(h->st_spks, spks, NMEL * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  CBX_CUDA(cudaMemcpyAsync(h->st_cond, cond, nb, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_z, z, nb_bytes, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_mu, mu, nb_bytes, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_spks, spks, (size_t)nb * NMEL * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(h->st_cond, cond, nb_bytes, cudaMemcpyDeviceToDevice, st));
   CBX_CUDA(cudaGraphLaunch(g->exec, st));
-  CBX_CUDA(cudaMemcpyAsync(mel_out, h->st_out, nb, cudaMemcpyDeviceToDevice, st));
+  CBX_CUDA(cudaMemcpyAsync(mel_out, h->st_out, nb_bytes, cudaMemcpyDeviceToDevice, st));
   h->launches += g->launches;
   return CBX_OK;
 }

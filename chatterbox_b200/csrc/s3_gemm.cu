@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       par[PAR_BIAS * 256 + c] = e.bias ? __ldg(e.bias + (e.bias_mod > 0 ? n % e.bias_mod : n)) : 0.f;
       par[PAR_G1 * 256 + c] = e.ln_g ? __ldg(e.ln_g + n) : 0.f;
       par[PAR_B1 * 256 + c] = e.ln_g ? __ldg(e.ln_b + n) : 0.f;
-      par[PAR_TEMB * 256 + c] = e.temb ? __ldg(e.temb + (size_t)b * p.N + n) : 0.f;
+      par[PAR_TEMB * 256 + c] = e.temb ? __ldg(e.temb + n) : 0.f;      // one vector [N]: every row of a solve shares t
       par[PAR_G2 * 256 + c] = e.out_ln ? __ldg(e.ln2_g + n) : 0.f;
       par[PAR_B2 * 256 + c] = e.out_ln ? __ldg(e.ln2_b + n) : 0.f;
       par[PAR_ALPHA * 256 + c] = e.snake_alpha ? __ldg(e.snake_alpha + n) : 1.f;

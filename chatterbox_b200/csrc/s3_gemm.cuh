@@ -8,7 +8,7 @@ struct GemmEpi {
   const float* bias;                       // [N] or null
   int bias_mod;                            // > 0: bias index is n % bias_mod (polyphase transposed convolution)
   const float* ln_g; const float* ln_b;    // LayerNorm over the N outputs of a row, then Mish (needs n_tile == N)
-  const float* temb;                       // [B][N] added after Mish, or null
+  const float* temb;                       // [N] added after Mish (the same time embedding for every batch row), or null
   int gelu;                                // exact (erf) GELU
   int elu;                                 // ELU(alpha = 1)
   const float* resid; int ld_resid;        // fp32 [rows][ld] added last

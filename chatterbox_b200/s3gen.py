@@ -23,7 +23,7 @@ S3GEN_SR = 24000
 
 class S3Gen:
     def __init__(self, flow_sd: Dict[str, torch.Tensor], hift_sd: Dict[str, torch.Tensor], device="cuda", *,
-                 rand_noise: Optional[torch.Tensor] = None, max_mel_len: int = 4096):
+                 rand_noise: Optional[torch.Tensor] = None, max_mel_len: int = 4096, max_batch: int = 1):
         if not torch.cuda.is_available():
             raise _lib.CbxError("chatterbox_b200.S3Gen needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device)
@@ -31,7 +31,8 @@ class S3Gen:
             self.device = torch.device("cuda", torch.cuda.current_device())
         keep = ("input_embedding.", "spk_embed_affine_layer.", "encoder.", "encoder_proj.")
         self.front = {k: v.to(self.device, torch.float32) for k, v in flow_sd.items() if k.startswith(keep)}
-        self.estimator = ConditionalDecoder(flow_sd, self.device, prefix="decoder.estimator.", max_len=max_mel_len)
+        self.estimator = ConditionalDecoder(flow_sd, self.device, prefix="decoder.estimator.", max_len=max_mel_len,
+                                            max_batch=max_batch)
         self.decoder = CausalConditionalCFM(self.estimator, rand_noise=rand_noise)
         self.mel2wav = HiFTGenerator(hift_sd, self.device, max_frames=max_mel_len)
         self.record_events = False
@@ -128,6 +129,49 @@ class S3Gen:
             ev["hift1"].record()
             self.events.update(ev)
         return wav, src
+
+    @torch.inference_mode()
+    def flow_inference_batch(self, speech_tokens_list, ref_dicts):
+        """Several utterances through ONE flow-matching solve (BASELINE config 4; the reference would call
+        `flow.inference` once per request, server.py:223-232): token front-end per utterance, (mu, cond) padded to the
+        longest mel length, `CausalConditionalCFM.forward_batch`, each utterance's own frames sliced out.
+        -> list of mel (1, 80, 2 T_u)."""
+        ev = {k: torch.cuda.Event(enable_timing=True) for k in ("front0", "cfm0", "cfm1")} if self.record_events else None
+        if ev:
+            ev["front0"].record()
+        mus, spk, conds, l1s = [], [], [], []
+        for tok, rd in zip(speech_tokens_list, ref_dicts):
+            ref = self._ref(rd)
+            tok = tok.to(self.device)
+            if tok.dim() == 1:
+                tok = tok.unsqueeze(0)
+            mu, spks, cond, l1 = self._front(tok.long(), ref["prompt_token"].long(), ref["prompt_feat"].float(),
+                                             ref["embedding"].float())
+            mus.append(mu.clone()); spk.append(spks.clone()); conds.append(cond.clone()); l1s.append(l1)   # graph outputs are static
+        if ev:
+            ev["cfm0"].record()
+        lens = [int(m.shape[2]) for m in mus]
+        L = max(lens)
+        pad = lambda a: torch.nn.functional.pad(a, (0, L - a.shape[2]))
+        feat = self.decoder.forward_batch(torch.cat([pad(m) for m in mus], 0), lens, 10, spks=torch.cat(spk, 0),
+                                          cond=torch.cat([pad(c) for c in conds], 0))
+        if ev:
+            ev["cfm1"].record()
+            self.events.update(ev)
+        return [feat[u:u + 1, :, l1s[u]:lens[u]].contiguous() for u in range(len(mus))]
+
+    @torch.inference_mode()
+    def inference_batch(self, speech_tokens_list, ref_dicts, *, seed: Optional[int] = None):
+        """-> list of (wav (1, n_u), source (1, 1, n_u)): batched flow matching, then the vocoder per utterance."""
+        mels = self.flow_inference_batch(speech_tokens_list, ref_dicts)
+        ev = {k: torch.cuda.Event(enable_timing=True) for k in ("hift0", "hift1")} if self.record_events else None
+        if ev:
+            ev["hift0"].record()
+        outs = [self.hift_inference(m, None, seed=seed, apply_fade=True) for m in mels]
+        if ev:
+            ev["hift1"].record()
+            self.events.update(ev)
+        return outs
 
     def launches(self) -> int:
         return self.estimator.launches() + self.mel2wav.launches()

@@ -166,6 +166,16 @@ int cbx_cfm_estimator(cbx_cfm* h, const float* x, const float* mu, const float* 
  * does); mel_out [80][L]. */
 int cbx_cfm_solve(cbx_cfm* h, const float* z, const float* mu, const float* spks, const float* cond, int L,
                   int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate, float* mel_out, void* stream);
+/* Batched variants (BASELINE config 4: the flow-matching stage of up to max_batch utterances as ONE solve, so the estimator's
+ * GEMMs see 2 nb L rows instead of 2 L).  z, mu, cond [nb][80][L], spks [nb][80], mel_out [nb][80][L], every utterance padded to
+ * L frames; lens: HOST array [nb] of true lengths (NULL = all L).  The padding is the reference's padded-batch semantics
+ * (decoder.py:25-33, utils/mask.py:167-193): the estimator is causal in its convolutions, so frames past lens[u] reach valid
+ * frames only through attention, where they are masked as keys; output frames past lens[u] are unspecified (the reference
+ * zeroes them) and must be sliced off by the caller. */
+int cbx_cfm_create_batched(int device, int max_len, int max_batch, const CbxCfmWeights* w, cbx_cfm** out);
+int cbx_cfm_solve_batch(cbx_cfm* h, int nb, const float* z, const float* mu, const float* spks, const float* cond,
+                        const int32_t* lens, int L, int n_steps, const float* t_vals, const float* dt_vals, float cfg_rate,
+                        float* mel_out, void* stream);
 int cbx_cfm_launches(cbx_cfm* h, int64_t* launches);
 /* Entries of the handle's two bounded caches: executable solve graphs (LRU, at most 8) and per-length op plans (at most 64). */
 int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans);

@@ -146,3 +146,38 @@ def test_solve_graph_cache_is_bounded(est):
                 assert _rel(mel, first) < 1e-5
     g, p = est.cache_sizes()
     assert g <= 8 and p <= 64, (g, p)
+
+
+def test_batched_ragged_solve_matches_each_utterance_alone_and_the_oracle():
+    """Padded batch (decoder.py:25-33, utils/mask.py:167-193): four utterances of different mel lengths in ONE solve —
+    every utterance must give the mel it gives alone (key-padding mask in the attention kernel; the causal convolutions
+    never look forward into the padding), and the shortest one is also checked against the CPU oracle."""
+    from chatterbox_b200.cfm import CausalConditionalCFM, ConditionalDecoder
+    from oracle import cfm_oracle as CO
+    sd = S.make_state_dict("flow")
+    est_b = ConditionalDecoder(sd, "cuda", prefix=PFX, max_len=320, max_batch=4)
+    cfm = CausalConditionalCFM(est_b, rand_noise=S.cfm_noise())
+    lens = [200, 64, 311, 129]
+    Lmax = max(lens)
+    inps = [S.cfm_inputs(L, seed=40 + k) for k, L in enumerate(lens)]
+    pad = lambda a: torch.nn.functional.pad(a, (0, Lmax - a.shape[2]))
+    mu = torch.cat([pad(i["mu"]) for i in inps], 0)
+    cond = torch.cat([pad(i["cond"]) for i in inps], 0)
+    spks = torch.cat([i["spks"] for i in inps], 0)
+    for rep in ("eager", "graph capture", "graph replay"):
+        out = cfm.forward_batch(mu, lens, 10, spks=spks, cond=cond).cpu()
+        for k, (L, i) in enumerate(zip(lens, inps)):
+            alone, _ = cfm(mu=i["mu"], mask=None, n_timesteps=10, spks=i["spks"], cond=i["cond"])
+            r = _rel(out[k:k + 1, :, :L], alone.cpu())
+            print(f"batched solve ({rep}), utterance {k} (L = {L} of {Lmax}): rel-L2 vs the same utterance alone {r:.3e}")
+            assert r < 2e-3          # same kernels, same data: only the tile an utterance's rows fall into differs
+    with torch.inference_mode():
+        i = inps[1]
+        ref = CO.solve_euler(sd, i["z"], i["mu"], i["spks"], i["cond"], pfx=PFX)
+    r = _rel(out[1:2, :, :lens[1]], ref)
+    print(f"batched solve, utterance 1 (L = {lens[1]}) rel-L2 vs oracle: {r:.3e}")
+    assert r < TOL
+    # equal lengths: no mask array at all
+    same = cfm.forward_batch(torch.cat([inps[0]["mu"]] * 3, 0), None, 10, spks=torch.cat([inps[0]["spks"]] * 3, 0),
+                             cond=torch.cat([inps[0]["cond"]] * 3, 0)).cpu()
+    assert _rel(same[2:3], same[0:1]) < 1e-6

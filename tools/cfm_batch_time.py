@@ -1,0 +1,24 @@
+"""Batched CFM solve timing: python tools/cfm_batch_time.py nb [L] -> ms per 10-step solve, ms per utterance, TFLOP/s."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from chatterbox_b200 import synthetic as S
+from chatterbox_b200.cfm import CausalConditionalCFM, ConditionalDecoder
+nb = int(sys.argv[1]) if len(sys.argv) > 1 else 16
+L = int(sys.argv[2]) if len(sys.argv) > 2 else 812
+est = ConditionalDecoder(S.make_state_dict("flow"), "cuda", prefix="decoder.estimator.", max_len=L, max_batch=nb)
+cfm = CausalConditionalCFM(est, rand_noise=S.cfm_noise())
+i = S.cfm_inputs(L)
+mu, cond, spks = (torch.cat([i[k]] * nb, 0).cuda() for k in ("mu", "cond", "spks"))
+for _ in range(3):
+    cfm.forward_batch(mu, None, 10, spks=spks, cond=cond)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(3):
+    cfm.forward_batch(mu, None, 10, spks=spks, cond=cond)
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / 3
+flop = nb * 10 * 2 * L * (132.18e6 + 114688.0 * L)
+print(f"nb={nb} L={L}: {ms:.2f} ms per solve, {ms / nb:.2f} ms per utterance, {flop / ms / 1e9:.1f} TFLOP/s")
