@@ -1,6 +1,6 @@
 """Generate the pinned vectors under tests/golden/ from the UNMODIFIED reference (container only).
 
-TEST INFRASTRUCTURE.  Run:  python -m oracle.make_golden [t3] [t3w] [cfm] [hift] [flow]
+TEST INFRASTRUCTURE.  Run:  python -m oracle.make_golden [t3] [t3w] [align] [cfm] [hift] [flow]
 
 The reference modules are imported from /root/reference through `oracle/ref_import.py`, loaded
 with the synthetic state dicts of `chatterbox_b200/synthetic.py`, and driven through their own
@@ -208,6 +208,104 @@ def make_t3w():
     print("[t3w] wrote tests/golden/t3_fp32w_golden.safetensors")
 
 
+def _ref_analyzer(S_text, eos):
+    """The UNMODIFIED reference class on a stand-in transformer (its constructor only installs a forward hook)."""
+    import types
+    R.install()
+    from chatterbox.models.t3.inference.alignment_stream_analyzer import AlignmentStreamAnalyzer
+
+    class _Attn(torch.nn.Module):
+        def forward(self, *a, **k):
+            return None
+    tf = types.SimpleNamespace(layers=[types.SimpleNamespace(self_attn=_Attn()) for _ in range(10)])
+    return AlignmentStreamAnalyzer(tf, None, (34, 34 + S_text), alignment_layer_idx=9, eos_idx=eos)
+
+
+def align_script(S_text: int, n_steps: int, seed: int, mode: str) -> torch.Tensor:
+    """Synthetic head-mean attention rows over the text columns, (n_steps + 1, S): two prompt rows' worth is rows 0-1 of
+    the first call, then one row per decode step.  mode "walk": a peak that walks monotonically through the text and
+    then dwells on the last tokens (-> complete, long tail); "repeat": walks to the end and jumps back (-> repetition);
+    "noise": near-uniform rows (-> false start forever, EOS suppressed)."""
+    g = torch.Generator().manual_seed(seed)
+    rows = torch.rand(n_steps + 1, S_text, generator=g) * 0.02
+    if mode == "noise":
+        return rows
+    for t in range(n_steps + 1):
+        if mode == "walk":
+            c = min(S_text - 1, t // 2)
+        else:
+            c = min(S_text - 1, t // 2) if t < 2 * S_text + 6 else 3 + (t % 5)
+        rows[t, c] = 0.9
+    return rows
+
+
+def make_align():
+    """AlignmentStreamAnalyzer.step (alignment_stream_analyzer.py:89-154): the reference class and the O(1)-state
+    restatement side by side, on crafted attention rows that reach every branch and on the layer-9 attention the
+    reference model itself produces; decisions per step committed as golden."""
+    eos = T3O.STOP_SPEECH
+    out = {}
+    for name, (S_text, n, mode) in {"walk": (12, 80, "walk"), "repeat": (16, 90, "repeat"), "noise": (20, 30, "noise")}.items():
+        rows = align_script(S_text, n, 5, mode)
+        ref, mine = _ref_analyzer(S_text, eos), T3O.AlignmentOracle(S_text, eos)
+        dec = []
+        for k in range(n):
+            chunk = rows[0:2] if k == 0 else rows[k + 1:k + 2]
+            full = torch.zeros(chunk.shape[0] if k else 34 + S_text + 2, 34 + S_text + 2 + k)
+            if k == 0:
+                full[34 + S_text:, 34:34 + S_text] = chunk
+            else:
+                full[:, 34:34 + S_text] = chunk
+            ref.last_aligned_attn = full
+            lg = torch.randn(2, 1, 8194, generator=torch.Generator().manual_seed(k))
+            a = ref.step(lg.clone())
+            b = mine.step(lg.clone(), chunk)
+            assert torch.equal(a, b), (name, k)
+            # "forced": every other logit is -2**15 (the reference's suppression runs AFTER the forcing and overrides the
+            # EOS logit itself when the current position is early: alignment_stream_analyzer.py:141-151)
+            forced = bool(a[0, 0, 0] == -2 ** 15 and a[0, 0, 1] == -2 ** 15)
+            sup = bool(a[0, 0, eos] == -2 ** 15)
+            dec.append([int(ref.text_position), int(ref.started), int(ref.complete), int(forced), int(sup)])
+            assert (int(mine.text_position), int(mine.started), int(mine.complete)) == tuple(dec[-1][:3])
+        dec = torch.tensor(dec, dtype=torch.int32)
+        print(f"[align] {name}: {n} steps, reference == restatement; started at {ref.started_at}, completed at {ref.completed_at}, "
+              f"forced EOS at steps {torch.nonzero(dec[:, 3]).flatten()[:3].tolist()}, suppressed {int(dec[:, 4].sum())} steps")
+        out[f"{name}_rows"] = rows
+        out[f"{name}_decisions"] = dec
+    assert int(out["walk_decisions"][:, 3].sum()) > 0 and int(out["repeat_decisions"][:, 3].sum()) > 0
+    # layer-9 attention of the reference model itself (teacher-forced, 2-layer... no: the full 30-layer synthetic model)
+    torch.manual_seed(0)
+    sd = S.make_state_dict("t3")
+    t3 = R.build_t3()
+    t3.load_state_dict(sd)
+    cond, text = S.t3_cond(), S.text_tokens()
+    text2 = torch.cat([text, text], 0)
+    S_text = text.shape[1]
+    params = dict(cfg_weight=0.5, temperature=0.8, repetition_penalty=1.2, min_p=0.05, top_p=1.0)
+    # transformers 5.5 keeps SDPA under output_attentions=True and returns no weights (4.46.3, the reference's pin, falls
+    # back to the eager path): select the eager path explicitly for this capture
+    t3.tfmr.config._attn_implementation = "eager"
+    maps = []
+    hk = t3.tfmr.layers[9].self_attn.register_forward_hook(lambda m, i, o: maps.append(o[1][0].mean(0).detach().clone()))
+    forced = torch.randint(0, 6561, (1, 12), generator=torch.Generator().manual_seed(91))
+    _ref_t3_run(t3, cond, text2, 12, forced=forced, **params)
+    hk.remove()
+    assert len(maps) >= 12 and maps[0].shape[0] == 34 + S_text + 2, (len(maps), maps[0].shape)
+    rows = [maps[0][34 + S_text:, 34:34 + S_text]] + [m[:, 34:34 + S_text] for m in maps[1:12]]
+    _, _, mo = T3O.inference(sd, cond, text2, max_new_tokens=12, forced_tokens=forced, return_model=True,
+                             attn_probe_layer=9, **params)
+    mine_rows = mo.attn_rows
+    for k, (a, b) in enumerate(zip(rows, mine_rows)):
+        assert (a - b).abs().max() < 1e-5, k
+    out["model_rows0"] = rows[0].clone()
+    out["model_rows"] = torch.cat(rows[1:], 0)
+    out["model_forced"] = forced[0].to(torch.int32)
+    print(f"[align] layer-9 head-mean attention rows of the reference model == restatement over 12 steps "
+          f"(row sums over the text columns: {float(rows[0][-1].sum()):.3f} ... {float(rows[-1].sum()):.3f})")
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(GOLD, "t3_align_golden.safetensors"))
+    print("[align] wrote tests/golden/t3_align_golden.safetensors")
+
+
 def make_cfm():
     """Reference ConditionalDecoder / CausalConditionalCFM vs oracle/cfm_oracle.py; golden outputs."""
     from oracle import cfm_oracle as CO
@@ -340,6 +438,8 @@ if __name__ == "__main__":
         make_t3()
     if "t3w" in which:
         make_t3w()
+    if "align" in which:
+        make_align()
     if "cfm" in which and "make_cfm" in globals():
         globals()["make_cfm"]()
     if "hift" in which and "make_hift" in globals():

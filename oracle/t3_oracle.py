@@ -207,16 +207,29 @@ def inference(sd, cond, text_tokens: torch.Tensor, *, max_new_tokens: int, cfg_w
               temperature: float = 0.8, repetition_penalty: float = 1.2, min_p: float = 0.05,
               top_p: float = 1.0, forced_tokens: Optional[torch.Tensor] = None, stop_on_eos: bool = True,
               n_layers: int = 30, weight_round: bool = False, kv_round: bool = False,
-              return_model: bool = False):
+              return_model: bool = False, attn_probe_layer: Optional[int] = None, analyzer: Optional["AlignmentOracle"] = None):
     """Greedy (argmax) or teacher-forced restatement of T3.inference.
     Returns (tokens (1, n) int64, raw_logits (n, B, V) — the `output.logits[:, -1]` of each step)."""
     emb = prepare_input_embeds(sd, cond, text_tokens, cfg_weight)
     B = emb.shape[0]
     m = LlamaOracle(sd, n_layers=n_layers, weight_round=weight_round, kv_round=kv_round)
+    if analyzer is not None and attn_probe_layer is None:
+        attn_probe_layer = 9
+    m.attn_probe_layer = attn_probe_layer
+    m.attn_rows = []          # head-mean attention of the conditional row over the text columns, per forward pass
+    ti, tj = 34, 34 + text_tokens.shape[1]
+
+    def probe_rows(first: bool):
+        a = m.attn_probe[0].mean(0)                       # (T_q, T_k)
+        return a[tj:, ti:tj] if first else a[:, ti:tj]
     logits = m.forward(emb)[:, -1]
+    if attn_probe_layer is not None:
+        m.attn_rows.append(probe_rows(True).clone())
     gen = torch.tensor([[START_SPEECH]], dtype=torch.long)
     toks, raw = [], []
     for i in range(max_new_tokens):
+        if analyzer is not None:          # t3_hf_backend.py:108-109 (the call the reference keeps commented out)
+            logits = analyzer.step(logits[:, None], m.attn_rows[-1])[:, 0]
         raw.append(logits.clone())
         proc = process_logits(logits, gen, cfg_weight=cfg_weight, temperature=temperature,
                               repetition_penalty=repetition_penalty, min_p=min_p, top_p=top_p)
@@ -227,5 +240,73 @@ def inference(sd, cond, text_tokens: torch.Tensor, *, max_new_tokens: int, cfg_w
             break
         e = (sd["speech_emb.weight"][nxt] + sd["speech_pos_emb.emb.weight"][i + 1]).expand(B, -1, -1)
         logits = m.forward(e)[:, -1]
+        if attn_probe_layer is not None:
+            m.attn_rows.append(probe_rows(False).clone())
     out = (torch.cat(toks, dim=1), torch.stack(raw))
     return out + (m,) if return_model else out
+
+
+# ---------------------------------------------------------------------------------------------
+# AlignmentStreamAnalyzer (inference/alignment_stream_analyzer.py:29-154)
+# ---------------------------------------------------------------------------------------------
+class AlignmentOracle:
+    """Restatement of `AlignmentStreamAnalyzer.step` (alignment_stream_analyzer.py:89-154) with O(1) state instead of
+    the growing alignment matrix A (T, S): every quantity the reference reads off A is a running statistic —
+      A[-2:, -2:].max()                      -> last-two-columns maximum of the two most recent rows
+      A[:, :4].max()                         -> running maximum over the first four columns
+      A[completed_at:, -3:].sum(0).max()     -> three running column sums over rows appended after completion
+      A[completed_at:, :-5].max(1).sum()     -> running sum of row maxima over columns [:S-5] after completion
+    `step(logits, rows)` takes the head-mean layer-9 attention of the conditional row over the text columns for the
+    queries of this forward pass ((2, S) or (1, S) for the prompt, (1, S) per decode step) and returns the logits with
+    EOS forced / suppressed exactly as the reference (±2**15).  tests/test_oracle_t3.py drives this and the reference
+    class side by side (golden: tests/golden/t3_align_golden.safetensors)."""
+
+    def __init__(self, n_text: int, eos_idx: int = STOP_SPEECH):
+        self.S, self.eos = n_text, eos_idx
+        self.frame, self.text_position = 0, 0
+        self.started, self.started_at = False, None
+        self.complete, self.completed_at = False, None
+        self.T = 0
+        self.last2 = [float("-inf"), float("-inf")]      # last-two-columns max of the previous / current row
+        self.first4 = float("-inf")
+        self.tail = [0.0, 0.0, 0.0]
+        self.rep = 0.0
+        self.history = []          # per step: (cur_text_posn, text_position, started, complete, forced, suppressed)
+
+    def step(self, logits: torch.Tensor, rows: torch.Tensor) -> torch.Tensor:
+        S = self.S
+        rows = rows.clone().float()
+        rows[:, self.frame + 1:] = 0                                       # monotonic masking (:107)
+        for r in rows:
+            self.T += 1
+            self.last2 = [self.last2[1], float(r[-2:].max())]
+            self.first4 = max(self.first4, float(r[:4].max()))
+            if self.complete:                                              # rows at index >= completed_at
+                for k in range(3):
+                    self.tail[k] += float(r[S - 3 + k])
+                if S > 5:
+                    self.rep += float(r[:S - 5].max())
+        cur = int(rows[-1].argmax())
+        if -4 < cur - self.text_position < 7:                              # not a discontinuity (:118-121)
+            self.text_position = cur
+        a_last2 = max(self.last2) if self.T >= 2 else self.last2[1]
+        false_start = (not self.started) and (a_last2 > 0.1 or self.first4 < 0.5)
+        self.started = not false_start
+        if self.started and self.started_at is None:
+            self.started_at = self.T
+        self.complete = self.complete or self.text_position >= S - 3
+        if self.complete and self.completed_at is None:
+            self.completed_at = self.T
+        long_tail = self.complete and max(self.tail) >= 10
+        repetition = self.complete and self.rep > 5
+        forced = bool(long_tail or repetition)
+        if forced:
+            logits = -(2 ** 15) * torch.ones_like(logits)
+            logits[..., self.eos] = 2 ** 15
+        suppressed = cur < S - 3
+        if suppressed:
+            logits = logits.clone()
+            logits[..., self.eos] = -2 ** 15
+        self.frame += 1
+        self.history.append((cur, self.text_position, self.started, self.complete, forced, suppressed))
+        return logits

@@ -65,3 +65,32 @@ def test_teacher_forced_logits_match_reference(sd):
     for j, st in enumerate(GOLD["forced_logit_steps"].tolist()):
         if st < n:
             assert (raw[st] - GOLD["forced_logits"][j]).abs().max() < 1e-4
+
+
+# ---- AlignmentStreamAnalyzer restatement vs the reference class's own decisions (oracle/make_golden.py align) ----
+ALIGN = load_file(os.path.join(os.path.dirname(__file__), "golden", "t3_align_golden.safetensors"))
+
+
+@pytest.mark.parametrize("name", ["walk", "repeat", "noise"])
+def test_alignment_oracle_reproduces_reference_decisions(name):
+    rows, dec = ALIGN[f"{name}_rows"], ALIGN[f"{name}_decisions"]
+    S_text = rows.shape[1]
+    an = T3O.AlignmentOracle(S_text)
+    for k in range(dec.shape[0]):
+        chunk = rows[0:2] if k == 0 else rows[k + 1:k + 2]
+        out = an.step(torch.zeros(2, 1, 8194), chunk)
+        forced = bool(out[0, 0, 0] == -2 ** 15)
+        sup = bool(out[0, 0, T3O.STOP_SPEECH] == -2 ** 15)
+        assert [an.text_position, int(an.started), int(an.complete), int(forced), int(sup)] == dec[k].tolist(), (name, k)
+    if name != "noise":
+        assert int(dec[:, 3].sum()) > 0          # the script reaches the forced-EOS branch
+
+
+def test_alignment_rows_of_the_oracle_model_match_the_reference_model(sd):
+    text2 = torch.cat([S.text_tokens()] * 2, 0)
+    forced = ALIGN["model_forced"].long()[None]
+    _, _, m = T3O.inference(sd, S.t3_cond(), text2, max_new_tokens=3, forced_tokens=forced, return_model=True,
+                            attn_probe_layer=9, **PARAMS)
+    assert (m.attn_rows[0] - ALIGN["model_rows0"]).abs().max() < 1e-5
+    for k in range(1, 3):
+        assert (m.attn_rows[k][0] - ALIGN["model_rows"][k - 1]).abs().max() < 1e-5
