@@ -59,6 +59,7 @@ SYMBOLS = {
     "cbx_t3_decode": (C.c_int, [C.c_void_p, C.POINTER(CbxSampleParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p]),
     "cbx_t3_set_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "cbx_t3_set_alignment": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cbx_t3_batch_create": (C.c_int, [C.POINTER(CbxT3BatchConfig), C.POINTER(CbxT3Weights), C.POINTER(C.c_void_p)]),
     "cbx_t3_batch_destroy": (C.c_int, [C.c_void_p]),
     "cbx_t3_batch_prefill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(CbxSampleParams), C.c_int,

@@ -108,11 +108,12 @@ constexpr int SMEM_XR = SMEM_GN + T3_H * 4;
 constexpr int SMEM_TOTAL = SMEM_XR + NCONS_WARPS * 2 * 16 * VPL * 4;
 static_assert(NSLOT > 4 || SMEM_TOTAL + 1024 <= 196 * 1024, "4-slot build: stay inside the 196 KB carve-out (the rest of the 256 KB is L1)");
 static_assert(SMEM_TOTAL <= 232448, "shared memory budget");
-static_assert(2 * NCONS_WARPS * 2 * 4 <= 256, "ssq buffer");
+static_assert(2 * NCONS_WARPS * 2 * 4 <= 128, "ssq buffer: the sums use the first 128 B, the analyzer state the rest");
 static_assert(SMEM_SCRATCH % 16 == 0 && SMEM_XT % 16 == 0, "alignment");
 
 // LL exchange buffers (elements are {fp32 bits, flag} 8-byte words), offsets in words
-enum { LLP_QKV = 0, LLP_PART = 1, LLP_OPROJ = 3, LLP_ACT = 4, LLP_DOWN = 5, LLP_LOGITS = 6, LLP_EMB = 7 };
+enum { LLP_QKV = 0, LLP_PART = 1, LLP_ALIGN = 2, LLP_OPROJ = 3, LLP_ACT = 4, LLP_DOWN = 5, LLP_LOGITS = 6, LLP_EMB = 7 };
+constexpr int AL_CAP = 2112;              // text columns the alignment analyzer can track (max_text_tokens 2048 + SOT / EOT, padded)
 constexpr size_t LL_QKV = 0;                                          // [2][3072]
 constexpr size_t LL_PART = LL_QKV + (size_t)2 * 3072;                 // [32 pairs][MAXS][PART_STRIDE]
 constexpr size_t LL_OPROJ = LL_PART + (size_t)32 * MAXS * PART_STRIDE;   // [2][1024]
@@ -120,7 +121,12 @@ constexpr size_t LL_ACT = LL_OPROJ + (size_t)2 * T3_H;                // [2][409
 constexpr size_t LL_DOWN = LL_ACT + (size_t)2 * T3_INTER;             // [4 k-slices][2][1024]
 constexpr size_t LL_LOGITS = LL_DOWN + (size_t)T3_DOWN_KS * 2 * T3_H; // [2][VOCAB_PAD]
 constexpr size_t LL_EMB = LL_LOGITS + (size_t)2 * VOCAB_PAD;          // [1024] + control word
-constexpr size_t LL_WORDS = LL_EMB + T3_H + 8;
+// alignment analyzer (alignment_stream_analyzer.py): un-normalised softmax terms of the text columns, per head, and the
+// (m, l) of every (head, KV split) of the analysed layer's conditional row
+constexpr size_t LL_AL = LL_EMB + T3_H + 8;                           // [16 heads][AL_CAP]
+constexpr size_t LL_ALML = LL_AL + (size_t)T3_NH * AL_CAP;            // [16][MAXS][2]
+constexpr size_t LL_WORDS = LL_ALML + (size_t)T3_NH * MAXS * 2;
+static_assert((AL_CAP + 64 + T3_NH * MAXS * 2 + T3_NH * 2) * 4 <= SCRATCH_BYTES, "analyzer scratch fits the sampling scratch");
 
 struct T3State {   // lives in global memory, persists between launches of one utterance
   int pos;         // KV cache length
@@ -128,6 +134,18 @@ struct T3State {   // lives in global memory, persists between launches of one u
   int stop;        // EOS seen
   int err;         // device-side error (1 = watchdog timeout)
 };
+
+// O(1) state of AlignmentStreamAnalyzer.step (alignment_stream_analyzer.py:89-154; oracle/t3_oracle.py AlignmentOracle):
+// everything the reference reads off its growing alignment matrix A is a running statistic
+struct AlState {
+  int frame, text_pos, started, complete, T;
+  float last2_prev, last2_cur;      // max of the last two columns of the two most recent rows      (A[-2:, -2:].max())
+  float first4;                     // running max over the first four columns                      (A[:, :4].max())
+  float tail0, tail1, tail2;        // column sums of the last three columns after completion       (A[completed_at:, -3:].sum(0))
+  float rep;                        // sum of row maxima over columns [:S-5] after completion       (A[completed_at:, :-5].max(1).sum())
+  int force, suppress, pad0, pad1;  // decision of the current step
+};
+static_assert(sizeof(AlState) == 64, "AlState layout");
 
 struct T3Params {
   const uint8_t* wstream; long long stride_bytes;
@@ -142,6 +160,13 @@ struct T3Params {
   const float* embeds; int P;   // prefill
   CbxSampleParams sp; int max_new; const int* forced; int* tokens_out; int* n_out; float* logits_out;
   unsigned long long* prof; int prof_it;   // optional: CTA 0 stamps %globaltimer after every phase of iteration prof_it
+  // alignment analyzer (off: al_layer < 0): analysed layer, first text position, text columns, query rows of the prompt
+  int al_layer, al_i, al_n, al_rows0;
+  const float* al_prefill;      // [al_rows0][AL_CAP] rows of the prompt prefill
+  const float* al_inject;       // optional [rows][al_n]: rows used INSTEAD of the measured attention (tests of the state machine)
+  float* al_rows_out;           // optional [rows][al_n]: every row the analyzer consumed, before the monotonic masking
+  int* al_out;                  // optional [max_new][4]: text position, flags (started | complete << 1 | forced << 2 | suppressed << 3), argmax
+  AlState* al_state;
 };
 
 struct Ctl {            // CTA-local control block in shared memory
@@ -842,6 +867,10 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
     M = fmaxf(M, (i < nrows) ? s_sm[i] : -INFINITY);
   }
   M = warp_max(M);
+  // alignment analyzer: the conditional row of the analysed layer publishes exp(s - m) of the text columns of this split
+  // and the split's (m, l); CTA 0 normalises across splits and averages the heads before it samples the next token
+  const bool al_pub = layer == p.al_layer && b == 0 && warp == 0;
+  const unsigned al_fl = ll_flag(it, L, layer, LLP_ALIGN);
   float lsum = 0.f;
   float acc[8];
 #pragma unroll
@@ -859,6 +888,15 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
     }
   }
   lsum = warp_sum(lsum);
+  if (al_pub) {        // one warp of 16 CTAs, one layer per token: kept out of the accumulation loop above
+    const int c0 = max(p.al_i - lo, 0), c1 = min(p.al_i + p.al_n - lo, n);      // rows of this split that are text columns
+    for (int i = c0 + lane; i < c1; i += 32)
+      ll_store(p.ll + LL_AL + (size_t)head * AL_CAP + (lo + i - p.al_i), __expf(s_sm[i] - M), al_fl);
+    if (lane == 0) {
+      ll_store(p.ll + LL_ALML + (size_t)(head * MAXS + split) * 2, M, al_fl);
+      ll_store(p.ll + LL_ALML + (size_t)(head * MAXS + split) * 2 + 1, lsum, al_fl);
+    }
+  }
   // reduce-scatter over the 32 lanes: 8 -> 4 -> 2 -> 1 values, then two plain steps; lane 4 j ends with dim j
   {
     const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
@@ -992,6 +1030,125 @@ __device__ __forceinline__ unsigned f2ord(float f) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+// ---- AlignmentStreamAnalyzer.step on CTA 0 (alignment_stream_analyzer.py:89-154) ---------------------------------
+// Runs before the pending logits are processed: builds the head-mean attention row(s) of the forward pass that
+// produced those logits over the text columns — from the prompt prefill (first call), from the LL words the analysed
+// layer's attention CTAs published (decode), or from an injected script (tests) — applies the monotonic masking,
+// updates the running statistics and leaves the decision (force / suppress EOS) in the shared-memory state.
+// `row` = the sampling scratch (free at this point): [AL_CAP] row, then 64 floats of reduction scratch, then (m, l) data.
+__device__ __noinline__ void align_step(const T3Params& p, int it, int pos0, float* row, AlState* as, Ctl* ctl, int warp,
+                                        int lane) {
+  const int tid = threadIdx.x, S = p.al_n, L = p.n_layers;
+  float* rs = row + AL_CAP;
+  int* ri = reinterpret_cast<int*>(rs + 32);
+  float* ml = rs + 64;                     // [16][MAXS][2] split (m, l), then [16][2] = {M_h, 1 / (16 L_h)}
+  const int nrows = (as->frame == 0) ? p.al_rows0 : 1;
+  for (int r = 0; r < nrows; ++r) {
+    const int T = as->T;                   // rows consumed so far (uniform: written by thread 0 behind a barrier)
+    if (p.al_inject) {
+      for (int c = tid; c < S; c += NCONS) row[c] = __ldg(p.al_inject + (size_t)T * S + c);
+    } else if (as->frame == 0) {
+      for (int c = tid; c < S; c += NCONS) row[c] = __ldcg(p.al_prefill + (size_t)r * AL_CAP + c);
+    } else {
+      const unsigned fl = ll_flag(it - 1, L, p.al_layer, LLP_ALIGN);
+      if (tid < T3_NH * MAXS * 2) {
+        const unsigned long long* wp = p.ll + LL_ALML + tid;
+        unsigned long long w;
+        unsigned spins = 0; unsigned long long t0 = 0;
+        for (;;) { w = ll_ld1(wp); if (ll_ok(w, fl)) break; if (poll_timeout(spins, t0, ctl, p.st)) break; }
+        ml[tid] = ll_val(w);
+      }
+      cbar();
+      if (tid < T3_NH) {
+        float Mt = -INFINITY;
+#pragma unroll
+        for (int s = 0; s < MAXS; ++s) Mt = fmaxf(Mt, ml[(tid * MAXS + s) * 2]);
+        float Lt = 0.f;
+#pragma unroll
+        for (int s = 0; s < MAXS; ++s) {
+          const float ms = ml[(tid * MAXS + s) * 2];
+          Lt += (ms == -INFINITY) ? 0.f : ml[(tid * MAXS + s) * 2 + 1] * __expf(ms - Mt);
+        }
+        ml[T3_NH * MAXS * 2 + tid * 2] = Mt;
+        ml[T3_NH * MAXS * 2 + tid * 2 + 1] = 1.0f / (Lt * (float)T3_NH);
+      }
+      cbar();
+      const int chunk = (pos0 - 1 + MAXS - 1) / MAXS;      // KV split size of the forward pass that produced the logits
+      for (int c = tid; c < S; c += NCONS) {
+        const int s = min((p.al_i + c) / chunk, MAXS - 1);
+        float acc = 0.f;
+        for (int h = 0; h < T3_NH; ++h) {
+          const unsigned long long* wp = p.ll + LL_AL + (size_t)h * AL_CAP + c;
+          unsigned long long w;
+          unsigned spins = 0; unsigned long long t0 = 0;
+          for (;;) { w = ll_ld1(wp); if (ll_ok(w, fl)) break; if (poll_timeout(spins, t0, ctl, p.st)) break; }
+          acc += ll_val(w) * __expf(ml[(h * MAXS + s) * 2] - ml[T3_NH * MAXS * 2 + h * 2]) * ml[T3_NH * MAXS * 2 + h * 2 + 1];
+        }
+        row[c] = acc;
+      }
+    }
+    cbar();
+    if (p.al_rows_out)
+      for (int c = tid; c < S; c += NCONS) p.al_rows_out[(size_t)T * S + c] = row[c];
+    // monotonic masking (:107), arg-max (first index on ties), max over columns [:S-5]
+    const int frame = as->frame;
+    float amax = -INFINITY, rmax = -INFINITY; int aidx = 0x7fffffff;
+    for (int c = tid; c < S; c += NCONS) {
+      const float v = (c >= frame + 1) ? 0.f : row[c];
+      row[c] = v;
+      if (v > amax) { amax = v; aidx = c; }
+      if (c < S - 5) rmax = fmaxf(rmax, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float m2 = __shfl_xor_sync(0xffffffffu, amax, o);
+      const int i2 = __shfl_xor_sync(0xffffffffu, aidx, o);
+      if (m2 > amax || (m2 == amax && i2 < aidx)) { amax = m2; aidx = i2; }
+      rmax = fmaxf(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+    }
+    cbar();
+    if (lane == 0) { rs[warp] = amax; ri[warp] = aidx; rs[NCONS_WARPS + warp] = rmax; }
+    cbar();
+    if (tid == 0) {
+      float A = rs[0], R = rs[NCONS_WARPS]; int I = ri[0];
+      for (int w = 1; w < NCONS_WARPS; ++w) {
+        if (rs[w] > A || (rs[w] == A && ri[w] < I)) { A = rs[w]; I = ri[w]; }
+        R = fmaxf(R, rs[NCONS_WARPS + w]);
+      }
+      as->T = T + 1;
+      as->last2_prev = as->last2_cur;
+      as->last2_cur = fmaxf(row[S - 2], row[S - 1]);
+      float f4 = as->first4;
+      for (int c = 0; c < 4 && c < S; ++c) f4 = fmaxf(f4, row[c]);
+      as->first4 = f4;
+      if (as->complete) {                    // rows at index >= completed_at
+        as->tail0 += row[S - 3]; as->tail1 += row[S - 2]; as->tail2 += row[S - 1];
+        if (S > 5) as->rep += R;
+      }
+      if (r == nrows - 1) {
+        const int cur = I, d = cur - as->text_pos;
+        if (d > -4 && d < 7) as->text_pos = cur;                                   // not a discontinuity (:118-121)
+        const float a2 = fmaxf(as->last2_prev, as->last2_cur);
+        const bool false_start = !as->started && (a2 > 0.1f || as->first4 < 0.5f);   // (:126)
+        as->started = false_start ? 0 : 1;
+        if (as->text_pos >= S - 3) as->complete = 1;                               // (:131)
+        const bool long_tail = as->complete && fmaxf(as->tail0, fmaxf(as->tail1, as->tail2)) >= 10.f;   // (:140)
+        const bool repetition = as->complete && as->rep > 5.f;                     // (:143)
+        as->force = (long_tail || repetition) ? 1 : 0;
+        as->suppress = (cur < S - 3) ? 1 : 0;                                      // (:153)
+        as->frame = frame + 1;
+        if (p.al_out) {
+          p.al_out[it * 4 + 0] = as->text_pos;
+          p.al_out[it * 4 + 1] = as->started | (as->complete << 1) | (as->force << 2) | (as->suppress << 3);
+          p.al_out[it * 4 + 2] = cur;
+          p.al_out[it * 4 + 3] = as->T;
+        }
+      }
+    }
+    cbar();
+  }
+}
+
 // Processes the pending logits of the CFG pair and emits token `it`.  All NCONS threads of CTA 0.
 #ifdef T3_PROFILE
 #define T3_SPROF(k) do { if (p.prof && threadIdx.x == 0 && it == p.prof_it) p.prof[300 + (k)] = gtime_ns(); } while (0)
@@ -999,8 +1156,15 @@ __device__ __forceinline__ unsigned f2ord(float f) {
 #define T3_SPROF(k) do {} while (0)
 #endif
 __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, float* sl, unsigned* seen, Ctl* ctl, int warp,
-                             int lane) {
+                             int lane, int pos0, AlState* as) {
   const int tid = threadIdx.x, L = p.n_layers;
+  bool al_force = false, al_sup = false;
+  if (p.al_layer >= 0) {
+    align_step(p, it, pos0, sl, as, ctl, warp, lane);
+    al_force = as->force != 0; al_sup = as->suppress != 0;
+    cbar();          // every thread has its copy of the decision before sl[] is reused for the logits
+  }
+  const bool al_any = al_force || al_sup;
   float* rs = sl + VOCAB_PAD;          // reduction scratch (64 floats)
   int* ri = reinterpret_cast<int*>(rs + 32);
   const CbxSampleParams& sp = p.sp;
@@ -1062,7 +1226,14 @@ __device__ __noinline__ void sample_phase(const T3Params& p, int it, int n_gen, 
           lout[((size_t)it * (1 + B2)) * T3_VOCAB + i] = c;
           if (B2) lout[((size_t)it * 2 + 1) * T3_VOCAB + i] = u;
         }
-        float x = cfg ? c + cfgw * (c - u) : c;
+        float cc = c, uu = u;
+        // alignment analyzer: both CFG rows get the reference's overrides (alignment_stream_analyzer.py:146-153); the
+        // suppression comes second and wins, as there
+        if (al_any) {
+          if (al_force) cc = uu = (i == STOP_SPEECH) ? 32768.f : -32768.f;
+          if (al_sup && i == STOP_SPEECH) cc = uu = -32768.f;
+        }
+        float x = cfg ? cc + cfgw * (cc - uu) : cc;
         if (temp != 1.0f) x = x / temp;
         if ((seen[i >> 5] >> (i & 31)) & 1u) x = (x < 0.f) ? x * rpen : x / rpen;
         sl[i] = x;
@@ -1189,6 +1360,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   float* scr = reinterpret_cast<float*>(smem + SMEM_SCRATCH);
   unsigned* seen = reinterpret_cast<unsigned*>(smem + SMEM_SEEN);
   T3Params* ps = reinterpret_cast<T3Params*>(smem + SMEM_PARAMS);
+  AlState* al_s = reinterpret_cast<AlState*>(smem + SMEM_SSQ + 128);      // second half of the ssq area (the sums use 128 B)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = gridDim.x, c = blockIdx.x;
@@ -1202,6 +1374,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   sm.head_from_iter = (p.mode == 1) ? 0 : n_iters - 1;
   sm.n_iters = n_iters;
   if (tid == 32) *ps = p;
+  if (tid == 64 && blockIdx.x == 0 && p.al_layer >= 0) *al_s = *p.al_state;
   if (tid == 0) {
     for (int s = 0; s < NSLOT; ++s) mbar_init(&full[s], 1);
     ctl->abort = 0; ctl->next_idx = 0; ctl->next_iter = 0;
@@ -1266,7 +1439,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
   for (int it = 0; it < n_iters; ++it) {
     if (p.mode == 1) {
       T3_PROF();
-      if (c == 0) sample_phase(*ps, it, n_gen, scr, seen, ctl, warp, lane);
+      if (c == 0) sample_phase(*ps, it, n_gen, scr, seen, ctl, warp, lane, pos0, al_s);
       // control word of this iteration: token id | stop bit
       const unsigned fl = ll_flag(it, L, 0, LLP_EMB);
       unsigned long long w;
@@ -1480,6 +1653,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) t3_megakernel(const T3Params p) {
     p.st->n_gen = n_gen;
     // a device error (watchdog) reaches the host in the same word as the token count: -(n + 1)
     if (p.mode == 1 && p.n_out) *p.n_out = (ctl->abort || __ldcg(&p.st->err)) ? -(n_done + 1) : n_done;
+    if (p.al_layer >= 0) *p.al_state = *al_s;
   }
   __syncthreads();
   // drain: every copy in flight must have landed before the CTA may exit (early stop on EOS / abort)
@@ -1505,6 +1679,10 @@ struct cbx_t3 {
   T3Params base;        // pointers to owned scratch, filled at create
   void* slab;           // one allocation for all scratch
   int B;                // rows of the current utterance
+  // alignment analyzer configuration (cbx_t3_set_alignment); layer < 0 = off
+  int al_layer, al_i, al_n, al_rows0;
+  const float* al_inject; float* al_rows_out; int* al_out;
+  float* al_prefill; AlState* al_state;
   int host_pos;         // upper bound of the cache length after the calls issued so far (EOS may stop a launch early)
   int host_gen;         // same for the generated-token count
   long long launches;
@@ -1557,7 +1735,8 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   CBX_CHECK(coop, "cbx_t3_create: device lacks cooperative launch");
 
   cbx_t3* h = new cbx_t3();
-  h->cfg = *cfg; h->w = *w; h->G = G; h->B = 2; h->host_pos = 0; h->host_gen = 0; h->launches = 0; h->prof = nullptr; h->prof_it = -1;
+  h->cfg = *cfg; h->w = *w; h->G = G; h->B = 2; h->host_pos = 0; h->host_gen = 0; h->launches = 0;
+  h->al_layer = -1; h->al_i = 0; h->al_n = 0; h->al_rows0 = 0; h->al_inject = nullptr; h->al_rows_out = nullptr; h->al_out = nullptr; h->prof = nullptr; h->prof_it = -1;
   const size_t kvel = cfg->kv_fp32 ? 4 : 2;
   const size_t kv_bytes = (size_t)cfg->n_layers * 2 * T3_NH * cfg->max_pos * T3_HD * kvel;
   size_t off = 0;
@@ -1566,6 +1745,7 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   const size_t o_ll = take(LL_WORDS * 8);
   const size_t o_logits = take(sizeof(float) * 2 * T3_VOCAB);
   const size_t o_st = take(256), o_seen = take(VOCAB_PAD);
+  const size_t o_alp = take((size_t)2 * AL_CAP * sizeof(float)), o_als = take(sizeof(AlState));
   const size_t o_ws = w->wplain ? take(cbx::t3_prefill_workspace_bytes(cfg->max_pos)) : 0;
   const size_t o_pfe = w->wplain ? take((size_t)2 * cfg->max_pos * T3_H * sizeof(float)) : 0;
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
@@ -1588,6 +1768,9 @@ extern "C" int cbx_t3_create(const CbxT3Config* cfg, const CbxT3Weights* w, cbx_
   p.logits = reinterpret_cast<float*>(s + o_logits);
   p.st = reinterpret_cast<T3State*>(s + o_st);
   p.seen = s + o_seen;
+  p.al_layer = -1;
+  h->al_prefill = reinterpret_cast<float*>(s + o_alp);
+  h->al_state = reinterpret_cast<AlState*>(s + o_als);
   h->prefill_ws = w->wplain ? s + o_ws : nullptr;
   h->pf_embeds = w->wplain ? reinterpret_cast<float*>(s + o_pfe) : nullptr;
   h->cap_stream = nullptr;
@@ -1628,6 +1811,13 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
   CBX_CUDA(cudaMemsetAsync(p.seen, 0, VOCAB_PAD, st));
   CBX_CUDA(cudaMemsetAsync(p.seen + 6561, 1, 1, st));
   p.mode = 0; p.B = B; p.embeds = embeds; p.P = P;
+  if (h->al_layer >= 0) {
+    h->al_rows0 = P - (h->al_i + h->al_n);        // query rows of the prompt behind the text: BOS (+ the doubled BOS)
+    CBX_CHECK(h->al_rows0 >= 1 && h->al_rows0 <= 2, "cbx_t3_prefill: alignment analyzer: %d prompt rows after the text slice [%d, %d) "
+              "(expected 1 or 2: P = %d)", h->al_rows0, h->al_i, h->al_i + h->al_n, P);
+    static const AlState al_init = {0, 0, 0, 0, 0, -INFINITY, -INFINITY, -INFINITY, 0.f, 0.f, 0.f, 0.f, 0, 0, 0, 0};
+    CBX_CUDA(cudaMemcpyAsync(h->al_state, &al_init, sizeof(AlState), cudaMemcpyHostToDevice, st));
+  }
   static const bool force_mega = [] { const char* v = getenv("CBX_T3_PREFILL"); return v && v[0] == 'm'; }();
   if (h->prefill_ws && !force_mega) {
     // the prompt through each weight matrix once (tcgen05 GEMMs); leaves the slab, the position counter and the
@@ -1637,10 +1827,11 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
     a.wplain = h->w.wplain; a.ln1 = p.ln1; a.ln2 = p.ln2; a.final_norm = p.final_norm;
     a.rope_cos = p.rope_cos; a.rope_sin = p.rope_sin; a.kcache = p.kcache; a.vcache = p.vcache;
     a.logits = p.logits; a.state = reinterpret_cast<int*>(p.st); a.workspace = h->prefill_ws;
+    a.al_layer = h->al_layer; a.al_i = h->al_i; a.al_n = h->al_n; a.al_rows0 = h->al_rows0; a.al_out = h->al_prefill; a.al_cap = AL_CAP;
     h->launches += 1 + h->cfg.n_layers * 8 + 2;
     static const bool use_graph = [] { const char* v = getenv("CBX_T3_PREFILL_GRAPH"); return !(v && v[0] == '0'); }();
     cbx_t3::PrefillGraph* g = nullptr;
-    if (use_graph) {
+    if (use_graph && h->al_layer < 0) {          // analyzer runs prefill eagerly (its extra kernel is not part of the cached graphs)
       for (auto& c : h->pf_graphs) if (c.B == B && c.P == P) { g = &c; break; }
       if (!g) {
         if (h->pf_graphs.size() >= 32) {            // bound the cache: drop the oldest entry
@@ -1674,6 +1865,7 @@ extern "C" int cbx_t3_prefill(cbx_t3* h, const float* embeds, int B, int P, void
     CBX_CUDA(cudaGraphLaunch(g->exec, st));
     return CBX_OK;
   }
+  CBX_CHECK(h->al_layer < 0, "cbx_t3_prefill: the alignment analyzer needs the GEMM prefill (CbxT3Weights.wplain)");
   return t3_launch(h, p, st);
 }
 
@@ -1696,7 +1888,30 @@ extern "C" int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_t
   p.mode = 1; p.B = h->B; p.sp = *sp; p.max_new = max_new_tokens; p.forced = forced_tokens;
   p.tokens_out = tokens_out; p.n_out = n_out; p.logits_out = logits_out;
   p.prof = h->prof; p.prof_it = h->prof_it;
+  if (h->al_layer >= 0) {
+    CBX_CHECK(h->host_gen == max_new_tokens, "cbx_t3_decode: with the alignment analyzer the decode launch must follow the prefill directly "
+              "(the attention row of an earlier launch's last step is gone)");
+    p.al_layer = h->al_layer; p.al_i = h->al_i; p.al_n = h->al_n; p.al_rows0 = h->al_rows0;
+    p.al_prefill = h->al_prefill; p.al_inject = h->al_inject; p.al_rows_out = h->al_rows_out; p.al_out = h->al_out;
+    p.al_state = h->al_state;
+  }
   return t3_launch(h, p, st);
+}
+
+extern "C" int cbx_t3_set_alignment(cbx_t3* h, int layer, int text_begin, int n_text, const float* inject_rows, float* rows_out,
+                                    int32_t* decisions_out) {
+  CBX_CHECK(h, "cbx_t3_set_alignment: null handle");
+  if (layer < 0) { h->al_layer = -1; return CBX_OK; }
+  CBX_CHECK(layer < h->cfg.n_layers, "cbx_t3_set_alignment: layer %d >= n_layers %d", layer, h->cfg.n_layers);
+  CBX_CHECK(!h->cfg.kv_fp32, "cbx_t3_set_alignment: the analyzer reads the tile attention path (bf16 KV slab only)");
+  CBX_CHECK(h->cfg.max_pos <= MAXS * ATT_TP, "cbx_t3_set_alignment: max_pos %d exceeds the tile attention path (%d positions)",
+            h->cfg.max_pos, MAXS * ATT_TP);
+  CBX_CHECK(h->prefill_ws, "cbx_t3_set_alignment: needs the GEMM prefill (CbxT3Weights.wplain)");
+  CBX_CHECK(n_text >= 6 && n_text <= AL_CAP && text_begin >= 0, "cbx_t3_set_alignment: text slice [%d, %d + %d) unsupported (6..%d columns)",
+            text_begin, text_begin, n_text, AL_CAP);
+  h->al_layer = layer; h->al_i = text_begin; h->al_n = n_text;
+  h->al_inject = inject_rows; h->al_rows_out = rows_out; h->al_out = decisions_out;
+  return CBX_OK;
 }
 
 extern "C" int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it) {

@@ -169,6 +169,41 @@ __global__ void __launch_bounds__(256) k_head(const float* __restrict__ x, int P
 
 __global__ void k_set_pos(int* st, int pos) { st[0] = pos; st[1] = 0; st[2] = 0; }
 
+// Alignment analyzer rows of the prompt (alignment_stream_analyzer.py:73-75,96-101): softmax(q k^T) of CFG row 0 at query
+// position P - rows0 + blockIdx.x, averaged over the 16 heads, for the text columns.  qkv holds q (RoPE, pre-scaled by
+// 1/8) and k (RoPE, rounded like the slab) of this layer.  512 threads = 16 warps = heads for the softmax statistics.
+__global__ void __launch_bounds__(512) k_align_rows(const float* __restrict__ qkv, int P, int rows0, int al_i, int al_n,
+                                                    float* __restrict__ out, int cap) {
+  __shared__ float qs[NH][HD];
+  __shared__ float ml[NH][2];
+  const int r = blockIdx.x, qi = P - rows0 + r, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  qs[warp][lane] = qkv[(size_t)qi * 3072 + warp * HD + lane];
+  qs[warp][lane + 32] = qkv[(size_t)qi * 3072 + warp * HD + lane + 32];
+  __syncthreads();
+  auto score = [&](int h, int k) {
+    const float* kr = qkv + (size_t)k * 3072 + 1024 + h * HD;
+    float s = 0.f;
+#pragma unroll 16
+    for (int d = 0; d < HD; ++d) s += qs[h][d] * kr[d];
+    return s;
+  };
+  float m = -INFINITY;
+  for (int k = lane; k <= qi; k += 32) m = fmaxf(m, score(warp, k));
+  m = warp_max(m);
+  float l = 0.f;
+  for (int k = lane; k <= qi; k += 32) l += __expf(score(warp, k) - m);
+  l = warp_sum(l);
+  if (lane == 0) { ml[warp][0] = m; ml[warp][1] = 1.0f / (l * (float)NH); }
+  __syncthreads();
+  for (int c = tid; c < al_n; c += 512) {
+    const int k = al_i + c;
+    float acc = 0.f;
+    if (k <= qi)
+      for (int h = 0; h < NH; ++h) acc += __expf(score(h, k) - ml[h][0]) * ml[h][1];
+    out[(size_t)r * cap + c] = acc;
+  }
+}
+
 }  // namespace
 
 size_t t3_prefill_workspace_bytes(int max_pos) {
@@ -205,6 +240,8 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
       k_rope_kv<__nv_bfloat16><<<dim3(a.P, a.B), 1024, 0, st>>>(qkv, a.P, 0, a.rope_cos, a.rope_sin,
                                                                static_cast<__nv_bfloat16*>(a.kcache),
                                                                static_cast<__nv_bfloat16*>(a.vcache), l, a.max_pos);
+    if (l == a.al_layer && a.al_out)
+      k_align_rows<<<a.al_rows0, 512, 0, st>>>(qkv, a.P, a.al_rows0, a.al_i, a.al_n, a.al_out, a.al_cap);
     k_attn_prefill<<<dim3((a.P + QT - 1) / QT, NH, a.B), 256, 0, st>>>(qkv, a.P, hl, hl_plane);
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
     if (gemm_make_hilo(&d, hl, H, hl_plane, wo, rows, H, H, e) || gemm_launch(d, st)) return CBX_ERR;

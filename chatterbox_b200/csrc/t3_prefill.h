@@ -16,6 +16,10 @@ struct T3PrefillArgs {
   int logits_ld;             // floats between the two rows (0 = 8194)
   int* state;                // {pos, n_gen, stop, err}
   void* workspace;           // t3_prefill_workspace_bytes(max_pos)
+  // alignment analyzer (al_layer < 0: off): head-mean attention of CFG row 0 over text columns [al_i, al_i + al_n) for the
+  // last al_rows0 prompt positions at layer al_layer -> al_out [al_rows0][al_cap]   (alignment_stream_analyzer.py:96-101)
+  int al_layer, al_i, al_n, al_rows0, al_cap;
+  float* al_out;
 };
 
 size_t t3_prefill_workspace_bytes(int max_pos);

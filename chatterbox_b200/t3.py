@@ -165,18 +165,24 @@ class T3:
                   stop_on_eos=True, do_sample=True, temperature=0.8, min_p=0.05, top_p=1.00,
                   length_penalty=1.0, repetition_penalty=1.2, cfg_weight=0,
                   forced_tokens: Optional[torch.Tensor] = None, return_logits: bool = False,
-                  seed: Optional[int] = None):
+                  seed: Optional[int] = None, alignment_analyzer: bool = False, alignment_layer_idx: int = 9,
+                  alignment_inject: Optional[torch.Tensor] = None, alignment_debug: bool = False):
         """Reference signature (t3.py:203-225) plus three keyword extensions used by the parity tests:
         `forced_tokens` (teacher forcing), `return_logits` (keep raw per-step logits in
         `self.last_logits`), `seed` (Philox seed).  `do_sample=False` selects greedy argmax (the
-        reference ignores the flag and always samples)."""
+        reference ignores the flag and always samples).
+        `alignment_analyzer=True` runs `AlignmentStreamAnalyzer` (inference/alignment_stream_analyzer.py:29-154; the
+        reference constructs the backend with `alignment_stream_analyzer=None`, t3.py:260, and keeps the `step` call
+        commented out, t3_hf_backend.py:108-109) on the device: layer `alignment_layer_idx` head-mean attention over the
+        text positions, EOS forced / suppressed before every token is sampled.  `alignment_debug=True` keeps the rows and
+        per-step decisions in `self.last_alignment`; `alignment_inject` (rows, n_text) replaces the measured rows."""
         assert prepend_prompt_speech_tokens is None, "not implemented"
         _ensure_BOT_EOT(text_tokens, self.hp)
         text_tokens = torch.atleast_2d(text_tokens).to(dtype=torch.long, device=self.device)
         if initial_speech_tokens is None:
             initial_speech_tokens = self.hp.start_speech_token * torch.ones_like(text_tokens[:, :1])
-        embeds, _ = self.prepare_input_embeds(t3_cond=t3_cond, text_tokens=text_tokens,
-                                              speech_tokens=initial_speech_tokens, cfg_weight=cfg_weight)
+        embeds, len_cond = self.prepare_input_embeds(t3_cond=t3_cond, text_tokens=text_tokens,
+                                                     speech_tokens=initial_speech_tokens, cfg_weight=cfg_weight)
         bos = (self.fe["speech_emb.weight"][self.hp.start_speech_token] +
                self.fe["speech_pos_emb.emb.weight"][0])[None, None]
         if cfg_weight > 0:   # the reference appends BOS a second time (t3.py:284-295)
@@ -202,6 +208,21 @@ class T3:
         sp = _lib.CbxSampleParams(float(cfg_weight), float(temperature), float(repetition_penalty), float(min_p),
                                   float(top_p), 0 if do_sample else 1, 1 if stop_on_eos else 0,
                                   int(seed if seed is not None else torch.initial_seed()) & (2 ** 64 - 1))
+        al_rows = al_dec = al_inj = None
+        if alignment_analyzer:
+            n_text = int(text_tokens.shape[1])
+            if alignment_inject is not None:
+                al_inj = alignment_inject.to(self.device, torch.float32).contiguous()
+                assert al_inj.shape[1] == n_text and al_inj.shape[0] >= max_new_tokens + 1
+            if alignment_debug:
+                al_rows = torch.zeros(max_new_tokens + 2, n_text, dtype=torch.float32, device=self.device)
+                al_dec = torch.zeros(max_new_tokens, 4, dtype=torch.int32, device=self.device)
+            _lib.check(self._lib.cbx_t3_set_alignment(self._h, int(alignment_layer_idx), int(len_cond), n_text,
+                                                      al_inj.data_ptr() if al_inj is not None else None,
+                                                      al_rows.data_ptr() if al_rows is not None else None,
+                                                      al_dec.data_ptr() if al_dec is not None else None))
+        else:
+            _lib.check(self._lib.cbx_t3_set_alignment(self._h, -1, 0, 0, None, None, None))
         ev = None
         if self.record_events:
             ev = {k: torch.cuda.Event(enable_timing=True) for k in ("prefill0", "decode0", "decode1")}
@@ -221,6 +242,7 @@ class T3:
         if n < 0:
             raise _lib.CbxError(f"T3 megakernel reported a device error after {-n - 1} tokens (watchdog timeout)")
         self.last_logits = logits[:n] if logits is not None else None
+        self.last_alignment = dict(rows=al_rows, decisions=al_dec[:n]) if al_dec is not None else None
         return tokens[:n].to(torch.long)[None]
 
     def state(self):

@@ -163,7 +163,8 @@ class ChatterboxTTS:
 
     def generate(self, text=None, repetition_penalty=1.2, min_p=0.05, top_p=1.0, audio_prompt_path=None, exaggeration=0.5,
                  cfg_weight=0.5, temperature=0.8, *, text_tokens: Optional[torch.Tensor] = None, do_sample: bool = True,
-                 max_new_tokens: int = 1000, stop_on_eos: bool = True, seed: Optional[int] = None):
+                 max_new_tokens: int = 1000, stop_on_eos: bool = True, seed: Optional[int] = None,
+                 alignment_analyzer: bool = False):
         if audio_prompt_path:
             self.prepare_conditionals(audio_prompt_path, exaggeration=exaggeration)
         else:
@@ -188,7 +189,8 @@ class ChatterboxTTS:
             speech_tokens = self.t3.inference(t3_cond=cond, text_tokens=text_tokens, max_new_tokens=max_new_tokens,
                                               temperature=temperature, cfg_weight=cfg_weight,
                                               repetition_penalty=repetition_penalty, min_p=min_p, top_p=top_p,
-                                              do_sample=do_sample, stop_on_eos=stop_on_eos, seed=seed)
+                                              do_sample=do_sample, stop_on_eos=stop_on_eos, seed=seed,
+                                              alignment_analyzer=alignment_analyzer)
             speech_tokens = drop_invalid_tokens(speech_tokens[0])
             speech_tokens = speech_tokens[speech_tokens < SPEECH_VOCAB_SIZE]
             self.last_speech_tokens = speech_tokens

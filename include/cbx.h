@@ -90,6 +90,19 @@ int cbx_t3_decode(cbx_t3* h, const CbxSampleParams* sp, int max_new_tokens, cons
  * and the number of kernel launches issued through this handle. */
 int cbx_t3_state(cbx_t3* h, int32_t* pos, int32_t* n_gen, int32_t* err, int64_t* launches);
 
+/* AlignmentStreamAnalyzer (src/chatterbox/models/t3/inference/alignment_stream_analyzer.py:29-154; BASELINE config 5): call
+ * before cbx_t3_prefill.  layer >= 0 (the reference uses 9) turns it on for the following utterances: the head-mean attention
+ * of the conditional row at that layer over the text positions [text_begin, text_begin + n_text) is taken from the prompt
+ * prefill and from every decode step's attention phase, the step() state machine runs on the device before each token is
+ * sampled, and the EOS logit (6562) is forced / suppressed as there (:141-153).  layer < 0 turns it off.  Needs the bf16 KV
+ * slab, the GEMM prefill (wplain) and max_pos <= 2176; one decode launch per utterance.  Optional device buffers: inject_rows
+ * [rows][n_text] replaces the measured attention (tests of the state machine), rows_out [rows][n_text] receives every row
+ * consumed (rows = prompt rows + one per step), decisions_out [max_new][4] = {text position, started | complete << 1 |
+ * forced << 2 | suppressed << 3, arg-max column, rows so far}.  (The reference ships the call disabled,
+ * t3_hf_backend.py:108-109; eos_idx here is the stop-speech token as upstream Chatterbox passes it.) */
+int cbx_t3_set_alignment(cbx_t3* h, int layer, int text_begin, int n_text, const float* inject_rows, float* rows_out,
+                         int32_t* decisions_out);
+
 /* Debug aid: CTA 0 writes %globaltimer (ns) after every phase of decode iteration `it` into
  * stamps[] (device, >= 512 entries); NULL disables.  The stamps are compiled in only with
  * -DT3_PROFILE (phases) or -DT3_TIMELINE (every CTA, stamps[] >= 1024 + 1024 * SMs entries): in the
