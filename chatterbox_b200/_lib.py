@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcbx.so")
+LIB_PATH = os.environ.get("CBX_LIBCBX") or os.path.join(HERE, "libcbx.so")     # CBX_LIBCBX: A/B another build of the library
 
 
 class CbxError(RuntimeError):

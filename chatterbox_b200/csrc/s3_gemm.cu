@@ -133,7 +133,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   // split-K over a cluster (1, 1, S): CTA `rank` accumulates K panels [kb0, kb0 + nkb) of the tile into its own
   // TMEM, the partial tiles meet in distributed shared memory and each CTA finishes 128 / S rows of the tile
   const int S = p.ksplit, rank = blockIdx.z;
-  const int kpb = p.K / BK, nkb_all = p.taps * kpb;
+  // hi/lo mode (T3): a k-block is ONE weight panel and BOTH activation planes (hi, lo) multiplied against it
+  const int kpb = p.K / BK, nkb_all = p.hilo ? kpb : p.taps * kpb;
+  const uint32_t w_bytes = (uint32_t)p.n_tile * BK * 2;
   const int nkb = nkb_all / S + (rank < nkb_all % S ? 1 : 0);                 // >= 1 (host: nkb_all >= S)
   const int kb0 = rank * (nkb_all / S) + min(rank, nkb_all % S);
   const int row_base = rank * (BM / S), rpw = 8 / S;        // epilogue rows of this CTA / per warp
@@ -189,13 +191,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
 
   if (warp == 0) {
     if (lane == 0) {
-      const uint32_t tx = A_BYTES + p.n_tile * BK * 2;
+      const uint32_t tx = (p.hilo ? 2 : 1) * A_BYTES + w_bytes;
       const int npre = nkb < NS ? nkb : NS;
       // weight panels of the first ring pass: issued before the PDL wait (they do not depend on the previous kernel)
       for (int i = 0; i < npre; ++i) {
         const int kb = kb0 + i;
         mbar_arrive_expect_tx(&full[i], tx);
-        tma_load_3d(smem + i * SB + A_BYTES, &p.tmW, &full[i], (p.hilo ? kb % kpb : kb) * BK, n0, 0);
+        tma_load_3d(smem + i * SB + A_BYTES, &p.tmW, &full[i], kb * BK, n0, 0);
       }
       pdl_wait();
       for (int i = 0; i < nkb; ++i) {
@@ -205,10 +207,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         if (i >= npre) {
           mbar_wait_spin(&empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&full[s], tx);
-          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], (p.hilo ? kk : kb) * BK, n0, 0);
+          tma_load_3d(sa + A_BYTES, &p.tmW, &full[s], kb * BK, n0, 0);
         }
-        if (p.hilo) tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0, tap);      // plane `tap` of A against the same W panel
-        else tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
+        if (p.hilo) {              // planes 0 (hi) and 1 (lo) of A; the lo tile sits behind the W tile
+          tma_load_3d(sa, &p.tmA, &full[s], kb * BK, t0, 0);
+          tma_load_3d(sa + A_BYTES + w_bytes, &p.tmA, &full[s], kb * BK, t0, 1);
+        } else tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
       }
       GEMM_STAMP(2);
     }
@@ -224,6 +228,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k)    // +32 bytes per K=16 step inside the 128-byte swizzle row
           umma_bf16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+        if (p.hilo) {
+          const uint64_t da1 = umma_desc_k128(sa + A_BYTES + w_bytes);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) umma_bf16(tmem_base, da1 + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, 1u);
+        }
         umma_commit(&empty[s]);
       }
       umma_commit(accum_bar);
@@ -241,16 +250,37 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       par[PAR_B2 * 256 + c] = e.out_ln ? __ldg(e.ln2_b + n) : 0.f;
       par[PAR_ALPHA * 256 + c] = e.snake_alpha ? __ldg(e.snake_alpha + n) : 1.f;
     }
-  } else {
-    // ===== epilogue, phase 1 (warps 2-5): drain the accumulator, thread <-> row (TMEM lane), to an fp32 tile in
-    // shared memory (the operand ring is idle once accum_bar fires) =====
+  }
+  __syncwarp();                                   // warps 0 / 1: lane 0 rejoins
+  {
+    // ===== epilogue, phase 1 (ALL 16 warps): drain the accumulator, thread <-> row (TMEM lane), to an fp32 tile in
+    // shared memory (the operand ring is idle once accum_bar fires).  A warp may touch the 32 TMEM lanes of its
+    // quarter (warp % 4) only, so the four warps of a quarter take every fourth 16-column chunk each. =====
     const int q = warp & 3, row = q * 32 + lane;
     const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
+    // GEMM_DRAIN: 0 = warps 2-5 only (round 1); 1 = all warps, each spinning on the accumulator barrier; 2 (default) = all
+    // warps, but only warps 2-5 wait on the mbarrier while the others sleep in a CTA barrier (no issue slots taken from
+    // the producer / MMA lanes during the main loop)
+#ifndef GEMM_DRAIN
+#define GEMM_DRAIN 2
+#endif
+#if GEMM_DRAIN == 2
+    if (warp >= 2 && warp <= 5) mbar_wait_spin(accum_bar, 0);
+    __syncthreads();
+#elif GEMM_DRAIN == 1
     mbar_wait_spin(accum_bar, 0);
+#else
+    if (warp >= 2 && warp <= 5) mbar_wait_spin(accum_bar, 0);
+#endif
     tc_fence_after();
     if (threadIdx.x == 64) GEMM_STAMP(4);
     const int nch = p.n_tile / 16;
+#if GEMM_DRAIN == 0
+    if (warp >= 2 && warp <= 5)
     for (int c = 0; c < nch; ++c) {
+#else
+    for (int c = warp >> 2; c < nch; c += 4) {
+#endif
       float v[16];
       tmem_ld16(trow + c * 16, v);
       float4* dst = reinterpret_cast<float4*>(tile + (size_t)row * pitch + c * 16);
@@ -260,7 +290,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
     tc_fence_before();
     if (threadIdx.x == 64) GEMM_STAMP(5);
   }
-  __syncwarp();                                   // warps 0 / 1: lane 0 rejoins before the aligned barrier
+  __syncwarp();
   if (S > 1) cluster_sync_all(); else __syncthreads();
   if (threadIdx.x == 64) GEMM_STAMP(8);
   // ===== epilogue, phase 2 (all 16 warps): warp <-> 8 rows, lanes across float4 column groups (lane, lane + 32),
@@ -544,9 +574,9 @@ int gemm_make_hilo_ex(GemmDesc* d, const __nv_bfloat16* A, int lda, long long pl
   CBX_CHECK(N_w >= 1 && N_w <= N, "gemm_make_hilo: %d weight rows for %d output columns", N_w, N);
   CBX_CHECK(!epi.swiglu || n_tile == 256, "gemm_make_hilo: SwiGLU pairs the halves of a 256-column tile (N=%d)", N);
   CBX_CHECK(!epi.ln_g && !epi.out_ln, "gemm_make_hilo: no row LayerNorm on this path");
-  d->B = 1; d->L = M; d->N = N; d->K = K; d->taps = 2; d->n_tile = n_tile; d->epi = epi;
+  d->B = 1; d->L = M; d->N = N; d->K = K; d->taps = 1; d->n_tile = n_tile; d->epi = epi;
   d->dil = 0; d->pad = 0; d->M_out = M; d->hilo = 1;
-  const int tiles = ((M + BM - 1) / BM) * (N / n_tile), nkb_all = 2 * (K / BK);
+  const int tiles = ((M + BM - 1) / BM) * (N / n_tile), nkb_all = K / BK;
   d->ksplit = 1;
   if (ksplit_req > 0) {
     CBX_CHECK(ksplit_req <= MAX_SPLIT && (ksplit_req & (ksplit_req - 1)) == 0 && nkb_all >= ksplit_req,
@@ -626,7 +656,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;
   p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit; p.hilo = d.hilo;
   p.tiles_l = (d.M_out + BM - 1) / BM;
-  p.stage_bytes = (A_BYTES + d.n_tile * BK * 2 + 1023) / 1024 * 1024;      // 128-byte-swizzled tiles start 1024-byte aligned
+  p.stage_bytes = ((d.hilo ? 2 : 1) * A_BYTES + d.n_tile * BK * 2 + 1023) / 1024 * 1024;   // swizzled tiles start 1024-byte aligned
   p.nstages = (STAGES * STAGE_BYTES) / p.stage_bytes;
   if (p.nstages > MAX_STAGES) p.nstages = MAX_STAGES;
   p.e = d.epi;
