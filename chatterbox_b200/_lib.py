@@ -29,6 +29,11 @@ class CbxSampleParams(C.Structure):
                 ("seed", C.c_uint64)]
 
 
+class CbxT3FrontWeights(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("spkr_w", "spkr_b", "query", "norm_g", "norm_b", "wq", "bq", "wk", "bk", "wv", "bv",
+                                          "wo", "bo", "emotion_w", "text_emb", "text_pos_emb", "speech_emb", "speech_pos_emb")]
+
+
 class CbxT3BatchConfig(C.Structure):
     _fields_ = [("device", C.c_int32), ("n_layers", C.c_int32), ("n_slots", C.c_int32), ("max_pos", C.c_int32),
                 ("kv_fp32", C.c_int32), ("max_new_cap", C.c_int32), ("keep_logits", C.c_int32),
@@ -36,6 +41,11 @@ class CbxT3BatchConfig(C.Structure):
 
 
 class CbxCfmWeights(C.Structure):
+    _fields_ = [("bf16_blob", C.c_void_p), ("f32_blob", C.c_void_p), ("bf16_off", C.POINTER(C.c_int64)),
+                ("f32_off", C.POINTER(C.c_int64))]
+
+
+class CbxFlowFrontWeights(C.Structure):
     _fields_ = [("bf16_blob", C.c_void_p), ("f32_blob", C.c_void_p), ("bf16_off", C.POINTER(C.c_int64)),
                 ("f32_off", C.POINTER(C.c_int64))]
 
@@ -60,6 +70,11 @@ SYMBOLS = {
                                 C.c_void_p, C.c_void_p]),
     "cbx_t3_set_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "cbx_t3_set_alignment": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cbx_t3_front_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxT3FrontWeights), C.POINTER(C.c_void_p)]),
+    "cbx_t3_front_destroy": (C.c_int, [C.c_void_p]),
+    "cbx_t3_front": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                               C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "cbx_t3_front_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "cbx_t3_batch_create": (C.c_int, [C.POINTER(CbxT3BatchConfig), C.POINTER(CbxT3Weights), C.POINTER(C.c_void_p)]),
     "cbx_t3_batch_destroy": (C.c_int, [C.c_void_p]),
     "cbx_t3_batch_prefill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(CbxSampleParams), C.c_int,
@@ -83,6 +98,11 @@ SYMBOLS = {
                                       C.c_void_p]),
     "cbx_cfm_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "cbx_cfm_cache_sizes": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "cbx_flowfe_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxFlowFrontWeights), C.POINTER(C.c_void_p)]),
+    "cbx_flowfe_destroy": (C.c_int, [C.c_void_p]),
+    "cbx_flowfe_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cbx_flowfe_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "cbx_hift_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(CbxHiftWeights), C.POINTER(C.c_void_p)]),
     "cbx_hift_destroy": (C.c_int, [C.c_void_p]),
     "cbx_hift_f0": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),

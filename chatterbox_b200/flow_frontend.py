@@ -1,105 +1,112 @@
-"""Token -> (mu, spks, cond) front-end of the S3Gen flow module: the part of
-`CausalMaskedDiffWithXvec.inference` (reference src/chatterbox/models/s3gen/flow.py:236-282) that runs ONCE
-per utterance before the flow-matching loop — x-vector projection, token embedding, the CosyVoice2
-`UpsampleConformerEncoder` (transformer/upsample_encoder.py:237-304: linear embed + ESPnet rel-pos,
-pre-lookahead convs, 6 rel-pos attention blocks @25 Hz, nearest x2 upsample + conv, 4 blocks @50 Hz,
-final LayerNorm) and `encoder_proj`.
+"""Token -> (mu, spks, cond) front-end of the S3Gen flow module over the C-ABI (`cbx_flowfe_*`, csrc/s3_front.cu): the part
+of `CausalMaskedDiffWithXvec.inference` (reference src/chatterbox/models/s3gen/flow.py:236-282) that runs ONCE per utterance
+before the flow-matching loop — x-vector projection, token embedding, the CosyVoice2 `UpsampleConformerEncoder`
+(transformer/upsample_encoder.py:237-304) and `encoder_proj`.
 
-SURVEY.md §8f lists this as the first "next" row: it is adjacent to, not part of, the three kernel rows of
-the hot path.  In this round it is a functional restatement on plain torch ops that run on the GPU
-(library GEMMs), checked against the unmodified reference on CPU (tests/test_flow_frontend.py).
-State-dict keys are the reference's (`input_embedding.*`, `spk_embed_affine_layer.*`, `encoder.*`,
-`encoder_proj.*`).
+State-dict keys are the reference's (`input_embedding.*`, `spk_embed_affine_layer.*`, `encoder.*`, `encoder_proj.*`), so a
+real `s3gen.safetensors` packs through the same function.  There is no CPU path (the torch restatement of this stage lives in
+`oracle/flow_oracle.py`, test infrastructure only).
 """
 from __future__ import annotations
 
-import math
-from typing import Dict, Tuple
+import ctypes as C
+from typing import Dict, List
 
 import torch
-import torch.nn.functional as F
 
-HEADS, DK, D = 8, 64, 512
+from . import _lib
 
-
-def _rel_pos_emb(T: int, device, dtype) -> torch.Tensor:
-    """EspnetRelPositionalEncoding.position_encoding (embedding.py:224-294): (1, 2T-1, 512), relative
-    positions T-1 ... -(T-1)."""
-    pos = torch.arange(T - 1, -T, -1, dtype=torch.float32, device=device).unsqueeze(1)
-    div = torch.exp(torch.arange(0, D, 2, dtype=torch.float32, device=device) * -(math.log(10000.0) / D))
-    pe = torch.zeros(2 * T - 1, D, device=device)
-    pe[:, 0::2] = torch.sin(pos * div)
-    pe[:, 1::2] = torch.cos(pos * div)
-    return pe.unsqueeze(0).to(dtype)
+N_LAYERS0, N_LAYERS1 = 6, 4
 
 
-def _rel_shift(x: torch.Tensor) -> torch.Tensor:
-    """attention.py:225-247."""
-    b, h, t, n = x.shape
-    xp = torch.cat([torch.zeros(b, h, t, 1, device=x.device, dtype=x.dtype), x], dim=-1)
-    xp = xp.view(b, h, n + 1, t)
-    return xp[:, :, 1:].reshape(b, h, t, n)[:, :, :, : n // 2 + 1]
+def _conv_as_gemm(w: torch.Tensor) -> torch.Tensor:
+    """Conv1d weight (Cout, Cin, k) -> GEMM matrix [Cout][k * Cin] with column index tap * Cin + ci."""
+    return w.permute(0, 2, 1).reshape(w.shape[0], -1)
 
 
-def _layer(sd, p: str, x: torch.Tensor, pos_emb: torch.Tensor) -> torch.Tensor:
-    """ConformerEncoderLayer (encoder_layer.py:155-236) without macaron / conv module, pre-norm, eps 1e-12."""
-    B, T, _ = x.shape
-    lin = lambda n, v, bias=True: F.linear(v, sd[p + n + ".weight"], sd[p + n + ".bias"] if bias else None)
-    h = F.layer_norm(x, (D,), sd[p + "norm_mha.weight"], sd[p + "norm_mha.bias"], 1e-12)
-    q = lin("self_attn.linear_q", h).view(B, T, HEADS, DK)
-    k = lin("self_attn.linear_k", h).view(B, T, HEADS, DK).transpose(1, 2)
-    v = lin("self_attn.linear_v", h).view(B, T, HEADS, DK).transpose(1, 2)
-    pe = lin("self_attn.linear_pos", pos_emb, bias=False).view(1, -1, HEADS, DK).transpose(1, 2)
-    qu = (q + sd[p + "self_attn.pos_bias_u"]).transpose(1, 2)
-    qv = (q + sd[p + "self_attn.pos_bias_v"]).transpose(1, 2)
-    ac = torch.matmul(qu, k.transpose(-2, -1))
-    bd = _rel_shift(torch.matmul(qv, pe.transpose(-2, -1)))
-    attn = torch.softmax((ac + bd) / math.sqrt(DK), dim=-1)
-    o = torch.matmul(attn, v).transpose(1, 2).reshape(B, T, D)
-    x = x + lin("self_attn.linear_out", o)
-    h = F.layer_norm(x, (D,), sd[p + "norm_ff.weight"], sd[p + "norm_ff.bias"], 1e-12)
-    return x + lin("feed_forward.w_2", F.silu(lin("feed_forward.w_1", h)))
+def pack_front(sd: Dict[str, torch.Tensor], device):
+    """-> (bf16 blob, f32 blob, bf16 offsets, f32 offsets) in the order csrc/s3_front.cu indexes (BF_* / F_* enums)."""
+    g = lambda k: sd[k].detach().to(torch.float32)
+    layers = [f"encoder.encoders.{i}." for i in range(N_LAYERS0)] + [f"encoder.up_encoders.{i}." for i in range(N_LAYERS1)]
+    bf: List[torch.Tensor] = [g("encoder.embed.out.0.weight"), _conv_as_gemm(g("encoder.pre_lookahead_layer.conv1.weight")),
+                              _conv_as_gemm(g("encoder.pre_lookahead_layer.conv2.weight"))]
+    f: List[torch.Tensor] = [g("input_embedding.weight"), g("encoder.embed.out.0.bias"), g("encoder.embed.out.1.weight"),
+                             g("encoder.embed.out.1.bias"), g("encoder.pre_lookahead_layer.conv1.bias"),
+                             g("encoder.pre_lookahead_layer.conv2.bias")]
+    for p in layers:
+        a = p + "self_attn."
+        bf += [torch.cat([g(a + "linear_q.weight"), g(a + "linear_k.weight"), g(a + "linear_v.weight")], 0), g(a + "linear_pos.weight"),
+               g(a + "linear_out.weight"), g(p + "feed_forward.w_1.weight"), g(p + "feed_forward.w_2.weight")]
+        f += [g(p + "norm_mha.weight"), g(p + "norm_mha.bias"),
+              torch.cat([g(a + "linear_q.bias"), g(a + "linear_k.bias"), g(a + "linear_v.bias")], 0), g(a + "linear_out.bias"),
+              g(a + "pos_bias_u").reshape(-1), g(a + "pos_bias_v").reshape(-1), g(p + "norm_ff.weight"), g(p + "norm_ff.bias"),
+              g(p + "feed_forward.w_1.bias"), g(p + "feed_forward.w_2.bias")]
+    bf += [_conv_as_gemm(g("encoder.up_layer.conv.weight")), g("encoder.up_embed.out.0.weight"), g("encoder_proj.weight")]
+    f += [g("encoder.up_layer.conv.bias"), g("encoder.up_embed.out.0.bias"), g("encoder.up_embed.out.1.weight"),
+          g("encoder.up_embed.out.1.bias"), g("encoder.after_norm.weight"), g("encoder.after_norm.bias"), g("encoder_proj.bias"),
+          g("spk_embed_affine_layer.weight"), g("spk_embed_affine_layer.bias")]
+    assert len(bf) == 56 and len(f) == 115
+
+    def blob(ts, dtype, align):
+        offs, n = [], 0
+        for t in ts:
+            offs.append(n)
+            n += (t.numel() + align - 1) // align * align
+        out = torch.zeros(n, dtype=dtype, device=device)
+        for o, t in zip(offs, ts):
+            out[o:o + t.numel()] = t.reshape(-1).to(device=device, dtype=dtype)
+        return out, offs
+
+    bfb, bfo = blob(bf, torch.bfloat16, 64)       # 128-byte aligned matrices (TMA global address alignment)
+    fb, fo = blob(f, torch.float32, 4)
+    return bfb, fb, bfo, fo
 
 
-def _embed(sd, p: str, x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-    """LinearNoSubsampling + EspnetRelPositionalEncoding (subsampling.py:69-113, embedding.py:256-268)."""
-    x = F.linear(x, sd[p + "out.0.weight"], sd[p + "out.0.bias"])
-    x = F.layer_norm(x, (D,), sd[p + "out.1.weight"], sd[p + "out.1.bias"], 1e-5)
-    return x * math.sqrt(D), _rel_pos_emb(x.shape[1], x.device, x.dtype)
+class FlowFrontend:
+    """`flow_inputs(token, prompt_token, prompt_feat, embedding) -> (mu (1,80,L), spks (1,80), cond (1,80,L), mel_len1)`:
+    flow.py:250-270."""
 
+    def __init__(self, flow_sd: Dict[str, torch.Tensor], device="cuda", *, max_tokens: int = 2048):
+        if not torch.cuda.is_available():
+            raise _lib.CbxError("chatterbox_b200.flow_frontend needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self._lib = _lib.lib()
+        self.bf, self.f32, bfo, fo = pack_front(flow_sd, self.device)
+        self._bfo = (C.c_int64 * len(bfo))(*bfo)
+        self._fo = (C.c_int64 * len(fo))(*fo)
+        w = _lib.CbxFlowFrontWeights(self.bf.data_ptr(), self.f32.data_ptr(), self._bfo, self._fo)
+        h = C.c_void_p()
+        _lib.check(self._lib.cbx_flowfe_create(self.device.index, int(max_tokens), C.byref(w), C.byref(h)))
+        self._h = h
+        self.max_tokens = max_tokens
 
-def encoder(sd: Dict[str, torch.Tensor], xs: torch.Tensor, pfx: str = "encoder.") -> torch.Tensor:
-    """UpsampleConformerEncoder.forward for one un-padded utterance: (1, T, 512) -> (1, 2T, 512)."""
-    x, pos = _embed(sd, pfx + "embed.", xs)
-    # PreLookaheadLayer (upsample_encoder.py:66-96): right context 3, then causal k3, residual
-    h = x.transpose(1, 2)
-    h = F.leaky_relu(F.conv1d(F.pad(h, (0, 3)), sd[pfx + "pre_lookahead_layer.conv1.weight"],
-                              sd[pfx + "pre_lookahead_layer.conv1.bias"]))
-    h = F.conv1d(F.pad(h, (2, 0)), sd[pfx + "pre_lookahead_layer.conv2.weight"], sd[pfx + "pre_lookahead_layer.conv2.bias"])
-    x = h.transpose(1, 2) + x
-    for i in range(6):
-        x = _layer(sd, pfx + f"encoders.{i}.", x, pos)
-    # Upsample1D (upsample_encoder.py:37-63): nearest x2, left pad 4, conv k5
-    h = F.interpolate(x.transpose(1, 2), scale_factor=2.0, mode="nearest")
-    h = F.conv1d(F.pad(h, (4, 0)), sd[pfx + "up_layer.conv.weight"], sd[pfx + "up_layer.conv.bias"])
-    x, pos = _embed(sd, pfx + "up_embed.", h.transpose(1, 2))
-    for i in range(4):
-        x = _layer(sd, pfx + f"up_encoders.{i}.", x, pos)
-    return F.layer_norm(x, (D,), sd[pfx + "after_norm.weight"], sd[pfx + "after_norm.bias"], 1e-5)
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self._lib.cbx_flowfe_destroy(h)
+            self._h = None
 
+    def launches(self) -> int:
+        n = C.c_int64()
+        _lib.check(self._lib.cbx_flowfe_launches(self._h, C.byref(n)))
+        return n.value
 
-def flow_inputs(sd: Dict[str, torch.Tensor], token: torch.Tensor, prompt_token: torch.Tensor, prompt_feat: torch.Tensor,
-                embedding: torch.Tensor):
-    """flow.py:250-270 -> (mu (1,80,L), spks (1,80), cond (1,80,L), mel_len1) for the CFM solve.
-    token (1,T) / prompt_token (1,Tp) int64, prompt_feat (1, 2Tp, 80), embedding (1,192)."""
-    emb = F.normalize(embedding, dim=1)
-    spks = F.linear(emb, sd["spk_embed_affine_layer.weight"], sd["spk_embed_affine_layer.bias"])
-    tok = torch.cat([prompt_token, token], dim=1)
-    x = sd["input_embedding.weight"][torch.clamp(tok, min=0)]
-    h = encoder(sd, x)
-    mel_len1 = prompt_feat.shape[1]
-    L = h.shape[1]
-    mu = F.linear(h, sd["encoder_proj.weight"], sd["encoder_proj.bias"])
-    cond = torch.zeros(1, L, 80, device=h.device, dtype=h.dtype)
-    cond[:, :mel_len1] = prompt_feat
-    return mu.transpose(1, 2).contiguous(), spks, cond.transpose(1, 2).contiguous(), mel_len1
+    @torch.inference_mode()
+    def flow_inputs(self, token: torch.Tensor, prompt_token: torch.Tensor, prompt_feat: torch.Tensor, embedding: torch.Tensor):
+        dev = self.device
+        tok = token.to(dev, torch.long).reshape(-1).contiguous()
+        ptk = prompt_token.to(dev, torch.long).reshape(-1).contiguous()
+        pf = prompt_feat.to(dev, torch.float32).reshape(-1, 80).contiguous()
+        emb = embedding.to(dev, torch.float32).reshape(-1).contiguous()
+        T, Tp, Lp = tok.numel(), ptk.numel(), pf.shape[0]
+        L = 2 * (T + Tp)
+        mu = torch.empty(1, 80, L, dtype=torch.float32, device=dev)
+        cond = torch.empty(1, 80, L, dtype=torch.float32, device=dev)
+        spks = torch.empty(1, 80, dtype=torch.float32, device=dev)
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(self._lib.cbx_flowfe_run(self._h, ptk.data_ptr() if Tp else None, Tp, tok.data_ptr(), T,
+                                            pf.data_ptr() if Lp else None, Lp, emb.data_ptr(), mu.data_ptr(), spks.data_ptr(),
+                                            cond.data_ptr(), stream))
+        return mu, spks, cond, Lp

@@ -1,7 +1,7 @@
 """Host-side mirror of the reference `S3Token2Wav` / `S3Gen` (src/chatterbox/models/s3gen/s3gen.py:212-298):
 speech tokens + reference-voice dict -> mel (flow-matching) -> waveform (HiFT), same method names and
-return values.  The CFM solve and the vocoder run in `libcbx.so`; the once-per-utterance token front-end
-(`flow_frontend.py`) is plain torch on the GPU.
+return values.  The token front-end (`flow_frontend.py` -> csrc/s3_front.cu), the CFM solve and the vocoder all run in
+`libcbx.so`.
 
 Not provided (conditioning preparation, out of the hot path — SURVEY.md §2 rows 9, 12 and §8f row 4):
 `embed_ref` (needs the absent third-party `s3tokenizer` network, CAM++ and librosa mel) — callers pass a
@@ -29,44 +29,17 @@ class S3Gen:
         self.device = torch.device(device)
         if self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
-        keep = ("input_embedding.", "spk_embed_affine_layer.", "encoder.", "encoder_proj.")
-        self.front = {k: v.to(self.device, torch.float32) for k, v in flow_sd.items() if k.startswith(keep)}
+        self.front = flow_frontend.FlowFrontend(flow_sd, self.device, max_tokens=max(2, max_mel_len // 2))
         self.estimator = ConditionalDecoder(flow_sd, self.device, prefix="decoder.estimator.", max_len=max_mel_len,
                                             max_batch=max_batch)
         self.decoder = CausalConditionalCFM(self.estimator, rand_noise=rand_noise)
         self.mel2wav = HiFTGenerator(hift_sd, self.device, max_frames=max_mel_len)
         self.record_events = False
         self.events: Dict[str, torch.cuda.Event] = {}
-        # token front-end replayed as a CUDA graph from its second call with the same lengths (it is ~300 small
-        # library launches: launch-bound when run eagerly); `front_graphs = False` keeps it eager
-        self.front_graphs = True
-        self._front_cache: Dict[tuple, dict] = {}
 
     def _front(self, tok, prompt_token, prompt_feat, embedding):
-        """flow_frontend.flow_inputs, eager on the first call for a (T, Tp, 2Tp) shape, captured on the second,
-        replayed afterwards.  The returned tensors of a replay are the graph's static outputs: they are consumed
-        by the CFM solve on the same stream before the next replay can overwrite them."""
-        args = (tok, prompt_token, prompt_feat, embedding)
-        if not self.front_graphs:
-            return flow_frontend.flow_inputs(self.front, *args)
-        key = (tok.shape[1], prompt_token.shape[1], prompt_feat.shape[1])
-        ent = self._front_cache.get(key)
-        if ent is None:
-            if len(self._front_cache) >= 8:          # bound the captured pools
-                self._front_cache.pop(next(iter(self._front_cache)))
-            self._front_cache[key] = {"graph": None}
-            return flow_frontend.flow_inputs(self.front, *args)
-        if ent["graph"] is None:
-            static = [a.clone() for a in args]
-            g = torch.cuda.CUDAGraph()
-            torch.cuda.synchronize(self.device)
-            with torch.cuda.graph(g):
-                outs = flow_frontend.flow_inputs(self.front, *static)
-            ent.update(graph=g, static=static, outs=outs)
-        for dst, src in zip(ent["static"], args):
-            dst.copy_(src)
-        ent["graph"].replay()
-        return ent["outs"]
+        """flow.py:250-270 on the kernels of csrc/s3_front.cu (~100 launches on the current stream, no host sync)."""
+        return self.front.flow_inputs(tok, prompt_token, prompt_feat, embedding)
 
     @classmethod
     def from_state_dict(cls, sd: Dict[str, torch.Tensor], device="cuda", **kw) -> "S3Gen":
@@ -147,7 +120,7 @@ class S3Gen:
                 tok = tok.unsqueeze(0)
             mu, spks, cond, l1 = self._front(tok.long(), ref["prompt_token"].long(), ref["prompt_feat"].float(),
                                              ref["embedding"].float())
-            mus.append(mu.clone()); spk.append(spks.clone()); conds.append(cond.clone()); l1s.append(l1)   # graph outputs are static
+            mus.append(mu); spk.append(spks); conds.append(cond); l1s.append(l1)
         if ev:
             ev["cfm0"].record()
         lens = [int(m.shape[2]) for m in mus]
@@ -174,4 +147,4 @@ class S3Gen:
         return outs
 
     def launches(self) -> int:
-        return self.estimator.launches() + self.mel2wav.launches()
+        return self.front.launches() + self.estimator.launches() + self.mel2wav.launches()

@@ -2,9 +2,9 @@
 
 Same constructor state (reference state-dict keys), same `inference(...)` signature and return
 value; the 30-layer backbone, logit processing, sampling and the decode loop run inside
-`libcbx.so` (csrc/t3_decode.cu).  The once-per-utterance conditioning front-end
-(`T3CondEnc`/`Perceiver`/embedding gathers, t3.py:71-108) is plain PyTorch on the device — SURVEY.md
-§8f lists it as a "next" row.  There is no CPU path: construction fails without CUDA + libcbx.so.
+`libcbx.so` (csrc/t3_decode.cu), and so does the once-per-utterance conditioning front-end
+(`T3CondEnc` / `Perceiver` / embedding gathers / doubled BOS, t3.py:71-108,284-295: csrc/t3_front.cu, fp32).
+There is no CPU path: construction fails without CUDA + libcbx.so.
 """
 from __future__ import annotations
 
@@ -13,7 +13,6 @@ from dataclasses import dataclass
 from typing import Dict, Optional
 
 import torch
-import torch.nn.functional as F
 
 from . import _lib
 from .pack import T3Packed, pack_t3
@@ -86,7 +85,7 @@ class T3:
         self.packed: T3Packed = pack_t3(state_dict, G, self.device, max_pos, n_layers, gemm_prefill=gemm_prefill)
         # front-end parameters (reference key names), fp32 on the device
         keep = ("cond_enc.", "text_emb.", "text_pos_emb.")
-        self.fe = {k: v.to(self.device, torch.float32) for k, v in state_dict.items() if k.startswith(keep)}
+        self.fe = {k: v.to(self.device, torch.float32).contiguous() for k, v in state_dict.items() if k.startswith(keep)}
         self.fe["speech_emb.weight"] = self.packed.speech_emb
         self.fe["speech_pos_emb.emb.weight"] = self.packed.speech_pos_emb
         p = self.packed
@@ -109,54 +108,68 @@ class T3:
         if h:
             self._lib.cbx_t3_destroy(h)
             self._h = None
+        hfe = getattr(self, "_hfe", None)
+        if hfe:
+            self._lib.cbx_t3_front_destroy(hfe)
+            self._hfe = None
 
-    # ---- conditioning front-end (t3.py:71-108, cond_enc.py:64-97, perceiver.py:113-212) ----
-    def _attn_block2(self, x1, x2):
-        fe, pfx = self.fe, "cond_enc.perceiver.attn."
-        lin = lambda n, x: F.linear(x, fe[pfx + n + ".weight"], fe[pfx + n + ".bias"])
-        x1n = F.layer_norm(x1, (1024,), fe[pfx + "norm.weight"], fe[pfx + "norm.bias"])
-        x2n = F.layer_norm(x2, (1024,), fe[pfx + "norm.weight"], fe[pfx + "norm.bias"])
-        sp = lambda t: t.view(t.shape[0], t.shape[1], 4, 256).permute(0, 2, 1, 3)
-        o = F.scaled_dot_product_attention(sp(lin("to_q", x1n)), sp(lin("to_k", x2n)), sp(lin("to_v", x2n)))
-        o = o.permute(0, 2, 1, 3).contiguous().view(x1.shape[0], x1.shape[1], 1024)
-        return x1 + lin("proj_out", o)
+    # ---- conditioning front-end (t3.py:71-108, cond_enc.py:64-97, perceiver.py:113-212): csrc/t3_front.cu ----
+    def _front_handle(self):
+        if getattr(self, "_hfe", None) is None:
+            fe = self.fe
+            g = lambda k: fe[k].data_ptr() if k in fe else None          # fe tensors are contiguous fp32 and live as long as self
+            pa = "cond_enc.perceiver.attn."
+            w = _lib.CbxT3FrontWeights(g("cond_enc.spkr_enc.weight"), g("cond_enc.spkr_enc.bias"),
+                                       g("cond_enc.perceiver.pre_attention_query"), g(pa + "norm.weight"), g(pa + "norm.bias"),
+                                       g(pa + "to_q.weight"), g(pa + "to_q.bias"), g(pa + "to_k.weight"), g(pa + "to_k.bias"),
+                                       g(pa + "to_v.weight"), g(pa + "to_v.bias"), g(pa + "proj_out.weight"), g(pa + "proj_out.bias"),
+                                       g("cond_enc.emotion_adv_fc.weight"), g("text_emb.weight"), g("text_pos_emb.emb.weight"),
+                                       g("speech_emb.weight"), g("speech_pos_emb.emb.weight"))
+            h = C.c_void_p()
+            _lib.check(self._lib.cbx_t3_front_create(self.device.index, 256, C.byref(w), C.byref(h)))
+            self._hfe = h
+        return self._hfe
+
+    def _prefill_embeds(self, t3_cond: T3Cond, text_tokens: torch.Tensor, cfg_weight: float, n_bos: int):
+        """-> (embeds (B, P, 1024) fp32 = [speaker | 32 perceiver rows | emotion | text | BOS x n_bos], len_cond).
+        All inputs stay on the device (no host synchronisation)."""
+        assert t3_cond.clap_emb is None, "clap_embed not implemented"
+        assert t3_cond.emotion_adv is not None
+        dev = self.device
+        text_tokens = torch.atleast_2d(text_tokens).to(device=dev, dtype=torch.long).contiguous()
+        B, N = text_tokens.shape
+        if N > self.fe["text_pos_emb.emb.weight"].shape[0]:
+            raise ValueError("text longer than the learned text position table")
+        spk = t3_cond.speaker_emb.to(dev, torch.float32).reshape(-1).contiguous()
+        emo = torch.as_tensor(t3_cond.emotion_adv, dtype=torch.float32, device=dev).reshape(-1).contiguous()
+        toks = t3_cond.cond_prompt_speech_tokens
+        pe = t3_cond.cond_prompt_speech_emb
+        n_cond, toks_p, pe_p = 0, None, None
+        if pe is not None:
+            pe = pe.to(dev, torch.float32).reshape(-1, 1024).contiguous()
+            n_cond, pe_p = pe.shape[0], pe.data_ptr()
+        elif toks is not None:
+            toks = toks.to(device=dev, dtype=torch.long).reshape(-1).contiguous()
+            n_cond, toks_p = toks.numel(), toks.data_ptr()
+        len_cond = 2 + (32 if n_cond else 0)
+        out = torch.empty(B, len_cond + N + n_bos, 1024, dtype=torch.float32, device=dev)
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(self._lib.cbx_t3_front(self._front_handle(), spk.data_ptr(), toks_p, pe_p, n_cond, emo.data_ptr(),
+                                          text_tokens.data_ptr(), B, N, 1 if cfg_weight > 0.0 else 0, n_bos, out.data_ptr(), stream))
+        return out, len_cond
 
     def prepare_conditioning(self, t3_cond: T3Cond) -> torch.Tensor:
-        fe = self.fe
-        if t3_cond.cond_prompt_speech_tokens is not None and t3_cond.cond_prompt_speech_emb is None:
-            toks = t3_cond.cond_prompt_speech_tokens
-            t3_cond.cond_prompt_speech_emb = fe["speech_emb.weight"][toks] + \
-                fe["speech_pos_emb.emb.weight"][: toks.shape[1]][None]
-        assert (t3_cond.cond_prompt_speech_tokens is None) == (t3_cond.cond_prompt_speech_emb is None), \
-            "no embeddings for cond_prompt_speech_tokens"
-        spk = F.linear(t3_cond.speaker_emb.view(-1, 256), fe["cond_enc.spkr_enc.weight"], fe["cond_enc.spkr_enc.bias"])[:, None]
-        empty = torch.zeros_like(spk[:, :0])
-        assert t3_cond.clap_emb is None, "clap_embed not implemented"
-        pe = t3_cond.cond_prompt_speech_emb
-        if pe is None:
-            pe = empty
-        else:
-            q = fe["cond_enc.perceiver.pre_attention_query"].expand(pe.shape[0], -1, -1)
-            pre = self._attn_block2(q, pe)
-            pe = self._attn_block2(pre, pre)
-        assert t3_cond.emotion_adv is not None
-        emo = F.linear(t3_cond.emotion_adv.view(-1, 1, 1), fe["cond_enc.emotion_adv_fc.weight"])
-        return torch.cat((spk, empty, pe, emo), dim=1)
+        """t3.py:71-78 -> (1, len_cond, 1024)."""
+        sot_eot = torch.tensor([[self.hp.start_text_token, self.hp.stop_text_token]], device=self.device)
+        out, len_cond = self._prefill_embeds(t3_cond, sot_eot, 0.0, 1)
+        return out[:, :len_cond]
 
     def prepare_input_embeds(self, *, t3_cond: T3Cond, text_tokens, speech_tokens, cfg_weight: float = 0.0):
-        fe = self.fe
-        cond_emb = self.prepare_conditioning(t3_cond)
-        text_emb = fe["text_emb.weight"][text_tokens].clone()
-        if cfg_weight > 0.0:
-            text_emb[1].zero_()
-        speech_emb = fe["speech_emb.weight"][speech_tokens]
-        text_emb = text_emb + fe["text_pos_emb.emb.weight"][: text_tokens.shape[1]][None]
-        speech_emb = speech_emb + fe["speech_pos_emb.emb.weight"][: speech_tokens.shape[1]][None]
-        len_cond = cond_emb.size(1)
-        if cond_emb.size(0) != text_emb.size(0):
-            cond_emb = cond_emb.expand(text_emb.size(0), -1, -1)
-        embeds = torch.cat((cond_emb, text_emb, speech_emb), dim=1)
-        return embeds, len_cond
+        """t3.py:80-108 for the initial speech tokens `T3.inference` passes (one BOS per row)."""
+        st = torch.atleast_2d(speech_tokens)
+        assert st.shape[1] == 1, "only the initial BOS speech token is supported here (T3.inference's own call)"
+        out, len_cond = self._prefill_embeds(t3_cond, text_tokens, cfg_weight, 1)
+        return out, len_cond
 
     # ---- the decode path ----
     @torch.inference_mode()
@@ -181,13 +194,8 @@ class T3:
         text_tokens = torch.atleast_2d(text_tokens).to(dtype=torch.long, device=self.device)
         if initial_speech_tokens is None:
             initial_speech_tokens = self.hp.start_speech_token * torch.ones_like(text_tokens[:, :1])
-        embeds, len_cond = self.prepare_input_embeds(t3_cond=t3_cond, text_tokens=text_tokens,
-                                                     speech_tokens=initial_speech_tokens, cfg_weight=cfg_weight)
-        bos = (self.fe["speech_emb.weight"][self.hp.start_speech_token] +
-               self.fe["speech_pos_emb.emb.weight"][0])[None, None]
-        if cfg_weight > 0:   # the reference appends BOS a second time (t3.py:284-295)
-            embeds = torch.cat([embeds, bos.expand(embeds.shape[0], -1, -1)], dim=1)
-        embeds = embeds.contiguous().float()
+        # conditioning prefix | text | BOS (| BOS: the reference appends BOS a second time on the CFG path, t3.py:284-295)
+        embeds, len_cond = self._prefill_embeds(t3_cond, text_tokens, cfg_weight, 2 if cfg_weight > 0 else 1)
         B, P, _ = embeds.shape
         assert B in (1, 2), "T3.inference runs one utterance (optionally as a CFG pair)"
         if max_new_tokens is None:

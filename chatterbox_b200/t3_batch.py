@@ -79,15 +79,9 @@ class T3Batch:
         _ensure_BOT_EOT(tt, t3.hp)
         if tt.shape[0] == 1:
             tt = torch.cat([tt, tt], 0)
-        bos_tok = t3.hp.start_speech_token * torch.ones_like(tt[:, :1])
-        # the engine always runs the CFG pair; with cfg_weight == 0 the second row is computed and ignored, its text
-        # embeddings are NOT zeroed (t3.py:90-92 zeroes them only when cfg_weight > 0)
-        embeds, _ = t3.prepare_input_embeds(t3_cond=req.t3_cond, text_tokens=tt, speech_tokens=bos_tok,
-                                            cfg_weight=req.cfg_weight)
-        bos = (t3.fe["speech_emb.weight"][t3.hp.start_speech_token] + t3.fe["speech_pos_emb.emb.weight"][0])[None, None]
-        if req.cfg_weight > 0:
-            embeds = torch.cat([embeds, bos.expand(2, -1, -1)], dim=1)
-        embeds = embeds.contiguous().float()
+        # the engine always runs the CFG pair; with cfg_weight == 0 the second row is computed and ignored (its text
+        # embeddings are NOT zeroed, t3.py:90-92, and there is a single BOS, t3.py:292-295)
+        embeds, _ = t3._prefill_embeds(req.t3_cond, tt, req.cfg_weight, 2 if req.cfg_weight > 0 else 1)
         P = embeds.shape[1]
         n = int(req.max_new_tokens)
         forced = None

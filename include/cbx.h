@@ -110,6 +110,44 @@ int cbx_t3_set_alignment(cbx_t3* h, int layer, int text_begin, int n_text, const
 int cbx_t3_set_profile(cbx_t3* h, uint64_t* stamps, int it);
 
 /* ------------------------------------------------------------------------------------------
+ * (1c) T3 conditioning front-end: the prompt embeddings cbx_t3_prefill consumes, once per utterance.
+ * Replaces T3CondEnc.forward (src/chatterbox/models/t3/modules/cond_enc.py:64-97), Perceiver / AttentionBlock2
+ * (modules/perceiver.py:113-212), the exaggeration projection (cond_enc.py:85-88; tts.py:204,225-231),
+ * T3.prepare_conditioning / prepare_input_embeds (t3.py:71-108) and the doubled BOS of t3.py:284-295.  fp32 throughout,
+ * like the reference; every input is a DEVICE pointer (the emotion scalar and the token ids are read on the device: no
+ * host synchronisation).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct cbx_t3fe cbx_t3fe;
+
+typedef struct CbxT3FrontWeights {       /* device pointers, fp32, caller-owned (reference state-dict keys in the comments) */
+  const float* spkr_w;                   /* cond_enc.spkr_enc.weight [1024][256] */
+  const float* spkr_b;                   /* cond_enc.spkr_enc.bias [1024] */
+  const float* query;                    /* cond_enc.perceiver.pre_attention_query [32][1024] */
+  const float* norm_g; const float* norm_b;              /* cond_enc.perceiver.attn.norm.{weight,bias} */
+  const float* wq; const float* bq;      /* cond_enc.perceiver.attn.to_q.{weight [1024][1024], bias} */
+  const float* wk; const float* bk;      /* ...to_k */
+  const float* wv; const float* bv;      /* ...to_v */
+  const float* wo; const float* bo;      /* ...proj_out */
+  const float* emotion_w;                /* cond_enc.emotion_adv_fc.weight [1024][1] */
+  const float* text_emb;                 /* text_emb.weight [704][1024] */
+  const float* text_pos_emb;             /* text_pos_emb.emb.weight [2050][1024] */
+  const float* speech_emb;               /* speech_emb.weight [8194][1024] */
+  const float* speech_pos_emb;           /* speech_pos_emb.emb.weight [4100][1024] */
+} CbxT3FrontWeights;
+
+int cbx_t3_front_create(int device, int max_cond_tokens, const CbxT3FrontWeights* w, cbx_t3fe** out);
+int cbx_t3_front_destroy(cbx_t3fe* h);
+/* speaker_emb [256]; cond_tokens int64 [n_cond] (T3Cond.cond_prompt_speech_tokens) or, when non-NULL, cond_prompt_emb
+ * [n_cond][1024] (T3Cond.cond_prompt_speech_emb) instead; n_cond == 0: no perceiver rows; emotion_adv [1];
+ * text_tokens int64 [B][N] incl. SOT / EOT; zero_uncond_text: row 1's text-token embeddings are zeroed (cfg_weight > 0,
+ * t3.py:90-92); n_bos: 1, or 2 for the doubled BOS of the CFG path.  embeds_out [B][P][1024], P = 1 + 32 + 1 + N + n_bos
+ * (2 + N + n_bos without conditioning tokens). */
+int cbx_t3_front(cbx_t3fe* h, const float* speaker_emb, const int64_t* cond_tokens, const float* cond_prompt_emb, int n_cond,
+                 const float* emotion_adv, const int64_t* text_tokens, int B, int N, int zero_uncond_text, int n_bos,
+                 float* embeds_out, void* stream);
+int cbx_t3_front_launches(cbx_t3fe* h, int64_t* launches);
+
+/* ------------------------------------------------------------------------------------------
  * (1b) Batched T3 decode: up to 64 concurrent utterances ("slots") per handle, one pass of all slots' CFG pairs
  * through every weight matrix per step (BASELINE config 4).  Replaces the reference server's one-request-at-a-time
  * loop (src/server/server.py:189-299: one synchronous tts_model.generate per request, :223,232; global
@@ -192,6 +230,30 @@ int cbx_cfm_solve_batch(cbx_cfm* h, int nb, const float* z, const float* mu, con
 int cbx_cfm_launches(cbx_cfm* h, int64_t* launches);
 /* Entries of the handle's two bounded caches: executable solve graphs (LRU, at most 8) and per-length op plans (at most 64). */
 int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans);
+
+/* ------------------------------------------------------------------------------------------
+ * (2b) S3Gen flow front-end: speech tokens -> (mu, spks, cond), the inputs of the flow-matching solve, once per utterance.
+ * Replaces CausalMaskedDiffWithXvec.inference up to the decoder call (src/chatterbox/models/s3gen/flow.py:236-270):
+ * F.normalize + spk_embed_affine_layer, input_embedding, UpsampleConformerEncoder.forward
+ * (s3gen/transformer/upsample_encoder.py:237-304; rel-pos attention transformer/attention.py:225-330 with rel_shift as an
+ * index transform), encoder_proj, and the prompt-mel conditioning tensor.  One un-padded utterance per call.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct cbx_flowfe cbx_flowfe;
+
+typedef struct CbxFlowFrontWeights {   /* device pointers, caller-owned, must outlive the handle */
+  const void* bf16_blob;               /* Linear / Conv1d matrices as bf16 [N][taps * K] (chatterbox_b200/flow_frontend.py: pack order) */
+  const float* f32_blob;               /* embedding table, biases, LayerNorm gains, pos_bias_u / v, speaker projection */
+  const int64_t* bf16_off;             /* HOST array [56] */
+  const int64_t* f32_off;              /* HOST array [115] */
+} CbxFlowFrontWeights;
+
+int cbx_flowfe_create(int device, int max_tokens, const CbxFlowFrontWeights* w, cbx_flowfe** out);
+int cbx_flowfe_destroy(cbx_flowfe* h);
+/* prompt_token int64 [Tp], token int64 [T] (negative ids clamp to 0, flow.py:254), prompt_feat fp32 [Lp][80] (Lp = 2 Tp in the
+ * reference), embedding fp32 [192]; outputs for L = 2 (Tp + T) mel frames: mu_out [80][L], spks_out [80], cond_out [80][L]. */
+int cbx_flowfe_run(cbx_flowfe* h, const int64_t* prompt_token, int Tp, const int64_t* token, int T, const float* prompt_feat,
+                   int Lp, const float* embedding, float* mu_out, float* spks_out, float* cond_out, void* stream);
+int cbx_flowfe_launches(cbx_flowfe* h, int64_t* launches);
 
 /* ------------------------------------------------------------------------------------------
  * (3) HiFT-GAN vocoder: mel -> f0 -> harmonic source -> waveform.

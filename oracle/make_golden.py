@@ -404,8 +404,8 @@ def make_hift():
 
 def make_flow():
     """Reference CausalMaskedDiffWithXvec.inference: captures the CFM inputs the front-end produces and the
-    final mel; checks chatterbox_b200/flow_frontend.py (plain torch) against them."""
-    from chatterbox_b200 import flow_frontend as FF
+    final mel; checks oracle/flow_oracle.py (plain torch) against them."""
+    from oracle import flow_oracle as FF
     sd = S.make_state_dict("flow")
     flow = R.build_flow()
     flow.load_state_dict(sd, strict=False)
