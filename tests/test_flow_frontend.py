@@ -12,7 +12,9 @@ from chatterbox_b200 import synthetic as S
 from oracle import flow_oracle as FO
 
 GOLD = load_file(os.path.join(os.path.dirname(__file__), "golden", "flow_golden.safetensors"))
-TOL_MU = 5e-3        # relative L2 of mu: bf16 weights, hi / lo activations, fp32 accumulation and attention (measured ~1e-3)
+TOL_MU = 6e-3        # relative L2 of mu.  Measured on B200: 3.2e-3 .. 3.4e-3 at T = 1 .. 900 tokens, independent of the length:
+                     # it is the bf16 rounding of the encoder weights (the oracle keeps them fp32); activations are hi / lo
+                     # split bf16 pairs (~2^-17) with fp32 accumulation, attention and layer norms are fp32
 
 
 def _inputs():
