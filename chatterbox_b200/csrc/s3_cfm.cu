@@ -134,7 +134,7 @@ __global__ void k_euler_b(const float* __restrict__ est, float* __restrict__ x, 
   if (last) mel_out[((size_t)u * NMEL + ch) * L + t] = xn;
 }
 
-struct Op { int kind; GemmDesc g; int temb_res; };   // kind 0 gemm, 1 attention, 2 skip copy
+struct Op { int kind; GemmDesc g; int temb_res; FfnDesc f; };   // kind 0 gemm, 1 attention, 2 skip copy, 3 fused feed-forward
 struct Plan { int L, nb; std::vector<Op> ops; };
 
 }  // namespace
@@ -169,6 +169,11 @@ static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
   if (it != h->plans.end()) { *out = &it->second; return CBX_OK; }
   Plan pl; pl.L = L; pl.nb = nb;
   int rc = CBX_OK;
+  // few row tiles (one utterance: 2 x ceil(L / 128)): the feed-forward pair runs as one 8-CTA-cluster kernel per tile;
+  // large padded batches keep the two full-width GEMMs (CBX_CFM_FFN=0 / CBX_CFM_FFN_MAXTILES=n for A/B)
+  static const int ffn_on = [] { const char* v = getenv("CBX_CFM_FFN"); return v ? atoi(v) : 1; }();
+  static const int ffn_max_tiles = [] { const char* v = getenv("CBX_CFM_FFN_MAXTILES"); return v ? atoi(v) : 64; }();
+  const bool fused_ffn = ffn_on && 2 * nb * ((L + 127) / 128) <= ffn_max_tiles;
   auto G = [&](const __nv_bfloat16* A, int lda, int wi, int N, int K, int taps, const GemmEpi& e, int temb_res) {
     Op op; op.kind = 0; op.temb_res = temb_res;
     if (gemm_make(&op.g, A, lda, BFW(h, wi), 2 * nb, L, N, K, taps, e)) rc = CBX_ERR;
@@ -192,6 +197,18 @@ static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
     GemmEpi eo{}; eo.bias = FW(h, f + 2); eo.resid = h->res; eo.ld_resid = C; eo.out_f32 = h->res; eo.ld_f32 = C;
     eo.ln2_g = FW(h, f + 3); eo.ln2_b = FW(h, f + 4); eo.out_ln = h->ln; eo.ld_ln = C;
     G(h->att, 512, w + 1, C, 512, 1, eo, -1);
+    if (fused_ffn) {
+      // FF1 + GELU + FF2 + residual (+ the next block's norm1) as ONE cluster kernel (csrc/s3_ffn.cu)
+      Op op; op.kind = 3; op.temb_res = -1;
+      if (ffn_make(&op.f, h->ln, C, BFW(h, w + 2), BFW(h, w + 3), 2 * nb, L)) rc = CBX_ERR;
+      op.f.b1 = FW(h, f + 5); op.f.b2 = FW(h, f + 6);
+      op.f.resid = h->res; op.f.ld_resid = C; op.f.out_f32 = h->res; op.f.ld_f32 = C;
+      op.f.ln_g = op.f.ln_b = nullptr; op.f.out_ln = nullptr; op.f.ld_ln = C; op.f.out_bf16 = nullptr; op.f.ld_bf16 = 0;
+      if (!last) { op.f.ln_g = FW(h, f + 7); op.f.ln_b = FW(h, f + 8); op.f.out_ln = h->ln; }
+      else { op.f.out_bf16 = dst; op.f.ld_bf16 = ld_dst; }
+      pl.ops.push_back(op);
+      return;
+    }
     GemmEpi e1{}; e1.bias = FW(h, f + 5); e1.gelu = 1; e1.out_bf16 = h->ff; e1.ld_bf16 = 1024;
     G(h->ln, C, w + 2, 1024, C, 1, e1, -1);
     GemmEpi e2{}; e2.bias = FW(h, f + 6); e2.resid = h->res; e2.ld_resid = C; e2.out_f32 = h->res; e2.ld_f32 = C;
@@ -235,6 +252,8 @@ static int run_estimator(cbx_cfm* h, Plan* pl, int step, const int* lens, cudaSt
         d.epi.temb = h->tvec + ((size_t)(step * NRES + op.temb_res) * 2) * C;      // [2][C] copies; the GEMM reads the first
         if (gemm_launch(d, st)) return CBX_ERR;
       } else if (gemm_launch(op.g, st)) return CBX_ERR;
+    } else if (op.kind == 3) {
+      if (ffn_launch(op.f, st)) return CBX_ERR;
     } else if (op.kind == 1) {
       if (s3_attn_launch(h->qkv, h->att, B, L, 1536, lens, st)) return CBX_ERR;
     } else {
@@ -437,9 +456,10 @@ extern "C" int cbx_cfm_solve_batch(cbx_cfm* h, int nb, const float* z, const flo
   return CBX_OK;
 }
 
-namespace cbx { void gemm_set_debug(unsigned long long* buf); }
+namespace cbx { void gemm_set_debug(unsigned long long* buf); void ffn_set_debug(unsigned long long* buf); }
 /* Debug aid (not in cbx.h): every following GEMM launch writes 8 %globaltimer stamps of CTA (0,0) to buf and advances it. */
 extern "C" int cbx_dbg_gemm_stamps(unsigned long long* buf) { cbx::gemm_set_debug(buf); return 0; }
+extern "C" int cbx_dbg_ffn_stamps(unsigned long long* buf) { cbx::ffn_set_debug(buf); return 0; }
 
 extern "C" int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans) {
   CBX_CHECK(h, "cbx_cfm_cache_sizes: null handle");

@@ -79,18 +79,6 @@ __device__ __forceinline__ float mish_f(float x) {
   const float t = n * (n + 2.0f);
   return x * __fdividef(t, t + 2.0f);
 }
-// exact-GELU through erf(z) = sign(z) (1 - P(u) e^{-z^2}), u = 1 / (1 + 0.3275911 |z|)  (Abramowitz-Stegun 7.1.26,
-// |error| <= 1.5e-7 — two orders below the bf16 rounding of the value this feeds)
-__device__ __forceinline__ float gelu_f(float x) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  const float u = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  float pl = fmaf(1.061405429f, u, -1.453152027f);
-  pl = fmaf(pl, u, 1.421413741f);
-  pl = fmaf(pl, u, -0.284496736f);
-  pl = fmaf(pl, u, 0.254829592f);
-  const float er = 1.0f - pl * u * __expf(-z * z);
-  return 0.5f * x * (1.0f + copysignf(er, x));
-}
 // sin with a two-constant Cody-Waite reduction to [-pi, pi] ahead of the SFU approximation
 __device__ __forceinline__ float sin_f(float x) {
   const float k = rintf(x * 0.15915494309189535f);

@@ -39,6 +39,21 @@ struct GemmDesc {
   GemmEpi epi;
 };
 
+#ifdef __CUDACC__
+// exact-GELU through erf(z) = sign(z) (1 - P(u) e^{-z^2}), u = 1 / (1 + 0.3275911 |z|)  (Abramowitz-Stegun 7.1.26,
+// |error| <= 1.5e-7 — two orders below the bf16 rounding of the value this feeds)
+__device__ __forceinline__ float gelu_f(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float u = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  float pl = fmaf(1.061405429f, u, -1.453152027f);
+  pl = fmaf(pl, u, 1.421413741f);
+  pl = fmaf(pl, u, -0.284496736f);
+  pl = fmaf(pl, u, 0.254829592f);
+  const float er = 1.0f - pl * u * __expf(-z * z);
+  return 0.5f * x * (1.0f + copysignf(er, x));
+}
+#endif
+
 // builds the tensor maps; A has row stride lda elements (>= K), W is dense [N][taps*K]
 int gemm_make(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, int B, int L, int N, int K, int taps,
               const GemmEpi& epi);    // causal taps: dil 1, pad taps-1, M_out = L
@@ -55,5 +70,22 @@ int gemm_make_hilo_ex(GemmDesc* d, const __nv_bfloat16* A, int lda, long long pl
 int gemm_launch(const GemmDesc& d, cudaStream_t st);
 // true unless CBX_PDL=0: kernels are launched with programmatic stream serialization (prologue overlap)
 bool pdl_enabled();
+
+// ---- fused feed-forward of a BasicTransformerBlock (csrc/s3_ffn.cu; matcha/transformer.py:300-316):
+//   y = resid + W2 gelu(W1 x + b1) + b2, then either LayerNorm(y) -> out_ln (the next block's norm1) or y -> out_bf16,
+// x = bf16 [B][L][256] (already normalised), hidden 1024.  One cluster of 8 CTAs per 128-row tile: CTA c owns hidden
+// columns [128 c, 128 c + 128) — FF1 slice, GELU, FF2 partial over that K slice — and the 8 partial tiles meet in
+// distributed shared memory, each CTA finishing 16 rows.
+struct FfnDesc {
+  CUtensorMap tmX, tmW1, tmW2;
+  int B, L;
+  const float *b1, *b2;
+  const float* resid; int ld_resid;
+  float* out_f32; int ld_f32;
+  const float *ln_g, *ln_b; __nv_bfloat16* out_ln; int ld_ln;      // ln_g == null: no LayerNorm output
+  __nv_bfloat16* out_bf16; int ld_bf16;                            // or null
+};
+int ffn_make(FfnDesc* d, const __nv_bfloat16* X, int ldx, const __nv_bfloat16* W1, const __nv_bfloat16* W2, int B, int L);
+int ffn_launch(const FfnDesc& d, cudaStream_t st);
 
 }  // namespace cbx
