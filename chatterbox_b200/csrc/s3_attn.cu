@@ -8,6 +8,7 @@
 // with fp32 accumulation and an fp32 online softmax.  (Round-1 kernel: the legacy tensor-core path;
 // the tcgen05 version is listed in DESIGN.md as the next step for this stage.)
 #include "s3_gemm.cuh"
+#include <cstdlib>
 
 namespace cbx {
 namespace {
@@ -207,7 +208,17 @@ __global__ void __launch_bounds__(128 * AT_G) s3_attn_kernel(const __nv_bfloat16
 
 }  // namespace
 
+int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st);
+int s3_attn_launch_mma(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st);
+
 int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st) {
+  // default: the tcgen05 kernel (csrc/s3_attn_tc.cu); CBX_ATTN_TC=0 keeps the mma.sync kernel below for A/B
+  static const bool use_tc = [] { const char* v = getenv("CBX_ATTN_TC"); return !(v && v[0] == '0'); }();
+  if (use_tc) return s3_attn_tc_launch(qkv, out, B, L, ld_qkv, lens, st);
+  return s3_attn_launch_mma(qkv, out, B, L, ld_qkv, lens, st);
+}
+
+int s3_attn_launch_mma(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st) {
   dim3 grid((L + AT_BM - 1) / AT_BM, 8, B);
   static CbxPerDeviceOnce once;
   if (once.first())

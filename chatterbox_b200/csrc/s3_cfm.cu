@@ -11,6 +11,7 @@
 
 namespace cbx {
 int s3_attn_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st);
+int s3_attn_launch_mma(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st);
 }
 using namespace cbx;
 
@@ -459,6 +460,15 @@ extern "C" int cbx_cfm_solve_batch(cbx_cfm* h, int nb, const float* z, const flo
 namespace cbx { void gemm_set_debug(unsigned long long* buf); void ffn_set_debug(unsigned long long* buf); }
 /* Debug aid (not in cbx.h): every following GEMM launch writes 8 %globaltimer stamps of CTA (0,0) to buf and advances it. */
 extern "C" int cbx_dbg_gemm_stamps(unsigned long long* buf) { cbx::gemm_set_debug(buf); return 0; }
+namespace cbx { int s3_attn_tc_launch(const __nv_bfloat16*, __nv_bfloat16*, int, int, int, const int*, cudaStream_t); }
+/* Debug aid (not in cbx.h): the estimator's attention kernel alone — qkv bf16 [B][L][1536] -> out bf16 [B][L][512];
+   tc != 0: the tcgen05 kernel, 0: the mma.sync kernel (tests/test_s3_attn_gpu.py). */
+extern "C" int cbx_dbg_s3_attn(const void* qkv, void* out, int B, int L, const int* lens, int tc, void* stream) {
+  CBX_CHECK(qkv && out && B >= 1 && L >= 1, "cbx_dbg_s3_attn: bad argument");
+  auto q = static_cast<const __nv_bfloat16*>(qkv); auto o = static_cast<__nv_bfloat16*>(out);
+  if (tc) return cbx::s3_attn_tc_launch(q, o, B, L, 1536, lens, static_cast<cudaStream_t>(stream));
+  return cbx::s3_attn_launch_mma(q, o, B, L, 1536, lens, static_cast<cudaStream_t>(stream));
+}
 extern "C" int cbx_dbg_ffn_stamps(unsigned long long* buf) { cbx::ffn_set_debug(buf); return 0; }
 
 extern "C" int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans) {
