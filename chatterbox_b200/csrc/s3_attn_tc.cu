@@ -3,17 +3,21 @@
 // (decoder.py:25-33, utils/mask.py:167-193)).
 //
 // One CTA owns 128 query rows of one (batch row, head).  Keys are taken in blocks of 128:
-//   warp 0      TMA producer: Q tile once, then K block [128 keys][64 d] and V block [128 keys][64 d] per stage
-//               (3-stage ring, 128-byte swizzle), straight out of the q|k|v buffer the GEMM wrote;
-//   warp 1      MMA issuer:  S = Q K^T   (tcgen05.mma M128 N128 K16 x 4, both operands K-major)  -> TMEM S[g]
-//                            O~ = P V     (M128 N64 K16 x 8; A = P from shared memory, B = the V block as it lies in
-//                                          memory = an MN-major operand: no transpose anywhere) -> TMEM O[g]
-//   warps 2-5 / 6-9   two softmax groups taking alternate key blocks (g = block & 1), thread <-> query row (TMEM lane):
-//               two passes over the S tile in TMEM (row max, then exp2 / row sum / bf16 P written to shared memory in the
-//               K-major swizzled operand layout), the running output lives in registers: o = o * corr + O~ with O~ read
-//               back from TMEM one block late, so the P V product of a block overlaps the softmax of the next.
+//   warp 8            the issuer: one thread issues every TMA load (Q tile once; K blocks [128 keys][64 d] into 4 slots,
+//                     V blocks into 3 slots, 128-byte swizzle, straight out of the q|k|v buffer the GEMM wrote) and every
+//                     tcgen05.mma, in the order their preconditions become true:
+//                       S_j = Q K_j^T    M128 N128 K16 x 4, both operands K-major -> TMEM S buffer j % 3, issued three
+//                                        blocks ahead, as soon as the buffer's previous reader is done
+//                       O~_j = P_j V_j   M128 N64 K16 x 8; A = P from shared memory, B = the V block as it lies in
+//                                        memory ([keys][d], d contiguous) = an MN-major operand: no transpose -> TMEM O[g]
+//   warps 0-3 / 4-7   two softmax groups taking alternate key blocks (g = block & 1), thread <-> query row (TMEM lane):
+//                     two passes over the S tile in TMEM (row max; exp2 / row sum / bf16 P written to shared memory in the
+//                     K-major swizzled operand layout), online rescaling in registers: o = o * corr + O~ with O~ read back
+//                     from TMEM one block late, so the P V product of a block overlaps the softmax of the next.
 // The two groups' (m, l, o) states are merged through shared memory at the end (as the mma.sync kernel did).
 // fp32 scores, fp32 online softmax, bf16 P (as before).  Replaces the mma.sync kernel of csrc/s3_attn.cu (kept: CBX_ATTN_TC=0).
+// (A variant in which thread 0 of each softmax group issued its own loads and MMAs — no issuer warp, 255 registers — was
+// slower: the issue sequence sits on the group's critical path.  33.6 vs 32.6 ms per solve.)
 #include "s3_gemm.cuh"
 #include <cstdlib>
 
@@ -21,14 +25,14 @@ namespace cbx {
 namespace {
 
 constexpr int TQ = 128, TK = 128, TD = 64;
-constexpr int NST = 3;                                 // K/V stages
+constexpr int NSK = 4, NST = 3;                        // K slots / V slots (released separately)
+constexpr int NSB = 3;                                 // S tiles in TMEM (3 x 128 columns) + 2 x 64 columns of P V output = 512
 constexpr int TILE_B = TQ * TD * 2;                    // 16 KB: [128][64] bf16
-constexpr int STAGE_B = 2 * TILE_B;                    // K + V
 constexpr int P_B = TQ * TK * 2;                       // 32 KB: two k-blocks of [128][64]
-constexpr int OFF_Q = 0, OFF_ST = TILE_B, OFF_P = OFF_ST + NST * STAGE_B, OFF_ML = OFF_P + 2 * P_B;
+constexpr int OFF_Q = 0, OFF_K = TILE_B, OFF_V = OFF_K + NSK * TILE_B, OFF_P = OFF_V + NST * TILE_B, OFF_ML = OFF_P + 2 * P_B;
 constexpr int OFF_BAR = OFF_ML + TQ * 2 * 4;
-constexpr int ATC_THREADS = 320;
-constexpr int ATC_SMEM = OFF_BAR + 256 + 1024;
+constexpr int ATC_THREADS = 288;       // warps 0-3 / 4-7: the two softmax groups; warp 8: one thread issues every TMA load and MMA
+constexpr int ATC_SMEM = OFF_BAR + 512 + 1024;
 static_assert(TQ * TD * 4 <= P_B, "group-1 output state fits its P buffer");
 
 struct AttnTcParams {
@@ -36,7 +40,14 @@ struct AttnTcParams {
   __nv_bfloat16* out;        // [B][L][512]
   const int* lens;
   int L;
+  unsigned long long* dbg;   // optional %globaltimer stamps of CTA (0, 0, 0) (tools/attn_stamps.py)
 };
+__device__ __forceinline__ unsigned long long atc_gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define ATC_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) p.dbg[k] = atc_gtimer(); } while (0)
 
 __device__ __forceinline__ float ex2f(float x) {
   float y;
@@ -49,211 +60,288 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) 
     if (++spins > (1u << 26)) __trap();
   }
 }
-__device__ __forceinline__ void group_bar(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+template <int ID> __device__ __forceinline__ void group_bar() { asm volatile("bar.sync %0, 128;" ::"n"(ID) : "memory"); }
+
+// TMEM -> registers without the wait: the caller overlaps the load with arithmetic on the previous chunk
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid_constant__ AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sQ = smem + OFF_Q;
+  uint8_t* sK = smem + OFF_K;
+  uint8_t* sV = smem + OFF_V;
   uint8_t* sP = smem + OFF_P;
   float* sML = reinterpret_cast<float*>(smem + OFF_ML);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* bar_q = bars;
-  uint64_t* full = bars + 1;             // [NST]
-  uint64_t* empty = full + NST;          // [NST]
-  uint64_t* s_full = empty + NST;        // [2]
-  uint64_t* s_free = s_full + 2;         // [2]
-  uint64_t* p_full = s_free + 2;         // [2]
-  uint64_t* o_full = p_full + 2;         // [2]
+  uint64_t* k_full = bars + 1;           // [NSK] K block landed
+  uint64_t* v_full = k_full + NSK;       // [NST] V block landed
+  uint64_t* v_free = v_full + NST;       // [NST] its P V product has completed
+  uint64_t* s_full = v_free + NST;       // [NSB] S tile of block j in TMEM buffer j % NSB
+  uint64_t* p_full = s_full + NSB;       // [2]   P of the group's block written, S buffer read (128 arrivals)
+  uint64_t* o_full = p_full + 2;         // [2]   the group's P V product has completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * TQ, head = blockIdx.y, b = blockIdx.z;
   pdl_launch_dependents();
   if (threadIdx.x == 0) {
+    ATC_STAMP(0);
     mbar_init(bar_q, 1);
-    for (int i = 0; i < NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 128); mbar_init(&p_full[i], 128); mbar_init(&o_full[i], 1); }
+    for (int i = 0; i < NSK; ++i) mbar_init(&k_full[i], 1);
+    for (int i = 0; i < NST; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1); }
+    for (int i = 0; i < NSB; ++i) mbar_init(&s_full[i], 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&p_full[i], 128); mbar_init(&o_full[i], 1); }
     mbar_fence_init();
     tma_prefetch_desc(&p.tm);
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 0) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_o = tmem_base + NSB * TK;           // O~[2] behind the S buffers
   const int Lk = p.lens ? min(max(p.lens[b], 1), p.L) : p.L;
   const int nkb = (Lk + TK - 1) / TK;
 
-  if (warp == 0) {
-    if (lane == 0) {
-      pdl_wait();                                  // q|k|v come from the GEMM just before
-      mbar_arrive_expect_tx(bar_q, TILE_B);
-      tma_load_3d(sQ, &p.tm, bar_q, head * TD, q0, b);
-      for (int j = 0; j < nkb; ++j) {
-        const int s = j % NST;
-        if (j >= NST) mbar_wait_sleep(&empty[s], ((j / NST) - 1) & 1);
-        uint8_t* st = smem + OFF_ST + s * STAGE_B;
-        mbar_arrive_expect_tx(&full[s], STAGE_B);
-        tma_load_3d(st, &p.tm, &full[s], 512 + head * TD, j * TK, b);
-        tma_load_3d(st + TILE_B, &p.tm, &full[s], 1024 + head * TD, j * TK, b);
-      }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
+  if (warp == 8) {
+    // ---- the issuer: every TMA load and every tcgen05.mma of the CTA, in the order their preconditions become true ----
     if (lane == 0) {
       const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
       const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
+      auto load_k = [&](int j) {
+        const int s = j % NSK;
+        mbar_arrive_expect_tx(&k_full[s], TILE_B);
+        tma_load_3d(sK + s * TILE_B, &p.tm, &k_full[s], 512 + head * TD, j * TK, b);
+      };
+      auto load_v = [&](int j) {
+        const int s = j % NST;
+        mbar_arrive_expect_tx(&v_full[s], TILE_B);
+        tma_load_3d(sV + s * TILE_B, &p.tm, &v_full[s], 1024 + head * TD, j * TK, b);
+      };
+      const uint64_t dq = umma_desc_k128(smem_u32(sQ));
+      auto issue_s = [&](int j) {            // S_j = Q K_j^T into S buffer j % NSB (the caller knows the buffer is free)
+        const int s = j % NSK, sb = j % NSB;
+        mbar_wait_sleep(&k_full[s], (j / NSK) & 1);
+        tc_fence_after();
+        const uint64_t db = umma_desc_k128(smem_u32(sK + s * TILE_B));
+#pragma unroll
+        for (int k = 0; k < TD / 16; ++k) umma_bf16(tmem_base + sb * TK, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
+        umma_commit(&s_full[sb]);
+      };
+      pdl_wait();                                  // q|k|v come from the GEMM just before
+      ATC_STAMP(1);
+      mbar_arrive_expect_tx(bar_q, TILE_B);
+      tma_load_3d(sQ, &p.tm, bar_q, head * TD, q0, b);
+      for (int j = 0; j < NSK && j < nkb; ++j) { load_k(j); if (j < NST) load_v(j); }
       mbar_wait_sleep(bar_q, 0);
-      for (int j = 0; j <= nkb; ++j) {
-        if (j < nkb) {
-          const int g = j & 1, it = j >> 1, s = j % NST;
-          mbar_wait_sleep(&full[s], (j / NST) & 1);
-          if (it > 0) mbar_wait_sleep(&s_free[g], (it - 1) & 1);
-          tc_fence_after();
-          const uint64_t da = umma_desc_k128(smem_u32(sQ)), db = umma_desc_k128(smem_u32(smem + OFF_ST + s * STAGE_B));
-#pragma unroll
-          for (int k = 0; k < TD / 16; ++k) umma_bf16(tmem_base + g * TK, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
-          umma_commit(&s_full[g]);
+      for (int j = 0; j < NSB && j < nkb; ++j) issue_s(j);
+      for (int j = 0; j < nkb; ++j) {
+        const int g = j & 1, it = j >> 1, s = j % NST;
+        // P_j is in shared memory, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
+        mbar_wait_sleep(&p_full[g], it & 1);
+        if (j + NSK < nkb) load_k(j + NSK);
+        if (j >= 1 && j + 2 < nkb) {             // V slot of block j - 1: its product was issued one iteration ago
+          mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+          load_v(j + 2);
         }
-        if (j >= 1) {
-          const int jj = j - 1, g = jj & 1, it = jj >> 1, s = jj % NST;
-          mbar_wait_sleep(&p_full[g], it & 1);
-          tc_fence_after();
-          const uint32_t pa = smem_u32(sP + g * P_B), va = smem_u32(smem + OFF_ST + s * STAGE_B + TILE_B);
+        mbar_wait_sleep(&v_full[s], (j / NST) & 1);
+        tc_fence_after();
+        const uint32_t pa = smem_u32(sP + g * P_B), va = smem_u32(sV + s * TILE_B);
 #pragma unroll
-          for (int k = 0; k < TK / 16; ++k) {
-            // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
-            const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
-            const uint64_t db = umma_desc_k128(va + k * 2048);
-            umma_bf16(tmem_base + 2 * TK + g * TD, da, db, idesc_o, k != 0);
-          }
-          umma_commit(&o_full[g]);
-          umma_commit(&empty[s]);
+        for (int k = 0; k < TK / 16; ++k) {
+          // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
+          const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
+          const uint64_t db = umma_desc_k128(va + k * 2048);
+          umma_bf16(tmem_o + g * TD, da, db, idesc_o, k != 0);
         }
+        umma_commit(&o_full[g]);
+        umma_commit(&v_free[s]);
+        if (j + NSB < nkb) issue_s(j + NSB);       // into the S buffer block j's group just finished with
       }
     }
     __syncwarp();
   } else {
-    // ---- softmax groups ----
-    const int g = (warp - 2) >> 2, q = warp & 3, row = q * 32 + lane;
-    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    const uint32_t tS = tmem_base + lane_off + g * TK, tO = tmem_base + lane_off + 2 * TK + g * TD;
-    const float sc = 0.125f * 1.4426950408889634f;              // 1/sqrt(64) * log2(e): scores in the log2 domain
-    float m = -INFINITY, l = 0.f, corr_prev = 1.f;
-    float o[TD];
+  const int g = warp >> 2, q = warp & 3, row = q * 32 + lane;
+  const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+  const uint32_t tO = tmem_o + lane_off + g * TD;
+  const float sc = 0.125f * 1.4426950408889634f;              // 1/sqrt(64) * log2(e): scores in the log2 domain
+  float m = -INFINITY, l = 0.f, corr_prev = 1.f;
+  float o[TD];
 #pragma unroll
-    for (int d = 0; d < TD; ++d) o[d] = 0.f;
-    uint8_t* prow = sP + g * P_B + row * 128;
-    int i = 0;
-    for (int j = g; j < nkb; j += 2, ++i) {
-      mbar_wait_sleep(&s_full[g], i & 1);
-      tc_fence_after();
-      const int kbase = j * TK;
-      const bool tail = kbase + TK > Lk;
-      // pass 1: row maximum
-      float mx = -INFINITY;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld32(tS + c * 32, v);
+  for (int d = 0; d < TD; ++d) o[d] = 0.f;
+  uint8_t* prow = sP + g * P_B + row * 128;
+  int i = 0;
+  for (int j = g; j < nkb; j += 2, ++i) {
+    const int sb = j % NSB;
+    const uint32_t tS = tmem_base + lane_off + sb * TK;
+    mbar_wait_sleep(&s_full[sb], (j / NSB) & 1);
+    tc_fence_after();
+    if (threadIdx.x == 0 && i < 4) ATC_STAMP(2 + i * 3);
+    const int kbase = j * TK;
+    const bool tail = kbase + TK > Lk;
+    // pass 1: row maximum, 32-column chunks (the load of chunk c + 1 is in flight while chunk c is reduced)
+    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // four independent chains (2 warps per scheduler:
+    {                                                                  // a 128-long dependent chain would be exposed)
+      uint32_t ra[32], rb[32];
+      auto red = [&](const uint32_t (&r)[32], int c) {
         if (tail) {
 #pragma unroll
-          for (int k = 0; k < 32; ++k) if (kbase + c * 32 + k >= Lk) v[k] = -INFINITY;
+          for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], (kbase + c * 32 + k >= Lk) ? -INFINITY : __uint_as_float(r[k]));
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(r[k]));
         }
-#pragma unroll
-        for (int k = 0; k < 32; ++k) mx = fmaxf(mx, v[k]);
-      }
-      const float m_new = fmaxf(m, mx * sc);
-      const float corr = ex2f(m - m_new);           // first block: exp2(-inf) = 0, and o = l = 0
-      // fold the previous block's P V product into the running output (it has been computing meanwhile); this also
-      // says the P buffer is free again
-      if (i > 0) {
-        mbar_wait_sleep(&o_full[g], (i - 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          float v[32];
-          tmem_ld32(tO + c * 32, v);
-#pragma unroll
-          for (int k = 0; k < 32; ++k) o[c * 32 + k] = fmaf(o[c * 32 + k], corr_prev, v[k]);
-        }
-      }
-      corr_prev = corr;
-      // pass 2: p = exp2(s - m), row sum, bf16 P in the swizzled K-major layout
-      float ls = 0.f;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld32(tS + c * 32, v);
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-          float pv = ex2f(fmaf(v[k], sc, -m_new));
-          if (tail && kbase + c * 32 + k >= Lk) pv = 0.f;
-          v[k] = pv; ls += pv;
-        }
-        uint8_t* pk = prow + (c >> 1) * TILE_B;
-#pragma unroll
-        for (int jc = 0; jc < 4; ++jc) {
-          const uint4 w = make_uint4(pack_bf16x2(v[jc * 8], v[jc * 8 + 1]), pack_bf16x2(v[jc * 8 + 2], v[jc * 8 + 3]),
-                                     pack_bf16x2(v[jc * 8 + 4], v[jc * 8 + 5]), pack_bf16x2(v[jc * 8 + 6], v[jc * 8 + 7]));
-          *reinterpret_cast<uint4*>(pk + ((((c & 1) * 4 + jc) ^ (row & 7)) << 4)) = w;
-        }
-      }
-      l = l * corr + ls;
-      m = m_new;
-      tc_fence_before();
-      mbar_arrive(&s_free[g]);                                          // S[g] may be overwritten
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // P visible to the tensor core
-      mbar_arrive(&p_full[g]);
+      };
+      tmem_ld32_issue(tS, ra);
+      tmem_ld_wait();
+      tmem_ld32_issue(tS + 32, rb);
+      red(ra, 0);
+      tmem_ld_wait();
+      tmem_ld32_issue(tS + 64, ra);
+      red(rb, 1);
+      tmem_ld_wait();
+      tmem_ld32_issue(tS + 96, rb);
+      red(ra, 2);
+      tmem_ld_wait();
+      red(rb, 3);
     }
+    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+    const float m_new = fmaxf(m, mx * sc);
+    const float corr = ex2f(m - m_new);           // first block: exp2(-inf) = 0, and o = l = 0
+    // fold the previous block's P V product into the running output (it has been computing meanwhile); its completion
+    // also frees the group's P buffer
     if (i > 0) {
       mbar_wait_sleep(&o_full[g], (i - 1) & 1);
       tc_fence_after();
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        float v[32];
-        tmem_ld32(tO + c * 32, v);
+        uint32_t r[32];
+        tmem_ld32_issue(tO + c * 32, r);
+        tmem_ld_wait();
 #pragma unroll
-        for (int k = 0; k < 32; ++k) o[c * 32 + k] = fmaf(o[c * 32 + k], corr_prev, v[k]);
+        for (int k = 0; k < 32; ++k) o[c * 32 + k] = fmaf(o[c * 32 + k], corr_prev, __uint_as_float(r[k]));
       }
     }
-    tc_fence_before();
-    // ---- merge group 1 into group 0 (group 1's P buffer is idle: its last product has completed) ----
-    float* xo = reinterpret_cast<float*>(sP + P_B);           // [64 d][128 rows]
-    if (g == 1) {
+    corr_prev = corr;
+    if (threadIdx.x == 0 && i < 4) ATC_STAMP(3 + i * 3);
+    // pass 2: p = exp2(s - m), row sum, bf16 P in the swizzled K-major layout
+    float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+    {
+      uint32_t ra[32], rb[32];
+      auto emit = [&](uint32_t (&r)[32], int c) {
+        uint8_t* pk = prow + (c >> 1) * TILE_B;
+        if (tail) {          // keys past the row's length: exp2(-inf) = 0
 #pragma unroll
-      for (int d = 0; d < TD; ++d) xo[d * TQ + row] = o[d];
-      sML[row * 2] = m; sML[row * 2 + 1] = l;
-    }
-    asm volatile("bar.sync 2, 256;" ::: "memory");
-    if (g == 0) {
-      const float m1 = sML[row * 2], l1 = sML[row * 2 + 1];
-      const float mn = fmaxf(m, m1);
-      const float c0 = (m == -INFINITY) ? 0.f : ex2f(m - mn), c1 = (m1 == -INFINITY) ? 0.f : ex2f(m1 - mn);
-      const float inv = 1.0f / (l * c0 + l1 * c1);
-      const int t = q0 + row;
-      if (t < p.L) {
-        __nv_bfloat16* dst = p.out + ((size_t)b * p.L + t) * 512 + head * TD;
-#pragma unroll
-        for (int d8 = 0; d8 < TD / 8; ++d8) {
-          float y[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) y[e] = (o[d8 * 8 + e] * c0 + xo[(d8 * 8 + e) * TQ + row] * c1) * inv;
-          *reinterpret_cast<uint4*>(dst + d8 * 8) = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]),
-                                                               pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
+          for (int k = 0; k < 32; ++k) if (kbase + c * 32 + k >= Lk) r[k] = 0xff800000u;
         }
+#pragma unroll
+        for (int jc = 0; jc < 4; ++jc) {
+          uint32_t w[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int k = jc * 8 + e * 2;
+            const float p0 = ex2f(fmaf(__uint_as_float(r[k]), sc, -m_new)), p1 = ex2f(fmaf(__uint_as_float(r[k + 1]), sc, -m_new));
+            ls4[e] += p0 + p1;
+            w[e] = pack_bf16x2(p0, p1);
+          }
+          *reinterpret_cast<uint4*>(pk + ((((c & 1) * 4 + jc) ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      };
+      tmem_ld32_issue(tS, ra);
+      tmem_ld_wait();
+      tmem_ld32_issue(tS + 32, rb);
+      emit(ra, 0);
+      tmem_ld_wait();
+      tmem_ld32_issue(tS + 64, ra);
+      emit(rb, 1);
+      tmem_ld_wait();
+      tmem_ld32_issue(tS + 96, rb);
+      emit(ra, 2);
+      tmem_ld_wait();
+      emit(rb, 3);
+    }
+    l = l * corr + ((ls4[0] + ls4[1]) + (ls4[2] + ls4[3]));
+    m = m_new;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // P visible to the tensor core
+    tc_fence_before();
+    mbar_arrive(&p_full[g]);          // P row written, and this thread is done with the S buffer
+    if (threadIdx.x == 0 && i < 4) ATC_STAMP(4 + i * 3);
+  }
+  if (i > 0) {
+    mbar_wait_sleep(&o_full[g], (i - 1) & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      float v[32];
+      tmem_ld32(tO + c * 32, v);
+#pragma unroll
+      for (int k = 0; k < 32; ++k) o[c * 32 + k] = fmaf(o[c * 32 + k], corr_prev, v[k]);
+    }
+  }
+  tc_fence_before();
+  if (threadIdx.x == 0) ATC_STAMP(14);
+  // ---- merge group 1 into group 0 (group 1's P buffer is idle: its last product has completed) ----
+  float* xo = reinterpret_cast<float*>(sP + P_B);           // [64 d][128 rows]
+  if (g == 1) {
+#pragma unroll
+    for (int d = 0; d < TD; ++d) xo[d * TQ + row] = o[d];
+    sML[row * 2] = m; sML[row * 2 + 1] = l;
+  }
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+  if (g == 0) {
+    const float m1 = sML[row * 2], l1 = sML[row * 2 + 1];
+    const float mn = fmaxf(m, m1);
+    const float c0 = (m == -INFINITY) ? 0.f : ex2f(m - mn), c1 = (m1 == -INFINITY) ? 0.f : ex2f(m1 - mn);
+    const float inv = 1.0f / (l * c0 + l1 * c1);
+    const int t = q0 + row;
+    if (t < p.L) {
+      __nv_bfloat16* dst = p.out + ((size_t)b * p.L + t) * 512 + head * TD;
+#pragma unroll
+      for (int d8 = 0; d8 < TD / 8; ++d8) {
+        float y[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y[e] = (o[d8 * 8 + e] * c0 + xo[(d8 * 8 + e) * TQ + row] * c1) * inv;
+        *reinterpret_cast<uint4*>(dst + d8 * 8) = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]),
+                                                             pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
       }
     }
   }
+  }
   __syncthreads();
-  if (warp == 1) {
+  if (threadIdx.x == 0) ATC_STAMP(15);
+  if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
 }
 
 }  // namespace
+
+static unsigned long long* g_atc_dbg = nullptr;
+void attn_tc_set_debug(unsigned long long* buf) { g_atc_dbg = buf; }
 
 int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st) {
   CBX_CHECK(ld_qkv == 1536, "s3_attn_tc: q|k|v row stride %d (expected 1536)", ld_qkv);
@@ -262,6 +350,8 @@ int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L
   AttnTcParams p;
   if (make_tmap_bf16_3d(&p.tm, qkv, 1536, L, B, 1536, (uint64_t)1536 * L, TD, TQ)) return CBX_ERR;
   p.out = out; p.lens = lens; p.L = L;
+  p.dbg = g_atc_dbg;
+  if (g_atc_dbg) g_atc_dbg += 16;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((L + TQ - 1) / TQ, 8, B); cfg.blockDim = dim3(ATC_THREADS); cfg.dynamicSmemBytes = ATC_SMEM; cfg.stream = st;
   cudaLaunchAttribute at[1];

@@ -469,6 +469,8 @@ extern "C" int cbx_dbg_s3_attn(const void* qkv, void* out, int B, int L, const i
   if (tc) return cbx::s3_attn_tc_launch(q, o, B, L, 1536, lens, static_cast<cudaStream_t>(stream));
   return cbx::s3_attn_launch_mma(q, o, B, L, 1536, lens, static_cast<cudaStream_t>(stream));
 }
+namespace cbx { void attn_tc_set_debug(unsigned long long* buf); }
+extern "C" int cbx_dbg_attn_stamps(unsigned long long* buf) { cbx::attn_tc_set_debug(buf); return 0; }
 extern "C" int cbx_dbg_ffn_stamps(unsigned long long* buf) { cbx::ffn_set_debug(buf); return 0; }
 
 extern "C" int cbx_cfm_cache_sizes(cbx_cfm* h, int32_t* n_graphs, int32_t* n_plans) {
