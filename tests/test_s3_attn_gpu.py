@@ -52,6 +52,23 @@ def test_attention_matches_fp32_torch(tc, B, L, lens):
     assert rel < 6e-3 and mx < 2e-2
 
 
+def test_late_key_blocks_far_above_the_running_maximum():
+    """Online-softmax rescaling across key blocks: scores that jump by hundreds from one 128-key block to the next (and fall
+    again) exercise the running-maximum correction of the block-late P V fold in both kernels."""
+    g = torch.Generator().manual_seed(11)
+    qkv = torch.randn(2, 700, 1536, generator=g)
+    qkv[:, 300:, 512:1024] *= 40.0            # keys of blocks >= 2: scores ~ 40 x larger
+    qkv[:, 600:, 512:1024] *= 0.01            # and small again in the last block
+    qkv = qkv.to(torch.bfloat16).cuda()
+    want = _ref(qkv, None)
+    for tc in (1, 0):
+        got = _run(qkv, None, tc).float()
+        assert torch.isfinite(got).all()
+        rel = float((got - want).norm() / want.norm())
+        print(f"{'tcgen05' if tc else 'mma.sync'} attention, score jumps between key blocks: rel-L2 {rel:.2e}")
+        assert rel < 6e-3
+
+
 def test_tcgen05_and_mma_kernels_agree_and_repeat():
     g = torch.Generator().manual_seed(3)
     qkv = torch.randn(2, 812, 1536, generator=g).to(torch.bfloat16).cuda()
