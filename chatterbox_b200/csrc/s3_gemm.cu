@@ -63,11 +63,12 @@ constexpr int MAX_SPLIT = 4;                         // largest split-K cluster
 constexpr int EPI_R = 2;                             // rows per epilogue iteration and warp
 enum { PAR_BIAS = 0, PAR_G1, PAR_B1, PAR_TEMB, PAR_G2, PAR_B2, PAR_ALPHA, PAR_COUNT };   // per-column epilogue vectors
 constexpr int PAR_BYTES = PAR_COUNT * 256 * 4;
-constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + PAR_BYTES;
+constexpr int STAT_BYTES = MAX_SPLIT * BM * 2 * 4;   // N-split LayerNorm: per-row (sum, sum of squares) pushed by every CTA of the cluster
+constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + PAR_BYTES + STAT_BYTES;
 
 struct GemmParams {
   CUtensorMap tmA, tmW;
-  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out, ksplit, hilo;
+  int B, L, N, K, taps, n_tile, tiles_l, dil, pad, M_out, ksplit, hilo, nsplit;
   int nstages, stage_bytes;   // ring geometry: stage = A tile (16 KB) + W tile (n_tile x 128 B), 1024-byte aligned
   GemmEpi e;
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0,0) (debug aid)
@@ -110,7 +111,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   uint64_t* accum_bar = empty + MAX_STAGES;
   const int NS = p.nstages, SB = p.stage_bytes;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  uint64_t* stat_bar = accum_bar + 2;        // N-split: 16 warps x NSP CTAs arrive once their row moments are in our shared memory
   float* par = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
+  float2* stat = reinterpret_cast<float2*>(smem + STAGES * STAGE_BYTES + 256 + PAR_BYTES);
   float* tile = reinterpret_cast<float*>(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -121,6 +124,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   // split-K over a cluster (1, 1, S): CTA `rank` accumulates K panels [kb0, kb0 + nkb) of the tile into its own
   // TMEM, the partial tiles meet in distributed shared memory and each CTA finishes 128 / S rows of the tile
   const int S = p.ksplit, rank = blockIdx.z;
+  const int NSP = p.nsplit;                  // N-split cluster (1, NSP, 1): LayerNorm moments are exchanged, S == 1
   // hi/lo mode (T3): a k-block is ONE weight panel and BOTH activation planes (hi, lo) multiplied against it
   const int kpb = p.K / BK, nkb_all = p.hilo ? kpb : p.taps * kpb;
   const uint32_t w_bytes = (uint32_t)p.n_tile * BK * 2;
@@ -133,6 +137,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(accum_bar, 1);
+    mbar_init(stat_bar, p.nsplit > 1 ? 16 * p.nsplit : 1);
     mbar_fence_init();
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmW);
@@ -142,6 +147,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // N-split: peers push into our shared memory / arrive on stat_bar later; they may only do so once it is initialised.
+  // Arrive now, wait just before the first remote access (the barrier completes somewhere behind the main loop).
+  if (p.nsplit > 1) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   if (threadIdx.x == 0) GEMM_STAMP(1);
   // PDL: everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel.  Warp 0 goes on to
   // issue the WEIGHT panels (constant data) before it waits; every other warp waits here, before its first read of
@@ -175,7 +183,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   };
 #pragma unroll
   for (int rr = 0; rr < EPI_R; ++rr) { rvn[rr][0] = make_float4(0.f, 0.f, 0.f, 0.f); rvn[rr][1] = rvn[rr][0]; }
-  if (has_resid && warp != 0) load_resid(row_base + warp * rpw);
+  if (has_resid && warp != 0 && NSP == 1) load_resid(row_base + warp * rpw);
+  // N-split ownership: thread <-> (row 8 warp + lane / 4, 16 columns): its residual values are requested now
+  float4 nres[4];
+  const int ns_r = warp * 8 + (lane >> 2), ns_c0 = (lane & 3) * 16;
+  const bool ns_ok = t0 + ns_r < p.M_out;
+  const size_t ns_gr = (size_t)b * p.M_out + (ns_ok ? t0 + ns_r : 0);
+  auto ns_prefetch = [&]() {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      nres[i] = (has_resid && ns_ok) ? *reinterpret_cast<const float4*>(e.resid + ns_gr * e.ld_resid + n0 + ns_c0 + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  };
+  if (NSP > 1 && warp != 0) ns_prefetch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -188,9 +207,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
         tma_load_3d(smem + i * SB + A_BYTES, &p.tmW, &full[i], kb * BK, n0, 0);
       }
       pdl_wait();
+      GEMM_STAMP(11);
+      // ring slot / phase and (tap, k-block-in-tap) advance as counters: this loop is one thread's serial code, a runtime
+      // integer division per index costs ~0.1 us per k-block on the critical path
+      int s = 0, ph = 0, tap = kb0 / kpb, kk = kb0 % kpb;
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % NS, ph = (i / NS) & 1, kb = kb0 + i;
-        const int tap = kb / kpb, kk = kb % kpb;
+        const int kb = kb0 + i;
         uint8_t* sa = smem + s * SB;
         if (i >= npre) {
           mbar_wait_spin(&empty[s], ph ^ 1);
@@ -201,14 +223,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
           tma_load_3d(sa, &p.tmA, &full[s], kb * BK, t0, 0);
           tma_load_3d(sa + A_BYTES + w_bytes, &p.tmA, &full[s], kb * BK, t0, 1);
         } else tma_load_3d(sa, &p.tmA, &full[s], kk * BK, t0 + tap * p.dil - p.pad, b);
+        if (++s == NS) { s = 0; ph ^= 1; }
+        if (++kk == kpb) { kk = 0; ++tap; }
       }
       GEMM_STAMP(2);
     }
+    if (NSP > 1) { __syncwarp(); pdl_wait(); ns_prefetch(); }      // the producer warp's own residual rows, once its loads are out
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(BM, p.n_tile);
+      int s = 0, ph = 0;
       for (int kb = 0; kb < nkb; ++kb) {      // kb: local panel index
-        const int s = kb % NS, ph = (kb / NS) & 1;
         mbar_wait_spin(&full[s], ph);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + s * SB);
@@ -222,6 +247,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
           for (int k = 0; k < BK / 16; ++k) umma_bf16(tmem_base, da1 + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, 1u);
         }
         umma_commit(&empty[s]);
+        if (++s == NS) { s = 0; ph ^= 1; }
       }
       umma_commit(accum_bar);
       GEMM_STAMP(3);
@@ -281,17 +307,124 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   __syncwarp();
   if (S > 1) cluster_sync_all(); else __syncthreads();
   if (threadIdx.x == 64) GEMM_STAMP(8);
+  const float inv_n = 1.0f / (float)(p.n_tile * NSP);
   // ===== epilogue, phase 2 (all 16 warps): warp <-> 8 rows, lanes across float4 column groups (lane, lane + 32),
   // two rows per iteration of a ROLLED loop (the body is executed cold once per CTA, so instruction fetch — not
   // issue — is what a large unrolled body costs); the residual rows of the next iteration are loaded one
   // iteration ahead, the first pair before the barrier (behind the main loop).  Every mode test is on a kernel
   // parameter, hoisted out of the element loops. =====
-  {
+  if (NSP > 1) {
+    // ===== N-split epilogue (cluster (1, NSP, 1), n_tile = 64): the LayerNorm of a row spans the NSP column tiles of the
+    // cluster.  A thread keeps its 16 values of the tile in registers (row = 8 warp + lane / 4, columns 16 (lane % 4) ...):
+    // partial (sum, sum of squares) over this CTA's 64 columns are PUSHED into every CTA of the cluster (st.shared::cluster) and
+    // announced by a remote mbarrier arrive; a CTA waits on its own mbarrier, adds the NSP partial moments from its own shared
+    // memory, normalises and stores.  Nothing is read twice, no cluster barrier on the path, no trailing barrier before exit
+    // (a peer writes here only before its arrive, and we leave only after all arrives). =====
+    if constexpr ((FEAT & (F_LN1 | F_LN2)) != 0) {
+      const int r = ns_r, c0 = ns_c0;
+      const bool ok = ns_ok;
+      const size_t gr = ns_gr;
+      float v[16];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 a = *reinterpret_cast<const float4*>(tile + (size_t)r * pitch + c0 + 4 * i);
+        const float4 bb = *reinterpret_cast<const float4*>(par + PAR_BIAS * 256 + c0 + 4 * i);
+        v[4 * i] = a.x + bb.x; v[4 * i + 1] = a.y + bb.y; v[4 * i + 2] = a.z + bb.z; v[4 * i + 3] = a.w + bb.w;
+      }
+      auto add_res = [&]() {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { v[4 * i] += nres[i].x; v[4 * i + 1] += nres[i].y; v[4 * i + 2] += nres[i].z; v[4 * i + 3] += nres[i].w; }
+      };
+      auto store_out = [&]() {
+        if (has_f32 && ok) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<float4*>(e.out_f32 + gr * e.ld_f32 + n0 + c0 + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        if (has_bf16 && ok) {
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+            *reinterpret_cast<uint4*>(e.out_bf16 + gr * e.ld_bf16 + n0 + c0 + 8 * i) =
+                make_uint4(pack_bf16x2(v[8 * i], v[8 * i + 1]), pack_bf16x2(v[8 * i + 2], v[8 * i + 3]),
+                           pack_bf16x2(v[8 * i + 4], v[8 * i + 5]), pack_bf16x2(v[8 * i + 6], v[8 * i + 7]));
+        }
+      };
+      if (!has_ln1) {          // LayerNorm of the final value: residual adds first
+        if (has_resid) add_res();
+        if (has_resid2 && ok) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 a = *reinterpret_cast<const float4*>(e.resid2 + gr * e.ld_resid2 + n0 + c0 + 4 * i);
+            v[4 * i] += a.x; v[4 * i + 1] += a.y; v[4 * i + 2] += a.z; v[4 * i + 3] += a.w;
+          }
+        }
+      }
+      float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 16; ++k) { s1 += v[k]; s2 += v[k] * v[k]; }
+      s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, 2); s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
+      // push the row's partial moments into every CTA of the cluster (slot = our rank), then one arrive per warp and peer
+      asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");        // every peer's stat_bar is initialised
+      const int my = blockIdx.y % NSP;
+      if ((lane & 3) == 0) {
+        const uint32_t la = smem_u32(&stat[my * BM + r]);
+        for (int j = 0; j < NSP; ++j)
+          asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(dsmem_addr(la, (uint32_t)j)), "f"(s1), "f"(s2) : "memory");
+      }
+      __syncwarp();
+      if (lane == 0) {
+        const uint32_t lb = smem_u32(stat_bar);
+        for (int j = 0; j < NSP; ++j)
+          asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(dsmem_addr(lb, (uint32_t)j)) : "memory");
+      }
+      if (!has_ln1) store_out();          // the fp32 / bf16 copies of the un-normalised value leave while the moments travel
+      {
+        unsigned spins = 0;
+        uint32_t done = 0;
+        while (!done) {
+          asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                       : "=r"(done) : "r"(smem_u32(stat_bar)), "r"(0u) : "memory");
+          if (++spins > (1u << 26)) __trap();
+        }
+      }
+      s1 = 0.f; s2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < MAX_SPLIT; ++j)
+        if (j < NSP) { const float2 m2 = stat[j * BM + r]; s1 += m2.x; s2 += m2.y; }
+      const float mean = s1 * inv_n;
+      const float rstd = rsqrtf(fmaxf(s2 * inv_n - mean * mean, 0.f) + 1e-5f);
+      if (has_ln1) {           // LayerNorm + Mish (+ time embedding) -> bf16 and / or fp32
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 g4 = *reinterpret_cast<const float4*>(par + PAR_G1 * 256 + c0 + 4 * i);
+          const float4 b4 = *reinterpret_cast<const float4*>(par + PAR_B1 * 256 + c0 + 4 * i);
+          const float4 t4 = *reinterpret_cast<const float4*>(par + PAR_TEMB * 256 + c0 + 4 * i);
+          v[4 * i] = mish_f((v[4 * i] - mean) * rstd * g4.x + b4.x) + t4.x;
+          v[4 * i + 1] = mish_f((v[4 * i + 1] - mean) * rstd * g4.y + b4.y) + t4.y;
+          v[4 * i + 2] = mish_f((v[4 * i + 2] - mean) * rstd * g4.z + b4.z) + t4.z;
+          v[4 * i + 3] = mish_f((v[4 * i + 3] - mean) * rstd * g4.w + b4.w) + t4.w;
+        }
+        if (has_resid) add_res();
+        store_out();
+      } else if (has_ln2 && ok) {
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 g4 = *reinterpret_cast<const float4*>(par + PAR_G2 * 256 + c0 + 4 * i);
+          const float4 b4 = *reinterpret_cast<const float4*>(par + PAR_B2 * 256 + c0 + 4 * i);
+          w[2 * i] = pack_bf16x2((v[4 * i] - mean) * rstd * g4.x + b4.x, (v[4 * i + 1] - mean) * rstd * g4.y + b4.y);
+          w[2 * i + 1] = pack_bf16x2((v[4 * i + 2] - mean) * rstd * g4.z + b4.z, (v[4 * i + 3] - mean) * rstd * g4.w + b4.w);
+        }
+        *reinterpret_cast<uint4*>(e.out_ln + gr * e.ld_ln + n0 + c0) = make_uint4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<uint4*>(e.out_ln + gr * e.ld_ln + n0 + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+      }
+    }
+  } else {
     if (warp == 0) {            // the producer warp skipped the early residual prefetch (it was issuing TMA loads)
       pdl_wait();
       if (has_resid) load_resid(row_base);
     }
-    const float inv_n = 1.0f / (float)p.n_tile;
     float4 bias4[2];
 #pragma unroll
     for (int i = 0; i < 2; ++i) bias4[i] = g_ok[i] ? *reinterpret_cast<const float4*>(par + PAR_BIAS * 256 + gcol[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -511,7 +644,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   }
   if (threadIdx.x == 64) GEMM_STAMP(6);
   __syncwarp();
-  if (S > 1) cluster_sync_all(); else __syncthreads();     // peers may still be reading this CTA's partial tile
+  if (S > 1) cluster_sync_all(); else __syncthreads();     // split-K: peers may still be reading this CTA's partial tile
   if (threadIdx.x == 0) GEMM_STAMP(7);
   if (warp == 1) {
     tc_fence_after();
@@ -533,14 +666,25 @@ int gemm_make_conv(GemmDesc* d, const __nv_bfloat16* A, int lda, const __nv_bflo
   for (int c = 256; c >= 16; c -= 16) if (N % c == 0) { n_tile = c; break; }
   CBX_CHECK(n_tile > 0, "gemm_make: N=%d unsupported (needs a divisor that is a multiple of 16, <= 256)", N);
   CBX_CHECK(B == 1 || M_out == L, "gemm_make: M_out != L needs B == 1");
-  CBX_CHECK(!(epi.ln_g || epi.out_ln) || n_tile == N, "gemm_make: row LayerNorm needs the whole row in one tile (N=%d)", N);
+  // a row LayerNorm over N = 256 channels: four 64-column tiles in one cluster exchange the row moments (every SM ingests
+  // a quarter of the weight panel and drains a quarter of the tile; no split-K partial tiles through DSMEM).
+  // CBX_GEMM_NSPLIT=1 restores the full-row tile + split-K form.
+  static const int nsplit_max = [] { const char* v = getenv("CBX_GEMM_NSPLIT"); return v ? atoi(v) : 4; }();
+  d->nsplit = 1;
+  const bool simple_epi = !epi.swiglu && !epi.out_hilo && !epi.gelu && !epi.elu && !epi.snake_alpha && epi.lrelu == 0.f &&
+                          epi.out_shift == 0 && epi.out_limit == 0 && epi.bias_mod == 0;
+  if ((epi.ln_g != nullptr) != (epi.out_ln != nullptr) && n_tile == N && N == 256 && nsplit_max == 4 && simple_epi &&
+      B * ((M_out + BM - 1) / BM) * nsplit_max <= 296) {
+    d->nsplit = nsplit_max; n_tile = N / nsplit_max;
+  }
+  CBX_CHECK(!(epi.ln_g || epi.out_ln) || n_tile * d->nsplit == N, "gemm_make: row LayerNorm needs the whole row in one tile / cluster (N=%d)", N);
     d->B = B; d->L = L; d->N = N; d->K = K; d->taps = taps; d->n_tile = n_tile; d->epi = epi;
   d->dil = dil; d->pad = pad; d->M_out = M_out; d->hilo = 0;
   // few output tiles (the estimator's 2 x ceil(L / 128) row tiles): spread the K panels of each tile over a cluster
   const int tiles = B * ((M_out + BM - 1) / BM) * (N / n_tile), nkb_all = taps * (K / BK);
   d->ksplit = 1;
   static const int max_split = [] { const char* v = getenv("CBX_GEMM_KSPLIT"); return v ? atoi(v) : 2; }();
-  for (int sp = max_split; sp >= 2; sp >>= 1)
+  for (int sp = max_split; sp >= 2 && d->nsplit == 1; sp >>= 1)
     if (nkb_all >= sp && tiles * sp <= 148) { d->ksplit = sp; break; }
   if (make_tmap_bf16_3d(&d->tmA, A, K, L, B, lda, (uint64_t)lda * L, BK, BM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW, W, (uint64_t)taps * K, N, 1, (uint64_t)taps * K, (uint64_t)taps * K * N, BK, n_tile)) return CBX_ERR;
@@ -563,7 +707,7 @@ int gemm_make_hilo_ex(GemmDesc* d, const __nv_bfloat16* A, int lda, long long pl
   CBX_CHECK(!epi.swiglu || n_tile == 256, "gemm_make_hilo: SwiGLU pairs the halves of a 256-column tile (N=%d)", N);
   CBX_CHECK(!epi.ln_g && !epi.out_ln, "gemm_make_hilo: no row LayerNorm on this path");
   d->B = 1; d->L = M; d->N = N; d->K = K; d->taps = 1; d->n_tile = n_tile; d->epi = epi;
-  d->dil = 0; d->pad = 0; d->M_out = M; d->hilo = 1;
+  d->dil = 0; d->pad = 0; d->M_out = M; d->hilo = 1; d->nsplit = 1;
   const int tiles = ((M + BM - 1) / BM) * (N / n_tile), nkb_all = K / BK;
   d->ksplit = 1;
   if (ksplit_req > 0) {
@@ -614,9 +758,9 @@ int launch_as(const GemmParams& p, dim3 grid, cudaStream_t st) {
   cfg.gridDim = grid; cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = GEMM_SMEM; cfg.stream = st;
   cudaLaunchAttribute at[2];
   int na = 0;
-  if (grid.z > 1) {
+  if (grid.z > 1 || p.nsplit > 1) {
     at[na].id = cudaLaunchAttributeClusterDimension;
-    at[na].val.clusterDim.x = 1; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = grid.z;
+    at[na].val.clusterDim.x = 1; at[na].val.clusterDim.y = p.nsplit; at[na].val.clusterDim.z = grid.z;
     ++na;
   }
   if (pdl_enabled()) {
@@ -642,7 +786,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t st) {
   GemmParams p;
   p.tmA = d.tmA; p.tmW = d.tmW;
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;
-  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit; p.hilo = d.hilo;
+  p.dil = d.dil; p.pad = d.pad; p.M_out = d.M_out; p.ksplit = d.ksplit; p.hilo = d.hilo; p.nsplit = d.nsplit;
   p.tiles_l = (d.M_out + BM - 1) / BM;
   p.stage_bytes = ((d.hilo ? 2 : 1) * A_BYTES + d.n_tile * BK * 2 + 1023) / 1024 * 1024;   // swizzled tiles start 1024-byte aligned
   p.nstages = (STAGES * STAGE_BYTES) / p.stage_bytes;

@@ -35,6 +35,8 @@ struct GemmDesc {
   CUtensorMap tmW;     // bf16 [N][taps*K], box {64, n_tile, 1}
   int B, L, N, K, taps, n_tile, dil, pad, M_out;
   int ksplit;          // CTAs per cluster sharing one output tile, each accumulating 1/ksplit of the K panels
+  int nsplit;          // > 1: the N / n_tile column tiles of a row tile form one cluster; a row LayerNorm exchanges its
+                       // per-row moments through distributed shared memory (no K split in this mode)
   int hilo;            // A is two planes (tensor-map dim 2): tap t reads plane t against the SAME W panel
   GemmEpi epi;
 };
