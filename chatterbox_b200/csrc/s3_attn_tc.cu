@@ -50,9 +50,13 @@ __device__ __forceinline__ unsigned long long atc_gtimer() {
 #define ATC_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) p.dbg[k] = atc_gtimer(); } while (0)
 
 __device__ __forceinline__ float ex2f(float x) {
+#ifdef ATC_ABL_NOEX2
+  return x * 0.001f + 1.0f;
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
   unsigned spins = 0;
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
   uint64_t* v_full = k_full + NSK;       // [NST] V block landed
   uint64_t* v_free = v_full + NST;       // [NST] its P V product has completed
   uint64_t* s_full = v_free + NST;       // [NSB] S tile of block j in TMEM buffer j % NSB
-  uint64_t* p_full = s_full + NSB;       // [2]   P of the group's block written, S buffer read (128 arrivals)
+  uint64_t* p_full = s_full + NSB;       // [2]   P of the group's block written, S buffer read (4 arrivals: one per warp)
   uint64_t* o_full = p_full + 2;         // [2]   the group's P V product has completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
@@ -113,7 +117,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
     for (int i = 0; i < NSK; ++i) mbar_init(&k_full[i], 1);
     for (int i = 0; i < NST; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1); }
     for (int i = 0; i < NSB; ++i) mbar_init(&s_full[i], 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&p_full[i], 128); mbar_init(&o_full[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
     mbar_fence_init();
     tma_prefetch_desc(&p.tm);
   }
@@ -199,7 +203,9 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
     const uint32_t tS = tmem_base + lane_off + sb * TK;
     mbar_wait_sleep(&s_full[sb], (j / NSB) & 1);
     tc_fence_after();
-    if (threadIdx.x == 0 && i < 4) ATC_STAMP(2 + i * 3);
+    if (threadIdx.x == 0 && i == 1) ATC_STAMP(2);
+    if (threadIdx.x == 0 && i == 2) ATC_STAMP(10);
+    if (threadIdx.x == 0 && i == 3) ATC_STAMP(11);
     const int kbase = j * TK;
     const bool tail = kbase + TK > Lk;
     // pass 1: row maximum, 32-column chunks (the load of chunk c + 1 is in flight while chunk c is reduced)
@@ -215,6 +221,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
           for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(r[k]));
         }
       };
+#ifndef ATC_ABL_NOPASS1      // timing-only ablation builds (results are garbage): -DATC_ABL_NOPASS1 / -DATC_ABL_NOEX2 / -DATC_ABL_NOFOLD
       tmem_ld32_issue(tS, ra);
       tmem_ld_wait();
       tmem_ld32_issue(tS + 32, rb);
@@ -227,8 +234,12 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
       red(ra, 2);
       tmem_ld_wait();
       red(rb, 3);
+#else
+      mx4[0] = 8.f;
+#endif
     }
     const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+    if (threadIdx.x == 0 && i == 1) ATC_STAMP(3);
     const float m_new = fmaxf(m, mx * sc);
     const float corr = ex2f(m - m_new);           // first block: exp2(-inf) = 0, and o = l = 0
     // fold the previous block's P V product into the running output (it has been computing meanwhile); its completion
@@ -236,6 +247,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
     if (i > 0) {
       mbar_wait_sleep(&o_full[g], (i - 1) & 1);
       tc_fence_after();
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(4);
+#ifndef ATC_ABL_NOFOLD
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
@@ -244,9 +257,10 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
 #pragma unroll
         for (int k = 0; k < 32; ++k) o[c * 32 + k] = fmaf(o[c * 32 + k], corr_prev, __uint_as_float(r[k]));
       }
+#endif
     }
     corr_prev = corr;
-    if (threadIdx.x == 0 && i < 4) ATC_STAMP(3 + i * 3);
+    if (threadIdx.x == 0 && i == 1) ATC_STAMP(5);
     // pass 2: p = exp2(s - m), row sum, bf16 P in the swizzled K-major layout
     float ls4[4] = {0.f, 0.f, 0.f, 0.f};
     {
@@ -283,12 +297,15 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
       tmem_ld_wait();
       emit(rb, 3);
     }
+    if (threadIdx.x == 0 && i == 1) { if (ls4[0] == 123.456f) ATC_STAMP(12); ATC_STAMP(6); }
     l = l * corr + ((ls4[0] + ls4[1]) + (ls4[2] + ls4[3]));
     m = m_new;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // P visible to the tensor core
+    if (threadIdx.x == 0 && i == 1) ATC_STAMP(7);
     tc_fence_before();
-    mbar_arrive(&p_full[g]);          // P row written, and this thread is done with the S buffer
-    if (threadIdx.x == 0 && i < 4) ATC_STAMP(4 + i * 3);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&p_full[g]);    // one arrive per warp: 32 P rows written, and the warp is done with the S buffer
+    if (threadIdx.x == 0 && i == 1) ATC_STAMP(8);
   }
   if (i > 0) {
     mbar_wait_sleep(&o_full[g], (i - 1) & 1);

@@ -62,6 +62,11 @@ constexpr int VPL = 1024 / NCONS_WARPS / 16;   // consecutive k one lane owns (8
 static_assert(VPL == 8 || VPL == 4, "T3_KW must be 8 or 16");
 constexpr int NCONS = NCONS_WARPS * 32;   // consumer threads
 constexpr int NTHREADS = NCONS;
+#define T3_STR_(x) #x
+#define T3_STR(x) T3_STR_(x)
+#ifndef T3_ATT_UNROLL
+#define T3_ATT_UNROLL 2                  // unroll of the tile attention's row loops (1 = rolled, as in round 1)
+#endif
 #ifndef T3_MAXS
 #define T3_MAXS 4
 #endif
@@ -838,7 +843,7 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
       const float4 t4 = *reinterpret_cast<const float4*>(q_s + qd * 16 + e);
       qv[e] = t4.x; qv[e + 1] = t4.y; qv[e + 2] = t4.z; qv[e + 3] = t4.w;
     }
-#pragma unroll 1
+_Pragma(T3_STR(unroll T3_ATT_UNROLL))
     for (int i0 = 0; i0 < nrows; i0 += 64) {
       const int i = (tid >> 2) + i0;
       float acc = 0.f;
@@ -861,7 +866,7 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
   // 4. max, then exponentials / their sum / output dims 8 warp .. 8 warp + 7 in one sweep: every warp over all rows
   //    (lane owns rows lane + 32 k)
   float M = -INFINITY;
-#pragma unroll 1
+#pragma unroll 4
   for (int k0 = 0; k0 < nrows; k0 += 32) {
     const int i = lane + k0;
     M = fmaxf(M, (i < nrows) ? s_sm[i] : -INFINITY);
@@ -875,7 +880,7 @@ __device__ __noinline__ void attn_phase_tile(const T3Params& p, int it, int laye
   float acc[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-#pragma unroll 1
+_Pragma(T3_STR(unroll T3_ATT_UNROLL))
   for (int k0 = 0; k0 < nrows; k0 += 32) {
     const int i = lane + k0;
     if (i < nrows) {

@@ -19,9 +19,9 @@ lib.cbx_dbg_attn_stamps(None)
 torch.cuda.synchronize()
 b = buf.cpu().view(-1, 16)
 n = int((b[:, 0] > 0).sum())
-names = ["pdl_wait (tma warp)"] + [f"blk{i} {w}" for i in range(4) for w in ("S ready", "max+fold", "P published")] + ["loop end", "exit"]
+names = ["pdl_wait (issuer)", "blk2 S ready", "blk2 max pass done", "blk2 o_full seen", "blk2 fold done", "blk2 exp pass done", "blk2 proxy fence done",
+         "blk2 arrived", "-", "blk4 S ready", "blk6 S ready", "-", "-", "loop end", "exit"]
 d = b[:n].double() / 1e3
-print(f"{n} attention launches; stamps of softmax group 0 relative to kernel start (us), launches 8..11 and the mean")
-for i in list(range(8, 12)) + [-1]:
-    r = d[i] if i >= 0 else d[4:].mean(0)
-    print("mean" if i < 0 else i, " ".join(f"{nm} {float(r[k + 1] - r[0]):.2f} |" for k, nm in enumerate(names)))
+print(f"{n} attention launches; stamps of thread 0 (softmax group 0) relative to kernel start (us), mean over launches")
+r = d[4:].mean(0)
+print(" | ".join(f"{nm} {float(r[k + 1] - r[0]):.2f}" for k, nm in enumerate(names) if nm != "-"))

@@ -65,3 +65,16 @@ d_end = tl[:, hs - 1, 2]; d_end = d_end[d_end > 0].max()
 for nm, k in (("staged", 0), ("units done", 1), ("published", 2)):
     v = tl[:, hs, k]; v = v[v > 0] - d_end
     print(f"head {nm}: min {float(v.min()):.2f} median {float(v.median()):.2f} max {float(v.max()):.2f} us after the last down epilogue")
+# attention phase, per CTA (medians / maxima over the CTAs that own a (pair, split), mean over layers 1..28):
+# qkv epilogue of THIS CTA -> q staged -> barrier -> keys done -> published
+seg = {k: [] for k in ("own_epi_to_q_staged med", "own_epi_to_q_staged max", "wait_all+bar med", "scores med", "softmax+pv+publish med", "softmax+pv+publish max",
+                       "q_staged_to_published med", "q_staged_to_published max")}
+for l in range(1, 29):
+    a = at[:, l, :]; m = a[:, 0] > 0
+    own = tl[m, 4 * l, 2]; pub = tl[m, 4 * l, 3]
+    seg["own_epi_to_q_staged med"].append(float((a[m, 0] - own).median())); seg["own_epi_to_q_staged max"].append(float((a[m, 0] - own).max()))
+    seg["wait_all+bar med"].append(float((a[m, 1] - a[m, 0]).median()))
+    seg["scores med"].append(float((a[m, 2] - a[m, 1]).median()))
+    seg["softmax+pv+publish med"].append(float((pub - a[m, 2]).median())); seg["softmax+pv+publish max"].append(float((pub - a[m, 2]).max()))
+    seg["q_staged_to_published med"].append(float((pub - a[m, 0]).median())); seg["q_staged_to_published max"].append(float((pub - a[m, 0]).max()))
+print("attention segments (us):", {k: round(stt.mean(v), 2) for k, v in seg.items()})
