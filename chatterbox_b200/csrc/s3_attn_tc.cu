@@ -24,6 +24,9 @@
 namespace cbx {
 namespace {
 
+#ifndef ATC_P_TMEM
+#define ATC_P_TMEM 1          // P travels to the second product through TMEM (in place over the S tile); 0: through shared memory
+#endif
 constexpr int TQ = 128, TK = 128, TD = 64;
 constexpr int NSK = 4, NST = 3;                        // K slots / V slots (released separately)
 constexpr int NSB = 3;                                 // S tiles in TMEM (3 x 128 columns) + 2 x 64 columns of P V output = 512
@@ -86,6 +89,25 @@ __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
         "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr)
+      : "memory");
+}
+// registers -> TMEM: this warp's 32 lanes x 16 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// D[tmem] (+)= A[tmem] * B[smem]: the A operand (128 lanes x 8 columns of packed bf16 pairs per K = 16 step) comes from TMEM
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0u)
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -173,13 +195,18 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
         }
         mbar_wait_sleep(&v_full[s], (j / NST) & 1);
         tc_fence_after();
-        const uint32_t pa = smem_u32(sP + g * P_B), va = smem_u32(sV + s * TILE_B);
+        [[maybe_unused]] const uint32_t pa = smem_u32(sP + g * P_B);
+        const uint32_t va = smem_u32(sV + s * TILE_B);
 #pragma unroll
         for (int k = 0; k < TK / 16; ++k) {
           // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
-          const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
           const uint64_t db = umma_desc_k128(va + k * 2048);
+#if ATC_P_TMEM
+          umma_bf16_ts(tmem_o + g * TD, tmem_base + (j % NSB) * TK + k * 8, db, idesc_o, k != 0);
+#else
+          const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
           umma_bf16(tmem_o + g * TD, da, db, idesc_o, k != 0);
+#endif
         }
         umma_commit(&o_full[g]);
         umma_commit(&v_free[s]);
@@ -266,7 +293,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
     {
       uint32_t ra[32], rb[32];
       auto emit = [&](uint32_t (&r)[32], int c) {
-        uint8_t* pk = prow + (c >> 1) * TILE_B;
+        [[maybe_unused]] uint8_t* pk = prow + (c >> 1) * TILE_B;
+        [[maybe_unused]] uint32_t pw[16];
         if (tail) {          // keys past the row's length: exp2(-inf) = 0
 #pragma unroll
           for (int k = 0; k < 32; ++k) if (kbase + c * 32 + k >= Lk) r[k] = 0xff800000u;
@@ -281,8 +309,16 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
             ls4[e] += p0 + p1;
             w[e] = pack_bf16x2(p0, p1);
           }
+#if ATC_P_TMEM
+#pragma unroll
+          for (int e = 0; e < 4; ++e) pw[jc * 4 + e] = w[e];
+#else
           *reinterpret_cast<uint4*>(pk + ((((c & 1) * 4 + jc) ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+#endif
         }
+#if ATC_P_TMEM
+        tmem_st16(tS + c * 16, pw);          // P chunk c over S columns [16 c, 16 c + 16): all of them already read
+#endif
       };
       tmem_ld32_issue(tS, ra);
       tmem_ld_wait();
@@ -300,7 +336,11 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
     if (threadIdx.x == 0 && i == 1) { if (ls4[0] == 123.456f) ATC_STAMP(12); ATC_STAMP(6); }
     l = l * corr + ((ls4[0] + ls4[1]) + (ls4[2] + ls4[3]));
     m = m_new;
+#if ATC_P_TMEM
+    tmem_st_wait();
+#else
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // P visible to the tensor core
+#endif
     if (threadIdx.x == 0 && i == 1) ATC_STAMP(7);
     tc_fence_before();
     __syncwarp();
