@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   uint64_t* accum_bar = empty + MAX_STAGES;
   const int NS = p.nstages, SB = p.stage_bytes;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
-  uint64_t* stat_bar = accum_bar + 2;        // N-split: 16 warps x NSP CTAs arrive once their row moments are in our shared memory
+  uint64_t* stat_bar = accum_bar + 2;        // N-split: completes when every CTA's row moments have landed in our shared memory
   float* par = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
   float2* stat = reinterpret_cast<float2*>(smem + STAGES * STAGE_BYTES + 256 + PAR_BYTES);
   float* tile = reinterpret_cast<float*>(smem);
@@ -137,7 +137,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(accum_bar, 1);
-    mbar_init(stat_bar, p.nsplit > 1 ? 16 * p.nsplit : 1);
+    mbar_init(stat_bar, 1);
+    // N-split: the cluster's CTAs deliver BM rows x (sum, sum of squares) each with st.async, completing bytes on this barrier
+    if (p.nsplit > 1) mbar_arrive_expect_tx(stat_bar, (uint32_t)(p.nsplit * BM * 8));
     mbar_fence_init();
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmW);
@@ -316,8 +318,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   if (NSP > 1) {
     // ===== N-split epilogue (cluster (1, NSP, 1), n_tile = 64): the LayerNorm of a row spans the NSP column tiles of the
     // cluster.  A thread keeps its 16 values of the tile in registers (row = 8 warp + lane / 4, columns 16 (lane % 4) ...):
-    // partial (sum, sum of squares) over this CTA's 64 columns are PUSHED into every CTA of the cluster (st.shared::cluster) and
-    // announced by a remote mbarrier arrive; a CTA waits on its own mbarrier, adds the NSP partial moments from its own shared
+    // partial (sum, sum of squares) over this CTA's 64 columns are PUSHED into every CTA of the cluster (st.async: the store
+    // completes bytes on the receiver's mbarrier); a CTA waits on its own mbarrier, adds the NSP partial moments from its own shared
     // memory, normalises and stores.  Nothing is read twice, no cluster barrier on the path, no trailing barrier before exit
     // (a peer writes here only before its arrive, and we leave only after all arrives). =====
     if constexpr ((FEAT & (F_LN1 | F_LN2)) != 0) {
@@ -364,21 +366,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
       for (int k = 0; k < 16; ++k) { s1 += v[k]; s2 += v[k] * v[k]; }
       s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
       s1 += __shfl_xor_sync(0xffffffffu, s1, 2); s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
+      if (threadIdx.x == 64) GEMM_STAMP(9);
       // push the row's partial moments into every CTA of the cluster (slot = our rank), then one arrive per warp and peer
       asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");        // every peer's stat_bar is initialised
       const int my = blockIdx.y % NSP;
       if ((lane & 3) == 0) {
-        const uint32_t la = smem_u32(&stat[my * BM + r]);
+        // st.async: the 8 bytes land in the peer's shared memory and complete on ITS mbarrier — data and signal in one
+        // fire-and-forget operation, no release fence / remote arrive round trips on this thread
+        const uint32_t la = smem_u32(&stat[my * BM + r]), lb = smem_u32(stat_bar);
         for (int j = 0; j < NSP; ++j)
-          asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(dsmem_addr(la, (uint32_t)j)), "f"(s1), "f"(s2) : "memory");
+          asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+                       ::"r"(dsmem_addr(la, (uint32_t)j)), "f"(s1), "f"(s2), "r"(dsmem_addr(lb, (uint32_t)j)) : "memory");
       }
-      __syncwarp();
-      if (lane == 0) {
-        const uint32_t lb = smem_u32(stat_bar);
-        for (int j = 0; j < NSP; ++j)
-          asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(dsmem_addr(lb, (uint32_t)j)) : "memory");
-      }
+      if (threadIdx.x == 64) GEMM_STAMP(10);
       if (!has_ln1) store_out();          // the fp32 / bf16 copies of the un-normalised value leave while the moments travel
+      if (threadIdx.x == 64) GEMM_STAMP(12);
       {
         unsigned spins = 0;
         uint32_t done = 0;
@@ -388,6 +390,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
           if (++spins > (1u << 26)) __trap();
         }
       }
+      if (threadIdx.x == 64) GEMM_STAMP(13);
       s1 = 0.f; s2 = 0.f;
 #pragma unroll
       for (int j = 0; j < MAX_SPLIT; ++j)

@@ -44,7 +44,7 @@ for k in ("gemm", "attn", "ffn"):
 # inside the GEMM: stamps of CTA 0 relative to "inputs ready" (pdl_wait returned in the producer lane)
 t = bufs["gemm"].cpu().view(-1, 16).double() / 1e3
 t = t[t[:, 0] > 0]
-lab = [("producer issued all", 2), ("mma issued all", 3), ("accumulator ready", 4), ("drained", 5), ("barrier", 8), ("epilogue done", 6), ("exit", 7)]
+lab = [("producer issued all", 2), ("mma issued all", 3), ("accumulator ready", 4), ("drained", 5), ("barrier", 8), ("N-split: moments", 9), ("pushed", 10), ("stored", 12), ("all moments in", 13), ("epilogue done", 6), ("exit", 7)]
 dur = (t[:, 7] - t[:, 11])
 for name, lo, hi in (("q|k|v-like (busy < 7 us)", 0, 7), ("out-proj-like (8.5 - 10.5 us)", 8.5, 10.5), ("resnet-like (> 10.5 us)", 10.5, 99)):
     m = (dur > lo) & (dur < hi)
