@@ -200,6 +200,171 @@ __global__ void __launch_bounds__(256) k_sf_relattn(const float* __restrict__ qk
   }
 }
 
+// ---- the same attention on the tensor cores: mma.sync m16n8k8 TF32 (fp32 operands straight from shared memory, 10-bit mantissa
+// products, fp32 accumulation).  CTA = (64 queries, head), 4 warps x 16 query rows; key tiles of 64, double-buffered with
+// cp.async: K, V and the 127 rows of p the tile's diagonals touch.  Per warp and tile: content scores (q + u) K^T, 16 x 64;
+// position scores (q + v) P_band^T, 16 x 80 (the band columns its rows can reach), written to a per-warp scratch and read back
+// along the diagonals (rel_shift is the index m = T - 1 - i + j, i.e. band column j - i + const); online softmax in the
+// accumulator layout; P V with the probabilities re-used as the A operand in place (the two key columns a thread holds are
+// presented as A columns t and t + 4, and the V rows are fetched in the same order).  (q + u), (q + v) live in registers as A
+// fragments for the whole key loop.  CBX_RELATTN_TC=0 selects the CUDA-core kernel above. ----
+constexpr int RT_Q = 64, RT_K = 64, RT_LD = 68, RT_BAND = 128, RT_BLD = 84;
+constexpr int RT_STAGE = (2 * RT_K + RT_BAND) * RT_LD;              // floats: K, V, band
+constexpr int RT_SMEM = (2 * RT_STAGE + 4 * 16 * RT_BLD) * 4;
+__device__ __forceinline__ void rt_cp16(float* dst, const float* src, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ uint32_t rt_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void rt_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__global__ void __launch_bounds__(128) k_sf_relattn_tc(const float* __restrict__ qkv, const float* __restrict__ pp, const float* __restrict__ bu,
+                                                       const float* __restrict__ bv, int T, __nv_bfloat16* __restrict__ out, long long plane) {
+  extern __shared__ __align__(16) float rt_smem[];
+  float* Bs = rt_smem + 2 * RT_STAGE;
+  const int i0 = blockIdx.x * RT_Q, h = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, t = lane & 3;
+  auto load_tile = [&](int kt, int buf) {
+    float* Ks = rt_smem + buf * RT_STAGE;
+    float* Vs = Ks + RT_K * RT_LD;
+    float* Ps = Vs + RT_K * RT_LD;
+    const int j0 = kt * RT_K;
+    for (int e = tid; e < RT_K * 16; e += 128) {
+      const int r = e >> 4, c = (e & 15) * 4;
+      const bool ok = j0 + r < T;
+      const float* src = qkv + (size_t)(ok ? j0 + r : 0) * 1536 + h * DK + c;
+      rt_cp16(Ks + r * RT_LD + c, src + 512, ok);
+      rt_cp16(Vs + r * RT_LD + c, src + 1024, ok);
+    }
+    const int m0 = T - 1 - (i0 + RT_Q - 1) + j0;       // band row bl <-> p row m0 + bl; bl = (j - j0) - (i - i0) + 63
+    for (int e = tid; e < RT_BAND * 16; e += 128) {
+      const int r = e >> 4, c = (e & 15) * 4, mm = m0 + r;
+      const bool ok = mm >= 0 && mm < 2 * T - 1;
+      rt_cp16(Ps + r * RT_LD + c, pp + (size_t)(ok ? mm : 0) * D + h * DK + c, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const int ntiles = (T + RT_K - 1) / RT_K;
+  load_tile(0, 0);
+  // (q + u), (q + v) of this warp's 16 rows as A fragments: a0 = (g, t), a1 = (g + 8, t), a2 = (g, t + 4), a3 = (g + 8, t + 4)
+  uint32_t qu[8][4], qv[8][4];
+  {
+    const int r0 = i0 + warp * 16 + g, r1 = r0 + 8;
+    const float* q0 = qkv + (size_t)(r0 < T ? r0 : 0) * 1536 + h * DK;
+    const float* q1 = qkv + (size_t)(r1 < T ? r1 : 0) * 1536 + h * DK;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const int c0 = ks * 8 + t, c1 = c0 + 4;
+      const float u0 = __ldg(bu + h * DK + c0), u1 = __ldg(bu + h * DK + c1), v0 = __ldg(bv + h * DK + c0), v1 = __ldg(bv + h * DK + c1);
+      const float a = r0 < T ? q0[c0] : 0.f, b2 = r1 < T ? q1[c0] : 0.f, c = r0 < T ? q0[c1] : 0.f, d2 = r1 < T ? q1[c1] : 0.f;
+      qu[ks][0] = rt_tf32(a + u0); qu[ks][1] = rt_tf32(b2 + u0); qu[ks][2] = rt_tf32(c + u1); qu[ks][3] = rt_tf32(d2 + u1);
+      qv[ks][0] = rt_tf32(a + v0); qv[ks][1] = rt_tf32(b2 + v0); qv[ks][2] = rt_tf32(c + v1); qv[ks][3] = rt_tf32(d2 + v1);
+    }
+  }
+  float o[8][4], m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float* Bw = Bs + warp * 16 * RT_BLD;
+  const int b0 = 48 - 16 * warp;                     // first band column this warp's rows can reach
+  for (int kt = 0; kt < ntiles; ++kt) {
+    if (kt + 1 < ntiles) load_tile(kt + 1, (kt + 1) & 1);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncthreads();
+    const float* Ks = rt_smem + (kt & 1) * RT_STAGE;
+    const float* Vs = Ks + RT_K * RT_LD;
+    const float* Ps = Vs + RT_K * RT_LD;
+    // position scores of the band: 16 rows x 80 columns -> per-warp scratch
+#pragma unroll
+    for (int nt = 0; nt < 10; ++nt) {
+      float c[4] = {0.f, 0.f, 0.f, 0.f};
+      const float* pr = Ps + (b0 + nt * 8 + g) * RT_LD + t;
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) rt_mma(c, qv[ks], __float_as_uint(pr[ks * 8]), __float_as_uint(pr[ks * 8 + 4]));
+      *reinterpret_cast<float2*>(Bw + g * RT_BLD + nt * 8 + 2 * t) = make_float2(c[0], c[1]);
+      *reinterpret_cast<float2*>(Bw + (g + 8) * RT_BLD + nt * 8 + 2 * t) = make_float2(c[2], c[3]);
+    }
+    __syncwarp();
+    // content scores + the band along the diagonals: row g takes scratch column (key - g + 15), row g + 8 column (key - g + 7)
+    float s[8][4];
+    const int j0 = kt * RT_K;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      float c[4] = {0.f, 0.f, 0.f, 0.f};
+      const float* kr = Ks + (nt * 8 + g) * RT_LD + t;
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) rt_mma(c, qu[ks], __float_as_uint(kr[ks * 8]), __float_as_uint(kr[ks * 8 + 4]));
+      const int key = nt * 8 + 2 * t;
+      const float* d0 = Bw + g * RT_BLD + key - g + 15;
+      const float* d1 = Bw + (g + 8) * RT_BLD + key - g + 7;
+      s[nt][0] = (j0 + key < T) ? (c[0] + d0[0]) * 0.125f : -INFINITY;
+      s[nt][1] = (j0 + key + 1 < T) ? (c[1] + d0[1]) * 0.125f : -INFINITY;
+      s[nt][2] = (j0 + key < T) ? (c[2] + d1[0]) * 0.125f : -INFINITY;
+      s[nt][3] = (j0 + key + 1 < T) ? (c[3] + d1[1]) * 0.125f : -INFINITY;
+    }
+    // online softmax (rows g and g + 8; the four lanes of a quad share a row)
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { mx[0] = fmaxf(mx[0], fmaxf(s[nt][0], s[nt][1])); mx[1] = fmaxf(mx[1], fmaxf(s[nt][2], s[nt][3])); }
+    float corr[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+      const float mn = fmaxf(m_run[r], mx[r]);       // finite: the first key of every tile exists
+      corr[r] = __expf(m_run[r] - mn);
+      m_run[r] = mn;
+    }
+    float ls[2] = {0.f, 0.f};
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      s[nt][0] = __expf(s[nt][0] - m_run[0]); s[nt][1] = __expf(s[nt][1] - m_run[0]);
+      s[nt][2] = __expf(s[nt][2] - m_run[1]); s[nt][3] = __expf(s[nt][3] - m_run[1]);
+      ls[0] += s[nt][0] + s[nt][1]; ls[1] += s[nt][2] + s[nt][3];
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) l_run[r] = l_run[r] * corr[r] + ls[r];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { o[i][0] *= corr[0]; o[i][1] *= corr[0]; o[i][2] *= corr[1]; o[i][3] *= corr[1]; }
+    // O += P V: k-step = key block nt; A columns t / t + 4 <-> keys 8 nt + 2 t / + 1, V rows fetched in the same order
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      const uint32_t a[4] = {rt_tf32(s[nt][0]), rt_tf32(s[nt][2]), rt_tf32(s[nt][1]), rt_tf32(s[nt][3])};
+      const float* vr = Vs + (nt * 8 + 2 * t) * RT_LD + g;
+#pragma unroll
+      for (int nd = 0; nd < 8; ++nd) rt_mma(o[nd], a, __float_as_uint(vr[nd * 8]), __float_as_uint(vr[RT_LD + nd * 8]));
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int row = i0 + warp * 16 + g + r * 8;
+    if (row < T) {
+      const float inv = 1.0f / l_run[r];
+      __nv_bfloat16* dst = out + (size_t)row * D + h * DK + 2 * t;
+#pragma unroll
+      for (int nd = 0; nd < 8; ++nd) {
+        uint32_t hi, lo;
+        split_hi_lo(o[nd][r * 2] * inv, o[nd][r * 2 + 1] * inv, hi, lo);
+        *reinterpret_cast<uint32_t*>(dst + nd * 8) = hi;
+        *reinterpret_cast<uint32_t*>(dst + nd * 8 + plane) = lo;
+      }
+    }
+  }
+}
+
 // spks = Linear(192 -> 80)(F.normalize(embedding))     (flow.py:250-251)
 __global__ void __launch_bounds__(96) k_sf_spk(const float* __restrict__ emb, const float* __restrict__ w, const float* __restrict__ b,
                                                float* __restrict__ out) {
@@ -370,7 +535,14 @@ static int fe_layer(cbx_flowfe* h, FePlan* p, int l, int T, const float* pp, cud
   const long long plane = (long long)T * D;
   k_sf_ln<<<T, 128, 0, st>>>(h->x, FFW(h, f + 0), FFW(h, f + 1), 1e-12f, 1.0f, nullptr, h->pl, plane);
   if (gemm_launch(p->qkv[l], st)) return CBX_ERR;
-  k_sf_relattn<<<dim3((T + RA_Q - 1) / RA_Q, NH), 256, 0, st>>>(h->qkv, pp, FFW(h, f + 4), FFW(h, f + 5), T, h->pl, plane);
+  static const bool relattn_tc = [] { const char* v = getenv("CBX_RELATTN_TC"); return !(v && v[0] == '0'); }();
+  if (relattn_tc) {
+    static CbxPerDeviceOnce once;
+    if (once.first()) CBX_CUDA(cudaFuncSetAttribute(k_sf_relattn_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, RT_SMEM));
+    k_sf_relattn_tc<<<dim3((T + RT_Q - 1) / RT_Q, NH), 128, RT_SMEM, st>>>(h->qkv, pp, FFW(h, f + 4), FFW(h, f + 5), T, h->pl, plane);
+  } else {
+    k_sf_relattn<<<dim3((T + RA_Q - 1) / RA_Q, NH), 256, 0, st>>>(h->qkv, pp, FFW(h, f + 4), FFW(h, f + 5), T, h->pl, plane);
+  }
   if (gemm_launch(p->out[l], st)) return CBX_ERR;                                     // x += linear_out(attn)
   k_sf_ln<<<T, 128, 0, st>>>(h->x, FFW(h, f + 6), FFW(h, f + 7), 1e-12f, 1.0f, nullptr, h->pl, plane);
   if (gemm_launch(p->w1[l], st)) return CBX_ERR;
