@@ -177,6 +177,8 @@ static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
   static const int ffn_on = [] { const char* v = getenv("CBX_CFM_FFN"); return v ? atoi(v) : 1; }();
   static const int ffn_max_tiles = [] { const char* v = getenv("CBX_CFM_FFN_MAXTILES"); return v ? atoi(v) : 64; }();
   const bool fused_ffn = ffn_on && 2 * nb * ((L + 127) / 128) <= ffn_max_tiles;
+  static const int out_on = [] { const char* v = getenv("CBX_CFM_OUTFFN"); return v ? atoi(v) : 1; }();
+  const bool fused_out = out_on != 0;          // the attention out-projection inside the feed-forward kernel (A/B switch)
   auto G = [&](const __nv_bfloat16* A, int lda, int wi, int N, int K, int taps, const GemmEpi& e, int temb_res) {
     Op op; op.kind = 0; op.temb_res = temb_res;
     if (gemm_make(&op.g, A, lda, BFW(h, wi), 2 * nb, L, N, K, taps, e)) rc = CBX_ERR;
@@ -197,9 +199,11 @@ static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
     GemmEpi eq{}; eq.out_bf16 = h->qkv; eq.ld_bf16 = 1536;
     G(h->ln, C, w + 0, 1536, C, 1, eq, -1);
     Op at; at.kind = 1; at.temb_res = -1; pl.ops.push_back(at);
-    GemmEpi eo{}; eo.bias = FW(h, f + 2); eo.resid = h->res; eo.ld_resid = C; eo.out_f32 = h->res; eo.ld_f32 = C;
-    eo.ln2_g = FW(h, f + 3); eo.ln2_b = FW(h, f + 4); eo.out_ln = h->ln; eo.ld_ln = C;
-    G(h->att, 512, w + 1, C, 512, 1, eo, -1);
+    if (!(fused_ffn && fused_out)) {
+      GemmEpi eo{}; eo.bias = FW(h, f + 2); eo.resid = h->res; eo.ld_resid = C; eo.out_f32 = h->res; eo.ld_f32 = C;
+      eo.ln2_g = FW(h, f + 3); eo.ln2_b = FW(h, f + 4); eo.out_ln = h->ln; eo.ld_ln = C;
+      G(h->att, 512, w + 1, C, 512, 1, eo, -1);
+    }
     if (fused_ffn) {
       // FF1 + GELU + FF2 + residual (+ the next block's norm1) as ONE cluster kernel (csrc/s3_ffn.cu)
       Op op; op.kind = 3; op.temb_res = -1;
@@ -209,6 +213,11 @@ static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
       op.f.ln_g = op.f.ln_b = nullptr; op.f.out_ln = nullptr; op.f.ld_ln = C; op.f.out_bf16 = nullptr; op.f.ld_bf16 = 0;
       if (!last) { op.f.ln_g = FW(h, f + 7); op.f.ln_b = FW(h, f + 8); op.f.out_ln = h->ln; }
       else { op.f.out_bf16 = dst; op.f.ld_bf16 = ld_dst; }
+      if (fused_out) {      // the attention out-projection + residual + norm3 run inside the same cluster kernel
+        if (ffn_make_out(&op.f, h->att, 512, BFW(h, w + 1))) rc = CBX_ERR;
+        op.f.bo = FW(h, f + 2); op.f.g0 = FW(h, f + 3); op.f.b0 = FW(h, f + 4);
+        op.f.resid0 = h->res; op.f.ld_res0 = C; op.f.out0_f32 = h->res; op.f.ld_out0 = C; op.f.xbuf = h->ln; op.f.ld_x = C;
+      }
       pl.ops.push_back(op);
       return;
     }

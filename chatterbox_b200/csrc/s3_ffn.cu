@@ -33,8 +33,14 @@ constexpr int KB_A = FBM * FBK * 2;              // 16 KB
 constexpr int KB_W2 = FD * FBK * 2;              // 32 KB
 constexpr int PITCH = FD + 4;                    // floats per row of the partial tile
 constexpr int PAR_OFF = X_BYTES + W1_BYTES + W2_BYTES;        // b1[128], b2[256], g[256], b[256]
-constexpr int BAR_OFF = PAR_OFF + (HC + 3 * FD) * 4;
-constexpr int FFN_SMEM = BAR_OFF + 128 + 1024 /*align*/;
+constexpr int OC = FD / FC;                      // 32 out-projection columns per CTA (fused attention out-projection)
+constexpr int AK = 512, A_KB = AK / FBK;         // attention width = K of the out-projection, 8 k-blocks
+constexpr int WO_KB = OC * FBK * 2;              // 4 KB: [32 rows][64 k]
+constexpr int PAR_N = HC + 3 * FD + 3 * OC;      // + bo[32], g0[32], b0[32] of the fused out-projection
+constexpr int STAT_OFF = PAR_OFF + 4096;         // [8 senders][128 rows] (sum, sum of squares)
+constexpr int BAR_OFF = STAT_OFF + FC * FBM * 8;
+constexpr int FFN_SMEM = BAR_OFF + 256 + 1024 /*align*/;
+static_assert(PAR_N * 4 <= 4096 && A_KB * KB_A <= X_BYTES + W1_BYTES && A_KB * WO_KB <= X_BYTES, "fused out-projection buffers");
 static_assert(FBM * PITCH * 4 <= PAR_OFF, "partial tile overlays the operand buffers");
 static_assert(FFN_SMEM <= 232448, "shared memory budget");
 
@@ -45,6 +51,13 @@ struct FfnParams {
   float* out_f32;
   __nv_bfloat16 *out_ln, *out_bf16;
   int ld_resid, ld_f32, ld_ln, ld_bf16;
+  // fused attention out-projection (OUT instantiation): x1 = resid0 + att Wo^T + bo -> out0_f32; LayerNorm(x1) -> xbuf (= the
+  // tensor tmX reads)
+  CUtensorMap tmA, tmWo;
+  const float *bo, *g0, *b0, *resid0;
+  float* out0_f32;
+  __nv_bfloat16* xbuf;
+  int ld_res0, ld_out0, ld_x;
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0, 0, 0) (debug aid, tools/ffn_stamps.py)
 };
 
@@ -55,18 +68,28 @@ __device__ __forceinline__ unsigned long long ffn_gtimer() {
 }
 #define FFN_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.z == 0) p.dbg[k] = ffn_gtimer(); } while (0)
 
+template <bool OUT>
 __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_ffn_kernel(const __grid_constant__ FfnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sX = smem;                              // x tile; after MMA 1 its first half holds h
-  uint8_t* sW1 = smem + X_BYTES;
-  uint8_t* sW2 = smem + X_BYTES + W1_BYTES;
+  // plain:  [x 64 KB | W1 slice 64 KB | W2 slice 64 KB]
+  // OUT:    [attention tile 128 KB -> W1 slice | W2 slice] [Wo slice 32 KB -> x 64 KB]: the weights of the feed-forward
+  //         take the attention tile's place once the out-projection's MMAs have completed
+  uint8_t* sX = smem + (OUT ? X_BYTES + W1_BYTES : 0);         // x tile; after MMA 1 its first half holds h
+  uint8_t* sW1 = smem + (OUT ? 0 : X_BYTES);
+  uint8_t* sW2 = smem + (OUT ? W1_BYTES : X_BYTES + W1_BYTES);
+  uint8_t* sA = smem;                                          // OUT: attention tile, 8 k-blocks of [128][64]
+  uint8_t* sWo = smem + X_BYTES + W1_BYTES;                    // OUT: Wo rows [32 rank, +32), 8 k-blocks of [32][64]
+  float2* stat = reinterpret_cast<float2*>(smem + STAT_OFF);
   float* par = reinterpret_cast<float*>(smem + PAR_OFF);
   uint64_t* bar_k = reinterpret_cast<uint64_t*>(smem + BAR_OFF);    // [4] x + W1 k-block landed
   uint64_t* bar_w2 = bar_k + 4;
   uint64_t* bar_d1 = bar_k + 5;
   uint64_t* bar_d2 = bar_k + 6;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_k + 7);
+  uint64_t* bar_a = bar_k + 7;                    // OUT: [8] attention + Wo k-block landed
+  uint64_t* bar_d0 = bar_k + 15;                  // OUT: out-projection accumulator ready
+  uint64_t* stat_bar = bar_k + 16;                // OUT: the 8 CTAs' row moments have landed (st.async bytes)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_k + 17);
   float* tile = reinterpret_cast<float*>(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -77,15 +100,23 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     FFN_STAMP(0);
     for (int i = 0; i < 4; ++i) mbar_init(&bar_k[i], 1);
     mbar_init(bar_w2, 1); mbar_init(bar_d1, 1); mbar_init(bar_d2, 1);
+    if (OUT) {
+      for (int i = 0; i < A_KB; ++i) mbar_init(&bar_a[i], 1);
+      mbar_init(bar_d0, 1); mbar_init(stat_bar, 1);
+      mbar_arrive_expect_tx(stat_bar, (uint32_t)(FC * FBM * 8));
+    }
     mbar_fence_init();
     tma_prefetch_desc(&p.tmX); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
+    if (OUT) { tma_prefetch_desc(&p.tmA); tma_prefetch_desc(&p.tmWo); }
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_d1 = tmem_base, tmem_d2 = tmem_base + 128;
+  const uint32_t tmem_d1 = tmem_base, tmem_d2 = tmem_base + 128, tmem_d0 = tmem_base + 384;
+  // OUT: peers push row moments into our shared memory later: tell them our barriers exist (waited for before the first push)
+  if (OUT) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   if (threadIdx.x == 0) FFN_STAMP(1);
 
   // final-epilogue ownership: this CTA finishes rows [16 rank, 16 rank + 16) of the tile, one row per warp; a lane
@@ -96,51 +127,162 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
   const int gc0 = lane * 4, gc1 = (lane + 32) * 4;
   float4 rv0 = make_float4(0.f, 0.f, 0.f, 0.f), rv1 = rv0;
 
+  auto issue_weights = [&]() {          // the feed-forward's weight slices (never depend on a kernel)
+    for (int kb = 0; kb < 4; ++kb) {
+      mbar_arrive_expect_tx(&bar_k[kb], 2 * KB_A);
+      tma_load_3d(sW1 + kb * KB_A, &p.tmW1, &bar_k[kb], kb * FBK, rank * HC, 0);
+    }
+    mbar_arrive_expect_tx(bar_w2, W2_BYTES);
+    for (int kb = 0; kb < 2; ++kb) tma_load_3d(sW2 + kb * KB_W2, &p.tmW2, bar_w2, rank * HC + kb * FBK, 0, 0);
+  };
+  auto mma1 = [&]() {
+    const uint32_t idesc = umma_idesc_bf16(FBM, HC);
+    for (int kb = 0; kb < 4; ++kb) {
+      mbar_wait_spin(&bar_k[kb], 0);
+      if (kb == 0) FFN_STAMP(3);
+      if (kb == 3) FFN_STAMP(4);
+      tc_fence_after();
+      const uint64_t da = umma_desc_k128(smem_u32(sX + kb * KB_A)), db = umma_desc_k128(smem_u32(sW1 + kb * KB_A));
+#pragma unroll
+      for (int k = 0; k < FBK / 16; ++k) umma_bf16(tmem_d1, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+    }
+    umma_commit(bar_d1);
+  };
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < 4; ++kb) {
-        mbar_arrive_expect_tx(&bar_k[kb], 2 * KB_A);
-        tma_load_3d(sW1 + kb * KB_A, &p.tmW1, &bar_k[kb], kb * FBK, rank * HC, 0);
+      if (!OUT) {
+        issue_weights();
+        pdl_wait();
+        FFN_STAMP(2);
+        for (int kb = 0; kb < 4; ++kb) tma_load_3d(sX + kb * KB_A, &p.tmX, &bar_k[kb], kb * FBK, t0, b);
+      } else {
+        for (int kb = 0; kb < A_KB; ++kb) {
+          mbar_arrive_expect_tx(&bar_a[kb], KB_A + WO_KB);
+          tma_load_3d(sWo + kb * WO_KB, &p.tmWo, &bar_a[kb], kb * FBK, rank * OC, 0);
+        }
+        pdl_wait();
+        FFN_STAMP(2);
+        for (int kb = 0; kb < A_KB; ++kb) tma_load_3d(sA + kb * KB_A, &p.tmA, &bar_a[kb], kb * FBK, t0, b);
+        mbar_wait_spin(bar_d0, 0);        // the out-projection's MMAs are done with the attention tile: its place is free
+        issue_weights();
       }
-      mbar_arrive_expect_tx(bar_w2, W2_BYTES);
-      for (int kb = 0; kb < 2; ++kb) tma_load_3d(sW2 + kb * KB_W2, &p.tmW2, bar_w2, rank * HC + kb * FBK, 0, 0);
-      pdl_wait();
-      FFN_STAMP(2);
-      for (int kb = 0; kb < 4; ++kb) tma_load_3d(sX + kb * KB_A, &p.tmX, &bar_k[kb], kb * FBK, t0, b);
     }
     __syncwarp();
     pdl_wait();
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(FBM, HC);
-      for (int kb = 0; kb < 4; ++kb) {
-        mbar_wait_spin(&bar_k[kb], 0);
-        if (kb == 0) FFN_STAMP(3);
-        if (kb == 3) FFN_STAMP(4);
-        tc_fence_after();
-        const uint64_t da = umma_desc_k128(smem_u32(sX + kb * KB_A)), db = umma_desc_k128(smem_u32(sW1 + kb * KB_A));
+      if (!OUT) mma1();
+      else {
+        const uint32_t idesc0 = umma_idesc_bf16(FBM, OC);
+        for (int kb = 0; kb < A_KB; ++kb) {
+          mbar_wait_spin(&bar_a[kb], 0);
+          tc_fence_after();
+          const uint64_t da = umma_desc_k128(smem_u32(sA + kb * KB_A)), db = umma_desc_k128(smem_u32(sWo + kb * WO_KB));
 #pragma unroll
-        for (int k = 0; k < FBK / 16; ++k) umma_bf16(tmem_d1, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          for (int k = 0; k < FBK / 16; ++k) umma_bf16(tmem_d0, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc0, (kb | k) != 0);
+        }
+        umma_commit(bar_d0);
       }
-      umma_commit(bar_d1);
     }
     __syncwarp();
     pdl_wait();
   } else {
-    // per-column vectors of both epilogues
-    for (int c = threadIdx.x - 64; c < HC + 3 * FD; c += FFN_THREADS - 64) {
+    // per-column vectors of the epilogues
+    for (int c = threadIdx.x - 64; c < (OUT ? PAR_N : HC + 3 * FD); c += FFN_THREADS - 64) {
       float v;
       if (c < HC) v = __ldg(p.b1 + rank * HC + c);
       else if (c < HC + FD) v = __ldg(p.b2 + c - HC);
       else if (c < HC + 2 * FD) v = p.ln_g ? __ldg(p.ln_g + c - HC - FD) : 1.f;
-      else v = p.ln_g ? __ldg(p.ln_b + c - HC - 2 * FD) : 0.f;
+      else if (c < HC + 3 * FD) v = p.ln_g ? __ldg(p.ln_b + c - HC - 2 * FD) : 0.f;
+      else if (c < HC + 3 * FD + OC) v = __ldg(p.bo + rank * OC + c - (HC + 3 * FD));
+      else if (c < HC + 3 * FD + 2 * OC) v = __ldg(p.g0 + rank * OC + c - (HC + 3 * FD + OC));
+      else v = __ldg(p.b0 + rank * OC + c - (HC + 3 * FD + 2 * OC));
       par[c] = v;
     }
     pdl_wait();
   }
+  if (OUT) {
+    // ---- fused attention out-projection: this CTA holds columns [32 rank, +32) of x1 = resid + att Wo^T + bo for the
+    // tile's 128 rows (warps 4-7, thread <-> row); the LayerNorm over the 256 channels needs the other CTAs' moments:
+    // pushed with st.async, then the normalised bf16 slice goes to global memory (the x buffer), and after a cluster
+    // barrier every CTA loads the full x tile by TMA — from here on the kernel is the plain feed-forward. ----
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");        // every peer's barriers exist
+    __syncthreads();                                                          // par[] staged
+    if (warp >= 4 && warp < 8) {
+      const int q = warp & 3, row = q * 32 + lane, t = t0 + row;
+      const bool ok = t < p.L;
+      const size_t g0row = (size_t)b * p.L + (ok ? t : 0);
+      float4 rs[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) rs[i] = ok ? *reinterpret_cast<const float4*>(p.resid0 + g0row * p.ld_res0 + rank * OC + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      mbar_wait_spin(bar_d0, 0);
+      tc_fence_after();
+      if (threadIdx.x == 128) FFN_STAMP(12);
+      float v[32];
+      tmem_ld32(tmem_d0 + ((uint32_t)(q * 32) << 16), v);
+      const float* pb = par + HC + 3 * FD;
+      float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        v[4 * i] += pb[4 * i] + rs[i].x; v[4 * i + 1] += pb[4 * i + 1] + rs[i].y;
+        v[4 * i + 2] += pb[4 * i + 2] + rs[i].z; v[4 * i + 3] += pb[4 * i + 3] + rs[i].w;
+      }
+#pragma unroll
+      for (int k = 0; k < 32; ++k) { s1 += v[k]; s2 += v[k] * v[k]; }
+      {
+        const uint32_t la = smem_u32(&stat[rank * FBM + row]), lb = smem_u32(stat_bar);
+#pragma unroll
+        for (int j = 0; j < FC; ++j)
+          asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+                       ::"r"(dsmem_addr(la, (uint32_t)j)), "f"(s1), "f"(s2), "r"(dsmem_addr(lb, (uint32_t)j)) : "memory");
+      }
+      if (ok) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(p.out0_f32 + g0row * p.ld_out0 + rank * OC + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+      {
+        unsigned spins = 0;
+        uint32_t done = 0;
+        while (!done) {
+          asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                       : "=r"(done) : "r"(smem_u32(stat_bar)), "r"(0u) : "memory");
+          if (++spins > (1u << 26)) __trap();
+        }
+      }
+      if (threadIdx.x == 128) FFN_STAMP(13);
+      s1 = 0.f; s2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < FC; ++j) { const float2 m2 = stat[j * FBM + row]; s1 += m2.x; s2 += m2.y; }
+      const float mean = s1 * (1.0f / FD);
+      const float rstd = rsqrtf(fmaxf(s2 * (1.0f / FD) - mean * mean, 0.f) + 1e-5f);
+      if (ok) {
+        const float* pg = pb + OC; const float* pbb = pb + 2 * OC;
+        uint32_t w[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          w[k] = pack_bf16x2((v[2 * k] - mean) * rstd * pg[2 * k] + pbb[2 * k], (v[2 * k + 1] - mean) * rstd * pg[2 * k + 1] + pbb[2 * k + 1]);
+        __nv_bfloat16* dst = p.xbuf + g0row * p.ld_x + rank * OC;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(dst + 8 * i) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+      }
+      asm volatile("fence.proxy.async;" ::: "memory");      // these global writes are read by the peers' TMA loads
+    }
+    if (threadIdx.x == 128) FFN_STAMP(14);
+    tc_fence_before();
+    cluster_sync_all();                 // x1 and the normalised x tile of all 8 column slices are in global memory
+    tc_fence_after();
+    if (threadIdx.x == 128) FFN_STAMP(15);
+    if (warp == 0 && lane == 0) {
+      asm volatile("fence.proxy.async;" ::: "memory");
+      for (int kb = 0; kb < 4; ++kb) tma_load_3d(sX + kb * KB_A, &p.tmX, &bar_k[kb], kb * FBK, t0, b);
+    }
+    if (warp == 1 && lane == 0) mma1();
+    __syncwarp();
+  }
   if (frow_ok) {
-    rv0 = *reinterpret_cast<const float4*>(p.resid + grow * p.ld_resid + gc0);
-    rv1 = *reinterpret_cast<const float4*>(p.resid + grow * p.ld_resid + gc1);
+    rv0 = __ldcg(reinterpret_cast<const float4*>(p.resid + grow * p.ld_resid + gc0));
+    rv1 = __ldcg(reinterpret_cast<const float4*>(p.resid + grow * p.ld_resid + gc1));
   }
   // ---- epilogue 1 (all 16 warps): D1 -> + b1 -> GELU -> bf16 -> h in the K-major swizzled operand layout ----
   if (warp >= 2 && warp <= 5) mbar_wait_spin(bar_d1, 0);
@@ -266,32 +408,48 @@ static unsigned long long* g_ffn_dbg = nullptr;
 void ffn_set_debug(unsigned long long* buf) { g_ffn_dbg = buf; }
 
 int ffn_make(FfnDesc* d, const __nv_bfloat16* X, int ldx, const __nv_bfloat16* W1, const __nv_bfloat16* W2, int B, int L) {
-  d->B = B; d->L = L;
+  d->B = B; d->L = L; d->fuse_out = 0;
+  d->bo = d->g0 = d->b0 = d->resid0 = nullptr; d->out0_f32 = nullptr; d->xbuf = nullptr; d->ld_res0 = d->ld_out0 = d->ld_x = 0;
   if (make_tmap_bf16_3d(&d->tmX, X, FD, L, B, ldx, (uint64_t)ldx * L, FBK, FBM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW1, W1, FD, FH, 1, FD, (uint64_t)FD * FH, FBK, HC)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW2, W2, FH, FD, 1, FH, (uint64_t)FH * FD, FBK, FD)) return CBX_ERR;
   return CBX_OK;
 }
 
-int ffn_launch(const FfnDesc& d, cudaStream_t st) {
+int ffn_make_out(FfnDesc* d, const __nv_bfloat16* att, int lda, const __nv_bfloat16* Wo) {
+  if (make_tmap_bf16_3d(&d->tmA, att, AK, d->L, d->B, lda, (uint64_t)lda * d->L, FBK, FBM)) return CBX_ERR;
+  if (make_tmap_bf16_3d(&d->tmWo, Wo, AK, FD, 1, AK, (uint64_t)AK * FD, FBK, OC)) return CBX_ERR;
+  d->fuse_out = 1;
+  return CBX_OK;
+}
+
+template <bool OUT>
+static int ffn_launch_as(const FfnParams& p, dim3 grid, cudaStream_t st) {
   static CbxPerDeviceOnce once;
-  if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_ffn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FFN_SMEM));
+  if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_ffn_kernel<OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, FFN_SMEM));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = dim3(FFN_THREADS); cfg.dynamicSmemBytes = FFN_SMEM; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_ffn_kernel<OUT>, p));
+  return CBX_OK;
+}
+
+int ffn_launch(const FfnDesc& d, cudaStream_t st) {
   FfnParams p;
   p.tmX = d.tmX; p.tmW1 = d.tmW1; p.tmW2 = d.tmW2;
   p.L = d.L; p.tiles_l = (d.L + FBM - 1) / FBM;
   p.b1 = d.b1; p.b2 = d.b2; p.resid = d.resid; p.ln_g = d.ln_g; p.ln_b = d.ln_b;
   p.out_f32 = d.out_f32; p.out_ln = d.ln_g ? d.out_ln : nullptr; p.out_bf16 = d.out_bf16;
   p.ld_resid = d.ld_resid; p.ld_f32 = d.ld_f32; p.ld_ln = d.ld_ln; p.ld_bf16 = d.ld_bf16;
+  p.tmA = d.tmA; p.tmWo = d.tmWo; p.bo = d.bo; p.g0 = d.g0; p.b0 = d.b0; p.resid0 = d.resid0; p.out0_f32 = d.out0_f32;
+  p.xbuf = d.xbuf; p.ld_res0 = d.ld_res0; p.ld_out0 = d.ld_out0; p.ld_x = d.ld_x;
   p.dbg = g_ffn_dbg;
   if (g_ffn_dbg) g_ffn_dbg += 16;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(d.B * p.tiles_l, 1, FC); cfg.blockDim = dim3(FFN_THREADS); cfg.dynamicSmemBytes = FFN_SMEM; cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_ffn_kernel, p));
-  return CBX_OK;
+  const dim3 grid(d.B * p.tiles_l, 1, FC);
+  return d.fuse_out ? ffn_launch_as<true>(p, grid, st) : ffn_launch_as<false>(p, grid, st);
 }
 
 }  // namespace cbx

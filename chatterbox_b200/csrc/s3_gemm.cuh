@@ -86,8 +86,17 @@ struct FfnDesc {
   float* out_f32; int ld_f32;
   const float *ln_g, *ln_b; __nv_bfloat16* out_ln; int ld_ln;      // ln_g == null: no LayerNorm output
   __nv_bfloat16* out_bf16; int ld_bf16;                            // or null
+  // optional fused attention out-projection in front (ffn_make_out): x1 = resid0 + att Wo^T + bo -> out0_f32, and
+  // LayerNorm(x1; g0, b0) -> the x tensor of ffn_make (the kernel then reads it back tile by tile)
+  int fuse_out;
+  CUtensorMap tmA, tmWo;
+  const float *bo, *g0, *b0, *resid0; int ld_res0;
+  float* out0_f32; int ld_out0;
+  __nv_bfloat16* xbuf; int ld_x;
 };
 int ffn_make(FfnDesc* d, const __nv_bfloat16* X, int ldx, const __nv_bfloat16* W1, const __nv_bfloat16* W2, int B, int L);
+// adds the out-projection: att = bf16 [B][L][512] (row stride lda), Wo = bf16 [256][512]; X of ffn_make must be d->xbuf
+int ffn_make_out(FfnDesc* d, const __nv_bfloat16* att, int lda, const __nv_bfloat16* Wo);
 int ffn_launch(const FfnDesc& d, cudaStream_t st);
 
 }  // namespace cbx

@@ -20,9 +20,10 @@ torch.cuda.synchronize()
 b = buf.cpu().view(-1, 16)
 n = int((b[:, 0] > 0).sum())
 names = ["init+tmem", "pdl_wait(tma warp)", "first k-block landed", "last k-block landed", "D1 ready (all warps)", "epi1 done+sync",
-         "D2 ready (all warps)", "drained", "cluster sync", "reduce+epilogue", "cluster sync 2"]
+         "D2 ready (all warps)", "drained", "cluster sync", "reduce+epilogue", "cluster sync 2",
+         "OUT: D0 ready", "OUT: moments in", "OUT: x slice stored", "OUT: cluster barrier"]
 d = b[:n].double() / 1e3
 print(f"{n} fused feed-forward launches; stamps relative to kernel start (us), launches 8..13 and the mean")
 for i in list(range(8, 14)) + [-1]:
     r = d[i] if i >= 0 else d[4:].mean(0)
-    print("mean" if i < 0 else i, " ".join(f"{nm} {float(r[k + 1] - r[0]):.2f} |" for k, nm in enumerate(names)))
+    print("mean" if i < 0 else i, " ".join(f"{nm} {float(r[k + 1] - r[0]):.2f} |" for k, nm in enumerate(names) if float(r[k + 1]) > 0))
