@@ -40,6 +40,7 @@ constexpr int PAR_N = HC + 3 * FD + 3 * OC;      // + bo[32], g0[32], b0[32] of 
 constexpr int STAT_OFF = PAR_OFF + 4096;         // [8 senders][128 rows] (sum, sum of squares)
 constexpr int BAR_OFF = STAT_OFF + FC * FBM * 8;
 constexpr int FFN_SMEM = BAR_OFF + 256 + 1024 /*align*/;
+static_assert(A_KB == FC, "one attention k-block per CTA of the cluster (multicast)");
 static_assert(PAR_N * 4 <= 4096 && A_KB * KB_A <= X_BYTES + W1_BYTES && A_KB * WO_KB <= X_BYTES, "fused out-projection buffers");
 static_assert(FBM * PITCH * 4 <= PAR_OFF, "partial tile overlays the operand buffers");
 static_assert(FFN_SMEM <= 232448, "shared memory budget");
@@ -149,6 +150,10 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     umma_commit(bar_d1);
   };
   if (warp == 0) {
+    // OUT: the attention tile is the same for the 8 CTAs of the cluster: each CTA fetches ONE of its 8 k-blocks and
+    // multicasts it into all 8 shared memories (1 / 8 of the L2 reads).  A peer's barriers must exist before data may land
+    // in its shared memory: the producer warp takes the cluster barrier here, the other warps further down.
+    if (OUT) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     if (lane == 0) {
       if (!OUT) {
         issue_weights();
@@ -162,7 +167,11 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
         }
         pdl_wait();
         FFN_STAMP(2);
+#ifndef FFN_NO_MULTICAST
+        tma_load_3d_multicast(sA + rank * KB_A, &p.tmA, &bar_a[rank], rank * FBK, t0, b, (uint16_t)0xFF);
+#else
         for (int kb = 0; kb < A_KB; ++kb) tma_load_3d(sA + kb * KB_A, &p.tmA, &bar_a[kb], kb * FBK, t0, b);
+#endif
         mbar_wait_spin(bar_d0, 0);        // the out-projection's MMAs are done with the attention tile: its place is free
         issue_weights();
       }
@@ -206,7 +215,7 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     // tile's 128 rows (warps 4-7, thread <-> row); the LayerNorm over the 256 channels needs the other CTAs' moments:
     // pushed with st.async, then the normalised bf16 slice goes to global memory (the x buffer), and after a cluster
     // barrier every CTA loads the full x tile by TMA — from here on the kernel is the plain feed-forward. ----
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");        // every peer's barriers exist
+    if (warp != 0) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");        // every peer's barriers exist
     __syncthreads();                                                          // par[] staged
     if (warp >= 4 && warp < 8) {
       const int q = warp & 3, row = q * 32 + lane, t = t0 + row;
