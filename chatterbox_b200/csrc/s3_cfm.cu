@@ -148,7 +148,8 @@ struct cbx_cfm {
   std::vector<long long> bo, fo;
   void* slab;
   __nv_bfloat16 *xin, *cur_a, *cur_b, *cat, *ln, *qkv, *att, *ff, *h1;
-  float *res, *h2, *est, *x, *mish_temb, *tvec, *tvals;
+  float *res, *h2, *est, *x, *mish_temb, *tvec, *tvals, *ffn_red;
+  int ffn_red_tiles;
   int max_steps;
   std::map<long long, Plan> plans;      // key = L * 256 + nb
   long long launches;
@@ -213,6 +214,8 @@ static int build_plan(cbx_cfm* h, int L, int nb, Plan** out) {
       op.f.ln_g = op.f.ln_b = nullptr; op.f.out_ln = nullptr; op.f.ld_ln = C; op.f.out_bf16 = nullptr; op.f.ld_bf16 = 0;
       if (!last) { op.f.ln_g = FW(h, f + 7); op.f.ln_b = FW(h, f + 8); op.f.out_ln = h->ln; }
       else { op.f.out_bf16 = dst; op.f.ld_bf16 = ld_dst; }
+      static const int red_l2 = [] { const char* v = getenv("CBX_FFN_RED_L2"); return v ? atoi(v) : 1; }();
+      if (red_l2 && 2 * nb * ((L + 127) / 128) <= h->ffn_red_tiles) op.f.red = h->ffn_red;
       if (fused_out) {      // the attention out-projection + residual + norm3 run inside the same cluster kernel
         if (ffn_make_out(&op.f, h->att, 512, BFW(h, w + 1))) rc = CBX_ERR;
         op.f.bo = FW(h, f + 2); op.f.g0 = FW(h, f + 3); op.f.b0 = FW(h, f + 4);
@@ -322,6 +325,9 @@ extern "C" int cbx_cfm_create_batched(int device, int max_len, int max_batch, co
   const size_t o_tv = take((size_t)h->max_steps * NRES * 2 * C * 4), o_t = take(h->max_steps * 4);
   const size_t o_sz = take(U1 * NMEL * 4), o_sm = take(U1 * NMEL * 4), o_ss = take((size_t)max_batch * NMEL * 4);
   const size_t o_sc = take(U1 * NMEL * 4), o_so = take(U1 * NMEL * 4), o_len = take((size_t)2 * max_batch * 4);
+  // fused feed-forward: the 8 partial tiles of a row tile meet in this scratch (1 MB per row tile, L2-resident)
+  h->ffn_red_tiles = std::min(64, 2 * max_batch * ((max_len + 127) / 128));
+  const size_t o_red = take((size_t)h->ffn_red_tiles * 8 * 128 * 256 * 4);
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_cfm_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -332,6 +338,7 @@ extern "C" int cbx_cfm_create_batched(int device, int max_len, int max_batch, co
   h->xin = (__nv_bfloat16*)(s + o_xin); h->cur_a = (__nv_bfloat16*)(s + o_ca); h->cur_b = (__nv_bfloat16*)(s + o_cb);
   h->cat = (__nv_bfloat16*)(s + o_cat); h->ln = (__nv_bfloat16*)(s + o_ln); h->qkv = (__nv_bfloat16*)(s + o_qkv);
   h->att = (__nv_bfloat16*)(s + o_att); h->ff = (__nv_bfloat16*)(s + o_ff); h->h1 = (__nv_bfloat16*)(s + o_h1);
+  h->ffn_red = (float*)(s + o_red);
   h->res = (float*)(s + o_res); h->h2 = (float*)(s + o_h2); h->est = (float*)(s + o_est); h->x = (float*)(s + o_x);
   h->mish_temb = (float*)(s + o_mt); h->tvec = (float*)(s + o_tv); h->tvals = (float*)(s + o_t);
   h->st_z = (float*)(s + o_sz); h->st_mu = (float*)(s + o_sm); h->st_spks = (float*)(s + o_ss); h->st_cond = (float*)(s + o_sc);

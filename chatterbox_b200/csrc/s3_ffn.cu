@@ -59,6 +59,7 @@ struct FfnParams {
   float* out0_f32;
   __nv_bfloat16* xbuf;
   int ld_res0, ld_out0, ld_x;
+  float* red;                  // optional global scratch [row tiles][8][128][256] fp32: the partial tiles meet in L2 instead of DSMEM
   unsigned long long* dbg;    // optional %globaltimer stamps of CTA (0, 0, 0) (debug aid, tools/ffn_stamps.py)
 };
 
@@ -351,15 +352,37 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     }
   }
   tc_fence_before();
+  float* red = p.red ? p.red + (size_t)blockIdx.x * FC * FBM * FD : nullptr;       // this row tile's [8][128][256]
+  if (red) {
+    // partial tile -> global scratch (L2), coalesced: warp <-> 8 rows, lanes across the row.  The SM-to-SM network moves
+    // ~20 B/clk per SM, L2 64 B/clk: at 112 KB per CTA the exchange through L2 is the faster one, and nobody reads our shared
+    // memory afterwards, so there is no barrier before exit.
+    __syncthreads();
+#pragma unroll
+    for (int rr = 0; rr < FBM / 16; ++rr) {
+      const int r = warp * (FBM / 16) + rr;
+      float* dst = red + ((size_t)rank * FBM + r) * FD;
+      *reinterpret_cast<float4*>(dst + gc0) = *reinterpret_cast<const float4*>(tile + (size_t)r * PITCH + gc0);
+      *reinterpret_cast<float4*>(dst + gc1) = *reinterpret_cast<const float4*>(tile + (size_t)r * PITCH + gc1);
+    }
+  }
   if (threadIdx.x == 64) FFN_STAMP(8);
   cluster_sync_all();
   if (threadIdx.x == 64) FFN_STAMP(9);
   // ---- reduce over the cluster + final epilogue: one row per warp ----
   {
     float4 u0[FC], u1[FC];
-    const uint32_t la0 = smem_u32(tile + (size_t)frow * PITCH + gc0), la1 = smem_u32(tile + (size_t)frow * PITCH + gc1);
+    if (red) {
 #pragma unroll
-    for (int j = 0; j < FC; ++j) { u0[j] = dsmem_ld4(dsmem_addr(la0, (uint32_t)j)); u1[j] = dsmem_ld4(dsmem_addr(la1, (uint32_t)j)); }
+      for (int j = 0; j < FC; ++j) {
+        u0[j] = __ldcg(reinterpret_cast<const float4*>(red + ((size_t)j * FBM + frow) * FD + gc0));
+        u1[j] = __ldcg(reinterpret_cast<const float4*>(red + ((size_t)j * FBM + frow) * FD + gc1));
+      }
+    } else {
+      const uint32_t la0 = smem_u32(tile + (size_t)frow * PITCH + gc0), la1 = smem_u32(tile + (size_t)frow * PITCH + gc1);
+#pragma unroll
+      for (int j = 0; j < FC; ++j) { u0[j] = dsmem_ld4(dsmem_addr(la0, (uint32_t)j)); u1[j] = dsmem_ld4(dsmem_addr(la1, (uint32_t)j)); }
+    }
     float x[8];
     {
       float4 a = u0[0], c = u1[0];
@@ -403,7 +426,7 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     }
   }
   if (threadIdx.x == 64) FFN_STAMP(10);
-  cluster_sync_all();          // peers may still be reading this CTA's partial tile
+  if (red) __syncthreads(); else cluster_sync_all();          // DSMEM form: peers may still be reading this CTA's partial tile
   if (threadIdx.x == 64) FFN_STAMP(11);
   if (warp == 1) {
     tc_fence_after();
@@ -417,7 +440,7 @@ static unsigned long long* g_ffn_dbg = nullptr;
 void ffn_set_debug(unsigned long long* buf) { g_ffn_dbg = buf; }
 
 int ffn_make(FfnDesc* d, const __nv_bfloat16* X, int ldx, const __nv_bfloat16* W1, const __nv_bfloat16* W2, int B, int L) {
-  d->B = B; d->L = L; d->fuse_out = 0;
+  d->B = B; d->L = L; d->fuse_out = 0; d->red = nullptr;
   d->bo = d->g0 = d->b0 = d->resid0 = nullptr; d->out0_f32 = nullptr; d->xbuf = nullptr; d->ld_res0 = d->ld_out0 = d->ld_x = 0;
   if (make_tmap_bf16_3d(&d->tmX, X, FD, L, B, ldx, (uint64_t)ldx * L, FBK, FBM)) return CBX_ERR;
   if (make_tmap_bf16_3d(&d->tmW1, W1, FD, FH, 1, FD, (uint64_t)FD * FH, FBK, HC)) return CBX_ERR;
@@ -455,6 +478,7 @@ int ffn_launch(const FfnDesc& d, cudaStream_t st) {
   p.ld_resid = d.ld_resid; p.ld_f32 = d.ld_f32; p.ld_ln = d.ld_ln; p.ld_bf16 = d.ld_bf16;
   p.tmA = d.tmA; p.tmWo = d.tmWo; p.bo = d.bo; p.g0 = d.g0; p.b0 = d.b0; p.resid0 = d.resid0; p.out0_f32 = d.out0_f32;
   p.xbuf = d.xbuf; p.ld_res0 = d.ld_res0; p.ld_out0 = d.ld_out0; p.ld_x = d.ld_x;
+  p.red = d.red;
   p.dbg = g_ffn_dbg;
   if (g_ffn_dbg) g_ffn_dbg += 16;
   const dim3 grid(d.B * p.tiles_l, 1, FC);

@@ -93,6 +93,7 @@ struct FfnDesc {
   const float *bo, *g0, *b0, *resid0; int ld_res0;
   float* out0_f32; int ld_out0;
   __nv_bfloat16* xbuf; int ld_x;
+  float* red;          // optional scratch, (row tiles) x 8 x 128 x 256 fp32: cluster reduce through L2 instead of DSMEM
 };
 int ffn_make(FfnDesc* d, const __nv_bfloat16* X, int ldx, const __nv_bfloat16* W1, const __nv_bfloat16* W2, int B, int L);
 // adds the out-projection: att = bf16 [B][L][512] (row stride lda), Wo = bf16 [256][512]; X of ffn_make must be d->xbuf
