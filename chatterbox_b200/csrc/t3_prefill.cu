@@ -13,6 +13,8 @@
 // so the decode launch that follows finds the slab, the position counter and the pending logits exactly as the
 // megakernel's own prefill mode leaves them.
 #include "t3_prefill.h"
+#include <cstdio>
+#include <cstdlib>
 #include "s3_gemm.cuh"
 #include "t3_rows.cuh"
 #include "../../include/cbx.h"
@@ -223,6 +225,18 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
   CBX_CUDA(cudaMemcpyAsync(x, a.embeds, (size_t)rows * H * 4, cudaMemcpyDeviceToDevice, st));
   const __nv_bfloat16* wp = static_cast<const __nv_bfloat16*>(a.wplain);
   const size_t per_layer = (size_t)3072 * H + (size_t)H * H + (size_t)8192 * H + (size_t)H * INTER;
+  // column tile / split-K cluster of the q|k|v, o_proj and down GEMMs: the prompt is 2 row tiles, so narrow tiles put ~100 CTAs
+  // on the SMs and every CTA streams a smaller weight panel (the widest tile left 24-48 CTAs ingesting 0.5 MB each).
+  // CBX_T3P_TILES="qkv_t,qkv_s,o_t,o_s,dn_t,dn_s" overrides; 0 = the GEMM's own choice.
+  struct PTiles { int qkv_t, qkv_s, o_t, o_s, dn_t, dn_s; };
+  static const PTiles pt = [] {
+    PTiles c{128, 2, 64, 4, 64, 4};      // measured at P = 102: 2.35 ms per prefill (widest tiles: 2.91; 64,2,32,4,32,4: 3.23)
+    if (const char* v = getenv("CBX_T3P_TILES")) {
+      int t[6];
+      if (sscanf(v, "%d,%d,%d,%d,%d,%d", t, t + 1, t + 2, t + 3, t + 4, t + 5) == 6) c = PTiles{t[0], t[1], t[2], t[3], t[4], t[5]};
+    }
+    return c;
+  }();
   for (int l = 0; l < a.n_layers; ++l) {
     const __nv_bfloat16* wqkv = wp + l * per_layer;
     const __nv_bfloat16* wo = wqkv + (size_t)3072 * H;
@@ -232,7 +246,7 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
     GemmEpi e;
     k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln1 + (size_t)l * H, hl, hl_plane);
     e = GemmEpi{}; e.out_f32 = qkv; e.ld_f32 = 3072;
-    if (gemm_make_hilo(&d, hl, H, hl_plane, wqkv, rows, 3072, H, e) || gemm_launch(d, st)) return CBX_ERR;
+    if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wqkv, rows, 3072, 3072, H, e, pt.qkv_t, pt.qkv_s) || gemm_launch(d, st)) return CBX_ERR;
     if (a.kv_fp32)
       k_rope_kv<float><<<dim3(a.P, a.B), 1024, 0, st>>>(qkv, a.P, 0, a.rope_cos, a.rope_sin, static_cast<float*>(a.kcache),
                                                         static_cast<float*>(a.vcache), l, a.max_pos);
@@ -244,12 +258,12 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
       k_align_rows<<<a.al_rows0, 512, 0, st>>>(qkv, a.P, a.al_rows0, a.al_i, a.al_n, a.al_out, a.al_cap);
     k_attn_prefill<<<dim3((a.P + QT - 1) / QT, NH, a.B), 256, 0, st>>>(qkv, a.P, hl, hl_plane);
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
-    if (gemm_make_hilo(&d, hl, H, hl_plane, wo, rows, H, H, e) || gemm_launch(d, st)) return CBX_ERR;
+    if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wo, rows, H, H, H, e, pt.o_t, pt.o_s) || gemm_launch(d, st)) return CBX_ERR;
     k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln2 + (size_t)l * H, hl, hl_plane);
     e = GemmEpi{}; e.swiglu = 1; e.out_hilo = act; e.ld_hilo = INTER; e.hilo_plane = act_plane;
     if (gemm_make_hilo(&d, hl, H, hl_plane, wgu, rows, 8192, H, e) || gemm_launch(d, st)) return CBX_ERR;
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
-    if (gemm_make_hilo(&d, act, INTER, act_plane, wdn, rows, H, INTER, e) || gemm_launch(d, st)) return CBX_ERR;
+    if (gemm_make_hilo_ex(&d, act, INTER, act_plane, wdn, rows, H, H, INTER, e, pt.dn_t, pt.dn_s) || gemm_launch(d, st)) return CBX_ERR;
   }
   k_head<<<(VOCAB + 7) / 8, 256, 0, st>>>(x, a.P, a.B, a.final_norm, wp + a.n_layers * per_layer, a.logits,
                                            a.logits_ld > 0 ? a.logits_ld : VOCAB);
