@@ -299,9 +299,17 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     def counters():
         return t3.state()["launches"] + s3.launches()
 
+    def stage_times(ev):
+        return {"t3_prefill": ev["prefill0"].elapsed_time(ev["decode0"]), "t3_decode": ev["decode0"].elapsed_time(ev["decode1"]),
+                "flow_frontend": ev["front0"].elapsed_time(ev["cfm0"]), "cfm_solve": ev["cfm0"].elapsed_time(ev["cfm1"]),
+                "hift": ev["hift0"].elapsed_time(ev["hift1"])}
+
+    warm_stages = []            # iteration 0 = every stage eager (first sight of the shapes), 1 = graph capture, 2+ = replay
     for _ in range(max(args.warmup, 3)):
         toks, wav = step_resident()
         assert toks.shape[1] == N_SPEECH and int((toks >= 6561).sum()) == 0 and wav.shape[1] == 480 * 2 * N_SPEECH
+        torch.cuda.synchronize()
+        warm_stages.append(stage_times({**t3.events, **s3.events}))
     l0 = counters()
 
     # ---- timed region 1: inputs resident in HBM ----
@@ -340,6 +348,37 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     e2e_ms = e0.elapsed_time(e1)
     assert out.shape == (1, 480 * 2 * N_SPEECH) and out.device.type == "cpu"
 
+    # ---- side arms (rank 0 reports them; NOT part of the headline): the default sampler, and lengths never seen before ----
+    side = {}
+    if rank == 0:
+        c = tts.conds.t3
+        cond = T3Cond(speaker_emb=c.speaker_emb, cond_prompt_speech_tokens=c.cond_prompt_speech_tokens, emotion_adv=c.emotion_adv)
+
+        def utterance(n_tok, do_sample):
+            toks = t3.inference(t3_cond=cond, text_tokens=text_dev, max_new_tokens=n_tok, do_sample=do_sample, stop_on_eos=False,
+                                seed=11, **SAMPLE)
+            s3.inference(speech_tokens=toks[0].clamp(max=6560), ref_dict=tts.conds.gen, seed=7)
+            torch.cuda.synchronize()
+            st = stage_times({**t3.events, **s3.events})
+            return sum(st.values()), st
+        # (a) do_sample=True (the product default: temperature / min-p / top-p / multinomial on CTA 0, fixed Philox seed)
+        utterance(N_SPEECH, True)
+        runs = [utterance(N_SPEECH, True) for _ in range(3)]
+        ms = statistics.mean(r[0] for r in runs)
+        side["sampling_arm"] = {"what": "same utterance with do_sample=True (temperature 0.8, min_p 0.05, top_p 1.0, repetition penalty 1.2, "
+                                        "Philox multinomial), EOS suppressed, graphs hot", "ms_per_utterance": ms,
+                                "tokens_per_s": N_SPEECH / (ms * 1e-3), "t3_decode_ms": statistics.mean(r[1]["t3_decode"] for r in runs)}
+        # (b) speech-token counts never seen before: the mel length is new, so the CFM solve / front-end plan / HiFT run eagerly
+        lens = [N_SPEECH - 5, N_SPEECH - 13, N_SPEECH - 19]
+        vruns = [(n, *utterance(n, False)) for n in lens]
+        side["variable_length_arm"] = {"what": "greedy utterances of 251 / 243 / 237 speech tokens, each length seen for the first time "
+                                               "(no CUDA graph of that mel length yet: eager launches)",
+                                       "tokens_per_s": sum(v[0] for v in vruns) / (sum(v[1] for v in vruns) * 1e-3),
+                                       "ms_per_utterance": [v[1] for v in vruns],
+                                       "stages_ms_mean": {k: statistics.mean(v[2][k] for v in vruns) for k in vruns[0][2]}}
+        side["first_call_stages_ms"] = {"eager_first_call": warm_stages[0], "graph_capture_call": warm_stages[1]}
+    barrier()
+
     total_ms, e2e_ms = D.max_over_ranks([total_ms, e2e_ms], dev, world)
 
     if rank == 0:
@@ -368,6 +407,9 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                              "algorithmic_bytes_per_launch": dbytes, "launch_ms": d_ms,
                              "share_of_step": d_ms / (total_ms / args.steps)},
                 "stages_ms": stages,
+                "headline_arm": "greedy (do_sample=False), EOS suppressed, one fixed shape: every CUDA-graph cache (prefill, CFM solve) is hot "
+                                "after warm-up; sampling_arm / variable_length_arm / first_call_stages_ms give the other paths",
+                **side,
                 "t3_decode_tokens_per_s": N_SPEECH / (d_ms * 1e-3),
                 "cfm_tflops": cfm_flop / (stages["cfm_solve"] * 1e-3) / 1e12,
                 "hift_tflops": hift_flop / (stages["hift"] * 1e-3) / 1e12,

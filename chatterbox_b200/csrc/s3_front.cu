@@ -426,6 +426,7 @@ struct cbx_flowfe {
   float *x, *tmp, *qkv, *ffb, *hproj;
   __nv_bfloat16* pl;           // hi / lo planes scratch
   std::vector<FePlan*> plans;
+  std::vector<float*> pp_pool;   // position-projection buffers of evicted plans (each sized for max_tokens): reused, never freed
   long long launches, clock;
 };
 
@@ -446,16 +447,19 @@ static int fe_plan(cbx_flowfe* h, int T0, FePlan** out, cudaStream_t st) {
   if ((int)h->plans.size() >= FE_MAX_PLANS) {                 // evict the least recently used length
     size_t v = 0;
     for (size_t i = 1; i < h->plans.size(); ++i) if (h->plans[i]->stamp < h->plans[v]->stamp) v = i;
-    CBX_CUDA(cudaStreamSynchronize(st));
-    cudaFree(h->plans[v]->pp);
+    // its buffer goes back to the pool: the next plan's kernels are enqueued behind the evicted plan's last use on the
+    // handle's stream, so no synchronisation (and no cudaFree / cudaMalloc: a new length used to cost 6 ms of driver time)
+    h->pp_pool.push_back(h->plans[v]->pp);
     delete h->plans[v];
     h->plans.erase(h->plans.begin() + v);
   }
   FePlan* p = new FePlan();
   p->T0 = T0; p->stamp = ++h->clock; p->pp = nullptr;
   const int T1 = 2 * T0, R0 = 2 * T0 - 1, R1 = 2 * T1 - 1;
-  const size_t pp_floats = ((size_t)N_LAYERS0 * R0 + (size_t)N_LAYERS1 * R1) * D;
-  if (cudaMalloc(&p->pp, pp_floats * sizeof(float)) != cudaSuccess) {
+  // every buffer is sized for max_tokens, so any plan can take any pooled buffer
+  const size_t pp_floats = ((size_t)N_LAYERS0 * (2 * h->max_tokens - 1) + (size_t)N_LAYERS1 * (4 * h->max_tokens - 1)) * D;
+  if (!h->pp_pool.empty()) { p->pp = h->pp_pool.back(); h->pp_pool.pop_back(); }
+  else if (cudaMalloc(&p->pp, pp_floats * sizeof(float)) != cudaSuccess) {
     cbx_set_error("cbx_flowfe: cudaMalloc of %zu bytes for the position projections failed", pp_floats * sizeof(float));
     delete p;
     return CBX_ERR;
@@ -486,7 +490,7 @@ static int fe_plan(cbx_flowfe* h, int T0, FePlan** out, cudaStream_t st) {
     if (!rc) rc |= gemm_launch(d, st);
     off += (size_t)R * D;
   }
-  if (rc || cudaGetLastError() != cudaSuccess) { cudaFree(p->pp); delete p; if (!rc) cbx_set_error("cbx_flowfe: plan kernels failed"); return CBX_ERR; }
+  if (rc || cudaGetLastError() != cudaSuccess) { h->pp_pool.push_back(p->pp); delete p; if (!rc) cbx_set_error("cbx_flowfe: plan kernels failed"); return CBX_ERR; }
   h->plans.push_back(p);
   *out = p;
   return CBX_OK;
@@ -524,6 +528,7 @@ extern "C" int cbx_flowfe_create(int device, int max_tokens, const CbxFlowFrontW
 extern "C" int cbx_flowfe_destroy(cbx_flowfe* h) {
   if (!h) return CBX_OK;
   for (FePlan* p : h->plans) { cudaFree(p->pp); delete p; }
+  for (float* b : h->pp_pool) cudaFree(b);
   cudaFree(h->slab);
   delete h;
   return CBX_OK;
