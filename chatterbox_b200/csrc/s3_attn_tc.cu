@@ -28,15 +28,22 @@ namespace {
 #define ATC_P_TMEM 1          // P travels to the second product through TMEM (in place over the S tile); 0: through shared memory
 #endif
 constexpr int TQ = 128, TK = 128, TD = 64;
-constexpr int NSK = 4, NST = 3;                        // K slots / V slots (released separately)
-constexpr int NSB = 3;                                 // S tiles in TMEM (3 x 128 columns) + 2 x 64 columns of P V output = 512
 constexpr int TILE_B = TQ * TD * 2;                    // 16 KB: [128][64] bf16
 constexpr int P_B = TQ * TK * 2;                       // 32 KB: two k-blocks of [128][64]
-constexpr int OFF_Q = 0, OFF_K = TILE_B, OFF_V = OFF_K + NSK * TILE_B, OFF_P = OFF_V + NST * TILE_B, OFF_ML = OFF_P + 2 * P_B;
-constexpr int OFF_BAR = OFF_ML + TQ * 2 * 4;
-constexpr int ATC_THREADS = 288;       // warps 0-3 / 4-7: the two softmax groups; warp 8: one thread issues every TMA load and MMA
-constexpr int ATC_SMEM = OFF_BAR + 512 + 1024;
+// NG = softmax groups per CTA.  2 (one utterance: 112 CTAs, one per SM): the groups take alternate key blocks, 3 S tiles
+// in TMEM, 4 K / 3 V slots, 512 TMEM columns.  1 (padded batches: thousands of CTAs): one group walks all key blocks,
+// 1 S tile, 2 K / 2 V slots, 256 TMEM columns, 80 KB of shared memory — TWO CTAs per SM overlap each other's latencies
+// instead of two groups inside one CTA, and there is nothing to merge.
+template <int NG> struct AtcCfg {
+  static constexpr int NSK = NG == 2 ? 4 : 2, NST = NG == 2 ? 3 : 2, NSB = NG == 2 ? 3 : 1;
+  static constexpr int OFF_Q = 0, OFF_K = TILE_B, OFF_V = OFF_K + NSK * TILE_B, OFF_P = OFF_V + NST * TILE_B;
+  static constexpr int OFF_ML = OFF_P + (NG == 2 ? 2 * P_B : 0), OFF_BAR = OFF_ML + (NG == 2 ? TQ * 2 * 4 : 0);
+  static constexpr int THREADS = 32 * (4 * NG + 1);      // softmax warps + the issuer warp
+  static constexpr int SMEM = OFF_BAR + 512 + 1024;
+  static constexpr int TMEM_COLS = NG == 2 ? 512 : 256;
+};
 static_assert(TQ * TD * 4 <= P_B, "group-1 output state fits its P buffer");
+static_assert(ATC_P_TMEM || true, "");
 
 struct AttnTcParams {
   CUtensorMap tm;            // q|k|v bf16 [B][L][1536], box {64, 128, 1}
@@ -112,7 +119,12 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-__global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid_constant__ AttnTcParams p) {
+template <int NG>
+__global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_tc_kernel(const __grid_constant__ AttnTcParams p) {
+  using C = AtcCfg<NG>;
+  constexpr int NSK = C::NSK, NST = C::NST, NSB = C::NSB, OFF_Q = C::OFF_Q, OFF_K = C::OFF_K, OFF_V = C::OFF_V, OFF_P = C::OFF_P,
+                OFF_ML = C::OFF_ML, OFF_BAR = C::OFF_BAR;
+  static_assert(NG == 2 || ATC_P_TMEM, "the one-group form keeps P in TMEM (no shared-memory P buffers)");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sQ = smem + OFF_Q;
@@ -139,11 +151,11 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
     for (int i = 0; i < NSK; ++i) mbar_init(&k_full[i], 1);
     for (int i = 0; i < NST; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1); }
     for (int i = 0; i < NSB; ++i) mbar_init(&s_full[i], 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
+    for (int i = 0; i < NG; ++i) { mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
     mbar_fence_init();
     tma_prefetch_desc(&p.tm);
   }
-  if (warp == 0) tmem_alloc(tmem_slot, 512);
+  if (warp == 0) tmem_alloc(tmem_slot, C::TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -152,7 +164,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
   const int Lk = p.lens ? min(max(p.lens[b], 1), p.L) : p.L;
   const int nkb = (Lk + TK - 1) / TK;
 
-  if (warp == 8) {
+  if (warp == 4 * NG) {
     // ---- the issuer: every TMA load and every tcgen05.mma of the CTA, in the order their preconditions become true ----
     if (lane == 0) {
       const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
@@ -185,13 +197,13 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
       mbar_wait_sleep(bar_q, 0);
       for (int j = 0; j < NSB && j < nkb; ++j) issue_s(j);
       for (int j = 0; j < nkb; ++j) {
-        const int g = j & 1, it = j >> 1, s = j % NST;
+        const int g = j % NG, it = j / NG, s = j % NST;
         // P_j is in shared memory, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
         mbar_wait_sleep(&p_full[g], it & 1);
         if (j + NSK < nkb) load_k(j + NSK);
-        if (j >= 1 && j + 2 < nkb) {             // V slot of block j - 1: its product was issued one iteration ago
+        if (j >= 1 && j - 1 + NST < nkb) {       // V slot of block j - 1: its product was issued one iteration ago
           mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
-          load_v(j + 2);
+          load_v(j - 1 + NST);
         }
         mbar_wait_sleep(&v_full[s], (j / NST) & 1);
         tc_fence_after();
@@ -225,7 +237,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
   for (int d = 0; d < TD; ++d) o[d] = 0.f;
   uint8_t* prow = sP + g * P_B + row * 128;
   int i = 0;
-  for (int j = g; j < nkb; j += 2, ++i) {
+  for (int j = g; j < nkb; j += NG, ++i) {
     const int sb = j % NSB;
     const uint32_t tS = tmem_base + lane_off + sb * TK;
     mbar_wait_sleep(&s_full[sb], (j / NSB) & 1);
@@ -360,19 +372,25 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
   }
   tc_fence_before();
   if (threadIdx.x == 0) ATC_STAMP(14);
-  // ---- merge group 1 into group 0 (group 1's P buffer is idle: its last product has completed) ----
-  float* xo = reinterpret_cast<float*>(sP + P_B);           // [64 d][128 rows]
-  if (g == 1) {
+  // ---- merge group 1 into group 0 (group 1's P buffer is idle: its last product has completed); one group: nothing to merge ----
+  float c0 = 1.f, c1 = 0.f, l_all = l;
+  [[maybe_unused]] float* xo = reinterpret_cast<float*>(sP + P_B);           // [64 d][128 rows]
+  if constexpr (NG == 2) {
+    if (g == 1) {
 #pragma unroll
-    for (int d = 0; d < TD; ++d) xo[d * TQ + row] = o[d];
-    sML[row * 2] = m; sML[row * 2 + 1] = l;
+      for (int d = 0; d < TD; ++d) xo[d * TQ + row] = o[d];
+      sML[row * 2] = m; sML[row * 2 + 1] = l;
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (g == 0) {
+      const float m1 = sML[row * 2], l1 = sML[row * 2 + 1];
+      const float mn = fmaxf(m, m1);
+      c0 = (m == -INFINITY) ? 0.f : ex2f(m - mn); c1 = (m1 == -INFINITY) ? 0.f : ex2f(m1 - mn);
+      l_all = l * c0 + l1 * c1;
+    }
   }
-  asm volatile("bar.sync 1, 256;" ::: "memory");
   if (g == 0) {
-    const float m1 = sML[row * 2], l1 = sML[row * 2 + 1];
-    const float mn = fmaxf(m, m1);
-    const float c0 = (m == -INFINITY) ? 0.f : ex2f(m - mn), c1 = (m1 == -INFINITY) ? 0.f : ex2f(m1 - mn);
-    const float inv = 1.0f / (l * c0 + l1 * c1);
+    const float inv = 1.0f / l_all;
     const int t = q0 + row;
     if (t < p.L) {
       __nv_bfloat16* dst = p.out + ((size_t)b * p.L + t) * 512 + head * TD;
@@ -380,7 +398,11 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
       for (int d8 = 0; d8 < TD / 8; ++d8) {
         float y[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) y[e] = (o[d8 * 8 + e] * c0 + xo[(d8 * 8 + e) * TQ + row] * c1) * inv;
+        for (int e = 0; e < 8; ++e) {
+          float v = o[d8 * 8 + e] * c0;
+          if constexpr (NG == 2) v += xo[(d8 * 8 + e) * TQ + row] * c1;
+          y[e] = v * inv;
+        }
         *reinterpret_cast<uint4*>(dst + d8 * 8) = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]),
                                                              pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
       }
@@ -391,7 +413,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
   if (threadIdx.x == 0) ATC_STAMP(15);
   if (warp == 0) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
   }
 }
 
@@ -400,23 +422,34 @@ __global__ void __launch_bounds__(ATC_THREADS, 1) s3_attn_tc_kernel(const __grid
 static unsigned long long* g_atc_dbg = nullptr;
 void attn_tc_set_debug(unsigned long long* buf) { g_atc_dbg = buf; }
 
+template <int NG>
+static int attn_tc_launch_as(const AttnTcParams& p, dim3 grid, cudaStream_t st) {
+  static CbxPerDeviceOnce once;
+  if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_attn_tc_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, AtcCfg<NG>::SMEM));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = dim3(AtcCfg<NG>::THREADS); cfg.dynamicSmemBytes = AtcCfg<NG>::SMEM; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_attn_tc_kernel<NG>, p));
+  return CBX_OK;
+}
+
 int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int ld_qkv, const int* lens, cudaStream_t st) {
   CBX_CHECK(ld_qkv == 1536, "s3_attn_tc: q|k|v row stride %d (expected 1536)", ld_qkv);
-  static CbxPerDeviceOnce once;
-  if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATC_SMEM));
   AttnTcParams p;
   if (make_tmap_bf16_3d(&p.tm, qkv, 1536, L, B, 1536, (uint64_t)1536 * L, TD, TQ)) return CBX_ERR;
   p.out = out; p.lens = lens; p.L = L;
   p.dbg = g_atc_dbg;
   if (g_atc_dbg) g_atc_dbg += 16;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((L + TQ - 1) / TQ, 8, B); cfg.blockDim = dim3(ATC_THREADS); cfg.dynamicSmemBytes = ATC_SMEM; cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_attn_tc_kernel, p));
-  return CBX_OK;
+  const dim3 grid((L + TQ - 1) / TQ, 8, B);
+  // few CTAs (one utterance): two softmax groups per CTA split the key blocks; more CTAs than two per SM (padded batches): one
+  // group per CTA and two CTAs per SM.  CBX_ATTN_GROUPS=1|2 forces a form.
+  static const int force = [] { const char* v = getenv("CBX_ATTN_GROUPS"); return v ? atoi(v) : 0; }();
+  const long long ctas = (long long)grid.x * grid.y * grid.z;
+  const int ng = force == 1 || force == 2 ? force : (ctas > 2 * 148 ? 1 : 2);
+  return ng == 1 ? attn_tc_launch_as<1>(p, grid, st) : attn_tc_launch_as<2>(p, grid, st);
 }
 
 }  // namespace cbx

@@ -1,4 +1,8 @@
-"""The estimator's attention kernels alone (csrc/s3_attn_tc.cu: tcgen05; csrc/s3_attn.cu: mma.sync) against a plain PyTorch
+"""(The tcgen05 kernel has two instantiations — two softmax groups per CTA for one utterance, one group and two CTAs per SM for
+padded batches, chosen by the CTA count: B = 2 cases run the first, the B >= 4 x 8 heads x q-tiles > 296 case the second; the
+switch test in test_cfm_switches_gpu.py style is not needed here: both are reached by shape.)
+
+The estimator's attention kernels alone (csrc/s3_attn_tc.cu: tcgen05; csrc/s3_attn.cu: mma.sync) against a plain PyTorch
 fp32 attention on the same bf16 q|k|v (reference: matcha/transformer.py:196-204 -> diffusers AttnProcessor2_0; 8 heads x 64,
 scale 1/8, key-padding mask of utils/mask.py:167-193).  Tolerance: the kernels round the probabilities to bf16 before the
 P V product and the output to bf16: 2^-8 relative on values of order 1 -> max-abs 2e-2, relative L2 6e-3 (measured ~3e-3)."""
@@ -36,7 +40,8 @@ def _ref(qkv, lens):
 
 @pytest.mark.parametrize("tc", [1, 0])
 @pytest.mark.parametrize("B,L,lens", [(2, 44, None), (2, 128, None), (2, 129, None), (2, 812, None), (2, 1800, None),
-                                      (4, 300, [300, 300, 17, 17]), (6, 520, [520, 520, 257, 257, 128, 128])])
+                                      (4, 300, [300, 300, 17, 17]), (6, 520, [520, 520, 257, 257, 128, 128]),
+                                      (16, 300, [300, 300, 17, 17, 200, 200, 129, 129, 128, 128, 64, 64, 300, 300, 1, 1])])
 def test_attention_matches_fp32_torch(tc, B, L, lens):
     g = torch.Generator().manual_seed(L * 7 + B)
     qkv = (torch.randn(B, L, 1536, generator=g) * 1.5).to(torch.bfloat16).cuda()
