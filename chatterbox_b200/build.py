@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcbx.so")
-SOURCES = ["cbx_core.cu", "t3_decode.cu", "t3_prefill.cu", "t3_batch.cu", "t3_front.cu", "s3_gemm.cu", "s3_ffn.cu", "s3_attn.cu", "s3_attn_tc.cu", "s3_cfm.cu", "s3_front.cu", "s3_hift.cu"]
+SOURCES = ["cbx_core.cu", "t3_decode.cu", "t3_prefill.cu", "t3_batch.cu", "t3_front.cu", "s3_gemm.cu", "s3_gemm_ws.cu", "s3_ffn.cu", "s3_attn.cu", "s3_attn_tc.cu", "s3_cfm.cu", "s3_front.cu", "s3_hift.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
 

@@ -785,7 +785,11 @@ constexpr uint32_t V_T3_F32 = F_RESID | F_F32;                        // T3 pref
 constexpr uint32_t V_T3_GU = F_SWIGLU | F_HILO;                       // T3 prefill: gate/up + SwiGLU -> hi/lo planes
 }  // namespace
 
+bool gemm_ws_eligible(const GemmDesc& d);
+int gemm_ws_launch(const GemmDesc& d, cudaStream_t st);
+
 int gemm_launch(const GemmDesc& d, cudaStream_t st) {
+  if (gemm_ws_eligible(d)) return gemm_ws_launch(d, st);      // padded batches: weight-stationary persistent kernel (s3_gemm_ws.cu)
   GemmParams p;
   p.tmA = d.tmA; p.tmW = d.tmW;
   p.B = d.B; p.L = d.L; p.N = d.N; p.K = d.K; p.taps = d.taps; p.n_tile = d.n_tile;

@@ -16,9 +16,13 @@ torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(3):
-    cfm.forward_batch(mu, None, 10, spks=spks, cond=cond)
+    out = cfm.forward_batch(mu, None, 10, spks=spks, cond=cond)
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 3
 flop = nb * 10 * 2 * L * (132.18e6 + 114688.0 * L)
 print(f"nb={nb} L={L}: {ms:.2f} ms per solve, {ms / nb:.2f} ms per utterance, {flop / ms / 1e9:.1f} TFLOP/s")
+o = out[0] if isinstance(out, (tuple, list)) else out
+print(f"checksum {float(o.double().sum()):.6f} absmax {float(o.abs().max()):.4f} finite {bool(torch.isfinite(o).all())}")
+if os.environ.get("CFM_SAVE"):
+    torch.save(o.cpu(), os.environ["CFM_SAVE"])
