@@ -27,6 +27,9 @@ namespace {
 #ifndef ATC_P_TMEM
 #define ATC_P_TMEM 1          // P travels to the second product through TMEM (in place over the S tile); 0: through shared memory
 #endif
+#ifndef ATC_ONEPASS
+#define ATC_ONEPASS 1         // bit (NG - 1): that instantiation reads each S tile from TMEM ONCE (see the softmax loop below)
+#endif
 constexpr int TQ = 128, TK = 128, TD = 64;
 constexpr int TILE_B = TQ * TD * 2;                    // 16 KB: [128][64] bf16
 constexpr int P_B = TQ * TK * 2;                       // 32 KB: two k-blocks of [128][64]
@@ -125,6 +128,12 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   constexpr int NSK = C::NSK, NST = C::NST, NSB = C::NSB, OFF_Q = C::OFF_Q, OFF_K = C::OFF_K, OFF_V = C::OFF_V, OFF_P = C::OFF_P,
                 OFF_ML = C::OFF_ML, OFF_BAR = C::OFF_BAR;
   static_assert(NG == 2 || ATC_P_TMEM, "the one-group form keeps P in TMEM (no shared-memory P buffers)");
+  constexpr bool ONEPASS = ((ATC_ONEPASS >> (NG - 1)) & 1) != 0;
+  static_assert(!ONEPASS || ATC_P_TMEM, "the one-pass softmax keeps P in TMEM");
+  // one group, one pass: P gets its OWN 64 TMEM columns (S [0, 128) | P [128, 192) | O~ [192, 256)), so the next block's
+  // Q K^T may overwrite the S tile as soon as the four softmax warps hold the row in registers (s_free) — it runs under
+  // the exponentials of this block instead of after this block's P V product
+  constexpr bool SPLIT_P = ONEPASS && NG == 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sQ = smem + OFF_Q;
@@ -140,7 +149,8 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   uint64_t* s_full = v_free + NST;       // [NSB] S tile of block j in TMEM buffer j % NSB
   uint64_t* p_full = s_full + NSB;       // [2]   P of the group's block written, S buffer read (4 arrivals: one per warp)
   uint64_t* o_full = p_full + 2;         // [2]   the group's P V product has completed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+  uint64_t* s_free = o_full + 2;         // [1]   SPLIT_P: the S tile has been read into registers (4 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * TQ, head = blockIdx.y, b = blockIdx.z;
@@ -152,6 +162,7 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
     for (int i = 0; i < NST; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1); }
     for (int i = 0; i < NSB; ++i) mbar_init(&s_full[i], 1);
     for (int i = 0; i < NG; ++i) { mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
+    mbar_init(s_free, 4);
     mbar_fence_init();
     tma_prefetch_desc(&p.tm);
   }
@@ -160,7 +171,7 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_o = tmem_base + NSB * TK;           // O~[2] behind the S buffers
+  const uint32_t tmem_o = tmem_base + NSB * TK + (SPLIT_P ? TK / 2 : 0);      // O~[NG] behind the S buffers (and the P tile)
   const int Lk = p.lens ? min(max(p.lens[b], 1), p.L) : p.L;
   const int nkb = (Lk + TK - 1) / TK;
 
@@ -196,6 +207,27 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
       for (int j = 0; j < NSK && j < nkb; ++j) { load_k(j); if (j < NST) load_v(j); }
       mbar_wait_sleep(bar_q, 0);
       for (int j = 0; j < NSB && j < nkb; ++j) issue_s(j);
+      if constexpr (SPLIT_P) {
+        for (int j = 0; j < nkb; ++j) {
+          const int s = j % NST;
+          mbar_wait_sleep(s_free, j & 1);            // S_j is in registers: the S tile and K slot j % NSK are free
+          if (j + NSK < nkb) load_k(j + NSK);
+          if (j + 1 < nkb) issue_s(j + 1);           // runs while the softmax warps exponentiate block j
+          mbar_wait_sleep(&p_full[0], j & 1);
+          if (j >= 1 && j - 1 + NST < nkb) {
+            mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+            load_v(j - 1 + NST);
+          }
+          mbar_wait_sleep(&v_full[s], (j / NST) & 1);
+          tc_fence_after();
+          const uint32_t va = smem_u32(sV + s * TILE_B);
+#pragma unroll
+          for (int k = 0; k < TK / 16; ++k)
+            umma_bf16_ts(tmem_o, tmem_base + TK + k * 8, umma_desc_k128(va + k * 2048), idesc_o, (k != 0) || (j > 0));
+          umma_commit(&o_full[0]);
+          umma_commit(&v_free[s]);
+        }
+      } else
       for (int j = 0; j < nkb; ++j) {
         const int g = j % NG, it = j / NG, s = j % NST;
         // P_j is in shared memory, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
@@ -214,7 +246,7 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
           // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
           const uint64_t db = umma_desc_k128(va + k * 2048);
 #if ATC_P_TMEM
-          umma_bf16_ts(tmem_o + g * TD, tmem_base + (j % NSB) * TK + k * 8, db, idesc_o, k != 0);
+          umma_bf16_ts(tmem_o + g * TD, tmem_base + (j % NSB) * TK + k * 8, db, idesc_o, (k != 0) || (ONEPASS && it > 0));
 #else
           const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
           umma_bf16(tmem_o + g * TD, da, db, idesc_o, k != 0);
@@ -231,12 +263,115 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   const uint32_t lane_off = (uint32_t)(q * 32) << 16;
   const uint32_t tO = tmem_o + lane_off + g * TD;
   const float sc = 0.125f * 1.4426950408889634f;              // 1/sqrt(64) * log2(e): scores in the log2 domain
-  float m = -INFINITY, l = 0.f, corr_prev = 1.f;
+  float m = -INFINITY, l = 0.f;
+  [[maybe_unused]] float corr_prev = 1.f;
   float o[TD];
 #pragma unroll
   for (int d = 0; d < TD; ++d) o[d] = 0.f;
-  uint8_t* prow = sP + g * P_B + row * 128;
+  [[maybe_unused]] uint8_t* prow = sP + g * P_B + row * 128;
   int i = 0;
+  if constexpr (ONEPASS) {
+    // One read of the S tile: the whole row (128 scores) sits in registers between the maximum and the exponentials, and
+    // the running output stays in TMEM — the P V products of consecutive blocks ACCUMULATE there, nothing is folded in
+    // registers.  The reference maximum m of a row is only raised when a block's maximum exceeds it by more than 8 (log2
+    // domain: p <= 256, far inside bf16 / fp32 range); then, and only then, the row's O~ and l are rescaled by
+    // exp2(m_old - m_new).  O / l does not depend on the reference, so the result is the same softmax.  Per key block
+    // the TMEM traffic of a row drops from 2 x 128 (S twice) + 64 (O~) reads to 128.
+    for (int j = g; j < nkb; j += NG, ++i) {
+      const int sb = j % NSB;
+      const uint32_t tS = tmem_base + lane_off + sb * TK;
+      mbar_wait_sleep(&s_full[sb], (j / NSB) & 1);
+      tc_fence_after();
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(2);
+      const int kbase = j * TK;
+      uint32_t s[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld32_issue(tS + c * 32, s[c]);
+      tmem_ld_wait();
+      if constexpr (SPLIT_P) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_free);
+      }
+      const uint32_t tP = SPLIT_P ? tmem_base + lane_off + TK : tS;
+      if (kbase + TK > Lk) {       // keys past the row's length: -inf (exp2 -> 0)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int k = 0; k < 32; ++k)
+            if (kbase + c * 32 + k >= Lk) s[c][k] = 0xff800000u;
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(s[c][k]));
+      const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sc;
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(3);
+      // Every phase of o_full is observed, in order (a parity wait cannot tell phases two apart): the group's previous
+      // product — the last writer of O~, and with SPLIT_P the last reader of the P tile — has completed.  Needed before a
+      // rescale, else before the first P store; it was issued a whole softmax ago, so this rarely spins.
+      bool waited = i == 0;
+      auto wait_prev = [&]() {
+        if (!waited) { mbar_wait_sleep(&o_full[g], (i - 1) & 1); tc_fence_after(); waited = true; }
+      };
+      const bool need = mb > m + 8.0f;              // first block: m = -inf
+      if (__any_sync(0xffffffffu, need)) {          // warp-uniform: tcgen05.ld / .st are warp-collective
+        const float m_new = need ? mb : m;
+        if (i > 0) {
+          const float f = ex2f(m - m_new);          // 1 for the rows of the warp that keep their reference
+          wait_prev();
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {             // 16 columns at a time: the score row stays in registers beside it
+            uint32_t r[16];
+            tmem_ld16_issue(tO + c * 16, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 16; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * f);
+            tmem_st16(tO + c * 16, r);
+          }
+          l *= f;
+        }
+        m = m_new;
+      }
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(5);
+      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pw[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float p0 = ex2f(fmaf(__uint_as_float(s[c][2 * e]), sc, -m)), p1 = ex2f(fmaf(__uint_as_float(s[c][2 * e + 1]), sc, -m));
+          pw[e] = pack_bf16x2(p0, p1);
+          // the row sum is taken over the ROUNDED probabilities, the values the tensor core multiplies: with a lazily
+          // raised reference the dominant key's p is no longer exactly 1, and its bf16 rounding would otherwise appear
+          // in the output unnormalised (numerator rounded, denominator not)
+          ls4[e & 3] += __uint_as_float(pw[e] << 16) + __uint_as_float(pw[e] & 0xffff0000u);
+        }
+        if (c == 0) wait_prev();
+        tmem_st16(tP + c * 16, pw);          // P chunk c (over S columns [16 c, 16 c + 16) unless SPLIT_P: the row is in registers)
+      }
+      l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(6);
+      tmem_st_wait();
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(7);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[g]);
+      if (threadIdx.x == 0 && i == 1) ATC_STAMP(8);
+    }
+    if (i > 0) {
+      mbar_wait_sleep(&o_full[g], (i - 1) & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float v[32];
+        tmem_ld32(tO + c * 32, v);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) o[c * 32 + k] = v[k];
+      }
+    }
+  } else {
   for (int j = g; j < nkb; j += NG, ++i) {
     const int sb = j % NSB;
     const uint32_t tS = tmem_base + lane_off + sb * TK;
@@ -369,6 +504,7 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
 #pragma unroll
       for (int k = 0; k < 32; ++k) o[c * 32 + k] = fmaf(o[c * 32 + k], corr_prev, v[k]);
     }
+  }
   }
   tc_fence_before();
   if (threadIdx.x == 0) ATC_STAMP(14);
