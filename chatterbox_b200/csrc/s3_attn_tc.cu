@@ -19,6 +19,7 @@
 // (A variant in which thread 0 of each softmax group issued its own loads and MMAs — no issuer warp, 255 registers — was
 // slower: the issue sequence sits on the group's critical path.  33.6 vs 32.6 ms per solve.)
 #include "s3_gemm.cuh"
+#include <cstdio>
 #include <cstdlib>
 
 namespace cbx {
@@ -53,13 +54,10 @@ struct AttnTcParams {
   __nv_bfloat16* out;        // [B][L][512]
   const int* lens;
   int L;
-  unsigned long long* dbg;   // optional %globaltimer stamps of CTA (0, 0, 0) (tools/attn_stamps.py)
+  unsigned long long* dbg;   // optional clock64 stamps of CTA (0, 0, 0), 32 slots per launch (tools/attn_stamps.py, attn_batch_stamps.py)
 };
-__device__ __forceinline__ unsigned long long atc_gtimer() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
+// stamps are SM cycle counts (clock64): every stamp of a launch comes from CTA (0, 0, 0), i.e. one SM — finer than %globaltimer
+__device__ __forceinline__ unsigned long long atc_gtimer() { return (unsigned long long)clock64(); }
 #define ATC_STAMP(k) do { if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) p.dbg[k] = atc_gtimer(); } while (0)
 
 __device__ __forceinline__ float ex2f(float x) {
@@ -176,85 +174,119 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   const int nkb = (Lk + TK - 1) / TK;
 
   if (warp == 4 * NG) {
-    // ---- the issuer: every TMA load and every tcgen05.mma of the CTA, in the order their preconditions become true ----
-    if (lane == 0) {
-      const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
-      const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
-      auto load_k = [&](int j) {
-        const int s = j % NSK;
+    // ---- the issuer: every TMA load and every tcgen05.mma of the CTA, in the order their preconditions become true.
+    // The WHOLE warp walks the loop (convergent control flow); lane 0 alone waits on barriers and executes the TMA / MMA /
+    // commit instructions.  Addresses and descriptors are computed outside those one-lane regions, from warp-uniform
+    // values, so they live in uniform registers: computed by the issuing lane inside a divergent branch they sat in vector
+    // registers and every tcgen05.mma paid three R2UR round trips (~90 cycles per MMA issued, measured with clock64
+    // stamps: the issuer, not the softmax warps, set the pace of a key block). ----
+    const bool lead = elect_one();
+    // values the compiler cannot prove warp-uniform (one came through shared memory, the other through a global load) are
+    // passed through a warp reduction, whose result lands in a uniform register
+    const uint32_t tbase = __reduce_max_sync(0xffffffffu, tmem_base), tmo = __reduce_max_sync(0xffffffffu, tmem_o);
+    const int nkb_u = (int)__reduce_max_sync(0xffffffffu, (unsigned)nkb);
+    const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
+    const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
+    const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV);
+    auto wait = [&](uint64_t* bar, uint32_t parity) {
+      if (lead) mbar_wait_sleep(bar, parity);
+      __syncwarp();
+    };
+    auto load_k = [&](int j) {
+      const int s = j % NSK;
+      if (lead) {
         mbar_arrive_expect_tx(&k_full[s], TILE_B);
         tma_load_3d(sK + s * TILE_B, &p.tm, &k_full[s], 512 + head * TD, j * TK, b);
-      };
-      auto load_v = [&](int j) {
-        const int s = j % NST;
+      }
+    };
+    auto load_v = [&](int j) {
+      const int s = j % NST;
+      if (lead) {
         mbar_arrive_expect_tx(&v_full[s], TILE_B);
         tma_load_3d(sV + s * TILE_B, &p.tm, &v_full[s], 1024 + head * TD, j * TK, b);
-      };
-      const uint64_t dq = umma_desc_k128(smem_u32(sQ));
-      auto issue_s = [&](int j) {            // S_j = Q K_j^T into S buffer j % NSB (the caller knows the buffer is free)
-        const int s = j % NSK, sb = j % NSB;
-        mbar_wait_sleep(&k_full[s], (j / NSK) & 1);
+      }
+    };
+    auto issue_s = [&](int j) {            // S_j = Q K_j^T into S buffer j % NSB (the caller knows the buffer is free)
+      const int s = j % NSK, sb = j % NSB;
+      wait(&k_full[s], (j / NSK) & 1);
+      const uint64_t dq = umma_desc_k128(q_addr), db = umma_desc_k128(k_addr + s * TILE_B);
+      const uint32_t d = tbase + sb * TK;
+      if (lead) {
         tc_fence_after();
-        const uint64_t db = umma_desc_k128(smem_u32(sK + s * TILE_B));
 #pragma unroll
-        for (int k = 0; k < TD / 16; ++k) umma_bf16(tmem_base + sb * TK, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
+        for (int k = 0; k < TD / 16; ++k) umma_bf16(d, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
         umma_commit(&s_full[sb]);
-      };
+      }
+    };
+    if (lead) {
       pdl_wait();                                  // q|k|v come from the GEMM just before
       ATC_STAMP(1);
       mbar_arrive_expect_tx(bar_q, TILE_B);
       tma_load_3d(sQ, &p.tm, bar_q, head * TD, q0, b);
-      for (int j = 0; j < NSK && j < nkb; ++j) { load_k(j); if (j < NST) load_v(j); }
-      mbar_wait_sleep(bar_q, 0);
-      for (int j = 0; j < NSB && j < nkb; ++j) issue_s(j);
-      if constexpr (SPLIT_P) {
-        for (int j = 0; j < nkb; ++j) {
-          const int s = j % NST;
-          mbar_wait_sleep(s_free, j & 1);            // S_j is in registers: the S tile and K slot j % NSK are free
-          if (j + NSK < nkb) load_k(j + NSK);
-          if (j + 1 < nkb) issue_s(j + 1);           // runs while the softmax warps exponentiate block j
-          mbar_wait_sleep(&p_full[0], j & 1);
-          if (j >= 1 && j - 1 + NST < nkb) {
-            mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
-            load_v(j - 1 + NST);
-          }
-          mbar_wait_sleep(&v_full[s], (j / NST) & 1);
+    }
+    __syncwarp();
+    for (int j = 0; j < NSK && j < nkb_u; ++j) { load_k(j); if (j < NST) load_v(j); }
+    wait(bar_q, 0);
+    for (int j = 0; j < NSB && j < nkb_u; ++j) issue_s(j);
+    if constexpr (SPLIT_P) {
+      for (int j = 0; j < nkb_u; ++j) {
+        const int s = j % NST;
+        wait(s_free, j & 1);                         // S_j is in registers: the S tile and K slot j % NSK are free
+        if (lead && j == 2) ATC_STAMP(20);
+        if (lead && j == 3) ATC_STAMP(25);
+        if (j + NSK < nkb_u) load_k(j + NSK);
+        if (j + 1 < nkb_u) issue_s(j + 1);             // runs while the softmax warps exponentiate block j
+        if (lead && j == 2) ATC_STAMP(21);
+        wait(&p_full[0], j & 1);
+        if (lead && j == 2) ATC_STAMP(22);
+        if (j >= 1 && j - 1 + NST < nkb_u) {
+          wait(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+          load_v(j - 1 + NST);
+        }
+        wait(&v_full[s], (j / NST) & 1);
+        if (lead && j == 2) ATC_STAMP(23);
+        const uint32_t va = v_addr + s * TILE_B, ta = tbase + TK;
+        const uint32_t acc0 = j > 0;
+        if (lead) {
           tc_fence_after();
-          const uint32_t va = smem_u32(sV + s * TILE_B);
 #pragma unroll
-          for (int k = 0; k < TK / 16; ++k)
-            umma_bf16_ts(tmem_o, tmem_base + TK + k * 8, umma_desc_k128(va + k * 2048), idesc_o, (k != 0) || (j > 0));
+          for (int k = 0; k < TK / 16; ++k) umma_bf16_ts(tmo, ta + k * 8, umma_desc_k128(va + k * 2048), idesc_o, k != 0 ? 1u : acc0);
           umma_commit(&o_full[0]);
           umma_commit(&v_free[s]);
         }
-      } else
-      for (int j = 0; j < nkb; ++j) {
+        if (lead && j == 2) ATC_STAMP(24);
+      }
+    } else {
+      for (int j = 0; j < nkb_u; ++j) {
         const int g = j % NG, it = j / NG, s = j % NST;
-        // P_j is in shared memory, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
-        mbar_wait_sleep(&p_full[g], it & 1);
-        if (j + NSK < nkb) load_k(j + NSK);
-        if (j >= 1 && j - 1 + NST < nkb) {       // V slot of block j - 1: its product was issued one iteration ago
-          mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+        // P_j is written, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
+        wait(&p_full[g], it & 1);
+        if (j + NSK < nkb_u) load_k(j + NSK);
+        if (j >= 1 && j - 1 + NST < nkb_u) {       // V slot of block j - 1: its product was issued one iteration ago
+          wait(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
           load_v(j - 1 + NST);
         }
-        mbar_wait_sleep(&v_full[s], (j / NST) & 1);
-        tc_fence_after();
+        wait(&v_full[s], (j / NST) & 1);
         [[maybe_unused]] const uint32_t pa = smem_u32(sP + g * P_B);
-        const uint32_t va = smem_u32(sV + s * TILE_B);
+        const uint32_t va = v_addr + s * TILE_B, ta = tbase + (j % NSB) * TK, td = tmo + g * TD;
+        const uint32_t acc0 = (ONEPASS && it > 0) ? 1u : 0u;
+        if (lead) {
+          tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < TK / 16; ++k) {
-          // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
-          const uint64_t db = umma_desc_k128(va + k * 2048);
+          for (int k = 0; k < TK / 16; ++k) {
+            // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
+            const uint64_t db = umma_desc_k128(va + k * 2048);
 #if ATC_P_TMEM
-          umma_bf16_ts(tmem_o + g * TD, tmem_base + (j % NSB) * TK + k * 8, db, idesc_o, (k != 0) || (ONEPASS && it > 0));
+            umma_bf16_ts(td, ta + k * 8, db, idesc_o, k != 0 ? 1u : acc0);
 #else
-          const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
-          umma_bf16(tmem_o + g * TD, da, db, idesc_o, k != 0);
+            const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
+            umma_bf16(td, da, db, idesc_o, k != 0);
 #endif
+          }
+          umma_commit(&o_full[g]);
+          umma_commit(&v_free[s]);
         }
-        umma_commit(&o_full[g]);
-        umma_commit(&v_free[s]);
-        if (j + NSB < nkb) issue_s(j + NSB);       // into the S buffer block j's group just finished with
+        if (j + NSB < nkb_u) issue_s(j + NSB);       // into the S buffer block j's group just finished with
       }
     }
     __syncwarp();
@@ -282,12 +314,23 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
       const uint32_t tS = tmem_base + lane_off + sb * TK;
       mbar_wait_sleep(&s_full[sb], (j / NSB) & 1);
       tc_fence_after();
-      if (threadIdx.x == 0 && i == 1) ATC_STAMP(2);
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(2);
+      if (threadIdx.x == 0 && i == 3) ATC_STAMP(10);
       const int kbase = j * TK;
       uint32_t s[4][32];
+#ifdef ATC_ABL_LD1            // timing-only ablation: a quarter of the TMEM reads
+      tmem_ld32_issue(tS, s[0]);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 1; c < 4; ++c)
+#pragma unroll
+        for (int k = 0; k < 32; ++k) s[c][k] = s[0][k] ^ (uint32_t)(c * 4096);
+#else
 #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32_issue(tS + c * 32, s[c]);
       tmem_ld_wait();
+#endif
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(4);
       if constexpr (SPLIT_P) {
         tc_fence_before();
         __syncwarp();
@@ -307,7 +350,7 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
 #pragma unroll
         for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(s[c][k]));
       const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sc;
-      if (threadIdx.x == 0 && i == 1) ATC_STAMP(3);
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(3);
       // Every phase of o_full is observed, in order (a parity wait cannot tell phases two apart): the group's previous
       // product — the last writer of O~, and with SPLIT_P the last reader of the P tile — has completed.  Needed before a
       // rescale, else before the first P store; it was issued a whole softmax ago, so this rarely spins.
@@ -334,7 +377,7 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
         }
         m = m_new;
       }
-      if (threadIdx.x == 0 && i == 1) ATC_STAMP(5);
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(5);
       float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -342,23 +385,27 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const float p0 = ex2f(fmaf(__uint_as_float(s[c][2 * e]), sc, -m)), p1 = ex2f(fmaf(__uint_as_float(s[c][2 * e + 1]), sc, -m));
+#ifdef ATC_ABL_TRUNC          // timing-only ablation: one byte-permute instead of the rounding conversion
+          pw[e] = __byte_perm(__float_as_uint(p0), __float_as_uint(p1), 0x7632);
+#else
           pw[e] = pack_bf16x2(p0, p1);
+#endif
           // the row sum is taken over the ROUNDED probabilities, the values the tensor core multiplies: with a lazily
           // raised reference the dominant key's p is no longer exactly 1, and its bf16 rounding would otherwise appear
           // in the output unnormalised (numerator rounded, denominator not)
           ls4[e & 3] += __uint_as_float(pw[e] << 16) + __uint_as_float(pw[e] & 0xffff0000u);
         }
-        if (c == 0) wait_prev();
+        if (c == 0) { if (threadIdx.x == 0 && i == 2) ATC_STAMP(26); wait_prev(); if (threadIdx.x == 0 && i == 2) ATC_STAMP(27); }
         tmem_st16(tP + c * 16, pw);          // P chunk c (over S columns [16 c, 16 c + 16) unless SPLIT_P: the row is in registers)
       }
       l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-      if (threadIdx.x == 0 && i == 1) ATC_STAMP(6);
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(6);
       tmem_st_wait();
-      if (threadIdx.x == 0 && i == 1) ATC_STAMP(7);
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(7);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[g]);
-      if (threadIdx.x == 0 && i == 1) ATC_STAMP(8);
+      if (threadIdx.x == 0 && i == 2) ATC_STAMP(8);
     }
     if (i > 0) {
       mbar_wait_sleep(&o_full[g], (i - 1) & 1);
@@ -553,6 +600,223 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Padded batches: TWO query tiles of one (batch row, head) per CTA.  The one-group kernel above leaves every SM
+// sub-partition with a single softmax warp (five warps occupy eight warp slots, so a second CTA does not fit beside the
+// first at 168 registers): nothing covers that warp's instruction latencies.  Here warps 0-3 own query tile 2 x and warps 4-7
+// tile 2 x + 1 — two independent one-pass softmax pipelines (the loop body is the one above: row in registers, O~
+// accumulating in TMEM, lazily raised reference, P in its own TMEM columns), two warps per sub-partition — and warp 8
+// issues for both.  They share every K and V block: one TMA load feeds both tiles' products.
+//   TMEM, per tile g: S [256 g, +128) | P [256 g + 128, +64) | O~ [256 g + 192, +64)
+struct QtCfg {
+  static constexpr int NSK = 4, NST = 4;         // a TMA load issued one key block ahead arrives late (1.5-2 us under load)
+  static constexpr int OFF_Q = 0, OFF_K = 2 * TILE_B, OFF_V = OFF_K + NSK * TILE_B, OFF_BAR = OFF_V + NST * TILE_B;
+  static constexpr int THREADS = 32 * 10, SMEM = OFF_BAR + 512 + 1024;
+};
+
+__global__ void __launch_bounds__(QtCfg::THREADS, 1) s3_attn_qt_kernel(const __grid_constant__ AttnTcParams p) {
+  constexpr int NSK = QtCfg::NSK, NST = QtCfg::NST;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sQ = smem + QtCfg::OFF_Q;
+  uint8_t* sK = smem + QtCfg::OFF_K;
+  uint8_t* sV = smem + QtCfg::OFF_V;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + QtCfg::OFF_BAR);
+  uint64_t* bar_q = bars;
+  uint64_t* k_full = bars + 1;           // [NSK]
+  uint64_t* v_full = k_full + NSK;       // [NST]
+  uint64_t* v_free = v_full + NST;       // [NST] both tiles' P V products of the block have completed
+  uint64_t* s_full = v_free + NST;       // [2]   per tile: S of the next block is in TMEM
+  uint64_t* s_free = s_full + 2;         // [2]   per tile: the S row is in registers (4 arrivals)
+  uint64_t* p_full = s_free + 2;         // [2]   per tile: P written (4 arrivals)
+  uint64_t* o_full = p_full + 2;         // [2]   per tile: the P V product has completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * 2 * TQ, head = blockIdx.y, b = blockIdx.z;
+  const int ntile = q0 + TQ < p.L ? 2 : 1;          // an odd tile count leaves the last CTA with one tile
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    mbar_init(bar_q, 1);
+    for (int i = 0; i < NSK; ++i) mbar_init(&k_full[i], 1);
+    for (int i = 0; i < NST; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
+    mbar_fence_init();
+    tma_prefetch_desc(&p.tm);
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int Lk = p.lens ? min(max(p.lens[b], 1), p.L) : p.L;
+  const int nkb = (Lk + TK - 1) / TK;
+
+  if (warp == 8) {
+    // ---- issuer 1: Q, the K ring, S = Q K^T of both tiles.  It only ever waits for what the NEXT score product needs
+    // (the tile's S columns free, the K block landed); the P V side has its own warp, so a late V block does not hold
+    // back a score product and vice versa ----
+    if (elect_one()) {
+      const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
+      auto load_k = [&](int j) {
+        const int s = j % NSK;
+        mbar_arrive_expect_tx(&k_full[s], TILE_B);
+        tma_load_3d(sK + s * TILE_B, &p.tm, &k_full[s], 512 + head * TD, j * TK, b);
+      };
+      auto issue_s = [&](int g, int j) {       // S_g,j = Q_g K_j^T over tile g's S columns (the caller knows they are free)
+        const int s = j % NSK;
+        mbar_wait_sleep(&k_full[s], (j / NSK) & 1);
+        tc_fence_after();
+        const uint64_t dq = umma_desc_k128(smem_u32(sQ + g * TILE_B)), db = umma_desc_k128(smem_u32(sK + s * TILE_B));
+#pragma unroll
+        for (int k = 0; k < TD / 16; ++k) umma_bf16(tmem_base + g * 256, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
+        umma_commit(&s_full[g]);
+      };
+      pdl_wait();                                  // q|k|v come from the GEMM just before
+      mbar_arrive_expect_tx(bar_q, ntile * TILE_B);
+      for (int g = 0; g < ntile; ++g) tma_load_3d(sQ + g * TILE_B, &p.tm, bar_q, head * TD, q0 + g * TQ, b);
+      for (int j = 0; j < NSK && j < nkb; ++j) load_k(j);
+      mbar_wait_sleep(bar_q, 0);
+      for (int g = 0; g < ntile; ++g) issue_s(g, 0);
+      for (int j = 0; j < nkb; ++j) {
+        // a tile's S row is in registers: its S columns are free — the next block's Q K^T runs under this block's exponentials
+        for (int g = 0; g < ntile; ++g) {
+          mbar_wait_sleep(&s_free[g], j & 1);
+          if (j + 1 < nkb) issue_s(g, j + 1);
+        }
+        if (j + NSK < nkb) load_k(j + NSK);        // both tiles' S_j have completed: K slot j % NSK is free
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // ---- issuer 2: the V ring, O~ += P V of both tiles ----
+    if (elect_one()) {
+      const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
+      auto load_v = [&](int j) {
+        const int s = j % NST;
+        mbar_arrive_expect_tx(&v_full[s], TILE_B);
+        tma_load_3d(sV + s * TILE_B, &p.tm, &v_full[s], 1024 + head * TD, j * TK, b);
+      };
+      pdl_wait();
+      for (int j = 0; j < NST && j < nkb; ++j) load_v(j);
+      for (int j = 0; j < nkb; ++j) {
+        const int s = j % NST;
+        if (j >= 1 && j - 1 + NST < nkb) {
+          mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+          load_v(j - 1 + NST);
+        }
+        mbar_wait_sleep(&v_full[s], (j / NST) & 1);
+        const uint32_t va = smem_u32(sV + s * TILE_B);
+        for (int g = 0; g < ntile; ++g) {
+          mbar_wait_sleep(&p_full[g], j & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < TK / 16; ++k)
+            umma_bf16_ts(tmem_base + g * 256 + 192, tmem_base + g * 256 + 128 + k * 8, umma_desc_k128(va + k * 2048), idesc_o, (k != 0) || (j > 0));
+          umma_commit(&o_full[g]);
+        }
+        umma_commit(&v_free[s]);
+      }
+    }
+    __syncwarp();
+  } else if ((warp >> 2) < ntile) {
+    const int g = warp >> 2, q = warp & 3, row = q * 32 + lane;
+    const uint32_t tS = tmem_base + ((uint32_t)(q * 32) << 16) + g * 256, tP = tS + 128, tO = tS + 192;
+    const float sc = 0.125f * 1.4426950408889634f;              // 1/sqrt(64) * log2(e): scores in the log2 domain
+    float m = -INFINITY, l = 0.f;
+    for (int j = 0; j < nkb; ++j) {
+      mbar_wait_sleep(&s_full[g], j & 1);
+      tc_fence_after();
+      const int kbase = j * TK;
+      uint32_t s[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld32_issue(tS + c * 32, s[c]);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_free[g]);
+      if (kbase + TK > Lk) {       // keys past the row's length: -inf (exp2 -> 0)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int k = 0; k < 32; ++k)
+            if (kbase + c * 32 + k >= Lk) s[c][k] = 0xff800000u;
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(s[c][k]));
+      const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sc;
+      bool waited = j == 0;        // every phase of o_full is observed, in order (see the one-pass loop above)
+      auto wait_prev = [&]() {
+        if (!waited) { mbar_wait_sleep(&o_full[g], (j - 1) & 1); tc_fence_after(); waited = true; }
+      };
+      const bool need = mb > m + 8.0f;
+      if (__any_sync(0xffffffffu, need)) {
+        const float m_new = need ? mb : m;
+        if (j > 0) {
+          const float f = ex2f(m - m_new);
+          wait_prev();
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t r[16];
+            tmem_ld16_issue(tO + c * 16, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 16; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * f);
+            tmem_st16(tO + c * 16, r);
+          }
+          l *= f;
+        }
+        m = m_new;
+      }
+      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pw[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float p0 = ex2f(fmaf(__uint_as_float(s[c][2 * e]), sc, -m)), p1 = ex2f(fmaf(__uint_as_float(s[c][2 * e + 1]), sc, -m));
+          pw[e] = pack_bf16x2(p0, p1);
+          ls4[e & 3] += __uint_as_float(pw[e] << 16) + __uint_as_float(pw[e] & 0xffff0000u);      // sum of the ROUNDED values
+        }
+        if (c == 0) wait_prev();
+        tmem_st16(tP + c * 16, pw);
+      }
+      l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[g]);
+    }
+    mbar_wait_sleep(&o_full[g], (nkb - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.0f / l;
+    const int t = q0 + g * TQ + row;
+    __nv_bfloat16* dst = p.out + ((size_t)b * p.L + (t < p.L ? t : 0)) * 512 + head * TD;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      float v[32];
+      tmem_ld32(tO + c * 32, v);
+      if (t < p.L) {
+#pragma unroll
+        for (int d8 = 0; d8 < 4; ++d8)
+          *reinterpret_cast<uint4*>(dst + c * 32 + d8 * 8) =
+              make_uint4(pack_bf16x2(v[d8 * 8] * inv, v[d8 * 8 + 1] * inv), pack_bf16x2(v[d8 * 8 + 2] * inv, v[d8 * 8 + 3] * inv),
+                         pack_bf16x2(v[d8 * 8 + 4] * inv, v[d8 * 8 + 5] * inv), pack_bf16x2(v[d8 * 8 + 6] * inv, v[d8 * 8 + 7] * inv));
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 }  // namespace
 
 static unsigned long long* g_atc_dbg = nullptr;
@@ -561,7 +825,14 @@ void attn_tc_set_debug(unsigned long long* buf) { g_atc_dbg = buf; }
 template <int NG>
 static int attn_tc_launch_as(const AttnTcParams& p, dim3 grid, cudaStream_t st) {
   static CbxPerDeviceOnce once;
-  if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_attn_tc_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, AtcCfg<NG>::SMEM));
+  if (once.first()) {
+    CBX_CUDA(cudaFuncSetAttribute(s3_attn_tc_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, AtcCfg<NG>::SMEM));
+    if (getenv("CBX_ATTN_OCC")) {      // debug aid: resident CTAs per SM as the runtime computes it
+      int nb = 0;
+      CBX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, s3_attn_tc_kernel<NG>, AtcCfg<NG>::THREADS, AtcCfg<NG>::SMEM));
+      fprintf(stderr, "[cbx] s3_attn_tc_kernel<%d>: %d CTAs per SM (%d threads, %d B shared memory)\n", NG, nb, AtcCfg<NG>::THREADS, AtcCfg<NG>::SMEM);
+    }
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = dim3(AtcCfg<NG>::THREADS); cfg.dynamicSmemBytes = AtcCfg<NG>::SMEM; cfg.stream = st;
   cudaLaunchAttribute at[1];
@@ -578,13 +849,26 @@ int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L
   if (make_tmap_bf16_3d(&p.tm, qkv, 1536, L, B, 1536, (uint64_t)1536 * L, TD, TQ)) return CBX_ERR;
   p.out = out; p.lens = lens; p.L = L;
   p.dbg = g_atc_dbg;
-  if (g_atc_dbg) g_atc_dbg += 16;
+  if (g_atc_dbg) g_atc_dbg += 32;
   const dim3 grid((L + TQ - 1) / TQ, 8, B);
   // few CTAs (one utterance): two softmax groups per CTA split the key blocks; more CTAs than two per SM (padded batches): one
   // group per CTA and two CTAs per SM.  CBX_ATTN_GROUPS=1|2 forces a form.
   static const int force = [] { const char* v = getenv("CBX_ATTN_GROUPS"); return v ? atoi(v) : 0; }();
   const long long ctas = (long long)grid.x * grid.y * grid.z;
   const int ng = force == 1 || force == 2 ? force : (ctas > 2 * 148 ? 1 : 2);
+  static const bool qt_on = [] { const char* v = getenv("CBX_ATTN_QT"); return !(v && v[0] == '0'); }();
+  if (ng == 1 && qt_on && force == 0) {        // padded batches: two query tiles per CTA
+    static CbxPerDeviceOnce once;
+    if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_attn_qt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, QtCfg::SMEM));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((grid.x + 1) / 2, 8, B); cfg.blockDim = dim3(QtCfg::THREADS); cfg.dynamicSmemBytes = QtCfg::SMEM; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    CBX_CUDA(cudaLaunchKernelEx(&cfg, s3_attn_qt_kernel, p));
+    return CBX_OK;
+  }
   return ng == 1 ? attn_tc_launch_as<1>(p, grid, st) : attn_tc_launch_as<2>(p, grid, st);
 }
 

@@ -155,7 +155,7 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     // multicasts it into all 8 shared memories (1 / 8 of the L2 reads).  A peer's barriers must exist before data may land
     // in its shared memory: the producer warp takes the cluster barrier here, the other warps further down.
     if (OUT) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-    if (lane == 0) {
+    if (elect_one()) {
       if (!OUT) {
         issue_weights();
         pdl_wait();
@@ -180,7 +180,7 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     __syncwarp();
     pdl_wait();
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       if (!OUT) mma1();
       else {
         const uint32_t idesc0 = umma_idesc_bf16(FBM, OC);
@@ -283,11 +283,11 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
     cluster_sync_all();                 // x1 and the normalised x tile of all 8 column slices are in global memory
     tc_fence_after();
     if (threadIdx.x == 128) FFN_STAMP(15);
-    if (warp == 0 && lane == 0) {
+    if (warp == 0 && elect_one()) {
       asm volatile("fence.proxy.async;" ::: "memory");
       for (int kb = 0; kb < 4; ++kb) tma_load_3d(sX + kb * KB_A, &p.tmX, &bar_k[kb], kb * FBK, t0, b);
     }
-    if (warp == 1 && lane == 0) mma1();
+    if (warp == 1 && elect_one()) mma1();
     __syncwarp();
   }
   if (frow_ok) {
@@ -321,7 +321,7 @@ __global__ void __cluster_dims__(1, 1, FC) __launch_bounds__(FFN_THREADS, 1) s3_
   tc_fence_before();
   __syncthreads();
   // ---- MMA 2 ----
-  if (warp == 1 && lane == 0) {
+  if (warp == 1 && elect_one()) {
     FFN_STAMP(6);
     tc_fence_after();
     mbar_wait_spin(bar_w2, 0);

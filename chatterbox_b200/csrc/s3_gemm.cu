@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
   if (NSP > 1 && warp != 0) ns_prefetch();
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t tx = (p.hilo ? 2 : 1) * A_BYTES + w_bytes;
       const int npre = nkb < NS ? nkb : NS;
       // weight panels of the first ring pass: issued before the PDL wait (they do not depend on the previous kernel)
@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) s3_gemm_kernel(const __grid_c
     }
     if (NSP > 1) { __syncwarp(); pdl_wait(); ns_prefetch(); }      // the producer warp's own residual rows, once its loads are out
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(BM, p.n_tile);
       int s = 0, ph = 0;
       for (int kb = 0; kb < nkb; ++kb) {      // kb: local panel index

@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) s3_gemm_ws_kernel(const __grid_
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(bar_w, WKB * W_KB);
       for (int kb = 0; kb < WKB; ++kb) tma_load_3d(sW + kb * W_KB, &p.tmW, bar_w, kb * WBK, n0, 0);
       pdl_wait();                        // the activations come from the kernel before
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) s3_gemm_ws_kernel(const __grid_
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(WM, WN);
       mbar_wait_spin(bar_w, 0);
       int s = 0, ph = 0, buf = 0, aph = 0;

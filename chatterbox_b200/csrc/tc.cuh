@@ -95,6 +95,15 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// One lane of a CONVERGED warp.  Use this — not `lane == 0` — for the thread that issues tcgen05.mma / TMA: the compiler
+// recognises elect.sync as "exactly one active thread" and hands the descriptors to UTCHMMA through uniform registers
+// directly.  Under a `lane == 0` branch it cannot know, and wraps EVERY tcgen05.mma in an elect / R2UR.BROADCAST / branch
+// loop (~90 cycles per MMA issued, measured in the attention kernel with clock64 stamps).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\t@p mov.u32 %0, 1;\n\t}" : "+r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
