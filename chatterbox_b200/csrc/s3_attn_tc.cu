@@ -54,6 +54,7 @@ struct AttnTcParams {
   __nv_bfloat16* out;        // [B][L][512]
   const int* lens;
   int L;
+  int nx, n_items;           // persistent two-tile kernel: query-tile pairs per (batch row, head); work items = B x 8 x nx
   unsigned long long* dbg;   // optional clock64 stamps of CTA (0, 0, 0), 32 slots per launch (tools/attn_stamps.py, attn_batch_stamps.py)
 };
 // stamps are SM cycle counts (clock64): every stamp of a launch comes from CTA (0, 0, 0), i.e. one SM — finer than %globaltimer
@@ -602,46 +603,68 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
 
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Padded batches: TWO query tiles of one (batch row, head) per CTA.  The one-group kernel above leaves every SM
-// sub-partition with a single softmax warp (five warps occupy eight warp slots, so a second CTA does not fit beside the
-// first at 168 registers): nothing covers that warp's instruction latencies.  Here warps 0-3 own query tile 2 x and warps 4-7
-// tile 2 x + 1 — two independent one-pass softmax pipelines (the loop body is the one above: row in registers, O~
-// accumulating in TMEM, lazily raised reference, P in its own TMEM columns), two warps per sub-partition — and warp 8
-// issues for both.  They share every K and V block: one TMA load feeds both tiles' products.
+// Padded batches: a PERSISTENT kernel, TWO query tiles of one (batch row, head) per work item.
+//   * warps 0-3 own query tile 2 x, warps 4-7 tile 2 x + 1: two independent one-pass softmax pipelines (the loop body is
+//     the one above: row in registers, O~ accumulating in TMEM, lazily raised reference, P in its own TMEM columns), two
+//     warps per SM sub-partition.  They share every K and V block: one TMA load feeds both tiles' products.
+//   * warp 8 issues the score products and owns the Q buffers (two: the next item's Q lands during this item) and the K
+//     ring; warp 9 issues the P V products and owns the V ring.  Neither ever waits for something the other side needs.
+//   * one CTA per SM walks work items blockIdx.x, + gridDim.x, ...: the K / V rings, the barriers' phases and TMEM run on
+//     ACROSS items, so an item's first blocks are in shared memory — and its first score product issued — before the
+//     previous item's last block is finished.  The one-item-per-CTA form paid ~2.5 us of load latency plus prologue and
+//     epilogue per 16 us item with nothing to overlap it (512 TMEM columns: one CTA per SM).
 //   TMEM, per tile g: S [256 g, +128) | P [256 g + 128, +64) | O~ [256 g + 192, +64)
 struct QtCfg {
-  static constexpr int NSK = 4, NST = 4;         // a TMA load issued one key block ahead arrives late (1.5-2 us under load)
-  static constexpr int OFF_Q = 0, OFF_K = 2 * TILE_B, OFF_V = OFF_K + NSK * TILE_B, OFF_BAR = OFF_V + NST * TILE_B;
+  static constexpr int NSK = 4, NST = 4;
+  static constexpr int OFF_Q = 0, OFF_K = 4 * TILE_B, OFF_V = OFF_K + NSK * TILE_B, OFF_BAR = OFF_V + NST * TILE_B;
   static constexpr int THREADS = 32 * 10, SMEM = OFF_BAR + 512 + 1024;
 };
+
+struct QtItem {                 // one (batch row, head, query-tile pair)
+  int w, b, head, q0, ntile, Lk, nkb;
+  bool valid;
+};
+__device__ __forceinline__ QtItem qt_item(const AttnTcParams& p, int w) {
+  QtItem it;
+  it.w = w; it.valid = w < p.n_items;
+  const int x = w % p.nx, t = w / p.nx;
+  it.head = t & 7; it.b = t >> 3;
+  it.q0 = x * 2 * TQ;
+  it.ntile = it.q0 + TQ < p.L ? 2 : 1;              // an odd tile count leaves the last pair with one tile
+  it.Lk = (it.valid && p.lens) ? min(max(p.lens[it.b], 1), p.L) : p.L;
+  it.nkb = (it.Lk + TK - 1) / TK;
+  return it;
+}
 
 __global__ void __launch_bounds__(QtCfg::THREADS, 1) s3_attn_qt_kernel(const __grid_constant__ AttnTcParams p) {
   constexpr int NSK = QtCfg::NSK, NST = QtCfg::NST;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sQ = smem + QtCfg::OFF_Q;
+  uint8_t* sQ = smem + QtCfg::OFF_Q;     // [2 buffers][2 tiles]
   uint8_t* sK = smem + QtCfg::OFF_K;
   uint8_t* sV = smem + QtCfg::OFF_V;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + QtCfg::OFF_BAR);
-  uint64_t* bar_q = bars;
-  uint64_t* k_full = bars + 1;           // [NSK]
+  uint64_t* bar_q = bars;                // [2]   Q of item i in buffer i & 1
+  uint64_t* k_full = bar_q + 2;          // [NSK] running K block n in slot n % NSK
   uint64_t* v_full = k_full + NSK;       // [NST]
-  uint64_t* v_free = v_full + NST;       // [NST] both tiles' P V products of the block have completed
-  uint64_t* s_full = v_free + NST;       // [2]   per tile: S of the next block is in TMEM
+  uint64_t* v_free = v_full + NST;       // [NST] the P V products of the block (both tiles) have completed
+  uint64_t* s_full = v_free + NST;       // [2]   per tile: S of its next block is in TMEM
   uint64_t* s_free = s_full + 2;         // [2]   per tile: the S row is in registers (4 arrivals)
   uint64_t* p_full = s_free + 2;         // [2]   per tile: P written (4 arrivals)
   uint64_t* o_full = p_full + 2;         // [2]   per tile: the P V product has completed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+  uint64_t* o_free = o_full + 2;         // [2]   per tile: the item's O~ has been read out (4 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * 2 * TQ, head = blockIdx.y, b = blockIdx.z;
-  const int ntile = q0 + TQ < p.L ? 2 : 1;          // an odd tile count leaves the last CTA with one tile
+  const int stride = gridDim.x;
   pdl_launch_dependents();
   if (threadIdx.x == 0) {
-    mbar_init(bar_q, 1);
+    for (int i = 0; i < 2; ++i) mbar_init(&bar_q[i], 1);
     for (int i = 0; i < NSK; ++i) mbar_init(&k_full[i], 1);
     for (int i = 0; i < NST; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); mbar_init(&p_full[i], 4); mbar_init(&o_full[i], 1); mbar_init(&o_free[i], 4);
+    }
     mbar_fence_init();
     tma_prefetch_desc(&p.tm);
   }
@@ -650,162 +673,206 @@ __global__ void __launch_bounds__(QtCfg::THREADS, 1) s3_attn_qt_kernel(const __g
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int Lk = p.lens ? min(max(p.lens[b], 1), p.L) : p.L;
-  const int nkb = (Lk + TK - 1) / TK;
 
   if (warp == 8) {
-    // ---- issuer 1: Q, the K ring, S = Q K^T of both tiles.  It only ever waits for what the NEXT score product needs
-    // (the tile's S columns free, the K block landed); the P V side has its own warp, so a late V block does not hold
-    // back a score product and vice versa ----
+    // ---- issuer 1: Q buffers, the K ring, S = Q K^T.  Every barrier phase is a running count across items. ----
     if (elect_one()) {
       const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
-      auto load_k = [&](int j) {
-        const int s = j % NSK;
-        mbar_arrive_expect_tx(&k_full[s], TILE_B);
-        tma_load_3d(sK + s * TILE_B, &p.tm, &k_full[s], 512 + head * TD, j * TK, b);
+      QtItem U = qt_item(p, blockIdx.x), LK = U;      // U: the item whose blocks are being consumed; LK: cursor of the K loads
+      int lk_j = 0;
+      uint32_t kload = 0, kuse = 0, item = 0, sfree_n[2] = {0, 0};
+      auto k_prefetch = [&]() {                   // keep the ring full: running block kload goes to slot kload % NSK
+        while (kload < kuse + NSK && LK.valid) {
+          const int s = kload % NSK;
+          mbar_arrive_expect_tx(&k_full[s], TILE_B);
+          tma_load_3d(sK + s * TILE_B, &p.tm, &k_full[s], 512 + LK.head * TD, lk_j * TK, LK.b);
+          ++kload;
+          if (++lk_j == LK.nkb) { LK = qt_item(p, LK.w + stride); lk_j = 0; }
+        }
       };
-      auto issue_s = [&](int g, int j) {       // S_g,j = Q_g K_j^T over tile g's S columns (the caller knows they are free)
-        const int s = j % NSK;
-        mbar_wait_sleep(&k_full[s], (j / NSK) & 1);
+      auto load_q = [&](const QtItem& it, uint32_t buf) {
+        mbar_arrive_expect_tx(&bar_q[buf], it.ntile * TILE_B);
+        for (int g = 0; g < it.ntile; ++g) tma_load_3d(sQ + (buf * 2 + g) * TILE_B, &p.tm, &bar_q[buf], it.head * TD, it.q0 + g * TQ, it.b);
+      };
+      auto issue_s = [&](int g, uint32_t buf, uint32_t n) {       // S of tile g <- Q_g (buffer buf) x running K block n
+        const int s = n % NSK;
+        mbar_wait_sleep(&k_full[s], (n / NSK) & 1);
         tc_fence_after();
-        const uint64_t dq = umma_desc_k128(smem_u32(sQ + g * TILE_B)), db = umma_desc_k128(smem_u32(sK + s * TILE_B));
+        const uint64_t dq = umma_desc_k128(smem_u32(sQ + (buf * 2 + g) * TILE_B)), db = umma_desc_k128(smem_u32(sK + s * TILE_B));
 #pragma unroll
         for (int k = 0; k < TD / 16; ++k) umma_bf16(tmem_base + g * 256, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
         umma_commit(&s_full[g]);
       };
       pdl_wait();                                  // q|k|v come from the GEMM just before
-      mbar_arrive_expect_tx(bar_q, ntile * TILE_B);
-      for (int g = 0; g < ntile; ++g) tma_load_3d(sQ + g * TILE_B, &p.tm, bar_q, head * TD, q0 + g * TQ, b);
-      for (int j = 0; j < NSK && j < nkb; ++j) load_k(j);
-      mbar_wait_sleep(bar_q, 0);
-      for (int g = 0; g < ntile; ++g) issue_s(g, 0);
-      for (int j = 0; j < nkb; ++j) {
-        // a tile's S row is in registers: its S columns are free — the next block's Q K^T runs under this block's exponentials
-        for (int g = 0; g < ntile; ++g) {
-          mbar_wait_sleep(&s_free[g], j & 1);
-          if (j + 1 < nkb) issue_s(g, j + 1);
+      if (U.valid) {
+        load_q(U, 0);
+        k_prefetch();
+        mbar_wait_sleep(&bar_q[0], 0);
+        for (int g = 0; g < U.ntile; ++g) issue_s(g, 0, 0);
+      }
+      while (U.valid) {
+        const QtItem N = qt_item(p, U.w + stride);
+        const uint32_t buf = item & 1, nbuf = buf ^ 1;
+        if (N.valid) load_q(N, nbuf);              // that buffer's last reader (item - 1) has completed all its score products
+        for (int j = 0; j < U.nkb; ++j) {
+          // a tile's S row is in registers: its S columns are free — its next score product runs under this block's exponentials
+          for (int g = 0; g < U.ntile; ++g) {
+            mbar_wait_sleep(&s_free[g], sfree_n[g] & 1);
+            ++sfree_n[g];
+            if (j + 1 < U.nkb) issue_s(g, buf, kuse + 1);
+          }
+          if (j + 1 == U.nkb && N.valid) {         // last block: the next item's first score products, for the tiles it has
+            mbar_wait_sleep(&bar_q[nbuf], ((item + 1) >> 1) & 1);
+            for (int g = 0; g < N.ntile; ++g) issue_s(g, nbuf, kuse + 1);
+          }
+          ++kuse;                                  // every score product of the block has completed: its K slot is free
+          k_prefetch();
         }
-        if (j + NSK < nkb) load_k(j + NSK);        // both tiles' S_j have completed: K slot j % NSK is free
+        U = N;
+        ++item;
       }
     }
     __syncwarp();
   } else if (warp == 9) {
-    // ---- issuer 2: the V ring, O~ += P V of both tiles ----
+    // ---- issuer 2: the V ring, O~ (+)= P V ----
     if (elect_one()) {
       const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
-      auto load_v = [&](int j) {
-        const int s = j % NST;
+      QtItem U = qt_item(p, blockIdx.x), LV = U;
+      int lv_j = 0;
+      uint32_t vload = 0, n = 0, pfull_n[2] = {0, 0}, items_g[2] = {0, 0};
+      auto load_v = [&]() {                        // running block vload -> slot vload % NST
+        const int s = vload % NST;
         mbar_arrive_expect_tx(&v_full[s], TILE_B);
-        tma_load_3d(sV + s * TILE_B, &p.tm, &v_full[s], 1024 + head * TD, j * TK, b);
+        tma_load_3d(sV + s * TILE_B, &p.tm, &v_full[s], 1024 + LV.head * TD, lv_j * TK, LV.b);
+        ++vload;
+        if (++lv_j == LV.nkb) { LV = qt_item(p, LV.w + stride); lv_j = 0; }
       };
       pdl_wait();
-      for (int j = 0; j < NST && j < nkb; ++j) load_v(j);
-      for (int j = 0; j < nkb; ++j) {
-        const int s = j % NST;
-        if (j >= 1 && j - 1 + NST < nkb) {
-          mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
-          load_v(j - 1 + NST);
-        }
-        mbar_wait_sleep(&v_full[s], (j / NST) & 1);
-        const uint32_t va = smem_u32(sV + s * TILE_B);
-        for (int g = 0; g < ntile; ++g) {
-          mbar_wait_sleep(&p_full[g], j & 1);
-          tc_fence_after();
+      while (vload < NST && LV.valid) load_v();
+      while (U.valid) {
+        for (int j = 0; j < U.nkb; ++j, ++n) {
+          const int s = n % NST;
+          if (n >= 1) {      // the block before: its products were issued one iteration ago; every v_free phase is observed, in order
+            mbar_wait_sleep(&v_free[(n - 1) % NST], ((n - 1) / NST) & 1);
+            if (LV.valid) load_v();                // vload == n - 1 + NST: into the slot just freed
+          }
+          mbar_wait_sleep(&v_full[s], (n / NST) & 1);
+          const uint32_t va = smem_u32(sV + s * TILE_B);
+          for (int g = 0; g < U.ntile; ++g) {
+            if (j == 0 && items_g[g] > 0) mbar_wait_sleep(&o_free[g], (items_g[g] - 1) & 1);     // the previous item's O~ has been read
+            mbar_wait_sleep(&p_full[g], pfull_n[g] & 1);
+            ++pfull_n[g];
+            tc_fence_after();
 #pragma unroll
-          for (int k = 0; k < TK / 16; ++k)
-            umma_bf16_ts(tmem_base + g * 256 + 192, tmem_base + g * 256 + 128 + k * 8, umma_desc_k128(va + k * 2048), idesc_o, (k != 0) || (j > 0));
-          umma_commit(&o_full[g]);
+            for (int k = 0; k < TK / 16; ++k)
+              umma_bf16_ts(tmem_base + g * 256 + 192, tmem_base + g * 256 + 128 + k * 8, umma_desc_k128(va + k * 2048), idesc_o, (k != 0) || (j > 0));
+            umma_commit(&o_full[g]);
+          }
+          umma_commit(&v_free[s]);
         }
-        umma_commit(&v_free[s]);
+        for (int g = 0; g < U.ntile; ++g) ++items_g[g];
+        U = qt_item(p, U.w + stride);
       }
     }
     __syncwarp();
-  } else if ((warp >> 2) < ntile) {
+  } else {
     const int g = warp >> 2, q = warp & 3, row = q * 32 + lane;
     const uint32_t tS = tmem_base + ((uint32_t)(q * 32) << 16) + g * 256, tP = tS + 128, tO = tS + 192;
     const float sc = 0.125f * 1.4426950408889634f;              // 1/sqrt(64) * log2(e): scores in the log2 domain
-    float m = -INFINITY, l = 0.f;
-    for (int j = 0; j < nkb; ++j) {
-      mbar_wait_sleep(&s_full[g], j & 1);
-      tc_fence_after();
-      const int kbase = j * TK;
-      uint32_t s[4][32];
+    uint32_t nb = 0;                                             // running count of this tile's key blocks (barrier phases)
+    for (QtItem U = qt_item(p, blockIdx.x); U.valid; U = qt_item(p, U.w + stride)) {
+      if (g >= U.ntile) continue;
+      const int Lk = U.Lk;
+      float m = -INFINITY, l = 0.f;
+      for (int j = 0; j < U.nkb; ++j, ++nb) {
+        mbar_wait_sleep(&s_full[g], nb & 1);
+        tc_fence_after();
+        const int kbase = j * TK;
+        uint32_t s[4][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32_issue(tS + c * 32, s[c]);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&s_free[g]);
-      if (kbase + TK > Lk) {       // keys past the row's length: -inf (exp2 -> 0)
+        for (int c = 0; c < 4; ++c) tmem_ld32_issue(tS + c * 32, s[c]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_free[g]);
+        if (kbase + TK > Lk) {       // keys past the row's length: -inf (exp2 -> 0)
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int k = 0; k < 32; ++k)
+              if (kbase + c * 32 + k >= Lk) s[c][k] = 0xff800000u;
+        }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int c = 0; c < 4; ++c)
 #pragma unroll
-          for (int k = 0; k < 32; ++k)
-            if (kbase + c * 32 + k >= Lk) s[c][k] = 0xff800000u;
-      }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+          for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(s[c][k]));
+        const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sc;
+        bool waited = j == 0;        // every phase of o_full is observed, in order (see the one-pass loop above)
+        auto wait_prev = [&]() {
+          if (!waited) { mbar_wait_sleep(&o_full[g], (nb - 1) & 1); tc_fence_after(); waited = true; }
+        };
+        const bool need = mb > m + 8.0f;
+        if (__any_sync(0xffffffffu, need)) {
+          const float m_new = need ? mb : m;
+          if (j > 0) {
+            const float f = ex2f(m - m_new);
+            wait_prev();
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
+            for (int c = 0; c < 4; ++c) {
+              uint32_t r[16];
+              tmem_ld16_issue(tO + c * 16, r);
+              tmem_ld_wait();
 #pragma unroll
-        for (int k = 0; k < 32; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], __uint_as_float(s[c][k]));
-      const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sc;
-      bool waited = j == 0;        // every phase of o_full is observed, in order (see the one-pass loop above)
-      auto wait_prev = [&]() {
-        if (!waited) { mbar_wait_sleep(&o_full[g], (j - 1) & 1); tc_fence_after(); waited = true; }
-      };
-      const bool need = mb > m + 8.0f;
-      if (__any_sync(0xffffffffu, need)) {
-        const float m_new = need ? mb : m;
-        if (j > 0) {
-          const float f = ex2f(m - m_new);
-          wait_prev();
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[16];
-            tmem_ld16_issue(tO + c * 16, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int k = 0; k < 16; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * f);
-            tmem_st16(tO + c * 16, r);
+              for (int k = 0; k < 16; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * f);
+              tmem_st16(tO + c * 16, r);
+            }
+            l *= f;
           }
-          l *= f;
+          m = m_new;
         }
-        m = m_new;
-      }
-      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+        float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t pw[16];
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pw[16];
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const float p0 = ex2f(fmaf(__uint_as_float(s[c][2 * e]), sc, -m)), p1 = ex2f(fmaf(__uint_as_float(s[c][2 * e + 1]), sc, -m));
-          pw[e] = pack_bf16x2(p0, p1);
-          ls4[e & 3] += __uint_as_float(pw[e] << 16) + __uint_as_float(pw[e] & 0xffff0000u);      // sum of the ROUNDED values
+          for (int e = 0; e < 16; ++e) {
+            const float p0 = ex2f(fmaf(__uint_as_float(s[c][2 * e]), sc, -m)), p1 = ex2f(fmaf(__uint_as_float(s[c][2 * e + 1]), sc, -m));
+            pw[e] = pack_bf16x2(p0, p1);
+            ls4[e & 3] += __uint_as_float(pw[e] << 16) + __uint_as_float(pw[e] & 0xffff0000u);      // sum of the ROUNDED values
+          }
+          if (c == 0) wait_prev();
+          tmem_st16(tP + c * 16, pw);
         }
-        if (c == 0) wait_prev();
-        tmem_st16(tP + c * 16, pw);
+        l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[g]);
       }
-      l += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-      tmem_st_wait();
+      // the item's last product: read O~ out, hand the columns back, then normalise and store from registers
+      mbar_wait_sleep(&o_full[g], (nb - 1) & 1);
+      tc_fence_after();
+      float o[TD];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float v[32];
+        tmem_ld32(tO + c * 32, v);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) o[c * 32 + k] = v[k];
+      }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[g]);
-    }
-    mbar_wait_sleep(&o_full[g], (nkb - 1) & 1);
-    tc_fence_after();
-    const float inv = 1.0f / l;
-    const int t = q0 + g * TQ + row;
-    __nv_bfloat16* dst = p.out + ((size_t)b * p.L + (t < p.L ? t : 0)) * 512 + head * TD;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      float v[32];
-      tmem_ld32(tO + c * 32, v);
+      if (lane == 0) mbar_arrive(&o_free[g]);
+      const float inv = 1.0f / l;
+      const int t = U.q0 + g * TQ + row;
       if (t < p.L) {
+        __nv_bfloat16* dst = p.out + ((size_t)U.b * p.L + t) * 512 + U.head * TD;
 #pragma unroll
-        for (int d8 = 0; d8 < 4; ++d8)
-          *reinterpret_cast<uint4*>(dst + c * 32 + d8 * 8) =
-              make_uint4(pack_bf16x2(v[d8 * 8] * inv, v[d8 * 8 + 1] * inv), pack_bf16x2(v[d8 * 8 + 2] * inv, v[d8 * 8 + 3] * inv),
-                         pack_bf16x2(v[d8 * 8 + 4] * inv, v[d8 * 8 + 5] * inv), pack_bf16x2(v[d8 * 8 + 6] * inv, v[d8 * 8 + 7] * inv));
+        for (int d8 = 0; d8 < TD / 8; ++d8)
+          *reinterpret_cast<uint4*>(dst + d8 * 8) =
+              make_uint4(pack_bf16x2(o[d8 * 8] * inv, o[d8 * 8 + 1] * inv), pack_bf16x2(o[d8 * 8 + 2] * inv, o[d8 * 8 + 3] * inv),
+                         pack_bf16x2(o[d8 * 8 + 4] * inv, o[d8 * 8 + 5] * inv), pack_bf16x2(o[d8 * 8 + 6] * inv, o[d8 * 8 + 7] * inv));
       }
     }
     tc_fence_before();
@@ -847,7 +914,7 @@ int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L
   CBX_CHECK(ld_qkv == 1536, "s3_attn_tc: q|k|v row stride %d (expected 1536)", ld_qkv);
   AttnTcParams p;
   if (make_tmap_bf16_3d(&p.tm, qkv, 1536, L, B, 1536, (uint64_t)1536 * L, TD, TQ)) return CBX_ERR;
-  p.out = out; p.lens = lens; p.L = L;
+  p.out = out; p.lens = lens; p.L = L; p.nx = 0; p.n_items = 0;
   p.dbg = g_atc_dbg;
   if (g_atc_dbg) g_atc_dbg += 32;
   const dim3 grid((L + TQ - 1) / TQ, 8, B);
@@ -861,7 +928,8 @@ int s3_attn_tc_launch(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L
     static CbxPerDeviceOnce once;
     if (once.first()) CBX_CUDA(cudaFuncSetAttribute(s3_attn_qt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, QtCfg::SMEM));
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((grid.x + 1) / 2, 8, B); cfg.blockDim = dim3(QtCfg::THREADS); cfg.dynamicSmemBytes = QtCfg::SMEM; cfg.stream = st;
+    p.nx = (int)(grid.x + 1) / 2; p.n_items = B * 8 * p.nx;
+    cfg.gridDim = dim3(p.n_items < 148 ? p.n_items : 148); cfg.blockDim = dim3(QtCfg::THREADS); cfg.dynamicSmemBytes = QtCfg::SMEM; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;

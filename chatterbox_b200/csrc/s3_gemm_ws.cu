@@ -9,8 +9,8 @@
 //               one row tile after the other through a 4-stage ring;
 //   warp 1      MMA issuer: M128 N256 K16 x 16 per row tile into one of TWO TMEM accumulators (2 x 256 columns);
 //   warps 2-17  epilogue: thread <-> accumulator row, 64 columns per warp (four warps per TMEM lane quarter): tcgen05.ld,
-//               bias, GELU, bf16, 128 contiguous bytes per thread straight to global memory — while the MMA warp is already
-//               filling the other accumulator with the next row tile.
+//               bias, GELU, bf16, through a per-warp staging tile so that global stores are whole 128-byte lines — while the
+//               MMA warp is already filling the other accumulator with the next row tile.
 // K = 256 and a 256-column tile only (the two shapes above); everything else stays on s3_gemm.cu.  CBX_GEMM_WS=0 disables it.
 #include "s3_gemm.cuh"
 #include <cstdlib>
@@ -23,9 +23,11 @@ constexpr int W_KB = WN * WBK * 2;            // 32 KB: [256 rows][64 k]
 constexpr int A_KB = WM * WBK * 2;            // 16 KB
 constexpr int WSTG = 4;                       // A ring stages (one row tile)
 constexpr int WS_OFF_A = WKB * W_KB;          // 128 KB of weights, then the ring
-constexpr int WS_OFF_BAR = WS_OFF_A + WSTG * A_KB;
-constexpr int WS_SMEM = WS_OFF_BAR + 256 + WN * 4 + 1024;
 constexpr int WS_EPI_WARPS = 16;
+constexpr int WS_OFF_STG = WS_OFF_A + WSTG * A_KB;       // 2 KB per epilogue warp: [16 rows][64 bf16], 128-byte rows, swizzled
+constexpr int WS_OFF_BAR = WS_OFF_STG + WS_EPI_WARPS * 2048;
+constexpr int WS_SMEM = WS_OFF_BAR + 256 + WN * 4 + 1024;
+static_assert(WS_SMEM <= 232448, "shared memory per CTA");
 constexpr int WS_THREADS = 32 * (2 + WS_EPI_WARPS);
 
 struct WsParams {
@@ -109,15 +111,16 @@ __global__ void __launch_bounds__(WS_THREADS, 1) s3_gemm_ws_kernel(const __grid_
     __syncwarp();
   } else {
     // ---- epilogue warps: quarter = warp % 4 (the TMEM lanes a warp may touch), 64 columns per warp ----
-    const int q = warp & 3, cc = (warp - 2) >> 2, row = q * 32 + lane;
+    const int q = warp & 3, cc = (warp - 2) >> 2;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     const float* bias = sBias + cc * 64;
+    uint8_t* stg = smem + WS_OFF_STG + (warp - 2) * 2048;
     int buf = 0, aph = 0;
     for (int rt = first; rt < p.n_row_tiles; rt += p.per_col) {
-      const int b = rt / p.tiles_l, t = (rt % p.tiles_l) * WM + row;
+      const int b = rt / p.tiles_l, tq0 = (rt % p.tiles_l) * WM + q * 32;      // first row of this warp's TMEM lane quarter
       mbar_wait_spin(&acc_full[buf], aph);
       tc_fence_after();
-      __nv_bfloat16* dst = p.out + ((size_t)b * p.M_out + (t < p.M_out ? t : 0)) * p.ld_out + n0 + cc * 64;
+      uint32_t w[32];                       // this thread's row, 64 columns, packed bf16
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         float v[32];
@@ -127,17 +130,33 @@ __global__ void __launch_bounds__(WS_THREADS, 1) s3_gemm_ws_kernel(const __grid_
           __syncwarp();
           if (lane == 0) mbar_arrive(&acc_empty[buf]);
         }
-        uint32_t w[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float a = v[2 * i] + bias[h * 32 + 2 * i], c = v[2 * i + 1] + bias[h * 32 + 2 * i + 1];
           if (p.gelu) { a = gelu_f(a); c = gelu_f(c); }
-          w[i] = pack_bf16x2(a, c);
+          w[h * 16 + i] = pack_bf16x2(a, c);
         }
-        if (t < p.M_out) {
+      }
+      // A thread owns a ROW (TMEM lane): stored straight from registers, a warp instruction would touch 32 different
+      // 128-byte lines.  Through a 2 KB staging tile instead, 16 rows at a time: 8 lanes then write one row's 128 contiguous
+      // bytes, 4 full lines per instruction.
+      __nv_bfloat16* dstq = p.out + ((size_t)b * p.M_out + tq0) * p.ld_out + n0 + cc * 64;
 #pragma unroll
-          for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(dst + h * 32 + 8 * i) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+      for (int ps = 0; ps < 2; ++ps) {
+        if ((lane >> 4) == ps) {
+          const int rl = lane & 15;
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<uint4*>(stg + rl * 128 + ((c ^ (rl & 7)) << 4)) = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
         }
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int rl = it * 4 + (lane >> 3), c = lane & 7, r = ps * 16 + rl;
+          const uint4 x = *reinterpret_cast<const uint4*>(stg + rl * 128 + ((c ^ (rl & 7)) << 4));
+          if (tq0 + r < p.M_out) *reinterpret_cast<uint4*>(dstq + (size_t)r * p.ld_out + c * 8) = x;
+        }
+        __syncwarp();
       }
       if (++buf == 2) { buf = 0; aph ^= 1; }
     }
