@@ -6,8 +6,8 @@ cd "$GRAFT_REPO_ROOT"; mkdir -p gpurun_out
   timeout 300 python tools/t3_time.py 256 2>&1 | tail -1
   timeout 300 python tools/t3b_time.py 64 2>&1 | tail -1
   timeout 300 python tools/t3b_time.py 1 2>&1 | tail -1
-  timeout 300 python tools/cfm_batch_time.py 64 2>&1 | tail -1
-  timeout 300 python tools/cfm_batch_time.py 16 2>&1 | tail -1
-  timeout 300 python tools/cfm_batch_time.py 1 2>&1 | tail -1
-  CBX_ATTN_TC=0 timeout 300 python tools/cfm_batch_time.py 64 2>&1 | tail -1
+  timeout 300 python tools/cfm_batch_time.py 64 2>&1 | tail -2 | head -1
+  timeout 300 python tools/cfm_batch_time.py 16 2>&1 | tail -2 | head -1
+  timeout 300 python tools/cfm_batch_time.py 1 2>&1 | tail -2 | head -1
+  CBX_ATTN_TC=0 timeout 300 python tools/cfm_batch_time.py 64 2>&1 | tail -2 | head -1
 } | tee gpurun_out/r02_z_configs.log
