@@ -79,6 +79,8 @@ SYMBOLS = {
     "cbx_t3_batch_destroy": (C.c_int, [C.c_void_p]),
     "cbx_t3_batch_prefill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(CbxSampleParams), C.c_int,
                                        C.c_void_p, C.c_void_p]),
+    "cbx_t3_batch_prefill_many": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(CbxSampleParams), C.c_int,
+                                            C.c_void_p, C.c_void_p]),
     "cbx_t3_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_void_p]),
     "cbx_t3_batch_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                     C.c_void_p]),

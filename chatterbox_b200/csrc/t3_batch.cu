@@ -486,6 +486,7 @@ struct cbx_t3b {
   unsigned* seen;
   int *forced, *tokens, *step_mask, *pf_state;
   void* prefill_ws;
+  long long pf_rows;      // activation rows the prefill workspace holds
   std::vector<GemmDesc> gemms;       // per layer: qkv, o, gate/up, down; then head
   cudaGraphExec_t step_graph;
   cudaStream_t cap_stream;
@@ -583,7 +584,12 @@ extern "C" int cbx_t3_batch_create(const CbxT3BatchConfig* cfg, const CbxT3Weigh
   const size_t o_forced = take((size_t)U * cfg->max_new_cap * 4), o_tok = take((size_t)U * cfg->max_new_cap * 4);
   const size_t o_mask = take(U * 4), o_pfs = take(64);
   const size_t o_lout = cfg->keep_logits ? take((size_t)U * cfg->max_new_cap * 2 * VOCAB * 4) : 0;
-  const size_t o_ws = take(t3_prefill_workspace_bytes(cfg->max_pos));
+  // prompt-prefill workspace: room for several utterances' prompts in one pass (cbx_t3_batch_prefill_many), at most 16 K rows
+  {
+    const long long one = 2LL * cfg->max_pos, all = one * U;
+    h->pf_rows = all < 16384 ? all : (one > 16384 ? one : 16384);
+  }
+  const size_t o_ws = take(t3_prefill_workspace_bytes_rows((size_t)h->pf_rows));
   if (cudaMalloc(&h->slab, off) != cudaSuccess) {
     cbx_set_error("cbx_t3_batch_create: cudaMalloc of %zu bytes failed", off);
     delete h;
@@ -662,7 +668,7 @@ extern "C" int cbx_t3_batch_prefill(cbx_t3b* h, int slot, const float* embeds, i
   a.kcache = static_cast<uint8_t*>(h->kc) + (size_t)slot * h->slot_stride * kvel;
   a.vcache = static_cast<uint8_t*>(h->vc) + (size_t)slot * h->slot_stride * kvel;
   a.logits = h->logits + (size_t)(2 * slot) * VOCAB_LD; a.logits_ld = VOCAB_LD;
-  a.state = h->pf_state; a.workspace = h->prefill_ws;
+  a.state = h->pf_state; a.workspace = h->prefill_ws; a.ws_rows = h->pf_rows; a.al_layer = -1;
   if (t3_prefill_gemm(a, st)) return CBX_ERR;
   CBX_CUDA(cudaMemcpyAsync(h->sp + slot, sp, sizeof(CbxSampleParams), cudaMemcpyHostToDevice, st));
   if (forced_tokens)
@@ -671,6 +677,47 @@ extern "C" int cbx_t3_batch_prefill(cbx_t3b* h, int slot, const float* embeds, i
   k_b_slot_init<<<1, 256, 0, st>>>(h->st + slot, h->seen + (size_t)slot * SEEN_WORDS, P, max_new_tokens, forced_tokens ? 1 : 0);
   CBX_CUDA(cudaGetLastError());
   h->launches += 1 + h->cfg.n_layers * 8 + 3;
+  return CBX_OK;
+}
+
+extern "C" int cbx_t3_batch_prefill_many(cbx_t3b* h, int slot0, int n, const float* embeds, int P, const CbxSampleParams* sp,
+                                         int max_new_tokens, const int32_t* forced_tokens, void* stream) {
+  CBX_CHECK(h && embeds && sp, "cbx_t3_batch_prefill_many: null argument");
+  CBX_CHECK(n >= 1 && slot0 >= 0 && slot0 + n <= h->U, "cbx_t3_batch_prefill_many: slots [%d, %d) out of range (%d slots)", slot0, slot0 + n, h->U);
+  CBX_CHECK(max_new_tokens >= 1 && max_new_tokens <= h->cfg.max_new_cap, "cbx_t3_batch_prefill_many: max_new_tokens %d exceeds the slot's token capacity %d",
+            max_new_tokens, h->cfg.max_new_cap);
+  CBX_CHECK(P >= 1 && P + max_new_tokens <= h->cfg.max_pos, "cbx_t3_batch_prefill_many: %d prompt + %d new positions exceed the slot's KV slab (max_pos %d)",
+            P, max_new_tokens, h->cfg.max_pos);
+  CBX_CHECK(h->cfg.speech_pos_rows <= 0 || max_new_tokens + 1 <= h->cfg.speech_pos_rows,
+            "cbx_t3_batch_prefill_many: max_new_tokens exceeds the learned speech position table");
+  for (int u = 0; u < n; ++u)
+    CBX_CHECK(sp[u].temperature > 0.f && sp[u].repetition_penalty > 0.f, "cbx_t3_batch_prefill_many: temperature and repetition_penalty must be > 0 (request %d)", u);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CBX_ON_DEVICE(h->cfg.device);
+  const size_t kvel = h->cfg.kv_fp32 ? 4 : 2;
+  const int per_pass = (int)(h->pf_rows / (2LL * P));        // utterances whose prompts fit the workspace at once (>= 1: P <= max_pos)
+  for (int u0 = 0; u0 < n; u0 += per_pass) {
+    const int nb = n - u0 < per_pass ? n - u0 : per_pass, slot = slot0 + u0;
+    T3PrefillArgs a{};
+    a.embeds = embeds + (size_t)u0 * 2 * P * H; a.B = 2 * nb; a.P = P; a.n_layers = h->cfg.n_layers; a.max_pos = h->cfg.max_pos; a.kv_fp32 = h->cfg.kv_fp32;
+    a.wplain = h->w.wplain; a.ln1 = h->w.ln1; a.ln2 = h->w.ln2; a.final_norm = h->w.final_norm;
+    a.rope_cos = h->w.rope_cos; a.rope_sin = h->w.rope_sin;
+    a.kcache = static_cast<uint8_t*>(h->kc) + (size_t)slot * h->slot_stride * kvel;
+    a.vcache = static_cast<uint8_t*>(h->vc) + (size_t)slot * h->slot_stride * kvel;
+    a.logits = h->logits + (size_t)(2 * slot) * VOCAB_LD; a.logits_ld = VOCAB_LD;
+    a.state = h->pf_state; a.workspace = h->prefill_ws; a.ws_rows = h->pf_rows; a.al_layer = -1;
+    a.nseq = nb; a.kv_seq_stride = h->slot_stride;
+    if (t3_prefill_gemm(a, st)) return CBX_ERR;
+    h->launches += 1 + h->cfg.n_layers * 8 + 2;
+  }
+  CBX_CUDA(cudaMemcpyAsync(h->sp + slot0, sp, sizeof(CbxSampleParams) * n, cudaMemcpyHostToDevice, st));
+  if (forced_tokens)
+    CBX_CUDA(cudaMemcpy2DAsync(h->forced + (size_t)slot0 * h->cfg.max_new_cap, (size_t)h->cfg.max_new_cap * 4, forced_tokens,
+                               (size_t)max_new_tokens * 4, (size_t)max_new_tokens * 4, n, cudaMemcpyDeviceToDevice, st));
+  for (int u = 0; u < n; ++u)
+    k_b_slot_init<<<1, 256, 0, st>>>(h->st + slot0 + u, h->seen + (size_t)(slot0 + u) * SEEN_WORDS, P, max_new_tokens, forced_tokens ? 1 : 0);
+  CBX_CUDA(cudaGetLastError());
+  h->launches += n;
   return CBX_OK;
 }
 

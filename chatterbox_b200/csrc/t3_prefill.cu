@@ -30,7 +30,7 @@ using namespace t3rows;
 template <typename KVT>
 __global__ void __launch_bounds__(1024) k_rope_kv(float* __restrict__ qkv, int P, int pos0, const float* __restrict__ rope_cos,
                                                   const float* __restrict__ rope_sin, KVT* __restrict__ kc, KVT* __restrict__ vc,
-                                                  int layer, int max_pos) {
+                                                  int layer, int max_pos, long long seq_stride) {
   const int p = blockIdx.x, b = blockIdx.y, head = threadIdx.x >> 6, d = threadIdx.x & 63;
   float* row = qkv + ((size_t)b * P + p) * 3072 + head * 64;
   const float q = row[d], qo = row[d ^ 32], k = row[1024 + d], ko = row[1024 + (d ^ 32)], v = row[2048 + d];
@@ -40,7 +40,10 @@ __global__ void __launch_bounds__(1024) k_rope_kv(float* __restrict__ qkv, int P
   const float vr = KVS<KVT>::round(v);
   __syncthreads();            // every thread has read its partner before anyone overwrites
   row[d] = qr; row[1024 + d] = kr; row[2048 + d] = vr;
-  const size_t off = (((size_t)(layer * 2 + b) * NH + head) * max_pos + (pos0 + p)) * HD + d;
+  // batched prefill: row b belongs to utterance b >> 1 (its own slab, seq_stride elements further), CFG row b & 1
+  const int bb = seq_stride ? (b & 1) : b;
+  const size_t off = (size_t)(seq_stride ? (b >> 1) : 0) * (size_t)seq_stride +
+                     (((size_t)(layer * 2 + bb) * NH + head) * max_pos + (pos0 + p)) * HD + d;
   KVS<KVT>::store(kc + off, kr);
   KVS<KVT>::store(vc + off, vr);
 }
@@ -128,6 +131,8 @@ __global__ void __launch_bounds__(256) k_head(const float* __restrict__ x, int P
   __shared__ float xs[2][H];
   __shared__ float red[2][8];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  x += (size_t)blockIdx.y * 2 * P * H;          // batched prefill: blockIdx.y = utterance (its CFG pair of rows / logits rows)
+  logits += (size_t)blockIdx.y * 2 * ld;
   for (int b = 0; b < B; ++b) {
     const float4 v = *reinterpret_cast<const float4*>(x + ((size_t)b * P + (P - 1)) * H + tid * 4);
     float s = warp_sum(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w);
@@ -208,14 +213,18 @@ __global__ void __launch_bounds__(512) k_align_rows(const float* __restrict__ qk
 
 }  // namespace
 
-size_t t3_prefill_workspace_bytes(int max_pos) {
-  const size_t rows = 2 * (size_t)max_pos;
+size_t t3_prefill_workspace_bytes_rows(size_t rows) {
   return rows * H * 4 + rows * 3072 * 4 + 2 * rows * H * 2 + 2 * rows * INTER * 2 + 1024;
 }
+size_t t3_prefill_workspace_bytes(int max_pos) { return t3_prefill_workspace_bytes_rows(2 * (size_t)max_pos); }
 
 int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
   const int rows = a.B * a.P;
-  const size_t maxrows = 2 * (size_t)a.max_pos;
+  const size_t maxrows = a.ws_rows > 0 ? (size_t)a.ws_rows : 2 * (size_t)a.max_pos;
+  const bool many = a.nseq > 1;
+  CBX_CHECK((size_t)rows <= maxrows, "t3_prefill_gemm: %d rows exceed the workspace (%zu rows)", rows, maxrows);
+  CBX_CHECK(!many || (a.B == 2 * a.nseq && a.kv_seq_stride > 0 && a.al_layer < 0), "t3_prefill_gemm: inconsistent batched arguments");
+  const long long kvs = many ? a.kv_seq_stride : 0;
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
   float* x = reinterpret_cast<float*>(ws);
   float* qkv = reinterpret_cast<float*>(ws + maxrows * H * 4);
@@ -237,6 +246,8 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
     }
     return c;
   }();
+  // many utterances: thousands of rows fill the GPU with the widest tiles, no split-K
+  const PTiles ptl = rows > 1024 ? PTiles{0, 1, 0, 1, 0, 1} : pt;
   for (int l = 0; l < a.n_layers; ++l) {
     const __nv_bfloat16* wqkv = wp + l * per_layer;
     const __nv_bfloat16* wo = wqkv + (size_t)3072 * H;
@@ -246,27 +257,27 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
     GemmEpi e;
     k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln1 + (size_t)l * H, hl, hl_plane);
     e = GemmEpi{}; e.out_f32 = qkv; e.ld_f32 = 3072;
-    if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wqkv, rows, 3072, 3072, H, e, pt.qkv_t, pt.qkv_s) || gemm_launch(d, st)) return CBX_ERR;
+    if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wqkv, rows, 3072, 3072, H, e, ptl.qkv_t, ptl.qkv_s) || gemm_launch(d, st)) return CBX_ERR;
     if (a.kv_fp32)
       k_rope_kv<float><<<dim3(a.P, a.B), 1024, 0, st>>>(qkv, a.P, 0, a.rope_cos, a.rope_sin, static_cast<float*>(a.kcache),
-                                                        static_cast<float*>(a.vcache), l, a.max_pos);
+                                                        static_cast<float*>(a.vcache), l, a.max_pos, kvs);
     else
       k_rope_kv<__nv_bfloat16><<<dim3(a.P, a.B), 1024, 0, st>>>(qkv, a.P, 0, a.rope_cos, a.rope_sin,
                                                                static_cast<__nv_bfloat16*>(a.kcache),
-                                                               static_cast<__nv_bfloat16*>(a.vcache), l, a.max_pos);
+                                                               static_cast<__nv_bfloat16*>(a.vcache), l, a.max_pos, kvs);
     if (l == a.al_layer && a.al_out)
       k_align_rows<<<a.al_rows0, 512, 0, st>>>(qkv, a.P, a.al_rows0, a.al_i, a.al_n, a.al_out, a.al_cap);
     k_attn_prefill<<<dim3((a.P + QT - 1) / QT, NH, a.B), 256, 0, st>>>(qkv, a.P, hl, hl_plane);
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
-    if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wo, rows, H, H, H, e, pt.o_t, pt.o_s) || gemm_launch(d, st)) return CBX_ERR;
+    if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wo, rows, H, H, H, e, ptl.o_t, ptl.o_s) || gemm_launch(d, st)) return CBX_ERR;
     k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln2 + (size_t)l * H, hl, hl_plane);
     e = GemmEpi{}; e.swiglu = 1; e.out_hilo = act; e.ld_hilo = INTER; e.hilo_plane = act_plane;
     if (gemm_make_hilo(&d, hl, H, hl_plane, wgu, rows, 8192, H, e) || gemm_launch(d, st)) return CBX_ERR;
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
-    if (gemm_make_hilo_ex(&d, act, INTER, act_plane, wdn, rows, H, H, INTER, e, pt.dn_t, pt.dn_s) || gemm_launch(d, st)) return CBX_ERR;
+    if (gemm_make_hilo_ex(&d, act, INTER, act_plane, wdn, rows, H, H, INTER, e, ptl.dn_t, ptl.dn_s) || gemm_launch(d, st)) return CBX_ERR;
   }
-  k_head<<<(VOCAB + 7) / 8, 256, 0, st>>>(x, a.P, a.B, a.final_norm, wp + a.n_layers * per_layer, a.logits,
-                                           a.logits_ld > 0 ? a.logits_ld : VOCAB);
+  k_head<<<dim3((VOCAB + 7) / 8, many ? a.nseq : 1), 256, 0, st>>>(x, a.P, many ? 2 : a.B, a.final_norm, wp + a.n_layers * per_layer,
+                                                                     a.logits, a.logits_ld > 0 ? a.logits_ld : VOCAB);
   k_set_pos<<<1, 1, 0, st>>>(a.state, a.P);
   CBX_CUDA(cudaGetLastError());
   return CBX_OK;

@@ -16,6 +16,12 @@ struct T3PrefillArgs {
   int logits_ld;             // floats between the two rows (0 = 8194)
   int* state;                // {pos, n_gen, stop, err}
   void* workspace;           // t3_prefill_workspace_bytes(max_pos)
+  // several utterances of the SAME prompt length in one pass (batched engine): B = 2 nseq rows, utterance u = rows 2u, 2u + 1;
+  // its KV slab starts kv_seq_stride ELEMENTS after utterance u - 1's, its logits rows 2 logits_ld floats after.  nseq <= 1: one
+  // utterance (B = 1 or 2), the fields below unused.  ws_rows: row capacity of `workspace` (0 = 2 max_pos).
+  int nseq;
+  long long kv_seq_stride;
+  long long ws_rows;
   // alignment analyzer (al_layer < 0: off): head-mean attention of CFG row 0 over text columns [al_i, al_i + al_n) for the
   // last al_rows0 prompt positions at layer al_layer -> al_out [al_rows0][al_cap]   (alignment_stream_analyzer.py:96-101)
   int al_layer, al_i, al_n, al_rows0, al_cap;
@@ -23,6 +29,7 @@ struct T3PrefillArgs {
 };
 
 size_t t3_prefill_workspace_bytes(int max_pos);
+size_t t3_prefill_workspace_bytes_rows(size_t rows);       // for `rows` activation rows (batched prefill)
 int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st);
 
 }  // namespace cbx

@@ -117,6 +117,17 @@ class HiFTGenerator:
         self.max_frames = max_frames
         self.sampling_rate = 24000
 
+    def sibling(self) -> "HiFTGenerator":
+        """A second handle (own workspace, own launch counter) over the SAME packed weights: lets several utterances'
+        vocoder passes run on different streams at once (S3Gen.inference_batch)."""
+        o = object.__new__(HiFTGenerator)
+        o.device, o._lib, o.bf, o.f32, o._bfo, o._fo = self.device, self._lib, self.bf, self.f32, self._bfo, self._fo
+        w = _lib.CbxHiftWeights(o.bf.data_ptr(), o.f32.data_ptr(), o._bfo, o._fo)
+        h = C.c_void_p()
+        _lib.check(o._lib.cbx_hift_create(o.device.index, int(self.max_frames), C.byref(w), C.byref(h)))
+        o._h, o.max_frames, o.sampling_rate = h, self.max_frames, self.sampling_rate
+        return o
+
     def __del__(self):
         h = getattr(self, "_h", None)
         if h:

@@ -23,7 +23,8 @@ S3GEN_SR = 24000
 
 class S3Gen:
     def __init__(self, flow_sd: Dict[str, torch.Tensor], hift_sd: Dict[str, torch.Tensor], device="cuda", *,
-                 rand_noise: Optional[torch.Tensor] = None, max_mel_len: int = 4096, max_batch: int = 1):
+                 rand_noise: Optional[torch.Tensor] = None, max_mel_len: int = 4096, max_batch: int = 1,
+                 vocoder_streams: int = 4):
         if not torch.cuda.is_available():
             raise _lib.CbxError("chatterbox_b200.S3Gen needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device)
@@ -34,6 +35,11 @@ class S3Gen:
                                             max_batch=max_batch)
         self.decoder = CausalConditionalCFM(self.estimator, rand_noise=rand_noise)
         self.mel2wav = HiFTGenerator(hift_sd, self.device, max_frames=max_mel_len)
+        # inference_batch: the vocoder passes of a batch are independent and each one is a chain of small launches that
+        # cannot fill the GPU, so they run vocoder_streams at a time, each on its own stream and handle (created on first use)
+        self.vocoder_streams = max(1, int(vocoder_streams))
+        self._voc_pool: list = []
+        self._voc_streams: list = []
         self.record_events = False
         self.events: Dict[str, torch.cuda.Event] = {}
 
@@ -140,11 +146,34 @@ class S3Gen:
         ev = {k: torch.cuda.Event(enable_timing=True) for k in ("hift0", "hift1")} if self.record_events else None
         if ev:
             ev["hift0"].record()
-        outs = [self.hift_inference(m, None, seed=seed, apply_fade=True) for m in mels]
+        K = min(self.vocoder_streams, len(mels))
+        if K <= 1:
+            outs = [self.hift_inference(m, None, seed=seed, apply_fade=True) for m in mels]
+        else:
+            if seed is None:       # one draw on the host, as the sequential path would make per utterance
+                seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            while len(self._voc_pool) < K:
+                self._voc_pool.append(self.mel2wav if not self._voc_pool else self.mel2wav.sibling())
+                self._voc_streams.append(torch.cuda.Stream(self.device))
+            main = torch.cuda.current_stream(self.device)
+            ready = torch.cuda.Event()
+            ready.record(main)                                   # the mels come from the solve on the caller's stream
+            outs = [None] * len(mels)
+            for i, m in enumerate(mels):
+                st = self._voc_streams[i % K]
+                if i < K:
+                    st.wait_event(ready)
+                with torch.cuda.stream(st):
+                    outs[i] = self._voc_pool[i % K].inference(m, None, seed=seed, apply_fade=True)
+                for t in outs[i]:
+                    t.record_stream(main)                        # allocated on the side stream, consumed on the caller's
+            for st in self._voc_streams[:K]:
+                main.wait_stream(st)
         if ev:
             ev["hift1"].record()
             self.events.update(ev)
         return outs
 
     def launches(self) -> int:
-        return self.front.launches() + self.estimator.launches() + self.mel2wav.launches()
+        return (self.front.launches() + self.estimator.launches() + self.mel2wav.launches()
+                + sum(v.launches() for v in self._voc_pool[1:]))

@@ -96,6 +96,44 @@ class T3Batch:
         self.prefill_len[slot] = P
         return P
 
+    @torch.inference_mode()
+    def admit_many(self, slot0: int, reqs: List[T3Request]) -> List[int]:
+        """Prompt prefill of `reqs` into the consecutive slots slot0, slot0 + 1, ...: runs of requests with the same prefill
+        length, token budget and forcing mode go through the layers TOGETHER (cbx_t3_batch_prefill_many: 2 n P rows per GEMM);
+        anything else falls back to `admit`.  Returns the prefill lengths."""
+        t3 = self.t3
+        prepped = []
+        for req in reqs:
+            tt = torch.atleast_2d(req.text_tokens).to(dtype=torch.long, device=self.device)
+            _ensure_BOT_EOT(tt, t3.hp)
+            if tt.shape[0] == 1:
+                tt = torch.cat([tt, tt], 0)
+            embeds, _ = t3._prefill_embeds(req.t3_cond, tt, req.cfg_weight, 2 if req.cfg_weight > 0 else 1)
+            prepped.append(embeds)
+        out, i = [], 0
+        while i < len(reqs):
+            P, n = prepped[i].shape[1], int(reqs[i].max_new_tokens)
+            j = i + 1
+            while (j < len(reqs) and prepped[j].shape[1] == P and int(reqs[j].max_new_tokens) == n
+                   and (reqs[j].forced_tokens is None) == (reqs[i].forced_tokens is None)):
+                j += 1
+            run = reqs[i:j]
+            emb = torch.cat([e.reshape(1, 2, P, -1) for e in prepped[i:j]], 0).contiguous().float()
+            forced = None
+            if run[0].forced_tokens is not None:
+                forced = torch.stack([r.forced_tokens.reshape(-1)[:n].to(device=self.device, dtype=torch.int32) for r in run]).contiguous()
+            sps = (_lib.CbxSampleParams * len(run))(*[
+                _lib.CbxSampleParams(float(r.cfg_weight), float(r.temperature), float(r.repetition_penalty), float(r.min_p),
+                                     float(r.top_p), 0 if r.do_sample else 1, 1 if r.stop_on_eos else 0, int(r.seed) & (2 ** 64 - 1))
+                for r in run])
+            _lib.check(self._lib.cbx_t3_batch_prefill_many(self._h, slot0 + i, len(run), emb.data_ptr(), P, sps, n,
+                                                           forced.data_ptr() if forced is not None else None, self._stream()))
+            for k in range(i, j):
+                self.prefill_len[slot0 + k] = P
+                out.append(P)
+            i = j
+        return out
+
     def step(self, n_steps: int = 1, slots: Optional[List[int]] = None) -> None:
         arr, n = None, 0
         if slots is not None:

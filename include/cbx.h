@@ -177,6 +177,12 @@ int cbx_t3_batch_destroy(cbx_t3b* h);
  * (teacher forcing).  The slot then takes part in every following cbx_t3_decode_batch until EOS / max_new_tokens. */
 int cbx_t3_batch_prefill(cbx_t3b* h, int slot, const float* embeds, int P, const CbxSampleParams* sp, int max_new_tokens,
                          const int32_t* forced_tokens, void* stream);
+/* The same for n requests with prompts of EQUAL length P into the consecutive slots [slot0, slot0 + n): embeds
+ * [n][2][P][1024], sp = HOST array [n], forced_tokens = nullable DEVICE array [n][max_new_tokens].  The n prompts go through
+ * the layers together (2 n P rows per GEMM instead of 2 P: the reference prefills one request per generate() call,
+ * t3.py:307-316, server.py:223-232); results per slot are those of cbx_t3_batch_prefill up to the GEMMs' summation order. */
+int cbx_t3_batch_prefill_many(cbx_t3b* h, int slot0, int n, const float* embeds, int P, const CbxSampleParams* sp,
+                              int max_new_tokens, const int32_t* forced_tokens, void* stream);
 /* n_steps decode steps (t3.py:319-367, one token per running slot and step), each ONE CUDA-graph launch.  slots:
  * HOST array of the slots to advance, NULL = every running slot.  Finished / free slots ride along as inert rows. */
 int cbx_t3_decode_batch(cbx_t3b* h, const int32_t* slots, int n_slots, int n_steps, void* stream);

@@ -158,3 +158,37 @@ def test_s3gen_chain_at_the_bench_shape():
           f"chained waveform {r_all:.3e}")
     assert r_mel < 2e-2 and r_voc < 2e-2
     assert r_all < 1e-1      # the vocoder amplifies the (in-tolerance) mel difference; stated, not hidden
+
+
+@pytest.mark.gpu
+def test_s3gen_inference_batch_streams_and_ragged_lengths():
+    """`S3Gen.inference_batch` (BASELINE config 4: one padded flow-matching solve for several utterances, then the vocoder per
+    utterance on a pool of streams / handles).  (a) the vocoder pool must not change a bit against the one-stream path, nor
+    against the vocoder called alone on the same mel — same kernels, same inputs, other streams / sibling handles; (b) the mel
+    of every utterance of a ragged batch (40 / 64 / 17 / 64 / 33 tokens, two voices) must match its own single-utterance
+    `flow_inference` to the tolerance the padded solve has in tests/test_cfm_gpu.py.  (Waveforms of (b) are not compared: the
+    sine source integrates f0, so an in-tolerance mel difference drifts its phase — the chained test above injects the source
+    for that reason.)"""
+    from chatterbox_b200.s3gen import S3Gen
+    sd, sdh = S.make_state_dict("flow"), S.make_state_dict("hift")
+    ns = [40, 64, 17, 64, 33]
+    toks = [S.speech_tokens(n, seed=20 + i)[0] for i, n in enumerate(ns)]
+    refs = [S.s3gen_ref(seed=4 + (i & 1), prompt_len=30) for i in range(len(ns))]
+    outs = {}
+    for k in (1, 3):
+        s3 = S3Gen(sd, sdh, "cuda", rand_noise=S.cfm_noise(), max_mel_len=512, max_batch=len(ns), vocoder_streams=k)
+        for _ in range(2):       # second call: every graph / plan cache hot, pool reused
+            outs[k] = [(w.cpu(), s.cpu()) for w, s in s3.inference_batch(toks, refs, seed=7)]
+    assert len(s3._voc_pool) == 3 and s3.launches() > 0
+    for (w1, s1), (w3, s3_), n in zip(outs[1], outs[3], ns):
+        assert w1.shape == (1, 480 * 2 * n) and torch.isfinite(w1).all()
+        assert torch.equal(w1, w3) and torch.equal(s1, s3_)
+    mels = s3.flow_inference_batch(toks, refs)
+    for u, (m, t, r, n) in enumerate(zip(mels, toks, refs, ns)):
+        assert m.shape == (1, 80, 2 * n)
+        w_alone, _ = s3.hift_inference(m, None, seed=7, apply_fade=True)
+        assert torch.equal(w_alone.cpu(), outs[3][u][0])
+        alone = s3.flow_inference(t[None], ref_dict=r)
+        rel = float((m - alone).norm() / alone.norm())
+        print(f"flow_inference_batch vs flow_inference, {n} tokens: mel rel-L2 {rel:.3e}")
+        assert rel < 5e-3

@@ -1,6 +1,7 @@
-"""(The tcgen05 kernel has two instantiations — two softmax groups per CTA for one utterance, one group and two CTAs per SM for
-padded batches, chosen by the CTA count: B = 2 cases run the first, the B >= 4 x 8 heads x q-tiles > 296 case the second; the
-switch test in test_cfm_switches_gpu.py style is not needed here: both are reached by shape.)
+"""(The tcgen05 attention has two forms chosen by the CTA count: two softmax groups per CTA for one utterance (B = 2 cases), and
+for padded batches — B x 8 heads x q-tiles > 296 — the persistent two-query-tile kernel, whose CTAs each walk several work items
+with different key counts in the ragged cases; the one-tile-per-CTA form behind CBX_ATTN_QT=0 is covered by
+tests/test_cfm_switches_gpu.py.)
 
 The estimator's attention kernels alone (csrc/s3_attn_tc.cu: tcgen05; csrc/s3_attn.cu: mma.sync) against a plain PyTorch
 fp32 attention on the same bf16 q|k|v (reference: matcha/transformer.py:196-204 -> diffusers AttnProcessor2_0; 8 heads x 64,
@@ -41,7 +42,9 @@ def _ref(qkv, lens):
 @pytest.mark.parametrize("tc", [1, 0])
 @pytest.mark.parametrize("B,L,lens", [(2, 44, None), (2, 128, None), (2, 129, None), (2, 812, None), (2, 1800, None),
                                       (4, 300, [300, 300, 17, 17]), (6, 520, [520, 520, 257, 257, 128, 128]),
-                                      (16, 300, [300, 300, 17, 17, 200, 200, 129, 129, 128, 128, 64, 64, 300, 300, 1, 1])])
+                                      (16, 300, [300, 300, 17, 17, 200, 200, 129, 129, 128, 128, 64, 64, 300, 300, 1, 1]),
+                                      (40, 257, None),          # 640 work items on 148 persistent CTAs, odd tile count
+                                      (24, 520, [520, 520, 1, 1, 130, 130, 257, 257, 400, 400, 128, 128] * 2)])
 def test_attention_matches_fp32_torch(tc, B, L, lens):
     g = torch.Generator().manual_seed(L * 7 + B)
     qkv = (torch.randn(B, L, 1536, generator=g) * 1.5).to(torch.bfloat16).cuda()

@@ -130,6 +130,32 @@ def test_an_utterance_gives_the_same_tokens_alone_and_in_a_batch(t3_30):
     assert d1 < 2e-3 and same >= n // 2
 
 
+def test_prompts_prefilled_together_match_prompts_prefilled_one_by_one(t3_30):
+    """`admit_many` (cbx_t3_batch_prefill_many): six requests — four with the same prompt length (one pass of 2 x 4 x P rows
+    through the layers, widest GEMM tiles, no split-K), two with other lengths (runs of one) — against the same requests
+    admitted one by one into another engine.  The prompts' rows never mix; the GEMMs' tile / split-K choice differs with the
+    row count, so step-0 logits agree to fp32 summation order and the greedy tokens are equal."""
+    from chatterbox_b200.t3_batch import T3Batch
+    n = 32
+    def mk(k):
+        nt, pl = (21, 60) if k in (1, 2, 3, 4) else (9 + 7 * k, 30 + 10 * k)
+        return _req(torch.cat([S.text_tokens(nt, seed=50 + k)] * 2, 0), _cond(30 + k, pl), n, do_sample=False, stop_on_eos=False)
+    one = T3Batch(t3_30, 6, max_pos=384, max_new_cap=n, keep_logits=True)
+    for k in range(6):
+        one.admit(k, mk(k))
+    one.step(n)
+    many = T3Batch(t3_30, 6, max_pos=384, max_new_cap=n, keep_logits=True)
+    Ps = many.admit_many(0, [mk(k) for k in range(6)])
+    assert Ps[1] == Ps[2] == Ps[3] == Ps[4] and Ps == [one.prefill_len[k] for k in range(6)]
+    many.step(n)
+    assert many.poll()[0] == [n] * 6
+    for k in range(6):
+        ta, tb = one.tokens(k, n).cpu(), many.tokens(k, n).cpu()
+        d = (one.logits(k, n)[0] - many.logits(k, n)[0]).abs().max().item()
+        print(f"slot {k} (P = {Ps[k]}): step-0 logits max-abs {d:.3e}, {int((ta == tb).sum())}/{n} greedy tokens equal")
+        assert d < 2e-3 and int((ta == tb).sum()) >= n - 2
+
+
 def test_eos_retires_a_slot_and_the_scheduler_refills_it():
     """Continuous batching: 7 requests of different lengths through a 3-slot engine; EOS (forced at different steps)
     retires slots early, freed slots are refilled from the queue, every request's tokens equal its forced prefix up to
