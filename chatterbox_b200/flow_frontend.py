@@ -82,6 +82,16 @@ class FlowFrontend:
         self._h = h
         self.max_tokens = max_tokens
 
+    def sibling(self) -> "FlowFrontend":
+        """A second handle (own workspace) over the SAME packed weights, for a second stream (S3Gen.flow_inference_batch)."""
+        o = object.__new__(FlowFrontend)
+        o.device, o._lib, o.bf, o.f32, o._bfo, o._fo, o.max_tokens = self.device, self._lib, self.bf, self.f32, self._bfo, self._fo, self.max_tokens
+        w = _lib.CbxFlowFrontWeights(o.bf.data_ptr(), o.f32.data_ptr(), o._bfo, o._fo)
+        h = C.c_void_p()
+        _lib.check(o._lib.cbx_flowfe_create(o.device.index, int(o.max_tokens), C.byref(w), C.byref(h)))
+        o._h = h
+        return o
+
     def __del__(self):
         h = getattr(self, "_h", None)
         if h:

@@ -40,6 +40,7 @@ class S3Gen:
         self.vocoder_streams = max(1, int(vocoder_streams))
         self._voc_pool: list = []
         self._voc_streams: list = []
+        self._front_pool: list = []        # the same for the token front-ends of a batch (flow_inference_batch)
         self.record_events = False
         self.events: Dict[str, torch.cuda.Event] = {}
 
@@ -119,14 +120,32 @@ class S3Gen:
         if ev:
             ev["front0"].record()
         mus, spk, conds, l1s = [], [], [], []
-        for tok, rd in zip(speech_tokens_list, ref_dicts):
+        K = min(self.vocoder_streams, len(speech_tokens_list))
+        while len(self._front_pool) < K:
+            self._front_pool.append(self.front if not self._front_pool else self.front.sibling())
+        while len(self._voc_streams) < K:
+            self._voc_streams.append(torch.cuda.Stream(self.device))
+        main = torch.cuda.current_stream(self.device)
+        for i, (tok, rd) in enumerate(zip(speech_tokens_list, ref_dicts)):
             ref = self._ref(rd)
             tok = tok.to(self.device)
             if tok.dim() == 1:
                 tok = tok.unsqueeze(0)
-            mu, spks, cond, l1 = self._front(tok.long(), ref["prompt_token"].long(), ref["prompt_feat"].float(),
-                                             ref["embedding"].float())
+            if K <= 1:
+                mu, spks, cond, l1 = self._front(tok.long(), ref["prompt_token"].long(), ref["prompt_feat"].float(),
+                                                 ref["embedding"].float())
+            else:              # ~100 small launches per utterance: K utterances at a time, each on its own stream / handle
+                st = self._voc_streams[i % K]
+                st.wait_stream(main)          # this utterance's tokens / reference tensors may just have been copied there
+                with torch.cuda.stream(st):
+                    mu, spks, cond, l1 = self._front_pool[i % K].flow_inputs(tok.long(), ref["prompt_token"].long(),
+                                                                             ref["prompt_feat"].float(), ref["embedding"].float())
+                for t in (mu, spks, cond):
+                    t.record_stream(main)
             mus.append(mu); spk.append(spks); conds.append(cond); l1s.append(l1)
+        if K > 1:
+            for st in self._voc_streams[:K]:
+                main.wait_stream(st)
         if ev:
             ev["cfm0"].record()
         lens = [int(m.shape[2]) for m in mus]
@@ -154,6 +173,7 @@ class S3Gen:
                 seed = int(torch.randint(0, 2 ** 62, (1,)).item())
             while len(self._voc_pool) < K:
                 self._voc_pool.append(self.mel2wav if not self._voc_pool else self.mel2wav.sibling())
+            while len(self._voc_streams) < K:
                 self._voc_streams.append(torch.cuda.Stream(self.device))
             main = torch.cuda.current_stream(self.device)
             ready = torch.cuda.Event()
@@ -176,4 +196,4 @@ class S3Gen:
 
     def launches(self) -> int:
         return (self.front.launches() + self.estimator.launches() + self.mel2wav.launches()
-                + sum(v.launches() for v in self._voc_pool[1:]))
+                + sum(v.launches() for v in self._voc_pool[1:]) + sum(v.launches() for v in self._front_pool[1:]))

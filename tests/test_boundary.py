@@ -179,7 +179,7 @@ def test_s3gen_inference_batch_streams_and_ragged_lengths():
         s3 = S3Gen(sd, sdh, "cuda", rand_noise=S.cfm_noise(), max_mel_len=512, max_batch=len(ns), vocoder_streams=k)
         for _ in range(2):       # second call: every graph / plan cache hot, pool reused
             outs[k] = [(w.cpu(), s.cpu()) for w, s in s3.inference_batch(toks, refs, seed=7)]
-    assert len(s3._voc_pool) == 3 and s3.launches() > 0
+    assert len(s3._voc_pool) == 3 and len(s3._front_pool) == 3 and s3.launches() > 0
     for (w1, s1), (w3, s3_), n in zip(outs[1], outs[3], ns):
         assert w1.shape == (1, 480 * 2 * n) and torch.isfinite(w1).all()
         assert torch.equal(w1, w3) and torch.equal(s1, s3_)
