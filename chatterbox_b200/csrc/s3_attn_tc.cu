@@ -175,119 +175,85 @@ __global__ void __launch_bounds__(AtcCfg<NG>::THREADS, NG == 1 ? 2 : 1) s3_attn_
   const int nkb = (Lk + TK - 1) / TK;
 
   if (warp == 4 * NG) {
-    // ---- the issuer: every TMA load and every tcgen05.mma of the CTA, in the order their preconditions become true.
-    // The WHOLE warp walks the loop (convergent control flow); lane 0 alone waits on barriers and executes the TMA / MMA /
-    // commit instructions.  Addresses and descriptors are computed outside those one-lane regions, from warp-uniform
-    // values, so they live in uniform registers: computed by the issuing lane inside a divergent branch they sat in vector
-    // registers and every tcgen05.mma paid three R2UR round trips (~90 cycles per MMA issued, measured with clock64
-    // stamps: the issuer, not the softmax warps, set the pace of a key block). ----
-    const bool lead = elect_one();
-    // values the compiler cannot prove warp-uniform (one came through shared memory, the other through a global load) are
-    // passed through a warp reduction, whose result lands in a uniform register
-    const uint32_t tbase = __reduce_max_sync(0xffffffffu, tmem_base), tmo = __reduce_max_sync(0xffffffffu, tmem_o);
-    const int nkb_u = (int)__reduce_max_sync(0xffffffffu, (unsigned)nkb);
-    const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
-    const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
-    const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV);
-    auto wait = [&](uint64_t* bar, uint32_t parity) {
-      if (lead) mbar_wait_sleep(bar, parity);
-      __syncwarp();
-    };
-    auto load_k = [&](int j) {
-      const int s = j % NSK;
-      if (lead) {
+    // ---- the issuer: every TMA load and every tcgen05.mma of the CTA, in the order their preconditions become true ----
+    if (elect_one()) {     // elect.sync, not lane == 0: the compiler then passes descriptors in uniform registers (tc.cuh)
+      const uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
+      const uint32_t idesc_o = umma_idesc_bf16(TQ, TD) | (1u << 16);        // B (= V) is MN-major
+      auto load_k = [&](int j) {
+        const int s = j % NSK;
         mbar_arrive_expect_tx(&k_full[s], TILE_B);
         tma_load_3d(sK + s * TILE_B, &p.tm, &k_full[s], 512 + head * TD, j * TK, b);
-      }
-    };
-    auto load_v = [&](int j) {
-      const int s = j % NST;
-      if (lead) {
+      };
+      auto load_v = [&](int j) {
+        const int s = j % NST;
         mbar_arrive_expect_tx(&v_full[s], TILE_B);
         tma_load_3d(sV + s * TILE_B, &p.tm, &v_full[s], 1024 + head * TD, j * TK, b);
-      }
-    };
-    auto issue_s = [&](int j) {            // S_j = Q K_j^T into S buffer j % NSB (the caller knows the buffer is free)
-      const int s = j % NSK, sb = j % NSB;
-      wait(&k_full[s], (j / NSK) & 1);
-      const uint64_t dq = umma_desc_k128(q_addr), db = umma_desc_k128(k_addr + s * TILE_B);
-      const uint32_t d = tbase + sb * TK;
-      if (lead) {
+      };
+      const uint64_t dq = umma_desc_k128(smem_u32(sQ));
+      auto issue_s = [&](int j) {            // S_j = Q K_j^T into S buffer j % NSB (the caller knows the buffer is free)
+        const int s = j % NSK, sb = j % NSB;
+        mbar_wait_sleep(&k_full[s], (j / NSK) & 1);
         tc_fence_after();
+        const uint64_t db = umma_desc_k128(smem_u32(sK + s * TILE_B));
 #pragma unroll
-        for (int k = 0; k < TD / 16; ++k) umma_bf16(d, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
+        for (int k = 0; k < TD / 16; ++k) umma_bf16(tmem_base + sb * TK, dq + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc_s, k != 0);
         umma_commit(&s_full[sb]);
-      }
-    };
-    if (lead) {
+      };
       pdl_wait();                                  // q|k|v come from the GEMM just before
       ATC_STAMP(1);
       mbar_arrive_expect_tx(bar_q, TILE_B);
       tma_load_3d(sQ, &p.tm, bar_q, head * TD, q0, b);
-    }
-    __syncwarp();
-    for (int j = 0; j < NSK && j < nkb_u; ++j) { load_k(j); if (j < NST) load_v(j); }
-    wait(bar_q, 0);
-    for (int j = 0; j < NSB && j < nkb_u; ++j) issue_s(j);
-    if constexpr (SPLIT_P) {
-      for (int j = 0; j < nkb_u; ++j) {
-        const int s = j % NST;
-        wait(s_free, j & 1);                         // S_j is in registers: the S tile and K slot j % NSK are free
-        if (lead && j == 2) ATC_STAMP(20);
-        if (lead && j == 3) ATC_STAMP(25);
-        if (j + NSK < nkb_u) load_k(j + NSK);
-        if (j + 1 < nkb_u) issue_s(j + 1);             // runs while the softmax warps exponentiate block j
-        if (lead && j == 2) ATC_STAMP(21);
-        wait(&p_full[0], j & 1);
-        if (lead && j == 2) ATC_STAMP(22);
-        if (j >= 1 && j - 1 + NST < nkb_u) {
-          wait(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
-          load_v(j - 1 + NST);
-        }
-        wait(&v_full[s], (j / NST) & 1);
-        if (lead && j == 2) ATC_STAMP(23);
-        const uint32_t va = v_addr + s * TILE_B, ta = tbase + TK;
-        const uint32_t acc0 = j > 0;
-        if (lead) {
+      for (int j = 0; j < NSK && j < nkb; ++j) { load_k(j); if (j < NST) load_v(j); }
+      mbar_wait_sleep(bar_q, 0);
+      for (int j = 0; j < NSB && j < nkb; ++j) issue_s(j);
+      if constexpr (SPLIT_P) {
+        for (int j = 0; j < nkb; ++j) {
+          const int s = j % NST;
+          mbar_wait_sleep(s_free, j & 1);            // S_j is in registers: the S tile and K slot j % NSK are free
+          if (j + NSK < nkb) load_k(j + NSK);
+          if (j + 1 < nkb) issue_s(j + 1);           // runs while the softmax warps exponentiate block j
+          mbar_wait_sleep(&p_full[0], j & 1);
+          if (j >= 1 && j - 1 + NST < nkb) {
+            mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+            load_v(j - 1 + NST);
+          }
+          mbar_wait_sleep(&v_full[s], (j / NST) & 1);
           tc_fence_after();
+          const uint32_t va = smem_u32(sV + s * TILE_B);
 #pragma unroll
-          for (int k = 0; k < TK / 16; ++k) umma_bf16_ts(tmo, ta + k * 8, umma_desc_k128(va + k * 2048), idesc_o, k != 0 ? 1u : acc0);
+          for (int k = 0; k < TK / 16; ++k)
+            umma_bf16_ts(tmem_o, tmem_base + TK + k * 8, umma_desc_k128(va + k * 2048), idesc_o, (k != 0) || (j > 0));
           umma_commit(&o_full[0]);
           umma_commit(&v_free[s]);
         }
-        if (lead && j == 2) ATC_STAMP(24);
-      }
-    } else {
-      for (int j = 0; j < nkb_u; ++j) {
+      } else
+      for (int j = 0; j < nkb; ++j) {
         const int g = j % NG, it = j / NG, s = j % NST;
-        // P_j is written, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
-        wait(&p_full[g], it & 1);
-        if (j + NSK < nkb_u) load_k(j + NSK);
-        if (j >= 1 && j - 1 + NST < nkb_u) {       // V slot of block j - 1: its product was issued one iteration ago
-          wait(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
+        // P_j is in shared memory, and its group is done with S buffer j % NSB (so S_j has long completed: K slot free)
+        mbar_wait_sleep(&p_full[g], it & 1);
+        if (j + NSK < nkb) load_k(j + NSK);
+        if (j >= 1 && j - 1 + NST < nkb) {       // V slot of block j - 1: its product was issued one iteration ago
+          mbar_wait_sleep(&v_free[(j - 1) % NST], ((j - 1) / NST) & 1);
           load_v(j - 1 + NST);
         }
-        wait(&v_full[s], (j / NST) & 1);
+        mbar_wait_sleep(&v_full[s], (j / NST) & 1);
+        tc_fence_after();
         [[maybe_unused]] const uint32_t pa = smem_u32(sP + g * P_B);
-        const uint32_t va = v_addr + s * TILE_B, ta = tbase + (j % NSB) * TK, td = tmo + g * TD;
-        const uint32_t acc0 = (ONEPASS && it > 0) ? 1u : 0u;
-        if (lead) {
-          tc_fence_after();
+        const uint32_t va = smem_u32(sV + s * TILE_B);
 #pragma unroll
-          for (int k = 0; k < TK / 16; ++k) {
-            // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
-            const uint64_t db = umma_desc_k128(va + k * 2048);
+        for (int k = 0; k < TK / 16; ++k) {
+          // A: k-block k / 4 of P, 32 bytes per K = 16 step inside the swizzle row; B: 16 key rows = 2048 bytes per step
+          const uint64_t db = umma_desc_k128(va + k * 2048);
 #if ATC_P_TMEM
-            umma_bf16_ts(td, ta + k * 8, db, idesc_o, k != 0 ? 1u : acc0);
+          umma_bf16_ts(tmem_o + g * TD, tmem_base + (j % NSB) * TK + k * 8, db, idesc_o, (k != 0) || (ONEPASS && it > 0));
 #else
-            const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
-            umma_bf16(td, da, db, idesc_o, k != 0);
+          const uint64_t da = umma_desc_k128(pa + (k >> 2) * TILE_B) + (uint64_t)((k & 3) * 2);
+          umma_bf16(tmem_o + g * TD, da, db, idesc_o, k != 0);
 #endif
-          }
-          umma_commit(&o_full[g]);
-          umma_commit(&v_free[s]);
         }
-        if (j + NSB < nkb_u) issue_s(j + NSB);       // into the S buffer block j's group just finished with
+        umma_commit(&o_full[g]);
+        umma_commit(&v_free[s]);
+        if (j + NSB < nkb) issue_s(j + NSB);       // into the S buffer block j's group just finished with
       }
     }
     __syncwarp();
