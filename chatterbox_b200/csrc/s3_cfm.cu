@@ -485,6 +485,18 @@ extern "C" int cbx_dbg_gemm_stamps(unsigned long long* buf) { cbx::gemm_set_debu
 namespace cbx { int s3_attn_tc_launch(const __nv_bfloat16*, __nv_bfloat16*, int, int, int, const int*, cudaStream_t); }
 /* Debug aid (not in cbx.h): the estimator's attention kernel alone — qkv bf16 [B][L][1536] -> out bf16 [B][L][512];
    tc != 0: the tcgen05 kernel, 0: the mma.sync kernel (tests/test_s3_attn_gpu.py). */
+// test hook: y[i] = gelu_f(x[i]), the GELU every estimator epilogue uses (tests/test_cfm_gpu.py pins its error against erf)
+__global__ void k_dbg_gelu(const float* __restrict__ x, float* __restrict__ y, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = cbx::gelu_f(x[i]);
+}
+extern "C" int cbx_dbg_gelu(const float* x, float* y, int n, void* stream) {
+  CBX_CHECK(x && y && n >= 1, "cbx_dbg_gelu: bad argument");
+  k_dbg_gelu<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, n);
+  CBX_CUDA(cudaGetLastError());
+  return CBX_OK;
+}
+
 extern "C" int cbx_dbg_s3_attn(const void* qkv, void* out, int B, int L, const int* lens, int tc, void* stream) {
   CBX_CHECK(qkv && out && B >= 1 && L >= 1, "cbx_dbg_s3_attn: bad argument");
   auto q = static_cast<const __nv_bfloat16*>(qkv); auto o = static_cast<__nv_bfloat16*>(out);

@@ -48,7 +48,8 @@ struct GemmDesc {
 // value this feeds.  One MUFU and 9 FMA-pipe instructions instead of two and 16: the up-projection epilogue of the padded-batch
 // solve is issue-bound on this function (profiles/r02_z_gemm_batch_ncu.md).  Fit: numpy lstsq on 4000 Chebyshev nodes.
 __device__ __forceinline__ float gelu_f(float x) {
-  const float a = fminf(fabsf(x), 6.0f);
+  float a;                                   // min(|x|, 6) that keeps a NaN (fminf would turn it into 6 and hide it)
+  asm("min.NaN.f32 %0, %1, %2;" : "=f"(a) : "f"(fabsf(x)), "f"(6.0f));
   float p = fmaf(3.33725729433354e-05f, a, -0.0007683017174713314f);
   p = fmaf(p, a, 0.008067665621638298f);
   p = fmaf(p, a, -0.053377795964479446f);

@@ -181,3 +181,25 @@ def test_batched_ragged_solve_matches_each_utterance_alone_and_the_oracle():
     same = cfm.forward_batch(torch.cat([inps[0]["mu"]] * 3, 0), None, 10, spks=torch.cat([inps[0]["spks"]] * 3, 0),
                              cond=torch.cat([inps[0]["cond"]] * 3, 0)).cpu()
     assert _rel(same[2:3], same[0:1]) < 1e-6
+
+
+def test_gelu_of_the_epilogues_against_erf():
+    """`gelu_f` (csrc/s3_gemm.cuh: relu(x) - |x| 2^P(|x|), P a degree-6 fit of log2(erfc(|x| / sqrt 2) / 2)) is the "exact" GELU of
+    the reference's feed-forward (diffusers `GELU`, approximate="none" -> erf).  Dense grid over [-12, 12] plus the edges:
+    absolute error <= 5e-7 (measured 2.5e-7; the bf16 rounding of the value it feeds is ~1e-3 relative), +inf -> +inf and
+    -inf -> -6e-9 (no NaN from the clamp), NaN propagates."""
+    import ctypes as C
+    from chatterbox_b200 import _lib
+    lib = C.CDLL(_lib.LIB_PATH)
+    x = torch.cat([torch.linspace(-12, 12, 2_000_001), torch.tensor([0.0, -0.0, 6.0, -6.0, 1e-30, -1e-30, 50.0, -50.0,
+                                                                     float("inf"), float("-inf"), float("nan")])]).cuda()
+    y = torch.empty_like(x)
+    assert lib.cbx_dbg_gelu(C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()), x.numel(), None) == 0
+    torch.cuda.synchronize()
+    fin = torch.isfinite(x)
+    want = (0.5 * x[fin].double() * (1.0 + torch.erf(x[fin].double() / 2 ** 0.5)))
+    err = (y[fin].double() - want).abs()
+    print(f"gelu_f: max abs error {float(err.max()):.3e} at x = {float(x[fin][err.argmax()]):.4f}")
+    assert float(err.max()) <= 5e-7
+    tail = y[-3:].cpu()
+    assert tail[0] == float("inf") and abs(float(tail[1])) < 1e-8 and torch.isnan(tail[2])      # -inf: -6 h(6) = -5.9e-9, not NaN
