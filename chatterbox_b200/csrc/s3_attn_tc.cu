@@ -10,10 +10,13 @@
 //                                        blocks ahead, as soon as the buffer's previous reader is done
 //                       O~_j = P_j V_j   M128 N64 K16 x 8; A = P from shared memory, B = the V block as it lies in
 //                                        memory ([keys][d], d contiguous) = an MN-major operand: no transpose -> TMEM O[g]
-//   warps 0-3 / 4-7   two softmax groups taking alternate key blocks (g = block & 1), thread <-> query row (TMEM lane):
-//                     two passes over the S tile in TMEM (row max; exp2 / row sum / bf16 P written to shared memory in the
-//                     K-major swizzled operand layout), online rescaling in registers: o = o * corr + O~ with O~ read back
-//                     from TMEM one block late, so the P V product of a block overlaps the softmax of the next.
+//   warps 0-3 / 4-7   two softmax groups taking alternate key blocks (g = block & 1), thread <-> query row (TMEM lane).
+//                     Default (ATC_ONEPASS): ONE pass over the S tile — the row's 128 scores sit in registers between the
+//                     maximum and the exponentials, bf16 P is written back over the S columns in TMEM (A operand of a TS-mode
+//                     tcgen05.mma), the group's running output accumulates in TMEM across its key blocks and is rescaled
+//                     there only when the row's reference maximum has to be raised (see the loop).  -DATC_ONEPASS=0 / 1
+//                     keeps the first form for this kernel: two passes (row max; exp2 / row sum / P), online rescaling
+//                     in registers with O~ read back from TMEM one block late.
 // The two groups' (m, l, o) states are merged through shared memory at the end (as the mma.sync kernel did).
 // fp32 scores, fp32 online softmax, bf16 P (as before).  Replaces the mma.sync kernel of csrc/s3_attn.cu (kept: CBX_ATTN_TC=0).
 // (A variant in which thread 0 of each softmax group issued its own loads and MMAs — no issuer warp, 255 registers — was
@@ -29,7 +32,7 @@ namespace {
 #define ATC_P_TMEM 1          // P travels to the second product through TMEM (in place over the S tile); 0: through shared memory
 #endif
 #ifndef ATC_ONEPASS
-#define ATC_ONEPASS 1         // bit (NG - 1): that instantiation reads each S tile from TMEM ONCE (see the softmax loop below)
+#define ATC_ONEPASS 3         // bit (NG - 1): that instantiation reads each S tile from TMEM ONCE (see the softmax loop below)
 #endif
 constexpr int TQ = 128, TK = 128, TD = 64;
 constexpr int TILE_B = TQ * TD * 2;                    // 16 KB: [128][64] bf16
