@@ -186,11 +186,23 @@ class BatchScheduler:
         self.queue.append(req)
 
     def _admit(self) -> None:
-        for s in range(self.engine.n_slots):
-            if self.slots[s] is None and self.queue:
-                req = self.queue.pop(0)
-                self.engine.admit(s, req)
-                self.slots[s] = req
+        """Queued requests into free slots, in queue order; a run of consecutive free slots is filled with ONE admit_many call
+        (prompts of equal length then share their prefill pass)."""
+        s, U = 0, self.engine.n_slots
+        while s < U and self.queue:
+            if self.slots[s] is not None:
+                s += 1
+                continue
+            e = s
+            while e < U and self.slots[e] is None and e - s < len(self.queue):
+                e += 1
+            reqs = [self.queue.pop(0) for _ in range(e - s)]
+            if len(reqs) == 1:
+                self.engine.admit(s, reqs[0])
+            else:
+                self.engine.admit_many(s, reqs)
+            self.slots[s:e] = reqs
+            s = e
 
     def run(self, on_finish=None) -> List[T3Request]:
         finished: List[T3Request] = []
