@@ -49,12 +49,20 @@ __global__ void __launch_bounds__(1024) k_rope_kv(float* __restrict__ qkv, int P
 }
 
 // Causal attention of the prompt over itself, fp32.  grid (ceil(P / 32), NH, B), 256 threads = 8 warps x 4 queries.
-// Keys are walked in tiles of 64 through shared memory (rows padded to 65 floats); a lane scores keys l and l + 32,
+// Keys are walked in tiles of 64 through shared memory (K rows padded to 65 floats); a lane scores keys l and l + 32 for
+// the warp's FOUR queries at once (every K / V value read from shared memory feeds four FMAs, the queries come as broadcast
+// float4 loads: the first form, one query at a time, was bound by its 1.5 shared-memory loads per FMA — 29 us per launch),
 // the warp keeps an online softmax per query, then lane l accumulates output dims l and l + 32.  Output: hi / lo planes.
+// Per (query, key) and per (query, dim) the sums run in the same order as before: same bits.
 constexpr int QT = 32, KT = 64, KPAD = 65;
+constexpr int ATTN_PF_SMEM = (KT * KPAD + KT * 64 + QT * 64 + 8 * KT * 4) * 4;      // 49 408 B: dynamic (just over the static limit)
 __global__ void __launch_bounds__(256) k_attn_prefill(const float* __restrict__ qkv, int P, __nv_bfloat16* __restrict__ out,
                                                       long long plane) {
-  __shared__ float Ks[KT * KPAD], Vs[KT * KPAD], Qs[QT * 64], Ps[8][KT];
+  extern __shared__ __align__(16) float attn_pf_sm[];
+  float* Ks = attn_pf_sm;                     // [KT][KPAD]
+  float* Vs = Ks + KT * KPAD;                 // [KT][64]   (read along a row: no padding needed)
+  float* Qs = Vs + KT * 64;                   // [QT][64]
+  float* Ps = Qs + QT * 64;                   // [8 warps][KT][4 queries]
   const int q0 = blockIdx.x * QT, head = blockIdx.y, b = blockIdx.z;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const float* base = qkv + (size_t)b * P * 3072 + head * 64;
@@ -66,50 +74,69 @@ __global__ void __launch_bounds__(256) k_attn_prefill(const float* __restrict__ 
 #pragma unroll
   for (int j = 0; j < 4; ++j) { m[j] = -INFINITY; l[j] = 0.f; o0[j] = 0.f; o1[j] = 0.f; }
   const int kmax = min(P, q0 + QT);        // causal: no key beyond the last query of the tile
+  const float* qw = Qs + warp * 4 * 64;
+  float* pw = Ps + warp * KT * 4;
   for (int k0 = 0; k0 < kmax; k0 += KT) {
     __syncthreads();
     for (int i = tid; i < KT * 64; i += 256) {
       const int kk = k0 + (i >> 6), d = i & 63;
       const bool ok = kk < kmax;
       Ks[(i >> 6) * KPAD + d] = ok ? base[(size_t)kk * 3072 + 1024 + d] : 0.f;
-      Vs[(i >> 6) * KPAD + d] = ok ? base[(size_t)kk * 3072 + 2048 + d] : 0.f;
+      Vs[(i >> 6) * 64 + d] = ok ? base[(size_t)kk * 3072 + 2048 + d] : 0.f;
     }
     __syncthreads();
+    if (q0 + warp * 4 >= P) continue;      // warp-uniform: none of the warp's queries exists (the barriers above were taken)
+    float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+    for (int d = 0; d < 64; d += 4) {
+      float4 q4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) q4[j] = *reinterpret_cast<const float4*>(qw + j * 64 + d);
+#pragma unroll
+      for (int dd = 0; dd < 4; ++dd) {
+        const float ka = Ks[lane * KPAD + d + dd], kb = Ks[(lane + 32) * KPAD + d + dd];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float qd = dd == 0 ? q4[j].x : dd == 1 ? q4[j].y : dd == 2 ? q4[j].z : q4[j].w;
+          s0[j] += qd * ka;
+          s1[j] += qd * kb;
+        }
+      }
+    }
+    float corr[4], p0[4], p1[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int qi = q0 + warp * 4 + j;
-      if (qi >= P) continue;               // warp-uniform
-      const float* qv = Qs + (warp * 4 + j) * 64;
-      float s0 = 0.f, s1 = 0.f;
-#pragma unroll 16
-      for (int d = 0; d < 64; ++d) {
-        const float qd = qv[d];
-        s0 += qd * Ks[lane * KPAD + d];
-        s1 += qd * Ks[(lane + 32) * KPAD + d];
-      }
-      if (k0 + lane > qi) s0 = -INFINITY;
-      if (k0 + lane + 32 > qi) s1 = -INFINITY;
-      float mx = fmaxf(s0, s1);
+      const int qi = q0 + warp * 4 + j;      // a query past the prompt: zeros in Qs, its state is never stored
+      if (k0 + lane > qi) s0[j] = -INFINITY;
+      if (k0 + lane + 32 > qi) s1[j] = -INFINITY;
+      float mx = fmaxf(s0[j], s1[j]);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
       const float mn = fmaxf(m[j], mx);    // finite: key k0 <= qi is always present in the first tile
-      const float corr = __expf(m[j] - mn);
-      const float p0 = __expf(s0 - mn), p1 = __expf(s1 - mn);
-      float ps = warp_sum(p0 + p1);
-      l[j] = l[j] * corr + ps;
+      corr[j] = __expf(m[j] - mn);
+      p0[j] = __expf(s0[j] - mn); p1[j] = __expf(s1[j] - mn);
+      const float ps = warp_sum(p0[j] + p1[j]);
+      l[j] = l[j] * corr[j] + ps;
       m[j] = mn;
-      __syncwarp();
-      Ps[warp][lane] = p0; Ps[warp][lane + 32] = p1;
-      __syncwarp();
-      float a0 = o0[j] * corr, a1 = o1[j] * corr;
-#pragma unroll 16
-      for (int kk = 0; kk < KT; ++kk) {
-        const float pk = Ps[warp][kk];
-        a0 += pk * Vs[kk * KPAD + lane];
-        a1 += pk * Vs[kk * KPAD + lane + 32];
-      }
-      o0[j] = a0; o1[j] = a1;
     }
+    __syncwarp();
+    *reinterpret_cast<float4*>(pw + lane * 4) = make_float4(p0[0], p0[1], p0[2], p0[3]);
+    *reinterpret_cast<float4*>(pw + (lane + 32) * 4) = make_float4(p1[0], p1[1], p1[2], p1[3]);
+    __syncwarp();
+    float a0[4], a1[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { a0[j] = o0[j] * corr[j]; a1[j] = o1[j] * corr[j]; }
+#pragma unroll 8
+    for (int kk = 0; kk < KT; ++kk) {
+      const float4 p4 = *reinterpret_cast<const float4*>(pw + kk * 4);
+      const float va = Vs[kk * 64 + lane], vb = Vs[kk * 64 + lane + 32];
+      a0[0] += p4.x * va; a1[0] += p4.x * vb;
+      a0[1] += p4.y * va; a1[1] += p4.y * vb;
+      a0[2] += p4.z * va; a1[2] += p4.z * vb;
+      a0[3] += p4.w * va; a1[3] += p4.w * vb;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { o0[j] = a0[j]; o1[j] = a1[j]; }
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -219,6 +246,8 @@ size_t t3_prefill_workspace_bytes_rows(size_t rows) {
 size_t t3_prefill_workspace_bytes(int max_pos) { return t3_prefill_workspace_bytes_rows(2 * (size_t)max_pos); }
 
 int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
+  static CbxPerDeviceOnce attn_once;
+  if (attn_once.first()) CBX_CUDA(cudaFuncSetAttribute(k_attn_prefill, cudaFuncAttributeMaxDynamicSharedMemorySize, ATTN_PF_SMEM));
   const int rows = a.B * a.P;
   const size_t maxrows = a.ws_rows > 0 ? (size_t)a.ws_rows : 2 * (size_t)a.max_pos;
   const bool many = a.nseq > 1;
@@ -267,7 +296,7 @@ int t3_prefill_gemm(const T3PrefillArgs& a, cudaStream_t st) {
                                                                static_cast<__nv_bfloat16*>(a.vcache), l, a.max_pos, kvs);
     if (l == a.al_layer && a.al_out)
       k_align_rows<<<a.al_rows0, 512, 0, st>>>(qkv, a.P, a.al_rows0, a.al_i, a.al_n, a.al_out, a.al_cap);
-    k_attn_prefill<<<dim3((a.P + QT - 1) / QT, NH, a.B), 256, 0, st>>>(qkv, a.P, hl, hl_plane);
+    k_attn_prefill<<<dim3((a.P + QT - 1) / QT, NH, a.B), 256, ATTN_PF_SMEM, st>>>(qkv, a.P, hl, hl_plane);
     e = GemmEpi{}; e.resid = x; e.ld_resid = H; e.out_f32 = x; e.ld_f32 = H;
     if (gemm_make_hilo_ex(&d, hl, H, hl_plane, wo, rows, H, H, H, e, ptl.o_t, ptl.o_s) || gemm_launch(d, st)) return CBX_ERR;
     k_rms_hilo<<<rows, 256, 0, st>>>(x, a.ln2 + (size_t)l * H, hl, hl_plane);
