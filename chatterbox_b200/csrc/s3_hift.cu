@@ -120,22 +120,44 @@ __global__ void k_stft(const float* __restrict__ s, float* __restrict__ out, int
     out[(size_t)m * 18 + 9 + k] = im;
   }
 }
-// source_downs[i]: Conv1d(18 -> C, k, stride, pad) on s_stft [frames][18]; w packed [18*k][C]
+// source_downs[i]: Conv1d(18 -> C, k, stride, pad) on s_stft [frames][18]; w packed [18*k][C].  A CTA computes SD_TT
+// consecutive output frames for all C channels (thread = channel): the input window is staged in shared memory once and every
+// weight read from global memory feeds SD_TT FMAs (one frame per CTA re-read the whole 18 k x C weight matrix per frame:
+// 120 us per launch at 512 mel frames).  Per output the taps are added in the same order as before (j outer, ci inner;
+// frames outside the signal contribute exact zeros), so the values are unchanged.
+constexpr int SD_TT = 8;
 __global__ void k_source_down(const float* __restrict__ sst, const float* __restrict__ w, const float* __restrict__ b,
                               const float* __restrict__ alpha, float* __restrict__ out, __nv_bfloat16* __restrict__ out_sn,
                               int frames, int T, int Cc, int k, int stride, int pad) {
-  const int t = blockIdx.x, co = threadIdx.x;
-  if (t >= T) return;
-  float acc = b[co];
-  for (int j = 0; j < k; ++j) {
-    const int src = t * stride + j - pad;
-    if (src < 0 || src >= frames) continue;
-    const float* sr = sst + (size_t)src * 18;
-#pragma unroll
-    for (int ci = 0; ci < 18; ++ci) acc += w[(size_t)(ci * k + j) * Cc + co] * sr[ci];
+  extern __shared__ float sd_win[];            // [(SD_TT - 1) stride + k][18]
+  const int t0 = blockIdx.x * SD_TT, co = threadIdx.x;
+  const int nrow = (SD_TT - 1) * stride + k, src0 = t0 * stride - pad;
+  for (int i = threadIdx.x; i < nrow * 18; i += blockDim.x) {
+    const int src = src0 + i / 18;
+    sd_win[i] = (src >= 0 && src < frames) ? sst[(size_t)src * 18 + i % 18] : 0.f;
   }
-  out[(size_t)t * Cc + co] = acc;
-  out_sn[(size_t)t * Cc + co] = __float2bfloat16_rn(snake_d(acc, alpha[co]));
+  __syncthreads();
+  float acc[SD_TT];
+  const float bias = b[co];
+#pragma unroll
+  for (int tt = 0; tt < SD_TT; ++tt) acc[tt] = bias;
+  for (int j = 0; j < k; ++j) {
+#pragma unroll
+    for (int ci = 0; ci < 18; ++ci) {
+      const float wv = w[(size_t)(ci * k + j) * Cc + co];
+#pragma unroll
+      for (int tt = 0; tt < SD_TT; ++tt) acc[tt] += wv * sd_win[(tt * stride + j) * 18 + ci];
+    }
+  }
+  const float al = alpha[co];
+#pragma unroll
+  for (int tt = 0; tt < SD_TT; ++tt) {
+    const int t = t0 + tt;
+    if (t < T) {
+      out[(size_t)t * Cc + co] = acc[tt];
+      out_sn[(size_t)t * Cc + co] = __float2bfloat16_rn(snake_d(acc[tt], al));
+    }
+  }
 }
 // x = pad(x_up) + si  (hifigan.py:423-429; reflect == 1 is ReflectionPad1d((1,0)) of the last stage);
 // also emits Snake(x) with the first activation of each of the three parallel ResBlocks
@@ -320,7 +342,7 @@ static int hift_decode(cbx_hift* h, const float* mel, int L, const float* s, int
       if (gemm_launch(op.g, st)) return CBX_ERR;
     } else if (op.kind == HK_SRC_DOWN) {
       const int i = op.a, Tt = op.b, Cc = ST_C[i];
-      k_source_down<<<Tt, Cc, 0, st>>>(h->sst, HF(h, F_SDW + i), HF(h, F_SDB + i), HF(h, F_RB + i * 12 + 6), h->si, h->xa[0],
+      k_source_down<<<(Tt + SD_TT - 1) / SD_TT, Cc, ((SD_TT - 1) * SD_S[i] + SD_K[i]) * 18 * sizeof(float), st>>>(h->sst, HF(h, F_SDW + i), HF(h, F_SDB + i), HF(h, F_RB + i * 12 + 6), h->si, h->xa[0],
                                        frames, Tt, Cc, SD_K[i], SD_S[i], SD_P[i]);
     } else if (op.kind == HK_FUSE) {
       const int i = op.a, Tt = op.b, Cc = ST_C[i];
